@@ -1,0 +1,156 @@
+// oracle/oracle_capi.cpp — TEST INFRASTRUCTURE.  C API (ctypes) over the CPU oracle.
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline/reference legs may load this.
+#include "orb_extract_oracle.hpp"
+#include "orb_match_oracle.hpp"
+#include <chrono>
+#include <thread>
+
+using namespace orbo;
+
+extern "C" {
+
+struct orc_ctx {
+    Extractor ex;
+    std::vector<KeyPoint> kps;
+    std::vector<uint8_t> desc;
+    orc_ctx(int nf, float sf, int nl, int ini, int mn) : ex(nf, sf, nl, ini, mn) {}
+};
+
+orc_ctx* orc_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, int tieMode, int legacyBlur)
+{
+    orc_ctx* c = new orc_ctx(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    c->ex.tieMode = tieMode; c->ex.legacyBlur = legacyBlur != 0;
+    return c;
+}
+void orc_destroy(orc_ctx* c) { delete c; }
+
+int orc_extract(orc_ctx* c, const uint8_t* img, int w, int h, long stride)
+{
+    c->ex.run(img, w, h, (size_t)stride, c->kps, c->desc);
+    return (int)c->kps.size();
+}
+int orc_get_result(orc_ctx* c, KeyPoint* kps, uint8_t* desc, int cap)
+{
+    int n = std::min<int>(cap, (int)c->kps.size());
+    if (n) { memcpy(kps, c->kps.data(), sizeof(KeyPoint) * n); memcpy(desc, c->desc.data(), (size_t)32 * n); }
+    return (int)c->kps.size();
+}
+void orc_tables(orc_ctx* c, float* scale, float* invScale, float* sigma2, float* invSigma2, int* perLevel, int* umax)
+{
+    for (int i = 0; i < c->ex.nlevels; i++) {
+        scale[i] = c->ex.mvScaleFactor[i]; invScale[i] = c->ex.mvInvScaleFactor[i];
+        sigma2[i] = c->ex.mvLevelSigma2[i]; invSigma2[i] = c->ex.mvInvLevelSigma2[i];
+        perLevel[i] = c->ex.mnFeaturesPerLevel[i];
+    }
+    for (int i = 0; i < 16; i++) umax[i] = c->ex.umax[i];
+}
+void orc_level_size(orc_ctx* c, int level, int* w, int* h) { *w = c->ex.pyramid[level].w; *h = c->ex.pyramid[level].h; }
+void orc_level_image(orc_ctx* c, int level, int blurred, uint8_t* dst)
+{
+    const Image& im = blurred ? c->ex.blurred[level] : c->ex.pyramid[level];
+    memcpy(dst, im.px.data(), im.px.size());
+}
+int orc_level_raw_count(orc_ctx* c, int level) { return (int)c->ex.dbg[level].toDistribute.size(); }
+void orc_level_raw(orc_ctx* c, int level, float* xyr)
+{
+    const auto& v = c->ex.dbg[level].toDistribute;
+    for (size_t i = 0; i < v.size(); i++) { xyr[3 * i] = v[i].x; xyr[3 * i + 1] = v[i].y; xyr[3 * i + 2] = v[i].response; }
+}
+int orc_level_kp_count(orc_ctx* c, int level) { return (int)c->ex.dbg[level].kps.size(); }
+void orc_level_kps(orc_ctx* c, int level, KeyPoint* out)
+{
+    const auto& v = c->ex.dbg[level].kps;
+    if (!v.empty()) memcpy(out, v.data(), v.size() * sizeof(KeyPoint));
+}
+
+// ---- primitives (for the cv2 pinning tests) ---------------------------------------------
+void orc_resize(const uint8_t* src, int sw, int sh, uint8_t* dst, int dw, int dh) { cvp::resize_linear_u8(src, sw, sh, sw, dst, dw, dh, dw); }
+void orc_blur(const uint8_t* src, int w, int h, uint8_t* dst, int legacy) { cvp::gaussian_blur7_u8(src, w, h, w, dst, w, legacy != 0); }
+int orc_fast(const uint8_t* img, int w, int h, int th, int* xys, int cap)
+{
+    std::vector<cvp::FastKp> v;
+    cvp::fast9_16_nms(img, w, h, w, th, v);
+    for (int i = 0; i < (int)v.size() && i < cap; i++) { xys[3 * i] = v[i].x; xys[3 * i + 1] = v[i].y; xys[3 * i + 2] = v[i].score; }
+    return (int)v.size();
+}
+void orc_fast_atan2(const float* y, const float* x, float* out, int n) { for (int i = 0; i < n; i++) out[i] = cvp::fast_atan2(y[i], x[i]); }
+
+// ---- matching -----------------------------------------------------------------------------
+void orc_distance_pairs(const uint8_t* a, const uint8_t* b, int n, int* out)
+{
+    for (int i = 0; i < n; i++) out[i] = DescriptorDistance(a + (size_t)i * 32, b + (size_t)i * 32);
+}
+void orc_bf_top2(const uint8_t* db, long M, const uint8_t* q, int nq, int32_t* d1, int64_t* i1, int32_t* d2, int nthreads)
+{
+    if (nthreads <= 1) { bf_top2(db, M, q, nq, d1, i1, d2); return; }
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; t++) {
+        int q0 = (int)((long)nq * t / nthreads), q1 = (int)((long)nq * (t + 1) / nthreads);
+        th.emplace_back([=]() { bf_top2(db, M, q + (size_t)q0 * 32, q1 - q0, d1 + q0, i1 + q0, d2 + q0); });
+    }
+    for (auto& t : th) t.join();
+}
+
+struct orc_frame { FrameGrid g; std::vector<KeyPoint> kps; std::vector<uint8_t> desc; };
+orc_frame* orc_frame_create(const KeyPoint* kps, const uint8_t* desc, int n, float minx, float miny, float maxx, float maxy)
+{
+    orc_frame* f = new orc_frame;
+    f->kps.assign(kps, kps + n); f->desc.assign(desc, desc + (size_t)n * 32);
+    f->g.build(f->kps.data(), f->desc.data(), n, minx, miny, maxx, maxy);
+    return f;
+}
+void orc_frame_destroy(orc_frame* f) { delete f; }
+int orc_features_in_area(orc_frame* f, float x, float y, float r, int minLevel, int maxLevel, int* out, int cap)
+{
+    std::vector<int> v;
+    f->g.GetFeaturesInArea(x, y, r, minLevel, maxLevel, v);
+    for (int i = 0; i < (int)v.size() && i < cap; i++) out[i] = v[i];
+    return (int)v.size();
+}
+// CSR candidate lists with distances, reference enumeration order (the contract of orbm_window_search)
+long orc_window_search(orc_frame* f, const ProjQuery* qs, int nq, int* offsets, int* idx, int* dist, long cap)
+{
+    std::vector<int> v; long total = 0;
+    for (int i = 0; i < nq; i++) {
+        offsets[i] = (int)total;
+        f->g.GetFeaturesInArea(qs[i].u, qs[i].v, qs[i].r, qs[i].minLevel, qs[i].maxLevel, v);
+        for (int c : v) {
+            if (total < cap) { idx[total] = c; dist[total] = DescriptorDistance(qs[i].desc, f->desc.data() + (size_t)c * 32); }
+            total++;
+        }
+    }
+    offsets[nq] = (int)total;
+    return total;
+}
+int orc_search_local_points(orc_frame* f, const float* mvuRight, const ProjQuery* qs, int nq, float nnratio, int* frameMP, int* frameMPObs)
+{
+    std::vector<ProjQuery> q(qs, qs + nq);
+    std::vector<int> mp(frameMP, frameMP + f->g.N), ob(frameMPObs, frameMPObs + f->g.N);
+    int n = SearchByProjection_LocalPoints(f->g, mvuRight, q, nnratio, mp, ob);
+    std::copy(mp.begin(), mp.end(), frameMP); std::copy(ob.begin(), ob.end(), frameMPObs);
+    return n;
+}
+int orc_search_last_frame(orc_frame* f, const float* mvuRight, const ProjQuery* qs, int nq, int checkOri, int* frameMP, int* frameMPObs)
+{
+    std::vector<ProjQuery> q(qs, qs + nq);
+    std::vector<int> mp(frameMP, frameMP + f->g.N), ob(frameMPObs, frameMPObs + f->g.N);
+    int n = SearchByProjection_LastFrame(f->g, mvuRight, q, checkOri != 0, mp, ob);
+    std::copy(mp.begin(), mp.end(), frameMP); std::copy(ob.begin(), ob.end(), frameMPObs);
+    return n;
+}
+int orc_search_for_initialization(orc_frame* f1, orc_frame* f2, float* prevMatchedXY, int* vnMatches12, int windowSize, float nnratio, int checkOri)
+{
+    std::vector<float> pm(prevMatchedXY, prevMatchedXY + 2 * f1->g.N);
+    std::vector<int> m12;
+    int n = SearchForInitialization(f1->g, f2->g, pm, m12, windowSize, nnratio, checkOri != 0);
+    std::copy(pm.begin(), pm.end(), prevMatchedXY); std::copy(m12.begin(), m12.end(), vnMatches12);
+    return n;
+}
+// Stereo: both extractors must have been run (pyramids are read from the contexts).
+void orc_stereo_match(orc_ctx* L, orc_ctx* R, float mbf, float mb, float* uRight, float* depth, int* bestIdxR, int* bestDist)
+{
+    ComputeStereoMatches(L->kps.data(), L->desc.data(), (int)L->kps.size(), R->kps.data(), R->desc.data(), (int)R->kps.size(),
+                         L->ex.pyramid, R->ex.pyramid, L->ex.mvScaleFactor, L->ex.mvInvScaleFactor, mbf, mb, uRight, depth, bestIdxR, bestDist);
+}
+
+}  // extern "C"

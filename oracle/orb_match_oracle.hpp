@@ -1,0 +1,366 @@
+// oracle/orb_match_oracle.hpp — TEST INFRASTRUCTURE (CPU oracle), never linked into the product.
+//
+// CPU restatement of the Hamming-matching half of the hot path.  Reference files followed:
+//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :474-590 :1506-1659 :1792-1854
+//   ORB-SLAM2/src/Frame.cpp       :241-257 :379-444 :540-748
+// ORBmatcher.cpp / Frame.cpp cannot be compiled here (they pull in KeyFrame/MapPoint/DBoW2/OpenCV/Eigen),
+// and the reference has no tests or golden vectors for them: parity for this half is "unpinned" beyond
+// DescriptorDistance (checked against numpy popcount) and hand-built known-answer cases in tests/.
+// MapPoint*/Frame bookkeeping is flattened to plain arrays; the control flow follows the reference.
+#pragma once
+#include <cstdint>
+#include <cmath>
+#include <climits>
+#include <vector>
+#include <algorithm>
+#include "orb_extract_oracle.hpp"
+
+namespace orbo {
+
+static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;          // ORBmatcher.cpp:37-39
+static const int FRAME_GRID_ROWS = 48, FRAME_GRID_COLS = 64;              // Frame.h:37-38
+
+// ORBmatcher::DescriptorDistance (ORBmatcher.cpp:1838-1854): SWAR popcount over 8 x 32 bit.
+static inline int DescriptorDistance(const uint8_t* a, const uint8_t* b)
+{
+    const int32_t* pa = (const int32_t*)a;
+    const int32_t* pb = (const int32_t*)b;
+    int dist = 0;
+    for (int i = 0; i < 8; i++, pa++, pb++) {
+        unsigned int v = *pa ^ *pb;
+        v = v - ((v >> 1) & 0x55555555);
+        v = (v & 0x33333333) + ((v >> 2) & 0x33333333);
+        dist += (((v + (v >> 4)) & 0xF0F0F0F) * 0x1010101) >> 24;
+    }
+    return dist;
+}
+
+// Frame grid (Frame.cpp:241-257, :434-444; constructor lines :115-116 for the inverse cell sizes)
+struct FrameGrid {
+    int N = 0;
+    const KeyPoint* kps = nullptr;        // undistorted keypoints (mvKeysUn)
+    const uint8_t* desc = nullptr;
+    float mnMinX, mnMinY, mnMaxX, mnMaxY, invW, invH;
+    std::vector<int> cells[FRAME_GRID_COLS][FRAME_GRID_ROWS];
+
+    void build(const KeyPoint* k, const uint8_t* d, int n, float minx, float miny, float maxx, float maxy)
+    {
+        kps = k; desc = d; N = n; mnMinX = minx; mnMinY = miny; mnMaxX = maxx; mnMaxY = maxy;
+        invW = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(mnMaxX - mnMinX);
+        invH = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(mnMaxY - mnMinY);
+        for (auto& col : cells) for (auto& c : col) c.clear();
+        for (int i = 0; i < N; i++) {
+            int px = (int)round((kps[i].x - mnMinX) * invW);
+            int py = (int)round((kps[i].y - mnMinY) * invH);
+            if (px < 0 || px >= FRAME_GRID_COLS || py < 0 || py >= FRAME_GRID_ROWS) continue;
+            cells[px][py].push_back(i);
+        }
+    }
+
+    // Frame::GetFeaturesInArea (Frame.cpp:379-432)
+    void GetFeaturesInArea(float x, float y, float r, int minLevel, int maxLevel, std::vector<int>& out) const
+    {
+        out.clear();
+        const int nMinCellX = std::max(0, (int)floor((x - mnMinX - r) * invW));
+        if (nMinCellX >= FRAME_GRID_COLS) return;
+        const int nMaxCellX = std::min((int)FRAME_GRID_COLS - 1, (int)ceil((x - mnMinX + r) * invW));
+        if (nMaxCellX < 0) return;
+        const int nMinCellY = std::max(0, (int)floor((y - mnMinY - r) * invH));
+        if (nMinCellY >= FRAME_GRID_ROWS) return;
+        const int nMaxCellY = std::min((int)FRAME_GRID_ROWS - 1, (int)ceil((y - mnMinY + r) * invH));
+        if (nMaxCellY < 0) return;
+        const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+        for (int ix = nMinCellX; ix <= nMaxCellX; ix++)
+            for (int iy = nMinCellY; iy <= nMaxCellY; iy++) {
+                const std::vector<int>& vCell = cells[ix][iy];
+                for (size_t j = 0; j < vCell.size(); j++) {
+                    const KeyPoint& kp = kps[vCell[j]];
+                    if (bCheckLevels) {
+                        if (kp.octave < minLevel) continue;
+                        if (maxLevel >= 0 && kp.octave > maxLevel) continue;
+                    }
+                    const float distx = kp.x - x, disty = kp.y - y;
+                    if (fabs(distx) < r && fabs(disty) < r) out.push_back(vCell[j]);
+                }
+            }
+    }
+};
+
+// ORBmatcher::ComputeThreeMaxima (ORBmatcher.cpp:1792-1833)
+static inline void ComputeThreeMaxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = (int)histo[i].size();
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+// Brute-force top-2 with the SearchByBoW update rule (ORBmatcher.cpp:249-275): strict '<' updates,
+// first index wins ties, second may equal best.  
+static inline void bf_top2(const uint8_t* db, long M, const uint8_t* q, int nq, int32_t* d1, int64_t* i1, int32_t* d2)
+{
+    for (int i = 0; i < nq; i++) {
+        int b1 = 256, b2 = 256; long bi = -1;
+        for (long j = 0; j < M; j++) {
+            int d = DescriptorDistance(q + (size_t)i * 32, db + (size_t)j * 32);
+            if (d < b1) { b2 = b1; b1 = d; bi = j; }
+            else if (d < b2) b2 = d;
+        }
+        d1[i] = b1; i1[i] = bi; d2[i] = b2;
+    }
+}
+
+// One projected query of the SearchByProjection family.
+struct ProjQuery {
+    float u, v, r;            // window centre and (already scaled) radius
+    int minLevel, maxLevel;   // as passed to GetFeaturesInArea
+    float uR;                 // projected right coordinate (a10: mTrackProjXR, a11: u - mbf*invzc)
+    float maxErrR;            // stereo gate: skip candidate if |uR - mvuRight[idx]| > maxErrR
+    uint8_t desc[32];
+    int id;                   // caller's identifier (map point index / last-frame index)
+    int hasObs;               // pMP->Observations()>0 once assigned
+    float angle;              // LastFrame.mvKeysUn[i].angle for the rotation histogram
+};
+
+// SearchByProjection(Frame&, vector<MapPoint*>&, th) (ORBmatcher.cpp:63-155).
+// frameMP[idx] = id of the assigned map point or -1; frameMPObs[idx] = its Observations()>0.
+static inline int SearchByProjection_LocalPoints(const FrameGrid& F, const float* mvuRight, const std::vector<ProjQuery>& qs,
+                                                 float nnratio, std::vector<int>& frameMP, std::vector<int>& frameMPObs)
+{
+    int nmatches = 0;
+    std::vector<int> vIndices;
+    for (size_t iMP = 0; iMP < qs.size(); iMP++) {
+        const ProjQuery& q = qs[iMP];
+        F.GetFeaturesInArea(q.u, q.v, q.r, q.minLevel, q.maxLevel, vIndices);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int idx : vIndices) {
+            if (frameMP[idx] >= 0 && frameMPObs[idx] > 0) continue;
+            if (mvuRight && mvuRight[idx] > 0) {
+                const float er = fabs(q.uR - mvuRight[idx]);
+                if (er > q.maxErrR) continue;
+            }
+            const int dist = DescriptorDistance(q.desc, F.desc + (size_t)idx * 32);
+            if (dist < bestDist) {
+                bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel;
+                bestLevel = F.kps[idx].octave; bestIdx = idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = F.kps[idx].octave; bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            frameMP[bestIdx] = q.id; frameMPObs[bestIdx] = q.hasObs;
+            nmatches++;
+        }
+    }
+    return nmatches;
+}
+
+// SearchByProjection(Frame& Current, const Frame& Last, th, bMono) (ORBmatcher.cpp:1506-1659), after the
+// projection step (queries carry u, v, radius and the octave window chosen at :1570-1575).
+static inline int SearchByProjection_LastFrame(const FrameGrid& F, const float* mvuRight, const std::vector<ProjQuery>& qs,
+                                               bool checkOri, std::vector<int>& frameMP, std::vector<int>& frameMPObs)
+{
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    std::vector<int> vIndices2;
+    for (size_t i = 0; i < qs.size(); i++) {
+        const ProjQuery& q = qs[i];
+        F.GetFeaturesInArea(q.u, q.v, q.r, q.minLevel, q.maxLevel, vIndices2);
+        if (vIndices2.empty()) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            if (frameMP[i2] >= 0 && frameMPObs[i2] > 0) continue;
+            if (mvuRight && mvuRight[i2] > 0) {
+                const float er = fabs(q.uR - mvuRight[i2]);
+                if (er > q.maxErrR) continue;
+            }
+            const int dist = DescriptorDistance(q.desc, F.desc + (size_t)i2 * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            frameMP[bestIdx2] = q.id; frameMPObs[bestIdx2] = q.hasObs;
+            nmatches++;
+            if (checkOri) {
+                float rot = q.angle - F.kps[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (size_t j = 0; j < rotHist[i].size(); j++) { frameMP[rotHist[i][j]] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
+// ORBmatcher::SearchForInitialization (ORBmatcher.cpp:474-590)
+static inline int SearchForInitialization(const FrameGrid& F1, const FrameGrid& F2, std::vector<float>& prevMatchedXY,
+                                          std::vector<int>& vnMatches12, int windowSize, float nnratio, bool checkOri)
+{
+    int nmatches = 0;
+    vnMatches12.assign(F1.N, -1);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    std::vector<int> vMatchedDistance(F2.N, INT_MAX), vnMatches21(F2.N, -1);
+    std::vector<int> vIndices2;
+    for (int i1 = 0; i1 < F1.N; i1++) {
+        const KeyPoint& kp1 = F1.kps[i1];
+        int level1 = kp1.octave;
+        if (level1 > 0) continue;
+        F2.GetFeaturesInArea(prevMatchedXY[2 * i1], prevMatchedXY[2 * i1 + 1], (float)windowSize, level1, level1, vIndices2);
+        if (vIndices2.empty()) continue;
+        const uint8_t* d1 = F1.desc + (size_t)i1 * 32;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            int dist = DescriptorDistance(d1, F2.desc + (size_t)i2 * 32);
+            if (vMatchedDistance[i2] <= dist) continue;
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist <= TH_LOW) {
+            if (bestDist < (float)bestDist2 * nnratio) {
+                if (vnMatches21[bestIdx2] >= 0) { vnMatches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+                vnMatches12[i1] = bestIdx2; vnMatches21[bestIdx2] = i1; vMatchedDistance[bestIdx2] = bestDist;
+                nmatches++;
+                if (checkOri) {
+                    float rot = F1.kps[i1].angle - F2.kps[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); j++) {
+                int idx1 = rotHist[i][j];
+                if (vnMatches12[idx1] >= 0) { vnMatches12[idx1] = -1; nmatches--; }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < F1.N; i1++)
+        if (vnMatches12[i1] >= 0) {
+            prevMatchedXY[2 * i1] = F2.kps[vnMatches12[i1]].x;
+            prevMatchedXY[2 * i1 + 1] = F2.kps[vnMatches12[i1]].y;
+        }
+    return nmatches;
+}
+
+// Frame::ComputeStereoMatches (Frame.cpp:540-748).  mb is whatever the member holds at the call
+// (0 in the stereo constructor => maxD = +inf).
+static inline void ComputeStereoMatches(const KeyPoint* keysL, const uint8_t* descL, int N,
+                                        const KeyPoint* keysR, const uint8_t* descR, int Nr,
+                                        const std::vector<Image>& pyrL, const std::vector<Image>& pyrR,
+                                        const std::vector<float>& scaleFactors, const std::vector<float>& invScaleFactors,
+                                        float mbf, float mb, float* mvuRight, float* mvDepth,
+                                        int* dbgBestIdxR = nullptr, int* dbgBestDist = nullptr)
+{
+    for (int i = 0; i < N; i++) { mvuRight[i] = -1.0f; mvDepth[i] = -1.0f; if (dbgBestIdxR) { dbgBestIdxR[i] = -1; dbgBestDist[i] = -1; } }
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    const int nRows = pyrL[0].h;
+    std::vector<std::vector<int>> vRowIndices(nRows);
+    for (int iR = 0; iR < Nr; iR++) {
+        const KeyPoint& kp = keysR[iR];
+        const float kpY = kp.y;
+        const float r = 2.0f * scaleFactors[kp.octave];
+        const int maxr = (int)ceil(kpY + r), minr = (int)floor(kpY - r);
+        for (int yi = minr; yi <= maxr; yi++)
+            if (yi >= 0 && yi < nRows) vRowIndices[yi].push_back(iR);   // guard: the reference indexes unchecked
+    }
+    const float minZ = mb, minD = 0, maxD = mbf / minZ;
+    std::vector<std::pair<int, int>> vDistIdx;
+    for (int iL = 0; iL < N; iL++) {
+        const KeyPoint& kpL = keysL[iL];
+        const int levelL = kpL.octave;
+        const float vL = kpL.y, uL = kpL.x;
+        const std::vector<int>& vCandidates = vRowIndices[(int)vL];
+        if (vCandidates.empty()) continue;
+        const float minU = uL - maxD, maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH; int bestIdxR = 0;
+        const uint8_t* dL = descL + (size_t)iL * 32;
+        for (size_t iC = 0; iC < vCandidates.size(); iC++) {
+            const int iR = vCandidates[iC];
+            const KeyPoint& kpR = keysR[iR];
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            const float uR = kpR.x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = DescriptorDistance(dL, descR + (size_t)iR * 32);
+                if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+            }
+        }
+        if (bestDist < thOrbDist) {
+            if (dbgBestIdxR) { dbgBestIdxR[iL] = bestIdxR; dbgBestDist[iL] = bestDist; }
+            const float uR0 = keysR[bestIdxR].x;
+            const float scaleFactor = invScaleFactors[kpL.octave];
+            const float scaleduL = round(kpL.x * scaleFactor);
+            const float scaledvL = round(kpL.y * scaleFactor);
+            const float scaleduR0 = round(uR0 * scaleFactor);
+            const int w = 5;
+            const Image& imL = pyrL[kpL.octave];
+            const Image& imR = pyrR[kpL.octave];
+            const int cxL = (int)scaleduL, cyL = (int)scaledvL;
+            int sadBest = INT_MAX, bestincR = 0;
+            const int L = 5;
+            std::vector<float> vDists(2 * L + 1);
+            const float iniu = scaleduR0 + L - w, endu = scaleduR0 + L + w + 1;
+            if (iniu < 0 || endu >= imR.w) continue;
+            for (int incR = -L; incR <= +L; incR++) {
+                const int cxR = (int)scaleduR0 + incR;
+                const float cL = (float)imL.row(cyL)[cxL], cR = (float)imR.row(cyL)[cxR];
+                double acc = 0;   // cv::norm(IL, IR, NORM_L1) on CV_32F windows (integers: exact)
+                for (int dy = -w; dy <= w; dy++)
+                    for (int dx = -w; dx <= w; dx++) {
+                        float a = (float)imL.row(cyL + dy)[cxL + dx] - cL;
+                        float b = (float)imR.row(cyL + dy)[cxR + dx] - cR;
+                        acc += fabs(a - b);
+                    }
+                float dist = (float)acc;
+                if (dist < sadBest) { sadBest = (int)dist; bestincR = incR; }
+                vDists[L + incR] = dist;
+            }
+            if (bestincR == -L || bestincR == L) continue;
+            const float dist1 = vDists[L + bestincR - 1], dist2 = vDists[L + bestincR], dist3 = vDists[L + bestincR + 1];
+            const float deltaR = (dist1 - dist3) / (2.0f * (dist1 + dist3 - 2.0f * dist2));
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = scaleFactors[kpL.octave] * ((float)scaleduR0 + (float)bestincR + deltaR);
+            float disparity = (uL - bestuR);
+            if (disparity >= minD && disparity < maxD) {
+                if (disparity <= 0) { disparity = (float)0.01; bestuR = (float)(uL - 0.01); }   // double literals as in :716-717
+                mvDepth[iL] = mbf / disparity;
+                mvuRight[iL] = bestuR;
+                vDistIdx.push_back(std::pair<int, int>(sadBest, iL));
+            }
+        }
+    }
+    if (vDistIdx.empty()) return;   // the reference indexes vDistIdx[0] unchecked here
+    std::sort(vDistIdx.begin(), vDistIdx.end());
+    const float median = (float)vDistIdx[vDistIdx.size() / 2].first;
+    const float thDist = 1.5f * 1.4f * median;
+    for (int i = (int)vDistIdx.size() - 1; i >= 0; i--) {
+        if (vDistIdx[i].first < thDist) break;
+        mvuRight[vDistIdx[i].second] = -1;
+        mvDepth[vDistIdx[i].second] = -1;
+    }
+}
+
+}  // namespace orbo

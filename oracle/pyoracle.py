@@ -1,0 +1,305 @@
+"""ctypes binding of the CPU oracle (oracle/liborb_oracle.so) and of oracle/_ref/liborb_ref.so.
+
+TEST INFRASTRUCTURE: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this module.  The product (orb-slam2-annotation_b200/) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("r", "<f4"), ("minLevel", "<i4"), ("maxLevel", "<i4"),
+                        ("uR", "<f4"), ("maxErrR", "<f4"), ("desc", "u1", (32,)), ("id", "<i4"),
+                        ("hasObs", "<i4"), ("angle", "<f4")])
+assert QUERY_DTYPE.itemsize == 72
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liborb_oracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "cv_prims.hpp", "orb_extract_oracle.hpp",
+                                              "orb_match_oracle.hpp", "orb_pattern.inc", "Makefile")]
+    stale = force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
+    if stale:
+        subprocess.run(["make", "-C", _HERE, "liborb_oracle.so"], check=True, capture_output=True)
+    if os.path.isdir("/root/reference/ORB-SLAM2/src"):
+        ref = os.path.join(_HERE, "_ref", "liborb_ref.so")
+        rsrcs = [os.path.join(_HERE, "ref_capi.cpp")] + [os.path.join(dp, f) for dp, _, fs in os.walk(os.path.join(_HERE, "cvshim")) for f in fs]
+        rsrcs = [s for s in rsrcs if os.path.exists(s)]
+        if rsrcs and (force or not os.path.exists(ref) or any(os.path.getmtime(s) > os.path.getmtime(ref) for s in rsrcs)):
+            subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
+    return so
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        L = _lib
+        L.orc_create.restype = C.c_void_p
+        L.orc_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.orc_destroy.argtypes = [C.c_void_p]
+        L.orc_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_long]
+        L.orc_get_result.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+        L.orc_level_size.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_level_image.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orc_level_raw_count.argtypes = [C.c_void_p, C.c_int]
+        L.orc_level_raw.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_level_kp_count.argtypes = [C.c_void_p, C.c_int]
+        L.orc_level_kps.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_resize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        L.orc_blur.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_fast.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_fast_atan2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_distance_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_bf_top2.argtypes = [C.c_void_p, C.c_long, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_frame_create.restype = C.c_void_p
+        L.orc_frame_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
+        L.orc_frame_destroy.argtypes = [C.c_void_p]
+        L.orc_features_in_area.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_window_search.restype = C.c_long
+        L.orc_window_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_long]
+        L.orc_search_local_points.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_search_last_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_search_for_initialization.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int]
+        L.orc_stereo_match.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float] + [C.c_void_p] * 4
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class OracleExtractor:
+    """CPU oracle of ORBextractor (reference ORBextractor.cpp); keeps every intermediate stage."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7, tie_mode=0, legacy_blur=False):
+        self.L = lib()
+        self.nlevels = nlevels
+        self.h = self.L.orc_create(nfeatures, scale, nlevels, ini_th, min_th, tie_mode, int(legacy_blur))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_destroy(self.h)
+            self.h = None
+
+    def extract(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        n = self.L.orc_extract(self.h, _p(img), w, h, w)
+        kps = np.zeros(n, KP_DTYPE)
+        desc = np.zeros((n, 32), np.uint8)
+        if n:
+            self.L.orc_get_result(self.h, _p(kps), _p(desc), n)
+        return kps, desc
+
+    def tables(self):
+        n = self.nlevels
+        sc, isc, s2, is2 = (np.zeros(n, np.float32) for _ in range(4))
+        per = np.zeros(n, np.int32)
+        um = np.zeros(16, np.int32)
+        self.L.orc_tables(self.h, _p(sc), _p(isc), _p(s2), _p(is2), _p(per), _p(um))
+        return dict(scale=sc, inv_scale=isc, sigma2=s2, inv_sigma2=is2, per_level=per, umax=um)
+
+    def level_size(self, level):
+        w, h = C.c_int(), C.c_int()
+        self.L.orc_level_size(self.h, level, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def level_image(self, level, blurred=False):
+        w, h = self.level_size(level)
+        out = np.zeros((h, w), np.uint8)
+        self.L.orc_level_image(self.h, level, int(blurred), _p(out))
+        return out
+
+    def level_raw(self, level):
+        n = self.L.orc_level_raw_count(self.h, level)
+        out = np.zeros((n, 3), np.float32)
+        if n:
+            self.L.orc_level_raw(self.h, level, _p(out))
+        return out
+
+    def level_kps(self, level):
+        n = self.L.orc_level_kp_count(self.h, level)
+        out = np.zeros(n, KP_DTYPE)
+        if n:
+            self.L.orc_level_kps(self.h, level, _p(out))
+        return out
+
+
+def resize(src, dw, dh):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros((dh, dw), np.uint8)
+    lib().orc_resize(_p(src), src.shape[1], src.shape[0], _p(dst), dw, dh)
+    return dst
+
+
+def blur(src, legacy=False):
+    src = np.ascontiguousarray(src, np.uint8)
+    dst = np.zeros_like(src)
+    lib().orc_blur(_p(src), src.shape[1], src.shape[0], _p(dst), int(legacy))
+    return dst
+
+
+def fast(img, th):
+    img = np.ascontiguousarray(img, np.uint8)
+    cap = img.size
+    out = np.zeros((cap, 3), np.int32)
+    n = lib().orc_fast(_p(img), img.shape[1], img.shape[0], th, _p(out), cap)
+    return out[:n]
+
+
+def fast_atan2(y, x):
+    y = np.ascontiguousarray(y, np.float32)
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros_like(y)
+    lib().orc_fast_atan2(_p(y), _p(x), _p(out), y.size)
+    return out
+
+
+def distance_pairs(a, b):
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    out = np.zeros(a.shape[0], np.int32)
+    lib().orc_distance_pairs(_p(a), _p(b), a.shape[0], _p(out))
+    return out
+
+
+def bf_top2(db, q, nthreads=1):
+    db = np.ascontiguousarray(db, np.uint8)
+    q = np.ascontiguousarray(q, np.uint8)
+    nq = q.shape[0]
+    d1 = np.zeros(nq, np.int32)
+    i1 = np.zeros(nq, np.int64)
+    d2 = np.zeros(nq, np.int32)
+    lib().orc_bf_top2(_p(db), db.shape[0], _p(q), nq, _p(d1), _p(i1), _p(d2), nthreads)
+    return d1, i1, d2
+
+
+class OracleFrame:
+    """Frame grid + GetFeaturesInArea + the Search* loops on flattened arrays (oracle)."""
+
+    def __init__(self, kps, desc, bounds):
+        self.L = lib()
+        self.kps = np.ascontiguousarray(kps, KP_DTYPE)
+        self.desc = np.ascontiguousarray(desc, np.uint8)
+        self.n = len(self.kps)
+        self.h = self.L.orc_frame_create(_p(self.kps), _p(self.desc), self.n, *[float(b) for b in bounds])
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_frame_destroy(self.h)
+            self.h = None
+
+    def features_in_area(self, x, y, r, min_level=-1, max_level=-1):
+        out = np.zeros(max(self.n, 1), np.int32)
+        n = self.L.orc_features_in_area(self.h, x, y, r, min_level, max_level, _p(out), self.n)
+        return out[:n].copy()
+
+    def window_search(self, queries):
+        q = np.ascontiguousarray(queries, QUERY_DTYPE)
+        nq = len(q)
+        offs = np.zeros(nq + 1, np.int32)
+        total = self.L.orc_window_search(self.h, _p(q), nq, _p(offs), None, None, 0)
+        idx = np.zeros(max(total, 1), np.int32)
+        dist = np.zeros(max(total, 1), np.int32)
+        self.L.orc_window_search(self.h, _p(q), nq, _p(offs), _p(idx), _p(dist), total)
+        return offs, idx[:total], dist[:total]
+
+    def search_local_points(self, queries, nnratio, frame_mp, frame_obs, uright=None):
+        q = np.ascontiguousarray(queries, QUERY_DTYPE)
+        mp = np.ascontiguousarray(frame_mp, np.int32).copy()
+        ob = np.ascontiguousarray(frame_obs, np.int32).copy()
+        ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+        n = self.L.orc_search_local_points(self.h, _p(ur), _p(q), len(q), nnratio, _p(mp), _p(ob))
+        return n, mp, ob
+
+    def search_last_frame(self, queries, check_ori, frame_mp, frame_obs, uright=None):
+        q = np.ascontiguousarray(queries, QUERY_DTYPE)
+        mp = np.ascontiguousarray(frame_mp, np.int32).copy()
+        ob = np.ascontiguousarray(frame_obs, np.int32).copy()
+        ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+        n = self.L.orc_search_last_frame(self.h, _p(ur), _p(q), len(q), int(check_ori), _p(mp), _p(ob))
+        return n, mp, ob
+
+
+def search_for_initialization(f1, f2, prev_matched, window=100, nnratio=0.9, check_ori=True):
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.zeros(f1.n, np.int32)
+    n = lib().orc_search_for_initialization(f1.h, f2.h, _p(pm), _p(m12), window, nnratio, int(check_ori))
+    return n, m12, pm
+
+
+def stereo_match(exL, exR, mbf, mb=0.0):
+    """exL/exR: OracleExtractor objects after extract()."""
+    n = lib().orc_get_result(exL.h, None, None, 0)
+    ur = np.zeros(n, np.float32)
+    dp = np.zeros(n, np.float32)
+    bi = np.zeros(n, np.int32)
+    bd = np.zeros(n, np.int32)
+    lib().orc_stereo_match(exL.h, exR.h, mbf, mb, _p(ur), _p(dp), _p(bi), _p(bd))
+    return ur, dp, bi, bd
+
+
+# ------------------------------------------------------------------------------------------
+# oracle/_ref: the reference's own ORBextractor.cpp (unmodified) over the mini-OpenCV shim.
+# ------------------------------------------------------------------------------------------
+_ref = None
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        build()
+        path = os.path.join(_HERE, "_ref", "liborb_ref.so")
+        if not os.path.exists(path):
+            return None
+        _ref = C.CDLL(path)
+        _ref.ref_create.restype = C.c_void_p
+        _ref.ref_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        _ref.ref_destroy.argtypes = [C.c_void_p]
+        _ref.ref_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_long, C.c_void_p, C.c_void_p, C.c_int]
+        _ref.ref_level_size.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        _ref.ref_level_image.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    return _ref
+
+
+class RefExtractor:
+    """ORB_SLAM2::ORBextractor compiled from /root/reference (oracle/_ref)."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.L = ref_lib()
+        if self.L is None:
+            raise RuntimeError("oracle/_ref/liborb_ref.so not built")
+        self.nlevels = nlevels
+        self.h = self.L.ref_create(nfeatures, scale, nlevels, ini_th, min_th)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_destroy(self.h)
+            self.h = None
+
+    def extract(self, img, cap=None):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        cap = cap or 200000
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = self.L.ref_extract(self.h, _p(img), w, h, w, _p(kps), _p(desc), cap)
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level_image(self, level):
+        w, h = C.c_int(), C.c_int()
+        self.L.ref_level_size(self.h, level, C.byref(w), C.byref(h))
+        out = np.zeros((h.value, w.value), np.uint8)
+        self.L.ref_level_image(self.h, level, _p(out))
+        return out
