@@ -1,0 +1,192 @@
+/* orbb200.h — C ABI of liborbb200.so: the B200-native (sm_100a CUDA) replacement for the ORB front-end hot
+ * path of ORB-SLAM2.  The reference has no FFI; its boundary is the C++ class surface, so each entry point
+ * cites the reference interface it replaces (paths relative to /root/reference/ORB-SLAM2/).
+ *
+ * Conventions: every function returns ORBB_OK (0) or a negative error code and never throws/aborts;
+ * the caller allocates outputs and passes capacities; one orbx_handle owns one CUDA stream plus scratch,
+ * calls on different handles are thread-safe, calls on one handle are serialised by the caller (the
+ * reference's ORBextractor is likewise not re-entrant per instance: operator() mutates mvImagePyramid).
+ * Pointers named *_host are host memory; pointers named *_dev are device memory on the handle's device.
+ * There is NO CPU fallback: without a CUDA device every compute entry point returns ORBB_E_CUDA.
+ */
+#ifndef ORBB200_H
+#define ORBB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    ORBB_OK = 0,
+    ORBB_E_INVALID = -1,     /* bad argument (null pointer, nlevels out of range, iniTh < minTh, ...) */
+    ORBB_E_CUDA = -2,        /* CUDA runtime error or no device; see orbb200_last_cuda_error() */
+    ORBB_E_CAPACITY = -3,    /* an output or internal buffer was too small; *n_out holds the needed count */
+    ORBB_E_BAD_SHAPE = -4,   /* image larger than the handle's max_w/max_h, or too small */
+    ORBB_E_NOMEM = -5,
+    ORBB_E_STATE = -6        /* call order violated (e.g. stereo match before both extractions) */
+};
+
+#define ORBB_MAX_LEVELS 16
+#define ORBB_DESC_BYTES 32
+
+/* Binary layout of cv::KeyPoint (28 bytes): what ORBextractor::operator() fills (ORBextractor.cpp:1084-1116). */
+typedef struct orbx_keypoint {
+    float x, y;        /* pt, level-0 pixel units (level coords * mvScaleFactor[octave]) */
+    float size;        /* (float)(int)(31 * mvScaleFactor[octave])                        */
+    float angle;       /* degrees in [0,360), IC_Angle / fastAtan2                        */
+    float response;    /* FAST corner score                                               */
+    int32_t octave;
+    int32_t class_id;  /* always -1 */
+} orbx_keypoint;
+
+/* Mirrors ORBextractor::ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+ * (include/ORBextractor.h:51-52, src/ORBextractor.cpp:412-472) plus the sizing a device handle needs. */
+typedef struct orbx_config {
+    int32_t nfeatures;
+    float scale_factor;
+    int32_t nlevels;         /* 1..ORBB_MAX_LEVELS */
+    int32_t ini_th_fast;
+    int32_t min_th_fast;     /* must be <= ini_th_fast */
+    int32_t max_width;       /* largest image this handle will see */
+    int32_t max_height;
+    int32_t max_batch;       /* frames processed per orbx_extract_batch call (>=1) */
+    int32_t device;          /* CUDA device ordinal */
+    int32_t blur_legacy;     /* 0: OpenCV>=3.4 fixed-point kernel (graded); 1: OpenCV<=3.3 kernel {18,34,49,55,49,34,18} */
+} orbx_config;
+
+typedef struct orbx_handle orbx_handle;
+
+/* -- extractor ------------------------------------------------------------------------------------- */
+
+/* ORBextractor constructor (ORBextractor.cpp:412-472): scale tables, per-level quotas, pattern, umax. */
+int orbx_create(const orbx_config* cfg, orbx_handle** out);
+int orbx_destroy(orbx_handle* h);
+
+/* Getters of ORBextractor.h:63-83 (GetScaleFactors, GetInverseScaleFactors, GetScaleSigmaSquares,
+ * GetInverseScaleSigmaSquares) and the protected mnFeaturesPerLevel / umax tables (for tests).
+ * Any output pointer may be NULL.  Arrays hold nlevels entries (umax: 16). */
+int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                    int32_t* features_per_level, int32_t* umax);
+
+/* ORBextractor::operator()(image, mask [ignored], keypoints, descriptors) (ORBextractor.cpp:1053-1117),
+ * host image in, host results out (includes H2D/D2H copies; this is the call Frame::ExtractORB makes,
+ * Frame.cpp:259-265).  img_host: 8-bit single channel, stride_bytes between rows.
+ * On success *n_out = number of keypoints (may exceed nfeatures slightly); if *n_out > capacity only the first
+ * `capacity` are written and ORBB_E_CAPACITY is returned.  Empty image (w or h == 0) => *n_out = 0, ORBB_OK. */
+int orbx_extract(orbx_handle* h, const uint8_t* img_host, int w, int h_, size_t stride_bytes,
+                 orbx_keypoint* kps_host, uint8_t* desc_host, int capacity, int* n_out);
+
+/* Same path with inputs already resident in HBM and results left in HBM: `nframes` (<= max_batch) images of
+ * identical shape at imgs_dev + f*frame_stride_bytes.  Results for frame f: kps_dev + f*capacity keypoints,
+ * desc_dev + f*capacity*32 bytes, counts_dev[f].  Asynchronous on the handle's stream. */
+int orbx_extract_batch_device(orbx_handle* h, const uint8_t* imgs_dev, int nframes, int w, int h_,
+                              size_t stride_bytes, size_t frame_stride_bytes,
+                              orbx_keypoint* kps_dev, uint8_t* desc_dev, int32_t* counts_dev, int capacity);
+
+/* Host-buffer batch: pinned or pageable host frames in, host results out (one H2D copy per batch, one D2H).
+ * counts_host[f] receives each frame's keypoint count. */
+int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int h_,
+                       size_t stride_bytes, size_t frame_stride_bytes,
+                       orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity);
+
+/* Blocks until the handle's stream is idle; returns the first asynchronous error, and ORBB_E_CAPACITY if an
+ * internal candidate buffer overflowed during the last extraction. */
+int orbx_sync(orbx_handle* h);
+/* cudaStream_t of the handle (for event timing by the caller). */
+void* orbx_stream(orbx_handle* h);
+
+/* Backs the public member ORBextractor::mvImagePyramid (ORBextractor.h:85; read by Frame.cpp:547,657-676):
+ * copies level `level` of frame `frame` of the last extraction to dst_host (tight rows of *w bytes when
+ * dst_stride == 0).  dst_host may be NULL to query the size only. */
+int orbx_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst_host, size_t dst_stride, int* w, int* h_);
+
+/* Parity-test access to intermediate stages of the last extraction (frame `frame`, level `level`). */
+enum {
+    ORBX_STAGE_BLUR = 1,      /* uint8 blurred level (GaussianBlur 7x7 s=2, ORBextractor.cpp:1097-1098), tight rows  */
+    ORBX_STAGE_FASTKPS = 2,   /* int32 triples (x, y, response) in level coords relative to minBorder: the list
+                                 handed to DistributeOctTree (ORBextractor.cpp:829-834); order unspecified        */
+    ORBX_STAGE_LEVELKPS = 3   /* orbx_keypoint records after octree + angle in level coordinates (:847-862), in
+                                 reference order                                                               */
+};
+int orbx_debug_stage(orbx_handle* h, int frame, int level, int stage, void* dst_host, size_t dst_bytes, size_t* bytes_out);
+
+/* -- matcher ---------------------------------------------------------------------------------------- */
+
+/* ORBmatcher::DescriptorDistance (ORBmatcher.cpp:1838-1854; twin DBoW2/FORB.cpp:82-102) for n pairs
+ * a[i], b[i] of 32-byte descriptors (host pointers). */
+int orbm_distance_pairs(const uint8_t* a_host, const uint8_t* b_host, int n, int32_t* out_host, int device);
+
+/* A Frame's matching state on the device: undistorted keypoints (mvKeysUn), descriptors (mDescriptors) and the
+ * 64x48 bucket grid of Frame::AssignFeaturesToGrid / PosInGrid (Frame.cpp:241-257, :434-444), built on device
+ * in insertion order.  Bounds are Frame::mnMinX/mnMinY/mnMaxX/mnMaxY. */
+typedef struct orbm_frame orbm_frame;
+int orbm_frame_create(orbm_frame** out, const orbx_keypoint* kps_un_host, const uint8_t* desc_host, int n,
+                      float min_x, float min_y, float max_x, float max_y, int device);
+int orbm_frame_destroy(orbm_frame* f);
+
+/* One projected query: what every SearchByProjection variant hands to GetFeaturesInArea + DescriptorDistance
+ * (ORBmatcher.cpp:63-155, :352-472, :1506-1659, :1661-1789; SearchForInitialization :474-590). */
+typedef struct orbm_query {
+    float u, v;             /* window centre                                                        */
+    float r;                /* radius, already multiplied by the scale factor                       */
+    int32_t min_level;      /* GetFeaturesInArea(x, y, r, minLevel, maxLevel) (Frame.cpp:379)        */
+    int32_t max_level;
+    uint8_t desc[ORBB_DESC_BYTES];
+} orbm_query;
+
+/* Frame::GetFeaturesInArea (Frame.cpp:379-432) + DescriptorDistance for nq queries at once.  Output is CSR:
+ * cand_offsets[nq+1], cand_idx / cand_dist in EXACTLY the reference's enumeration order (ix, iy, insertion),
+ * so the caller's order-dependent resolution loops (already-matched skips, ratio tests, rotation histogram)
+ * run unchanged on the host.  If the total exceeds cap, ORBB_E_CAPACITY is returned with cand_offsets filled. */
+int orbm_window_search(const orbm_frame* f, const orbm_query* q_host, int nq,
+                       int32_t* cand_offsets_host, int32_t* cand_idx_host, int32_t* cand_dist_host, int cap);
+
+/* Frame::ComputeStereoMatches (Frame.cpp:540-748) on the device, reading both extractors' pyramids
+ * (mpORBextractorLeft/Right->mvImagePyramid) in place.  left/right must hold their last extraction (frame 0);
+ * kps/desc are the host vectors those extractions returned.  mb is the member value at call time (0 in the
+ * reference's stereo constructor => no max-disparity cut).  Outputs mvuRight / mvDepth (n_left floats, -1 = none). */
+int orbm_stereo_match(orbx_handle* left, orbx_handle* right,
+                      const orbx_keypoint* kps_left_host, const uint8_t* desc_left_host, int n_left,
+                      const orbx_keypoint* kps_right_host, const uint8_t* desc_right_host, int n_right,
+                      float mbf, float mb, float* u_right_host, float* depth_host);
+
+/* Brute-force top-2 over a descriptor database shard with the reference's top-2 update rule
+ * (SearchByBoW, ORBmatcher.cpp:249-275: strict '<', first index wins, second may equal best).
+ * A database object holds one shard: rows [row_offset, row_offset + nrows) of the global database. */
+typedef struct orbm_db orbm_db;
+int orbm_db_create(orbm_db** out, int64_t capacity_rows, int64_t row_offset, int device);
+int orbm_db_append(orbm_db* db, const uint8_t* rows_host, int64_t nrows);
+int orbm_db_append_device(orbm_db* db, const uint8_t* rows_dev, int64_t nrows);
+int orbm_db_destroy(orbm_db* db);
+int64_t orbm_db_rows(const orbm_db* db);
+
+/* Host queries in, host results out: d1[i] best distance, idx1[i] GLOBAL row index of the best (first on ties),
+ * d2[i] second-best distance (256 when the shard has < 2 rows; d1 = 256, idx1 = -1 when it has none). */
+int orbm_bf_top2(const orbm_db* db, const uint8_t* q_host, int nq, int32_t* d1_host, int64_t* idx1_host, int32_t* d2_host);
+/* Device queries / device results, asynchronous on `stream` (cudaStream_t, may be NULL). */
+int orbm_bf_top2_device(const orbm_db* db, const uint8_t* q_dev, int nq, int32_t* d1_dev, int64_t* idx1_dev,
+                        int32_t* d2_dev, void* stream);
+/* Merge of G per-shard results laid out [g][nq] (shards ordered by ascending row range) into the global top-2
+ *  — the step that follows the NCCL all-gather.  Device pointers, asynchronous on `stream`. */
+int orbm_merge_top2_device(const int32_t* d1_all, const int64_t* idx1_all, const int32_t* d2_all, int nshards, int nq,
+                           int32_t* d1_dev, int64_t* idx1_dev, int32_t* d2_dev, void* stream);
+/* Ratio test of the reference (ORBmatcher.cpp:278-305): accept iff d1 <= th_low && (float)d1 < ratio*(float)d2.
+ * Host arrays; accepted[i] = 0/1. */
+int orbm_ratio_test(const int32_t* d1, const int32_t* d2, int nq, int th_low, float ratio, uint8_t* accepted);
+
+/* -- misc ------------------------------------------------------------------------------------------- */
+const char* orbb200_strerror(int code);
+const char* orbb200_last_cuda_error(void);
+int orbb200_device_count(void);
+/* Measured throughput (1e9 POPC.32 per second) of a register-only __popc loop on `device`: the roofline
+ * denominator for the matching kernels. */
+int orbb200_measure_popc_peak(int device, double* gpopc_per_s);
+/* Number of kernel launches issued by this library since load (bench.py's gpu_launches claim). */
+uint64_t orbb200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBB200_H */

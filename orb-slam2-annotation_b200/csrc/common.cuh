@@ -1,0 +1,53 @@
+// common.cuh — shared helpers of liborbb200 (sm_100a only; no CPU fallback anywhere in this library).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <atomic>
+#include <mutex>
+#include <new>
+#include <vector>
+#include "../../include/orbb200.h"
+
+namespace orbb {
+
+extern std::atomic<uint64_t> g_launches;     // kernels launched by this library (orbb200_launch_count)
+void set_cuda_error(cudaError_t e, const char* what);
+
+#define ORBB_CUDA(call)                                              \
+    do {                                                             \
+        cudaError_t _e = (call);                                     \
+        if (_e != cudaSuccess) {                                     \
+            ::orbb::set_cuda_error(_e, #call);                       \
+            return ORBB_E_CUDA;                                      \
+        }                                                            \
+    } while (0)
+
+#define ORBB_LAUNCHED() (::orbb::g_launches.fetch_add(1, std::memory_order_relaxed))
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Device-side pyramid geometry of one handle (levels of all frames share it).
+struct LevelGeom {
+    int w, h;            // level size: cvRound(W * mvInvScaleFactor[L]) (ORBextractor.cpp:1128)
+    int pitch;           // row pitch in bytes inside the pyramid / blur buffers (multiple of 128)
+    size_t off;          // byte offset of this level inside one frame's pyramid (and blur) block
+    int nCols, nRows, wCell, hCell;   // FAST cell grid (ORBextractor.cpp:781-795); nCols==0 => no FAST on this level
+    int nIni;            // octree roots (ORBextractor.cpp:545)
+    float hX;            // root width as float
+    int quota;           // mnFeaturesPerLevel[L]
+    int rec_cap;         // capacity of the raw FAST record list of this level
+    size_t rec_off;      // element offset of this level's record list inside one frame's record block
+    int out_cap;         // capacity of the per-level octree output
+    size_t out_off;      // element offset of the per-level octree output inside one frame's block
+    int node_cap;        // octree node pool capacity
+    float scale;         // mvScaleFactor[L]
+    float size;          // (float)(int)(31 * scale)
+    // resize tables for L -> L+1 (unused on the last level)
+    int xt_off, yt_off;  // offsets into the coefficient table (int2 {s0, a0 | a1 << 16})
+    int dxs_off, dys_off;// offsets into the per-tile first-destination-index tables
+};
+
+}  // namespace orbb

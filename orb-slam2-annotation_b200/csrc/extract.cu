@@ -1,0 +1,593 @@
+// extract.cu — host side of the extractor half of liborbb200: handle, geometry/tables, launches, C ABI.
+// Replaces ORB_SLAM2::ORBextractor (reference include/ORBextractor.h:45-111, src/ORBextractor.cpp:412-472, :1053-1148).
+#include "extract_kernels.cuh"
+#include <math.h>
+#include <stdlib.h>
+
+namespace orbb {
+
+std::atomic<uint64_t> g_launches{0};
+static std::mutex g_err_mu;
+static char g_err[512] = "";
+void set_cuda_error(cudaError_t e, const char* what)
+{
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    snprintf(g_err, sizeof g_err, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+}
+
+static const int8_t h_pattern[1024] = {
+#include "orb_pattern.inc"
+};
+
+static inline int cv_round_f(float v) { return (int)nearbyintf(v); }
+static inline int cv_round_d(double v) { return (int)nearbyint(v); }
+
+}  // namespace orbb
+
+using namespace orbb;
+
+struct orbx_handle {
+    orbx_config cfg;
+    int nlevels;
+    cudaStream_t stream = nullptr;
+    // ORBextractor tables (ORBextractor.cpp:417-448, :456-471)
+    float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS], sigma2[ORBB_MAX_LEVELS], inv_sigma2[ORBB_MAX_LEVELS];
+    int per_level[ORBB_MAX_LEVELS], umax[16];
+    int q[7];
+    float factorPI;
+    // geometry for the current image shape
+    int cur_w = 0, cur_h = 0;
+    LevelGeom geom[ORBB_MAX_LEVELS];
+    long long node_off[ORBB_MAX_LEVELS], cell_off[ORBB_MAX_LEVELS];
+    size_t pyr_fstride = 0, rec_total = 0, node_total = 0, cell_total = 0, out_total = 0, tab_total = 0, tile_total = 0;
+    // capacities (sized for max_width x max_height at creation)
+    size_t cap_pyr = 0, cap_rec = 0, cap_node = 0, cap_cell = 0, cap_out = 0, cap_tab = 0, cap_tile = 0;
+    int dev_capacity = 0;         // per-frame capacity of the internal final output buffers
+    // device buffers
+    uint8_t *d_pyr = nullptr, *d_blur = nullptr, *d_cellflag = nullptr, *d_desc = nullptr;
+    uint32_t *d_rec = nullptr, *d_pts = nullptr;
+    uint4* d_nodes = nullptr;
+    int *d_iscr = nullptr, *d_rec_count = nullptr, *d_out_count = nullptr, *d_status = nullptr, *d_counts = nullptr, *d_tiles = nullptr;
+    int4* d_out = nullptr;
+    int2* d_tab = nullptr;
+    LevelGeom* d_geom = nullptr;
+    long long *d_node_off = nullptr, *d_cell_off = nullptr;
+    orbx_keypoint* d_kps = nullptr;
+    // pinned staging
+    uint8_t *h_img = nullptr, *h_desc = nullptr;
+    orbx_keypoint* h_kps = nullptr;
+    int *h_counts = nullptr, *h_status = nullptr;
+    // last extraction
+    int last_frames = 0;
+    const uint8_t* last_src = nullptr; long long last_src_pitch = 0, last_src_fstride = 0;
+    const orbx_keypoint* last_kps_dev = nullptr; int last_capacity = 0;
+};
+
+static void level_sizes(const orbx_handle* h, int w, int ht, int* lw, int* lh)
+{
+    for (int l = 0; l < h->nlevels; l++) {
+        lw[l] = cv_round_f((float)w * h->inv_scale[l]);     // ORBextractor.cpp:1128
+        lh[l] = cv_round_f((float)ht * h->inv_scale[l]);
+    }
+}
+
+// cv::resize INTER_LINEAR coefficient tables for src -> dst along one axis.
+static void build_axis_table(int src, int dst, int tile, int2* tab, int* tile_first, int ntiles)
+{
+    const double inv_scale = (double)dst / src;
+    const double sc = 1.0 / inv_scale;
+    int t = 0;
+    for (int d = 0; d < dst; d++) {
+        float f = (float)((d + 0.5) * sc - 0.5);
+        int s = (int)floorf(f);
+        f -= s;
+        if (s < 0) { s = 0; f = 0.f; }
+        if (s >= src - 1) { s = src - 1; f = 0.f; }
+        const int a0 = cv_round_f((1.f - f) * 2048.f), a1 = cv_round_f(f * 2048.f);
+        tab[d] = make_int2(s, (a0 & 0xffff) | (a1 << 16));
+        while (t < ntiles && s >= t * tile) tile_first[t++] = d;
+    }
+    while (t <= ntiles) tile_first[t++] = dst;
+}
+
+// Computes the per-shape geometry; returns false if the shape cannot be handled by this handle's buffers.
+static int setup_geometry(orbx_handle* h, int w, int ht, bool allocate_only)
+{
+    int lw[ORBB_MAX_LEVELS], lh[ORBB_MAX_LEVELS];
+    level_sizes(h, w, ht, lw, lh);
+    size_t off = 0, rec = 0, node = 0, cell = 0, out = 0, tab = 0, tile = 0;
+    for (int l = 0; l < h->nlevels; l++) {
+        LevelGeom& g = h->geom[l];
+        memset(&g, 0, sizeof g);
+        if (lw[l] < 1 || lh[l] < 1) return ORBB_E_BAD_SHAPE;
+        g.w = lw[l]; g.h = lh[l];
+        g.pitch = (int)align_up((size_t)g.w, 128);
+        g.off = off; off += (size_t)g.pitch * g.h;
+        // cell grid (ORBextractor.cpp:781-795)
+        const int maxBX = g.w - 16, maxBY = g.h - 16;
+        const float width = (float)(maxBX - 16), height = (float)(maxBY - 16);
+        int nCols = width > 0 ? (int)(width / 30.f) : 0, nRows = height > 0 ? (int)(height / 30.f) : 0;
+        if (nCols < 1 || nRows < 1) { nCols = nRows = 0; }     // level smaller than one cell: no keypoints (reference: UB)
+        g.nCols = nCols; g.nRows = nRows;
+        g.wCell = nCols ? (int)ceilf(width / nCols) : 1;
+        g.hCell = nRows ? (int)ceilf(height / nRows) : 1;
+        // octree roots (ORBextractor.cpp:545-547)
+        int nIni = nCols ? (int)roundf((float)(maxBX - 16) / (float)(maxBY - 16)) : 1;
+        if (nIni < 1) nIni = 1;
+        if (nIni > 256) return ORBB_E_BAD_SHAPE;
+        g.nIni = nIni;
+        g.hX = (float)(maxBX - 16) / nIni;
+        g.quota = h->per_level[l];
+        g.rec_cap = (int)((size_t)g.w * g.h / 10 + 1024);
+        g.rec_off = rec; rec += g.rec_cap;
+        g.node_cap = 6 * g.quota + 8 * nIni + 64;
+        g.out_cap = g.node_cap;
+        g.out_off = out; out += g.out_cap;
+        h->node_off[l] = (long long)node; node += g.node_cap;
+        h->cell_off[l] = (long long)cell; cell += align_up((size_t)nCols * nRows + 16, 16);
+        g.scale = h->scale[l];
+        g.size = (float)(int)(31 * h->scale[l]);              // ORBextractor.cpp:847
+        if (l + 1 < h->nlevels) {
+            g.xt_off = (int)tab; tab += lw[l + 1];
+            g.yt_off = (int)tab; tab += lh[l + 1];
+            g.dxs_off = (int)tile; tile += ceil_div(g.w, TW) + 1;
+            g.dys_off = (int)tile; tile += ceil_div(g.h, TH) + 1;
+        }
+    }
+    if (allocate_only) {
+        h->cap_pyr = off; h->cap_rec = rec; h->cap_node = node; h->cap_cell = cell; h->cap_out = out;
+        h->cap_tab = tab + 64; h->cap_tile = tile + 64;
+        return ORBB_OK;
+    }
+    if (off > h->cap_pyr || rec > h->cap_rec || node > h->cap_node || cell > h->cap_cell || out > h->cap_out ||
+        tab > h->cap_tab || tile > h->cap_tile)
+        return ORBB_E_BAD_SHAPE;
+    h->pyr_fstride = off; h->rec_total = rec; h->node_total = node; h->cell_total = cell; h->out_total = out;
+    h->tab_total = tab; h->tile_total = tile;
+    return ORBB_OK;
+}
+
+static int upload_geometry(orbx_handle* h)
+{
+    std::vector<int2> tab(h->tab_total + 1);
+    std::vector<int> tiles(h->tile_total + 1);
+    for (int l = 0; l + 1 < h->nlevels; l++) {
+        const LevelGeom& g = h->geom[l];
+        const LevelGeom& n = h->geom[l + 1];
+        build_axis_table(g.w, n.w, TW, tab.data() + g.xt_off, tiles.data() + g.dxs_off, ceil_div(g.w, TW));
+        build_axis_table(g.h, n.h, TH, tab.data() + g.yt_off, tiles.data() + g.dys_off, ceil_div(g.h, TH));
+    }
+    // plain synchronous copies: shape changes are rare (once per camera), and the stream must not race them
+    ORBB_CUDA(cudaStreamSynchronize(h->stream));
+    ORBB_CUDA(cudaMemcpy(h->d_tab, tab.data(), h->tab_total * sizeof(int2), cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(h->d_tiles, tiles.data(), h->tile_total * sizeof(int), cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(h->d_geom, h->geom, sizeof(LevelGeom) * h->nlevels, cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(h->d_node_off, h->node_off, sizeof(long long) * h->nlevels, cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(h->d_cell_off, h->cell_off, sizeof(long long) * h->nlevels, cudaMemcpyHostToDevice));
+    return ORBB_OK;
+}
+
+static std::mutex g_const_mu;
+static bool g_const_done[64] = {false};
+
+static int init_constants(orbx_handle* h)
+{
+    std::lock_guard<std::mutex> lk(g_const_mu);
+    const int dev = h->cfg.device;
+    if (dev < 64 && g_const_done[dev]) return ORBB_OK;
+    // cv::fastAtan2 polynomial, degrees
+    const float sc = (float)(180.0 / 3.14159265358979323846);
+    const float at[4] = {0.9997878412794807f * sc, -0.3258083974640975f * sc, 0.1555786518463281f * sc, -0.04432655554792128f * sc};
+    ORBB_CUDA(cudaMemcpyToSymbol(c_pattern, h_pattern, sizeof h_pattern));
+    ORBB_CUDA(cudaMemcpyToSymbol(c_umax, h->umax, sizeof(int) * 16));
+    ORBB_CUDA(cudaMemcpyToSymbol(c_atan, at, sizeof at));
+    if (dev < 64) g_const_done[dev] = true;
+    return ORBB_OK;
+}
+
+template <typename T> static int dev_alloc(T** p, size_t n)
+{
+    ORBB_CUDA(cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)));
+    return ORBB_OK;
+}
+template <typename T> static int host_alloc(T** p, size_t n)
+{
+    ORBB_CUDA(cudaMallocHost((void**)p, (n ? n : 1) * sizeof(T)));
+    return ORBB_OK;
+}
+
+extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
+{
+    if (!cfg || !out) return ORBB_E_INVALID;
+    *out = nullptr;
+    if (cfg->nlevels < 1 || cfg->nlevels > ORBB_MAX_LEVELS || cfg->nfeatures < 0 || !(cfg->scale_factor > 1.0f) ||
+        cfg->min_th_fast < 0 || cfg->ini_th_fast < cfg->min_th_fast || cfg->ini_th_fast > 254 || cfg->max_batch < 1)
+        return ORBB_E_INVALID;
+    if (cfg->max_width < 1 || cfg->max_height < 1 || cfg->max_width > 4096 || cfg->max_height > 4096) return ORBB_E_BAD_SHAPE;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || cfg->device < 0 || cfg->device >= ndev) {
+        set_cuda_error(cudaErrorNoDevice, "orbx_create: no CUDA device (this library has no CPU fallback)");
+        return ORBB_E_CUDA;
+    }
+    ORBB_CUDA(cudaSetDevice(cfg->device));
+    orbx_handle* h = new (std::nothrow) orbx_handle();
+    if (!h) return ORBB_E_NOMEM;
+    h->cfg = *cfg;
+    const int nl = h->nlevels = cfg->nlevels;
+    // --- ORBextractor constructor tables (ORBextractor.cpp:417-448); scaleFactor member is a double holding the float ---
+    const double scaleFactor = (double)cfg->scale_factor;
+    h->scale[0] = 1.0f; h->sigma2[0] = 1.0f;
+    for (int i = 1; i < nl; i++) {
+        h->scale[i] = (float)(h->scale[i - 1] * scaleFactor);
+        h->sigma2[i] = h->scale[i] * h->scale[i];
+    }
+    for (int i = 0; i < nl; i++) { h->inv_scale[i] = 1.0f / h->scale[i]; h->inv_sigma2[i] = 1.0f / h->sigma2[i]; }
+    {
+        const float factor = (float)(1.0f / scaleFactor);
+        float nDesired = cfg->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+        int sum = 0;
+        for (int l = 0; l < nl - 1; l++) {
+            h->per_level[l] = cv_round_f(nDesired);
+            sum += h->per_level[l];
+            nDesired *= factor;
+        }
+        h->per_level[nl - 1] = cfg->nfeatures - sum > 0 ? cfg->nfeatures - sum : 0;
+    }
+    {   // umax (ORBextractor.cpp:456-471)
+        int v, v0;
+        const int vmax = (int)floor(15 * sqrt(2.f) / 2 + 1), vmin = (int)ceil(15 * sqrt(2.f) / 2);
+        for (v = 0; v <= vmax; ++v) h->umax[v] = cv_round_d(sqrt(225.0 - v * v));
+        for (v = 15, v0 = 0; v >= vmin; --v) {
+            while (h->umax[v0] == h->umax[v0 + 1]) ++v0;
+            h->umax[v] = v0;
+            ++v0;
+        }
+    }
+    {
+        static const int Q[7] = {18, 34, 48, 56, 48, 34, 18}, QL[7] = {18, 34, 49, 55, 49, 34, 18};
+        for (int i = 0; i < 7; i++) h->q[i] = cfg->blur_legacy ? QL[i] : Q[i];
+    }
+    h->factorPI = (float)(3.14159265358979323846 / 180.f);
+
+    int rc = setup_geometry(h, cfg->max_width, cfg->max_height, true);
+    if (rc != ORBB_OK) { delete h; return rc; }
+    // non-max-size shapes can need slightly different totals (rounding): keep a margin
+    h->cap_pyr += 64 * 1024; h->cap_rec += 16 * 1024; h->cap_cell += 4096;
+    h->dev_capacity = (int)h->cap_out;
+    const size_t B = (size_t)cfg->max_batch;
+    rc = ORBB_OK;
+    auto ok = [&](int r) { if (rc == ORBB_OK) rc = r; };
+    ORBB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    ok(dev_alloc(&h->d_pyr, B * h->cap_pyr)); ok(dev_alloc(&h->d_blur, B * h->cap_pyr));
+    ok(dev_alloc(&h->d_rec, B * h->cap_rec)); ok(dev_alloc(&h->d_pts, 2 * B * h->cap_rec));
+    ok(dev_alloc(&h->d_nodes, B * h->cap_node)); ok(dev_alloc(&h->d_iscr, B * h->cap_node * ISCR_PER_NODE));
+    ok(dev_alloc(&h->d_cellflag, B * h->cap_cell));
+    ok(dev_alloc(&h->d_out, B * h->cap_out));
+    ok(dev_alloc(&h->d_rec_count, B * ORBB_MAX_LEVELS)); ok(dev_alloc(&h->d_out_count, B * ORBB_MAX_LEVELS));
+    ok(dev_alloc(&h->d_status, B)); ok(dev_alloc(&h->d_counts, B));
+    ok(dev_alloc(&h->d_tab, h->cap_tab)); ok(dev_alloc(&h->d_tiles, h->cap_tile));
+    ok(dev_alloc(&h->d_geom, (size_t)ORBB_MAX_LEVELS));
+    ok(dev_alloc(&h->d_node_off, (size_t)ORBB_MAX_LEVELS)); ok(dev_alloc(&h->d_cell_off, (size_t)ORBB_MAX_LEVELS));
+    ok(dev_alloc(&h->d_kps, B * h->dev_capacity)); ok(dev_alloc(&h->d_desc, B * h->dev_capacity * 32));
+    ok(host_alloc(&h->h_img, B * (size_t)cfg->max_width * cfg->max_height));
+    ok(host_alloc(&h->h_kps, B * h->dev_capacity)); ok(host_alloc(&h->h_desc, B * h->dev_capacity * 32));
+    ok(host_alloc(&h->h_counts, B)); ok(host_alloc(&h->h_status, B));
+    if (rc == ORBB_OK) rc = init_constants(h);
+    if (rc != ORBB_OK) { orbx_destroy(h); return rc; }
+    *out = h;
+    return ORBB_OK;
+}
+
+extern "C" int orbx_destroy(orbx_handle* h)
+{
+    if (!h) return ORBB_E_INVALID;
+    cudaSetDevice(h->cfg.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    cudaFree(h->d_pyr); cudaFree(h->d_blur); cudaFree(h->d_rec); cudaFree(h->d_pts); cudaFree(h->d_nodes);
+    cudaFree(h->d_iscr); cudaFree(h->d_cellflag); cudaFree(h->d_out); cudaFree(h->d_rec_count); cudaFree(h->d_out_count);
+    cudaFree(h->d_status); cudaFree(h->d_counts); cudaFree(h->d_tab); cudaFree(h->d_tiles); cudaFree(h->d_geom);
+    cudaFree(h->d_node_off); cudaFree(h->d_cell_off); cudaFree(h->d_kps); cudaFree(h->d_desc);
+    cudaFreeHost(h->h_img); cudaFreeHost(h->h_kps); cudaFreeHost(h->h_desc); cudaFreeHost(h->h_counts); cudaFreeHost(h->h_status);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return ORBB_OK;
+}
+
+extern "C" int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                               int32_t* per_level, int32_t* umax)
+{
+    if (!h) return ORBB_E_INVALID;
+    for (int i = 0; i < h->nlevels; i++) {
+        if (scale) scale[i] = h->scale[i];
+        if (inv_scale) inv_scale[i] = h->inv_scale[i];
+        if (sigma2) sigma2[i] = h->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = h->inv_sigma2[i];
+        if (per_level) per_level[i] = h->per_level[i];
+    }
+    if (umax) for (int i = 0; i < 16; i++) umax[i] = h->umax[i];
+    return ORBB_OK;
+}
+
+// Enqueue the whole extraction of `nframes` device-resident frames on the handle's stream.
+static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes, int w, int ht, size_t stride, size_t fstride,
+                           orbx_keypoint* kps_dev, uint8_t* desc_dev, int32_t* counts_dev, int capacity)
+{
+    if (w != h->cur_w || ht != h->cur_h) {
+        int rc = setup_geometry(h, w, ht, false);
+        if (rc != ORBB_OK) return rc;
+        rc = upload_geometry(h);
+        if (rc != ORBB_OK) return rc;
+        h->cur_w = w; h->cur_h = ht;
+    }
+    const int nl = h->nlevels;
+    cudaStream_t st = h->stream;
+    ORBB_CUDA(cudaMemsetAsync(h->d_rec_count, 0, sizeof(int) * (size_t)nframes * nl, st));
+    ORBB_CUDA(cudaMemsetAsync(h->d_status, 0, sizeof(int) * (size_t)nframes, st));
+    for (int l = 0; l < nl; l++) {
+        const LevelGeom& g = h->geom[l];
+        LevelArgs a;
+        memset(&a, 0, sizeof a);
+        if (l == 0) { a.src = imgs_dev; a.src_pitch = (long long)stride; a.src_fstride = (long long)fstride; }
+        else { a.src = h->d_pyr + g.off; a.src_pitch = g.pitch; a.src_fstride = (long long)h->pyr_fstride; }
+        a.w = g.w; a.h = g.h;
+        a.blur = h->d_blur + g.off; a.blur_pitch = g.pitch; a.blur_fstride = (long long)h->pyr_fstride;
+        if (l + 1 < nl) {
+            const LevelGeom& n = h->geom[l + 1];
+            a.dst = h->d_pyr + n.off; a.dst_pitch = n.pitch; a.dst_fstride = (long long)h->pyr_fstride;
+            a.xt = h->d_tab + g.xt_off; a.yt = h->d_tab + g.yt_off;
+            a.dxs = h->d_tiles + g.dxs_off; a.dys = h->d_tiles + g.dys_off;
+        }
+        a.fast_on = g.nCols > 0; a.wCell = g.wCell; a.hCell = g.hCell; a.minTh = h->cfg.min_th_fast;
+        a.rec = h->d_rec + g.rec_off; a.rec_cap = g.rec_cap; a.rec_fstride = (long long)h->rec_total;
+        a.rec_count = h->d_rec_count + l; a.rec_count_stride = nl;
+        for (int i = 0; i < 7; i++) a.q[i] = h->q[i];
+        dim3 grid(ceil_div(g.w, TW), ceil_div(g.h, TH), nframes);
+        level_kernel<<<grid, NT, 0, st>>>(a);
+        ORBB_LAUNCHED();
+    }
+    {
+        OctArgs a;
+        memset(&a, 0, sizeof a);
+        a.geom = h->d_geom; a.nlevels = nl; a.iniTh = h->cfg.ini_th_fast;
+        a.rec = h->d_rec; a.rec_fstride = (long long)h->rec_total; a.rec_count = h->d_rec_count;
+        a.pts = h->d_pts; a.pts_fstride = 2 * (long long)h->rec_total;
+        a.nodes = h->d_nodes; a.nodes_fstride = (long long)h->node_total;
+        a.iscr = h->d_iscr; a.iscr_fstride = (long long)h->node_total * ISCR_PER_NODE;
+        a.cellflag = h->d_cellflag; a.cellflag_fstride = (long long)h->cell_total;
+        a.node_off = h->d_node_off; a.cell_off = h->d_cell_off;
+        a.out = h->d_out; a.out_fstride = (long long)h->out_total;
+        a.out_count = h->d_out_count; a.status = h->d_status;
+        octree_kernel<<<dim3(nl, nframes), NTO, 0, st>>>(a);
+        ORBB_LAUNCHED();
+    }
+    {
+        DescArgs a;
+        memset(&a, 0, sizeof a);
+        a.geom = h->d_geom; a.nlevels = nl;
+        a.src0 = imgs_dev; a.src0_pitch = (long long)stride; a.src0_fstride = (long long)fstride;
+        a.pyr = h->d_pyr; a.pyr_fstride = (long long)h->pyr_fstride;
+        a.blur = h->d_blur; a.blur_fstride = (long long)h->pyr_fstride;
+        a.lvl = h->d_out; a.lvl_fstride = (long long)h->out_total; a.lvl_count = h->d_out_count;
+        a.kps = kps_dev; a.desc = desc_dev; a.counts = counts_dev; a.capacity = capacity;
+        a.factorPI = h->factorPI;
+        const int maxk = capacity < (int)h->out_total ? capacity : (int)h->out_total;
+        orient_desc_kernel<<<dim3(ceil_div(maxk > 0 ? maxk : 1, 8), nframes), 256, 0, st>>>(a);
+        ORBB_LAUNCHED();
+    }
+    ORBB_CUDA(cudaGetLastError());
+    h->last_frames = nframes;
+    h->last_src = imgs_dev; h->last_src_pitch = (long long)stride; h->last_src_fstride = (long long)fstride;
+    h->last_kps_dev = kps_dev; h->last_capacity = capacity;
+    return ORBB_OK;
+}
+
+extern "C" int orbx_extract_batch_device(orbx_handle* h, const uint8_t* imgs_dev, int nframes, int w, int ht,
+                                         size_t stride, size_t fstride, orbx_keypoint* kps_dev, uint8_t* desc_dev,
+                                         int32_t* counts_dev, int capacity)
+{
+    if (!h || !imgs_dev || !kps_dev || !desc_dev || !counts_dev || capacity < 1) return ORBB_E_INVALID;
+    if (nframes < 1 || nframes > h->cfg.max_batch) return ORBB_E_INVALID;
+    if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w) return ORBB_E_BAD_SHAPE;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    return enqueue_extract(h, imgs_dev, nframes, w, ht, stride, fstride, kps_dev, desc_dev, counts_dev, capacity);
+}
+
+extern "C" int orbx_sync(orbx_handle* h)
+{
+    if (!h) return ORBB_E_INVALID;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    ORBB_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->last_frames > 0) {
+        ORBB_CUDA(cudaMemcpy(h->h_status, h->d_status, sizeof(int) * h->last_frames, cudaMemcpyDeviceToHost));
+        for (int f = 0; f < h->last_frames; f++) if (h->h_status[f]) return ORBB_E_CAPACITY;
+    }
+    return ORBB_OK;
+}
+
+extern "C" void* orbx_stream(orbx_handle* h) { return h ? (void*)h->stream : nullptr; }
+
+extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
+                                  size_t fstride, orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity)
+{
+    if (!h || !counts_host || capacity < 0 || (capacity > 0 && (!kps_host || !desc_host))) return ORBB_E_INVALID;
+    if (nframes < 1 || nframes > h->cfg.max_batch) return ORBB_E_INVALID;
+    if (w == 0 || ht == 0 || !imgs_host) {              // empty image: silent return (ORBextractor.cpp:1056-1057)
+        for (int f = 0; f < nframes; f++) counts_host[f] = 0;
+        return ORBB_OK;
+    }
+    if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w) return ORBB_E_BAD_SHAPE;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    cudaStream_t st = h->stream;
+    // H2D straight into the level-0 slots of the pyramid (pitch = geom[0].pitch)
+    if (w != h->cur_w || ht != h->cur_h) {
+        int rc = setup_geometry(h, w, ht, false);
+        if (rc != ORBB_OK) return rc;
+        rc = upload_geometry(h);
+        if (rc != ORBB_OK) return rc;
+        h->cur_w = w; h->cur_h = ht;
+    }
+    const LevelGeom& g0 = h->geom[0];
+    cudaPointerAttributes attr;
+    bool pinned = cudaPointerGetAttributes(&attr, imgs_host) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    for (int f = 0; f < nframes; f++) {
+        const uint8_t* src = imgs_host + (size_t)f * fstride;
+        size_t spitch = stride;
+        if (!pinned) {     // stage through pinned memory so the copy is truly asynchronous
+            uint8_t* stg = h->h_img + (size_t)f * w * ht;
+            for (int y = 0; y < ht; y++) memcpy(stg + (size_t)y * w, src + (size_t)y * stride, w);
+            src = stg; spitch = w;
+        }
+        ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, g0.pitch, src, spitch, w, ht,
+                                    cudaMemcpyHostToDevice, st));
+    }
+    const int devcap = capacity < h->dev_capacity ? (capacity > 0 ? capacity : 1) : h->dev_capacity;
+    int rc = enqueue_extract(h, h->d_pyr + g0.off, nframes, w, ht, g0.pitch, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
+    if (rc != ORBB_OK) return rc;
+    ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaMemcpyAsync(h->h_kps, h->d_kps, sizeof(orbx_keypoint) * (size_t)nframes * devcap, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaMemcpyAsync(h->h_desc, h->d_desc, (size_t)32 * nframes * devcap, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaStreamSynchronize(st));
+    int ret = ORBB_OK;
+    for (int f = 0; f < nframes; f++) {
+        const int n = h->h_counts[f];
+        counts_host[f] = n;
+        if (h->h_status[f]) ret = ORBB_E_CAPACITY;
+        const int m = n < capacity ? n : capacity;
+        if (n > capacity) ret = ORBB_E_CAPACITY;
+        if (m > 0) {
+            memcpy(kps_host + (size_t)f * capacity, h->h_kps + (size_t)f * devcap, sizeof(orbx_keypoint) * m);
+            memcpy(desc_host + (size_t)f * capacity * 32, h->h_desc + (size_t)f * devcap * 32, (size_t)32 * m);
+        }
+    }
+    return ret;
+}
+
+extern "C" int orbx_extract(orbx_handle* h, const uint8_t* img_host, int w, int ht, size_t stride,
+                            orbx_keypoint* kps_host, uint8_t* desc_host, int capacity, int* n_out)
+{
+    if (!n_out) return ORBB_E_INVALID;
+    int32_t n = 0;
+    const int rc = orbx_extract_batch(h, img_host, 1, w, ht, stride, 0, kps_host, desc_host, &n, capacity);
+    *n_out = n;
+    return rc;
+}
+
+extern "C" int orbx_pyramid_level(orbx_handle* h, int frame, int level, uint8_t* dst_host, size_t dst_stride, int* w, int* ht)
+{
+    if (!h || level < 0 || level >= h->nlevels || frame < 0) return ORBB_E_INVALID;
+    if (h->last_frames < 1 || frame >= h->last_frames) return ORBB_E_STATE;
+    const LevelGeom& g = h->geom[level];
+    if (w) *w = g.w;
+    if (ht) *ht = g.h;
+    if (!dst_host) return ORBB_OK;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    ORBB_CUDA(cudaStreamSynchronize(h->stream));
+    if (dst_stride == 0) dst_stride = g.w;
+    if (level == 0)
+        ORBB_CUDA(cudaMemcpy2D(dst_host, dst_stride, h->last_src + (size_t)frame * h->last_src_fstride, h->last_src_pitch, g.w, g.h, cudaMemcpyDeviceToHost));
+    else
+        ORBB_CUDA(cudaMemcpy2D(dst_host, dst_stride, h->d_pyr + (size_t)frame * h->pyr_fstride + g.off, g.pitch, g.w, g.h, cudaMemcpyDeviceToHost));
+    return ORBB_OK;
+}
+
+extern "C" int orbx_debug_stage(orbx_handle* h, int frame, int level, int stage, void* dst_host, size_t dst_bytes, size_t* bytes_out)
+{
+    if (!h || level < 0 || level >= h->nlevels || frame < 0) return ORBB_E_INVALID;
+    if (h->last_frames < 1 || frame >= h->last_frames) return ORBB_E_STATE;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    ORBB_CUDA(cudaStreamSynchronize(h->stream));
+    const LevelGeom& g = h->geom[level];
+    const int nl = h->nlevels;
+    if (stage == ORBX_STAGE_BLUR) {
+        const size_t need = (size_t)g.w * g.h;
+        if (bytes_out) *bytes_out = need;
+        if (!dst_host) return ORBB_OK;
+        if (dst_bytes < need) return ORBB_E_CAPACITY;
+        ORBB_CUDA(cudaMemcpy2D(dst_host, g.w, h->d_blur + (size_t)frame * h->pyr_fstride + g.off, g.pitch, g.w, g.h, cudaMemcpyDeviceToHost));
+        return ORBB_OK;
+    }
+    if (stage == ORBX_STAGE_FASTKPS) {
+        // the records after the per-cell threshold decision = the octree's point buffer is permuted in place, so
+        // re-derive the decision here from the raw records (same rule as octree_kernel).
+        int nraw = 0;
+        ORBB_CUDA(cudaMemcpy(&nraw, h->d_rec_count + (size_t)frame * nl + level, sizeof(int), cudaMemcpyDeviceToHost));
+        if (nraw > g.rec_cap) nraw = g.rec_cap;
+        std::vector<uint32_t> rec(nraw > 0 ? nraw : 1);
+        if (nraw > 0)
+            ORBB_CUDA(cudaMemcpy(rec.data(), h->d_rec + (size_t)frame * h->rec_total + g.rec_off, sizeof(uint32_t) * nraw, cudaMemcpyDeviceToHost));
+        std::vector<uint8_t> flag((size_t)(g.nCols * g.nRows) + 1, 0);
+        auto cell = [&](uint32_t r) { const int x = (r >> 8) & 0xfff, y = r >> 20; return ((y - 19) / g.hCell) * g.nCols + (x - 19) / g.wCell; };
+        for (int i = 0; i < nraw; i++) if ((int)(rec[i] & 0xff) > h->cfg.ini_th_fast) flag[cell(rec[i])] = 1;
+        std::vector<int32_t> outv;
+        for (int i = 0; i < nraw; i++) {
+            const int m = rec[i] & 0xff;
+            if (m > h->cfg.ini_th_fast || !flag[cell(rec[i])]) {
+                outv.push_back((int)((rec[i] >> 8) & 0xfff) - 16); outv.push_back((int)(rec[i] >> 20) - 16); outv.push_back(m - 1);
+            }
+        }
+        const size_t need = outv.size() * sizeof(int32_t);
+        if (bytes_out) *bytes_out = need;
+        if (!dst_host) return ORBB_OK;
+        if (dst_bytes < need) return ORBB_E_CAPACITY;
+        if (need) memcpy(dst_host, outv.data(), need);
+        return ORBB_OK;
+    }
+    if (stage == ORBX_STAGE_LEVELKPS) {
+        std::vector<int> cnt(nl);
+        ORBB_CUDA(cudaMemcpy(cnt.data(), h->d_out_count + (size_t)frame * nl, sizeof(int) * nl, cudaMemcpyDeviceToHost));
+        const int n = cnt[level];
+        const size_t need = (size_t)n * sizeof(orbx_keypoint);
+        if (bytes_out) *bytes_out = need;
+        if (!dst_host) return ORBB_OK;
+        if (dst_bytes < need) return ORBB_E_CAPACITY;
+        if (!n) return ORBB_OK;
+        std::vector<int4> lv(n);
+        ORBB_CUDA(cudaMemcpy(lv.data(), h->d_out + (size_t)frame * h->out_total + g.out_off, sizeof(int4) * n, cudaMemcpyDeviceToHost));
+        int before = 0;
+        for (int l = 0; l < level; l++) before += cnt[l];
+        std::vector<orbx_keypoint> fin(n);
+        if (before + n > h->last_capacity) return ORBB_E_CAPACITY;
+        ORBB_CUDA(cudaMemcpy(fin.data(), h->last_kps_dev + (size_t)frame * h->last_capacity + before, sizeof(orbx_keypoint) * n, cudaMemcpyDeviceToHost));
+        orbx_keypoint* o = (orbx_keypoint*)dst_host;
+        for (int i = 0; i < n; i++) { o[i] = fin[i]; o[i].x = (float)lv[i].x; o[i].y = (float)lv[i].y; }
+        return ORBB_OK;
+    }
+    return ORBB_E_INVALID;
+}
+
+extern "C" const char* orbb200_strerror(int code)
+{
+    switch (code) {
+        case ORBB_OK: return "ok";
+        case ORBB_E_INVALID: return "invalid argument";
+        case ORBB_E_CUDA: return "CUDA error (see orbb200_last_cuda_error)";
+        case ORBB_E_CAPACITY: return "output or internal buffer capacity exceeded";
+        case ORBB_E_BAD_SHAPE: return "unsupported image shape for this handle";
+        case ORBB_E_NOMEM: return "out of memory";
+        case ORBB_E_STATE: return "call order violated";
+        default: return "unknown error";
+    }
+}
+extern "C" const char* orbb200_last_cuda_error(void) { return g_err; }
+extern "C" int orbb200_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+extern "C" uint64_t orbb200_launch_count(void) { return g_launches.load(); }
+
+// Internal (not part of include/orbb200.h): lets match.cu read a handle's pyramid in place for ComputeStereoMatches.
+extern "C" int orbx__pyramid_view(orbx_handle* h, const LevelGeom** geom_host, const LevelGeom** geom_dev, int* nlevels,
+                                  const uint8_t** src0, long long* src0_pitch, const uint8_t** pyr, int* device,
+                                  const float** scale, const float** inv_scale, void** stream)
+{
+    if (!h) return ORBB_E_INVALID;
+    if (h->last_frames < 1) return ORBB_E_STATE;
+    *geom_host = h->geom; *geom_dev = h->d_geom; *nlevels = h->nlevels;
+    *src0 = h->last_src; *src0_pitch = h->last_src_pitch; *pyr = h->d_pyr; *device = h->cfg.device;
+    *scale = h->scale; *inv_scale = h->inv_scale; *stream = (void*)h->stream;
+    return ORBB_OK;
+}

@@ -1,0 +1,796 @@
+// extract_kernels.cuh — sm_100a kernels of the ORB extractor hot path.
+//
+//   level_kernel     : one launch per pyramid level, grid = (tiles_x, tiles_y, frames).  A CTA stages a 64x32 tile of
+//                      level L (+4 px halo) in shared memory ONCE and produces from it (a) the 7x7 sigma-2 blurred level
+//                      (ORBextractor.cpp:1097-1098), (b) the FAST-9-16 arc score, cell-local 3x3 NMS and the ini/min
+//                      threshold candidates (ORBextractor.cpp:797-838), (c) the bilinear-resized tile of level L+1
+//                      (ORBextractor.cpp:1136).  Level L is therefore read from HBM once.
+//   octree_kernel    : DistributeOctTree (ORBextractor.cpp:541-770), one CTA per (level, frame).
+//   orient_desc_kernel: IC_Angle (ORBextractor.cpp:79-106) + computeOrbDescriptor (:110-149) + the coordinate scaling
+//                      and concatenation of operator() (:1084-1116), one warp per keypoint.
+//
+// Exact-arithmetic notes: integer fixed-point resize/blur, threshold-independent FAST score
+// m = max over 9-arcs, float ops with explicit _rn intrinsics (no FMA contraction), round-half-even conversions.
+#pragma once
+#include "common.cuh"
+
+namespace orbb {
+
+constexpr int TW = 64, TH = 32, HALO = 4, NT = 256;
+constexpr int SMW = 80;               // shared tile pitch (72 bytes used)
+constexpr int SMH = TH + 2 * HALO;    // 40 rows
+constexpr int SCW = TW + 2, SCH = TH + 2;
+constexpr int EMIT_CAP = 1024;
+
+__constant__ int8_t c_pattern[1024];  // rBRIEF pattern (ORBextractor.cpp:152-410), x0,y0,x1,y1 per test
+__constant__ int c_umax[16];          // circular patch row ends (ORBextractor.cpp:456-471)
+__constant__ float c_atan[4];         // fastAtan2 polynomial p1,p3,p5,p7 (already scaled to degrees)
+
+struct LevelArgs {
+    const uint8_t* src; long long src_pitch, src_fstride;   // level L (external input image when L == 0)
+    int w, h;
+    uint8_t* blur; long long blur_pitch, blur_fstride;      // blurred level L out
+    uint8_t* dst; long long dst_pitch, dst_fstride;         // level L+1 out (null on the last level)
+    const int2* xt; const int2* yt; const int* dxs; const int* dys;
+    int fast_on, wCell, hCell, minTh;
+    uint32_t* rec; int rec_cap; long long rec_fstride;      // raw FAST records  y<<20 | x<<8 | m
+    int* rec_count; int rec_count_stride;
+    int q[7];                                               // Q8 blur kernel
+};
+
+__device__ __forceinline__ int reflect101(int p, int n)
+{
+    if (p < 0) p = -p;
+    if (p >= n) p = 2 * (n - 1) - p;
+    return min(max(p, 0), n - 1);
+}
+
+// Threshold-independent FAST arc score m(x,y) = max over the 16 arcs of 9 contiguous ring pixels of
+// max(min(v - p_k), min(p_k - v)).  Corner at threshold t iff m > t; cv::FAST's response is m - 1.
+__device__ __forceinline__ int fast_arc_score(const uint8_t (*tile)[SMW], int ty, int tx)
+{
+    const int v = tile[ty][tx];
+    int d[16];
+    d[0] = v - tile[ty + 3][tx];      d[1] = v - tile[ty + 3][tx + 1];  d[2] = v - tile[ty + 2][tx + 2];
+    d[3] = v - tile[ty + 1][tx + 3];  d[4] = v - tile[ty][tx + 3];      d[5] = v - tile[ty - 1][tx + 3];
+    d[6] = v - tile[ty - 2][tx + 2];  d[7] = v - tile[ty - 3][tx + 1];  d[8] = v - tile[ty - 3][tx];
+    d[9] = v - tile[ty - 3][tx - 1];  d[10] = v - tile[ty - 2][tx - 2]; d[11] = v - tile[ty - 1][tx - 3];
+    d[12] = v - tile[ty][tx - 3];     d[13] = v - tile[ty + 1][tx - 3]; d[14] = v - tile[ty + 2][tx - 2];
+    d[15] = v - tile[ty + 3][tx - 1];
+    // Both polarities are reduced with MIN networks (e = p_k - v is formed explicitly).  Do NOT rewrite this as
+    // max(mn9, -mx9): ptxas 12.9 (-O1 and above, sm_100a) fuses that into VIMNMX3 and drops the negation
+    // (found by tests; -Xptxas -O0 was correct).  tools/level_dbg.cu is the regression harness.
+    int e[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) e[k] = -d[k];
+    int a2[16], b2[16], a4[16], b4[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) { a2[k] = min(d[k], d[(k + 1) & 15]); b2[k] = min(e[k], e[(k + 1) & 15]); }
+#pragma unroll
+    for (int k = 0; k < 16; k++) { a4[k] = min(a2[k], a2[(k + 2) & 15]); b4[k] = min(b2[k], b2[(k + 2) & 15]); }
+    int best = -256;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        const int a9 = min(min(a4[k], a4[(k + 4) & 15]), d[(k + 8) & 15]);
+        const int b9 = min(min(b4[k], b4[(k + 4) & 15]), e[(k + 8) & 15]);
+        best = max(best, max(a9, b9));
+    }
+    return best;
+}
+
+__global__ void __launch_bounds__(NT) level_kernel(const __grid_constant__ LevelArgs a)
+{
+    __shared__ __align__(16) uint8_t tile[SMH][SMW];
+    __shared__ uint16_t hb[TH + 6][TW];
+    __shared__ uint8_t sc[SCH][SCW + 2];
+    __shared__ uint16_t queue[SCH * SCW];
+    __shared__ uint32_t emit[EMIT_CAP];
+    __shared__ int s_qn, s_en, s_ebase;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int f = blockIdx.z;
+    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
+    const uint8_t* __restrict__ src = a.src + (long long)f * a.src_fstride;
+    if (tid == 0) { s_qn = 0; s_en = 0; }
+
+    // ---- 1. stage tile + halo (REFLECT_101 at the image border, as the blur of a cloned level sees it) ----
+    for (int r = warp; r < SMH; r += NT / 32) {
+        const int gy = reflect101(y0 - HALO + r, a.h);
+        const uint8_t* row = src + (long long)gy * a.src_pitch;
+        for (int c = lane; c < TW + 2 * HALO; c += 32) tile[r][c] = row[reflect101(x0 - HALO + c, a.w)];
+    }
+    for (int i = tid; i < SCH * (SCW + 2); i += NT) (&sc[0][0])[i] = 0;
+    __syncthreads();
+
+    // ---- 2. blur, horizontal pass (Q8.8) ----
+#ifndef DBG_NOBLUR
+    for (int i = tid; i < (TH + 6) * TW; i += NT) {
+        const int r = i >> 6, c = i & 63;
+        const uint8_t* p = &tile[r + 1][c + 1];
+        int s = 0;
+#pragma unroll
+        for (int k = 0; k < 7; k++) s += a.q[k] * p[k];
+        hb[r][c] = (uint16_t)s;
+    }
+#endif
+
+    // ---- 3. FAST quick test -> candidate queue ----
+    const bool fast_tile = a.fast_on && (x0 + TW >= 19) && (x0 - 1 <= a.w - 20) && (y0 + TH >= 19) && (y0 - 1 <= a.h - 20);
+    if (fast_tile) {
+        const int t = a.minTh;
+        for (int r = warp; r < SCH; r += NT / 32) {
+            const int gy = y0 - 1 + r;
+            const bool rowok = gy >= 19 && gy <= a.h - 20;
+            for (int c = lane; c < SCW + 30; c += 32) {     // 3 warp iterations cover 66 columns
+                bool pass = false;
+                if (rowok && c < SCW) {
+                    const int gx = x0 - 1 + c;
+                    if (gx >= 19 && gx <= a.w - 20) {
+                        const int ty = r + 3, tx = c + 3;
+                        const int v = tile[ty][tx];
+                        const int d0 = v - tile[ty + 3][tx], d4 = v - tile[ty][tx + 3];
+                        const int d8 = v - tile[ty - 3][tx], d12 = v - tile[ty][tx - 3];
+                        // any 9-arc contains two ADJACENT compass points: both darker or both brighter
+                        const int dk = (d0 > t) | ((d4 > t) << 1) | ((d8 > t) << 2) | ((d12 > t) << 3);
+                        const int br = (-d0 > t) | ((-d4 > t) << 1) | ((-d8 > t) << 2) | ((-d12 > t) << 3);
+                        const int dk2 = dk & ((dk >> 1) | (dk << 3)), br2 = br & ((br >> 1) | (br << 3));
+                        pass = ((dk2 | br2) & 15) != 0;
+#ifdef DBG_NOQUICK
+                        pass = true;
+#endif
+                    }
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, pass);
+                if (bal) {
+                    int base = 0;
+                    if (lane == 0) base = atomicAdd(&s_qn, __popc(bal));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (pass) queue[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)(r * SCW + c);
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- 4. blur, vertical pass (Q16.16) and store ----
+#ifndef DBG_NOBLUR
+    {
+        uint8_t* __restrict__ bl = a.blur + (long long)f * a.blur_fstride;
+        for (int i = tid; i < TH * TW; i += NT) {
+            const int r = i >> 6, c = i & 63;
+            const int gy = y0 + r, gx = x0 + c;
+            if (gy < a.h && gx < a.w) {
+                unsigned s = 0;
+#pragma unroll
+                for (int k = 0; k < 7; k++) s += (unsigned)a.q[k] * hb[r + k][c];
+                bl[(long long)gy * a.blur_pitch + gx] = (uint8_t)min((s + 32768u) >> 16, 255u);
+            }
+        }
+    }
+#endif
+
+    // ---- 5. bilinear resize of the destination pixels whose source origin lies in this tile ----
+    if (a.dst) {
+        uint8_t* __restrict__ dst = a.dst + (long long)f * a.dst_fstride;
+        const int dx0 = a.dxs[blockIdx.x], dx1 = a.dxs[blockIdx.x + 1];
+        const int dy0 = a.dys[blockIdx.y], dy1 = a.dys[blockIdx.y + 1];
+        const int cx_i = tid & 63;
+        if (dx0 + cx_i < dx1) {
+            const int dx = dx0 + cx_i;
+            const int2 cx = a.xt[dx];
+            const int tx = cx.x - (x0 - HALO);
+            const int a0 = (short)(cx.y & 0xffff), a1 = cx.y >> 16;
+            for (int dy = dy0 + (tid >> 6); dy < dy1; dy += NT / 64) {
+                const int2 cy = a.yt[dy];
+                const int ty = cy.x - (y0 - HALO);
+                const int b0 = (short)(cy.y & 0xffff), b1 = cy.y >> 16;
+                const int h0 = tile[ty][tx] * a0 + tile[ty][tx + 1] * a1;
+                const int h1 = tile[ty + 1][tx] * a0 + tile[ty + 1][tx + 1] * a1;
+                const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
+                dst[(long long)dy * a.dst_pitch + dx] = (uint8_t)min(max(v, 0), 255);
+            }
+        }
+    }
+
+    if (!fast_tile) return;
+
+    // ---- 6. full arc score for the queued pixels ----
+    const int qn = s_qn;
+    for (int j = tid; j < qn; j += NT) {
+        const int pos = queue[j];
+        const int r = pos / SCW, c = pos - r * SCW;
+        const int m = fast_arc_score(tile, r + 3, c + 3);
+        sc[r][c] = (uint8_t)(m > a.minTh ? m : 0);
+    }
+    __syncthreads();
+
+    // ---- 7. cell-local 3x3 non-max suppression (strict '>') and emission ----
+    for (int j = tid; j < qn; j += NT) {
+        const int pos = queue[j];
+        const int r = pos / SCW, c = pos - r * SCW;
+        if (r < 1 || r > TH || c < 1 || c > TW) continue;       // halo ring: scored for neighbours only
+        const int m = sc[r][c];
+        if (!m) continue;
+        const int gx = x0 - 1 + c, gy = y0 - 1 + r;
+        const int cellx = (gx - 19) / a.wCell, celly = (gy - 19) / a.hCell;
+        bool keep = true;
+#pragma unroll
+        for (int dy = -1; dy <= 1; dy++)
+#pragma unroll
+            for (int dx = -1; dx <= 1; dx++) {
+                if (!dx && !dy) continue;
+                const int mq = sc[r + dy][c + dx];
+                if (mq >= m) {   // neighbour is a corner with score >= ours: it suppresses us iff it is in OUR cell
+                    if ((gx + dx - 19) / a.wCell == cellx && (gy + dy - 19) / a.hCell == celly) keep = false;
+                }
+            }
+#ifdef DBG_PRINT
+        {
+            const int m2 = fast_arc_score(tile, r + 3, c + 3);
+            const int gv = src[(long long)gy * a.src_pitch + gx];
+            if (gx == 599 && gy == 450) {
+                printf("GPU ring around (599,450) center %d:", tile[r+3][c+3]);
+                for (int yy = -3; yy <= 3; yy++) { printf("\n   "); for (int xx = -3; xx <= 3; xx++) printf("%4d", tile[r + 3 + yy][c + 3 + xx]); }
+                printf("\n sc=%d\n", m);
+            }
+            if ((m2 != m || gv != tile[r + 3][c + 3]) && blockIdx.x == 3 && blockIdx.y == 2)
+                printf("blk(%d,%d) j=%d pos=%d r=%d c=%d gx=%d gy=%d sc=%d recomputed=%d tilev=%d globalv=%d\n", blockIdx.x, blockIdx.y, j, pos, r, c, gx, gy, m, m2, tile[r + 3][c + 3], gv);
+        }
+#endif
+        if (keep) {
+            const int e = atomicAdd(&s_en, 1);
+            if (e < EMIT_CAP) emit[e] = ((unsigned)gy << 20) | ((unsigned)gx << 8) | (unsigned)m;
+        }
+    }
+    __syncthreads();
+    const int en = s_en;
+    if (en == 0) return;
+    if (tid == 0) s_ebase = atomicAdd(a.rec_count + (long long)f * a.rec_count_stride, en);
+    __syncthreads();
+    const int ebase = s_ebase;
+    uint32_t* __restrict__ rec = a.rec + (long long)f * a.rec_fstride;
+    for (int j = tid; j < min(en, EMIT_CAP); j += NT)
+        if (ebase + j < a.rec_cap) rec[ebase + j] = emit[j];
+}
+
+// =====================================================================================================
+// Octree distribution (ORBextractor.cpp:541-770).  Order-free formulation: the reference's result depends on the
+// keypoint ORDER only through "first maximum wins" inside a leaf (:751-767); since vKeys order is always the
+// cell-row-major / pixel-row-major input order (stable partitions, :512-528), the winner is the max-response point
+// with the smallest (cellRow, cellCol, y, x) key.  Node-list order (push_front of n1..n4, erase of the parent) and
+// the (count, creation-sequence) sort of :690 are reproduced exactly with scans.
+// =====================================================================================================
+constexpr int NTO = 256;
+constexpr int BIG_NODE = 512;
+
+struct OctArgs {
+    const LevelGeom* geom; int nlevels; int iniTh;
+    const uint32_t* rec; long long rec_fstride; const int* rec_count;
+    uint32_t* pts; long long pts_fstride;          // per level: 2 * rec_cap  (points + partition temp)
+    uint4* nodes; long long nodes_fstride;         // per level: node_cap       {x0|y0<<16, x1|y1<<16, begin, count}
+    int* iscr; long long iscr_fstride;             // per level: ISCR_PER_NODE * node_cap ints of scratch
+    uint8_t* cellflag; long long cellflag_fstride; // per level: nCols*nRows bytes at cell_off
+    const long long* node_off; const long long* cell_off;   // per-level offsets (elements)
+    int4* out; long long out_fstride;              // per level: out_cap  {x, y, response, 0} in level coordinates
+    int* out_count;                                // [frame][level]
+    int* status;                                   // [frame] sticky error bits (1: raw overflow, 2: node pool, 4: out cap)
+};
+constexpr int ISCR_PER_NODE = 12;
+
+__device__ __forceinline__ int warp_incl_scan(int v, int lane)
+{
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += t; }
+    return v;
+}
+// Exclusive scan over the block; returns the exclusive prefix and writes the block total.  All threads must call.
+__device__ __forceinline__ int block_excl_scan(int v, int* total, int* s_warp /*[NTO/32 + 1]*/)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int inc = warp_incl_scan(v, lane);
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < NTO / 32 ? s_warp[lane] : 0;
+        int wi = warp_incl_scan(w, lane);
+        if (lane < NTO / 32) s_warp[lane] = wi - w;
+        if (lane == NTO / 32 - 1) s_warp[NTO / 32] = wi;
+    }
+    __syncthreads();
+    const int r = s_warp[warp] + inc - v;
+    *total = s_warp[NTO / 32];
+    __syncthreads();
+    return r;
+}
+
+struct Quad { int c[4]; };
+
+__device__ __forceinline__ int pt_quadrant(uint32_t p, int midx, int midy)
+{
+    const int px = (p >> 8) & 0xfff, py = p >> 20;
+    return (px < midx ? 0 : 1) + (py < midy ? 0 : 2);
+}
+
+// One warp divides one node in place (via tmp): returns the 4 child counts; children occupy consecutive
+// sub-ranges [begin, begin+c0), ... in n1,n2,n3,n4 order.
+__device__ Quad warp_divide(uint32_t* pts, uint32_t* tmp, uint4 nd, int lane, bool scatter)
+{
+    const int x0 = nd.x & 0xffff, y0 = nd.x >> 16, x1 = nd.y & 0xffff, y1 = nd.y >> 16;
+    const int midx = x0 + ((x1 - x0 + 1) >> 1), midy = y0 + ((y1 - y0 + 1) >> 1);
+    const int begin = nd.z, count = nd.w;
+    Quad q; q.c[0] = q.c[1] = q.c[2] = q.c[3] = 0;
+    for (int i = lane; i < ((count + 31) & ~31); i += 32) {
+        int k = -1;
+        if (i < count) k = pt_quadrant(pts[begin + i], midx, midy);
+#pragma unroll
+        for (int j = 0; j < 4; j++) q.c[j] += __popc(__ballot_sync(0xffffffffu, k == j));
+    }
+    if (!scatter) return q;
+    int base[4] = {begin, begin + q.c[0], begin + q.c[0] + q.c[1], begin + q.c[0] + q.c[1] + q.c[2]};
+    for (int i = lane; i < ((count + 31) & ~31); i += 32) {
+        int k = -1; uint32_t p = 0;
+        if (i < count) { p = pts[begin + i]; k = pt_quadrant(p, midx, midy); }
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const unsigned b = __ballot_sync(0xffffffffu, k == j);
+            if (k == j) tmp[base[j] + __popc(b & ((1u << lane) - 1))] = p;
+            base[j] += __popc(b);
+        }
+    }
+    __syncwarp();
+    for (int i = lane; i < count; i += 32) pts[begin + i] = tmp[begin + i];
+    __syncwarp();
+    return q;
+}
+
+// The whole block divides one big node (unordered scatter: point order inside a node is irrelevant).
+__device__ Quad block_divide(uint32_t* pts, uint32_t* tmp, uint4 nd, int* s_cnt /*[8]*/)
+{
+    const int x0 = nd.x & 0xffff, y0 = nd.x >> 16, x1 = nd.y & 0xffff, y1 = nd.y >> 16;
+    const int midx = x0 + ((x1 - x0 + 1) >> 1), midy = y0 + ((y1 - y0 + 1) >> 1);
+    const int begin = nd.z, count = nd.w, lane = threadIdx.x & 31;
+    if (threadIdx.x < 8) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < ((count + NTO - 1) / NTO) * NTO; i += NTO) {
+        int k = -1;
+        if (i < count) k = pt_quadrant(pts[begin + i], midx, midy);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const unsigned b = __ballot_sync(0xffffffffu, k == j);
+            if (lane == 0 && b) atomicAdd(&s_cnt[j], __popc(b));
+        }
+    }
+    __syncthreads();
+    Quad q; for (int j = 0; j < 4; j++) q.c[j] = s_cnt[j];
+    __syncthreads();
+    if (threadIdx.x == 0) { s_cnt[4] = begin; s_cnt[5] = begin + q.c[0]; s_cnt[6] = begin + q.c[0] + q.c[1]; s_cnt[7] = begin + q.c[0] + q.c[1] + q.c[2]; }
+    __syncthreads();
+    for (int i = threadIdx.x; i < ((count + NTO - 1) / NTO) * NTO; i += NTO) {
+        int k = -1; uint32_t p = 0;
+        if (i < count) { p = pts[begin + i]; k = pt_quadrant(p, midx, midy); }
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const unsigned b = __ballot_sync(0xffffffffu, k == j);
+            int base = 0;
+            if (lane == 0 && b) base = atomicAdd(&s_cnt[4 + j], __popc(b));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (k == j) tmp[base + __popc(b & ((1u << lane) - 1))] = p;
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < count; i += NTO) pts[begin + i] = tmp[begin + i];
+    __syncthreads();
+    return q;
+}
+
+__device__ __forceinline__ uint4 make_child(uint4 p, int j, int begin, int count)
+{
+    const int x0 = p.x & 0xffff, y0 = p.x >> 16, x1 = p.y & 0xffff, y1 = p.y >> 16;
+    const int midx = x0 + ((x1 - x0 + 1) >> 1), midy = y0 + ((y1 - y0 + 1) >> 1);
+    const int cx0 = (j & 1) ? midx : x0, cx1 = (j & 1) ? x1 : midx;
+    const int cy0 = (j & 2) ? midy : y0, cy1 = (j & 2) ? y1 : midy;
+    return make_uint4((unsigned)cx0 | ((unsigned)cy0 << 16), (unsigned)cx1 | ((unsigned)cy1 << 16), (unsigned)begin, (unsigned)count);
+}
+
+__global__ void __launch_bounds__(NTO) octree_kernel(const __grid_constant__ OctArgs a)
+{
+    __shared__ int s_warp[NTO / 32 + 1];
+    __shared__ int s_cnt[8];
+    __shared__ int s_root[256];
+    __shared__ int s_n, s_misc[8];
+
+    const int L = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const LevelGeom g = a.geom[L];
+    int* out_count = a.out_count + (long long)f * a.nlevels + L;
+    int nraw = a.rec_count[(long long)f * a.nlevels + L];
+    if (nraw > g.rec_cap) { if (tid == 0) atomicOr(a.status + f, 1); nraw = g.rec_cap; }
+    if (g.nCols < 1 || nraw == 0) { if (tid == 0) *out_count = 0; return; }
+
+    const uint32_t* __restrict__ rec = a.rec + (long long)f * a.rec_fstride + g.rec_off;
+    uint32_t* pts = a.pts + (long long)f * a.pts_fstride + 2 * g.rec_off;
+    uint32_t* tmp = pts + g.rec_cap;
+    uint4* nodes = a.nodes + (long long)f * a.nodes_fstride + a.node_off[L];
+    int* iscr = a.iscr + (long long)f * a.iscr_fstride + a.node_off[L] * ISCR_PER_NODE;
+    const int NC = g.node_cap;
+    int* listA = iscr;            // node ids front -> back
+    int* listB = iscr + NC;
+    int* expl = iscr + 2 * NC;    // expandable node ids of this pass, list order   /  phase 2: processing order
+    int* nml = iscr + 3 * NC;     // kept (non-divided) node ids, list order
+    int* cand = iscr + 4 * NC;    // phase-2 candidates (children with > 1 point)
+    int* cq = iscr + 5 * NC;      // 4 child counts per divided node -> cq[4*e + j]   (4*NC ints)
+    int* cbase = iscr + 9 * NC;   // exclusive prefix of non-empty children
+    int* rank = iscr + 10 * NC;
+    int* bigl = iscr + 11 * NC;   // big nodes of this pass
+    uint8_t* cellflag = a.cellflag + (long long)f * a.cellflag_fstride + a.cell_off[L];
+    int4* out = a.out + (long long)f * a.out_fstride + g.out_off;
+
+    // ---- cell threshold fallback (ORBextractor.cpp:818-825): a cell uses the iniTh set if it is non-empty ----
+    const int ncell = g.nCols * g.nRows;
+    for (int i = tid; i < ncell; i += NTO) cellflag[i] = 0;
+    if (tid == 0) s_n = 0;
+    __syncthreads();
+    for (int i = tid; i < nraw; i += NTO) {
+        const uint32_t r = rec[i];
+        const int m = r & 0xff, x = (r >> 8) & 0xfff, y = r >> 20;
+        if (m > a.iniTh) cellflag[((y - 19) / g.hCell) * g.nCols + (x - 19) / g.wCell] = 1;
+    }
+    __syncthreads();
+    for (int i = tid; i < ((nraw + NTO - 1) / NTO) * NTO; i += NTO) {
+        bool keep = false; uint32_t r = 0;
+        if (i < nraw) {
+            r = rec[i];
+            const int m = r & 0xff, x = (r >> 8) & 0xfff, y = r >> 20;
+            keep = (m > a.iniTh) || !cellflag[((y - 19) / g.hCell) * g.nCols + (x - 19) / g.wCell];
+        }
+        const unsigned b = __ballot_sync(0xffffffffu, keep);
+        int base = 0;
+        if (lane == 0 && b) base = atomicAdd(&s_n, __popc(b));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (keep) {
+            const int m = r & 0xff, x = (r >> 8) & 0xfff, y = r >> 20;
+            tmp[base + __popc(b & ((1u << lane) - 1))] = ((unsigned)(y - 16) << 20) | ((unsigned)(x - 16) << 8) | (unsigned)m;
+        }
+    }
+    __syncthreads();
+    const int n = s_n;
+    if (n == 0) { if (tid == 0) *out_count = 0; return; }
+
+    // ---- roots (ORBextractor.cpp:545-587) ----
+    const int nIni = g.nIni;
+    for (int i = tid; i < nIni; i += NTO) s_root[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += NTO) {
+        const int rx = (tmp[i] >> 8) & 0xfff;
+        int ri = (int)__fdiv_rn((float)rx, g.hX);
+        ri = min(ri, nIni - 1);
+        atomicAdd(&s_root[ri], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int acc = 0, size = 0;
+        for (int i = 0; i < nIni; i++) {
+            const int c = s_root[i];
+            if (c > 0) {
+                const int rx0 = (int)__fmul_rn(g.hX, (float)i), rx1 = (int)__fmul_rn(g.hX, (float)(i + 1));
+                nodes[size] = make_uint4((unsigned)rx0, (unsigned)rx1 | ((unsigned)(g.h - 32) << 16), (unsigned)acc, (unsigned)c);
+                listA[size] = size;
+                size++;
+            }
+            s_root[i] = acc;          // becomes the scatter cursor
+            acc += c;
+        }
+        s_misc[0] = size;
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += NTO) {
+        const uint32_t p = tmp[i];
+        const int rx = (p >> 8) & 0xfff;
+        int ri = (int)__fdiv_rn((float)rx, g.hX);
+        ri = min(ri, nIni - 1);
+        pts[atomicAdd(&s_root[ri], 1)] = p;
+    }
+    __syncthreads();
+
+    int size = s_misc[0];
+    int nodeCount = size;
+    int* list = listA; int* nlist = listB;
+    const int N = g.quota;
+    int K = 0;                  // phase-2 candidate count
+    bool finish = false, phase2 = false, poolFull = false;
+
+    // ---- phase 1: divide every node with more than one point (ORBextractor.cpp:595-677) ----
+    while (!finish && !phase2) {
+        const int prevSize = size;
+        // classify list entries (ordered compaction into expandable / kept)
+        int E = 0, M = 0;
+        for (int base = 0; base < size; base += NTO) {
+            const int i = base + tid;
+            int id = -1, flag = 0;
+            if (i < size) { id = list[i]; flag = nodes[id].w > 1; }
+            int tot;
+            const int ex = block_excl_scan(flag, &tot, s_warp);
+            if (i < size) { if (flag) expl[E + ex] = id; else nml[M + (i - base) - ex] = id; }
+            const int chunk = min(NTO, size - base);
+            E += tot; M += chunk - tot;
+        }
+        if (nodeCount + 4 * E > NC) { poolFull = true; break; }
+        __syncthreads();
+        // divide: big nodes by the whole block, the rest one warp each
+        if (tid == 0) s_misc[1] = 0;
+        __syncthreads();
+        for (int e = tid; e < E; e += NTO)
+            if (nodes[expl[e]].w >= BIG_NODE) bigl[atomicAdd(&s_misc[1], 1)] = e;
+        __syncthreads();
+        const int nbig = s_misc[1];
+        for (int b = 0; b < nbig; b++) {
+            const int e = bigl[b];
+            const Quad q = block_divide(pts, tmp, nodes[expl[e]], s_cnt);
+            if (tid == 0) { cq[4 * e] = q.c[0]; cq[4 * e + 1] = q.c[1]; cq[4 * e + 2] = q.c[2]; cq[4 * e + 3] = q.c[3]; }
+        }
+        for (int e = warp; e < E; e += NTO / 32) {
+            const uint4 nd = nodes[expl[e]];
+            if (nd.w >= BIG_NODE) continue;
+            const Quad q = warp_divide(pts, tmp, nd, lane, true);
+            if (lane == 0) { cq[4 * e] = q.c[0]; cq[4 * e + 1] = q.c[1]; cq[4 * e + 2] = q.c[2]; cq[4 * e + 3] = q.c[3]; }
+        }
+        __syncthreads();
+        // children ids in creation order (parents front->back, n1..n4)
+        int C = 0;
+        for (int base = 0; base < E; base += NTO) {
+            const int e = base + tid;
+            int c = 0;
+            if (e < E) c = (cq[4 * e] > 0) + (cq[4 * e + 1] > 0) + (cq[4 * e + 2] > 0) + (cq[4 * e + 3] > 0);
+            int tot;
+            const int ex = block_excl_scan(c, &tot, s_warp);
+            if (e < E) cbase[e] = C + ex;
+            C += tot;
+        }
+        if (tid == 0) { s_misc[2] = 0; s_misc[3] = 0; }
+        __syncthreads();
+        for (int e = tid; e < E; e += NTO) {
+            const uint4 p = nodes[expl[e]];
+            int k = cbase[e], begin = p.z, nexp = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int c = cq[4 * e + j];
+                if (c > 0) {
+                    const int id = nodeCount + k;
+                    nodes[id] = make_child(p, j, begin, c);
+                    nlist[C - 1 - k] = id;                 // push_front: newest child is the list front
+                    if (c > 1) { nexp++; cand[atomicAdd(&s_misc[3], 1)] = id; }
+                    k++; begin += c;
+                }
+            }
+            if (nexp) atomicAdd(&s_misc[2], nexp);
+        }
+        for (int i = tid; i < M; i += NTO) nlist[C + i] = nml[i];
+        __syncthreads();
+        const int nToExpand = s_misc[2];
+        K = s_misc[3];
+        nodeCount += C;
+        size = C + M;
+        { int* t = list; list = nlist; nlist = t; }
+        if (size >= N || size == prevSize) finish = true;
+        else if (size + nToExpand * 3 > N) phase2 = true;
+        __syncthreads();
+    }
+
+    // ---- phase 2: split the largest nodes first until N is reached (ORBextractor.cpp:678-745) ----
+    while (!finish && !poolFull) {
+        const int prevSize = size;
+        if (nodeCount + 4 * K > NC) { poolFull = true; break; }
+        // child counts of every candidate (no scatter yet)
+        if (tid == 0) s_misc[1] = 0;
+        __syncthreads();
+        for (int k = tid; k < K; k += NTO)
+            if (nodes[cand[k]].w >= BIG_NODE) bigl[atomicAdd(&s_misc[1], 1)] = k;
+        __syncthreads();
+        const int nbig = s_misc[1];
+        for (int k = warp; k < K; k += NTO / 32) {
+            const uint4 nd = nodes[cand[k]];
+            const Quad q = warp_divide(pts, tmp, nd, lane, false);
+            if (lane == 0) { cq[4 * k] = q.c[0]; cq[4 * k + 1] = q.c[1]; cq[4 * k + 2] = q.c[2]; cq[4 * k + 3] = q.c[3]; }
+        }
+        __syncthreads();
+        // sort by (count, creation sequence) ascending; process from the back (ORBextractor.cpp:690-691)
+        for (int k = tid; k < K; k += NTO) {
+            const int idk = cand[k];
+            const unsigned long long key = ((unsigned long long)nodes[idk].w << 32) | (unsigned)idk;
+            int r = 0;
+            for (int j = 0; j < K; j++) {
+                const int idj = cand[j];
+                r += (((unsigned long long)nodes[idj].w << 32) | (unsigned)idj) < key;
+            }
+            expl[K - 1 - r] = k;            // expl[t] = candidate processed t-th
+        }
+        __syncthreads();
+        // how many get processed before lNodes.size() >= N (the `break` at :739-740)
+        if (tid == 0) s_misc[4] = K;
+        __syncthreads();
+        int P = 0;
+        for (int base = 0; base < K; base += NTO) {
+            const int t = base + tid;
+            int c = 0;
+            if (t < K) { const int k = expl[t]; c = (cq[4 * k] > 0) + (cq[4 * k + 1] > 0) + (cq[4 * k + 2] > 0) + (cq[4 * k + 3] > 0); }
+            int tot;
+            const int ex = block_excl_scan(c, &tot, s_warp);
+            if (t < K) {
+                cbase[t] = P + ex;
+                if (size + (P + ex + c) - (t + 1) >= N) atomicMin(&s_misc[4], t + 1);
+            }
+            P += tot;
+        }
+        __syncthreads();
+        const int T = s_misc[4];           // nodes actually divided this round
+        if (tid == 0) { s_misc[2] = 0; s_misc[3] = 0; }
+        __syncthreads();
+        // scatter the divided nodes
+        for (int b = 0; b < nbig; b++) {
+            const int k = bigl[b];
+            // processed iff its position in expl is < T
+            bool proc = false;
+            for (int t = 0; t < T; t++) if (expl[t] == k) { proc = true; break; }
+            if (proc) (void)block_divide(pts, tmp, nodes[cand[k]], s_cnt);
+        }
+        for (int t = warp; t < T; t += NTO / 32) {
+            const uint4 nd = nodes[cand[expl[t]]];
+            if (nd.w >= BIG_NODE) continue;
+            (void)warp_divide(pts, tmp, nd, lane, true);
+        }
+        __syncthreads();
+        int C = 0;
+        if (T > 0) { const int k = expl[T - 1]; C = cbase[T - 1] + (cq[4 * k] > 0) + (cq[4 * k + 1] > 0) + (cq[4 * k + 2] > 0) + (cq[4 * k + 3] > 0); }
+        // create children (creation order = processing order), mark parents erased
+        for (int t = tid; t < T; t += NTO) {
+            const int k = expl[t];
+            const int pid = cand[k];
+            const uint4 p = nodes[pid];
+            int kk = cbase[t], begin = p.z;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int c = cq[4 * k + j];
+                if (c > 0) {
+                    const int id = nodeCount + kk;
+                    nodes[id] = make_child(p, j, begin, c);
+                    nlist[C - 1 - kk] = id;
+                    if (c > 1) rank[atomicAdd(&s_misc[3], 1)] = id;     // next round's candidates
+                    kk++; begin += c;
+                }
+            }
+            nodes[pid].w = 0;                                           // erased (lNodes.erase(...->lit), :736)
+        }
+        __syncthreads();
+        // surviving old nodes keep their relative order behind the new children
+        int M = 0;
+        for (int base = 0; base < size; base += NTO) {
+            const int i = base + tid;
+            int id = -1, flag = 0;
+            if (i < size) { id = list[i]; flag = nodes[id].w > 0; }
+            int tot;
+            const int ex = block_excl_scan(flag, &tot, s_warp);
+            if (flag) nlist[C + M + ex] = id;
+            M += tot;
+        }
+        __syncthreads();
+        const int newK = s_misc[3];
+        for (int k = tid; k < newK; k += NTO) cand[k] = rank[k];
+        nodeCount += C;
+        size = C + M;
+        K = newK;
+        { int* t = list; list = nlist; nlist = t; }
+        if (size >= N || size == prevSize) finish = true;
+        __syncthreads();
+    }
+    if (poolFull && tid == 0) atomicOr(a.status + f, 2);
+
+    // ---- best point per node, list order (ORBextractor.cpp:748-767) ----
+    if (size > g.out_cap) { if (tid == 0) atomicOr(a.status + f, 4); size = g.out_cap; }
+    for (int i = tid; i < size; i += NTO) {
+        const uint4 nd = nodes[list[i]];
+        int bm = -1; unsigned long long bkey = 0; uint32_t bp = 0;
+        for (unsigned j = 0; j < nd.w; j++) {
+            const uint32_t p = pts[nd.z + j];
+            const int m = p & 0xff, x = ((p >> 8) & 0xfff) + 16, y = (p >> 20) + 16;
+            const unsigned long long key = ((unsigned long long)(((y - 19) / g.hCell) * g.nCols + (x - 19) / g.wCell) << 24) | ((unsigned)y << 12) | (unsigned)x;
+            if (m > bm || (m == bm && key < bkey)) { bm = m; bkey = key; bp = p; }
+        }
+        out[i] = make_int4((int)((bp >> 8) & 0xfff) + 16, (int)(bp >> 20) + 16, bm - 1, 0);
+    }
+    if (tid == 0) *out_count = size;
+}
+
+// =====================================================================================================
+// Orientation + descriptor + final gather, one warp per keypoint.
+// =====================================================================================================
+struct DescArgs {
+    const LevelGeom* geom; int nlevels;
+    const uint8_t* src0; long long src0_pitch, src0_fstride;     // level 0 = the caller's image
+    const uint8_t* pyr; long long pyr_fstride;                   // levels >= 1
+    const uint8_t* blur; long long blur_fstride;
+    const int4* lvl; long long lvl_fstride; const int* lvl_count;  // octree output
+    orbx_keypoint* kps; uint8_t* desc; int* counts; int capacity;  // final output, frame f at f*capacity
+    float factorPI;
+};
+
+__device__ __forceinline__ float fast_atan2_deg(float y, float x)
+{
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a;
+    if (ax >= ay) {
+        const float c = __fdiv_rn(ay, __fadd_rn(ax, 2.2204460492503131e-16f));
+        const float c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(c_atan[3], c2), c_atan[2]), c2), c_atan[1]), c2), c_atan[0]), c);
+    } else {
+        const float c = __fdiv_rn(ax, __fadd_rn(ay, 2.2204460492503131e-16f));
+        const float c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(c_atan[3], c2), c_atan[2]), c2), c_atan[1]), c2), c_atan[0]), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+__global__ void __launch_bounds__(256) orient_desc_kernel(const __grid_constant__ DescArgs a)
+{
+    const int f = blockIdx.y, lane = threadIdx.x & 31;
+    const int wid = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    // locate (level, index) from the per-level counts
+    const int* cnt = a.lvl_count + (long long)f * a.nlevels;
+    int level = -1, idx = 0, acc = 0, total = 0;
+    for (int l = 0; l < a.nlevels; l++) {
+        const int c = cnt[l];
+        if (level < 0 && wid < acc + c) { level = l; idx = wid - acc; }
+        acc += c;
+    }
+    total = acc;
+    if (wid == 0 && lane == 0) a.counts[f] = total;
+    if (level < 0 || wid >= a.capacity) return;
+
+    const LevelGeom g = a.geom[level];
+    const int4 k = a.lvl[(long long)f * a.lvl_fstride + g.out_off + idx];
+    const uint8_t* img; long long pitch;
+    if (level == 0) { img = a.src0 + (long long)f * a.src0_fstride; pitch = a.src0_pitch; }
+    else { img = a.pyr + (long long)f * a.pyr_fstride + g.off; pitch = g.pitch; }
+
+    // IC_Angle: lane l handles patch row v = l - 15
+    int s_u = 0, s_1 = 0;
+    const int v = lane - 15;
+    if (lane < 31) {
+        const int d = c_umax[abs(v)];
+        const uint8_t* row = img + (long long)(k.y + v) * pitch + k.x;
+        for (int u = -d; u <= d; u++) { const int val = row[u]; s_u += u * val; s_1 += val; }
+    }
+    int m10 = s_u, m01 = v * s_1;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // steered BRIEF: lane i computes descriptor byte i
+    const float ar = __fmul_rn(angle, a.factorPI);
+    const float ca = (float)cos((double)ar), sb = (float)sin((double)ar);
+    const uint8_t* bimg = a.blur + (long long)f * a.blur_fstride + g.off;
+    const uint8_t* center = bimg + (long long)k.y * g.pitch + k.x;
+    const int8_t* pat = c_pattern + lane * 32;
+    int val = 0;
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+        const float x0 = (float)pat[4 * b], y0 = (float)pat[4 * b + 1], x1 = (float)pat[4 * b + 2], y1 = (float)pat[4 * b + 3];
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
+        const int t0 = center[(long long)r0 * g.pitch + c0], t1 = center[(long long)r1 * g.pitch + c1];
+        val |= (t0 < t1) << b;
+    }
+    const long long o = (long long)f * a.capacity + wid;
+    a.desc[o * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        orbx_keypoint kp;
+        kp.x = level ? __fmul_rn((float)k.x, g.scale) : (float)k.x;
+        kp.y = level ? __fmul_rn((float)k.y, g.scale) : (float)k.y;
+        kp.size = g.size; kp.angle = angle; kp.response = (float)k.z; kp.octave = level; kp.class_id = -1;
+        a.kps[o] = kp;
+    }
+}
+
+}  // namespace orbb

@@ -1,0 +1,370 @@
+// match.cu — host side of the matcher half of liborbb200 (C ABI of include/orbb200.h, section "matcher").
+// Replaces the Hamming core of ORB_SLAM2::ORBmatcher / Frame (reference src/ORBmatcher.cpp, src/Frame.cpp).
+#include "match_kernels.cuh"
+#include <stdlib.h>
+
+using namespace orbb;
+
+// ---- internal accessors into orbx_handle (defined in extract.cu) -------------------------------------
+extern "C" int orbx__pyramid_view(orbx_handle* h, const LevelGeom** geom_host, const LevelGeom** geom_dev, int* nlevels,
+                                  const uint8_t** src0, long long* src0_pitch, const uint8_t** pyr, int* device,
+                                  const float** scale, const float** inv_scale, void** stream);
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes) { ORBB_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); return ORBB_OK; }
+    template <typename T> T* as() { return (T*)p; }
+};
+
+int check_device(int device)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n < 1 || device < 0 || device >= n) {
+        cudaGetLastError();
+        set_cuda_error(cudaErrorNoDevice, "no CUDA device (liborbb200 has no CPU fallback)");
+        return ORBB_E_CUDA;
+    }
+    ORBB_CUDA(cudaSetDevice(device));
+    return ORBB_OK;
+}
+
+}  // namespace
+
+extern "C" int orbm_distance_pairs(const uint8_t* a_host, const uint8_t* b_host, int n, int32_t* out_host, int device)
+{
+    if (n < 0 || (n > 0 && (!a_host || !b_host || !out_host))) return ORBB_E_INVALID;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    if (n == 0) return ORBB_OK;
+    DevBuf a, b, o;
+    if ((rc = a.alloc((size_t)n * 32)) || (rc = b.alloc((size_t)n * 32)) || (rc = o.alloc((size_t)n * 4))) return rc;
+    ORBB_CUDA(cudaMemcpy(a.p, a_host, (size_t)n * 32, cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(b.p, b_host, (size_t)n * 32, cudaMemcpyHostToDevice));
+    hamming_pairs_kernel<<<ceil_div(n, 256), 256>>>(a.as<uint4>(), b.as<uint4>(), n, o.as<int>());
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    ORBB_CUDA(cudaMemcpy(out_host, o.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return ORBB_OK;
+}
+
+// ---- frame -------------------------------------------------------------------------------------------
+struct orbm_frame {
+    int device = 0, n = 0;
+    FrameDev f{};
+    DevBuf kps, desc, cell_of, cell_start, cell_items, cursor;
+};
+
+extern "C" int orbm_frame_create(orbm_frame** out, const orbx_keypoint* kps, const uint8_t* desc, int n,
+                                 float min_x, float min_y, float max_x, float max_y, int device)
+{
+    if (!out || n < 0 || (n > 0 && (!kps || !desc)) || !(max_x > min_x) || !(max_y > min_y)) return ORBB_E_INVALID;
+    *out = nullptr;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    orbm_frame* fr = new (std::nothrow) orbm_frame();
+    if (!fr) return ORBB_E_NOMEM;
+    fr->device = device; fr->n = n;
+    const int NC = GRID_COLS * GRID_ROWS;
+    if ((rc = fr->kps.alloc((size_t)n * sizeof(orbx_keypoint))) || (rc = fr->desc.alloc((size_t)n * 32)) ||
+        (rc = fr->cell_of.alloc((size_t)n * 4)) || (rc = fr->cell_start.alloc((size_t)(NC + 1) * 4)) ||
+        (rc = fr->cell_items.alloc((size_t)n * 4)) || (rc = fr->cursor.alloc((size_t)NC * 4))) { delete fr; return rc; }
+    FrameDev& f = fr->f;
+    f.kps = fr->kps.as<orbx_keypoint>(); f.desc = fr->desc.as<uint4>(); f.n = n;
+    f.minX = min_x; f.minY = min_y;
+    // Frame.cpp:115-116 (mfGridElementWidthInv / HeightInv)
+    f.invW = static_cast<float>(GRID_COLS) / static_cast<float>(max_x - min_x);
+    f.invH = static_cast<float>(GRID_ROWS) / static_cast<float>(max_y - min_y);
+    f.cell_of = fr->cell_of.as<int>(); f.cell_start = fr->cell_start.as<int>(); f.cell_items = fr->cell_items.as<int>();
+    auto fail = [&](int code) { delete fr; return code; };
+    if (n > 0) {
+        if (cudaMemcpy(fr->kps.p, kps, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice) != cudaSuccess) return fail(ORBB_E_CUDA);
+        if (cudaMemcpy(fr->desc.p, desc, (size_t)n * 32, cudaMemcpyHostToDevice) != cudaSuccess) return fail(ORBB_E_CUDA);
+    }
+    if (cudaMemset(fr->cursor.p, 0, (size_t)NC * 4) != cudaSuccess) return fail(ORBB_E_CUDA);
+    if (n > 0) { grid_assign_kernel<<<ceil_div(n, 256), 256>>>(f, fr->cursor.as<int>()); ORBB_LAUNCHED(); }
+    grid_scan_kernel<<<1, 1024>>>(fr->cursor.as<int>(), f.cell_start); ORBB_LAUNCHED();
+    if (n > 0) {
+        grid_fill_kernel<<<ceil_div(n, 256), 256>>>(f, fr->cursor.as<int>()); ORBB_LAUNCHED();
+        grid_sort_kernel<<<ceil_div(NC, 256), 256>>>(f); ORBB_LAUNCHED();
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { set_cuda_error(e, "orbm_frame_create"); return fail(ORBB_E_CUDA); }
+    *out = fr;
+    return ORBB_OK;
+}
+
+extern "C" int orbm_frame_destroy(orbm_frame* f)
+{
+    if (!f) return ORBB_E_INVALID;
+    cudaSetDevice(f->device);
+    delete f;
+    return ORBB_OK;
+}
+
+extern "C" int orbm_window_search(const orbm_frame* fr, const orbm_query* q_host, int nq, int32_t* offs_host,
+                                  int32_t* idx_host, int32_t* dist_host, int cap)
+{
+    if (!fr || nq < 0 || !offs_host || cap < 0 || (nq > 0 && !q_host) || (cap > 0 && (!idx_host || !dist_host))) return ORBB_E_INVALID;
+    int rc = check_device(fr->device);
+    if (rc != ORBB_OK) return rc;
+    if (nq == 0) { offs_host[0] = 0; return ORBB_OK; }
+    DevBuf q, counts, offs, idx, dist;
+    if ((rc = q.alloc((size_t)nq * sizeof(orbm_query))) || (rc = counts.alloc((size_t)nq * 4)) || (rc = offs.alloc((size_t)(nq + 1) * 4)) ||
+        (rc = idx.alloc((size_t)cap * 4)) || (rc = dist.alloc((size_t)cap * 4))) return rc;
+    ORBB_CUDA(cudaMemcpy(q.p, q_host, (size_t)nq * sizeof(orbm_query), cudaMemcpyHostToDevice));
+    const int wpb = 8;
+    window_search_kernel<false><<<ceil_div(nq, wpb), wpb * 32>>>(fr->f, q.as<orbm_query>(), nq, counts.as<int>(), nullptr, nullptr, nullptr, 0);
+    ORBB_LAUNCHED();
+    excl_scan_kernel<<<1, 1024>>>(counts.as<int>(), offs.as<int>(), nq);
+    ORBB_LAUNCHED();
+    window_search_kernel<true><<<ceil_div(nq, wpb), wpb * 32>>>(fr->f, q.as<orbm_query>(), nq, nullptr, offs.as<int>(), idx.as<int>(), dist.as<int>(), cap);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    ORBB_CUDA(cudaMemcpy(offs_host, offs.p, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost));
+    const int total = offs_host[nq];
+    const int m = total < cap ? total : cap;
+    if (m > 0) {
+        ORBB_CUDA(cudaMemcpy(idx_host, idx.p, (size_t)m * 4, cudaMemcpyDeviceToHost));
+        ORBB_CUDA(cudaMemcpy(dist_host, dist.p, (size_t)m * 4, cudaMemcpyDeviceToHost));
+    }
+    return total > cap ? ORBB_E_CAPACITY : ORBB_OK;
+}
+
+// ---- stereo ------------------------------------------------------------------------------------------
+extern "C" int orbm_stereo_match(orbx_handle* left, orbx_handle* right, const orbx_keypoint* kL, const uint8_t* dL, int nL,
+                                 const orbx_keypoint* kR, const uint8_t* dR, int nR, float mbf, float mb,
+                                 float* uR_host, float* depth_host)
+{
+    if (!left || !right || nL < 0 || nR < 0 || (nL > 0 && (!kL || !dL || !uR_host || !depth_host)) || (nR > 0 && (!kR || !dR))) return ORBB_E_INVALID;
+    if (nR >= 65536) return ORBB_E_CAPACITY;
+    const LevelGeom *ghL, *gdL, *ghR, *gdR; int nlL, nlR, devL, devR; const uint8_t *s0L, *s0R, *pL, *pR; long long spL, spR;
+    const float *scL, *iscL, *scR, *iscR; void *stL, *stR;
+    int rc = orbx__pyramid_view(left, &ghL, &gdL, &nlL, &s0L, &spL, &pL, &devL, &scL, &iscL, &stL);
+    if (rc != ORBB_OK) return rc;
+    rc = orbx__pyramid_view(right, &ghR, &gdR, &nlR, &s0R, &spR, &pR, &devR, &scR, &iscR, &stR);
+    if (rc != ORBB_OK) return rc;
+    if (devL != devR || nlL != nlR || ghL[0].w != ghR[0].w || ghL[0].h != ghR[0].h) return ORBB_E_STATE;
+    rc = check_device(devL);
+    if (rc != ORBB_OK) return rc;
+    if (nL == 0) return ORBB_OK;
+    ORBB_CUDA(cudaStreamSynchronize((cudaStream_t)stL));
+    ORBB_CUDA(cudaStreamSynchronize((cudaStream_t)stR));
+    DevBuf bkL, bdL, bkR, bdR, bu, bd, bs, bi, bb;
+    if ((rc = bkL.alloc((size_t)nL * sizeof(orbx_keypoint))) || (rc = bdL.alloc((size_t)nL * 32)) ||
+        (rc = bkR.alloc((size_t)nR * sizeof(orbx_keypoint))) || (rc = bdR.alloc((size_t)nR * 32)) ||
+        (rc = bu.alloc((size_t)nL * 4)) || (rc = bd.alloc((size_t)nL * 4)) || (rc = bs.alloc((size_t)nL * 4)) ||
+        (rc = bi.alloc((size_t)nL * 4)) || (rc = bb.alloc((size_t)nL * 4))) return rc;
+    ORBB_CUDA(cudaMemcpy(bkL.p, kL, (size_t)nL * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(bdL.p, dL, (size_t)nL * 32, cudaMemcpyHostToDevice));
+    if (nR > 0) {
+        ORBB_CUDA(cudaMemcpy(bkR.p, kR, (size_t)nR * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
+        ORBB_CUDA(cudaMemcpy(bdR.p, dR, (size_t)nR * 32, cudaMemcpyHostToDevice));
+    }
+    StereoArgs a;
+    memset(&a, 0, sizeof a);
+    a.kL = bkL.as<orbx_keypoint>(); a.dL = bdL.as<uint4>(); a.nL = nL;
+    a.kR = bkR.as<orbx_keypoint>(); a.dR = bdR.as<uint4>(); a.nR = nR;
+    a.geom = gdL; a.nlevels = nlL; a.nRows = ghL[0].h;
+    a.src0L = s0L; a.src0L_pitch = spL; a.pyrL = pL;
+    a.src0R = s0R; a.src0R_pitch = spR; a.pyrR = pR;
+    for (int i = 0; i < nlL; i++) { a.scale[i] = scL[i]; a.inv_scale[i] = iscL[i]; }
+    // Frame.cpp:579-581: minZ = mb, minD = 0, maxD = mbf/minZ (mb == 0 at the reference's call => +inf)
+    a.mbf = mbf; a.minD = 0.f; a.maxD = mbf / mb;
+    a.uRight = bu.as<float>(); a.depth = bd.as<float>(); a.sad = bs.as<int>(); a.bestIdx = bi.as<int>(); a.bestDist = bb.as<int>();
+    stereo_match_kernel<<<ceil_div(nL, 8), 256>>>(a);
+    ORBB_LAUNCHED();
+    const float k21 = 1.5f * 1.4f;
+    stereo_median_filter_kernel<<<1, 256>>>(nL, a.sad, a.uRight, a.depth, k21);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    ORBB_CUDA(cudaMemcpy(uR_host, bu.p, (size_t)nL * 4, cudaMemcpyDeviceToHost));
+    ORBB_CUDA(cudaMemcpy(depth_host, bd.p, (size_t)nL * 4, cudaMemcpyDeviceToHost));
+    return ORBB_OK;
+}
+
+// ---- brute-force database ----------------------------------------------------------------------------
+struct orbm_db {
+    int device = 0;
+    int64_t capacity = 0, rows = 0, row_offset = 0;
+    uint4* d_rows = nullptr;
+    // scratch for queries / partial results, grown on demand
+    int nq_cap = 0, chunk_cap = 0;
+    uint4* d_q = nullptr; unsigned *d_k1 = nullptr, *d_k2 = nullptr;
+    int *d_d1 = nullptr, *d_d2 = nullptr; long long* d_i1 = nullptr;
+    int variant = 0;
+};
+
+extern "C" int orbm_db_create(orbm_db** out, int64_t capacity_rows, int64_t row_offset, int device)
+{
+    if (!out || capacity_rows < 0 || row_offset < 0) return ORBB_E_INVALID;
+    *out = nullptr;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    orbm_db* db = new (std::nothrow) orbm_db();
+    if (!db) return ORBB_E_NOMEM;
+    db->device = device; db->capacity = capacity_rows; db->row_offset = row_offset;
+    const char* v = getenv("ORBB_BF_VARIANT");
+    db->variant = v ? atoi(v) : 1;
+    if (cudaMalloc((void**)&db->d_rows, (size_t)(capacity_rows > 0 ? capacity_rows : 1) * 32) != cudaSuccess) {
+        set_cuda_error(cudaGetLastError(), "orbm_db_create: cudaMalloc");
+        delete db;
+        return ORBB_E_NOMEM;
+    }
+    *out = db;
+    return ORBB_OK;
+}
+
+extern "C" int orbm_db_destroy(orbm_db* db)
+{
+    if (!db) return ORBB_E_INVALID;
+    cudaSetDevice(db->device);
+    cudaFree(db->d_rows); cudaFree(db->d_q); cudaFree(db->d_k1); cudaFree(db->d_k2); cudaFree(db->d_d1); cudaFree(db->d_d2); cudaFree(db->d_i1);
+    delete db;
+    return ORBB_OK;
+}
+
+extern "C" int64_t orbm_db_rows(const orbm_db* db) { return db ? db->rows : -1; }
+
+static int db_append(orbm_db* db, const uint8_t* rows, int64_t n, cudaMemcpyKind kind)
+{
+    if (!db || n < 0 || (n > 0 && !rows)) return ORBB_E_INVALID;
+    if (db->rows + n > db->capacity) return ORBB_E_CAPACITY;
+    ORBB_CUDA(cudaSetDevice(db->device));
+    if (n > 0) ORBB_CUDA(cudaMemcpy((uint8_t*)db->d_rows + (size_t)db->rows * 32, rows, (size_t)n * 32, kind));
+    db->rows += n;
+    return ORBB_OK;
+}
+extern "C" int orbm_db_append(orbm_db* db, const uint8_t* rows_host, int64_t n) { return db_append(db, rows_host, n, cudaMemcpyHostToDevice); }
+extern "C" int orbm_db_append_device(orbm_db* db, const uint8_t* rows_dev, int64_t n) { return db_append(db, rows_dev, n, cudaMemcpyDeviceToDevice); }
+
+static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nchunks)
+{
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, db->device);
+    const int qtiles = ceil_div(nq, BF_QTILE);
+    int target = ceil_div(sms * 4, qtiles);                         // ~4 CTAs per SM in flight
+    long long rpc = (db->rows + target - 1) / target;
+    rpc = (rpc + BF_ROWS - 1) / BF_ROWS * BF_ROWS;
+    if (rpc < BF_ROWS) rpc = BF_ROWS;
+    if (rpc > (1ll << BF_IDX_BITS)) rpc = 1ll << BF_IDX_BITS;
+    *rows_per_chunk = rpc;
+    *nchunks = (int)((db->rows + rpc - 1) / rpc);
+    if (*nchunks < 1) *nchunks = 1;
+    return ORBB_OK;
+}
+
+static int db_reserve(orbm_db* db, int nq, int nchunks)
+{
+    if (nq > db->nq_cap) {
+        cudaFree(db->d_q); cudaFree(db->d_d1); cudaFree(db->d_d2); cudaFree(db->d_i1);
+        db->d_q = nullptr; db->d_d1 = db->d_d2 = nullptr; db->d_i1 = nullptr; db->nq_cap = 0;
+        ORBB_CUDA(cudaMalloc((void**)&db->d_q, (size_t)nq * 32));
+        ORBB_CUDA(cudaMalloc((void**)&db->d_d1, (size_t)nq * 4));
+        ORBB_CUDA(cudaMalloc((void**)&db->d_d2, (size_t)nq * 4));
+        ORBB_CUDA(cudaMalloc((void**)&db->d_i1, (size_t)nq * 8));
+        db->nq_cap = nq;
+        db->chunk_cap = 0;
+    }
+    if ((long long)nq * nchunks > (long long)db->chunk_cap) {
+        cudaFree(db->d_k1); cudaFree(db->d_k2); db->d_k1 = db->d_k2 = nullptr; db->chunk_cap = 0;
+        ORBB_CUDA(cudaMalloc((void**)&db->d_k1, (size_t)db->nq_cap * nchunks * 4));
+        ORBB_CUDA(cudaMalloc((void**)&db->d_k2, (size_t)db->nq_cap * nchunks * 4));
+        db->chunk_cap = db->nq_cap * nchunks;
+    }
+    return ORBB_OK;
+}
+
+extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int nq, int32_t* d1, int64_t* i1, int32_t* d2, void* stream)
+{
+    orbm_db* db = const_cast<orbm_db*>(cdb);
+    if (!db || nq < 0 || (nq > 0 && (!q_dev || !d1 || !i1 || !d2))) return ORBB_E_INVALID;
+    if (nq == 0) return ORBB_OK;
+    ORBB_CUDA(cudaSetDevice(db->device));
+    long long rpc; int nchunks;
+    db_plan(db, nq, &rpc, &nchunks);
+    int rc = db_reserve(db, nq, nchunks);
+    if (rc != ORBB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    BfArgs a;
+    a.db = db->d_rows; a.nrows = db->rows; a.q = (const uint4*)q_dev; a.nq = nq;
+    a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = db->d_k1; a.part_k2 = db->d_k2;
+    dim3 grid(ceil_div(nq, BF_QTILE), nchunks);
+    if (db->variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
+    else bf_top2_kernel<1><<<grid, BF_THREADS, 0, st>>>(a);
+    ORBB_LAUNCHED();
+    bf_merge_chunks_kernel<<<ceil_div(nq, 256), 256, 0, st>>>(db->d_k1, db->d_k2, nchunks, nq, rpc, db->row_offset, d1, (long long*)i1, d2);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    return ORBB_OK;
+}
+
+extern "C" int orbm_bf_top2(const orbm_db* cdb, const uint8_t* q_host, int nq, int32_t* d1, int64_t* i1, int32_t* d2)
+{
+    orbm_db* db = const_cast<orbm_db*>(cdb);
+    if (!db || nq < 0 || (nq > 0 && (!q_host || !d1 || !i1 || !d2))) return ORBB_E_INVALID;
+    if (nq == 0) return ORBB_OK;
+    ORBB_CUDA(cudaSetDevice(db->device));
+    long long rpc; int nchunks;
+    db_plan(db, nq, &rpc, &nchunks);
+    int rc = db_reserve(db, nq, nchunks);
+    if (rc != ORBB_OK) return rc;
+    ORBB_CUDA(cudaMemcpy(db->d_q, q_host, (size_t)nq * 32, cudaMemcpyHostToDevice));
+    rc = orbm_bf_top2_device(db, (const uint8_t*)db->d_q, nq, db->d_d1, (int64_t*)db->d_i1, db->d_d2, nullptr);
+    if (rc != ORBB_OK) return rc;
+    ORBB_CUDA(cudaMemcpy(d1, db->d_d1, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    ORBB_CUDA(cudaMemcpy(i1, db->d_i1, (size_t)nq * 8, cudaMemcpyDeviceToHost));
+    ORBB_CUDA(cudaMemcpy(d2, db->d_d2, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    return ORBB_OK;
+}
+
+extern "C" int orbm_merge_top2_device(const int32_t* d1_all, const int64_t* i1_all, const int32_t* d2_all, int G, int nq,
+                                      int32_t* d1, int64_t* i1, int32_t* d2, void* stream)
+{
+    if (G < 1 || nq < 0 || (nq > 0 && (!d1_all || !i1_all || !d2_all || !d1 || !i1 || !d2))) return ORBB_E_INVALID;
+    if (nq == 0) return ORBB_OK;
+    bf_merge_shards_kernel<<<ceil_div(nq, 256), 256, 0, (cudaStream_t)stream>>>(d1_all, (const long long*)i1_all, d2_all, G, nq, d1, (long long*)i1, d2);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    return ORBB_OK;
+}
+
+extern "C" int orbm_ratio_test(const int32_t* d1, const int32_t* d2, int nq, int th_low, float ratio, uint8_t* accepted)
+{
+    if (nq < 0 || (nq > 0 && (!d1 || !d2 || !accepted))) return ORBB_E_INVALID;
+    // ORBmatcher.cpp:278-281: bestDist1 <= TH_LOW && (float)bestDist1 < mfNNratio*(float)bestDist2
+    for (int i = 0; i < nq; i++) accepted[i] = (d1[i] <= th_low && static_cast<float>(d1[i]) < ratio * static_cast<float>(d2[i])) ? 1 : 0;
+    return ORBB_OK;
+}
+
+// Measured POPC throughput (G popc/s) of a register-only loop: the roofline denominator for matching.
+extern "C" int orbb200_measure_popc_peak(int device, double* gpopc_per_s)
+{
+    if (!gpopc_per_s) return ORBB_E_INVALID;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    DevBuf o;
+    const int blocks = sms * 8, threads = 256, iters = 4096;
+    if ((rc = o.alloc((size_t)blocks * threads * 4))) return rc;
+    cudaEvent_t e0, e1;
+    ORBB_CUDA(cudaEventCreate(&e0)); ORBB_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 5; rep++) {
+        ORBB_CUDA(cudaEventRecord(e0));
+        popc_peak_kernel<<<blocks, threads>>>(o.as<unsigned>(), iters, 12345u + rep);
+        ORBB_LAUNCHED();
+        ORBB_CUDA(cudaEventRecord(e1));
+        ORBB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ORBB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double g = (double)blocks * threads * iters * 8 / (ms * 1e-3) / 1e9;
+        if (rep > 0 && g > best) best = g;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *gpopc_per_s = best;
+    return ORBB_OK;
+}

@@ -1,0 +1,474 @@
+// match_kernels.cuh — sm_100a kernels of the Hamming-matching half of the hot path.
+//
+//   hamming_pairs_kernel   : ORBmatcher::DescriptorDistance (ORBmatcher.cpp:1838-1854) on n pairs.
+//   grid_*                 : Frame::AssignFeaturesToGrid / PosInGrid (Frame.cpp:241-257, :434-444) as a device CSR grid.
+//   window_count/fill      : Frame::GetFeaturesInArea (Frame.cpp:379-432) + DescriptorDistance, one warp per query,
+//                            candidates emitted in the reference's enumeration order.
+//   stereo_*               : Frame::ComputeStereoMatches (Frame.cpp:540-748).
+//   bf_top2_kernel         : brute-force top-2 (SearchByBoW update rule, ORBmatcher.cpp:249-275) over a DB shard;
+//                            queries live in registers, DB rows stream through shared memory, XOR + POPC on the integer
+//                            pipe; top-2 kept as packed (distance, row) keys so ties resolve to the first row.
+#pragma once
+#include "common.cuh"
+
+namespace orbb {
+
+constexpr int GRID_COLS = 64, GRID_ROWS = 48;      // Frame.h:37-38
+constexpr int TH_HIGH = 100, TH_LOW = 50;          // ORBmatcher.cpp:37-38
+
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__global__ void hamming_pairs_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, int* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = hamming256(a[2 * i], a[2 * i + 1], b[2 * i], b[2 * i + 1]);
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Frame grid
+// ------------------------------------------------------------------------------------------------------
+struct FrameDev {
+    const orbx_keypoint* kps; const uint4* desc; int n;
+    float minX, minY, invW, invH;
+    int* cell_of;        // [n]  cell id (ix * GRID_ROWS + iy) or -1
+    int* cell_start;     // [GRID_COLS*GRID_ROWS + 1]
+    int* cell_items;     // [n]  keypoint indices, ascending inside each cell (insertion order)
+};
+
+__global__ void grid_assign_kernel(FrameDev f, int* cell_count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= f.n) return;
+    // PosInGrid (Frame.cpp:434-444): round(), not floor()
+    const int px = (int)roundf(__fmul_rn(__fsub_rn(f.kps[i].x, f.minX), f.invW));
+    const int py = (int)roundf(__fmul_rn(__fsub_rn(f.kps[i].y, f.minY), f.invH));
+    int c = -1;
+    if (px >= 0 && px < GRID_COLS && py >= 0 && py < GRID_ROWS) { c = px * GRID_ROWS + py; atomicAdd(&cell_count[c], 1); }
+    f.cell_of[i] = c;
+}
+
+// single block: exclusive scan of the 3072 cell counts -> cell_start; cell_count is reset to the cursor
+__global__ void grid_scan_kernel(int* cell_count, int* cell_start)
+{
+    __shared__ int s[1024];
+    const int NC = GRID_COLS * GRID_ROWS;       // 3072 = 3 * 1024
+    int v[3], sum = 0;
+    for (int j = 0; j < 3; j++) { v[j] = cell_count[threadIdx.x * 3 + j]; sum += v[j]; }
+    s[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        int t = threadIdx.x >= o ? s[threadIdx.x - o] : 0;
+        __syncthreads();
+        s[threadIdx.x] += t;
+        __syncthreads();
+    }
+    int acc = s[threadIdx.x] - sum;
+    for (int j = 0; j < 3; j++) { cell_start[threadIdx.x * 3 + j] = acc; cell_count[threadIdx.x * 3 + j] = acc; acc += v[j]; }
+    if (threadIdx.x == 1023) cell_start[NC] = acc;
+}
+
+__global__ void grid_fill_kernel(FrameDev f, int* cursor)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= f.n) return;
+    const int c = f.cell_of[i];
+    if (c >= 0) f.cell_items[atomicAdd(&cursor[c], 1)] = i;
+}
+
+// one thread per cell: insertion sort => ascending keypoint index == push_back order of AssignFeaturesToGrid
+__global__ void grid_sort_kernel(FrameDev f)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= GRID_COLS * GRID_ROWS) return;
+    const int b = f.cell_start[c], e = f.cell_start[c + 1];
+    for (int i = b + 1; i < e; i++) {
+        const int v = f.cell_items[i];
+        int j = i - 1;
+        while (j >= b && f.cell_items[j] > v) { f.cell_items[j + 1] = f.cell_items[j]; j--; }
+        f.cell_items[j + 1] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// GetFeaturesInArea + DescriptorDistance.  One warp per query; FILL=false counts, FILL=true writes.
+// ------------------------------------------------------------------------------------------------------
+template <bool FILL>
+__global__ void window_search_kernel(FrameDev f, const orbm_query* __restrict__ qs, int nq,
+                                     int* __restrict__ counts, const int* __restrict__ offsets,
+                                     int* __restrict__ cand_idx, int* __restrict__ cand_dist, int cap)
+{
+    const int lane = threadIdx.x & 31;
+    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (qi >= nq) return;
+    const orbm_query& q = qs[qi];
+    const float x = q.u, y = q.v, r = q.r;
+    const int minLevel = q.min_level, maxLevel = q.max_level;
+    int total = 0;
+    const int obase = FILL ? offsets[qi] : 0;
+    // cell window (Frame.cpp:384-398)
+    const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, f.minX), r), f.invW)));
+    const int nMaxCellX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, f.minX), r), f.invW)));
+    const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, f.minY), r), f.invH)));
+    const int nMaxCellY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, f.minY), r), f.invH)));
+    const bool empty = nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0;
+    if (!empty) {
+        const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+        uint4 q0, q1;
+        if (FILL) { const uint4* qd = reinterpret_cast<const uint4*>(q.desc); q0 = qd[0]; q1 = qd[1]; }
+        for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
+            // cells (ix, nMinCellY..nMaxCellY) are contiguous in the CSR (cell id = ix*GRID_ROWS + iy)
+            const int b = f.cell_start[ix * GRID_ROWS + nMinCellY], e = f.cell_start[ix * GRID_ROWS + nMaxCellY + 1];
+            for (int base = b; base < e; base += 32) {
+                const int j = base + lane;
+                bool ok = false; int idx = -1;
+                if (j < e) {
+                    idx = f.cell_items[j];
+                    const orbx_keypoint kp = f.kps[idx];
+                    ok = true;
+                    if (bCheckLevels) {
+                        if (kp.octave < minLevel) ok = false;
+                        if (maxLevel >= 0 && kp.octave > maxLevel) ok = false;
+                    }
+                    const float dx = __fsub_rn(kp.x, x), dy = __fsub_rn(kp.y, y);
+                    if (!(fabsf(dx) < r && fabsf(dy) < r)) ok = false;
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, ok);
+                if (FILL && ok) {
+                    const int pos = obase + total + __popc(bal & ((1u << lane) - 1));
+                    if (pos < cap) {
+                        cand_idx[pos] = idx;
+                        cand_dist[pos] = hamming256(q0, q1, f.desc[2 * idx], f.desc[2 * idx + 1]);
+                    }
+                }
+                total += __popc(bal);
+            }
+        }
+    }
+    if (!FILL && lane == 0) counts[qi] = total;
+}
+
+// single-block exclusive scan (n up to a few hundred thousand): offsets[0..n], offsets[n] = total
+__global__ void excl_scan_kernel(const int* __restrict__ in, int* __restrict__ out, int n)
+{
+    __shared__ int s[1024];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int v = i < n ? in[i] : 0;
+        s[threadIdx.x] = v;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {
+            int t = threadIdx.x >= o ? s[threadIdx.x - o] : 0;
+            __syncthreads();
+            s[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (i < n) out[i] = carry + s[threadIdx.x] - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += s[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[n] = carry;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Stereo (Frame.cpp:540-748)
+// ------------------------------------------------------------------------------------------------------
+struct StereoArgs {
+    const orbx_keypoint* kL; const uint4* dL; int nL;
+    const orbx_keypoint* kR; const uint4* dR; int nR;
+    const LevelGeom* geom; int nlevels; int nRows;
+    const uint8_t* src0L; long long src0L_pitch; const uint8_t* pyrL;   // level 0 / levels >= 1 of the left extractor
+    const uint8_t* src0R; long long src0R_pitch; const uint8_t* pyrR;
+    float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS];
+    float mbf, minD, maxD;
+    float* uRight; float* depth; int* sad; int* bestIdx; int* bestDist;
+};
+
+__global__ void stereo_match_kernel(const __grid_constant__ StereoArgs a)
+{
+    const int lane = threadIdx.x & 31;
+    const int iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (iL >= a.nL) return;
+    const orbx_keypoint kpL = a.kL[iL];
+    const int levelL = kpL.octave;
+    const float vL = kpL.y, uL = kpL.x;
+    const int rowL = (int)vL;                          // vRowIndices[vL] (Frame.cpp:602)
+    const float minU = __fsub_rn(uL, a.maxD), maxU = __fsub_rn(uL, a.minD);
+    const uint4 l0 = a.dL[2 * iL], l1 = a.dL[2 * iL + 1];
+    // best right candidate in the row band: min (dist, iR) with dist < TH_HIGH (strict '<' in ascending iR)
+    unsigned best = ((unsigned)TH_HIGH << 16);         // key = dist << 16 | iR  (iR < 65536 checked by the host)
+    if (maxU >= 0) {
+        for (int iR = lane; iR < a.nR; iR += 32) {
+            const orbx_keypoint kpR = a.kR[iR];
+            const float r = __fmul_rn(2.0f, a.scale[kpR.octave]);
+            const int maxr = (int)ceilf(__fadd_rn(kpR.y, r)), minr = (int)floorf(__fsub_rn(kpR.y, r));
+            if (rowL < minr || rowL > maxr) continue;
+            if (kpR.octave < levelL - 1 || kpR.octave > levelL + 1) continue;
+            if (!(kpR.x >= minU && kpR.x <= maxU)) continue;
+            const unsigned d = (unsigned)hamming256(l0, l1, a.dR[2 * iR], a.dR[2 * iR + 1]);
+            if (d < (unsigned)TH_HIGH) best = min(best, (d << 16) | (unsigned)iR);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    const int bestDist = (int)(best >> 16), bestIdxR = (int)(best & 0xffff);
+    float out_u = -1.f, out_d = -1.f; int out_sad = -1;
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    if (lane == 0) { a.bestIdx[iL] = bestDist < thOrbDist ? bestIdxR : -1; a.bestDist[iL] = bestDist < thOrbDist ? bestDist : -1; }
+    if (bestDist < thOrbDist) {
+        const float uR0 = a.kR[bestIdxR].x;
+        const float sf = a.inv_scale[levelL];
+        const float scaleduL = roundf(__fmul_rn(kpL.x, sf)), scaledvL = roundf(__fmul_rn(kpL.y, sf));
+        const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
+        const int w = 5, Lw = 5;
+        const LevelGeom g = a.geom[levelL];
+        const float iniu = scaleduR0 + Lw - w, endu = scaleduR0 + Lw + w + 1;
+        if (!(iniu < 0 || endu >= (float)g.w)) {
+            const uint8_t* imL; const uint8_t* imR; long long pL, pR;
+            if (levelL == 0) { imL = a.src0L; pL = a.src0L_pitch; imR = a.src0R; pR = a.src0R_pitch; }
+            else { imL = a.pyrL + g.off; pL = g.pitch; imR = a.pyrR + g.off; pR = g.pitch; }
+            const int cxL = (int)scaleduL, cy = (int)scaledvL, cxR0 = (int)scaleduR0;
+            const int cL = imL[(long long)cy * pL + cxL];
+            int sums[11];
+#pragma unroll
+            for (int s = 0; s < 11; s++) sums[s] = 0;
+            for (int p = lane; p < 121; p += 32) {
+                const int dy = p / 11 - w, dx = p % 11 - w;
+                const int vl = (int)imL[(long long)(cy + dy) * pL + cxL + dx] - cL;
+                const uint8_t* rr = imR + (long long)(cy + dy) * pR + cxR0 + dx;
+#pragma unroll
+                for (int s = 0; s < 11; s++) {
+                    const int cR = imR[(long long)cy * pR + cxR0 + s - Lw];
+                    sums[s] += abs(vl - ((int)rr[s - Lw] - cR));
+                }
+            }
+#pragma unroll
+            for (int s = 0; s < 11; s++)
+#pragma unroll
+                for (int o = 16; o; o >>= 1) sums[s] += __shfl_xor_sync(0xffffffffu, sums[s], o);
+            int sadBest = 0x7fffffff, bestinc = 0;
+#pragma unroll
+            for (int s = 0; s < 11; s++) if (sums[s] < sadBest) { sadBest = sums[s]; bestinc = s - Lw; }
+            if (!(bestinc == -Lw || bestinc == Lw)) {
+                float dist1 = 0.f, dist2 = 0.f, dist3 = 0.f;
+#pragma unroll
+                for (int s = 1; s < 10; s++) if (s - Lw == bestinc) { dist1 = (float)sums[s - 1]; dist2 = (float)sums[s]; dist3 = (float)sums[s + 1]; }
+                const float deltaR = __fdiv_rn(__fsub_rn(dist1, dist3),
+                                               __fmul_rn(2.0f, __fsub_rn(__fadd_rn(dist1, dist3), __fmul_rn(2.0f, dist2))));
+                if (!(deltaR < -1 || deltaR > 1)) {
+                    float bestuR = __fmul_rn(a.scale[levelL], __fadd_rn(__fadd_rn(scaleduR0, (float)bestinc), deltaR));
+                    float disparity = __fsub_rn(uL, bestuR);
+                    if (disparity >= a.minD && disparity < a.maxD) {
+                        if (disparity <= 0) { disparity = 0.01f; bestuR = (float)((double)uL - 0.01); }
+                        out_d = __fdiv_rn(a.mbf, disparity);
+                        out_u = bestuR;
+                        out_sad = sadBest;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) { a.uRight[iL] = out_u; a.depth[iL] = out_d; a.sad[iL] = out_sad; }
+}
+
+// single block: median of the accepted SADs (element size()/2 of the sorted list) and the 1.5*1.4*median cut
+// (Frame.cpp:734-747).  SAD <= 121*510 < 2^16: two-pass radix select.
+__global__ void stereo_median_filter_kernel(int n, const int* __restrict__ sad, float* uRight, float* depth, float k21)
+{
+    __shared__ int hist[256];
+    __shared__ int s_m, s_bin, s_rem, s_val;
+    const int tid = threadIdx.x;
+    if (tid == 0) s_m = 0;
+    for (int i = tid; i < 256; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    int cnt = 0;
+    for (int i = tid; i < n; i += blockDim.x) if (sad[i] >= 0) { cnt++; atomicAdd(&hist[sad[i] >> 8], 1); }
+    atomicAdd(&s_m, cnt);
+    __syncthreads();
+    const int M = s_m;
+    if (M == 0) return;
+    if (tid == 0) {
+        int k = M / 2, b = 0;
+        while (k >= hist[b]) { k -= hist[b]; b++; }
+        s_bin = b; s_rem = k;
+    }
+    __syncthreads();
+    const int bin = s_bin;
+    __syncthreads();
+    for (int i = tid; i < 256; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x) if (sad[i] >= 0 && (sad[i] >> 8) == bin) atomicAdd(&hist[sad[i] & 255], 1);
+    __syncthreads();
+    if (tid == 0) {
+        int k = s_rem, b = 0;
+        while (k >= hist[b]) { k -= hist[b]; b++; }
+        s_val = (bin << 8) | b;
+    }
+    __syncthreads();
+    const float median = (float)s_val;
+    const float thDist = __fmul_rn(k21, median);
+    for (int i = tid; i < n; i += blockDim.x)
+        if (sad[i] >= 0 && !((float)sad[i] < thDist)) { uRight[i] = -1.f; depth[i] = -1.f; }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Brute-force top-2
+// ------------------------------------------------------------------------------------------------------
+constexpr int BF_THREADS = 128;
+constexpr int BF_TQ = 4;                       // queries per thread (registers)
+constexpr int BF_QTILE = BF_THREADS * BF_TQ;   // 512 queries per CTA
+constexpr int BF_ROWS = 128;                   // DB rows per shared-memory stage (4 KB)
+constexpr int BF_IDX_BITS = 23;                // packed key = dist << 23 | row-in-chunk
+
+// distance of one query (8 words in registers) to one DB row (8 words), variant 0: 8 XOR + 8 POPC.
+__device__ __forceinline__ unsigned ham_plain(const unsigned (&q)[8], const uint4& r0, const uint4& r1)
+{
+    return __popc(q[0] ^ r0.x) + __popc(q[1] ^ r0.y) + __popc(q[2] ^ r0.z) + __popc(q[3] ^ r0.w) +
+           __popc(q[4] ^ r1.x) + __popc(q[5] ^ r1.y) + __popc(q[6] ^ r1.z) + __popc(q[7] ^ r1.w);
+}
+// variant 1: three carry-save full adders (LOP3 pairs) fold 7 of the 8 XOR words into {ones, twos x3}: 5 POPC
+// instead of 8, trading the quarter-rate POPC pipe for full-rate LOP3s.
+__device__ __forceinline__ unsigned ham_csa(const unsigned (&q)[8], const uint4& r0, const uint4& r1)
+{
+    const unsigned x0 = q[0] ^ r0.x, x1 = q[1] ^ r0.y, x2 = q[2] ^ r0.z, x3 = q[3] ^ r0.w;
+    const unsigned x4 = q[4] ^ r1.x, x5 = q[5] ^ r1.y, x6 = q[6] ^ r1.z, x7 = q[7] ^ r1.w;
+    const unsigned s0 = x0 ^ x1 ^ x2, c0 = (x0 & x1) | (x2 & (x0 ^ x1));
+    const unsigned s1 = x3 ^ x4 ^ x5, c1 = (x3 & x4) | (x5 & (x3 ^ x4));
+    const unsigned s2 = s0 ^ s1 ^ x6, c2 = (s0 & s1) | (x6 & (s0 ^ s1));
+    return __popc(s2) + __popc(x7) + 2 * (__popc(c0) + __popc(c1) + __popc(c2));
+}
+
+struct BfArgs {
+    const uint4* db; long long nrows;          // shard rows
+    const uint4* q; int nq;
+    long long rows_per_chunk; int nchunks;
+    unsigned* part_k1; unsigned* part_k2;      // [nchunks][nq] packed keys
+};
+
+template <int VARIANT>
+__global__ void __launch_bounds__(BF_THREADS) bf_top2_kernel(const __grid_constant__ BfArgs a)
+{
+    __shared__ uint4 rows[2][BF_ROWS * 2];
+    const int tid = threadIdx.x;
+    const int chunk = blockIdx.y;
+    const long long r_begin = (long long)chunk * a.rows_per_chunk;
+    const long long r_end = min(a.nrows, r_begin + a.rows_per_chunk);
+    // queries -> registers
+    unsigned q[BF_TQ][8];
+    unsigned k1[BF_TQ], k2[BF_TQ];
+#pragma unroll
+    for (int j = 0; j < BF_TQ; j++) {
+        const int qi = blockIdx.x * BF_QTILE + j * BF_THREADS + tid;
+        uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0;
+        if (qi < a.nq) { v0 = a.q[2 * qi]; v1 = a.q[2 * qi + 1]; }
+        q[j][0] = v0.x; q[j][1] = v0.y; q[j][2] = v0.z; q[j][3] = v0.w;
+        q[j][4] = v1.x; q[j][5] = v1.y; q[j][6] = v1.z; q[j][7] = v1.w;
+        k1[j] = 0xffffffffu; k2[j] = 0xffffffffu;
+    }
+    const long long nrows = r_end - r_begin;
+    const int nstages = (int)((nrows + BF_ROWS - 1) / BF_ROWS);
+    auto load_stage = [&](int s, int buf) {
+        // 128 rows x 32 B = 256 uint4: two per thread, 16-byte cp.async (LDGSTS), zero-fill past the end
+        const long long base = r_begin + (long long)s * BF_ROWS;
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            const int e = tid + j * BF_THREADS;                  // uint4 index inside the stage
+            const long long row = base + (e >> 1);
+            const uint4* src = a.db + (row < r_end ? row * 2 + (e & 1) : 0);
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(&rows[buf][e]);
+            const int bytes = row < r_end ? 16 : 0;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+        }
+        asm volatile("cp.async.commit_group;");
+    };
+    if (nstages > 0) load_stage(0, 0);
+    for (int s = 0; s < nstages; s++) {
+        const int buf = s & 1;
+        if (s + 1 < nstages) { load_stage(s + 1, buf ^ 1); asm volatile("cp.async.wait_group 1;"); }
+        else asm volatile("cp.async.wait_group 0;");
+        __syncthreads();
+        const int nr = (int)min((long long)BF_ROWS, nrows - (long long)s * BF_ROWS);
+        const unsigned rbase = (unsigned)(s * BF_ROWS);
+#pragma unroll 2
+        for (int r = 0; r < nr; r++) {
+            const uint4 r0 = rows[buf][2 * r], r1 = rows[buf][2 * r + 1];
+#pragma unroll
+            for (int j = 0; j < BF_TQ; j++) {
+                const unsigned d = VARIANT == 0 ? ham_plain(q[j], r0, r1) : ham_csa(q[j], r0, r1);
+                const unsigned key = (d << BF_IDX_BITS) + (rbase + (unsigned)r);
+                k2[j] = min(k2[j], max(k1[j], key));
+                k1[j] = min(k1[j], key);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < BF_TQ; j++) {
+        const int qi = blockIdx.x * BF_QTILE + j * BF_THREADS + tid;
+        if (qi < a.nq) {
+            a.part_k1[(long long)chunk * a.nq + qi] = k1[j];
+            a.part_k2[(long long)chunk * a.nq + qi] = k2[j];
+        }
+    }
+}
+
+// Merge the per-chunk keys in ascending chunk (= ascending row) order: sequential-scan semantics.
+__global__ void bf_merge_chunks_kernel(const unsigned* __restrict__ k1, const unsigned* __restrict__ k2, int nchunks, int nq,
+                                       long long rows_per_chunk, long long row_offset,
+                                       int* __restrict__ d1, long long* __restrict__ i1, int* __restrict__ d2)
+{
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    int b1 = 256, b2 = 256; long long bi = -1;
+    for (int c = 0; c < nchunks; c++) {
+        const unsigned a1 = k1[(long long)c * nq + qi], a2 = k2[(long long)c * nq + qi];
+        if (a1 == 0xffffffffu) continue;
+        const int c1 = (int)(a1 >> BF_IDX_BITS);
+        const int c2 = a2 == 0xffffffffu ? 256 : (int)(a2 >> BF_IDX_BITS);
+        if (c1 < b1) { b2 = min(b1, c2); b1 = c1; bi = row_offset + (long long)c * rows_per_chunk + (a1 & ((1u << BF_IDX_BITS) - 1)); }
+        else b2 = min(b2, c1);
+    }
+    d1[qi] = b1; i1[qi] = bi; d2[qi] = b2;
+}
+
+// Merge G shard results [g][nq] (ascending shard row ranges) — the step after the all-gather.
+__global__ void bf_merge_shards_kernel(const int* __restrict__ d1a, const long long* __restrict__ i1a, const int* __restrict__ d2a,
+                                       int G, int nq, int* __restrict__ d1, long long* __restrict__ i1, int* __restrict__ d2)
+{
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    int b1 = 256, b2 = 256; long long bi = -1;
+    for (int g = 0; g < G; g++) {
+        const int c1 = d1a[(long long)g * nq + qi], c2 = d2a[(long long)g * nq + qi];
+        const long long ci = i1a[(long long)g * nq + qi];
+        if (ci < 0) continue;
+        if (c1 < b1) { b2 = min(b1, c2); b1 = c1; bi = ci; }
+        else b2 = min(b2, c1);
+    }
+    d1[qi] = b1; i1[qi] = bi; d2[qi] = b2;
+}
+
+// register-only POPC throughput probe (roofline denominator for matching)
+__global__ void popc_peak_kernel(unsigned* out, int iters, unsigned seed)
+{
+    unsigned x[8], acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) { x[j] = seed * (threadIdx.x + 1) + j * 0x9e3779b9u; acc[j] = 0; }
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) { acc[j] += __popc(x[j]); x[j] ^= acc[j]; }
+    }
+    unsigned s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) s += acc[j];
+    if (s == 0x12345678u) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+}  // namespace orbb

@@ -1,0 +1,355 @@
+"""ctypes harness over liborbb200.so (the C ABI of include/orbb200.h) for tests and bench.py.
+
+The product is the CUDA library and the C++ host mirror in host/; this module is plumbing that lets pytest and the
+benchmark drive the same C entry points a C++ caller binds.  It never computes anything on the CPU and raises
+if the library is missing or a call fails (no fallback).
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "liborbb200.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),
+                        ("desc", "u1", (32,))])
+assert KP_DTYPE.itemsize == 28 and QUERY_DTYPE.itemsize == 52
+
+OK, E_INVALID, E_CUDA, E_CAPACITY, E_BAD_SHAPE, E_NOMEM, E_STATE = 0, -1, -2, -3, -4, -5, -6
+STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
+
+# every symbol include/orbb200.h declares (tests check the .so exports all of them)
+SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
+           "orbx_extract_batch", "orbx_sync", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
+           "orbm_distance_pairs", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
+           "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
+           "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
+           "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak",
+           "orbb200_launch_count"]
+
+
+class OrbConfig(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32), ("max_width", C.c_int32),
+                ("max_height", C.c_int32), ("max_batch", C.c_int32), ("device", C.c_int32), ("blur_legacy", C.c_int32)]
+
+
+class OrbError(RuntimeError):
+    def __init__(self, code, where):
+        self.code = code
+        L = lib()
+        msg = L.orbb200_strerror(code).decode()
+        if code == E_CUDA:
+            msg += ": " + L.orbb200_last_cuda_error().decode()
+        super().__init__(f"{where}: {msg} ({code})")
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise RuntimeError(f"{SO_PATH} is missing: build it with __graft_entry__.build() (there is no CPU fallback)")
+        L = C.CDLL(SO_PATH)
+        vp, i32, f32, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+        L.orbx_create.argtypes = [C.POINTER(OrbConfig), C.POINTER(vp)]
+        L.orbx_destroy.argtypes = [vp]
+        L.orbx_get_tables.argtypes = [vp] + [vp] * 6
+        L.orbx_extract.argtypes = [vp, vp, i32, i32, sz, vp, vp, i32, C.POINTER(i32)]
+        L.orbx_extract_batch_device.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32]
+        L.orbx_extract_batch.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32]
+        L.orbx_sync.argtypes = [vp]
+        L.orbx_stream.argtypes = [vp]
+        L.orbx_stream.restype = vp
+        L.orbx_pyramid_level.argtypes = [vp, i32, i32, vp, sz, C.POINTER(i32), C.POINTER(i32)]
+        L.orbx_debug_stage.argtypes = [vp, i32, i32, i32, vp, sz, C.POINTER(sz)]
+        L.orbm_distance_pairs.argtypes = [vp, vp, i32, vp, i32]
+        L.orbm_frame_create.argtypes = [C.POINTER(vp), vp, vp, i32, f32, f32, f32, f32, i32]
+        L.orbm_frame_destroy.argtypes = [vp]
+        L.orbm_window_search.argtypes = [vp, vp, i32, vp, vp, vp, i32]
+        L.orbm_stereo_match.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, f32, f32, vp, vp]
+        L.orbm_db_create.argtypes = [C.POINTER(vp), C.c_int64, C.c_int64, i32]
+        L.orbm_db_append.argtypes = [vp, vp, C.c_int64]
+        L.orbm_db_append_device.argtypes = [vp, vp, C.c_int64]
+        L.orbm_db_destroy.argtypes = [vp]
+        L.orbm_db_rows.argtypes = [vp]
+        L.orbm_db_rows.restype = C.c_int64
+        L.orbm_bf_top2.argtypes = [vp, vp, i32, vp, vp, vp]
+        L.orbm_bf_top2_device.argtypes = [vp, vp, i32, vp, vp, vp, vp]
+        L.orbm_merge_top2_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp]
+        L.orbm_ratio_test.argtypes = [vp, vp, i32, i32, f32, vp]
+        L.orbb200_strerror.argtypes = [i32]
+        L.orbb200_strerror.restype = C.c_char_p
+        L.orbb200_last_cuda_error.restype = C.c_char_p
+        L.orbb200_measure_popc_peak.argtypes = [i32, C.POINTER(C.c_double)]
+        L.orbb200_launch_count.restype = C.c_uint64
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _check(code, where):
+    if code != OK:
+        raise OrbError(code, where)
+
+
+def launch_count():
+    return int(lib().orbb200_launch_count())
+
+
+def popc_peak(device=0):
+    v = C.c_double()
+    _check(lib().orbb200_measure_popc_peak(device, C.byref(v)), "orbb200_measure_popc_peak")
+    return v.value
+
+
+class ORBextractor:
+    """Mirror of ORB_SLAM2::ORBextractor (reference include/ORBextractor.h:45-111) over the C ABI.
+
+    ex = ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, max_size=(w, h))
+    keypoints, descriptors = ex(image)        # == operator()(image, mask, keypoints, descriptors)
+    """
+
+    def __init__(self, nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7,
+                 max_size=(640, 480), max_batch=1, device=0, blur_legacy=False):
+        self.L = lib()
+        self.cfg = OrbConfig(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, max_size[0], max_size[1],
+                             max_batch, device, int(blur_legacy))
+        self.h = C.c_void_p()
+        _check(self.L.orbx_create(C.byref(self.cfg), C.byref(self.h)), "orbx_create")
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self.device = device
+        self.default_capacity = nfeatures + 64 * nlevels + 256
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.orbx_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- getters (ORBextractor.h:63-83) ---
+    def _tables(self):
+        n = self.nlevels
+        sc, isc, s2, is2 = (np.zeros(n, np.float32) for _ in range(4))
+        per = np.zeros(n, np.int32)
+        um = np.zeros(16, np.int32)
+        _check(self.L.orbx_get_tables(self.h, _p(sc), _p(isc), _p(s2), _p(is2), _p(per), _p(um)), "orbx_get_tables")
+        return dict(scale=sc, inv_scale=isc, sigma2=s2, inv_sigma2=is2, per_level=per, umax=um)
+
+    def GetLevels(self):
+        return self.nlevels
+
+    def GetScaleFactor(self):
+        return float(self.cfg.scale_factor)
+
+    def GetScaleFactors(self):
+        return self._tables()["scale"]
+
+    def GetInverseScaleFactors(self):
+        return self._tables()["inv_scale"]
+
+    def GetScaleSigmaSquares(self):
+        return self._tables()["sigma2"]
+
+    def GetInverseScaleSigmaSquares(self):
+        return self._tables()["inv_sigma2"]
+
+    # --- operator() ---
+    def __call__(self, image, mask=None, capacity=None):
+        image = np.asarray(image)
+        if image.size == 0:
+            return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        assert image.dtype == np.uint8 and image.ndim == 2, "image.type() == CV_8UC1 (ORBextractor.cpp:1060)"
+        if image.strides[1] != 1:
+            image = np.ascontiguousarray(image)
+        h, w = image.shape
+        cap = capacity or self.default_capacity
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        n = C.c_int()
+        rc = self.L.orbx_extract(self.h, _p(image), w, h, image.strides[0], _p(kps), _p(desc), cap, C.byref(n))
+        if rc == E_CAPACITY and capacity is None and n.value > cap:
+            return self.__call__(image, mask, capacity=n.value + 16)
+        _check(rc, "orbx_extract")
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_batch(self, images, capacity=None):
+        """images: (F, H, W) uint8 host array (pinned or pageable). Returns list of (kps, desc)."""
+        images = np.ascontiguousarray(images, np.uint8)
+        F, h, w = images.shape
+        cap = capacity or self.default_capacity
+        kps = np.zeros((F, cap), KP_DTYPE)
+        desc = np.zeros((F, cap, 32), np.uint8)
+        counts = np.zeros(F, np.int32)
+        _check(self.L.orbx_extract_batch(self.h, _p(images), F, w, h, w, w * h, _p(kps), _p(desc), _p(counts), cap),
+               "orbx_extract_batch")
+        return [(kps[f, :counts[f]].copy(), desc[f, :counts[f]].copy()) for f in range(F)]
+
+    def extract_batch_device(self, imgs_ptr, F, w, h, stride, fstride, kps_ptr, desc_ptr, counts_ptr, capacity):
+        """Raw device-pointer entry (ints): asynchronous on the handle's stream."""
+        _check(self.L.orbx_extract_batch_device(self.h, _p(imgs_ptr), F, w, h, stride, fstride, _p(kps_ptr),
+                                                _p(desc_ptr), _p(counts_ptr), capacity), "orbx_extract_batch_device")
+
+    def sync(self):
+        _check(self.L.orbx_sync(self.h), "orbx_sync")
+
+    def stream(self):
+        return int(self.L.orbx_stream(self.h) or 0)
+
+    # --- mvImagePyramid (ORBextractor.h:85) and parity stages ---
+    def pyramid_level(self, level, frame=0):
+        w, h = C.c_int(), C.c_int()
+        _check(self.L.orbx_pyramid_level(self.h, frame, level, None, 0, C.byref(w), C.byref(h)), "orbx_pyramid_level")
+        out = np.zeros((h.value, w.value), np.uint8)
+        _check(self.L.orbx_pyramid_level(self.h, frame, level, _p(out), w.value, C.byref(w), C.byref(h)), "orbx_pyramid_level")
+        return out
+
+    @property
+    def mvImagePyramid(self):
+        return [self.pyramid_level(l) for l in range(self.nlevels)]
+
+    def _stage(self, level, stage, frame=0):
+        need = C.c_size_t()
+        _check(self.L.orbx_debug_stage(self.h, frame, level, stage, None, 0, C.byref(need)), "orbx_debug_stage")
+        buf = np.zeros(max(need.value, 1), np.uint8)
+        _check(self.L.orbx_debug_stage(self.h, frame, level, stage, _p(buf), need.value, C.byref(need)), "orbx_debug_stage")
+        return buf[:need.value]
+
+    def blurred_level(self, level, frame=0):
+        w, h = C.c_int(), C.c_int()
+        _check(self.L.orbx_pyramid_level(self.h, frame, level, None, 0, C.byref(w), C.byref(h)), "orbx_pyramid_level")
+        return self._stage(level, STAGE_BLUR, frame).reshape(h.value, w.value)
+
+    def fast_keypoints(self, level, frame=0):
+        return self._stage(level, STAGE_FASTKPS, frame).view(np.int32).reshape(-1, 3)
+
+    def level_keypoints(self, level, frame=0):
+        return self._stage(level, STAGE_LEVELKPS, frame).view(KP_DTYPE)
+
+
+def DescriptorDistance(a, b, device=0):
+    """ORBmatcher::DescriptorDistance for n pairs (rows of a, b)."""
+    a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32)
+    b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+    out = np.zeros(a.shape[0], np.int32)
+    _check(lib().orbm_distance_pairs(_p(a), _p(b), a.shape[0], _p(out), device), "orbm_distance_pairs")
+    return out
+
+
+class FrameMatcher:
+    """Device image of a Frame's matching state (mvKeysUn, mDescriptors, 64x48 grid)."""
+
+    def __init__(self, kps_un, desc, bounds, device=0):
+        self.L = lib()
+        self.kps = np.ascontiguousarray(kps_un, KP_DTYPE)
+        self.desc = np.ascontiguousarray(desc, np.uint8)
+        self.n = len(self.kps)
+        self.h = C.c_void_p()
+        _check(self.L.orbm_frame_create(C.byref(self.h), _p(self.kps), _p(self.desc), self.n,
+                                        *[float(b) for b in bounds], device), "orbm_frame_create")
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.orbm_frame_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def window_search(self, queries, cap=None):
+        q = np.ascontiguousarray(queries, QUERY_DTYPE)
+        nq = len(q)
+        cap = cap or max(1024, 64 * nq)
+        offs = np.zeros(nq + 1, np.int32)
+        idx = np.zeros(cap, np.int32)
+        dist = np.zeros(cap, np.int32)
+        rc = self.L.orbm_window_search(self.h, _p(q), nq, _p(offs), _p(idx), _p(dist), cap)
+        if rc == E_CAPACITY:
+            return self.window_search(queries, cap=int(offs[nq]) + 16)
+        _check(rc, "orbm_window_search")
+        return offs, idx[:offs[nq]].copy(), dist[:offs[nq]].copy()
+
+
+def stereo_match(exL, exR, kpsL, descL, kpsR, descR, mbf, mb=0.0):
+    """Frame::ComputeStereoMatches on the two extractors' device pyramids."""
+    kL = np.ascontiguousarray(kpsL, KP_DTYPE); dL = np.ascontiguousarray(descL, np.uint8)
+    kR = np.ascontiguousarray(kpsR, KP_DTYPE); dR = np.ascontiguousarray(descR, np.uint8)
+    ur = np.zeros(len(kL), np.float32)
+    dp = np.zeros(len(kL), np.float32)
+    with np.errstate(divide="ignore"):
+        _check(lib().orbm_stereo_match(exL.h, exR.h, _p(kL), _p(dL), len(kL), _p(kR), _p(dR), len(kR), mbf, mb, _p(ur), _p(dp)),
+               "orbm_stereo_match")
+    return ur, dp
+
+
+class DescriptorDB:
+    """One shard of a keyframe-descriptor database for brute-force top-2 (rows [row_offset, row_offset+n))."""
+
+    def __init__(self, capacity_rows, row_offset=0, device=0):
+        self.L = lib()
+        self.h = C.c_void_p()
+        _check(self.L.orbm_db_create(C.byref(self.h), capacity_rows, row_offset, device), "orbm_db_create")
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.orbm_db_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def append(self, rows):
+        rows = np.ascontiguousarray(rows, np.uint8).reshape(-1, 32)
+        _check(self.L.orbm_db_append(self.h, _p(rows), rows.shape[0]), "orbm_db_append")
+
+    def append_device(self, ptr, nrows):
+        _check(self.L.orbm_db_append_device(self.h, _p(ptr), nrows), "orbm_db_append_device")
+
+    def rows(self):
+        return int(self.L.orbm_db_rows(self.h))
+
+    def top2(self, queries):
+        q = np.ascontiguousarray(queries, np.uint8).reshape(-1, 32)
+        nq = q.shape[0]
+        d1 = np.zeros(nq, np.int32); i1 = np.zeros(nq, np.int64); d2 = np.zeros(nq, np.int32)
+        _check(self.L.orbm_bf_top2(self.h, _p(q), nq, _p(d1), _p(i1), _p(d2)), "orbm_bf_top2")
+        return d1, i1, d2
+
+    def top2_device(self, q_ptr, nq, d1_ptr, i1_ptr, d2_ptr, stream=0):
+        _check(self.L.orbm_bf_top2_device(self.h, _p(q_ptr), nq, _p(d1_ptr), _p(i1_ptr), _p(d2_ptr), _p(stream) if stream else None),
+               "orbm_bf_top2_device")
+
+
+def merge_top2_device(d1_all, i1_all, d2_all, nshards, nq, d1, i1, d2, stream=0):
+    _check(lib().orbm_merge_top2_device(_p(d1_all), _p(i1_all), _p(d2_all), nshards, nq, _p(d1), _p(i1), _p(d2),
+                                        _p(stream) if stream else None), "orbm_merge_top2_device")
+
+
+def ratio_test(d1, d2, th_low=50, ratio=0.75):
+    d1 = np.ascontiguousarray(d1, np.int32); d2 = np.ascontiguousarray(d2, np.int32)
+    acc = np.zeros(len(d1), np.uint8)
+    _check(lib().orbm_ratio_test(_p(d1), _p(d2), len(d1), th_low, ratio, _p(acc)), "orbm_ratio_test")
+    return acc.astype(bool)
