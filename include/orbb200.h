@@ -143,6 +143,31 @@ typedef struct orbm_query {
 int orbm_window_search(const orbm_frame* f, const orbm_query* q_host, int nq,
                        int32_t* cand_offsets_host, int32_t* cand_idx_host, int32_t* cand_dist_host, int cap);
 
+/* A projected query plus the per-query state the reference's resolution loops read. */
+typedef struct orbm_proj_query {
+    orbm_query q;
+    float u_right;          /* a10: pMP->mTrackProjXR; a11: u - mbf*invzc (ORBmatcher.cpp:116, :1597)        */
+    float max_err_right;    /* candidate skipped if mvuRight[idx] > 0 && |u_right - mvuRight[idx]| > this     */
+    int32_t id;             /* caller's identifier of the map point (stored into frame_mp on a match)       */
+    int32_t has_obs;        /* pMP->Observations() > 0                                                      */
+    float angle;            /* LastFrame.mvKeysUn[i].angle, for the rotation histogram (a11)                */
+} orbm_proj_query;
+
+/* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (ORBmatcher.cpp:63-155): window candidates and
+ * distances on the device, then the reference's order-dependent top-2 / level-aware ratio / already-matched loop on
+ * the host.  frame_mp[n] (in/out) is F.mvpMapPoints flattened to ids (-1 = none), frame_mp_obs[n] the matched point's
+ * Observations()>0.  mvuRight_host may be NULL (monocular).  Queries are the visible, non-bad map points in order. */
+int orbm_search_by_projection_points(const orbm_frame* f, const float* mvuRight_host, const orbm_proj_query* q_host, int nq,
+                                     float nnratio, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches);
+/* ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th, bMono) (ORBmatcher.cpp:1506-1659) after the
+ * projection step: top-1 <= TH_HIGH, already-matched skips, rotation histogram (ComputeThreeMaxima :1792-1833). */
+int orbm_search_by_projection_frame(const orbm_frame* f, const float* mvuRight_host, const orbm_proj_query* q_host, int nq,
+                                    int check_orientation, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches);
+/* ORBmatcher::SearchForInitialization (ORBmatcher.cpp:474-590): level-0 keypoints of f1 against f2 in a window around
+ * prev_matched_xy (in/out, 2*n1 floats); matches12_out[n1] = index in f2 or -1. */
+int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev_matched_xy, int32_t* matches12_out,
+                                   int window_size, float nnratio, int check_orientation, int* nmatches);
+
 /* Frame::ComputeStereoMatches (Frame.cpp:540-748) on the device, reading both extractors' pyramids
  * (mpORBextractorLeft/Right->mvImagePyramid) in place.  left/right must hold their last extraction (frame 0);
  * kps/desc are the host vectors those extractions returned.  mb is the member value at call time (0 in the

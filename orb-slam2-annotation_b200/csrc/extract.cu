@@ -135,6 +135,9 @@ static int setup_geometry(orbx_handle* h, int w, int ht, bool allocate_only)
         }
     }
     if (allocate_only) {
+        // other shapes (<= max) can have more octree roots per level (aspect ratio): reserve room for 16 roots/level
+        const size_t root_margin = (size_t)h->nlevels * 8 * 16;
+        node += root_margin; out += root_margin;
         h->cap_pyr = off; h->cap_rec = rec; h->cap_node = node; h->cap_cell = cell; h->cap_out = out;
         h->cap_tab = tab + 64; h->cap_tile = tile + 64;
         return ORBB_OK;

@@ -54,6 +54,8 @@ extern "C" int orbm_distance_pairs(const uint8_t* a_host, const uint8_t* b_host,
 struct orbm_frame {
     int device = 0, n = 0;
     FrameDev f{};
+    std::vector<orbx_keypoint> h_kps;      // host copies for the order-dependent resolution loops
+    std::vector<uint8_t> h_desc;
     DevBuf kps, desc, cell_of, cell_start, cell_items, cursor;
 };
 
@@ -67,6 +69,7 @@ extern "C" int orbm_frame_create(orbm_frame** out, const orbx_keypoint* kps, con
     orbm_frame* fr = new (std::nothrow) orbm_frame();
     if (!fr) return ORBB_E_NOMEM;
     fr->device = device; fr->n = n;
+    if (n > 0) { fr->h_kps.assign(kps, kps + n); fr->h_desc.assign(desc, desc + (size_t)n * 32); }
     const int NC = GRID_COLS * GRID_ROWS;
     if ((rc = fr->kps.alloc((size_t)n * sizeof(orbx_keypoint))) || (rc = fr->desc.alloc((size_t)n * 32)) ||
         (rc = fr->cell_of.alloc((size_t)n * 4)) || (rc = fr->cell_start.alloc((size_t)(NC + 1) * 4)) ||
@@ -131,6 +134,180 @@ extern "C" int orbm_window_search(const orbm_frame* fr, const orbm_query* q_host
         ORBB_CUDA(cudaMemcpy(dist_host, dist.p, (size_t)m * 4, cudaMemcpyDeviceToHost));
     }
     return total > cap ? ORBB_E_CAPACITY : ORBB_OK;
+}
+
+// ---- full Search* functions: device candidates + host resolution -------------------------------------------
+namespace {
+constexpr int HISTO_LENGTH = 30;                 // ORBmatcher.cpp:39
+
+// CSR candidates for a query list, growing the buffers until they fit.
+int run_window_search(const orbm_frame* f, const std::vector<orbm_query>& q, std::vector<int>& offs, std::vector<int>& idx, std::vector<int>& dist)
+{
+    const int nq = (int)q.size();
+    offs.assign(nq + 1, 0);
+    int cap = 64 * nq + 1024;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        idx.resize(cap); dist.resize(cap);
+        const int rc = orbm_window_search(f, q.data(), nq, offs.data(), idx.data(), dist.data(), cap);
+        if (rc == ORBB_OK) return ORBB_OK;
+        if (rc != ORBB_E_CAPACITY) return rc;
+        cap = offs[nq] + 16;
+    }
+    return ORBB_E_CAPACITY;
+}
+
+// ORBmatcher::ComputeThreeMaxima (ORBmatcher.cpp:1792-1833)
+void three_maxima(const std::vector<int>* histo, int L, int& ind1, int& ind2, int& ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    for (int i = 0; i < L; i++) {
+        const int s = (int)histo[i].size();
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+        else if (s > max3) { max3 = s; ind3 = i; }
+    }
+    if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+    else if (max3 < 0.1f * (float)max1) ind3 = -1;
+}
+
+inline int rot_bin(float a1, float a2)
+{
+    float rot = a1 - a2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = (int)roundf(rot * (HISTO_LENGTH / 360.0f));
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+}
+}  // namespace
+
+extern "C" int orbm_search_by_projection_points(const orbm_frame* f, const float* uright, const orbm_proj_query* pq, int nq,
+                                                float nnratio, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches)
+{
+    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && (!frame_mp || !frame_mp_obs))) return ORBB_E_INVALID;
+    *nmatches = 0;
+    if (nq == 0) return ORBB_OK;
+    std::vector<orbm_query> q(nq);
+    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
+    std::vector<int> offs, idx, dist;
+    const int rc = run_window_search(f, q, offs, idx, dist);
+    if (rc != ORBB_OK) return rc;
+    int nm = 0;
+    for (int i = 0; i < nq; i++) {
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int c = offs[i]; c < offs[i + 1]; c++) {
+            const int k = idx[c];
+            if (frame_mp[k] >= 0 && frame_mp_obs[k] > 0) continue;                       // :112-114
+            if (uright && uright[k] > 0) {                                              // :116-121
+                const float er = fabsf(pq[i].u_right - uright[k]);
+                if (er > pq[i].max_err_right) continue;
+            }
+            const int d = dist[c];
+            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestLevel2 = bestLevel; bestLevel = f->h_kps[k].octave; bestIdx = k; }
+            else if (d < bestDist2) { bestLevel2 = f->h_kps[k].octave; bestDist2 = d; }
+        }
+        if (bestDist <= TH_HIGH) {                                                      // :142-151
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            frame_mp[bestIdx] = pq[i].id; frame_mp_obs[bestIdx] = pq[i].has_obs;
+            nm++;
+        }
+    }
+    *nmatches = nm;
+    return ORBB_OK;
+}
+
+extern "C" int orbm_search_by_projection_frame(const orbm_frame* f, const float* uright, const orbm_proj_query* pq, int nq,
+                                               int check_ori, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches)
+{
+    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && (!frame_mp || !frame_mp_obs))) return ORBB_E_INVALID;
+    *nmatches = 0;
+    if (nq == 0) return ORBB_OK;
+    std::vector<orbm_query> q(nq);
+    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
+    std::vector<int> offs, idx, dist;
+    const int rc = run_window_search(f, q, offs, idx, dist);
+    if (rc != ORBB_OK) return rc;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nm = 0;
+    for (int i = 0; i < nq; i++) {
+        int bestDist = 256, bestIdx2 = -1;
+        for (int c = offs[i]; c < offs[i + 1]; c++) {
+            const int k = idx[c];
+            if (frame_mp[k] >= 0 && frame_mp_obs[k] > 0) continue;                       // :1590-1592
+            if (uright && uright[k] > 0) {                                              // :1594-1601
+                const float er = fabsf(pq[i].u_right - uright[k]);
+                if (er > pq[i].max_err_right) continue;
+            }
+            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx2 = k; }
+        }
+        if (bestDist <= TH_HIGH) {                                                      // :1615-1632
+            frame_mp[bestIdx2] = pq[i].id; frame_mp_obs[bestIdx2] = pq[i].has_obs;
+            nm++;
+            if (check_ori) rotHist[rot_bin(pq[i].angle, f->h_kps[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (check_ori) {                                                                    // :1636-1656
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int b = 0; b < HISTO_LENGTH; b++)
+            if (b != ind1 && b != ind2 && b != ind3)
+                for (size_t j = 0; j < rotHist[b].size(); j++) { frame_mp[rotHist[b][j]] = -1; nm--; }
+    }
+    *nmatches = nm;
+    return ORBB_OK;
+}
+
+extern "C" int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev_xy, int32_t* m12,
+                                              int window, float nnratio, int check_ori, int* nmatches)
+{
+    if (!f1 || !f2 || !nmatches || (f1->n > 0 && (!prev_xy || !m12))) return ORBB_E_INVALID;
+    *nmatches = 0;
+    const int n1 = f1->n, n2 = f2->n;
+    for (int i = 0; i < n1; i++) m12[i] = -1;
+    // level-0 keypoints of F1 are the queries (:490-494)
+    std::vector<orbm_query> q; std::vector<int> qi;
+    for (int i = 0; i < n1; i++) {
+        if (f1->h_kps[i].octave > 0) continue;
+        orbm_query e;
+        e.u = prev_xy[2 * i]; e.v = prev_xy[2 * i + 1]; e.r = (float)window; e.min_level = 0; e.max_level = 0;
+        memcpy(e.desc, &f1->h_desc[(size_t)i * 32], 32);
+        q.push_back(e); qi.push_back(i);
+    }
+    std::vector<int> offs, idx, dist;
+    if (!q.empty()) { const int rc = run_window_search(f2, q, offs, idx, dist); if (rc != ORBB_OK) return rc; }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<int> vMatchedDistance(n2, 0x7fffffff), vnMatches21(n2, -1);
+    int nm = 0;
+    for (size_t qq = 0; qq < q.size(); qq++) {
+        const int i1 = qi[qq];
+        int bestDist = 0x7fffffff, bestDist2 = 0x7fffffff, bestIdx2 = -1;
+        for (int c = offs[qq]; c < offs[qq + 1]; c++) {
+            const int i2 = idx[c], d = dist[c];
+            if (vMatchedDistance[i2] <= d) continue;                                    // :513-514
+            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestIdx2 = i2; }
+            else if (d < bestDist2) bestDist2 = d;
+        }
+        if (bestDist <= TH_LOW && bestDist < (float)bestDist2 * nnratio) {              // :529-531
+            if (vnMatches21[bestIdx2] >= 0) { m12[vnMatches21[bestIdx2]] = -1; nm--; }
+            m12[i1] = bestIdx2; vnMatches21[bestIdx2] = i1; vMatchedDistance[bestIdx2] = bestDist;
+            nm++;
+            if (check_ori) rotHist[rot_bin(f1->h_kps[i1].angle, f2->h_kps[bestIdx2].angle)].push_back(i1);
+        }
+    }
+    if (check_ori) {                                                                    // :558-580
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int b = 0; b < HISTO_LENGTH; b++) {
+            if (b == ind1 || b == ind2 || b == ind3) continue;
+            for (size_t j = 0; j < rotHist[b].size(); j++) {
+                const int i1 = rotHist[b][j];
+                if (m12[i1] >= 0) { m12[i1] = -1; nm--; }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < n1; i1++)                                                     // :584-587
+        if (m12[i1] >= 0) { prev_xy[2 * i1] = f2->h_kps[m12[i1]].x; prev_xy[2 * i1 + 1] = f2->h_kps[m12[i1]].y; }
+    *nmatches = nm;
+    return ORBB_OK;
 }
 
 // ---- stereo ------------------------------------------------------------------------------------------

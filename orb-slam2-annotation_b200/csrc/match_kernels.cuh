@@ -118,7 +118,10 @@ __global__ void window_search_kernel(FrameDev f, const orbm_query* __restrict__ 
     if (!empty) {
         const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
         uint4 q0, q1;
-        if (FILL) { const uint4* qd = reinterpret_cast<const uint4*>(q.desc); q0 = qd[0]; q1 = qd[1]; }
+        if (FILL) {   // orbm_query::desc sits at byte offset 20 of a 52-byte record: 4-byte aligned only
+            const unsigned* qd = reinterpret_cast<const unsigned*>(q.desc);
+            q0 = make_uint4(qd[0], qd[1], qd[2], qd[3]); q1 = make_uint4(qd[4], qd[5], qd[6], qd[7]);
+        }
         for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
             // cells (ix, nMinCellY..nMaxCellY) are contiguous in the CSR (cell id = ix*GRID_ROWS + iy)
             const int b = f.cell_start[ix * GRID_ROWS + nMinCellY], e = f.cell_start[ix * GRID_ROWS + nMaxCellY + 1];

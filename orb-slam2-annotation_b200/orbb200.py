@@ -15,7 +15,9 @@ KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4
                      ("octave", "<i4"), ("class_id", "<i4")])
 QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"),
                         ("desc", "u1", (32,))])
-assert KP_DTYPE.itemsize == 28 and QUERY_DTYPE.itemsize == 52
+PROJ_QUERY_DTYPE = np.dtype([("q", QUERY_DTYPE), ("u_right", "<f4"), ("max_err_right", "<f4"), ("id", "<i4"),
+                             ("has_obs", "<i4"), ("angle", "<f4")])
+assert KP_DTYPE.itemsize == 28 and QUERY_DTYPE.itemsize == 52 and PROJ_QUERY_DTYPE.itemsize == 72
 
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_BAD_SHAPE, E_NOMEM, E_STATE = 0, -1, -2, -3, -4, -5, -6
 STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
@@ -24,6 +26,7 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
            "orbx_extract_batch", "orbx_sync", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbm_distance_pairs", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
+           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak",
@@ -71,6 +74,9 @@ def lib():
         L.orbm_frame_create.argtypes = [C.POINTER(vp), vp, vp, i32, f32, f32, f32, f32, i32]
         L.orbm_frame_destroy.argtypes = [vp]
         L.orbm_window_search.argtypes = [vp, vp, i32, vp, vp, vp, i32]
+        L.orbm_search_by_projection_points.argtypes = [vp, vp, vp, i32, f32, vp, vp, C.POINTER(i32)]
+        L.orbm_search_by_projection_frame.argtypes = [vp, vp, vp, i32, i32, vp, vp, C.POINTER(i32)]
+        L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, C.POINTER(i32)]
         L.orbm_stereo_match.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, f32, f32, vp, vp]
         L.orbm_db_create.argtypes = [C.POINTER(vp), C.c_int64, C.c_int64, i32]
         L.orbm_db_append.argtypes = [vp, vp, C.c_int64]
@@ -288,6 +294,46 @@ class FrameMatcher:
             return self.window_search(queries, cap=int(offs[nq]) + 16)
         _check(rc, "orbm_window_search")
         return offs, idx[:offs[nq]].copy(), dist[:offs[nq]].copy()
+
+
+class ORBmatcher:
+    """Mirror of ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:37-141) on flattened Frame state."""
+    TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30
+
+    def __init__(self, nnratio=0.6, checkOri=True):
+        self.mfNNratio = float(nnratio)
+        self.mbCheckOrientation = bool(checkOri)
+        self.L = lib()
+
+    @staticmethod
+    def DescriptorDistance(a, b, device=0):
+        return int(DescriptorDistance(a, b, device)[0])
+
+    def SearchByProjection_points(self, frame, proj_queries, frame_mp, frame_mp_obs, mvuRight=None):
+        q = np.ascontiguousarray(proj_queries, PROJ_QUERY_DTYPE)
+        mp = np.ascontiguousarray(frame_mp, np.int32).copy(); ob = np.ascontiguousarray(frame_mp_obs, np.int32).copy()
+        ur = None if mvuRight is None else np.ascontiguousarray(mvuRight, np.float32)
+        n = C.c_int()
+        _check(self.L.orbm_search_by_projection_points(frame.h, _p(ur), _p(q), len(q), self.mfNNratio, _p(mp), _p(ob), C.byref(n)),
+               "orbm_search_by_projection_points")
+        return n.value, mp, ob
+
+    def SearchByProjection_frame(self, frame, proj_queries, frame_mp, frame_mp_obs, mvuRight=None):
+        q = np.ascontiguousarray(proj_queries, PROJ_QUERY_DTYPE)
+        mp = np.ascontiguousarray(frame_mp, np.int32).copy(); ob = np.ascontiguousarray(frame_mp_obs, np.int32).copy()
+        ur = None if mvuRight is None else np.ascontiguousarray(mvuRight, np.float32)
+        n = C.c_int()
+        _check(self.L.orbm_search_by_projection_frame(frame.h, _p(ur), _p(q), len(q), int(self.mbCheckOrientation), _p(mp), _p(ob), C.byref(n)),
+               "orbm_search_by_projection_frame")
+        return n.value, mp, ob
+
+    def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
+        pm = np.ascontiguousarray(vbPrevMatched, np.float32).copy()
+        m12 = np.zeros(max(F1.n, 1), np.int32)
+        n = C.c_int()
+        _check(self.L.orbm_search_for_initialization(F1.h, F2.h, _p(pm), _p(m12), windowSize, self.mfNNratio,
+                                                     int(self.mbCheckOrientation), C.byref(n)), "orbm_search_for_initialization")
+        return n.value, m12[:F1.n], pm
 
 
 def stereo_match(exL, exR, kpsL, descL, kpsR, descR, mbf, mb=0.0):

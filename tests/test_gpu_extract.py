@@ -53,3 +53,108 @@ def test_final_parity(gpu, w, h, nf, seed):
     assert np.max(np.abs(ok["angle"] - gk["angle"])) <= 1e-3      # tolerance of BASELINE.json north_star
     bad = np.any(od != gd, axis=1).sum()
     assert bad <= 0.001 * len(od), f"{bad} of {len(od)} descriptors differ (> 0.1 %)"
+
+
+def test_edge_cases(gpu):
+    import orbb200, pyoracle
+    from synth import synth
+    ex = orbb200.ORBextractor(1000, max_size=(640, 480))
+    # flat image: zero keypoints, descriptors released (ORBextractor.cpp:1076-1077)
+    k, d = ex(np.full((480, 640), 77, np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+    # empty image: silent return (ORBextractor.cpp:1056-1057)
+    k, d = ex(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0
+    # non-contiguous rows (stride > width)
+    big = synth(700, 480, 31)
+    view = big[:, 30:670]
+    k1, d1 = ex(view)
+    k2, d2 = ex(np.ascontiguousarray(view))
+    assert k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
+    ok, od = pyoracle.OracleExtractor(1000).extract(np.ascontiguousarray(view))
+    assert k1.tobytes() == ok.tobytes() and np.array_equal(d1, od)
+    # a smaller image through the same handle (geometry switch), then back
+    small = synth(333, 257, 32)
+    ks, ds = ex(small)
+    oks, ods = pyoracle.OracleExtractor(1000).extract(small)
+    assert ks.tobytes() == oks.tobytes() and np.array_equal(ds, ods)
+    k3, d3 = ex(view)
+    assert k3.tobytes() == k1.tobytes()
+    # larger than the handle's maximum
+    with pytest.raises(orbb200.OrbError) as e:
+        ex(synth(800, 480, 1))
+    assert e.value.code == orbb200.E_BAD_SHAPE
+    # capacity too small: count reported, error returned, first `capacity` rows valid
+    import ctypes as C
+    cap = 100
+    kps = np.zeros(cap, orbb200.KP_DTYPE); desc = np.zeros((cap, 32), np.uint8); n = C.c_int()
+    img = np.ascontiguousarray(view)
+    rc = ex.L.orbx_extract(ex.h, img.ctypes.data_as(C.c_void_p), 640, 480, 640, kps.ctypes.data_as(C.c_void_p),
+                           desc.ctypes.data_as(C.c_void_p), cap, C.byref(n))
+    assert rc == orbb200.E_CAPACITY and n.value == len(k1) and kps.tobytes() == k1[:cap].tobytes()
+    # invalid configuration
+    with pytest.raises(orbb200.OrbError):
+        orbb200.ORBextractor(1000, iniThFAST=5, minThFAST=7)
+    # constructor tables
+    t = ex._tables(); o = pyoracle.OracleExtractor(1000).tables()
+    for key in t:
+        assert np.array_equal(t[key], o[key]), key
+
+
+def test_noise_and_extreme_textures(gpu):
+    """Uniform noise (10x the usual corner density, stresses the candidate buffers) and a hard checkerboard (score ties)."""
+    import orbb200, pyoracle
+    rng = np.random.default_rng(0)
+    ex = orbb200.ORBextractor(1500, max_size=(640, 480))
+    noise = rng.integers(0, 256, (480, 640), dtype=np.uint8)
+    yy, xx = np.mgrid[0:480, 0:640]
+    checker = ((((xx // 9) + (yy // 7)) & 1) * 200 + 20).astype(np.uint8)
+    for img in (noise, checker):
+        k, d = ex(img)
+        ok, od = pyoracle.OracleExtractor(1500).extract(img)
+        assert len(k) == len(ok)
+        for f in ("x", "y", "size", "response", "octave"):
+            assert np.array_equal(k[f], ok[f]), f
+        assert np.max(np.abs(k["angle"] - ok["angle"]), initial=0) <= 1e-3
+        assert np.any(d != od, axis=1).sum() <= max(1, 0.001 * len(d))
+
+
+def test_batch_equals_single(gpu):
+    """orbx_extract_batch (one launch sequence for F frames) == F single-frame calls; device-resident API too."""
+    import torch, orbb200
+    from synth import synth
+    F, w, h = 6, 752, 480
+    imgs = np.stack([synth(w, h, 100 + i) for i in range(F)])
+    ex1 = orbb200.ORBextractor(1200, max_size=(w, h))
+    exb = orbb200.ORBextractor(1200, max_size=(w, h), max_batch=F)
+    single = [ex1(imgs[i]) for i in range(F)]
+    batch = exb.extract_batch(imgs)
+    for (k1, d1), (k2, d2) in zip(single, batch):
+        assert k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
+    cap = 1500
+    dimg = torch.from_numpy(imgs).cuda()
+    kps = torch.zeros((F, cap, 7), dtype=torch.float32, device="cuda")
+    desc = torch.zeros((F, cap, 32), dtype=torch.uint8, device="cuda")
+    cnt = torch.zeros(F, dtype=torch.int32, device="cuda")
+    exb.extract_batch_device(dimg.data_ptr(), F, w, h, w, w * h, kps.data_ptr(), desc.data_ptr(), cnt.data_ptr(), cap)
+    exb.sync()
+    cnt = cnt.cpu().numpy()
+    for i in range(F):
+        k = kps[i, :cnt[i]].cpu().numpy().view(orbb200.KP_DTYPE).reshape(-1)
+        assert k.tobytes() == single[i][0].tobytes()
+        assert np.array_equal(desc[i, :cnt[i]].cpu().numpy(), single[i][1])
+
+
+def test_4k_frame(gpu):
+    """C4 shape: 3840x2160, 8000 keypoints, against the oracle."""
+    import orbb200, pyoracle
+    from synth import synth
+    img = synth(3840, 2160, 5000)
+    ex = orbb200.ORBextractor(8000, max_size=(3840, 2160))
+    k, d = ex(img)
+    ok, od = pyoracle.OracleExtractor(8000).extract(img)
+    assert len(k) == len(ok) and len(k) >= 8000
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(k[f], ok[f]), f
+    assert np.max(np.abs(k["angle"] - ok["angle"])) <= 1e-3
+    assert np.any(d != od, axis=1).sum() <= 0.001 * len(d)

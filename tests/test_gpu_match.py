@@ -1,0 +1,232 @@
+"""GPU parity of the Hamming-matching half: distances, grid window search, Search* functions, stereo, brute-force top-2.
+Every comparison is bit-exact (integer / index work) against the CPU oracle, through the C ABI."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _frames(w=640, h=480, nf=1000, seed=11, shift=(3, 1)):
+    """Two overlapping views: `cur` and `last` (= cur translated by `shift`), extracted with the CPU oracle."""
+    import pyoracle
+    from synth import synth
+    big = synth(w + 16, h + 16, seed)
+    cur = big[8:8 + h, 8:8 + w].copy()
+    last = big[8 + shift[1]:8 + shift[1] + h, 8 + shift[0]:8 + shift[0] + w].copy()
+    ex = pyoracle.OracleExtractor(nf)
+    kc, dc = ex.extract(cur)
+    kl, dl = ex.extract(last)
+    scale = ex.tables()["scale"]
+    return (cur, kc, dc), (last, kl, dl), scale
+
+
+def test_descriptor_distance(gpu):
+    import orbb200, pyoracle
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 256, (4097, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (4097, 32), dtype=np.uint8)
+    b[:10] = a[:10]                       # distance 0
+    b[10:20] = ~a[10:20]                  # distance 256
+    g = orbb200.DescriptorDistance(a, b)
+    assert np.array_equal(g, pyoracle.distance_pairs(a, b))
+    assert np.array_equal(g, np.unpackbits(a ^ b, axis=1).sum(1))
+    assert g[:10].max() == 0 and g[10:20].min() == 256
+    assert len(orbb200.DescriptorDistance(a[:0], b[:0])) == 0
+
+
+def _queries(kl, dl, scale, th, shift, rng, levels="pm1"):
+    import orbb200
+    q = np.zeros(len(kl), orbb200.PROJ_QUERY_DTYPE)
+    q["q"]["u"] = kl["x"] + shift[0]
+    q["q"]["v"] = kl["y"] + shift[1]
+    q["q"]["r"] = th * scale[kl["octave"]]
+    if levels == "pm1":
+        q["q"]["min_level"] = kl["octave"] - 1; q["q"]["max_level"] = kl["octave"] + 1
+    elif levels == "fwd":
+        q["q"]["min_level"] = kl["octave"]; q["q"]["max_level"] = -1
+    elif levels == "back":
+        q["q"]["min_level"] = 0; q["q"]["max_level"] = kl["octave"]
+    else:
+        q["q"]["min_level"] = kl["octave"] - 1; q["q"]["max_level"] = kl["octave"]
+    q["q"]["desc"] = dl
+    q["u_right"] = q["q"]["u"] - rng.uniform(0, 30, len(kl)).astype(np.float32)
+    q["max_err_right"] = q["q"]["r"]
+    q["id"] = np.arange(len(kl)); q["has_obs"] = (rng.random(len(kl)) < 0.9).astype(np.int32)
+    q["angle"] = kl["angle"]
+    return q
+
+
+def _to_oracle_queries(q):
+    import pyoracle
+    o = np.zeros(len(q), pyoracle.QUERY_DTYPE)
+    o["u"] = q["q"]["u"]; o["v"] = q["q"]["v"]; o["r"] = q["q"]["r"]
+    o["minLevel"] = q["q"]["min_level"]; o["maxLevel"] = q["q"]["max_level"]; o["desc"] = q["q"]["desc"]
+    o["uR"] = q["u_right"]; o["maxErrR"] = q["max_err_right"]; o["id"] = q["id"]; o["hasObs"] = q["has_obs"]; o["angle"] = q["angle"]
+    return o
+
+
+@pytest.mark.parametrize("levels", ["pm1", "fwd", "back", "pred"])
+def test_window_search_matches_GetFeaturesInArea(gpu, levels):
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames()
+    rng = np.random.default_rng(3)
+    h, w = cur.shape
+    F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h))
+    O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    q = _queries(kl, dl, scale, 15.0, (3, 1), rng, levels)
+    # edge cases: windows fully outside, huge radius, zero radius, queries on the image border
+    extra = q[:6].copy()
+    extra["q"]["u"] = [-500, 5000, 0, w, w / 2, w / 2]; extra["q"]["v"] = [h / 2, h / 2, 0, h, -400, h / 2]
+    extra["q"]["r"] = [10, 10, 50, 50, 10, 1e4]; extra["q"]["min_level"] = -1; extra["q"]["max_level"] = -1
+    q = np.concatenate([q, extra])
+    offs, idx, dist = F.window_search(q["q"])
+    oo, oi, od = O.window_search(_to_oracle_queries(q))
+    assert np.array_equal(offs, oo)
+    assert np.array_equal(idx, oi), "candidate ORDER must equal GetFeaturesInArea's (ix, iy, insertion)"
+    assert np.array_equal(dist, od)
+    assert offs[-1] - offs[-2] == len(kc)          # the 1e4-radius query sees every keypoint, in grid order
+
+
+def test_search_by_projection_last_frame(gpu):
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames()
+    rng = np.random.default_rng(8)
+    h, w = cur.shape
+    F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h)); O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    ur = np.where(rng.random(len(kc)) < 0.5, kc["x"] - rng.uniform(0, 30, len(kc)), -1).astype(np.float32)
+    for th, check in [(7.0, True), (15.0, True), (15.0, False)]:
+        q = _queries(kl, dl, scale, th, (3, 1), rng)
+        mp0 = np.full(len(kc), -1, np.int32); ob0 = np.zeros(len(kc), np.int32)
+        mp0[::17] = 9999; ob0[::17] = 1; mp0[5::23] = 7777          # pre-assigned points with / without observations
+        for uright in (None, ur):
+            n, mp, ob = orbb200.ORBmatcher(0.9, check).SearchByProjection_frame(F, q, mp0, ob0, uright)
+            on, omp, oob = O.search_last_frame(_to_oracle_queries(q), check, mp0, ob0, uright)
+            assert n == on and np.array_equal(mp, omp) and np.array_equal(ob, oob)
+            assert n > 0.3 * len(kl)                                 # the scenario really matches something
+
+
+def test_search_by_projection_local_points(gpu):
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=12)
+    rng = np.random.default_rng(9)
+    h, w = cur.shape
+    F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h)); O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    ur = np.where(rng.random(len(kc)) < 0.5, kc["x"] - rng.uniform(0, 30, len(kc)), -1).astype(np.float32)
+    for th in (1.0, 3.0):
+        q = _queries(kl, dl, scale, 1.0, (3, 1), rng, "pred")
+        rview = np.where(rng.random(len(kl)) < 0.5, 2.5, 4.0).astype(np.float32)     # RadiusByViewingCos
+        q["q"]["r"] = rview * (th if th != 1.0 else 1.0) * scale[kl["octave"]]
+        q["max_err_right"] = q["q"]["r"]
+        mp0 = np.full(len(kc), -1, np.int32); ob0 = np.zeros(len(kc), np.int32)
+        mp0[::19] = 4242; ob0[::19] = 1
+        for nnratio in (0.8, 0.6):
+            for uright in (None, ur):
+                n, mp, ob = orbb200.ORBmatcher(nnratio).SearchByProjection_points(F, q, mp0, ob0, uright)
+                on, omp, oob = O.search_local_points(_to_oracle_queries(q), nnratio, mp0, ob0, uright)
+                assert n == on and np.array_equal(mp, omp) and np.array_equal(ob, oob)
+    assert n > 50
+
+
+def test_search_for_initialization(gpu):
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(nf=2000, seed=13, shift=(6, -4))
+    h, w = cur.shape
+    F1 = orbb200.FrameMatcher(kl, dl, (0, 0, w, h)); F2 = orbb200.FrameMatcher(kc, dc, (0, 0, w, h))
+    O1 = pyoracle.OracleFrame(kl, dl, (0, 0, w, h)); O2 = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    prev = np.stack([kl["x"], kl["y"]], 1).astype(np.float32)
+    for check in (True, False):
+        n, m12, pm = orbb200.ORBmatcher(0.9, check).SearchForInitialization(F1, F2, prev, 100)
+        on, om12, opm = pyoracle.search_for_initialization(O1, O2, prev, 100, 0.9, check)
+        assert n == on and np.array_equal(m12, om12) and np.array_equal(pm, opm.reshape(pm.shape))
+        assert n > 100
+
+
+@pytest.mark.parametrize("w,h,nf,seed", [(1241, 376, 2000, 21), (752, 480, 1200, 22)])
+def test_stereo_matches(gpu, w, h, nf, seed):
+    """Frame::ComputeStereoMatches: uRight and depth bit-equal to the oracle (C2 / C3 shapes)."""
+    import orbb200, pyoracle
+    from synth import synth_stereo
+    L, R = synth_stereo(w, h, seed)
+    oL, oR = pyoracle.OracleExtractor(nf), pyoracle.OracleExtractor(nf)
+    okL, odL = oL.extract(L); okR, odR = oR.extract(R)
+    gL, gR = orbb200.ORBextractor(nf, max_size=(w, h)), orbb200.ORBextractor(nf, max_size=(w, h))
+    kL, dL = gL(L); kR, dR = gR(R)
+    assert kL.tobytes() == okL.tobytes() and kR.tobytes() == okR.tobytes()
+    mbf = 386.1448 if w == 1241 else 47.90639384423901           # KITTI00-02.yaml / EuRoC.yaml Camera.bf
+    for mb in (0.0, 0.537):                                       # reference call (mb == 0) and a finite baseline
+        ur, dp = orbb200.stereo_match(gL, gR, kL, dL, kR, dR, mbf, mb)
+        with np.errstate(divide="ignore"):
+            our, odp, _, _ = pyoracle.stereo_match(oL, oR, mbf, mb)
+        assert np.array_equal(ur, our) and np.array_equal(dp, odp)
+    assert (ur >= 0).sum() > 0.2 * len(kL)
+
+
+def test_bf_top2_small_and_edges(gpu):
+    import orbb200, pyoracle
+    from synth import synth_descriptor_db, synth_queries
+    db = synth_descriptor_db(50_000, seed=1)
+    db[777] = db[123]; db[40_000] = db[123]                       # exact duplicates: first index must win, d2 == d1
+    q = synth_queries(db, 1037, seed=2)                           # not a multiple of the 512-query tile
+    q[0] = db[123]
+    for nrows in (0, 1, 2, 127, 128, 129, 4097, 50_000):
+        D = orbb200.DescriptorDB(max(nrows, 1)); D.append(db[:nrows])
+        d1, i1, d2 = D.top2(q)
+        o1, oi, o2 = pyoracle.bf_top2(db[:nrows], q, nthreads=8)
+        assert np.array_equal(d1, o1) and np.array_equal(i1, oi) and np.array_equal(d2, o2), nrows
+        D.close()
+    assert d1[0] == 0 and i1[0] == 123 and d2[0] == 0
+    assert len(orbb200.DescriptorDB(4).top2(q[:0])[0]) == 0
+
+
+def test_bf_top2_sharded_merge_equals_single(gpu):
+    """Shard the DB into contiguous ranges, merge per-shard top-2 on the device (the post-all-gather step):
+    identical to the unsharded scan and to the oracle."""
+    import torch, orbb200, pyoracle
+    from synth import synth_descriptor_db, synth_queries
+    db = synth_descriptor_db(300_000, seed=3)
+    db[250_000] = db[10]                                          # a tie that straddles shards
+    q = synth_queries(db, 2000, seed=4); q[1] = db[10]
+    o1, oi, o2 = pyoracle.bf_top2(db, q, nthreads=8)
+    for G in (1, 3, 8):
+        bounds = np.linspace(0, len(db), G + 1).astype(np.int64)
+        d1a = torch.empty((G, len(q)), dtype=torch.int32, device="cuda"); i1a = torch.empty((G, len(q)), dtype=torch.int64, device="cuda")
+        d2a = torch.empty((G, len(q)), dtype=torch.int32, device="cuda")
+        qd = torch.from_numpy(q).cuda()
+        shards = []
+        for g in range(G):
+            D = orbb200.DescriptorDB(int(bounds[g + 1] - bounds[g]), row_offset=int(bounds[g])); D.append(db[bounds[g]:bounds[g + 1]])
+            D.top2_device(qd.data_ptr(), len(q), d1a[g].data_ptr(), i1a[g].data_ptr(), d2a[g].data_ptr())
+            shards.append(D)
+        d1 = torch.empty(len(q), dtype=torch.int32, device="cuda"); i1 = torch.empty(len(q), dtype=torch.int64, device="cuda")
+        d2 = torch.empty(len(q), dtype=torch.int32, device="cuda")
+        orbb200.merge_top2_device(d1a.data_ptr(), i1a.data_ptr(), d2a.data_ptr(), G, len(q), d1.data_ptr(), i1.data_ptr(), d2.data_ptr())
+        torch.cuda.synchronize()
+        assert np.array_equal(d1.cpu().numpy(), o1) and np.array_equal(i1.cpu().numpy(), oi) and np.array_equal(d2.cpu().numpy(), o2), G
+    acc = orbb200.ratio_test(o1, o2, 50, 0.75)
+    assert 0.3 * len(q) < acc.sum() < 0.6 * len(q)                # about the planted half passes the ratio test
+
+
+def test_bf_top2_full_size_properties(gpu):
+    """C5 at one GPU's full size (10 M rows): planted queries are found at distance 0 with the FIRST duplicate's index,
+    d1 <= d2 everywhere, and a sample of queries equals the CPU scan of the whole database."""
+    import torch, orbb200, pyoracle
+    M = 10_000_000
+    g = torch.Generator(device="cuda"); g.manual_seed(42)
+    dbt = torch.randint(0, 256, (M, 32), dtype=torch.uint8, device="cuda", generator=g)
+    rows = torch.tensor([5, 123_456, 9_999_999, 5_000_000], device="cuda")
+    dbt[7_000_000] = dbt[123_456]                                 # duplicate later in the DB
+    q = torch.randint(0, 256, (2000, 32), dtype=torch.uint8, device="cuda", generator=g)
+    q[:4] = dbt[rows]
+    D = orbb200.DescriptorDB(M); D.append_device(dbt.data_ptr(), M)
+    d1 = torch.empty(2000, dtype=torch.int32, device="cuda"); i1 = torch.empty(2000, dtype=torch.int64, device="cuda")
+    d2 = torch.empty(2000, dtype=torch.int32, device="cuda")
+    D.top2_device(q.data_ptr(), 2000, d1.data_ptr(), i1.data_ptr(), d2.data_ptr())
+    torch.cuda.synchronize()
+    d1, i1, d2 = d1.cpu().numpy(), i1.cpu().numpy(), d2.cpu().numpy()
+    assert np.array_equal(d1[:4], [0, 0, 0, 0]) and np.array_equal(i1[:4], [5, 123_456, 9_999_999, 5_000_000])
+    assert d2[1] == 0                                             # the duplicate is the second best
+    assert np.all(d1 <= d2) and np.all((i1 >= 0) & (i1 < M))
+    dbh = dbt.cpu().numpy(); qh = q.cpu().numpy()
+    sel = np.array([0, 1, 2, 3, 500, 1999])
+    o1, oi, o2 = pyoracle.bf_top2(dbh, qh[sel], nthreads=8)
+    assert np.array_equal(d1[sel], o1) and np.array_equal(i1[sel], oi) and np.array_equal(d2[sel], o2)
