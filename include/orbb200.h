@@ -94,6 +94,12 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, in
 /* Blocks until the handle's stream is idle; returns the first asynchronous error, and ORBB_E_CAPACITY if an
  * internal candidate buffer overflowed during the last extraction. */
 int orbx_sync(orbx_handle* h);
+/* Measurement support: with profiling on, every extraction records CUDA events around its three kernel classes on the
+ * handle's stream and accumulates their durations: ms3[0] the per-level resize/blur/FAST kernels, ms3[1] the octree
+ * kernel, ms3[2] the orientation+descriptor kernel; *calls = extractions accumulated.  (Adds one host sync per call:
+ * never leave it on inside a throughput measurement.) */
+int orbx_set_profiling(orbx_handle* h, int on);
+int orbx_get_profile(orbx_handle* h, double* ms3, int* calls);
 /* cudaStream_t of the handle (for event timing by the caller). */
 void* orbx_stream(orbx_handle* h);
 

@@ -16,6 +16,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <cstddef>
 #include <vector>
 #include <algorithm>
 
@@ -99,22 +100,26 @@ static inline void gaussian_blur7_u8(const uint8_t* src, int w, int h, size_t ss
     static const int Q[7] = {18, 34, 48, 56, 48, 34, 18};
     static const int QL[7] = {18, 34, 49, 55, 49, 34, 18};
     const int* q = legacy ? QL : Q;
-    std::vector<uint32_t> hbuf((size_t)w * h);
+    std::vector<uint16_t> hbuf((size_t)w * h);
+    std::vector<uint8_t> pad((size_t)w + 6);
     for (int y = 0; y < h; y++) {
         const uint8_t* S = src + (size_t)y * sstride;
+        for (int x = 0; x < w + 6; x++) pad[x] = S[reflect101(x - 3, w)];
+        uint16_t* H = &hbuf[(size_t)y * w];
         for (int x = 0; x < w; x++) {
-            uint32_t acc = 0;
-            for (int k = 0; k < 7; k++) acc += (uint32_t)q[k] * S[reflect101(x + k - 3, w)];
-            hbuf[(size_t)y * w + x] = acc;
+            const uint8_t* p = &pad[x];
+            H[x] = (uint16_t)(q[0] * p[0] + q[1] * p[1] + q[2] * p[2] + q[3] * p[3] + q[4] * p[4] + q[5] * p[5] + q[6] * p[6]);
         }
     }
     for (int y = 0; y < h; y++) {
+        const uint16_t* R[7];
+        for (int k = 0; k < 7; k++) R[k] = &hbuf[(size_t)reflect101(y + k - 3, h) * w];
         uint8_t* D = dst + (size_t)y * dstride;
         for (int x = 0; x < w; x++) {
-            uint32_t acc = 0;
-            for (int k = 0; k < 7; k++) acc += (uint32_t)q[k] * hbuf[(size_t)reflect101(y + k - 3, h) * w + x];
-            uint32_t v = (acc + 32768u) >> 16;
-            D[x] = (uint8_t)std::min<uint32_t>(v, 255u);
+            const uint32_t acc = (uint32_t)q[0] * R[0][x] + (uint32_t)q[1] * R[1][x] + (uint32_t)q[2] * R[2][x] + (uint32_t)q[3] * R[3][x] +
+                                 (uint32_t)q[4] * R[4][x] + (uint32_t)q[5] * R[5][x] + (uint32_t)q[6] * R[6][x];
+            const uint32_t v = (acc + 32768u) >> 16;
+            D[x] = (uint8_t)(v > 255u ? 255u : v);
         }
     }
 }
@@ -133,15 +138,16 @@ static const int kRingDy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1,
 static inline int fast_arc_score(const uint8_t* img, size_t stride, int x, int y)
 {
     const int v = img[(size_t)y * stride + x];
-    int d[25];
-    for (int k = 0; k < 16; k++)
-        d[k] = v - img[(size_t)(y + kRingDy[k]) * stride + (x + kRingDx[k])];
-    for (int k = 16; k < 25; k++) d[k] = d[k - 16];
+    int d[16], e[16];
+    for (int k = 0; k < 16; k++) { d[k] = v - img[(size_t)(y + kRingDy[k]) * stride + (x + kRingDx[k])]; e[k] = -d[k]; }
+    int a2[16], b2[16], a4[16], b4[16];
+    for (int k = 0; k < 16; k++) { a2[k] = std::min(d[k], d[(k + 1) & 15]); b2[k] = std::min(e[k], e[(k + 1) & 15]); }
+    for (int k = 0; k < 16; k++) { a4[k] = std::min(a2[k], a2[(k + 2) & 15]); b4[k] = std::min(b2[k], b2[(k + 2) & 15]); }
     int best = -256;
     for (int k = 0; k < 16; k++) {
-        int mn = d[k], mx = d[k];
-        for (int j = 1; j < 9; j++) { mn = std::min(mn, d[k + j]); mx = std::max(mx, d[k + j]); }
-        best = std::max(best, std::max(mn, -mx));
+        const int a9 = std::min(std::min(a4[k], a4[(k + 4) & 15]), d[(k + 8) & 15]);
+        const int b9 = std::min(std::min(b4[k], b4[(k + 4) & 15]), e[(k + 8) & 15]);
+        best = std::max(best, std::max(a9, b9));
     }
     return best;
 }
@@ -151,25 +157,51 @@ static inline void fast9_16_nms(const uint8_t* img, int w, int h, size_t stride,
 {
     out.clear();
     if (w < 7 || h < 7) return;
-    std::vector<int> score((size_t)w * h, 0);
-    for (int y = 3; y < h - 3; y++)
+    std::vector<uint8_t> score((size_t)w * h, 0);
+    std::vector<int> cand;
+    std::vector<uint8_t> flag((size_t)w, 0);
+    const int t = threshold;
+    std::ptrdiff_t off[16];
+    for (int k = 0; k < 16; k++) off[k] = (std::ptrdiff_t)kRingDy[k] * (std::ptrdiff_t)stride + kRingDx[k];
+    for (int y = 3; y < h - 3; y++) {
+        const uint8_t* r0 = img + (size_t)y * stride;
+        const uint8_t* rm = r0 - 3 * stride;
+        const uint8_t* rp = r0 + 3 * stride;
+        // pass 1 (auto-vectorised): necessary condition, as cv::FAST's first tests — any 9-arc holds two ADJACENT
+        // compass pixels of one polarity
         for (int x = 3; x < w - 3; x++) {
-            int m = fast_arc_score(img, stride, x, y);
-            if (m > threshold) score[(size_t)y * w + x] = m - 1;
+            const int v = r0[x];
+            const int d0 = v - rp[x], d4 = v - r0[x + 3], d8 = v - rm[x], d12 = v - r0[x - 3];
+            const int k0 = d0 > t, k4 = d4 > t, k8 = d8 > t, k12 = d12 > t;
+            const int b0 = -d0 > t, b4 = -d4 > t, b8 = -d8 > t, b12 = -d12 > t;
+            flag[x] = (uint8_t)((k0 & k4) | (k4 & k8) | (k8 & k12) | (k12 & k0) | (b0 & b4) | (b4 & b8) | (b8 & b12) | (b12 & b0));
         }
-    for (int y = 3; y < h - 3; y++)
+        // pass 2: exact corner test on 16-bit brighter/darker masks, score only for corners
         for (int x = 3; x < w - 3; x++) {
-            int s = score[(size_t)y * w + x];
-            if (s == 0) continue;   // m > th >= 0  =>  m-1 >= th; th==0 corner with m==1 scores 0 and
-                                    // can never beat its (>=0) neighbours under strict '>' either.
-            bool keep = true;
-            for (int dy = -1; dy <= 1 && keep; dy++)
-                for (int dx = -1; dx <= 1; dx++) {
-                    if (!dx && !dy) continue;
-                    if (s <= score[(size_t)(y + dy) * w + (x + dx)]) { keep = false; break; }
-                }
-            if (keep) out.push_back(FastKp{x, y, s});
+            if (!flag[x]) continue;
+            const uint8_t* pc = r0 + x;
+            const int v = *pc, lo = v - t, hi = v + t;
+            unsigned dk = 0, br = 0;
+            for (int k = 0; k < 16; k++) {
+                const int p = pc[off[k]];
+                dk |= (unsigned)(p < lo) << k; br |= (unsigned)(p > hi) << k;
+            }
+            unsigned a = dk | (dk << 16), b = br | (br << 16);
+            unsigned ya = a & (a >> 1), yb = b & (b >> 1);
+            ya &= ya >> 2; yb &= yb >> 2; ya &= ya >> 4; yb &= yb >> 4; ya &= a >> 8; yb &= b >> 8;
+            if (!((ya | yb) & 0xffffu)) continue;
+            const int m = fast_arc_score(img, stride, x, y);
+            score[(size_t)y * w + x] = (uint8_t)(m - 1); cand.push_back(y * w + x);
         }
+    }
+    for (int idx : cand) {
+        const int y = idx / w, x = idx - y * w;
+        const int s = score[idx];
+        if (s == 0) continue;   // threshold 0 with m == 1: response 0 never beats its neighbours under strict '>'
+        const uint8_t* c = &score[idx];
+        if (s > c[-1] && s > c[1] && s > c[-w - 1] && s > c[-w] && s > c[-w + 1] && s > c[w - 1] && s > c[w] && s > c[w + 1])
+            out.push_back(FastKp{x, y, s});
+    }
 }
 
 // ---------------------------------------------------------------------------------------

@@ -20,7 +20,7 @@ struct Arena {
         void* p = base + used; used += n; return p;
     }
 };
-Arena g_arena;
+thread_local Arena g_arena;   // one arena per calling thread: the timed CPU baseline runs one extractor per thread
 }
 
 void* operator new(size_t n) { return g_arena.take(n); }

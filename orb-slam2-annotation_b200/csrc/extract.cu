@@ -57,6 +57,11 @@ struct orbx_handle {
     uint8_t *h_img = nullptr, *h_desc = nullptr;
     orbx_keypoint* h_kps = nullptr;
     int *h_counts = nullptr, *h_status = nullptr;
+    // optional per-kernel timing (bench.py roofline): events around each kernel class
+    bool profiling = false;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    double prof_ms[3] = {0, 0, 0};     // level kernels, octree, orientation+descriptor
+    int prof_calls = 0;
     // last extraction
     int last_frames = 0;
     const uint8_t* last_src = nullptr; long long last_src_pitch = 0, last_src_fstride = 0;
@@ -291,6 +296,7 @@ extern "C" int orbx_destroy(orbx_handle* h)
     cudaFree(h->d_status); cudaFree(h->d_counts); cudaFree(h->d_tab); cudaFree(h->d_tiles); cudaFree(h->d_geom);
     cudaFree(h->d_node_off); cudaFree(h->d_cell_off); cudaFree(h->d_kps); cudaFree(h->d_desc);
     cudaFreeHost(h->h_img); cudaFreeHost(h->h_kps); cudaFreeHost(h->h_desc); cudaFreeHost(h->h_counts); cudaFreeHost(h->h_status);
+    for (int i = 0; i < 4; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBB_OK;
@@ -326,6 +332,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
     cudaStream_t st = h->stream;
     ORBB_CUDA(cudaMemsetAsync(h->d_rec_count, 0, sizeof(int) * (size_t)nframes * nl, st));
     ORBB_CUDA(cudaMemsetAsync(h->d_status, 0, sizeof(int) * (size_t)nframes, st));
+    if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[0], st));
     for (int l = 0; l < nl; l++) {
         const LevelGeom& g = h->geom[l];
         LevelArgs a;
@@ -348,6 +355,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         level_kernel<<<grid, NT, 0, st>>>(a);
         ORBB_LAUNCHED();
     }
+    if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[1], st));
     {
         OctArgs a;
         memset(&a, 0, sizeof a);
@@ -363,6 +371,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         octree_kernel<<<dim3(nl, nframes), NTO, 0, st>>>(a);
         ORBB_LAUNCHED();
     }
+    if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[2], st));
     {
         DescArgs a;
         memset(&a, 0, sizeof a);
@@ -376,6 +385,12 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         const int maxk = capacity < (int)h->out_total ? capacity : (int)h->out_total;
         orient_desc_kernel<<<dim3(ceil_div(maxk > 0 ? maxk : 1, 8), nframes), 256, 0, st>>>(a);
         ORBB_LAUNCHED();
+    }
+    if (h->profiling) {
+        ORBB_CUDA(cudaEventRecord(h->ev[3], st));
+        ORBB_CUDA(cudaEventSynchronize(h->ev[3]));
+        for (int i = 0; i < 3; i++) { float ms = 0; ORBB_CUDA(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1])); h->prof_ms[i] += ms; }
+        h->prof_calls++;
     }
     ORBB_CUDA(cudaGetLastError());
     h->last_frames = nframes;
@@ -404,6 +419,23 @@ extern "C" int orbx_sync(orbx_handle* h)
         ORBB_CUDA(cudaMemcpy(h->h_status, h->d_status, sizeof(int) * h->last_frames, cudaMemcpyDeviceToHost));
         for (int f = 0; f < h->last_frames; f++) if (h->h_status[f]) return ORBB_E_CAPACITY;
     }
+    return ORBB_OK;
+}
+
+extern "C" int orbx_set_profiling(orbx_handle* h, int on)
+{
+    if (!h) return ORBB_E_INVALID;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    if (on && !h->ev[0]) for (int i = 0; i < 4; i++) ORBB_CUDA(cudaEventCreate(&h->ev[i]));
+    h->profiling = on != 0;
+    h->prof_ms[0] = h->prof_ms[1] = h->prof_ms[2] = 0; h->prof_calls = 0;
+    return ORBB_OK;
+}
+extern "C" int orbx_get_profile(orbx_handle* h, double* ms3, int* calls)
+{
+    if (!h || !ms3) return ORBB_E_INVALID;
+    for (int i = 0; i < 3; i++) ms3[i] = h->prof_ms[i];
+    if (calls) *calls = h->prof_calls;
     return ORBB_OK;
 }
 
@@ -449,8 +481,18 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     if (rc != ORBB_OK) return rc;
     ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
     ORBB_CUDA(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
-    ORBB_CUDA(cudaMemcpyAsync(h->h_kps, h->d_kps, sizeof(orbx_keypoint) * (size_t)nframes * devcap, cudaMemcpyDeviceToHost, st));
-    ORBB_CUDA(cudaMemcpyAsync(h->h_desc, h->d_desc, (size_t)32 * nframes * devcap, cudaMemcpyDeviceToHost, st));
+    // results: straight into the caller's buffers when they are pinned and share the device layout, else via staging
+    bool direct = capacity == devcap && capacity > 0;
+    if (direct) {
+        cudaPointerAttributes a1, a2;
+        direct = cudaPointerGetAttributes(&a1, kps_host) == cudaSuccess && a1.type == cudaMemoryTypeHost &&
+                 cudaPointerGetAttributes(&a2, desc_host) == cudaSuccess && a2.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+    }
+    orbx_keypoint* kdst = direct ? kps_host : h->h_kps;
+    uint8_t* ddst = direct ? desc_host : h->h_desc;
+    ORBB_CUDA(cudaMemcpyAsync(kdst, h->d_kps, sizeof(orbx_keypoint) * (size_t)nframes * devcap, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaMemcpyAsync(ddst, h->d_desc, (size_t)32 * nframes * devcap, cudaMemcpyDeviceToHost, st));
     ORBB_CUDA(cudaStreamSynchronize(st));
     int ret = ORBB_OK;
     for (int f = 0; f < nframes; f++) {
@@ -459,7 +501,7 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
         if (h->h_status[f]) ret = ORBB_E_CAPACITY;
         const int m = n < capacity ? n : capacity;
         if (n > capacity) ret = ORBB_E_CAPACITY;
-        if (m > 0) {
+        if (m > 0 && !direct) {
             memcpy(kps_host + (size_t)f * capacity, h->h_kps + (size_t)f * devcap, sizeof(orbx_keypoint) * m);
             memcpy(desc_host + (size_t)f * capacity * 32, h->h_desc + (size_t)f * devcap * 32, (size_t)32 * m);
         }

@@ -24,7 +24,7 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 
 # every symbol include/orbb200.h declares (tests check the .so exports all of them)
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
-           "orbx_extract_batch", "orbx_sync", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
+           "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbm_distance_pairs", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
@@ -66,6 +66,8 @@ def lib():
         L.orbx_extract_batch_device.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32]
         L.orbx_extract_batch.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32]
         L.orbx_sync.argtypes = [vp]
+        L.orbx_set_profiling.argtypes = [vp, i32]
+        L.orbx_get_profile.argtypes = [vp, vp, C.POINTER(i32)]
         L.orbx_stream.argtypes = [vp]
         L.orbx_stream.restype = vp
         L.orbx_pyramid_level.argtypes = [vp, i32, i32, vp, sz, C.POINTER(i32), C.POINTER(i32)]
@@ -218,6 +220,15 @@ class ORBextractor:
 
     def stream(self):
         return int(self.L.orbx_stream(self.h) or 0)
+
+    def set_profiling(self, on):
+        _check(self.L.orbx_set_profiling(self.h, int(on)), "orbx_set_profiling")
+
+    def get_profile(self):
+        ms = np.zeros(3, np.float64)
+        calls = C.c_int()
+        _check(self.L.orbx_get_profile(self.h, _p(ms), C.byref(calls)), "orbx_get_profile")
+        return dict(level_ms=ms[0], octree_ms=ms[1], desc_ms=ms[2], calls=calls.value)
 
     # --- mvImagePyramid (ORBextractor.h:85) and parity stages ---
     def pyramid_level(self, level, frame=0):

@@ -68,12 +68,13 @@ def synth_descriptor_db(m, seed=42):
 
 
 def synth_queries(db, nq, seed=43, max_flips=60):
-    """Half of the queries are database rows with k~U{0..max_flips} random bit flips, half fresh random."""
+    """Half of the queries are database rows with k~U{0..max_flips} random bit flips, half fresh random.
+    If `db` holds exactly nq//2 rows they are used as the planted rows in order."""
     rng = np.random.default_rng(seed)
     m = db.shape[0]
     q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
     nhit = nq // 2
-    rows = rng.integers(0, m, nhit)
+    rows = np.arange(nhit) if m == nhit else rng.integers(0, m, nhit)
     hit = db[rows].copy()
     bits = np.unpackbits(hit, axis=1)
     for i in range(nhit):
