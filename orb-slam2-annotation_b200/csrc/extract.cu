@@ -383,7 +383,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         a.kps = kps_dev; a.desc = desc_dev; a.counts = counts_dev; a.capacity = capacity;
         a.factorPI = h->factorPI;
         const int maxk = capacity < (int)h->out_total ? capacity : (int)h->out_total;
-        orient_desc_kernel<<<dim3(ceil_div(maxk > 0 ? maxk : 1, 8), nframes), 256, 0, st>>>(a);
+        orient_desc_kernel<<<dim3(ceil_div(maxk > 0 ? maxk : 1, 256), nframes), 256, 0, st>>>(a);
         ORBB_LAUNCHED();
     }
     if (h->profiling) {

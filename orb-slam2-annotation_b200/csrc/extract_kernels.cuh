@@ -730,66 +730,89 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
     return a;
 }
 
+// One warp owns 32 consecutive output slots.  Phase A: the warp visits its keypoints one by one, lane = patch COLUMN
+// u (coalesced row reads), REDUX-reduces m10/m01 and parks them in lane j.  Phase B: every lane finishes ITS keypoint
+// (fastAtan2, cos/sin in double -> float: 32 keypoints per instruction instead of one).  Phase C: the warp visits the
+// keypoints again, lane = descriptor BYTE, the 16 pattern points of that byte live in registers as floats.
 __global__ void __launch_bounds__(256) orient_desc_kernel(const __grid_constant__ DescArgs a)
 {
     const int f = blockIdx.y, lane = threadIdx.x & 31;
     const int wid = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    // locate (level, index) from the per-level counts
+    const int base = wid * 32;
     const int* cnt = a.lvl_count + (long long)f * a.nlevels;
-    int level = -1, idx = 0, acc = 0, total = 0;
+    // own keypoint: (level, index) from the per-level counts
+    const int slot = base + lane;
+    int level = -1, idx = 0, acc = 0;
     for (int l = 0; l < a.nlevels; l++) {
         const int c = cnt[l];
-        if (level < 0 && wid < acc + c) { level = l; idx = wid - acc; }
+        if (level < 0 && slot < acc + c) { level = l; idx = slot - acc; }
         acc += c;
     }
-    total = acc;
+    const int total = acc;
     if (wid == 0 && lane == 0) a.counts[f] = total;
-    if (level < 0 || wid >= a.capacity) return;
-
-    const LevelGeom g = a.geom[level];
-    const int4 k = a.lvl[(long long)f * a.lvl_fstride + g.out_off + idx];
-    const uint8_t* img; long long pitch;
-    if (level == 0) { img = a.src0 + (long long)f * a.src0_fstride; pitch = a.src0_pitch; }
-    else { img = a.pyr + (long long)f * a.pyr_fstride + g.off; pitch = g.pitch; }
-
-    // IC_Angle: lane l handles patch row v = l - 15
-    int s_u = 0, s_1 = 0;
-    const int v = lane - 15;
-    if (lane < 31) {
-        const int d = c_umax[abs(v)];
-        const uint8_t* row = img + (long long)(k.y + v) * pitch + k.x;
-        for (int u = -d; u <= d; u++) { const int val = row[u]; s_u += u * val; s_1 += val; }
+    const int nvalid = min(min(total, a.capacity) - base, 32);      // keypoints handled by this warp
+    if (nvalid <= 0) return;
+    const bool mine = lane < nvalid;
+    int kx = 0, ky = 0, kresp = 0, pitch = 0, bpitch = 0;
+    const uint8_t* img = nullptr; const uint8_t* bimg = nullptr;
+    float scale = 1.f, size = 0.f;
+    if (mine) {
+        const LevelGeom& g = a.geom[level];
+        const int4 k = a.lvl[(long long)f * a.lvl_fstride + g.out_off + idx];
+        kx = k.x; ky = k.y; kresp = k.z;
+        if (level == 0) { img = a.src0 + (long long)f * a.src0_fstride; pitch = (int)a.src0_pitch; }
+        else { img = a.pyr + (long long)f * a.pyr_fstride + g.off; pitch = g.pitch; }
+        bimg = a.blur + (long long)f * a.blur_fstride + g.off; bpitch = g.pitch;
+        img += (long long)ky * pitch + kx; bimg += (long long)ky * bpitch + kx;          // patch centres
+        scale = g.scale; size = g.size;
     }
-    int m10 = s_u, m01 = v * s_1;
+    // ---- phase A: intensity centroid (IC_Angle, ORBextractor.cpp:79-106); lane = column u = lane - 15 ----
+    const int u = lane - 15;
+    const int dmax = lane < 31 ? c_umax[abs(u)] : -1;      // the disc is symmetric: |v| <= umax[|u|]
+    int my_m10 = 0, my_m01 = 0;
+    for (int j = 0; j < nvalid; j++) {
+        const uint8_t* c = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)img, j);
+        const int p = __shfl_sync(0xffffffffu, pitch, j);
+        int s = 0, sv = 0;
 #pragma unroll
-    for (int o = 16; o; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
-
-    // steered BRIEF: lane i computes descriptor byte i
+        for (int v = -15; v <= 15; v++) {
+            if (abs(v) <= dmax) { const int val = c[v * p + u]; s += val; sv += v * val; }
+        }
+        const int m10 = __reduce_add_sync(0xffffffffu, u * s);
+        const int m01 = __reduce_add_sync(0xffffffffu, sv);
+        if (lane == j) { my_m10 = m10; my_m01 = m01; }
+    }
+    // ---- phase B: per-lane angle and rotation ----
+    const float angle = fast_atan2_deg((float)my_m01, (float)my_m10);
     const float ar = __fmul_rn(angle, a.factorPI);
     const float ca = (float)cos((double)ar), sb = (float)sin((double)ar);
-    const uint8_t* bimg = a.blur + (long long)f * a.blur_fstride + g.off;
-    const uint8_t* center = bimg + (long long)k.y * g.pitch + k.x;
-    const int8_t* pat = c_pattern + lane * 32;
-    int val = 0;
-#pragma unroll
-    for (int b = 0; b < 8; b++) {
-        const float x0 = (float)pat[4 * b], y0 = (float)pat[4 * b + 1], x1 = (float)pat[4 * b + 2], y1 = (float)pat[4 * b + 3];
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sb), __fmul_rn(y0, ca)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sb)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sb), __fmul_rn(y1, ca)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sb)));
-        const int t0 = center[(long long)r0 * g.pitch + c0], t1 = center[(long long)r1 * g.pitch + c1];
-        val |= (t0 < t1) << b;
-    }
-    const long long o = (long long)f * a.capacity + wid;
-    a.desc[o * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
+    if (mine) {
         orbx_keypoint kp;
-        kp.x = level ? __fmul_rn((float)k.x, g.scale) : (float)k.x;
-        kp.y = level ? __fmul_rn((float)k.y, g.scale) : (float)k.y;
-        kp.size = g.size; kp.angle = angle; kp.response = (float)k.z; kp.octave = level; kp.class_id = -1;
-        a.kps[o] = kp;
+        kp.x = level ? __fmul_rn((float)kx, scale) : (float)kx;
+        kp.y = level ? __fmul_rn((float)ky, scale) : (float)ky;
+        kp.size = size; kp.angle = angle; kp.response = (float)kresp; kp.octave = level; kp.class_id = -1;
+        a.kps[(long long)f * a.capacity + slot] = kp;
+    }
+    // ---- phase C: steered BRIEF (computeOrbDescriptor, ORBextractor.cpp:110-149); lane = descriptor byte ----
+    float px[16], py[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) { px[i] = (float)c_pattern[lane * 32 + 2 * i]; py[i] = (float)c_pattern[lane * 32 + 2 * i + 1]; }
+    uint8_t* dout = a.desc + ((long long)f * a.capacity + base) * 32 + lane;
+    for (int j = 0; j < nvalid; j++) {
+        const uint8_t* c = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)bimg, j);
+        const int p = __shfl_sync(0xffffffffu, bpitch, j);
+        const float cj = __shfl_sync(0xffffffffu, ca, j), sj = __shfl_sync(0xffffffffu, sb, j);
+        int val = 0;
+#pragma unroll
+        for (int b = 0; b < 8; b++) {
+            const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(px[2 * b], sj), __fmul_rn(py[2 * b], cj)));
+            const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(px[2 * b], cj), __fmul_rn(py[2 * b], sj)));
+            const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(px[2 * b + 1], sj), __fmul_rn(py[2 * b + 1], cj)));
+            const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(px[2 * b + 1], cj), __fmul_rn(py[2 * b + 1], sj)));
+            const int t0 = c[r0 * p + c0], t1 = c[r1 * p + c1];
+            val |= (t0 < t1) << b;
+        }
+        dout[j * 32] = (uint8_t)val;
     }
 }
 
