@@ -348,6 +348,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
             a.dxs = h->d_tiles + g.dxs_off; a.dys = h->d_tiles + g.dys_off;
         }
         a.fast_on = g.nCols > 0; a.wCell = g.wCell; a.hCell = g.hCell; a.minTh = h->cfg.min_th_fast;
+        a.magicW = (unsigned)((0x100000000ull + g.wCell - 1) / g.wCell); a.magicH = (unsigned)((0x100000000ull + g.hCell - 1) / g.hCell);
         a.rec = h->d_rec + g.rec_off; a.rec_cap = g.rec_cap; a.rec_fstride = (long long)h->rec_total;
         a.rec_count = h->d_rec_count + l; a.rec_count_stride = nl;
         for (int i = 0; i < 7; i++) a.q[i] = h->q[i];

@@ -13,245 +13,13 @@
 // m = max over 9-arcs, float ops with explicit _rn intrinsics (no FMA contraction), round-half-even conversions.
 #pragma once
 #include "common.cuh"
+#include "level_kernel.cuh"
 
 namespace orbb {
-
-constexpr int TW = 64, TH = 32, HALO = 4, NT = 256;
-constexpr int SMW = 80;               // shared tile pitch (72 bytes used)
-constexpr int SMH = TH + 2 * HALO;    // 40 rows
-constexpr int SCW = TW + 2, SCH = TH + 2;
-constexpr int EMIT_CAP = 1024;
 
 __constant__ int8_t c_pattern[1024];  // rBRIEF pattern (ORBextractor.cpp:152-410), x0,y0,x1,y1 per test
 __constant__ int c_umax[16];          // circular patch row ends (ORBextractor.cpp:456-471)
 __constant__ float c_atan[4];         // fastAtan2 polynomial p1,p3,p5,p7 (already scaled to degrees)
-
-struct LevelArgs {
-    const uint8_t* src; long long src_pitch, src_fstride;   // level L (external input image when L == 0)
-    int w, h;
-    uint8_t* blur; long long blur_pitch, blur_fstride;      // blurred level L out
-    uint8_t* dst; long long dst_pitch, dst_fstride;         // level L+1 out (null on the last level)
-    const int2* xt; const int2* yt; const int* dxs; const int* dys;
-    int fast_on, wCell, hCell, minTh;
-    uint32_t* rec; int rec_cap; long long rec_fstride;      // raw FAST records  y<<20 | x<<8 | m
-    int* rec_count; int rec_count_stride;
-    int q[7];                                               // Q8 blur kernel
-};
-
-__device__ __forceinline__ int reflect101(int p, int n)
-{
-    if (p < 0) p = -p;
-    if (p >= n) p = 2 * (n - 1) - p;
-    return min(max(p, 0), n - 1);
-}
-
-// Threshold-independent FAST arc score m(x,y) = max over the 16 arcs of 9 contiguous ring pixels of
-// max(min(v - p_k), min(p_k - v)).  Corner at threshold t iff m > t; cv::FAST's response is m - 1.
-__device__ __forceinline__ int fast_arc_score(const uint8_t (*tile)[SMW], int ty, int tx)
-{
-    const int v = tile[ty][tx];
-    int d[16];
-    d[0] = v - tile[ty + 3][tx];      d[1] = v - tile[ty + 3][tx + 1];  d[2] = v - tile[ty + 2][tx + 2];
-    d[3] = v - tile[ty + 1][tx + 3];  d[4] = v - tile[ty][tx + 3];      d[5] = v - tile[ty - 1][tx + 3];
-    d[6] = v - tile[ty - 2][tx + 2];  d[7] = v - tile[ty - 3][tx + 1];  d[8] = v - tile[ty - 3][tx];
-    d[9] = v - tile[ty - 3][tx - 1];  d[10] = v - tile[ty - 2][tx - 2]; d[11] = v - tile[ty - 1][tx - 3];
-    d[12] = v - tile[ty][tx - 3];     d[13] = v - tile[ty + 1][tx - 3]; d[14] = v - tile[ty + 2][tx - 2];
-    d[15] = v - tile[ty + 3][tx - 1];
-    // Both polarities are reduced with MIN networks (e = p_k - v is formed explicitly).  Do NOT rewrite this as
-    // max(mn9, -mx9): ptxas 12.9 (-O1 and above, sm_100a) fuses that into VIMNMX3 and drops the negation
-    // (found by tests; -Xptxas -O0 was correct).  tools/level_dbg.cu is the regression harness.
-    int e[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) e[k] = -d[k];
-    int a2[16], b2[16], a4[16], b4[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) { a2[k] = min(d[k], d[(k + 1) & 15]); b2[k] = min(e[k], e[(k + 1) & 15]); }
-#pragma unroll
-    for (int k = 0; k < 16; k++) { a4[k] = min(a2[k], a2[(k + 2) & 15]); b4[k] = min(b2[k], b2[(k + 2) & 15]); }
-    int best = -256;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const int a9 = min(min(a4[k], a4[(k + 4) & 15]), d[(k + 8) & 15]);
-        const int b9 = min(min(b4[k], b4[(k + 4) & 15]), e[(k + 8) & 15]);
-        best = max(best, max(a9, b9));
-    }
-    return best;
-}
-
-__global__ void __launch_bounds__(NT) level_kernel(const __grid_constant__ LevelArgs a)
-{
-    __shared__ __align__(16) uint8_t tile[SMH][SMW];
-    __shared__ uint16_t hb[TH + 6][TW];
-    __shared__ uint8_t sc[SCH][SCW + 2];
-    __shared__ uint16_t queue[SCH * SCW];
-    __shared__ uint32_t emit[EMIT_CAP];
-    __shared__ int s_qn, s_en, s_ebase;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int f = blockIdx.z;
-    const int x0 = blockIdx.x * TW, y0 = blockIdx.y * TH;
-    const uint8_t* __restrict__ src = a.src + (long long)f * a.src_fstride;
-    if (tid == 0) { s_qn = 0; s_en = 0; }
-
-    // ---- 1. stage tile + halo (REFLECT_101 at the image border, as the blur of a cloned level sees it) ----
-    for (int r = warp; r < SMH; r += NT / 32) {
-        const int gy = reflect101(y0 - HALO + r, a.h);
-        const uint8_t* row = src + (long long)gy * a.src_pitch;
-        for (int c = lane; c < TW + 2 * HALO; c += 32) tile[r][c] = row[reflect101(x0 - HALO + c, a.w)];
-    }
-    for (int i = tid; i < SCH * (SCW + 2); i += NT) (&sc[0][0])[i] = 0;
-    __syncthreads();
-
-    // ---- 2. blur, horizontal pass (Q8.8) ----
-#ifndef DBG_NOBLUR
-    for (int i = tid; i < (TH + 6) * TW; i += NT) {
-        const int r = i >> 6, c = i & 63;
-        const uint8_t* p = &tile[r + 1][c + 1];
-        int s = 0;
-#pragma unroll
-        for (int k = 0; k < 7; k++) s += a.q[k] * p[k];
-        hb[r][c] = (uint16_t)s;
-    }
-#endif
-
-    // ---- 3. FAST quick test -> candidate queue ----
-    const bool fast_tile = a.fast_on && (x0 + TW >= 19) && (x0 - 1 <= a.w - 20) && (y0 + TH >= 19) && (y0 - 1 <= a.h - 20);
-    if (fast_tile) {
-        const int t = a.minTh;
-        for (int r = warp; r < SCH; r += NT / 32) {
-            const int gy = y0 - 1 + r;
-            const bool rowok = gy >= 19 && gy <= a.h - 20;
-            for (int c = lane; c < SCW + 30; c += 32) {     // 3 warp iterations cover 66 columns
-                bool pass = false;
-                if (rowok && c < SCW) {
-                    const int gx = x0 - 1 + c;
-                    if (gx >= 19 && gx <= a.w - 20) {
-                        const int ty = r + 3, tx = c + 3;
-                        const int v = tile[ty][tx];
-                        const int d0 = v - tile[ty + 3][tx], d4 = v - tile[ty][tx + 3];
-                        const int d8 = v - tile[ty - 3][tx], d12 = v - tile[ty][tx - 3];
-                        // any 9-arc contains two ADJACENT compass points: both darker or both brighter
-                        const int dk = (d0 > t) | ((d4 > t) << 1) | ((d8 > t) << 2) | ((d12 > t) << 3);
-                        const int br = (-d0 > t) | ((-d4 > t) << 1) | ((-d8 > t) << 2) | ((-d12 > t) << 3);
-                        const int dk2 = dk & ((dk >> 1) | (dk << 3)), br2 = br & ((br >> 1) | (br << 3));
-                        pass = ((dk2 | br2) & 15) != 0;
-#ifdef DBG_NOQUICK
-                        pass = true;
-#endif
-                    }
-                }
-                const unsigned bal = __ballot_sync(0xffffffffu, pass);
-                if (bal) {
-                    int base = 0;
-                    if (lane == 0) base = atomicAdd(&s_qn, __popc(bal));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (pass) queue[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)(r * SCW + c);
-                }
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- 4. blur, vertical pass (Q16.16) and store ----
-#ifndef DBG_NOBLUR
-    {
-        uint8_t* __restrict__ bl = a.blur + (long long)f * a.blur_fstride;
-        for (int i = tid; i < TH * TW; i += NT) {
-            const int r = i >> 6, c = i & 63;
-            const int gy = y0 + r, gx = x0 + c;
-            if (gy < a.h && gx < a.w) {
-                unsigned s = 0;
-#pragma unroll
-                for (int k = 0; k < 7; k++) s += (unsigned)a.q[k] * hb[r + k][c];
-                bl[(long long)gy * a.blur_pitch + gx] = (uint8_t)min((s + 32768u) >> 16, 255u);
-            }
-        }
-    }
-#endif
-
-    // ---- 5. bilinear resize of the destination pixels whose source origin lies in this tile ----
-    if (a.dst) {
-        uint8_t* __restrict__ dst = a.dst + (long long)f * a.dst_fstride;
-        const int dx0 = a.dxs[blockIdx.x], dx1 = a.dxs[blockIdx.x + 1];
-        const int dy0 = a.dys[blockIdx.y], dy1 = a.dys[blockIdx.y + 1];
-        const int cx_i = tid & 63;
-        if (dx0 + cx_i < dx1) {
-            const int dx = dx0 + cx_i;
-            const int2 cx = a.xt[dx];
-            const int tx = cx.x - (x0 - HALO);
-            const int a0 = (short)(cx.y & 0xffff), a1 = cx.y >> 16;
-            for (int dy = dy0 + (tid >> 6); dy < dy1; dy += NT / 64) {
-                const int2 cy = a.yt[dy];
-                const int ty = cy.x - (y0 - HALO);
-                const int b0 = (short)(cy.y & 0xffff), b1 = cy.y >> 16;
-                const int h0 = tile[ty][tx] * a0 + tile[ty][tx + 1] * a1;
-                const int h1 = tile[ty + 1][tx] * a0 + tile[ty + 1][tx + 1] * a1;
-                const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-                dst[(long long)dy * a.dst_pitch + dx] = (uint8_t)min(max(v, 0), 255);
-            }
-        }
-    }
-
-    if (!fast_tile) return;
-
-    // ---- 6. full arc score for the queued pixels ----
-    const int qn = s_qn;
-    for (int j = tid; j < qn; j += NT) {
-        const int pos = queue[j];
-        const int r = pos / SCW, c = pos - r * SCW;
-        const int m = fast_arc_score(tile, r + 3, c + 3);
-        sc[r][c] = (uint8_t)(m > a.minTh ? m : 0);
-    }
-    __syncthreads();
-
-    // ---- 7. cell-local 3x3 non-max suppression (strict '>') and emission ----
-    for (int j = tid; j < qn; j += NT) {
-        const int pos = queue[j];
-        const int r = pos / SCW, c = pos - r * SCW;
-        if (r < 1 || r > TH || c < 1 || c > TW) continue;       // halo ring: scored for neighbours only
-        const int m = sc[r][c];
-        if (!m) continue;
-        const int gx = x0 - 1 + c, gy = y0 - 1 + r;
-        const int cellx = (gx - 19) / a.wCell, celly = (gy - 19) / a.hCell;
-        bool keep = true;
-#pragma unroll
-        for (int dy = -1; dy <= 1; dy++)
-#pragma unroll
-            for (int dx = -1; dx <= 1; dx++) {
-                if (!dx && !dy) continue;
-                const int mq = sc[r + dy][c + dx];
-                if (mq >= m) {   // neighbour is a corner with score >= ours: it suppresses us iff it is in OUR cell
-                    if ((gx + dx - 19) / a.wCell == cellx && (gy + dy - 19) / a.hCell == celly) keep = false;
-                }
-            }
-#ifdef DBG_PRINT
-        {
-            const int m2 = fast_arc_score(tile, r + 3, c + 3);
-            const int gv = src[(long long)gy * a.src_pitch + gx];
-            if (gx == 599 && gy == 450) {
-                printf("GPU ring around (599,450) center %d:", tile[r+3][c+3]);
-                for (int yy = -3; yy <= 3; yy++) { printf("\n   "); for (int xx = -3; xx <= 3; xx++) printf("%4d", tile[r + 3 + yy][c + 3 + xx]); }
-                printf("\n sc=%d\n", m);
-            }
-            if ((m2 != m || gv != tile[r + 3][c + 3]) && blockIdx.x == 3 && blockIdx.y == 2)
-                printf("blk(%d,%d) j=%d pos=%d r=%d c=%d gx=%d gy=%d sc=%d recomputed=%d tilev=%d globalv=%d\n", blockIdx.x, blockIdx.y, j, pos, r, c, gx, gy, m, m2, tile[r + 3][c + 3], gv);
-        }
-#endif
-        if (keep) {
-            const int e = atomicAdd(&s_en, 1);
-            if (e < EMIT_CAP) emit[e] = ((unsigned)gy << 20) | ((unsigned)gx << 8) | (unsigned)m;
-        }
-    }
-    __syncthreads();
-    const int en = s_en;
-    if (en == 0) return;
-    if (tid == 0) s_ebase = atomicAdd(a.rec_count + (long long)f * a.rec_count_stride, en);
-    __syncthreads();
-    const int ebase = s_ebase;
-    uint32_t* __restrict__ rec = a.rec + (long long)f * a.rec_fstride;
-    for (int j = tid; j < min(en, EMIT_CAP); j += NT)
-        if (ebase + j < a.rec_cap) rec[ebase + j] = emit[j];
-}
 
 // =====================================================================================================
 // Octree distribution (ORBextractor.cpp:541-770).  Order-free formulation: the reference's result depends on the

@@ -16,7 +16,7 @@ int main()
     cudaMemcpy(d_img, img.data(), W * H, cudaMemcpyHostToDevice); cudaMemset(d_cnt, 0, 4);
     LevelArgs a; memset(&a, 0, sizeof a);
     a.src = d_img; a.src_pitch = W; a.w = W; a.h = H; a.blur = d_blur; a.blur_pitch = W;
-    a.fast_on = 1; a.wCell = 31; a.hCell = 32; a.minTh = 7; a.rec = d_rec; a.rec_cap = 100000; a.rec_count = d_cnt; a.rec_count_stride = 1;
+    a.fast_on = 1; a.wCell = 31; a.hCell = 32; a.minTh = 7; a.magicW = (unsigned)((0x100000000ull + 30) / 31); a.magicH = (unsigned)((0x100000000ull + 31) / 32); a.rec = d_rec; a.rec_cap = 100000; a.rec_count = d_cnt; a.rec_count_stride = 1;
     const int Q[7] = {18, 34, 48, 56, 48, 34, 18}; for (int i = 0; i < 7; i++) a.q[i] = Q[i];
     level_kernel<<<dim3((W + TW - 1) / TW, (H + TH - 1) / TH, 1), NT>>>(a);
     int n = 0; cudaMemcpy(&n, d_cnt, 4, cudaMemcpyDeviceToHost);
