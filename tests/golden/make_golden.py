@@ -1,0 +1,109 @@
+#!/usr/bin/env python3
+"""Generates the golden fixtures under tests/golden/ (run in the build container, where cv2 4.13 and /root/reference exist).
+
+The reference (SFXiang/ORB-SLAM2-Annotation) ships no golden vectors or tests for this path, so the oracle is
+pinned against outputs of the real implementations, generated here and committed:
+
+  cv2_prims.npz   OpenCV 4.13.0 itself (cv2): the third-party primitives ORBextractor.cpp calls —
+                  cv::resize INTER_LINEAR (ORBextractor.cpp:1136), cv::GaussianBlur 7x7 s=2 REFLECT_101 (:1098),
+                  cv::FAST 9-16 + NMS at thresholds 20 and 7 (:818-825), cv::fastAtan2 (:105), BFMatcher Hamming knn (k=2).
+  ref_extract.npz the reference's own ORBextractor.cpp, compiled unmodified from /root/reference (oracle/_ref), run on
+                  seeded synthetic frames: full keypoint + descriptor output, pyramid checksums.
+
+Inputs are regenerated from seeds by synth.py (numpy only), so only outputs are stored.  Usage: python tests/golden/make_golden.py
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path[:0] = [os.path.join(ROOT, "orb-slam2-annotation_b200"), os.path.join(ROOT, "oracle")]
+
+from synth import synth, synth_descriptor_db, synth_queries  # noqa: E402
+
+PRIM_SHAPES = [(160, 120, 11), (97, 61, 12), (203, 77, 13)]     # (w, h, seed): small, odd widths, ragged cell grids
+ATAN_N = 4096
+
+
+def level_sizes(w, h, nlevels=8, sf=1.2):
+    sc = np.float32(1.0)
+    out = []
+    for _ in range(nlevels):
+        inv = np.float32(1.0) / sc
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+        sc = np.float32(np.float64(sc) * np.float64(np.float32(sf)))
+    return out
+
+
+def kp_exact_bytes(k):
+    """The bit-exact part of a keypoint array (everything but the angle), field by field."""
+    return b"".join(np.ascontiguousarray(k[f]).tobytes() for f in ("x", "y", "size", "response", "octave", "class_id"))
+
+
+def atan_inputs():
+    rng = np.random.default_rng(99)
+    y = rng.integers(-200000, 200000, ATAN_N).astype(np.float32)
+    x = rng.integers(-200000, 200000, ATAN_N).astype(np.float32)
+    y[:8] = [0, 0, 1, -1, 5, -5, 0, 3]
+    x[:8] = [0, 1, 0, 0, 5, 5, -7, -3]
+    return y, x
+
+
+def main():
+    import cv2
+    cv2.setNumThreads(1)
+    out = {"cv2_version": np.array(cv2.__version__)}
+    for (w, h, seed) in PRIM_SHAPES:
+        img = synth(w, h, seed)
+        tag = f"{w}x{h}_{seed}"
+        cur = img
+        for L, (lw, lh) in enumerate(level_sizes(w, h)):
+            if L > 0:
+                cur = cv2.resize(cur, (lw, lh), interpolation=cv2.INTER_LINEAR)
+                out[f"pyr_{tag}_L{L}"] = cur
+            out[f"blur_{tag}_L{L}"] = cv2.GaussianBlur(cur, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+        for th in (20, 7):
+            det = cv2.FastFeatureDetector_create(th, True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+            kps = det.detect(img)
+            out[f"fast{th}_{tag}"] = np.array([(int(k.pt[0]), int(k.pt[1]), int(k.response)) for k in kps], np.int32).reshape(-1, 3)
+    tiny = synth(13, 9, 14)
+    out["blur_13x9_14"] = cv2.GaussianBlur(tiny, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+    out["resize_13x9_14_to_11x8"] = cv2.resize(tiny, (11, 8), interpolation=cv2.INTER_LINEAR)
+    y, x = atan_inputs()
+    out["atan2"] = np.array([cv2.fastAtan2(float(a), float(b)) for a, b in zip(y, x)], np.float32)
+    # Hamming: cv2.BFMatcher knn (k=2) distances on a small random DB; indices only where the best is unique
+    db = synth_descriptor_db(3000, seed=5)
+    q = synth_queries(db, 64, seed=6)
+    m = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, db, k=2)
+    out["bf_d1"] = np.array([p[0].distance for p in m], np.int32)
+    out["bf_d2"] = np.array([p[1].distance for p in m], np.int32)
+    out["bf_i1"] = np.array([p[0].trainIdx for p in m], np.int64)
+    np.savez_compressed(os.path.join(HERE, "cv2_prims.npz"), **out)
+
+    import pyoracle
+    ref = {}
+    for (w, h, nf, seed) in [(320, 240, 500, 21), (203, 177, 300, 22)]:
+        ex = pyoracle.RefExtractor(nf)
+        k, d = ex.extract(synth(w, h, seed))
+        tag = f"{w}x{h}_{nf}_{seed}"
+        ref[f"kps_{tag}"] = k
+        ref[f"desc_{tag}"] = d
+        ref[f"pyrsha_{tag}"] = np.array([hashlib.sha256(ex.level_image(L).tobytes()).hexdigest() for L in range(8)])
+    for (w, h, nf, seed) in [(640, 480, 1000, 1), (1241, 376, 2000, 2), (752, 480, 1200, 3)]:   # config shapes: checksums only
+        ex = pyoracle.RefExtractor(nf)
+        k, d = ex.extract(synth(w, h, seed))
+        tag = f"{w}x{h}_{nf}_{seed}"
+        ref[f"count_{tag}"] = np.array(len(k))
+        ref[f"kpsha_{tag}"] = np.array(hashlib.sha256(kp_exact_bytes(k)).hexdigest())
+        ref[f"angles_{tag}"] = k["angle"].copy()
+        ref[f"descsha_{tag}"] = np.array(hashlib.sha256(d.tobytes()).hexdigest())
+    np.savez_compressed(os.path.join(HERE, "ref_extract.npz"), **ref)
+    for f in ("cv2_prims.npz", "ref_extract.npz"):
+        print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")
+
+
+if __name__ == "__main__":
+    main()
