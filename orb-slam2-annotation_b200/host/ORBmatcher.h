@@ -1,0 +1,145 @@
+// ORBmatcher.h — host-side mirror of the Hamming core of ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:37-141)
+// over liborbb200's C ABI.  The reference's Search* members take Frame / KeyFrame / MapPoint objects, which stay in the
+// reference; what moves to the device is their inner loop: GetFeaturesInArea + DescriptorDistance + top-1/top-2
+// bookkeeping.  This header offers the same constants and DescriptorDistance, plus RAII wrappers for the device-side
+// Frame image and descriptor database, so the bodies of ORBmatcher.cc shrink to "fill queries -> one call -> copy the
+// result into mvpMapPoints" (INTEGRATION.md shows the patch).
+#ifndef ORBB_HOST_ORBMATCHER_H
+#define ORBB_HOST_ORBMATCHER_H
+
+#include <stdint.h>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "orbb_cv.h"
+#include "../../include/orbb200.h"
+
+namespace ORB_SLAM2 {
+
+class MatcherDeviceError : public std::runtime_error {
+public:
+    MatcherDeviceError(int code_, const std::string& what_) : std::runtime_error(what_), code(code_) {}
+    int code;
+};
+
+inline void orbm_check(int rc, const char* where)
+{
+    if (rc == ORBB_OK) return;
+    std::string msg = std::string(where) + ": " + orbb200_strerror(rc);
+    if (rc == ORBB_E_CUDA) msg += std::string(" — ") + orbb200_last_cuda_error();
+    throw MatcherDeviceError(rc, msg);
+}
+
+// Device image of a Frame's matching state: mvKeysUn, mDescriptors and the 64x48 grid (src/Frame.cc:241-257).
+class DeviceFrame {
+public:
+    DeviceFrame(const std::vector<cv::KeyPoint>& keysUn, const cv::Mat& descriptors, float minX, float minY, float maxX, float maxY, int device = 0)
+        : f_(nullptr), n_((int)keysUn.size())
+    {
+        std::vector<uint8_t> d((size_t)n_ * 32);
+        for (int i = 0; i < n_; i++) memcpy(&d[(size_t)i * 32], descriptors.ptr(i), 32);
+        orbm_check(orbm_frame_create(&f_, (const orbx_keypoint*)keysUn.data(), d.data(), n_, minX, minY, maxX, maxY, device), "orbm_frame_create");
+    }
+    ~DeviceFrame() { if (f_) orbm_frame_destroy(f_); }
+    DeviceFrame(const DeviceFrame&) = delete;
+    DeviceFrame& operator=(const DeviceFrame&) = delete;
+    const orbm_frame* get() const { return f_; }
+    int size() const { return n_; }
+
+private:
+    orbm_frame* f_;
+    int n_;
+};
+
+// One shard of a keyframe-descriptor database for relocalisation / loop-candidate brute-force matching.
+class DeviceDescriptorDB {
+public:
+    DeviceDescriptorDB(int64_t capacityRows, int64_t rowOffset = 0, int device = 0) : db_(nullptr)
+    {
+        orbm_check(orbm_db_create(&db_, capacityRows, rowOffset, device), "orbm_db_create");
+    }
+    ~DeviceDescriptorDB() { if (db_) orbm_db_destroy(db_); }
+    DeviceDescriptorDB(const DeviceDescriptorDB&) = delete;
+    DeviceDescriptorDB& operator=(const DeviceDescriptorDB&) = delete;
+    void Append(const cv::Mat& descriptors)
+    {
+        std::vector<uint8_t> d((size_t)descriptors.rows * 32);
+        for (int i = 0; i < descriptors.rows; i++) memcpy(&d[(size_t)i * 32], descriptors.ptr(i), 32);
+        orbm_check(orbm_db_append(db_, d.data(), descriptors.rows), "orbm_db_append");
+    }
+    int64_t Rows() const { return orbm_db_rows(db_); }
+    // best distance, GLOBAL row of the best (first on ties), second-best distance per query row
+    void Top2(const cv::Mat& queries, std::vector<int32_t>& d1, std::vector<int64_t>& idx1, std::vector<int32_t>& d2) const
+    {
+        const int nq = queries.rows;
+        std::vector<uint8_t> q((size_t)nq * 32);
+        for (int i = 0; i < nq; i++) memcpy(&q[(size_t)i * 32], queries.ptr(i), 32);
+        d1.resize(nq); idx1.resize(nq); d2.resize(nq);
+        orbm_check(orbm_bf_top2(db_, q.data(), nq, d1.data(), idx1.data(), d2.data()), "orbm_bf_top2");
+    }
+    const orbm_db* get() const { return db_; }
+
+private:
+    orbm_db* db_;
+};
+
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+
+    // include/ORBmatcher.h:45, src/ORBmatcher.cpp:1838-1854.  Routed to the device like everything else in this mirror (no
+    // host arithmetic); per-pair callers outside the hot path (MapPoint::ComputeDistinctiveDescriptors, SearchByBoW) should
+    // keep the reference's own static function or batch their pairs through DescriptorDistances().
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b, int device = 0)
+    {
+        int32_t d = -1;
+        orbm_check(orbm_distance_pairs(a.ptr(0), b.ptr(0), 1, &d, device), "orbm_distance_pairs");
+        return d;
+    }
+    static void DescriptorDistances(const uint8_t* a, const uint8_t* b, int n, int32_t* out, int device = 0)
+    {
+        orbm_check(orbm_distance_pairs(a, b, n, out, device), "orbm_distance_pairs");
+    }
+
+    // src/ORBmatcher.cpp:63-155 after the caller filled one orbm_proj_query per visible map point.
+    int SearchByProjection(const DeviceFrame& F, const std::vector<float>* mvuRight, const std::vector<orbm_proj_query>& q,
+                           std::vector<int32_t>& frameMapPointIds, std::vector<int32_t>& frameMapPointHasObs) const
+    {
+        int n = 0;
+        orbm_check(orbm_search_by_projection_points(F.get(), mvuRight ? mvuRight->data() : nullptr, q.data(), (int)q.size(), mfNNratio,
+                                                    frameMapPointIds.data(), frameMapPointHasObs.data(), &n), "orbm_search_by_projection_points");
+        return n;
+    }
+    // src/ORBmatcher.cpp:1506-1659 (Current vs Last frame) after the projection step.
+    int SearchByProjectionLastFrame(const DeviceFrame& Current, const std::vector<float>* mvuRight, const std::vector<orbm_proj_query>& q,
+                                    std::vector<int32_t>& frameMapPointIds, std::vector<int32_t>& frameMapPointHasObs) const
+    {
+        int n = 0;
+        orbm_check(orbm_search_by_projection_frame(Current.get(), mvuRight ? mvuRight->data() : nullptr, q.data(), (int)q.size(),
+                                                   mbCheckOrientation ? 1 : 0, frameMapPointIds.data(), frameMapPointHasObs.data(), &n),
+                   "orbm_search_by_projection_frame");
+        return n;
+    }
+    // src/ORBmatcher.cpp:474-590
+    int SearchForInitialization(const DeviceFrame& F1, const DeviceFrame& F2, std::vector<cv::Point2f>& vbPrevMatched,
+                                std::vector<int>& vnMatches12, int windowSize = 10) const
+    {
+        int n = 0;
+        vnMatches12.assign(F1.size(), -1);
+        static_assert(sizeof(cv::Point2f) == 8, "Point2f layout");
+        orbm_check(orbm_search_for_initialization(F1.get(), F2.get(), (float*)vbPrevMatched.data(), vnMatches12.data(), windowSize, mfNNratio,
+                                                  mbCheckOrientation ? 1 : 0, &n), "orbm_search_for_initialization");
+        return n;
+    }
+
+    static const int TH_LOW = 50;         // src/ORBmatcher.cpp:37-39
+    static const int TH_HIGH = 100;
+    static const int HISTO_LENGTH = 30;
+
+protected:
+    float mfNNratio;
+    bool mbCheckOrientation;
+};
+
+}  // namespace ORB_SLAM2
+#endif
