@@ -34,6 +34,7 @@ struct orbx_handle {
     float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS], sigma2[ORBB_MAX_LEVELS], inv_sigma2[ORBB_MAX_LEVELS];
     int per_level[ORBB_MAX_LEVELS], umax[16];
     int q[7];
+    int l3_warps = 4;          // warps per level-kernel CTA (tile = 120 x 8*warps pixels)
     float factorPI;
     // geometry for the current image shape
     int cur_w = 0, cur_h = 0;
@@ -76,12 +77,14 @@ static void level_sizes(const orbx_handle* h, int w, int ht, int* lw, int* lh)
     }
 }
 
-// cv::resize INTER_LINEAR coefficient tables for src -> dst along one axis.
-static void build_axis_table(int src, int dst, int tile, int2* tab, int* tile_first, int ntiles)
+// cv::resize INTER_LINEAR coefficient tables for src -> dst along one axis: tab[d] = {source index, a0 | a1 << 16}.
+// `padded` >= dst entries are written (the tail replicates the last real entry: destination words are stored whole).
+// own_first[t] = first destination UNIT (unit = `unit` destination entries; x: a 4-pixel word, y: a row) whose first
+// entry has source index >= t * tile - bias; own_first[ntiles] = number of units.
+static void build_axis_table(int src, int dst, int padded, int2* tab, int tile, int bias, int unit, int* own_first, int ntiles)
 {
     const double inv_scale = (double)dst / src;
     const double sc = 1.0 / inv_scale;
-    int t = 0;
     for (int d = 0; d < dst; d++) {
         float f = (float)((d + 0.5) * sc - 0.5);
         int s = (int)floorf(f);
@@ -90,9 +93,17 @@ static void build_axis_table(int src, int dst, int tile, int2* tab, int* tile_fi
         if (s >= src - 1) { s = src - 1; f = 0.f; }
         const int a0 = cv_round_f((1.f - f) * 2048.f), a1 = cv_round_f(f * 2048.f);
         tab[d] = make_int2(s, (a0 & 0xffff) | (a1 << 16));
-        while (t < ntiles && s >= t * tile) tile_first[t++] = d;
     }
-    while (t <= ntiles) tile_first[t++] = dst;
+    for (int d = dst; d < padded; d++) tab[d] = tab[dst - 1];
+    const int nunits = ceil_div(dst, unit);
+    int t = 0;
+    for (int u = 0; u < nunits; u++) {
+        const int s = tab[u * unit].x;
+        while (t < ntiles && s >= t * tile - bias) own_first[t++] = u;
+    }
+    own_first[0] = 0;
+    while (t <= ntiles) own_first[t++] = nunits;
+    own_first[ntiles] = nunits;
 }
 
 // Computes the per-shape geometry; returns false if the shape cannot be handled by this handle's buffers.
@@ -133,10 +144,10 @@ static int setup_geometry(orbx_handle* h, int w, int ht, bool allocate_only)
         g.scale = h->scale[l];
         g.size = (float)(int)(31 * h->scale[l]);              // ORBextractor.cpp:847
         if (l + 1 < h->nlevels) {
-            g.xt_off = (int)tab; tab += lw[l + 1];
+            g.xt_off = (int)tab; tab += align_up((size_t)lw[l + 1], 4);
             g.yt_off = (int)tab; tab += lh[l + 1];
-            g.dxs_off = (int)tile; tile += ceil_div(g.w, TW) + 1;
-            g.dys_off = (int)tile; tile += ceil_div(g.h, TH) + 1;
+            g.dxs_off = (int)tile; tile += ceil_div(g.w, L3_TWPX) + 1;
+            g.dys_off = (int)tile; tile += ceil_div(g.h, L3_RG) + 1;
         }
     }
     if (allocate_only) {
@@ -162,8 +173,10 @@ static int upload_geometry(orbx_handle* h)
     for (int l = 0; l + 1 < h->nlevels; l++) {
         const LevelGeom& g = h->geom[l];
         const LevelGeom& n = h->geom[l + 1];
-        build_axis_table(g.w, n.w, TW, tab.data() + g.xt_off, tiles.data() + g.dxs_off, ceil_div(g.w, TW));
-        build_axis_table(g.h, n.h, TH, tab.data() + g.yt_off, tiles.data() + g.dys_off, ceil_div(g.h, TH));
+        // x: a tile column owns the destination WORDS whose first source column is in [x0 - 2, x0 + 118)
+        build_axis_table(g.w, n.w, (int)align_up((size_t)n.w, 4), tab.data() + g.xt_off, L3_TWPX, 2, 4, tiles.data() + g.dxs_off, ceil_div(g.w, L3_TWPX));
+        // y: an 8-row group owns the destination rows whose (upper) source row lies in it
+        build_axis_table(g.h, n.h, n.h, tab.data() + g.yt_off, L3_RG, 0, 1, tiles.data() + g.dys_off, ceil_div(g.h, L3_RG));
     }
     // plain synchronous copies: shape changes are rare (once per camera), and the stream must not race them
     ORBB_CUDA(cudaStreamSynchronize(h->stream));
@@ -256,6 +269,7 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
         for (int i = 0; i < 7; i++) h->q[i] = cfg->blur_legacy ? QL[i] : Q[i];
     }
     h->factorPI = (float)(3.14159265358979323846 / 180.f);
+    { const char* e = getenv("ORBB_L3_WARPS"); if (e && atoi(e) == 8) h->l3_warps = 8; }
 
     int rc = setup_geometry(h, cfg->max_width, cfg->max_height, true);
     if (rc != ORBB_OK) { delete h; return rc; }
@@ -335,26 +349,44 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[0], st));
     for (int l = 0; l < nl; l++) {
         const LevelGeom& g = h->geom[l];
-        LevelArgs a;
+        Level3Args a;
         memset(&a, 0, sizeof a);
         if (l == 0) { a.src = imgs_dev; a.src_pitch = (long long)stride; a.src_fstride = (long long)fstride; }
         else { a.src = h->d_pyr + g.off; a.src_pitch = g.pitch; a.src_fstride = (long long)h->pyr_fstride; }
         a.w = g.w; a.h = g.h;
         a.blur = h->d_blur + g.off; a.blur_pitch = g.pitch; a.blur_fstride = (long long)h->pyr_fstride;
-        if (l + 1 < nl) {
+        const bool has_next = l + 1 < nl;
+        // the fused resize needs the 4 source columns of a destination word inside the 4-pixel halo: scale <= 1.25
+        const bool fused_resize = has_next && (double)g.w <= 1.25 * h->geom[l + 1].w && (double)g.h <= 1.25 * h->geom[l + 1].h;
+        if (has_next) {
+            a.xt = h->d_tab + g.xt_off; a.yt = h->d_tab + g.yt_off;
+            a.xws = h->d_tiles + g.dxs_off; a.yrs = h->d_tiles + g.dys_off;
+        }
+        if (fused_resize) {
             const LevelGeom& n = h->geom[l + 1];
             a.dst = h->d_pyr + n.off; a.dst_pitch = n.pitch; a.dst_fstride = (long long)h->pyr_fstride;
-            a.xt = h->d_tab + g.xt_off; a.yt = h->d_tab + g.yt_off;
-            a.dxs = h->d_tiles + g.dxs_off; a.dys = h->d_tiles + g.dys_off;
         }
         a.fast_on = g.nCols > 0; a.wCell = g.wCell; a.hCell = g.hCell; a.minTh = h->cfg.min_th_fast;
         a.magicW = (unsigned)((0x100000000ull + g.wCell - 1) / g.wCell); a.magicH = (unsigned)((0x100000000ull + g.hCell - 1) / g.hCell);
         a.rec = h->d_rec + g.rec_off; a.rec_cap = g.rec_cap; a.rec_fstride = (long long)h->rec_total;
         a.rec_count = h->d_rec_count + l; a.rec_count_stride = nl;
         for (int i = 0; i < 7; i++) a.q[i] = h->q[i];
-        dim3 grid(ceil_div(g.w, TW), ceil_div(g.h, TH), nframes);
-        level_kernel<<<grid, NT, 0, st>>>(a);
+        a.legacy = h->cfg.blur_legacy ? 1 : 0;
+        if (h->l3_warps == 8) {
+            dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, 8 * L3_RG), nframes);
+            level3_kernel<8><<<grid, 256, 0, st>>>(a);
+        } else {
+            dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, 4 * L3_RG), nframes);
+            level3_kernel<4><<<grid, 128, 0, st>>>(a);
+        }
         ORBB_LAUNCHED();
+        if (has_next && !fused_resize) {
+            const LevelGeom& n = h->geom[l + 1];
+            dim3 grid(ceil_div(n.w, 128), n.h, nframes);
+            resize_plain_kernel<<<grid, 128, 0, st>>>(a.src, a.src_pitch, a.src_fstride, g.w, g.h, h->d_pyr + n.off, n.pitch,
+                                                       (long long)h->pyr_fstride, n.w, n.h, a.xt, a.yt);
+            ORBB_LAUNCHED();
+        }
     }
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[1], st));
     {

@@ -13,7 +13,7 @@
 // m = max over 9-arcs, float ops with explicit _rn intrinsics (no FMA contraction), round-half-even conversions.
 #pragma once
 #include "common.cuh"
-#include "level_kernel.cuh"
+#include "level_kernel3.cuh"
 
 namespace orbb {
 

@@ -158,3 +158,48 @@ def test_4k_frame(gpu):
         assert np.array_equal(k[f], ok[f]), f
     assert np.max(np.abs(k["angle"] - ok["angle"])) <= 1e-3
     assert np.any(d != od, axis=1).sum() <= 0.001 * len(d)
+
+
+def test_legacy_blur_and_large_scale_factor(gpu):
+    """blur_legacy (OpenCV <= 3.3 kernel, needs the clamp path) and scaleFactor 1.5 (resize falls back to the plain kernel)."""
+    import orbb200, pyoracle
+    from synth import synth
+    img = synth(640, 480, 77)
+    ex = orbb200.ORBextractor(1000, max_size=(640, 480), blur_legacy=True)
+    k, d = ex(img)
+    orc = pyoracle.OracleExtractor(1000, legacy_blur=True)
+    ok, od = orc.extract(img)
+    for L in range(8):
+        assert np.array_equal(ex.blurred_level(L), orc.level_image(L, blurred=True)), f"legacy blur level {L}"
+    assert k.tobytes() == ok.tobytes() or (np.array_equal(k["x"], ok["x"]) and np.max(np.abs(k["angle"] - ok["angle"])) <= 1e-3)
+    assert np.any(d != od, axis=1).sum() <= 0.001 * len(d)
+    for sf, nl in ((1.5, 5), (1.1, 8), (1.25, 6)):
+        ex2 = orbb200.ORBextractor(800, scaleFactor=sf, nlevels=nl, max_size=(640, 480))
+        k2, d2 = ex2(img)
+        orc2 = pyoracle.OracleExtractor(800, sf, nl)
+        ok2, od2 = orc2.extract(img)
+        for L in range(nl):
+            assert np.array_equal(ex2.pyramid_level(L), orc2.level_image(L)), f"scale {sf} pyramid level {L}"
+        assert len(k2) == len(ok2)
+        for f in ("x", "y", "size", "response", "octave"):
+            assert np.array_equal(k2[f], ok2[f]), (sf, f)
+        assert np.any(d2 != od2, axis=1).sum() <= 0.001 * len(d2)
+
+
+@pytest.mark.parametrize("w,h", [(641, 481), (123, 97), (1000, 37), (36, 300), (119, 64), (121, 65), (240, 33)])
+def test_odd_shapes(gpu, w, h):
+    """Widths that are not multiples of 4, tiles cut at every offset, images smaller than one FAST cell row."""
+    import orbb200, pyoracle
+    from synth import synth
+    img = synth(w, h, w * 7 + h)
+    ex = orbb200.ORBextractor(500, max_size=(w, h))
+    k, d = ex(img)
+    orc = pyoracle.OracleExtractor(500)
+    ok, od = orc.extract(img)
+    for L in range(8):
+        assert np.array_equal(ex.pyramid_level(L), orc.level_image(L)), f"pyramid level {L}"
+        assert np.array_equal(ex.blurred_level(L), orc.level_image(L, blurred=True)), f"blur level {L}"
+    assert len(k) == len(ok)
+    for f in ("x", "y", "size", "response", "octave"):
+        assert np.array_equal(k[f], ok[f]), f
+    assert np.any(d != od, axis=1).sum() <= max(1, 0.001 * len(d))
