@@ -145,7 +145,7 @@ static int setup_geometry(orbx_handle* h, int w, int ht, bool allocate_only)
         g.size = (float)(int)(31 * h->scale[l]);              // ORBextractor.cpp:847
         if (l + 1 < h->nlevels) {
             g.xt_off = (int)tab; tab += align_up((size_t)lw[l + 1], 4);
-            g.yt_off = (int)tab; tab += lh[l + 1];
+            g.yt_off = (int)tab; tab += align_up((size_t)lh[l + 1], 4);      // keeps every xt 16-byte aligned (int4 loads)
             g.dxs_off = (int)tile; tile += ceil_div(g.w, L3_TWPX) + 1;
             g.dys_off = (int)tile; tile += ceil_div(g.h, L3_RG) + 1;
         }
@@ -372,6 +372,11 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         a.rec_count = h->d_rec_count + l; a.rec_count_stride = nl;
         for (int i = 0; i < 7; i++) a.q[i] = h->q[i];
         a.legacy = h->cfg.blur_legacy ? 1 : 0;
+        {   // quick-reject threshold t' = 2^k - 1 <= minTh (k >= 1); minTh == 0 disables the reject
+            int k = 0;
+            while ((2 << k) - 1 <= h->cfg.min_th_fast && k < 7) k++;
+            if (k >= 1) { a.qmask = ((0xffu << k) & 0xffu) * 0x01010101u; a.qadd = (0x80u - (1u << (k - 1))) * 0x01010101u; }
+        }
         if (h->l3_warps == 8) {
             dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, 8 * L3_RG), nframes);
             level3_kernel<8><<<grid, 256, 0, st>>>(a);

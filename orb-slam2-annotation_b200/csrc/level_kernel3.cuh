@@ -37,6 +37,7 @@ struct Level3Args {
     const int* xws;          // [tiles_x + 1] first destination WORD owned by each tile column
     const int* yrs;          // [ceil(h / 8) + 1] first destination row whose source row lies in each 8-row group
     int fast_on, wCell, hCell, minTh;
+    unsigned qmask, qadd;                                   // quick-reject constants: ~t' and 0x80 - 2^(k-1) per byte, t' = 2^k - 1 <= minTh
     unsigned magicW, magicH;                                // ceil(2^32 / wCell), ceil(2^32 / hCell)
     uint32_t* rec; int rec_cap; long long rec_fstride;      // raw FAST records  y<<20 | x<<8 | m
     int* rec_count; int rec_count_stride;
@@ -91,7 +92,7 @@ __device__ __forceinline__ unsigned l3_pack4(int b0, int b1, int b2, int b3)
 }
 
 template <int NW>
-__global__ void __launch_bounds__(32 * NW) level3_kernel(const __grid_constant__ Level3Args a)
+__global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const __grid_constant__ Level3Args a)
 {
     constexpr int TH = L3_RG * NW, SMH = TH + 8, SCH = TH + 2, NT = 32 * NW;
     constexpr int QCAP = SCH * 122;                      // every scored pixel a candidate (uniform-noise images)
@@ -110,22 +111,45 @@ __global__ void __launch_bounds__(32 * NW) level3_kernel(const __grid_constant__
     const uint8_t* tb = reinterpret_cast<const uint8_t*>(tw);
     if (tid == 0) { s_qn = 0; s_en = 0; }
 
-    // ---- 1. stage tile + halo: lane = word column; REFLECT_101 at the image border (what the blur of a cloned level sees) ----
+    // ---- 1. stage tile + halo: lane = word column; REFLECT_101 at the image border (what the blur of a cloned level sees).
+    //         All loads of a warp are issued before the first store (no per-row control flow): one memory latency per warp. ----
     {
+        constexpr int RPW = SMH / NW;                             // staged rows per warp (SMH is a multiple of NW)
         const bool word_ok = ((a.src_pitch & 3) == 0) && ((reinterpret_cast<unsigned long long>(src) & 3) == 0);
         const int gx = x0 - 4 + 4 * lane;
         const bool inside = word_ok && gx >= 0 && gx + 3 < a.w;
+        const bool bytes = !inside && gx < a.w + 4;               // edge lanes: 4 reflected byte loads per row
+        const bool yin = y0 >= 4 && y0 + TH + 4 <= a.h;           // no vertical reflection needed (block-uniform)
+        const unsigned pitch = (unsigned)a.src_pitch;             // one frame is < 4 GB: 32-bit offsets
+        unsigned v[RPW];
+        if (__all_sync(FULL, inside)) {
 #pragma unroll
-        for (int r = warp; r < SMH; r += NW) {
-            const int gy = l3_reflect101(y0 - 4 + r, a.h);
-            const uint8_t* row = src + (long long)gy * a.src_pitch;
-            unsigned v = 0;
-            if (inside) v = *reinterpret_cast<const uint32_t*>(row + gx);
-            else if (gx < a.w + 4) {
-#pragma unroll
-                for (int b = 0; b < 4; b++) v |= (unsigned)row[l3_reflect101(gx + b, a.w)] << (8 * b);
+            for (int i = 0; i < RPW; i++) {
+                const int r = warp + NW * i;
+                const int gy = yin ? y0 - 4 + r : l3_reflect101(y0 - 4 + r, a.h);
+                v[i] = *reinterpret_cast<const uint32_t*>(src + ((unsigned)gy * pitch + (unsigned)gx));
             }
-            tw[r * L3_SP + 1 + lane] = v;
+        } else {
+            // mixed warp (tile on the left / right image border or unaligned source): every lane issues the same loads from a
+            // safe address and selects afterwards, so the loads still go out back to back
+            const unsigned xw = inside ? (unsigned)gx : 0u;
+            const unsigned xb0 = bytes ? l3_reflect101(gx, a.w) : 0, xb1 = bytes ? l3_reflect101(gx + 1, a.w) : 0;
+            const unsigned xb2 = bytes ? l3_reflect101(gx + 2, a.w) : 0, xb3 = bytes ? l3_reflect101(gx + 3, a.w) : 0;
+#pragma unroll
+            for (int i = 0; i < RPW; i++) {
+                const int r = warp + NW * i;
+                const int gy = yin ? y0 - 4 + r : l3_reflect101(y0 - 4 + r, a.h);
+                const uint8_t* row = src + (unsigned)gy * pitch;
+                unsigned vw = 0;
+                if (word_ok) vw = *reinterpret_cast<const uint32_t*>(row + xw);
+                const unsigned vb = (unsigned)row[xb0] | ((unsigned)row[xb1] << 8) | ((unsigned)row[xb2] << 16) | ((unsigned)row[xb3] << 24);
+                v[i] = inside ? vw : (bytes ? vb : 0u);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < RPW; i++) {
+            const int r = warp + NW * i;
+            tw[r * L3_SP + 1 + lane] = v[i];
             if (lane < 2) tw[r * L3_SP + lane * (L3_SP - 1)] = 0;       // pad words: read (and masked out) by the edge lanes
         }
     }
@@ -148,9 +172,10 @@ __global__ void __launch_bounds__(32 * NW) level3_kernel(const __grid_constant__
         const unsigned KA = l3_pack4(q0, q2, 0, q1), KB = l3_pack4(q3, q1, q2, q0), KC = l3_pack4(0, q0, 0, q1);
         const unsigned KD = l3_pack4(q2, q2, q3, q1), KE = l3_pack4(q0, 0, q1, 0), KF = l3_pack4(q1, q3, q2, q2);
         const unsigned KG = l3_pack4(q0, q2, q1, q3), KH = l3_pack4(q2, q0, q1, 0);
-        uint8_t* __restrict__ bl = a.blur + (long long)f * a.blur_fstride;
         const int gx = x0 - 4 + 4 * lane;
         const bool store_lane = lane >= 1 && lane <= L3_OWNW && gx < a.w;
+        uint8_t* __restrict__ bp = a.blur + (long long)f * a.blur_fstride + (long long)(y0 + ry0) * a.blur_pitch + gx;
+        const int nrows = store_lane ? min(L3_RG, a.h - (y0 + ry0)) : 0;
 #pragma unroll
         for (int j = 0; j < L3_RG; j++) {
             const unsigned VE = q3 * E[j + 3] + q2 * (E[j + 2] + E[j + 4]) + q1 * (E[j + 1] + E[j + 5]) + q0 * (E[j] + E[j + 6]);
@@ -170,46 +195,52 @@ __global__ void __launch_bounds__(32 * NW) level3_kernel(const __grid_constant__
             } else {
                 o = min(r0 >> 16, 255u) | (min(r1 >> 16, 255u) << 8) | (min(r2 >> 16, 255u) << 16) | (min(r3 >> 16, 255u) << 24);
             }
-            const int gy = y0 + ry0 + j;
-            if (store_lane && gy < a.h) *reinterpret_cast<uint32_t*>(bl + (long long)gy * a.blur_pitch + gx) = o;
+            if (j < nrows) *reinterpret_cast<uint32_t*>(bp) = o;
+            bp += a.blur_pitch;
         }
     }
 
-    // ---- 3. bilinear resize: lane = one destination word whose first source column lies in this tile, rows of this warp ----
+    // ---- 3. bilinear resize: lane = one destination word whose first source column lies in this tile; the warp walks the 9
+    //         staged source rows of its group once (horizontal pass per source row, unrolled), emitting a destination row
+    //         whenever its two source rows are at hand ----
     if (a.dst && rows_live) {
         uint8_t* __restrict__ dst = a.dst + (long long)f * a.dst_fstride;
-        const int k1 = a.xws[blockIdx.x + 1];
+        const int k0 = a.xws[blockIdx.x], k1 = a.xws[blockIdx.x + 1];
         const int g8 = (y0 + ry0) >> 3;
         const int dy0 = a.yrs[g8], dy1 = a.yrs[g8 + 1];
-        for (int k = a.xws[blockIdx.x] + lane; k < k1; k += 32) {
-            int off[4]; unsigned ca[4], cb[4];
+        int2 eyl = make_int2(0x7fffffff, 0);                     // this group's yt entries, one per lane (at most 8 rows)
+        if (dy0 + lane < dy1) eyl = a.yt[dy0 + lane];
+        for (int kb = k0; kb < k1; kb += 32) {
+            const bool active = kb + lane < k1;
+            const int k = active ? kb + lane : k1 - 1;
+            // the 4 pixels of a destination word read source bytes s0 .. s0+5 (scale <= 1.25): an 8-byte window of the staged row
+            const int4 e01 = *reinterpret_cast<const int4*>(a.xt + 4 * k), e23 = *reinterpret_cast<const int4*>(a.xt + 4 * k + 2);
+            const int off0 = e01.x - (x0 - 4) + 4;               // byte offset of the first source pixel inside a staged row
+            const unsigned sh = 8u * (unsigned)(off0 & 3);
+            const unsigned r1 = (unsigned)(e01.z - e01.x), r2 = (unsigned)(e23.x - e01.x), r3 = (unsigned)(e23.z - e01.x);
+            const unsigned sel0 = 0x10u, sel1 = ((r1 + 1) << 4) | r1, sel2 = ((r2 + 1) << 4) | r2, sel3 = ((r3 + 1) << 4) | r3;
+            const unsigned c0 = (unsigned)e01.y, c1 = (unsigned)e01.w, c2 = (unsigned)e23.y, c3 = (unsigned)e23.w;   // a0 | a1 << 16
+            const uint32_t* p0 = tw + (ry0 + 4) * L3_SP + (off0 >> 2);
+            uint8_t* dp = dst + (long long)dy0 * a.dst_pitch + 4 * k;
+            int dy = dy0;
+            int sy = __shfl_sync(FULL, eyl.x, 0); unsigned cy = (unsigned)__shfl_sync(FULL, eyl.y, 0);
+            unsigned Hp0 = 0, Hp1 = 0, Hp2 = 0, Hp3 = 0;
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const int2 e = a.xt[4 * k + j];
-                off[j] = e.x - (x0 - 4) + 4;                    // byte offset of the left source pixel inside a staged row
-                ca[j] = (unsigned)e.y & 0xffffu; cb[j] = (unsigned)e.y >> 16;
-            }
-            int have = -100000;                                  // staged row whose interpolation sits in H1
-            unsigned H0[4], H1[4] = {0, 0, 0, 0};
-            for (int dy = dy0; dy < dy1; dy++) {
-                const int2 ey = a.yt[dy];
-                const int rr = ey.x - (y0 - 4);
-                const unsigned b0 = ((unsigned)ey.y & 0xffffu) << 16, b1 = ((unsigned)ey.y >> 16) << 16;
-                const uint8_t* p0 = tb + rr * L3_SPB;
-                if (rr == have) {
-#pragma unroll
-                    for (int j = 0; j < 4; j++) H0[j] = H1[j];
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; j++) H0[j] = (p0[off[j]] * ca[j] + p0[off[j] + 1] * cb[j]) >> 4;
+            for (int r = 0; r <= L3_RG; r++) {
+                const unsigned X = __funnelshift_r(p0[r * L3_SP], p0[r * L3_SP + 1], sh), Y = __funnelshift_r(p0[r * L3_SP + 1], p0[r * L3_SP + 2], sh);
+                const unsigned Hc0 = __dp2a_lo(c0, __byte_perm(X, Y, sel0), 0u) >> 4, Hc1 = __dp2a_lo(c1, __byte_perm(X, Y, sel1), 0u) >> 4;
+                const unsigned Hc2 = __dp2a_lo(c2, __byte_perm(X, Y, sel2), 0u) >> 4, Hc3 = __dp2a_lo(c3, __byte_perm(X, Y, sel3), 0u) >> 4;
+                if (r > 0 && sy == 8 * g8 + r - 1) {             // warp-uniform: destination row dy interpolates rows r-1 and r
+                    const unsigned b0 = (cy & 0xffffu) << 16, b1 = (cy >> 16) << 16;
+                    const unsigned o = ((__umulhi(b0, Hp0) + __umulhi(b1, Hc0) + 2u) >> 2) + (((__umulhi(b0, Hp1) + __umulhi(b1, Hc1) + 2u) >> 2) << 8) +
+                                       (((__umulhi(b0, Hp2) + __umulhi(b1, Hc2) + 2u) >> 2) << 16) + (((__umulhi(b0, Hp3) + __umulhi(b1, Hc3) + 2u) >> 2) << 24);
+                    if (active) *reinterpret_cast<uint32_t*>(dp) = o;
+                    dp += a.dst_pitch;
+                    dy++;
+                    sy = __shfl_sync(FULL, eyl.x, (dy - dy0) & 31); cy = (unsigned)__shfl_sync(FULL, eyl.y, (dy - dy0) & 31);
+                    if (dy >= dy1) sy = 0x7fffffff;
                 }
-#pragma unroll
-                for (int j = 0; j < 4; j++) H1[j] = (p0[L3_SPB + off[j]] * ca[j] + p0[L3_SPB + off[j] + 1] * cb[j]) >> 4;
-                have = rr + 1;
-                unsigned o = 0;
-#pragma unroll
-                for (int j = 0; j < 4; j++) o |= ((__umulhi(b0, H0[j]) + __umulhi(b1, H1[j]) + 2u) >> 2) << (8 * j);
-                *reinterpret_cast<uint32_t*>(dst + (long long)dy * a.dst_pitch + 4 * k) = o;
+                Hp0 = Hc0; Hp1 = Hc1; Hp2 = Hc2; Hp3 = Hc3;
             }
         }
     }
@@ -217,7 +248,9 @@ __global__ void __launch_bounds__(32 * NW) level3_kernel(const __grid_constant__
     // ---- 4. FAST quick reject on words -> warp-compacted candidate queue; score rows -1 .. TH of the tile ----
     const bool fast_tile = a.fast_on && (x0 + L3_TWPX >= 19) && (x0 - 1 <= a.w - 20) && (y0 + TH >= 19) && (y0 - 1 <= a.h - 20);
     if (fast_tile) {
-        const unsigned t1 = (unsigned)(min(a.minTh, 126) + 1) * 0x01010101u;
+        // Conservative threshold t' = 2^k - 1 <= minTh (exact for the usual minTh = 7): |d| > t'  <=>  (|d| & ~t') != 0, so the
+        // OR of two ring differences is tested with one mask; nz(x) = bit 7 of (x >> 1) + (0x80 - 2^(k-1)) for x with k low zero bits.
+        const unsigned M = a.qmask, C = a.qadd;
         // valid bytes of this lane's word: pixels max(19, x0-1) .. min(w-20, x0+120)
         const int lo = max(19, x0 - 1) - (x0 - 4) - 4 * lane, hi = min(a.w - 20, x0 + L3_TWPX) - (x0 - 4) - 4 * lane;
         unsigned valid = 0x80808080u;
@@ -226,63 +259,83 @@ __global__ void __launch_bounds__(32 * NW) level3_kernel(const __grid_constant__
             if (lo > 0) valid &= 0xffffffffu << (8 * lo);
             if (hi < 3) valid &= 0xffffffffu >> (8 * (3 - hi));
         }
-        for (int s = warp - 1; s <= TH; s += NW) {
+        unsigned m0 = 0, m1 = 0;                                  // private candidate flags: 4 bits per row, rows it = 0..7 | 8
+        constexpr int NIT = (TH + 2 + NW - 1) / NW;
+        static_assert(NIT <= 9, "candidate masks hold 9 rows per warp");
+#pragma unroll
+        for (int it = 0; it < NIT; it++) {
+            const int s = warp - 1 + NW * it;
             const int gy = y0 + s;
-            if (gy < 19 || gy > a.h - 20) continue;                                  // warp-uniform
+            if (s > TH || gy < 19 || gy > a.h - 20) continue;                        // warp-uniform
             const uint32_t* rowp = tw + (s + 4) * L3_SP + 1 + lane;
             const unsigned V = rowp[0], Lw = rowp[-1], Rw = rowp[1];
-            // ring pixels 0 (0,+3), 8 (0,-3), 4 (+3,0), 12 (-3,0): any 9-arc contains two ADJACENT ones of these four
-            const unsigned g0 = l3_gt_raw(__vabsdiffu4(V, rowp[3 * L3_SP]), t1), g8 = l3_gt_raw(__vabsdiffu4(V, rowp[-3 * L3_SP]), t1);
-            const unsigned g4 = l3_gt_raw(__vabsdiffu4(V, __funnelshift_r(V, Rw, 24)), t1);
-            const unsigned g12 = l3_gt_raw(__vabsdiffu4(V, __funnelshift_r(Lw, V, 8)), t1);
-            unsigned cand = (g0 | g8) & (g4 | g12) & valid;
-            if (cand) {
-                // ... and two adjacent ones of the diagonal four: 2 (+2,+2), 6 (+2,-2), 10 (-2,-2), 14 (-2,+2)
-                const unsigned Vd = rowp[2 * L3_SP], Ld = rowp[2 * L3_SP - 1], Rd = rowp[2 * L3_SP + 1];
-                const unsigned Vu = rowp[-2 * L3_SP], Lu = rowp[-2 * L3_SP - 1], Ru = rowp[-2 * L3_SP + 1];
-                const unsigned g2 = l3_gt_raw(__vabsdiffu4(V, __funnelshift_r(Vd, Rd, 16)), t1);
-                const unsigned g14 = l3_gt_raw(__vabsdiffu4(V, __funnelshift_r(Ld, Vd, 16)), t1);
-                const unsigned g6 = l3_gt_raw(__vabsdiffu4(V, __funnelshift_r(Vu, Ru, 16)), t1);
-                const unsigned g10 = l3_gt_raw(__vabsdiffu4(V, __funnelshift_r(Lu, Vu, 16)), t1);
-                cand &= (g2 | g10) & (g6 | g14);
+            const unsigned Vd = rowp[2 * L3_SP], Ld = rowp[2 * L3_SP - 1], Rd = rowp[2 * L3_SP + 1];
+            const unsigned Vu = rowp[-2 * L3_SP], Lu = rowp[-2 * L3_SP - 1], Ru = rowp[-2 * L3_SP + 1];
+            // any 9-arc contains two ADJACENT ones of the axis four  0 (0,+3), 4 (+3,0), 8 (0,-3), 12 (-3,0)
+            // and two adjacent ones of the diagonal four             2 (+2,+2), 6 (+2,-2), 10 (-2,-2), 14 (-2,+2)
+            const unsigned p08 = (__vabsdiffu4(V, rowp[3 * L3_SP]) | __vabsdiffu4(V, rowp[-3 * L3_SP])) & M;
+            const unsigned p4c = (__vabsdiffu4(V, __funnelshift_r(V, Rw, 24)) | __vabsdiffu4(V, __funnelshift_r(Lw, V, 8))) & M;
+            const unsigned p2a = (__vabsdiffu4(V, __funnelshift_r(Vd, Rd, 16)) | __vabsdiffu4(V, __funnelshift_r(Lu, Vu, 16))) & M;
+            const unsigned p6e = (__vabsdiffu4(V, __funnelshift_r(Vu, Ru, 16)) | __vabsdiffu4(V, __funnelshift_r(Ld, Vd, 16))) & M;
+            unsigned cand = ((p08 >> 1) + C) & ((p4c >> 1) + C) & ((p2a >> 1) + C) & ((p6e >> 1) + C) & valid;
+            if (a.qmask == 0) cand = valid;                                          // minTh == 0: no quick reject possible
+            const unsigned nib = (((cand >> 7) * 0x00204081u) >> 21) & 15u;
+            if (it < 8) m0 |= nib << (4 * (it & 7)); else m1 = nib;
+        }
+        // each lane appends its own candidates: one shared atomic per lane, no warp scan (queue order is irrelevant)
+        const int n = __popc(m0) + __popc(m1);
+        if (n) {
+            int slot = atomicAdd(&s_qn, n);
+            const int pbase = warp * L3_SCP + 4 * lane;          // position of (row s = warp - 1, byte 0): (s + 1) * SCP + 4 * lane
+            while (m0) {
+                const int t = __ffs((int)m0) - 1;
+                m0 &= m0 - 1;
+                queue[slot++] = (uint16_t)(pbase + (t >> 2) * (NW * L3_SCP) + (t & 3));
             }
-            if (__any_sync(FULL, cand != 0)) {
-                const int n = (int)(((cand >> 7) * 0x01010101u) >> 24);
-                int incl = n;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += t; }
-                int base = 0;
-                if (lane == 31) base = atomicAdd(&s_qn, incl);
-                base = __shfl_sync(FULL, base, 31);
-                int slot = base + incl - n;
-                const int pos = (s + 1) * L3_SCP + 4 * lane;
-#pragma unroll
-                for (int b = 0; b < 4; b++)
-                    if (cand & (0x80u << (8 * b))) queue[slot++] = (uint16_t)(pos + b);
+            while (m1) {
+                const int t = __ffs((int)m1) - 1;
+                m1 &= m1 - 1;
+                queue[slot++] = (uint16_t)(pbase + 8 * (NW * L3_SCP) + t);
             }
         }
     }
     __syncthreads();
     if (!fast_tile) return;
 
-    // ---- 5. exact arc score of the queued pixels ----
+    // ---- 5. exact arc score of the queued pixels; owned pixels above minTh are re-queued (in place) for the NMS ----
     const int qn = s_qn;
-    for (int j = tid; j < qn; j += NT) {
-        const int pos = queue[j];
-        const int r = pos >> 7, c = pos & 127;                    // score-map row (tile row + 1), staged byte column
-        const int m = l3_arc_score(tb + (r + 3) * L3_SPB + 4 + c);
-        sc[pos] = (uint8_t)(m > a.minTh ? m : 0);
+    __syncthreads();                                             // everyone has read s_qn: it becomes the survivor counter
+    if (tid == 0) s_qn = 0;
+    __syncthreads();
+    for (int j0 = 0; j0 < qn; j0 += NT) {
+        const int j = j0 + tid;
+        bool surv = false; int pos = 0;
+        if (j < qn) {
+            pos = queue[j];
+            const int r = pos >> 7, c = pos & 127;                // score-map row (tile row + 1), staged byte column
+            const int m = l3_arc_score(tb + (r + 3) * L3_SPB + 4 + c);
+            if (m > a.minTh) {
+                sc[pos] = (uint8_t)m;
+                surv = r >= 1 && r <= TH && c >= 4 && c < 4 + L3_TWPX;     // the ring around the tile is scored for its neighbours only
+            }
+        }
+        // survivors overwrite the front of the queue: slot index < j0 + NT of an entry already consumed by this pass
+        const unsigned bal = __ballot_sync(FULL, surv);
+        int base = 0;
+        if (lane == 0 && bal) base = atomicAdd(&s_qn, __popc(bal));
+        base = __shfl_sync(FULL, base, 0);
+        __syncthreads();                                         // all entries of this pass are consumed before any is overwritten
+        if (surv) queue[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)pos;
     }
     __syncthreads();
 
     // ---- 6. cell-local 3x3 non-max suppression (strict '>') and emission ----
-    for (int j = tid; j < qn; j += NT) {
+    const int sn = s_qn;
+    for (int j = tid; j < sn; j += NT) {
         const int pos = queue[j];
         const int r = pos >> 7, c = pos & 127;
-        if (r < 1 || r > TH || c < 4 || c >= 4 + L3_TWPX) continue;     // the ring around the tile is scored for its neighbours only
         const uint8_t* sp = sc + pos;
         const int m = sp[0];
-        if (!m) continue;
         const int gx = x0 - 4 + c, gy = y0 - 1 + r;
         // position inside the 30-px FAST cell: a neighbour in ANOTHER cell never suppresses (cv::FAST ran per cell)
         const int cellx = __umulhi((unsigned)(gx - 19), a.magicW), celly = __umulhi((unsigned)(gy - 19), a.magicH);
