@@ -30,6 +30,8 @@ struct orbx_handle {
     orbx_config cfg;
     int nlevels;
     cudaStream_t stream = nullptr;
+    cudaStream_t s_in = nullptr, s_out = nullptr;      // copy streams of the host-buffer batch pipeline
+    std::vector<cudaEvent_t> ev_in, ev_done;          // per chunk: frames landed in HBM / results ready
     // ORBextractor tables (ORBextractor.cpp:417-448, :456-471)
     float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS], sigma2[ORBB_MAX_LEVELS], inv_sigma2[ORBB_MAX_LEVELS];
     int per_level[ORBB_MAX_LEVELS], umax[16];
@@ -280,6 +282,8 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
     rc = ORBB_OK;
     auto ok = [&](int r) { if (rc == ORBB_OK) rc = r; };
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+    ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
     ok(dev_alloc(&h->d_pyr, B * h->cap_pyr)); ok(dev_alloc(&h->d_blur, B * h->cap_pyr));
     ok(dev_alloc(&h->d_rec, B * h->cap_rec)); ok(dev_alloc(&h->d_pts, 2 * B * h->cap_rec));
     ok(dev_alloc(&h->d_nodes, B * h->cap_node)); ok(dev_alloc(&h->d_iscr, B * h->cap_node * ISCR_PER_NODE));
@@ -311,6 +315,10 @@ extern "C" int orbx_destroy(orbx_handle* h)
     cudaFree(h->d_node_off); cudaFree(h->d_cell_off); cudaFree(h->d_kps); cudaFree(h->d_desc);
     cudaFreeHost(h->h_img); cudaFreeHost(h->h_kps); cudaFreeHost(h->h_desc); cudaFreeHost(h->h_counts); cudaFreeHost(h->h_status);
     for (int i = 0; i < 4; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    for (cudaEvent_t e : h->ev_in) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
+    if (h->s_in) cudaStreamDestroy(h->s_in);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBB_OK;
@@ -331,9 +339,11 @@ extern "C" int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_sc
     return ORBB_OK;
 }
 
-// Enqueue the whole extraction of `nframes` device-resident frames on the handle's stream.
-static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes, int w, int ht, size_t stride, size_t fstride,
-                           orbx_keypoint* kps_dev, uint8_t* desc_dev, int32_t* counts_dev, int capacity)
+// Enqueue the extraction of frames [f0, f0 + nframes) of a device-resident batch on the handle's stream.  imgs_dev / kps_dev /
+// desc_dev / counts_dev address frame 0 of the batch; every per-frame scratch buffer of the handle is indexed the same way, so
+// chunks of one batch can be enqueued independently (orbx_extract_batch pipelines them against the host copies).
+static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int nframes, int w, int ht, size_t stride, size_t fstride,
+                           orbx_keypoint* kps_dev0, uint8_t* desc_dev0, int32_t* counts_dev0, int capacity)
 {
     if (w != h->cur_w || ht != h->cur_h) {
         int rc = setup_geometry(h, w, ht, false);
@@ -344,17 +354,25 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
     }
     const int nl = h->nlevels;
     cudaStream_t st = h->stream;
-    ORBB_CUDA(cudaMemsetAsync(h->d_rec_count, 0, sizeof(int) * (size_t)nframes * nl, st));
-    ORBB_CUDA(cudaMemsetAsync(h->d_status, 0, sizeof(int) * (size_t)nframes, st));
+    const size_t F0 = (size_t)f0;
+    const uint8_t* imgs_dev = imgs_dev0 + F0 * fstride;
+    orbx_keypoint* kps_dev = kps_dev0 + F0 * capacity; uint8_t* desc_dev = desc_dev0 + F0 * capacity * 32; int32_t* counts_dev = counts_dev0 + F0;
+    uint8_t* const d_pyr = h->d_pyr + F0 * h->pyr_fstride; uint8_t* const d_blur = h->d_blur + F0 * h->pyr_fstride;
+    uint32_t* const d_rec = h->d_rec + F0 * h->rec_total; uint32_t* const d_pts = h->d_pts + F0 * 2 * h->rec_total;
+    uint4* const d_nodes = h->d_nodes + F0 * h->node_total; int* const d_iscr = h->d_iscr + F0 * h->node_total * ISCR_PER_NODE;
+    uint8_t* const d_cellflag = h->d_cellflag + F0 * h->cell_total; int4* const d_out = h->d_out + F0 * h->out_total;
+    int* const d_rec_count = h->d_rec_count + F0 * nl; int* const d_out_count = h->d_out_count + F0 * nl; int* const d_status = h->d_status + F0;
+    ORBB_CUDA(cudaMemsetAsync(d_rec_count, 0, sizeof(int) * (size_t)nframes * nl, st));
+    ORBB_CUDA(cudaMemsetAsync(d_status, 0, sizeof(int) * (size_t)nframes, st));
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[0], st));
     for (int l = 0; l < nl; l++) {
         const LevelGeom& g = h->geom[l];
         Level3Args a;
         memset(&a, 0, sizeof a);
         if (l == 0) { a.src = imgs_dev; a.src_pitch = (long long)stride; a.src_fstride = (long long)fstride; }
-        else { a.src = h->d_pyr + g.off; a.src_pitch = g.pitch; a.src_fstride = (long long)h->pyr_fstride; }
+        else { a.src = d_pyr + g.off; a.src_pitch = g.pitch; a.src_fstride = (long long)h->pyr_fstride; }
         a.w = g.w; a.h = g.h;
-        a.blur = h->d_blur + g.off; a.blur_pitch = g.pitch; a.blur_fstride = (long long)h->pyr_fstride;
+        a.blur = d_blur + g.off; a.blur_pitch = g.pitch; a.blur_fstride = (long long)h->pyr_fstride;
         const bool has_next = l + 1 < nl;
         // the fused resize needs the 4 source columns of a destination word inside the 4-pixel halo: scale <= 1.25
         const bool fused_resize = has_next && (double)g.w <= 1.25 * h->geom[l + 1].w && (double)g.h <= 1.25 * h->geom[l + 1].h;
@@ -364,12 +382,12 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         }
         if (fused_resize) {
             const LevelGeom& n = h->geom[l + 1];
-            a.dst = h->d_pyr + n.off; a.dst_pitch = n.pitch; a.dst_fstride = (long long)h->pyr_fstride;
+            a.dst = d_pyr + n.off; a.dst_pitch = n.pitch; a.dst_fstride = (long long)h->pyr_fstride;
         }
         a.fast_on = g.nCols > 0; a.wCell = g.wCell; a.hCell = g.hCell; a.minTh = h->cfg.min_th_fast;
         a.magicW = (unsigned)((0x100000000ull + g.wCell - 1) / g.wCell); a.magicH = (unsigned)((0x100000000ull + g.hCell - 1) / g.hCell);
-        a.rec = h->d_rec + g.rec_off; a.rec_cap = g.rec_cap; a.rec_fstride = (long long)h->rec_total;
-        a.rec_count = h->d_rec_count + l; a.rec_count_stride = nl;
+        a.rec = d_rec + g.rec_off; a.rec_cap = g.rec_cap; a.rec_fstride = (long long)h->rec_total;
+        a.rec_count = d_rec_count + l; a.rec_count_stride = nl;
         for (int i = 0; i < 7; i++) a.q[i] = h->q[i];
         a.legacy = h->cfg.blur_legacy ? 1 : 0;
         {   // quick-reject threshold t' = 2^k - 1 <= minTh (k >= 1); minTh == 0 disables the reject
@@ -388,7 +406,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         if (has_next && !fused_resize) {
             const LevelGeom& n = h->geom[l + 1];
             dim3 grid(ceil_div(n.w, 128), n.h, nframes);
-            resize_plain_kernel<<<grid, 128, 0, st>>>(a.src, a.src_pitch, a.src_fstride, g.w, g.h, h->d_pyr + n.off, n.pitch,
+            resize_plain_kernel<<<grid, 128, 0, st>>>(a.src, a.src_pitch, a.src_fstride, g.w, g.h, d_pyr + n.off, n.pitch,
                                                        (long long)h->pyr_fstride, n.w, n.h, a.xt, a.yt);
             ORBB_LAUNCHED();
         }
@@ -398,14 +416,14 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         OctArgs a;
         memset(&a, 0, sizeof a);
         a.geom = h->d_geom; a.nlevels = nl; a.iniTh = h->cfg.ini_th_fast;
-        a.rec = h->d_rec; a.rec_fstride = (long long)h->rec_total; a.rec_count = h->d_rec_count;
-        a.pts = h->d_pts; a.pts_fstride = 2 * (long long)h->rec_total;
-        a.nodes = h->d_nodes; a.nodes_fstride = (long long)h->node_total;
-        a.iscr = h->d_iscr; a.iscr_fstride = (long long)h->node_total * ISCR_PER_NODE;
-        a.cellflag = h->d_cellflag; a.cellflag_fstride = (long long)h->cell_total;
+        a.rec = d_rec; a.rec_fstride = (long long)h->rec_total; a.rec_count = d_rec_count;
+        a.pts = d_pts; a.pts_fstride = 2 * (long long)h->rec_total;
+        a.nodes = d_nodes; a.nodes_fstride = (long long)h->node_total;
+        a.iscr = d_iscr; a.iscr_fstride = (long long)h->node_total * ISCR_PER_NODE;
+        a.cellflag = d_cellflag; a.cellflag_fstride = (long long)h->cell_total;
         a.node_off = h->d_node_off; a.cell_off = h->d_cell_off;
-        a.out = h->d_out; a.out_fstride = (long long)h->out_total;
-        a.out_count = h->d_out_count; a.status = h->d_status;
+        a.out = d_out; a.out_fstride = (long long)h->out_total;
+        a.out_count = d_out_count; a.status = d_status;
         octree_kernel<<<dim3(nl, nframes), NTO, 0, st>>>(a);
         ORBB_LAUNCHED();
     }
@@ -415,9 +433,9 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         memset(&a, 0, sizeof a);
         a.geom = h->d_geom; a.nlevels = nl;
         a.src0 = imgs_dev; a.src0_pitch = (long long)stride; a.src0_fstride = (long long)fstride;
-        a.pyr = h->d_pyr; a.pyr_fstride = (long long)h->pyr_fstride;
-        a.blur = h->d_blur; a.blur_fstride = (long long)h->pyr_fstride;
-        a.lvl = h->d_out; a.lvl_fstride = (long long)h->out_total; a.lvl_count = h->d_out_count;
+        a.pyr = d_pyr; a.pyr_fstride = (long long)h->pyr_fstride;
+        a.blur = d_blur; a.blur_fstride = (long long)h->pyr_fstride;
+        a.lvl = d_out; a.lvl_fstride = (long long)h->out_total; a.lvl_count = d_out_count;
         a.kps = kps_dev; a.desc = desc_dev; a.counts = counts_dev; a.capacity = capacity;
         a.factorPI = h->factorPI;
         const int maxk = capacity < (int)h->out_total ? capacity : (int)h->out_total;
@@ -431,9 +449,9 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev, int nframes,
         h->prof_calls++;
     }
     ORBB_CUDA(cudaGetLastError());
-    h->last_frames = nframes;
-    h->last_src = imgs_dev; h->last_src_pitch = (long long)stride; h->last_src_fstride = (long long)fstride;
-    h->last_kps_dev = kps_dev; h->last_capacity = capacity;
+    h->last_frames = f0 + nframes;
+    h->last_src = imgs_dev0; h->last_src_pitch = (long long)stride; h->last_src_fstride = (long long)fstride;
+    h->last_kps_dev = kps_dev0; h->last_capacity = capacity;
     return ORBB_OK;
 }
 
@@ -445,7 +463,7 @@ extern "C" int orbx_extract_batch_device(orbx_handle* h, const uint8_t* imgs_dev
     if (nframes < 1 || nframes > h->cfg.max_batch) return ORBB_E_INVALID;
     if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w) return ORBB_E_BAD_SHAPE;
     ORBB_CUDA(cudaSetDevice(h->cfg.device));
-    return enqueue_extract(h, imgs_dev, nframes, w, ht, stride, fstride, kps_dev, desc_dev, counts_dev, capacity);
+    return enqueue_extract(h, imgs_dev, 0, nframes, w, ht, stride, fstride, kps_dev, desc_dev, counts_dev, capacity);
 }
 
 extern "C" int orbx_sync(orbx_handle* h)
@@ -479,6 +497,17 @@ extern "C" int orbx_get_profile(orbx_handle* h, double* ms3, int* calls)
 
 extern "C" void* orbx_stream(orbx_handle* h) { return h ? (void*)h->stream : nullptr; }
 
+// Frames per pipeline chunk of orbx_extract_batch: large enough to fill the GPU (64 VGA frames = 46 k CTAs on level 0), small
+// enough that the H2D copy of chunk c+1 and the D2H copy of chunk c-1 overlap the kernels of chunk c.
+static int pipeline_chunk(int w, int ht)
+{
+    const long long px = (long long)w * ht;
+    int c = (int)((64ll * 640 * 480) / (px > 0 ? px : 1));
+    if (c < 1) c = 1;
+    if (c > 64) c = 64;
+    return c;
+}
+
 extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
                                   size_t fstride, orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity)
 {
@@ -501,24 +530,9 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     }
     const LevelGeom& g0 = h->geom[0];
     cudaPointerAttributes attr;
-    bool pinned = cudaPointerGetAttributes(&attr, imgs_host) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    const bool pinned = cudaPointerGetAttributes(&attr, imgs_host) == cudaSuccess && attr.type == cudaMemoryTypeHost;
     cudaGetLastError();
-    for (int f = 0; f < nframes; f++) {
-        const uint8_t* src = imgs_host + (size_t)f * fstride;
-        size_t spitch = stride;
-        if (!pinned) {     // stage through pinned memory so the copy is truly asynchronous
-            uint8_t* stg = h->h_img + (size_t)f * w * ht;
-            for (int y = 0; y < ht; y++) memcpy(stg + (size_t)y * w, src + (size_t)y * stride, w);
-            src = stg; spitch = w;
-        }
-        ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, g0.pitch, src, spitch, w, ht,
-                                    cudaMemcpyHostToDevice, st));
-    }
     const int devcap = capacity < h->dev_capacity ? (capacity > 0 ? capacity : 1) : h->dev_capacity;
-    int rc = enqueue_extract(h, h->d_pyr + g0.off, nframes, w, ht, g0.pitch, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
-    if (rc != ORBB_OK) return rc;
-    ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
-    ORBB_CUDA(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
     // results: straight into the caller's buffers when they are pinned and share the device layout, else via staging
     bool direct = capacity == devcap && capacity > 0;
     if (direct) {
@@ -529,8 +543,54 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     }
     orbx_keypoint* kdst = direct ? kps_host : h->h_kps;
     uint8_t* ddst = direct ? desc_host : h->h_desc;
-    ORBB_CUDA(cudaMemcpyAsync(kdst, h->d_kps, sizeof(orbx_keypoint) * (size_t)nframes * devcap, cudaMemcpyDeviceToHost, st));
-    ORBB_CUDA(cudaMemcpyAsync(ddst, h->d_desc, (size_t)32 * nframes * devcap, cudaMemcpyDeviceToHost, st));
+
+    // ---- three-stage pipeline over chunks of frames: H2D (s_in) -> kernels (stream) -> D2H (s_out) ----
+    ORBB_CUDA(cudaStreamSynchronize(st));       // an earlier asynchronous device-API call may still be reading the level-0 slots
+    const int CH = pipeline_chunk(w, ht);
+    const int nchunks = ceil_div(nframes, CH);
+    while ((int)h->ev_in.size() < nchunks) {
+        cudaEvent_t e1, e2;
+        ORBB_CUDA(cudaEventCreateWithFlags(&e1, cudaEventDisableTiming));
+        ORBB_CUDA(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+        h->ev_in.push_back(e1); h->ev_done.push_back(e2);
+    }
+    const bool prof = h->profiling;      // per-kernel-class event timing needs the whole batch in one enqueue
+    for (int c = 0; c < nchunks; c++) {
+        const int f0 = c * CH, nf = nframes - f0 < CH ? nframes - f0 : CH;
+        for (int f = f0; f < f0 + nf; f++) {
+            const uint8_t* src = imgs_host + (size_t)f * fstride;
+            size_t spitch = stride;
+            if (!pinned) {     // stage through pinned memory so the copy is truly asynchronous
+                uint8_t* stg = h->h_img + (size_t)f * w * ht;
+                for (int y = 0; y < ht; y++) memcpy(stg + (size_t)y * w, src + (size_t)y * stride, w);
+                src = stg; spitch = w;
+            }
+            ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, g0.pitch, src, spitch, w, ht,
+                                        cudaMemcpyHostToDevice, h->s_in));
+        }
+        ORBB_CUDA(cudaEventRecord(h->ev_in[c], h->s_in));
+        if (prof) continue;
+        ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_in[c], 0));
+        const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, g0.pitch, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
+        if (rc != ORBB_OK) return rc;
+        ORBB_CUDA(cudaEventRecord(h->ev_done[c], st));
+        ORBB_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));
+        ORBB_CUDA(cudaMemcpyAsync(h->h_counts + f0, h->d_counts + f0, sizeof(int) * nf, cudaMemcpyDeviceToHost, h->s_out));
+        ORBB_CUDA(cudaMemcpyAsync(h->h_status + f0, h->d_status + f0, sizeof(int) * nf, cudaMemcpyDeviceToHost, h->s_out));
+        ORBB_CUDA(cudaMemcpyAsync(kdst + (size_t)f0 * devcap, h->d_kps + (size_t)f0 * devcap, sizeof(orbx_keypoint) * (size_t)nf * devcap, cudaMemcpyDeviceToHost, h->s_out));
+        ORBB_CUDA(cudaMemcpyAsync(ddst + (size_t)f0 * devcap * 32, h->d_desc + (size_t)f0 * devcap * 32, (size_t)32 * nf * devcap, cudaMemcpyDeviceToHost, h->s_out));
+    }
+    if (prof) {
+        ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_in[nchunks - 1], 0));
+        const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, g0.pitch, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
+        if (rc != ORBB_OK) return rc;
+        ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
+        ORBB_CUDA(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
+        ORBB_CUDA(cudaMemcpyAsync(kdst, h->d_kps, sizeof(orbx_keypoint) * (size_t)nframes * devcap, cudaMemcpyDeviceToHost, st));
+        ORBB_CUDA(cudaMemcpyAsync(ddst, h->d_desc, (size_t)32 * nframes * devcap, cudaMemcpyDeviceToHost, st));
+        ORBB_CUDA(cudaStreamSynchronize(st));
+    }
+    ORBB_CUDA(cudaStreamSynchronize(h->s_out));
     ORBB_CUDA(cudaStreamSynchronize(st));
     int ret = ORBB_OK;
     for (int f = 0; f < nframes; f++) {

@@ -123,11 +123,16 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
         const unsigned pitch = (unsigned)a.src_pitch;             // one frame is < 4 GB: 32-bit offsets
         unsigned v[RPW];
         if (__all_sync(FULL, inside)) {
+            const uint8_t* p = src + gx;                          // one 64-bit pointer per lane, then 32-bit row offsets
+            if (yin) {
+                p += (unsigned)(y0 - 4 + warp) * pitch;
+                const unsigned step = NW * pitch;
 #pragma unroll
-            for (int i = 0; i < RPW; i++) {
-                const int r = warp + NW * i;
-                const int gy = yin ? y0 - 4 + r : l3_reflect101(y0 - 4 + r, a.h);
-                v[i] = *reinterpret_cast<const uint32_t*>(src + ((unsigned)gy * pitch + (unsigned)gx));
+                for (int i = 0; i < RPW; i++) v[i] = *reinterpret_cast<const uint32_t*>(p + i * step);
+            } else {
+#pragma unroll
+                for (int i = 0; i < RPW; i++)
+                    v[i] = *reinterpret_cast<const uint32_t*>(p + (unsigned)l3_reflect101(y0 - 4 + warp + NW * i, a.h) * pitch);
             }
         } else {
             // mixed warp (tile on the left / right image border or unaligned source): every lane issues the same loads from a
