@@ -208,6 +208,41 @@ static int init_constants(orbx_handle* h)
     return ORBB_OK;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda).
+typedef CUresult (*tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static tmap_encode_fn get_tmap_encode()
+{
+    static tmap_encode_fn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (tmap_encode_fn)p;
+        cudaGetLastError();
+    });
+    return fn;
+}
+
+// Level image as a 3-D u8 tensor (x, y, frame) with a 144 B x box_rows x 1 box.  Returns false when the layout cannot be
+// described (base or strides not 16-byte aligned): the kernel then stages its tile with ordinary loads.
+static bool encode_level_tmap(CUtensorMap* tm, const uint8_t* base, int w, int ht, int nframes, size_t pitch, size_t fstride, int box_rows)
+{
+    static const bool off = getenv("ORBB_NO_TMA") != nullptr;
+    tmap_encode_fn enc = get_tmap_encode();
+    if (off || !enc || ((uintptr_t)base & 15) || (pitch & 15) || (nframes > 1 && (fstride & 15)) || pitch == 0) return false;
+    if (fstride == 0 || (fstride & 15)) fstride = pitch * (size_t)ht;           // single frame: any valid stride
+    if (fstride & 15) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)ht, (cuuint64_t)(nframes > 0 ? nframes : 1)};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)fstride};
+    const cuuint32_t box[3] = {144u, (cuuint32_t)box_rows, 1u};             // 128 B tile + halo, start rounded down to 16 B
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <typename T> static int dev_alloc(T** p, size_t n)
 {
     ORBB_CUDA(cudaMalloc((void**)p, (n ? n : 1) * sizeof(T)));
@@ -372,6 +407,8 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         if (l == 0) { a.src = imgs_dev; a.src_pitch = (long long)stride; a.src_fstride = (long long)fstride; }
         else { a.src = d_pyr + g.off; a.src_pitch = g.pitch; a.src_fstride = (long long)h->pyr_fstride; }
         a.w = g.w; a.h = g.h;
+        a.status = d_status;
+        a.use_tma = encode_level_tmap(&a.tmap, a.src, g.w, g.h, nframes, (size_t)a.src_pitch, (size_t)a.src_fstride, 8 * h->l3_warps + 8) ? 1 : 0;
         a.blur = d_blur + g.off; a.blur_pitch = g.pitch; a.blur_fstride = (long long)h->pyr_fstride;
         const bool has_next = l + 1 < nl;
         // the fused resize needs the 4 source columns of a destination word inside the 4-pixel halo: scale <= 1.25

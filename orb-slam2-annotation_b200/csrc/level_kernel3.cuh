@@ -16,6 +16,7 @@
 // Level L is read from HBM once; every store is a coalesced 32-bit word.  Bit-exact with the oracle.
 #pragma once
 #include "common.cuh"
+#include <cuda.h>                             // CUtensorMap (the driver entry point is fetched at run time, no -lcuda)
 
 namespace orbb {
 
@@ -23,11 +24,15 @@ constexpr int L3_LANES = 32;                 // staged word columns: halo word |
 constexpr int L3_OWNW = 30;                  // owned words per tile row
 constexpr int L3_TWPX = 4 * L3_OWNW;         // 120 owned pixels per tile row
 constexpr int L3_RG = 8;                     // rows per warp
-constexpr int L3_SP = 34;                    // shared tile pitch in words (1 pad word on each side of the 32 staged)
+constexpr int L3_SP = 36;                    // shared tile pitch in words: the TMA box is 144 B wide because its first column must
+                                             // be 16-byte aligned in global memory; tile word (r, c) sits at r*36 + cb + c, cb = 1 or 3
 constexpr int L3_SPB = 4 * L3_SP;            // ... in bytes
 constexpr int L3_SCP = 128;                  // score map pitch (byte column = staged tile byte column)
 
 struct Level3Args {
+    CUtensorMap tmap;        // level L as a 3-D tensor (x, y, frame), box 144 B x (tile rows + 8) x 1; valid when use_tma
+    int use_tma;             // 0: source pitch / base not 16-byte aligned -> the tile is staged with ordinary loads
+    int* status;             // [frame] sticky error bits (8: TMA transaction never completed)
     const uint8_t* src; long long src_pitch, src_fstride;   // level L (external input image when L == 0)
     int w, h;
     uint8_t* blur; long long blur_pitch, blur_fstride;      // blurred level L out
@@ -98,7 +103,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
     constexpr int QCAP = SCH * 122;                      // every scored pixel a candidate (uniform-noise images)
     constexpr int EMIT_CAP = (TH / 2 + 3) * 65;          // NMS survivors are never 8-adjacent inside a cell
     constexpr unsigned FULL = 0xffffffffu;
-    __shared__ __align__(16) uint32_t tw[SMH * L3_SP];   // tile + halo, 4 pixels per word, word (r, c) at r*SP + 1 + c
+    __shared__ __align__(128) uint32_t tws[SMH * L3_SP]; // tile + halo, 4 pixels per word (TMA destination)
+    __shared__ __align__(8) unsigned long long mbar;      // completion barrier of the bulk tensor copy
     __shared__ __align__(4) uint8_t sc[SCH * L3_SCP];    // arc scores (> minTh) of the tile's pixels + 1-px ring
     __shared__ uint16_t queue[QCAP];
     __shared__ uint32_t emit[EMIT_CAP];
@@ -108,55 +114,79 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
     const int f = blockIdx.z;
     const int x0 = blockIdx.x * L3_TWPX, y0 = blockIdx.y * TH;
     const uint8_t* __restrict__ src = a.src + (long long)f * a.src_fstride;
+    // the box starts at the 16-byte boundary below x0 - 4: the tile's first word is word cb of each staged row
+    const int cb = ((x0 - 4) & 15) >> 2;
+    uint32_t* const tw = tws + cb;                          // tile word (r, c) = tw[r * L3_SP + c]
     const uint8_t* tb = reinterpret_cast<const uint8_t*>(tw);
     if (tid == 0) { s_qn = 0; s_en = 0; }
 
-    // ---- 1. stage tile + halo: lane = word column; REFLECT_101 at the image border (what the blur of a cloned level sees).
-    //         All loads of a warp are issued before the first store (no per-row control flow): one memory latency per warp. ----
-    {
+    // ---- 1. stage tile + halo (128 bytes x SMH rows, lane = word column).  Normal case: ONE bulk tensor copy (TMA) issued by
+    //         thread 0 lands the box [(x0-4) & ~15, +144) x [y0-4, y0+TH+4) of frame f in shared memory (out-of-image bytes arrive as
+    //         zeros) and signals an mbarrier; border tiles then mirror the few missing rows / columns in place (REFLECT_101, what
+    //         the blur of a cloned level sees).  Fallback (source not 16-byte aligned): ordinary loads, all issued before the
+    //         first store. ----
+    if (a.use_tma) {
+        const unsigned mb = (unsigned)__cvta_generic_to_shared(&mbar), dstp = (unsigned)__cvta_generic_to_shared(tws);
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mb));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(SMH * L3_SPB) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                         ::"r"(dstp), "l"(reinterpret_cast<unsigned long long>(&a.tmap)), "r"((x0 - 4) & ~15), "r"(y0 - 4), "r"(f), "r"(mb) : "memory");
+        }
+        __syncthreads();                                          // the barrier is initialised before anyone polls it
+        unsigned done = 0;
+        for (int spin = 0; spin < (1 << 22) && !done; spin++)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(mb) : "memory");
+        if (!done && tid == 0) atomicOr(a.status + f, 8);
+        const bool ytop = y0 < 4, ybot = y0 + TH + 4 > a.h, xl = x0 < 4, xr = x0 + L3_TWPX + 4 > a.w;
+        if (ytop || ybot || xl || xr) {                           // block-uniform: border tile
+            if (ytop || ybot) {                                   // rows outside the image <- their mirror rows (which are inside)
+                for (int r = warp; r < SMH; r += NW) {
+                    const int gy = y0 - 4 + r;
+                    if (gy < 0 || gy >= a.h) {
+                        const int rs = min(max(l3_reflect101(gy, a.h) - (y0 - 4), 0), SMH - 1);
+                        tw[r * L3_SP + lane] = tw[rs * L3_SP + lane];
+                    }
+                }
+                __syncthreads();
+            }
+            if (xl || xr) {
+                uint8_t* tbw = reinterpret_cast<uint8_t*>(tw);
+                for (int r = tid; r < SMH; r += NT) {
+                    if (xl) tw[r * L3_SP] = __byte_perm(tw[r * L3_SP + 1], tw[r * L3_SP + 2], 0x1234);      // pixels -4..-1 <- 4, 3, 2, 1
+                    if (xr) {
+#pragma unroll
+                        for (int b = 0; b < 4; b++) {                                                     // pixels w..w+3 <- w-2 .. w-5
+                            const int di = a.w + b - (x0 - 4), si = l3_reflect101(a.w + b, a.w) - (x0 - 4);
+                            if (di >= 0 && di < 128) tbw[r * L3_SPB + di] = tbw[r * L3_SPB + max(si, 0)];
+                        }
+                    }
+                }
+            }
+        }
+    } else {
         constexpr int RPW = SMH / NW;                             // staged rows per warp (SMH is a multiple of NW)
         const bool word_ok = ((a.src_pitch & 3) == 0) && ((reinterpret_cast<unsigned long long>(src) & 3) == 0);
         const int gx = x0 - 4 + 4 * lane;
         const bool inside = word_ok && gx >= 0 && gx + 3 < a.w;
         const bool bytes = !inside && gx < a.w + 4;               // edge lanes: 4 reflected byte loads per row
-        const bool yin = y0 >= 4 && y0 + TH + 4 <= a.h;           // no vertical reflection needed (block-uniform)
         const unsigned pitch = (unsigned)a.src_pitch;             // one frame is < 4 GB: 32-bit offsets
+        // every lane issues the same loads from a safe address and selects afterwards, so the loads go out back to back
+        const unsigned xw = inside ? (unsigned)gx : 0u;
+        const unsigned xb0 = bytes ? l3_reflect101(gx, a.w) : 0, xb1 = bytes ? l3_reflect101(gx + 1, a.w) : 0;
+        const unsigned xb2 = bytes ? l3_reflect101(gx + 2, a.w) : 0, xb3 = bytes ? l3_reflect101(gx + 3, a.w) : 0;
         unsigned v[RPW];
-        if (__all_sync(FULL, inside)) {
-            const uint8_t* p = src + gx;                          // one 64-bit pointer per lane, then 32-bit row offsets
-            if (yin) {
-                p += (unsigned)(y0 - 4 + warp) * pitch;
-                const unsigned step = NW * pitch;
-#pragma unroll
-                for (int i = 0; i < RPW; i++) v[i] = *reinterpret_cast<const uint32_t*>(p + i * step);
-            } else {
-#pragma unroll
-                for (int i = 0; i < RPW; i++)
-                    v[i] = *reinterpret_cast<const uint32_t*>(p + (unsigned)l3_reflect101(y0 - 4 + warp + NW * i, a.h) * pitch);
-            }
-        } else {
-            // mixed warp (tile on the left / right image border or unaligned source): every lane issues the same loads from a
-            // safe address and selects afterwards, so the loads still go out back to back
-            const unsigned xw = inside ? (unsigned)gx : 0u;
-            const unsigned xb0 = bytes ? l3_reflect101(gx, a.w) : 0, xb1 = bytes ? l3_reflect101(gx + 1, a.w) : 0;
-            const unsigned xb2 = bytes ? l3_reflect101(gx + 2, a.w) : 0, xb3 = bytes ? l3_reflect101(gx + 3, a.w) : 0;
-#pragma unroll
-            for (int i = 0; i < RPW; i++) {
-                const int r = warp + NW * i;
-                const int gy = yin ? y0 - 4 + r : l3_reflect101(y0 - 4 + r, a.h);
-                const uint8_t* row = src + (unsigned)gy * pitch;
-                unsigned vw = 0;
-                if (word_ok) vw = *reinterpret_cast<const uint32_t*>(row + xw);
-                const unsigned vb = (unsigned)row[xb0] | ((unsigned)row[xb1] << 8) | ((unsigned)row[xb2] << 16) | ((unsigned)row[xb3] << 24);
-                v[i] = inside ? vw : (bytes ? vb : 0u);
-            }
-        }
 #pragma unroll
         for (int i = 0; i < RPW; i++) {
-            const int r = warp + NW * i;
-            tw[r * L3_SP + 1 + lane] = v[i];
-            if (lane < 2) tw[r * L3_SP + lane * (L3_SP - 1)] = 0;       // pad words: read (and masked out) by the edge lanes
+            const uint8_t* row = src + (unsigned)l3_reflect101(y0 - 4 + warp + NW * i, a.h) * pitch;
+            unsigned vw = 0;
+            if (word_ok) vw = *reinterpret_cast<const uint32_t*>(row + xw);
+            const unsigned vb = (unsigned)row[xb0] | ((unsigned)row[xb1] << 8) | ((unsigned)row[xb2] << 16) | ((unsigned)row[xb3] << 24);
+            v[i] = inside ? vw : (bytes ? vb : 0u);
         }
+#pragma unroll
+        for (int i = 0; i < RPW; i++) tw[(warp + NW * i) * L3_SP + lane] = v[i];
     }
     for (int i = tid; i < SCH * L3_SCP / 4; i += NT) reinterpret_cast<uint32_t*>(sc)[i] = 0;
     __syncthreads();
@@ -169,7 +199,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
         unsigned E[14], O[14];
 #pragma unroll
         for (int i = 0; i < 14; i++) {
-            const unsigned w = tw[(ry0 + 1 + i) * L3_SP + 1 + lane];
+            const unsigned w = tw[(ry0 + 1 + i) * L3_SP + lane];
             E[i] = w & 0x00ff00ffu;
             O[i] = __byte_perm(w, 0u, 0x4341);
         }
@@ -220,7 +250,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
             const int k = active ? kb + lane : k1 - 1;
             // the 4 pixels of a destination word read source bytes s0 .. s0+5 (scale <= 1.25): an 8-byte window of the staged row
             const int4 e01 = *reinterpret_cast<const int4*>(a.xt + 4 * k), e23 = *reinterpret_cast<const int4*>(a.xt + 4 * k + 2);
-            const int off0 = e01.x - (x0 - 4) + 4;               // byte offset of the first source pixel inside a staged row
+            const int off0 = e01.x - (x0 - 4);                   // byte offset of the first source pixel inside a staged row
             const unsigned sh = 8u * (unsigned)(off0 & 3);
             const unsigned r1 = (unsigned)(e01.z - e01.x), r2 = (unsigned)(e23.x - e01.x), r3 = (unsigned)(e23.z - e01.x);
             const unsigned sel0 = 0x10u, sel1 = ((r1 + 1) << 4) | r1, sel2 = ((r2 + 1) << 4) | r2, sel3 = ((r3 + 1) << 4) | r3;
@@ -272,7 +302,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
             const int s = warp - 1 + NW * it;
             const int gy = y0 + s;
             if (s > TH || gy < 19 || gy > a.h - 20) continue;                        // warp-uniform
-            const uint32_t* rowp = tw + (s + 4) * L3_SP + 1 + lane;
+            const uint32_t* rowp = tw + (s + 4) * L3_SP + lane;
             const unsigned V = rowp[0], Lw = rowp[-1], Rw = rowp[1];
             const unsigned Vd = rowp[2 * L3_SP], Ld = rowp[2 * L3_SP - 1], Rd = rowp[2 * L3_SP + 1];
             const unsigned Vu = rowp[-2 * L3_SP], Lu = rowp[-2 * L3_SP - 1], Ru = rowp[-2 * L3_SP + 1];
@@ -318,7 +348,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
         if (j < qn) {
             pos = queue[j];
             const int r = pos >> 7, c = pos & 127;                // score-map row (tile row + 1), staged byte column
-            const int m = l3_arc_score(tb + (r + 3) * L3_SPB + 4 + c);
+            const int m = l3_arc_score(tb + (r + 3) * L3_SPB + c);
             if (m > a.minTh) {
                 sc[pos] = (uint8_t)m;
                 surv = r >= 1 && r <= TH && c >= 4 && c < 4 + L3_TWPX;     // the ring around the tile is scored for its neighbours only
