@@ -101,14 +101,12 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
 {
     constexpr int TH = L3_RG * NW, SMH = TH + 8, SCH = TH + 2, NT = 32 * NW;
     constexpr int QCAP = SCH * 122;                      // every scored pixel a candidate (uniform-noise images)
-    constexpr int EMIT_CAP = (TH / 2 + 3) * 65;          // NMS survivors are never 8-adjacent inside a cell
     constexpr unsigned FULL = 0xffffffffu;
     __shared__ __align__(128) uint32_t tws[SMH * L3_SP]; // tile + halo, 4 pixels per word (TMA destination)
     __shared__ __align__(8) unsigned long long mbar;      // completion barrier of the bulk tensor copy
     __shared__ __align__(4) uint8_t sc[SCH * L3_SCP];    // arc scores (> minTh) of the tile's pixels + 1-px ring
     __shared__ uint16_t queue[QCAP];
-    __shared__ uint32_t emit[EMIT_CAP];
-    __shared__ int s_qn, s_en, s_ebase;
+    __shared__ int s_qn;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int f = blockIdx.z;
@@ -118,7 +116,9 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
     const int cb = ((x0 - 4) & 15) >> 2;
     uint32_t* const tw = tws + cb;                          // tile word (r, c) = tw[r * L3_SP + c]
     const uint8_t* tb = reinterpret_cast<const uint8_t*>(tw);
-    if (tid == 0) { s_qn = 0; s_en = 0; }
+    if (tid == 0) s_qn = 0;
+
+    for (int i = tid; i < SCH * L3_SCP / 4; i += NT) reinterpret_cast<uint32_t*>(sc)[i] = 0;     // visible after the next barrier
 
     // ---- 1. stage tile + halo (128 bytes x SMH rows, lane = word column).  Normal case: ONE bulk tensor copy (TMA) issued by
     //         thread 0 lands the box [(x0-4) & ~15, +144) x [y0-4, y0+TH+4) of frame f in shared memory (out-of-image bytes arrive as
@@ -164,6 +164,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
                     }
                 }
             }
+            __syncthreads();
         }
     } else {
         constexpr int RPW = SMH / NW;                             // staged rows per warp (SMH is a multiple of NW)
@@ -187,9 +188,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
         }
 #pragma unroll
         for (int i = 0; i < RPW; i++) tw[(warp + NW * i) * L3_SP + lane] = v[i];
+        __syncthreads();
     }
-    for (int i = tid; i < SCH * L3_SCP / 4; i += NT) reinterpret_cast<uint32_t*>(sc)[i] = 0;
-    __syncthreads();
 
     const int ry0 = L3_RG * warp;                 // this warp's rows inside the tile
     const bool rows_live = y0 + ry0 < a.h;
@@ -260,7 +260,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
             int dy = dy0;
             int sy = __shfl_sync(FULL, eyl.x, 0); unsigned cy = (unsigned)__shfl_sync(FULL, eyl.y, 0);
             unsigned Hp0 = 0, Hp1 = 0, Hp2 = 0, Hp3 = 0;
-#pragma unroll
+#pragma unroll 3
             for (int r = 0; r <= L3_RG; r++) {
                 const unsigned X = __funnelshift_r(p0[r * L3_SP], p0[r * L3_SP + 1], sh), Y = __funnelshift_r(p0[r * L3_SP + 1], p0[r * L3_SP + 2], sh);
                 const unsigned Hc0 = __dp2a_lo(c0, __byte_perm(X, Y, sel0), 0u) >> 4, Hc1 = __dp2a_lo(c1, __byte_perm(X, Y, sel1), 0u) >> 4;
@@ -297,8 +297,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
         unsigned m0 = 0, m1 = 0;                                  // private candidate flags: 4 bits per row, rows it = 0..7 | 8
         constexpr int NIT = (TH + 2 + NW - 1) / NW;
         static_assert(NIT <= 9, "candidate masks hold 9 rows per warp");
-#pragma unroll
-        for (int it = 0; it < NIT; it++) {
+#pragma unroll 3
+        for (int it = 0; it < NIT; it++) {                                           // (partly rolled: instruction-cache footprint)
             const int s = warp - 1 + NW * it;
             const int gy = y0 + s;
             if (s > TH || gy < 19 || gy > a.h - 20) continue;                        // warp-uniform
@@ -337,15 +337,16 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
     __syncthreads();
     if (!fast_tile) return;
 
-    // ---- 5. exact arc score of the queued pixels; owned pixels above minTh are re-queued (in place) for the NMS ----
+    // ---- 5. exact arc score of the queued pixels.  Each warp owns a contiguous chunk of the queue and compacts the entries that
+    //         survive (owned pixel, score above minTh) to the front of its own chunk: warp-level sync only. ----
     const int qn = s_qn;
-    __syncthreads();                                             // everyone has read s_qn: it becomes the survivor counter
-    if (tid == 0) s_qn = 0;
-    __syncthreads();
-    for (int j0 = 0; j0 < qn; j0 += NT) {
-        const int j = j0 + tid;
+    const int chunk = (qn + NW - 1) / NW;
+    const int cbeg = warp * chunk, cend = min(qn, cbeg + chunk);
+    int wcnt = 0;
+    for (int j0 = cbeg; j0 < cend; j0 += 32) {
+        const int j = j0 + lane;
         bool surv = false; int pos = 0;
-        if (j < qn) {
+        if (j < cend) {
             pos = queue[j];
             const int r = pos >> 7, c = pos & 127;                // score-map row (tile row + 1), staged byte column
             const int m = l3_arc_score(tb + (r + 3) * L3_SPB + c);
@@ -354,46 +355,43 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
                 surv = r >= 1 && r <= TH && c >= 4 && c < 4 + L3_TWPX;     // the ring around the tile is scored for its neighbours only
             }
         }
-        // survivors overwrite the front of the queue: slot index < j0 + NT of an entry already consumed by this pass
-        const unsigned bal = __ballot_sync(FULL, surv);
-        int base = 0;
-        if (lane == 0 && bal) base = atomicAdd(&s_qn, __popc(bal));
-        base = __shfl_sync(FULL, base, 0);
-        __syncthreads();                                         // all entries of this pass are consumed before any is overwritten
-        if (surv) queue[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)pos;
+        const unsigned bal = __ballot_sync(FULL, surv);          // (also orders this pass's queue reads before the writes below)
+        if (surv) queue[cbeg + wcnt + __popc(bal & ((1u << lane) - 1))] = (uint16_t)pos;
+        wcnt += __popc(bal);
     }
-    __syncthreads();
+    __syncthreads();                                             // every score of the tile is in the map
 
-    // ---- 6. cell-local 3x3 non-max suppression (strict '>') and emission ----
-    const int sn = s_qn;
-    for (int j = tid; j < sn; j += NT) {
-        const int pos = queue[j];
-        const int r = pos >> 7, c = pos & 127;
-        const uint8_t* sp = sc + pos;
-        const int m = sp[0];
-        const int gx = x0 - 4 + c, gy = y0 - 1 + r;
-        // position inside the 30-px FAST cell: a neighbour in ANOTHER cell never suppresses (cv::FAST ran per cell)
-        const int cellx = __umulhi((unsigned)(gx - 19), a.magicW), celly = __umulhi((unsigned)(gy - 19), a.magicH);
-        const int rx = gx - 19 - cellx * a.wCell, ry = gy - 19 - celly * a.hCell;
-        const bool left = rx > 0, right = rx < a.wCell - 1, up = ry > 0, down = ry < a.hCell - 1;
-        bool keep = true;
-        if (up) { if ((left && sp[-L3_SCP - 1] >= m) || sp[-L3_SCP] >= m || (right && sp[-L3_SCP + 1] >= m)) keep = false; }
-        if ((left && sp[-1] >= m) || (right && sp[1] >= m)) keep = false;
-        if (down) { if ((left && sp[L3_SCP - 1] >= m) || sp[L3_SCP] >= m || (right && sp[L3_SCP + 1] >= m)) keep = false; }
-        if (keep) {
-            const int e = atomicAdd(&s_en, 1);
-            if (e < EMIT_CAP) emit[e] = ((unsigned)gy << 20) | ((unsigned)gx << 8) | (unsigned)m;
+    // ---- 6. cell-local 3x3 non-max suppression (strict '>') on the warp's survivors; kept corners go straight to the frame's
+    //         record list (one global atomic per warp pass) ----
+    uint32_t* __restrict__ rec = a.rec + (long long)f * a.rec_fstride;
+    int* rec_count = a.rec_count + (long long)f * a.rec_count_stride;
+    for (int j0 = cbeg; j0 < cbeg + wcnt; j0 += 32) {
+        const int j = j0 + lane;
+        bool keep = false; unsigned record = 0;
+        if (j < cbeg + wcnt) {
+            const int pos = queue[j];
+            const int r = pos >> 7, c = pos & 127;
+            const uint8_t* sp = sc + pos;
+            const int m = sp[0];
+            const int gx = x0 - 4 + c, gy = y0 - 1 + r;
+            // position inside the 30-px FAST cell: a neighbour in ANOTHER cell never suppresses (cv::FAST ran per cell)
+            const int cellx = __umulhi((unsigned)(gx - 19), a.magicW), celly = __umulhi((unsigned)(gy - 19), a.magicH);
+            const int rx = gx - 19 - cellx * a.wCell, ry = gy - 19 - celly * a.hCell;
+            const bool left = rx > 0, right = rx < a.wCell - 1, up = ry > 0, down = ry < a.hCell - 1;
+            keep = true;
+            if (up) { if ((left && sp[-L3_SCP - 1] >= m) || sp[-L3_SCP] >= m || (right && sp[-L3_SCP + 1] >= m)) keep = false; }
+            if ((left && sp[-1] >= m) || (right && sp[1] >= m)) keep = false;
+            if (down) { if ((left && sp[L3_SCP - 1] >= m) || sp[L3_SCP] >= m || (right && sp[L3_SCP + 1] >= m)) keep = false; }
+            record = ((unsigned)gy << 20) | ((unsigned)gx << 8) | (unsigned)m;
+        }
+        const unsigned bal = __ballot_sync(FULL, keep);
+        if (bal) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(rec_count, __popc(bal));
+            base = __shfl_sync(FULL, base, 0) + __popc(bal & ((1u << lane) - 1));
+            if (keep && base < a.rec_cap) rec[base] = record;
         }
     }
-    __syncthreads();
-    const int en = min(s_en, EMIT_CAP);
-    if (en == 0) return;
-    if (tid == 0) s_ebase = atomicAdd(a.rec_count + (long long)f * a.rec_count_stride, en);
-    __syncthreads();
-    const int ebase = s_ebase;
-    uint32_t* __restrict__ rec = a.rec + (long long)f * a.rec_fstride;
-    for (int j = tid; j < en; j += NT)
-        if (ebase + j < a.rec_cap) rec[ebase + j] = emit[j];
 }
 
 // Generic bilinear resize (one thread per destination pixel, reads global memory): used instead of the fused path when
