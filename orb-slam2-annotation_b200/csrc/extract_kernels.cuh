@@ -498,14 +498,50 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
     return a;
 }
 
-// One warp owns 32 consecutive output slots.  Phase A: the warp visits its keypoints one by one, lane = patch COLUMN
-// u (coalesced row reads), REDUX-reduces m10/m01 and parks them in lane j.  Phase B: every lane finishes ITS keypoint
-// (fastAtan2, cos/sin in double -> float: 32 keypoints per instruction instead of one).  Phase C: the warp visits the
-// keypoints again, lane = descriptor BYTE, the 16 pattern points of that byte live in registers as floats.
-__global__ void __launch_bounds__(256) orient_desc_kernel(const __grid_constant__ DescArgs a)
+// One warp owns 32 consecutive output slots.
+//   Phase A (IC_Angle, ORBextractor.cpp:79-106): the warp visits its keypoints one by one.  The 31x31 window is read as
+//            ALIGNED 32-bit words, 9 per row, three rows per warp load (lane = row%3 * 9 + word: coalesced, and the address
+//            is a running pointer).  The circular mask is a packed byte compare (|u| <= umax[|v|]) and the moments come from
+//            three IDP.4A per word: S = sum(p), T = sum(b*p) (b = byte 0..3), A = sum(it*p), from which
+//            m10 = u0*S + T and m01 = 3*A + (row%3 - 15)*S per lane.  REDUX-reduced and parked in lane j.
+//            The next keypoint's words are requested before the current ones are consumed.
+//   Phase B: every lane finishes ITS keypoint (fastAtan2, cos/sin in double -> float: 32 keypoints per instruction).
+//   Phase C (computeOrbDescriptor, :110-149): the 37x37 blurred window (10 aligned words per row) is staged in shared memory
+//            with the same three-rows-per-load scheme, then lane = descriptor BYTE: 16 rotated pattern points per lane are
+//            read from the staged window.  Again the next window is in flight while the current one is used.
+constexpr int OD_WARPS = 8;
+constexpr int OD_AW = 9, OD_AIT = 11;          // phase A: words per row, warp loads per window (33 >= 31 rows)
+constexpr int OD_PW = 10, OD_PIT = 13;         // phase C: words per staged row (37 bytes + 3 alignment), warp loads (39 >= 37 rows)
+constexpr int OD_PROWS = 37;
+
+__device__ __forceinline__ unsigned od_dp4a_us(unsigned a, unsigned b, unsigned c)
 {
-    const int f = blockIdx.y, lane = threadIdx.x & 31;
-    const int wid = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    unsigned d; asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
+}
+
+// NIT warp loads of three rows each: lane's word of row 3*it + r3, zero where the lane has no item
+template <int NIT, int NROWS>
+__device__ __forceinline__ void od_load_rows(unsigned (&w)[NIT], const uint8_t* q, int p3, int r3, bool lane_ok)
+{
+#pragma unroll
+    for (int it = 0; it < NIT; it++) {
+        const bool ok = lane_ok && ((3 * it + 2 < NROWS) || (3 * it + r3 < NROWS));
+        w[it] = 0;
+        if (ok) w[it] = __ldg(reinterpret_cast<const unsigned*>(q + (long long)it * p3));
+    }
+}
+
+__global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __grid_constant__ DescArgs a)
+{
+    __shared__ uint32_t patch_s[OD_WARPS][OD_PROWS * OD_PW + 2];
+    __shared__ uint32_t absu_s[40];            // |u0+b| packed per byte, indexed by u0 + 18
+    const int f = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x < 40) {
+        const int u0 = (int)threadIdx.x - 18;
+        absu_s[threadIdx.x] = (unsigned)abs(u0) | ((unsigned)abs(u0 + 1) << 8) | ((unsigned)abs(u0 + 2) << 16) | ((unsigned)abs(u0 + 3) << 24);
+    }
+    __syncthreads();
+    const int wid = blockIdx.x * OD_WARPS + warp;
     const int base = wid * 32;
     const int* cnt = a.lvl_count + (long long)f * a.nlevels;
     // own keypoint: (level, index) from the per-level counts
@@ -530,25 +566,71 @@ __global__ void __launch_bounds__(256) orient_desc_kernel(const __grid_constant_
         kx = k.x; ky = k.y; kresp = k.z;
         if (level == 0) { img = a.src0 + (long long)f * a.src0_fstride; pitch = (int)a.src0_pitch; }
         else { img = a.pyr + (long long)f * a.pyr_fstride + g.off; pitch = g.pitch; }
-        bimg = a.blur + (long long)f * a.blur_fstride + g.off; bpitch = g.pitch;
-        img += (long long)ky * pitch + kx; bimg += (long long)ky * bpitch + kx;          // patch centres
+        bimg = a.blur + (long long)f * a.blur_fstride + g.off; bpitch = g.pitch;      // level bases; the centre is (kx, ky)
         scale = g.scale; size = g.size;
     }
-    // ---- phase A: intensity centroid (IC_Angle, ORBextractor.cpp:79-106); lane = column u = lane - 15 ----
-    const int u = lane - 15;
-    const int dmax = lane < 31 ? c_umax[abs(u)] : -1;      // the disc is symmetric: |v| <= umax[|u|]
+    // ---- phase A: intensity centroid ----
     int my_m10 = 0, my_m01 = 0;
-    for (int j = 0; j < nvalid; j++) {
-        const uint8_t* c = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)img, j);
-        const int p = __shfl_sync(0xffffffffu, pitch, j);
-        int s = 0, sv = 0;
+    {
+        const int r3 = lane / OD_AW, wc = lane - r3 * OD_AW;        // lanes 27..31 carry no item
+        const bool lane_ok = lane < 3 * OD_AW;
+        // umax of the lane's row in each of the 11 loads, as 0x80|umax bytes (four loads per register)
+        unsigned umr[3] = {0u, 0u, 0u};
 #pragma unroll
-        for (int v = -15; v <= 15; v++) {
-            if (abs(v) <= dmax) { const int val = c[v * p + u]; s += val; sv += v * val; }
+        for (int it = 0; it < OD_AIT; it++) {
+            const int row = 3 * it + r3;
+            const unsigned um = 0x80u | (unsigned)c_umax[min(abs(row - 15), 15)];
+            umr[it >> 2] |= um << (8 * (it & 3));
         }
-        const int m10 = __reduce_add_sync(0xffffffffu, u * s);
-        const int m01 = __reduce_add_sync(0xffffffffu, sv);
-        if (lane == j) { my_m10 = m10; my_m01 = m01; }
+        unsigned wn[OD_AIT]; int cxn = 0, uan = 0; bool aln = false;
+        const uint8_t* ibn = nullptr; int pn = 0, cyn = 0;
+        // request keypoint j's window
+        auto request = [&](int j) {
+            ibn = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)img, j);
+            pn = __shfl_sync(0xffffffffu, pitch, j); cxn = __shfl_sync(0xffffffffu, kx, j); cyn = __shfl_sync(0xffffffffu, ky, j);
+            aln = (((unsigned long long)ibn | (unsigned)pn) & 3) == 0;   // warp-uniform
+            if (aln) {
+                const int xs = (cxn - 15) & ~3;
+                uan = xs - cxn;                                          // u of byte 0 of word 0 (-18 .. -15)
+                od_load_rows<OD_AIT, 31>(wn, ibn + (long long)(cyn - 15 + r3) * pn + xs + 4 * wc, 3 * pn, r3, lane_ok);
+            }
+        };
+        request(0);
+        for (int j = 0; j < nvalid; j++) {
+            unsigned w[OD_AIT];
+#pragma unroll
+            for (int it = 0; it < OD_AIT; it++) w[it] = wn[it];
+            const bool al = aln; const int ua = uan, cx = cxn, cy = cyn, p = pn; const uint8_t* ib = ibn;
+            if (j + 1 < nvalid) request(j + 1);
+            int m10, m01;
+            if (al) {
+                const int u0 = ua + 4 * wc;
+                const unsigned au = absu_s[u0 + 18];
+                unsigned S = 0, T = 0, A = 0;
+#pragma unroll
+                for (int it = 0; it < OD_AIT; it++) {
+                    const unsigned umb = __byte_perm(umr[it >> 2], 0u, 0x1111u * (it & 3));     // 0x80|umax in every byte
+                    const unsigned ge = ((umb - au) >> 7) & 0x01010101u;                          // umax >= |u| per byte
+                    const unsigned wm = w[it] & (ge * 0xffu);
+                    S = od_dp4a_us(wm, 0x01010101u, S);
+                    T = od_dp4a_us(wm, 0x03020100u, T);
+                    A = od_dp4a_us(wm, 0x01010101u * (unsigned)it, A);
+                }
+                m10 = u0 * (int)S + (int)T;
+                m01 = 3 * (int)A + (r3 - 15) * (int)S;
+            } else {                                                    // unaligned caller image (level 0 only): bytes, lane = column
+                const int u = lane - 15;
+                const int dmax = lane < 31 ? c_umax[abs(u)] : -1;       // the disc is symmetric: |v| <= umax[|u|]
+                const uint8_t* c = ib + (long long)cy * p + cx;
+                int s = 0, sv = 0;
+                for (int v = -15; v <= 15; v++)
+                    if (abs(v) <= dmax) { const int val = c[v * p + u]; s += val; sv += v * val; }
+                m10 = u * s; m01 = sv;
+            }
+            m10 = __reduce_add_sync(0xffffffffu, m10);
+            m01 = __reduce_add_sync(0xffffffffu, m01);
+            if (lane == j) { my_m10 = m10; my_m01 = m01; }
+        }
     }
     // ---- phase B: per-lane angle and rotation ----
     const float angle = fast_atan2_deg((float)my_m01, (float)my_m10);
@@ -561,15 +643,37 @@ __global__ void __launch_bounds__(256) orient_desc_kernel(const __grid_constant_
         kp.size = size; kp.angle = angle; kp.response = (float)kresp; kp.octave = level; kp.class_id = -1;
         a.kps[(long long)f * a.capacity + slot] = kp;
     }
-    // ---- phase C: steered BRIEF (computeOrbDescriptor, ORBextractor.cpp:110-149); lane = descriptor byte ----
+    // ---- phase C: steered BRIEF; lane = descriptor byte ----
     float px[16], py[16];
 #pragma unroll
     for (int i = 0; i < 16; i++) { px[i] = (float)c_pattern[lane * 32 + 2 * i]; py[i] = (float)c_pattern[lane * 32 + 2 * i + 1]; }
     uint8_t* dout = a.desc + ((long long)f * a.capacity + base) * 32 + lane;
+    uint32_t* ps = patch_s[warp];
+    const uint8_t* pb = reinterpret_cast<const uint8_t*>(ps);
+    const int r3 = lane / OD_PW, wc = lane - r3 * OD_PW;           // lanes 30, 31 carry no item
+    const bool lane_ok = lane < 3 * OD_PW;
+    unsigned wn[OD_PIT]; int con = 0; float cjn = 0.f, sjn = 0.f;
+    // request keypoint j's blurred window: rows cy-18 .. cy+18, aligned words from (cx-18) & ~3 (the blurred levels are
+    // pitch-aligned buffers of this library)
+    auto request = [&](int j) {
+        const uint8_t* bb = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)bimg, j);
+        const int p = __shfl_sync(0xffffffffu, bpitch, j), cx = __shfl_sync(0xffffffffu, kx, j), cy = __shfl_sync(0xffffffffu, ky, j);
+        cjn = __shfl_sync(0xffffffffu, ca, j); sjn = __shfl_sync(0xffffffffu, sb, j);
+        const int xs = (cx - 18) & ~3;
+        con = 18 * (4 * OD_PW) + (cx - xs);                         // window centre inside the staged rows
+        od_load_rows<OD_PIT, OD_PROWS>(wn, bb + (long long)(cy - 18 + r3) * p + xs + 4 * wc, 3 * p, r3, lane_ok);
+    };
+    request(0);
     for (int j = 0; j < nvalid; j++) {
-        const uint8_t* c = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)bimg, j);
-        const int p = __shfl_sync(0xffffffffu, bpitch, j);
-        const float cj = __shfl_sync(0xffffffffu, ca, j), sj = __shfl_sync(0xffffffffu, sb, j);
+        __syncwarp();                                                   // the previous keypoint's reads are done
+        if (lane_ok) {
+#pragma unroll
+            for (int it = 0; it < OD_PIT; it++)
+                if ((3 * it + 2 < OD_PROWS) || (3 * it + r3 < OD_PROWS)) ps[it * (3 * OD_PW) + lane] = wn[it];
+        }
+        const uint8_t* c = pb + con; const float cj = cjn, sj = sjn;
+        __syncwarp();
+        if (j + 1 < nvalid) request(j + 1);
         int val = 0;
 #pragma unroll
         for (int b = 0; b < 8; b++) {
@@ -577,7 +681,7 @@ __global__ void __launch_bounds__(256) orient_desc_kernel(const __grid_constant_
             const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(px[2 * b], cj), __fmul_rn(py[2 * b], sj)));
             const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(px[2 * b + 1], sj), __fmul_rn(py[2 * b + 1], cj)));
             const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(px[2 * b + 1], cj), __fmul_rn(py[2 * b + 1], sj)));
-            const int t0 = c[r0 * p + c0], t1 = c[r1 * p + c1];
+            const int t0 = c[r0 * (4 * OD_PW) + c0], t1 = c[r1 * (4 * OD_PW) + c1];
             val |= (t0 < t1) << b;
         }
         dout[j * 32] = (uint8_t)val;
