@@ -519,21 +519,18 @@ __device__ __forceinline__ unsigned od_dp4a_us(unsigned a, unsigned b, unsigned 
     unsigned d; asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d;
 }
 
-// NIT warp loads of three rows each: lane's word of row 3*it + r3, zero where the lane has no item
-template <int NIT, int NROWS>
-__device__ __forceinline__ void od_load_rows(unsigned (&w)[NIT], const uint8_t* q, int p3, int r3, bool lane_ok)
+// NIT warp loads of three rows each: lane's word of row 3*it + r3.  Unconditional: rows past the window and the idle lanes'
+// items stay inside the level (keypoints are >= 19 px from the border) or the buffer margin, and are masked by the consumer.
+template <int NIT>
+__device__ __forceinline__ void od_load_rows(unsigned (&w)[NIT], const uint8_t* q, unsigned p3)
 {
 #pragma unroll
-    for (int it = 0; it < NIT; it++) {
-        const bool ok = lane_ok && ((3 * it + 2 < NROWS) || (3 * it + r3 < NROWS));
-        w[it] = 0;
-        if (ok) w[it] = __ldg(reinterpret_cast<const unsigned*>(q + (long long)it * p3));
-    }
+    for (int it = 0; it < NIT; it++) w[it] = __ldg(reinterpret_cast<const unsigned*>(q + (unsigned long long)it * p3));
 }
 
 __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __grid_constant__ DescArgs a)
 {
-    __shared__ uint32_t patch_s[OD_WARPS][OD_PROWS * OD_PW + 2];
+    __shared__ uint32_t patch_s[OD_WARPS][3 * OD_PIT * OD_PW + 2];
     __shared__ uint32_t absu_s[40];            // |u0+b| packed per byte, indexed by u0 + 18
     const int f = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x < 40) {
@@ -573,13 +570,13 @@ __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __g
     int my_m10 = 0, my_m01 = 0;
     {
         const int r3 = lane / OD_AW, wc = lane - r3 * OD_AW;        // lanes 27..31 carry no item
-        const bool lane_ok = lane < 3 * OD_AW;
-        // umax of the lane's row in each of the 11 loads, as 0x80|umax bytes (four loads per register)
+        // umax of the lane's row in each of the 11 loads, as 0x80|umax bytes (four loads per register); 0x7f = nothing passes
+        // (rows past the window, and lanes 27..31 whose rows belong to other lanes)
         unsigned umr[3] = {0u, 0u, 0u};
 #pragma unroll
         for (int it = 0; it < OD_AIT; it++) {
             const int row = 3 * it + r3;
-            const unsigned um = 0x80u | (unsigned)c_umax[min(abs(row - 15), 15)];
+            const unsigned um = (r3 < 3 && row < 31) ? 0x80u | (unsigned)c_umax[min(abs(row - 15), 15)] : 0x7fu;
             umr[it >> 2] |= um << (8 * (it & 3));
         }
         unsigned wn[OD_AIT]; int cxn = 0, uan = 0; bool aln = false;
@@ -592,7 +589,7 @@ __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __g
             if (aln) {
                 const int xs = (cxn - 15) & ~3;
                 uan = xs - cxn;                                          // u of byte 0 of word 0 (-18 .. -15)
-                od_load_rows<OD_AIT, 31>(wn, ibn + (long long)(cyn - 15 + r3) * pn + xs + 4 * wc, 3 * pn, r3, lane_ok);
+                od_load_rows<OD_AIT>(wn, ibn + (long long)(cyn - 15 + r3) * pn + xs + 4 * wc, 3u * (unsigned)pn);
             }
         };
         request(0);
@@ -661,15 +658,14 @@ __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __g
         cjn = __shfl_sync(0xffffffffu, ca, j); sjn = __shfl_sync(0xffffffffu, sb, j);
         const int xs = (cx - 18) & ~3;
         con = 18 * (4 * OD_PW) + (cx - xs);                         // window centre inside the staged rows
-        od_load_rows<OD_PIT, OD_PROWS>(wn, bb + (long long)(cy - 18 + r3) * p + xs + 4 * wc, 3 * p, r3, lane_ok);
+        od_load_rows<OD_PIT>(wn, bb + (long long)(cy - 18 + r3) * p + xs + 4 * wc, 3u * (unsigned)p);
     };
     request(0);
     for (int j = 0; j < nvalid; j++) {
         __syncwarp();                                                   // the previous keypoint's reads are done
         if (lane_ok) {
 #pragma unroll
-            for (int it = 0; it < OD_PIT; it++)
-                if ((3 * it + 2 < OD_PROWS) || (3 * it + r3 < OD_PROWS)) ps[it * (3 * OD_PW) + lane] = wn[it];
+            for (int it = 0; it < OD_PIT; it++) ps[it * (3 * OD_PW) + lane] = wn[it];
         }
         const uint8_t* c = pb + con; const float cj = cjn, sj = sjn;
         __syncwarp();
