@@ -31,6 +31,7 @@ struct orbx_handle {
     int nlevels;
     cudaStream_t stream = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;      // copy streams of the host-buffer batch pipeline
+    cudaStream_t s_k2 = nullptr;                       // second kernel stream: odd chunks (their latency-bound tails overlap the next chunk)
     std::vector<cudaEvent_t> ev_in, ev_done;          // per chunk: frames landed in HBM / results ready
     // ORBextractor tables (ORBextractor.cpp:417-448, :456-471)
     float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS], sigma2[ORBB_MAX_LEVELS], inv_sigma2[ORBB_MAX_LEVELS];
@@ -319,6 +320,7 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+    ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_k2, cudaStreamNonBlocking));
     ok(dev_alloc(&h->d_pyr, B * h->cap_pyr)); ok(dev_alloc(&h->d_blur, B * h->cap_pyr));
     ok(dev_alloc(&h->d_rec, B * h->cap_rec)); ok(dev_alloc(&h->d_pts, 2 * B * h->cap_rec));
     ok(dev_alloc(&h->d_nodes, B * h->cap_node)); ok(dev_alloc(&h->d_iscr, B * h->cap_node * ISCR_PER_NODE));
@@ -354,6 +356,7 @@ extern "C" int orbx_destroy(orbx_handle* h)
     for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
+    if (h->s_k2) cudaStreamDestroy(h->s_k2);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBB_OK;
@@ -378,7 +381,7 @@ extern "C" int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_sc
 // desc_dev / counts_dev address frame 0 of the batch; every per-frame scratch buffer of the handle is indexed the same way, so
 // chunks of one batch can be enqueued independently (orbx_extract_batch pipelines them against the host copies).
 static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int nframes, int w, int ht, size_t stride, size_t fstride,
-                           orbx_keypoint* kps_dev0, uint8_t* desc_dev0, int32_t* counts_dev0, int capacity)
+                           orbx_keypoint* kps_dev0, uint8_t* desc_dev0, int32_t* counts_dev0, int capacity, cudaStream_t on_stream = nullptr)
 {
     if (w != h->cur_w || ht != h->cur_h) {
         int rc = setup_geometry(h, w, ht, false);
@@ -388,7 +391,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         h->cur_w = w; h->cur_h = ht;
     }
     const int nl = h->nlevels;
-    cudaStream_t st = h->stream;
+    cudaStream_t st = on_stream ? on_stream : h->stream;
     const size_t F0 = (size_t)f0;
     const uint8_t* imgs_dev = imgs_dev0 + F0 * fstride;
     orbx_keypoint* kps_dev = kps_dev0 + F0 * capacity; uint8_t* desc_dev = desc_dev0 + F0 * capacity * 32; int32_t* counts_dev = counts_dev0 + F0;
@@ -542,6 +545,7 @@ static int pipeline_chunk(int w, int ht)
     int c = (int)((64ll * 640 * 480) / (px > 0 ? px : 1));
     if (c < 1) c = 1;
     if (c > 64) c = 64;
+    if (const char* e = getenv("ORBB_CHUNK")) { const int v = atoi(e); if (v > 0) c = v; }
     return c;
 }
 
@@ -592,25 +596,48 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
         h->ev_in.push_back(e1); h->ev_done.push_back(e2);
     }
     const bool prof = h->profiling;      // per-kernel-class event timing needs the whole batch in one enqueue
+    // Level-0 layout on the device: rows packed at pitch w when that keeps the TMA path (16-byte pitch); then a chunk of
+    // packed host frames travels as ONE copy whose "rows" are whole frames (the copy engine runs at PCIe speed on large rows;
+    // one 2-D copy per frame with 752-byte rows reaches about half of it).
+    const bool tight = (w % 16) == 0 && (size_t)w * ht <= (size_t)g0.pitch * g0.h;
+    const size_t dpitch0 = tight ? (size_t)w : (size_t)g0.pitch;
+    const bool packed = tight && (!pinned || (stride == (size_t)w && (nframes == 1 || fstride >= (size_t)w * ht)));
     for (int c = 0; c < nchunks; c++) {
         const int f0 = c * CH, nf = nframes - f0 < CH ? nframes - f0 : CH;
-        for (int f = f0; f < f0 + nf; f++) {
-            const uint8_t* src = imgs_host + (size_t)f * fstride;
-            size_t spitch = stride;
-            if (!pinned) {     // stage through pinned memory so the copy is truly asynchronous
+        if (!pinned) {         // stage through pinned memory so the copy is truly asynchronous
+            for (int f = f0; f < f0 + nf; f++) {
+                const uint8_t* src = imgs_host + (size_t)f * fstride;
                 uint8_t* stg = h->h_img + (size_t)f * w * ht;
-                for (int y = 0; y < ht; y++) memcpy(stg + (size_t)y * w, src + (size_t)y * stride, w);
-                src = stg; spitch = w;
+                if (stride == (size_t)w) memcpy(stg, src, (size_t)w * ht);
+                else for (int y = 0; y < ht; y++) memcpy(stg + (size_t)y * w, src + (size_t)y * stride, w);
             }
-            ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, g0.pitch, src, spitch, w, ht,
-                                        cudaMemcpyHostToDevice, h->s_in));
+        }
+        const uint8_t* cbase = pinned ? imgs_host : h->h_img;
+        const size_t cstride = pinned ? stride : (size_t)w, cfstride = pinned ? fstride : (size_t)w * ht;
+        static const int h2d_mode = getenv("ORBB_H2D_MODE") ? atoi(getenv("ORBB_H2D_MODE")) : 0;
+        if (packed && h2d_mode == 1) {
+            for (int f = f0; f < f0 + nf; f++)
+                ORBB_CUDA(cudaMemcpyAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, cbase + (size_t)f * cfstride, (size_t)w * ht,
+                                          cudaMemcpyHostToDevice, h->s_in));
+        } else if (packed) {
+            ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, h->pyr_fstride, cbase + (size_t)f0 * cfstride,
+                                        nf > 1 ? cfstride : (size_t)w * ht, (size_t)w * ht, nf, cudaMemcpyHostToDevice, h->s_in));
+        } else {
+            for (int f = f0; f < f0 + nf; f++)
+                ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, dpitch0, cbase + (size_t)f * cfstride, cstride, w, ht,
+                                            cudaMemcpyHostToDevice, h->s_in));
         }
         ORBB_CUDA(cudaEventRecord(h->ev_in[c], h->s_in));
-        if (prof) continue;
-        ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_in[c], 0));
-        const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, g0.pitch, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
+    }
+    // every input copy is queued before the first kernel: the copy engine never waits for the host to finish launching a chunk
+    for (int c = 0; c < nchunks && !prof; c++) {
+        const int f0 = c * CH, nf = nframes - f0 < CH ? nframes - f0 : CH;
+        static const int two_streams = getenv("ORBB_ONE_KSTREAM") ? 0 : 1;
+        cudaStream_t kst = (two_streams && (c & 1)) ? h->s_k2 : st;
+        ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
+        const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, kst);
         if (rc != ORBB_OK) return rc;
-        ORBB_CUDA(cudaEventRecord(h->ev_done[c], st));
+        ORBB_CUDA(cudaEventRecord(h->ev_done[c], kst));
         ORBB_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));
         ORBB_CUDA(cudaMemcpyAsync(h->h_counts + f0, h->d_counts + f0, sizeof(int) * nf, cudaMemcpyDeviceToHost, h->s_out));
         ORBB_CUDA(cudaMemcpyAsync(h->h_status + f0, h->d_status + f0, sizeof(int) * nf, cudaMemcpyDeviceToHost, h->s_out));
@@ -619,7 +646,7 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     }
     if (prof) {
         ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_in[nchunks - 1], 0));
-        const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, g0.pitch, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
+        const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
         if (rc != ORBB_OK) return rc;
         ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
         ORBB_CUDA(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
@@ -628,6 +655,7 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
         ORBB_CUDA(cudaStreamSynchronize(st));
     }
     ORBB_CUDA(cudaStreamSynchronize(h->s_out));
+    ORBB_CUDA(cudaStreamSynchronize(h->s_k2));
     ORBB_CUDA(cudaStreamSynchronize(st));
     int ret = ORBB_OK;
     for (int f = 0; f < nframes; f++) {

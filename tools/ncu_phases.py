@@ -18,7 +18,7 @@ def find(s):
         if s in l: return i + 1
     raise KeyError(s)
 marks = [('prologue', find('level3_kernel(const')), ('stage', find('---- 1. stage')), ('blur', find('---- 2. blur')), ('resize', find('---- 3. bilinear')),
-         ('reject', find('---- 4. FAST')), ('score', find('---- 5. exact')), ('nms', find('---- 6. cell-local')), ('emit', find('const int en = min')), ('end', find('// Generic bilinear'))]
+         ('reject', find('---- 4. FAST')), ('score', find('---- 5. exact')), ('nms', find('---- 6. cell-local')), ('end', find('// Generic bilinear'))]
 ph = {}
 def add(name, a):
     p = ph.setdefault(name, [0, 0]); p[0] += a[0]; p[1] += a[1]
