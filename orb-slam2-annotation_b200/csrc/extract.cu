@@ -31,7 +31,8 @@ struct orbx_handle {
     int nlevels;
     cudaStream_t stream = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;      // copy streams of the host-buffer batch pipeline
-    cudaStream_t s_k2 = nullptr;                       // second kernel stream: odd chunks (their latency-bound tails overlap the next chunk)
+    cudaStream_t s_k[3] = {nullptr, nullptr, nullptr};  // extra kernel streams: chunks rotate over stream + these (latency-bound tails overlap the next chunk)
+    int n_kstreams = 2;
     std::vector<cudaEvent_t> ev_in, ev_done;          // per chunk: frames landed in HBM / results ready
     // ORBextractor tables (ORBextractor.cpp:417-448, :456-471)
     float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS], sigma2[ORBB_MAX_LEVELS], inv_sigma2[ORBB_MAX_LEVELS];
@@ -320,7 +321,8 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
-    ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_k2, cudaStreamNonBlocking));
+    for (int i = 0; i < 3; i++) ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_k[i], cudaStreamNonBlocking));
+    if (const char* e = getenv("ORBB_KSTREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 4) h->n_kstreams = v; }
     ok(dev_alloc(&h->d_pyr, B * h->cap_pyr)); ok(dev_alloc(&h->d_blur, B * h->cap_pyr));
     ok(dev_alloc(&h->d_rec, B * h->cap_rec)); ok(dev_alloc(&h->d_pts, 2 * B * h->cap_rec));
     ok(dev_alloc(&h->d_nodes, B * h->cap_node)); ok(dev_alloc(&h->d_iscr, B * h->cap_node * ISCR_PER_NODE));
@@ -356,7 +358,7 @@ extern "C" int orbx_destroy(orbx_handle* h)
     for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
-    if (h->s_k2) cudaStreamDestroy(h->s_k2);
+    for (int i = 0; i < 3; i++) if (h->s_k[i]) cudaStreamDestroy(h->s_k[i]);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBB_OK;
@@ -632,8 +634,8 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     // every input copy is queued before the first kernel: the copy engine never waits for the host to finish launching a chunk
     for (int c = 0; c < nchunks && !prof; c++) {
         const int f0 = c * CH, nf = nframes - f0 < CH ? nframes - f0 : CH;
-        static const int two_streams = getenv("ORBB_ONE_KSTREAM") ? 0 : 1;
-        cudaStream_t kst = (two_streams && (c & 1)) ? h->s_k2 : st;
+        const int ks = c % h->n_kstreams;
+        cudaStream_t kst = ks ? h->s_k[ks - 1] : st;
         ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
         const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, kst);
         if (rc != ORBB_OK) return rc;
@@ -655,7 +657,7 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
         ORBB_CUDA(cudaStreamSynchronize(st));
     }
     ORBB_CUDA(cudaStreamSynchronize(h->s_out));
-    ORBB_CUDA(cudaStreamSynchronize(h->s_k2));
+    for (int i = 0; i < 3; i++) ORBB_CUDA(cudaStreamSynchronize(h->s_k[i]));
     ORBB_CUDA(cudaStreamSynchronize(st));
     int ret = ORBB_OK;
     for (int f = 0; f < nframes; f++) {
