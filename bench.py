@@ -224,7 +224,7 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_src = measured_peaks()
     achieved = lvl_bytes * B / (lvl_ms * 1e-3) / 1e9
     traffic = ncu_traffic()
-    roofline = {"kernel": "level_kernel (8 launches per batch: resize+blur+FAST fused per pyramid level)", "bound": "hbm",
+    roofline = {"kernel": "level3_kernel (8 launches per batch: TMA-staged tile -> blur + FAST/NMS + next-level resize, fused per pyramid level)", "bound": "hbm",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "algorithmic_bytes_per_frame": lvl_bytes, "frames_per_launch_sequence": B, "ms_per_launch_sequence": lvl_ms,
                 "traffic": traffic["level_kernel_bytes_per_sequence"] if traffic else None,

@@ -1,10 +1,11 @@
-"""Small fixed workload for ncu: 64-frame C1 batches through the device-resident API, plus one 2 M-row top-2."""
+"""Small fixed workload for ncu: 64-frame C1 batches (--frames N for the bench's 512) through the device-resident API, plus one 2 M-row top-2."""
 import sys, os
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "orb-slam2-annotation_b200")]
 import numpy as np, torch, orbb200
 from synth import synth
 B, W, H, CAP = 64, 640, 480, 1280
+if "--frames" in sys.argv: B = int(sys.argv[sys.argv.index("--frames") + 1])
 frames = torch.from_numpy(np.stack([synth(W, H, 1 + i % 16) for i in range(B)])).cuda()
 ex = orbb200.ORBextractor(1000, max_size=(W, H), max_batch=B)
 kps = torch.zeros((B, CAP, 7), device="cuda"); desc = torch.zeros((B, CAP, 32), dtype=torch.uint8, device="cuda"); cnt = torch.zeros(B, dtype=torch.int32, device="cuda")
