@@ -31,7 +31,7 @@ struct orbx_handle {
     int nlevels;
     cudaStream_t stream = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;      // copy streams of the host-buffer batch pipeline
-    cudaStream_t s_k[3] = {nullptr, nullptr, nullptr};  // extra kernel streams: chunks rotate over stream + these (latency-bound tails overlap the next chunk)
+    cudaStream_t s_k[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // extra kernel streams: chunks rotate over stream + these (latency-bound tails overlap the next chunk)
     int n_kstreams = 2;
     std::vector<cudaEvent_t> ev_in, ev_done;          // per chunk: frames landed in HBM / results ready
     // ORBextractor tables (ORBextractor.cpp:417-448, :456-471)
@@ -321,8 +321,8 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
-    for (int i = 0; i < 3; i++) ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_k[i], cudaStreamNonBlocking));
-    if (const char* e = getenv("ORBB_KSTREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 4) h->n_kstreams = v; }
+    for (int i = 0; i < 7; i++) ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_k[i], cudaStreamNonBlocking));
+    if (const char* e = getenv("ORBB_KSTREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 8) h->n_kstreams = v; }
     ok(dev_alloc(&h->d_pyr, B * h->cap_pyr)); ok(dev_alloc(&h->d_blur, B * h->cap_pyr));
     ok(dev_alloc(&h->d_rec, B * h->cap_rec)); ok(dev_alloc(&h->d_pts, 2 * B * h->cap_rec));
     ok(dev_alloc(&h->d_nodes, B * h->cap_node)); ok(dev_alloc(&h->d_iscr, B * h->cap_node * ISCR_PER_NODE));
@@ -358,7 +358,7 @@ extern "C" int orbx_destroy(orbx_handle* h)
     for (cudaEvent_t e : h->ev_done) cudaEventDestroy(e);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
-    for (int i = 0; i < 3; i++) if (h->s_k[i]) cudaStreamDestroy(h->s_k[i]);
+    for (int i = 0; i < 7; i++) if (h->s_k[i]) cudaStreamDestroy(h->s_k[i]);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBB_OK;
@@ -590,11 +590,34 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     // ---- three-stage pipeline over chunks of frames: H2D (s_in) -> kernels (stream) -> D2H (s_out) ----
     ORBB_CUDA(cudaStreamSynchronize(st));       // an earlier asynchronous device-API call may still be reading the level-0 slots
     const int CH = pipeline_chunk(w, ht);
-    const int nchunks = ceil_div(nframes, CH);
+    // chunk schedule: full chunks in the middle, shorter ones at both ends (the first kernels start sooner, and less work is
+    // left when the last input copy lands)
+    std::vector<int> cstart;
+    {
+        static const int ramp = getenv("ORBB_RAMP") ? atoi(getenv("ORBB_RAMP")) : 1;
+        std::vector<int> head, tail;
+        int left = nframes;
+        if (ramp && nframes >= 4 * CH && CH >= 8) {
+            head = {CH / 4, CH / 2}; tail = {CH / 2, CH / 4};
+            if (ramp >= 2) { head = {CH / 4, CH / 4, CH / 2}; tail = {CH / 2, CH / 4, CH / 4}; }
+            for (int v : head) left -= v;
+            for (int v : tail) left -= v;
+        }
+        int f = 0;
+        for (int v : head) { cstart.push_back(f); f += v; }
+        const int nmid = ceil_div(left, CH);
+        for (int i = 0; i < nmid; i++) { cstart.push_back(f); f += (left - i * CH < CH ? left - i * CH : CH); }
+        for (int v : tail) { cstart.push_back(f); f += v; }
+        cstart.push_back(nframes);
+    }
+    const int nchunks = (int)cstart.size() - 1;
+    static const bool trace = getenv("ORBB_TRACE") != nullptr;      // debugging aid: per-chunk timeline on stderr
+    static cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+    if (trace && !ev_t0) { cudaEventCreate(&ev_t0); cudaEventCreate(&ev_t1); }
     while ((int)h->ev_in.size() < nchunks) {
         cudaEvent_t e1, e2;
-        ORBB_CUDA(cudaEventCreateWithFlags(&e1, cudaEventDisableTiming));
-        ORBB_CUDA(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+        ORBB_CUDA(cudaEventCreateWithFlags(&e1, trace ? cudaEventDefault : cudaEventDisableTiming));
+        ORBB_CUDA(cudaEventCreateWithFlags(&e2, trace ? cudaEventDefault : cudaEventDisableTiming));
         h->ev_in.push_back(e1); h->ev_done.push_back(e2);
     }
     const bool prof = h->profiling;      // per-kernel-class event timing needs the whole batch in one enqueue
@@ -604,8 +627,9 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     const bool tight = (w % 16) == 0 && (size_t)w * ht <= (size_t)g0.pitch * g0.h;
     const size_t dpitch0 = tight ? (size_t)w : (size_t)g0.pitch;
     const bool packed = tight && (!pinned || (stride == (size_t)w && (nframes == 1 || fstride >= (size_t)w * ht)));
+    if (trace) cudaEventRecord(ev_t0, h->s_in);
     for (int c = 0; c < nchunks; c++) {
-        const int f0 = c * CH, nf = nframes - f0 < CH ? nframes - f0 : CH;
+        const int f0 = cstart[c], nf = cstart[c + 1] - f0;
         if (!pinned) {         // stage through pinned memory so the copy is truly asynchronous
             for (int f = f0; f < f0 + nf; f++) {
                 const uint8_t* src = imgs_host + (size_t)f * fstride;
@@ -633,7 +657,7 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     }
     // every input copy is queued before the first kernel: the copy engine never waits for the host to finish launching a chunk
     for (int c = 0; c < nchunks && !prof; c++) {
-        const int f0 = c * CH, nf = nframes - f0 < CH ? nframes - f0 : CH;
+        const int f0 = cstart[c], nf = cstart[c + 1] - f0;
         const int ks = c % h->n_kstreams;
         cudaStream_t kst = ks ? h->s_k[ks - 1] : st;
         ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
@@ -656,8 +680,18 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
         ORBB_CUDA(cudaMemcpyAsync(ddst, h->d_desc, (size_t)32 * nframes * devcap, cudaMemcpyDeviceToHost, st));
         ORBB_CUDA(cudaStreamSynchronize(st));
     }
+    if (trace) cudaEventRecord(ev_t1, h->s_out);
     ORBB_CUDA(cudaStreamSynchronize(h->s_out));
-    for (int i = 0; i < 3; i++) ORBB_CUDA(cudaStreamSynchronize(h->s_k[i]));
+    for (int i = 0; i < 7; i++) ORBB_CUDA(cudaStreamSynchronize(h->s_k[i]));
+    if (trace && !prof) {
+        float t = 0.f, u = 0.f;
+        for (int c = 0; c < nchunks; c++) {
+            cudaEventElapsedTime(&t, ev_t0, h->ev_in[c]); cudaEventElapsedTime(&u, ev_t0, h->ev_done[c]);
+            fprintf(stderr, "[orbb trace] chunk %2d frames %3d..%3d  h2d done %.3f ms  kernels done %.3f ms\n", c, cstart[c], cstart[c + 1], t, u);
+        }
+        cudaEventElapsedTime(&t, ev_t0, ev_t1);
+        fprintf(stderr, "[orbb trace] results on host %.3f ms\n", t);
+    }
     ORBB_CUDA(cudaStreamSynchronize(st));
     int ret = ORBB_OK;
     for (int f = 0; f < nframes; f++) {
