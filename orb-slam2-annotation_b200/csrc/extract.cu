@@ -32,7 +32,12 @@ struct orbx_handle {
     cudaStream_t stream = nullptr;
     cudaStream_t s_in = nullptr, s_out = nullptr;      // copy streams of the host-buffer batch pipeline
     cudaStream_t s_k[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // extra kernel streams: chunks rotate over stream + these (latency-bound tails overlap the next chunk)
-    int n_kstreams = 2;
+    int n_kstreams = 4;
+    // per kernel stream: a side stream on which the octree of level L runs while the main stream works on levels L+1..
+    cudaStream_t s_side[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_side[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::vector<cudaEvent_t> ev_lvl[8];
+    bool oct_overlap = true;
     std::vector<cudaEvent_t> ev_in, ev_done;          // per chunk: frames landed in HBM / results ready
     // ORBextractor tables (ORBextractor.cpp:417-448, :456-471)
     float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS], sigma2[ORBB_MAX_LEVELS], inv_sigma2[ORBB_MAX_LEVELS];
@@ -322,6 +327,11 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
     ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
     for (int i = 0; i < 7; i++) ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_k[i], cudaStreamNonBlocking));
+    for (int i = 0; i < 8; i++) {
+        ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_side[i], cudaStreamNonBlocking));
+        ORBB_CUDA(cudaEventCreateWithFlags(&h->ev_side[i], cudaEventDisableTiming));
+    }
+    if (getenv("ORBB_NO_OCT_OVERLAP")) h->oct_overlap = false;
     if (const char* e = getenv("ORBB_KSTREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 8) h->n_kstreams = v; }
     ok(dev_alloc(&h->d_pyr, B * h->cap_pyr)); ok(dev_alloc(&h->d_blur, B * h->cap_pyr));
     ok(dev_alloc(&h->d_rec, B * h->cap_rec)); ok(dev_alloc(&h->d_pts, 2 * B * h->cap_rec));
@@ -359,6 +369,11 @@ extern "C" int orbx_destroy(orbx_handle* h)
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
     for (int i = 0; i < 7; i++) if (h->s_k[i]) cudaStreamDestroy(h->s_k[i]);
+    for (int i = 0; i < 8; i++) {
+        if (h->s_side[i]) cudaStreamDestroy(h->s_side[i]);
+        if (h->ev_side[i]) cudaEventDestroy(h->ev_side[i]);
+        for (cudaEvent_t e : h->ev_lvl[i]) cudaEventDestroy(e);
+    }
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBB_OK;
@@ -383,7 +398,7 @@ extern "C" int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_sc
 // desc_dev / counts_dev address frame 0 of the batch; every per-frame scratch buffer of the handle is indexed the same way, so
 // chunks of one batch can be enqueued independently (orbx_extract_batch pipelines them against the host copies).
 static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int nframes, int w, int ht, size_t stride, size_t fstride,
-                           orbx_keypoint* kps_dev0, uint8_t* desc_dev0, int32_t* counts_dev0, int capacity, cudaStream_t on_stream = nullptr)
+                           orbx_keypoint* kps_dev0, uint8_t* desc_dev0, int32_t* counts_dev0, int capacity, int slot = 0, bool side_octree = true)
 {
     if (w != h->cur_w || ht != h->cur_h) {
         int rc = setup_geometry(h, w, ht, false);
@@ -393,7 +408,16 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         h->cur_w = w; h->cur_h = ht;
     }
     const int nl = h->nlevels;
-    cudaStream_t st = on_stream ? on_stream : h->stream;
+    cudaStream_t st = slot ? h->s_k[slot - 1] : h->stream;
+    cudaStream_t side = h->s_side[slot];
+    // the octree of a level only needs that level's FAST records: it runs beside the next levels' kernels (not while profiling:
+    // the per-kernel-class event times are taken with the classes back to back)
+    const bool overlap = h->oct_overlap && side_octree && !h->profiling;
+    while ((int)h->ev_lvl[slot].size() < nl) {
+        cudaEvent_t e;
+        ORBB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->ev_lvl[slot].push_back(e);
+    }
     const size_t F0 = (size_t)f0;
     const uint8_t* imgs_dev = imgs_dev0 + F0 * fstride;
     orbx_keypoint* kps_dev = kps_dev0 + F0 * capacity; uint8_t* desc_dev = desc_dev0 + F0 * capacity * 32; int32_t* counts_dev = counts_dev0 + F0;
@@ -404,6 +428,17 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
     int* const d_rec_count = h->d_rec_count + F0 * nl; int* const d_out_count = h->d_out_count + F0 * nl; int* const d_status = h->d_status + F0;
     ORBB_CUDA(cudaMemsetAsync(d_rec_count, 0, sizeof(int) * (size_t)nframes * nl, st));
     ORBB_CUDA(cudaMemsetAsync(d_status, 0, sizeof(int) * (size_t)nframes, st));
+    OctArgs oa;
+    memset(&oa, 0, sizeof oa);
+    oa.geom = h->d_geom; oa.nlevels = nl; oa.iniTh = h->cfg.ini_th_fast;
+    oa.rec = d_rec; oa.rec_fstride = (long long)h->rec_total; oa.rec_count = d_rec_count;
+    oa.pts = d_pts; oa.pts_fstride = 2 * (long long)h->rec_total;
+    oa.nodes = d_nodes; oa.nodes_fstride = (long long)h->node_total;
+    oa.iscr = d_iscr; oa.iscr_fstride = (long long)h->node_total * ISCR_PER_NODE;
+    oa.cellflag = d_cellflag; oa.cellflag_fstride = (long long)h->cell_total;
+    oa.node_off = h->d_node_off; oa.cell_off = h->d_cell_off;
+    oa.out = d_out; oa.out_fstride = (long long)h->out_total;
+    oa.out_count = d_out_count; oa.status = d_status;
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[0], st));
     for (int l = 0; l < nl; l++) {
         const LevelGeom& g = h->geom[l];
@@ -452,22 +487,21 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
                                                        (long long)h->pyr_fstride, n.w, n.h, a.xt, a.yt);
             ORBB_LAUNCHED();
         }
+        if (overlap) {
+            ORBB_CUDA(cudaEventRecord(h->ev_lvl[slot][l], st));
+            ORBB_CUDA(cudaStreamWaitEvent(side, h->ev_lvl[slot][l], 0));
+            oa.level0 = l;
+            octree_kernel<<<dim3(1, nframes), NTO, 0, side>>>(oa);
+            ORBB_LAUNCHED();
+        }
     }
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[1], st));
-    {
-        OctArgs a;
-        memset(&a, 0, sizeof a);
-        a.geom = h->d_geom; a.nlevels = nl; a.iniTh = h->cfg.ini_th_fast;
-        a.rec = d_rec; a.rec_fstride = (long long)h->rec_total; a.rec_count = d_rec_count;
-        a.pts = d_pts; a.pts_fstride = 2 * (long long)h->rec_total;
-        a.nodes = d_nodes; a.nodes_fstride = (long long)h->node_total;
-        a.iscr = d_iscr; a.iscr_fstride = (long long)h->node_total * ISCR_PER_NODE;
-        a.cellflag = d_cellflag; a.cellflag_fstride = (long long)h->cell_total;
-        a.node_off = h->d_node_off; a.cell_off = h->d_cell_off;
-        a.out = d_out; a.out_fstride = (long long)h->out_total;
-        a.out_count = d_out_count; a.status = d_status;
-        octree_kernel<<<dim3(nl, nframes), NTO, 0, st>>>(a);
+    if (!overlap) {
+        octree_kernel<<<dim3(nl, nframes), NTO, 0, st>>>(oa);
         ORBB_LAUNCHED();
+    } else {
+        ORBB_CUDA(cudaEventRecord(h->ev_side[slot], side));
+        ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_side[slot], 0));
     }
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[2], st));
     {
@@ -661,7 +695,7 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
         const int ks = c % h->n_kstreams;
         cudaStream_t kst = ks ? h->s_k[ks - 1] : st;
         ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
-        const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, kst);
+        const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, ks, false);   // chunks already overlap each other: side octrees only add launches
         if (rc != ORBB_OK) return rc;
         ORBB_CUDA(cudaEventRecord(h->ev_done[c], kst));
         ORBB_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));

@@ -32,7 +32,7 @@ constexpr int NTO = 256;
 constexpr int BIG_NODE = 512;
 
 struct OctArgs {
-    const LevelGeom* geom; int nlevels; int iniTh;
+    const LevelGeom* geom; int nlevels; int iniTh; int level0;     // the CTA's level = level0 + blockIdx.x
     const uint32_t* rec; long long rec_fstride; const int* rec_count;
     uint32_t* pts; long long pts_fstride;          // per level: 2 * rec_cap  (points + partition temp)
     uint4* nodes; long long nodes_fstride;         // per level: node_cap       {x0|y0<<16, x1|y1<<16, begin, count}
@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(NTO) octree_kernel(const __grid_constant__ Oct
     __shared__ int s_root[256];
     __shared__ int s_n, s_misc[8];
 
-    const int L = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int L = a.level0 + blockIdx.x, f = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const LevelGeom g = a.geom[L];
     int* out_count = a.out_count + (long long)f * a.nlevels + L;
     int nraw = a.rec_count[(long long)f * a.nlevels + L];
