@@ -124,6 +124,17 @@ int orbx_debug_stage(orbx_handle* h, int frame, int level, int stage, void* dst_
  * a[i], b[i] of 32-byte descriptors (host pointers). */
 int orbm_distance_pairs(const uint8_t* a_host, const uint8_t* b_host, int n, int32_t* out_host, int device);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cpp:302-380), batched over map points.
+ * Map point p owns the descriptor rows [offsets[p], offsets[p+1]) of `desc` (32 B each): the rows of its observations, in
+ * the order the caller walks mObservations.  best_row[p] = index, relative to offsets[p], of the row whose median Hamming
+ * distance to the point's rows (itself included, median = sorted[int(0.5*(N-1))], :361-365) is smallest, first row on
+ * ties (:368); -1 for a point without rows (the reference returns early, :316-317, :330-331).  best_median may be NULL.
+ * The _device form takes device pointers (desc 16-byte aligned) and a cudaStream_t and does not synchronise. */
+int orbm_distinctive_descriptors(const uint8_t* desc_host, const int64_t* offsets_host, int npoints,
+                                 int32_t* best_row_host, int32_t* best_median_host, int device);
+int orbm_distinctive_descriptors_device(const uint8_t* desc_dev, const int64_t* offsets_dev, int npoints,
+                                        int32_t* best_row_dev, int32_t* best_median_dev, void* stream);
+
 /* A Frame's matching state on the device: undistorted keypoints (mvKeysUn), descriptors (mDescriptors) and the
  * 64x48 bucket grid of Frame::AssignFeaturesToGrid / PosInGrid (Frame.cpp:241-257, :434-444), built on device
  * in insertion order.  Bounds are Frame::mnMinX/mnMinY/mnMaxX/mnMaxY. */

@@ -80,6 +80,14 @@ void orc_distance_pairs(const uint8_t* a, const uint8_t* b, int n, int* out)
 {
     for (int i = 0; i < n; i++) out[i] = DescriptorDistance(a + (size_t)i * 32, b + (size_t)i * 32);
 }
+void orc_distinctive(const uint8_t* desc, const int64_t* off, int npoints, int32_t* best_row, int32_t* best_median)
+{
+    for (int p = 0; p < npoints; p++) {
+        int med = -1;
+        best_row[p] = DistinctiveDescriptor(desc + (size_t)off[p] * 32, (int)(off[p + 1] - off[p]), &med);
+        best_median[p] = med;
+    }
+}
 void orc_bf_top2(const uint8_t* db, long M, const uint8_t* q, int nq, int32_t* d1, int64_t* i1, int32_t* d2, int nthreads)
 {
     if (nthreads <= 1) { bf_top2(db, M, q, nq, d1, i1, d2); return; }

@@ -3,6 +3,7 @@
 // CPU restatement of the Hamming-matching half of the hot path.  Reference files followed:
 //   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :474-590 :1506-1659 :1792-1854
 //   ORB-SLAM2/src/Frame.cpp       :241-257 :379-444 :540-748
+//   ORB-SLAM2/src/MapPoint.cpp    :302-380 (ComputeDistinctiveDescriptors)
 // ORBmatcher.cpp / Frame.cpp cannot be compiled here (they pull in KeyFrame/MapPoint/DBoW2/OpenCV/Eigen),
 // and the reference has no tests or golden vectors for them: parity for this half is "unpinned" beyond
 // DescriptorDistance (checked against numpy popcount) and hand-built known-answer cases in tests/.
@@ -33,6 +34,32 @@ static inline int DescriptorDistance(const uint8_t* a, const uint8_t* b)
         dist += (((v + (v >> 4)) & 0xF0F0F0F) * 0x1010101) >> 24;
     }
     return dist;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors (MapPoint.cpp:302-380) on the N descriptor rows of one map point: the float
+// distance matrix (:340-352), the per-row sort of the distances as ints and the median vDists[0.5*(N-1)] (:358-365),
+// first smallest median wins (:368-372).  Returns the winning row, -1 when the point has no rows (:316-317, :330-331).
+static inline int DistinctiveDescriptor(const uint8_t* rows, int N, int* median_out)
+{
+    if (N <= 0) { if (median_out) *median_out = -1; return -1; }
+    std::vector<std::vector<float> > Distances(N, std::vector<float>(N, 0));
+    for (int i = 0; i < N; i++) {
+        Distances[i][i] = 0;
+        for (int j = i + 1; j < N; j++) {
+            int distij = DescriptorDistance(rows + (size_t)i * 32, rows + (size_t)j * 32);
+            Distances[i][j] = distij;
+            Distances[j][i] = distij;
+        }
+    }
+    int BestMedian = INT_MAX, BestIdx = 0;
+    for (int i = 0; i < N; i++) {
+        std::vector<int> vDists(Distances[i].begin(), Distances[i].end());
+        std::sort(vDists.begin(), vDists.end());
+        int median = vDists[0.5 * (N - 1)];
+        if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+    }
+    if (median_out) *median_out = BestMedian;
+    return BestIdx;
 }
 
 // Frame grid (Frame.cpp:241-257, :434-444; constructor lines :115-116 for the inverse cell sizes)

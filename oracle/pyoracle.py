@@ -61,6 +61,7 @@ def lib():
         L.orc_fast.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.orc_fast_atan2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_distance_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_distinctive.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_bf_top2.argtypes = [C.c_void_p, C.c_long, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_frame_create.restype = C.c_void_p
         L.orc_frame_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
@@ -172,6 +173,17 @@ def distance_pairs(a, b):
     out = np.zeros(a.shape[0], np.int32)
     lib().orc_distance_pairs(_p(a), _p(b), a.shape[0], _p(out))
     return out
+
+
+def distinctive_descriptors(desc, offsets):
+    """MapPoint::ComputeDistinctiveDescriptors per CSR segment -> (best_row, best_median)."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    n = offsets.size - 1
+    row = np.zeros(n, np.int32)
+    med = np.zeros(n, np.int32)
+    lib().orc_distinctive(_p(desc), _p(offsets), n, _p(row), _p(med))
+    return row, med
 
 
 def bf_top2(db, q, nthreads=1):

@@ -50,6 +50,43 @@ extern "C" int orbm_distance_pairs(const uint8_t* a_host, const uint8_t* b_host,
     return ORBB_OK;
 }
 
+// ---- MapPoint::ComputeDistinctiveDescriptors, batched (MapPoint.cpp:302-380) --------------------------
+extern "C" int orbm_distinctive_descriptors_device(const uint8_t* desc_dev, const int64_t* offsets_dev, int npoints,
+                                                   int32_t* best_row_dev, int32_t* best_median_dev, void* stream)
+{
+    if (npoints < 0 || (npoints > 0 && (!desc_dev || !offsets_dev || !best_row_dev))) return ORBB_E_INVALID;
+    if (npoints == 0) return ORBB_OK;
+    if (((uintptr_t)desc_dev & 15) != 0) return ORBB_E_INVALID;
+    distinctive_kernel<<<ceil_div(npoints, DD_WARPS), 32 * DD_WARPS, 0, (cudaStream_t)stream>>>(
+        (const uint4*)desc_dev, (const long long*)offsets_dev, npoints, best_row_dev, best_median_dev);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    return ORBB_OK;
+}
+
+extern "C" int orbm_distinctive_descriptors(const uint8_t* desc_host, const int64_t* offsets_host, int npoints,
+                                            int32_t* best_row_host, int32_t* best_median_host, int device)
+{
+    if (npoints < 0 || (npoints > 0 && (!offsets_host || !best_row_host))) return ORBB_E_INVALID;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    if (npoints == 0) return ORBB_OK;
+    for (int p = 0; p < npoints; p++) if (offsets_host[p + 1] < offsets_host[p]) return ORBB_E_INVALID;
+    if (offsets_host[0] < 0) return ORBB_E_INVALID;
+    const int64_t nrows = offsets_host[npoints];
+    if (nrows > 0 && !desc_host) return ORBB_E_INVALID;
+    DevBuf d, o, r, m;
+    if ((rc = d.alloc((size_t)nrows * 32)) || (rc = o.alloc((size_t)(npoints + 1) * 8)) || (rc = r.alloc((size_t)npoints * 4)) ||
+        (rc = m.alloc((size_t)npoints * 4))) return rc;
+    if (nrows > 0) ORBB_CUDA(cudaMemcpy(d.p, desc_host, (size_t)nrows * 32, cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(o.p, offsets_host, (size_t)(npoints + 1) * 8, cudaMemcpyHostToDevice));
+    rc = orbm_distinctive_descriptors_device(d.as<uint8_t>(), o.as<int64_t>(), npoints, r.as<int32_t>(), m.as<int32_t>(), nullptr);
+    if (rc != ORBB_OK) return rc;
+    ORBB_CUDA(cudaMemcpy(best_row_host, r.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost));
+    if (best_median_host) ORBB_CUDA(cudaMemcpy(best_median_host, m.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost));
+    return ORBB_OK;
+}
+
 // ---- frame -------------------------------------------------------------------------------------------
 struct orbm_frame {
     int device = 0, n = 0;

@@ -29,6 +29,55 @@ __global__ void hamming_pairs_kernel(const uint4* __restrict__ a, const uint4* _
 }
 
 // ------------------------------------------------------------------------------------------------------
+// MapPoint::ComputeDistinctiveDescriptors (MapPoint.cpp:302-380), batched over map points: one warp per point.
+// Point p owns rows [off[p], off[p+1]) (its observations).  For row i the reference sorts the N distances of row i
+// (d(i,i) = 0 included) and takes element int(0.5*(N-1)); the row with the smallest such median wins, first row on ties.
+// The k-th smallest of a row is found by bisection on the value (9 counting passes over the point's rows, which sit in
+// shared memory for N <= DD_SMEM_ROWS); rows are spread over the lanes, the winner is a packed-key min reduction.
+// ------------------------------------------------------------------------------------------------------
+constexpr int DD_WARPS = 8, DD_SMEM_ROWS = 64;
+
+__global__ void __launch_bounds__(32 * DD_WARPS) distinctive_kernel(const uint4* __restrict__ desc, const long long* __restrict__ off, int npoints,
+                                                                    int* __restrict__ best_row, int* __restrict__ best_median)
+{
+    __shared__ uint4 rows_s[DD_WARPS][DD_SMEM_ROWS * 2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int p = blockIdx.x * DD_WARPS + warp;
+    if (p >= npoints) return;
+    const long long b = off[p];
+    const long long N64 = off[p + 1] - b;
+    if (N64 <= 0) { if (lane == 0) { best_row[p] = -1; if (best_median) best_median[p] = -1; } return; }
+    const int N = (int)N64;
+    const uint4* rows = desc + 2 * b;
+    const bool staged = N <= DD_SMEM_ROWS;
+    if (staged) {
+        for (int i = lane; i < 2 * N; i += 32) rows_s[warp][i] = rows[i];
+        __syncwarp();
+        rows = rows_s[warp];
+    }
+    const int k = (int)(0.5 * (N - 1));                      // vDists[0.5*(N-1)]
+    unsigned long long best = ~0ull;                         // median << 32 | row
+    for (int i = lane; i < N; i += 32) {
+        const uint4 a0 = rows[2 * i], a1 = rows[2 * i + 1];
+        int lo = 0, hi = 256;                                // smallest v with #{j : d(i,j) <= v} >= k + 1
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int c = 0;
+            for (int j = 0; j < N; j++) c += hamming256(a0, a1, rows[2 * j], rows[2 * j + 1]) <= mid;
+            if (c >= k + 1) hi = mid; else lo = mid + 1;
+        }
+        const unsigned long long key = ((unsigned long long)lo << 32) | (unsigned)i;
+        best = key < best ? key : best;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long t = __shfl_xor_sync(0xffffffffu, best, o);
+        best = t < best ? t : best;
+    }
+    if (lane == 0) { best_row[p] = (int)(best & 0xffffffffu); if (best_median) best_median[p] = (int)(best >> 32); }
+}
+
+// ------------------------------------------------------------------------------------------------------
 // Frame grid
 // ------------------------------------------------------------------------------------------------------
 struct FrameDev {

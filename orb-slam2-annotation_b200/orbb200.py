@@ -25,7 +25,7 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 # every symbol include/orbb200.h declares (tests check the .so exports all of them)
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
            "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
-           "orbm_distance_pairs", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
+           "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
@@ -73,6 +73,8 @@ def lib():
         L.orbx_pyramid_level.argtypes = [vp, i32, i32, vp, sz, C.POINTER(i32), C.POINTER(i32)]
         L.orbx_debug_stage.argtypes = [vp, i32, i32, i32, vp, sz, C.POINTER(sz)]
         L.orbm_distance_pairs.argtypes = [vp, vp, i32, vp, i32]
+        L.orbm_distinctive_descriptors.argtypes = [vp, vp, i32, vp, vp, i32]
+        L.orbm_distinctive_descriptors_device.argtypes = [vp, vp, i32, vp, vp, vp]
         L.orbm_frame_create.argtypes = [C.POINTER(vp), vp, vp, i32, f32, f32, f32, f32, i32]
         L.orbm_frame_destroy.argtypes = [vp]
         L.orbm_window_search.argtypes = [vp, vp, i32, vp, vp, vp, i32]
@@ -268,6 +270,18 @@ def DescriptorDistance(a, b, device=0):
     out = np.zeros(a.shape[0], np.int32)
     _check(lib().orbm_distance_pairs(_p(a), _p(b), a.shape[0], _p(out), device), "orbm_distance_pairs")
     return out
+
+
+def distinctive_descriptors(desc, offsets, device=0):
+    """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cpp:302-380) for a batch of map points in CSR form:
+    rows offsets[p]..offsets[p+1] of desc are point p's observed descriptors.  Returns (best_row, best_median)."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    offsets = np.ascontiguousarray(offsets, np.int64)
+    n = offsets.size - 1
+    row = np.zeros(max(n, 0), np.int32); med = np.zeros(max(n, 0), np.int32)
+    _check(lib().orbm_distinctive_descriptors(_p(desc) if desc.size else None, _p(offsets), n, _p(row), _p(med), device),
+           "orbm_distinctive_descriptors")
+    return row, med
 
 
 class FrameMatcher:

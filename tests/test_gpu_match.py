@@ -230,3 +230,75 @@ def test_bf_top2_full_size_properties(gpu):
     sel = np.array([0, 1, 2, 3, 500, 1999])
     o1, oi, o2 = pyoracle.bf_top2(dbh, qh[sel], nthreads=8)
     assert np.array_equal(d1[sel], o1) and np.array_equal(i1[sel], oi) and np.array_equal(d2[sel], o2)
+
+
+def _map_point_rows(rng, sizes):
+    """CSR descriptor rows: each map point's observations are noisy copies of a base descriptor (plus some outliers)."""
+    rows, off = [], [0]
+    for n in sizes:
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        for i in range(n):
+            r = base.copy()
+            if rng.random() < 0.15:
+                r = rng.integers(0, 256, 32, dtype=np.uint8)                   # a wrong association
+            else:
+                flips = rng.integers(0, 256, int(rng.integers(0, 40)))
+                for b in flips:
+                    r[b >> 3] ^= np.uint8(1 << (b & 7))
+            rows.append(r)
+        off.append(off[-1] + n)
+    desc = np.stack(rows) if rows else np.zeros((0, 32), np.uint8)
+    return desc, np.asarray(off, np.int64)
+
+
+def _numpy_distinctive(desc, off):
+    """Independent restatement: full distance matrix, np.sort, element int(0.5*(N-1)), first argmin."""
+    bits = np.unpackbits(desc, axis=1).astype(np.int32)
+    row, med = [], []
+    for p in range(len(off) - 1):
+        b = bits[off[p]:off[p + 1]]
+        n = len(b)
+        if n == 0:
+            row.append(-1); med.append(-1); continue
+        d = (b[:, None, :] != b[None, :, :]).sum(2)
+        m = np.sort(d, axis=1)[:, int(0.5 * (n - 1))]
+        row.append(int(np.argmin(m))); med.append(int(m.min()))
+    return np.asarray(row, np.int32), np.asarray(med, np.int32)
+
+
+def test_distinctive_descriptors(gpu):
+    """MapPoint::ComputeDistinctiveDescriptors, batched (SURVEY 8(f)-3): oracle, numpy and GPU agree bit-exactly,
+    including empty points, single rows, ties (duplicate rows) and points larger than the shared-memory staging."""
+    import orbb200, pyoracle
+    rng = np.random.default_rng(17)
+    sizes = [0, 1, 2, 3, 4, 5, 7, 8, 31, 32, 33, 63, 64, 65, 100, 0, 200] + [int(x) for x in rng.integers(1, 30, 400)]
+    desc, off = _map_point_rows(rng, sizes)
+    # ties: a point made of identical rows, and one with two identical clusters
+    dup = np.repeat(desc[5:6], 6, 0)
+    two = np.concatenate([np.repeat(desc[9:10], 3, 0), np.repeat(desc[20:21], 3, 0)])
+    desc = np.concatenate([desc, dup, two]); off = np.concatenate([off, [off[-1] + 6, off[-1] + 12]])
+    want_row, want_med = pyoracle.distinctive_descriptors(desc, off)
+    np_row, np_med = _numpy_distinctive(desc, off)
+    assert np.array_equal(want_row, np_row) and np.array_equal(want_med, np_med)
+    got_row, got_med = orbb200.distinctive_descriptors(desc, off)
+    assert np.array_equal(got_row, want_row)
+    assert np.array_equal(got_med, want_med)
+    assert got_row[0] == -1 and got_row[1] == 0 and got_row[-2] == 0
+    # no points at all
+    r, m = orbb200.distinctive_descriptors(np.zeros((0, 32), np.uint8), np.zeros(1, np.int64))
+    assert len(r) == 0
+
+
+def test_distinctive_descriptors_map_scale(gpu):
+    """A map's worth of points (50 k points, ~8 observations each) against the oracle."""
+    import orbb200, pyoracle
+    rng = np.random.default_rng(23)
+    sizes = rng.integers(2, 15, 50_000)
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    base = rng.integers(0, 256, (len(sizes), 32), dtype=np.uint8)
+    desc = np.repeat(base, sizes, axis=0)
+    noise = (rng.random((len(desc), 32, 8)) < 0.06)
+    desc ^= np.packbits(noise, axis=2).reshape(len(desc), 32)
+    want_row, want_med = pyoracle.distinctive_descriptors(desc, off)
+    got_row, got_med = orbb200.distinctive_descriptors(desc, off)
+    assert np.array_equal(got_row, want_row) and np.array_equal(got_med, want_med)
