@@ -91,6 +91,18 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, in
                        size_t stride_bytes, size_t frame_stride_bytes,
                        orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity);
 
+/* Colour frames in front of the extractor: Tracking::GrabImageStereo / RGBD / Monocular convert with
+ * cv::cvtColor(CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) before calling ORBextractor::operator()
+ * (src/Tracking.cpp:202-227, :233-250, :264-281).  channels = 3 or 4 (alpha ignored), rgb_order = mbRGB (1: R first,
+ * 0: B first); arithmetic of OpenCV 4.x: (R*9798 + G*19235 + B*3735 + 2^14) >> 15.
+ * orbx_extract_batch_color = the conversion on the device followed by orbx_extract_batch (stride / fstride in bytes of the
+ * colour frames; everything else as orbx_extract_batch).  orbx_cvt_gray_device converts device frames on a cudaStream_t. */
+int orbx_extract_batch_color(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int h_,
+                             size_t stride_bytes, size_t frame_stride_bytes, int channels, int rgb_order,
+                             orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity);
+int orbx_cvt_gray_device(const uint8_t* src_dev, int nframes, int w, int h_, size_t src_stride, size_t src_frame_stride,
+                         int channels, int rgb_order, uint8_t* dst_dev, size_t dst_stride, size_t dst_frame_stride, void* stream);
+
 /* Blocks until the handle's stream is idle; returns the first asynchronous error, and ORBB_E_CAPACITY if an
  * internal candidate buffer overflowed during the last extraction. */
 int orbx_sync(orbx_handle* h);

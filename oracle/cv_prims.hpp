@@ -12,6 +12,8 @@
 //   cv::FAST(cell, th, true)     :818-825   -> fast9_16_nms
 //   cv::fastAtan2                :105       -> fast_atan2
 //   cvRound                      :83,117-122,1128 -> cv_round
+// and, for the SURVEY 8(f)-4 "next" row (ORB-SLAM2/src/Tracking.cpp:202-227, 233-250, 264-281):
+//   cv::cvtColor RGB/BGR/RGBA/BGRA -> GRAY    -> cvt_gray_u8
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -27,6 +29,25 @@ static inline int cv_round(double v) { return (int)std::nearbyint(v); }
 static inline int cv_round(float v) { return (int)std::nearbyintf(v); }
 static inline int cv_floor(double v) { int i = (int)v; return i - (i > v); }
 static inline int cv_ceil(double v) { int i = (int)v; return i + (i < v); }
+
+// ---------------------------------------------------------------------------------------
+// cv::cvtColor(src, dst, CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) for 8-bit images (OpenCV 4.x
+// imgproc/color_rgb: RGB2Gray<uchar>, 15-bit fixed point): gray = (R*9798 + G*19235 + B*3735 + 2^14) >> 15; alpha ignored.
+// Checked against cv2 4.13 on all 2^24 colours (tests/golden/cv2_cvtcolor.npz holds the digest).
+// ---------------------------------------------------------------------------------------
+static inline void cvt_gray_u8(const uint8_t* src, int w, int h, size_t sstride, int channels, bool rgb_order,
+                               uint8_t* dst, size_t dstride)
+{
+    const int RY = 9798, GY = 19235, BY = 3735, shift = 15;
+    for (int y = 0; y < h; y++) {
+        const uint8_t* s = src + (size_t)y * sstride;
+        uint8_t* d = dst + (size_t)y * dstride;
+        for (int x = 0; x < w; x++, s += channels) {
+            const int r = rgb_order ? s[0] : s[2], g = s[1], b = rgb_order ? s[2] : s[0];
+            d[x] = (uint8_t)((r * RY + g * GY + b * BY + (1 << (shift - 1))) >> shift);
+        }
+    }
+}
 
 // ---------------------------------------------------------------------------------------
 // cv::resize(src, dst, dsize, 0, 0, INTER_LINEAR) for CV_8UC1 (OpenCV imgproc/resize.cpp:

@@ -58,6 +58,7 @@ def lib():
         L.orc_level_kps.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.orc_resize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int]
         L.orc_blur.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_cvt_gray.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.orc_fast.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.orc_fast_atan2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orc_distance_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -142,6 +143,15 @@ def resize(src, dw, dh):
     dst = np.zeros((dh, dw), np.uint8)
     lib().orc_resize(_p(src), src.shape[1], src.shape[0], _p(dst), dw, dh)
     return dst
+
+
+def cvt_gray(src, rgb_order=True):
+    """cv::cvtColor RGB/BGR/RGBA/BGRA -> GRAY of an (h, w, 3|4) u8 image."""
+    src = np.ascontiguousarray(src, np.uint8)
+    h, w, ch = src.shape
+    out = np.zeros((h, w), np.uint8)
+    lib().orc_cvt_gray(_p(src), w, h, ch, 1 if rgb_order else 0, _p(out))
+    return out
 
 
 def blur(src, legacy=False):

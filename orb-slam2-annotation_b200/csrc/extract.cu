@@ -65,6 +65,7 @@ struct orbx_handle {
     orbx_keypoint* d_kps = nullptr;
     // pinned staging
     uint8_t *h_img = nullptr, *h_desc = nullptr;
+    uint8_t* d_color = nullptr;          // colour frames of orbx_extract_batch_color (allocated on first use)
     orbx_keypoint* h_kps = nullptr;
     int *h_counts = nullptr, *h_status = nullptr;
     // optional per-kernel timing (bench.py roofline): events around each kernel class
@@ -358,7 +359,7 @@ extern "C" int orbx_destroy(orbx_handle* h)
     if (!h) return ORBB_E_INVALID;
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    cudaFree(h->d_pyr); cudaFree(h->d_blur); cudaFree(h->d_rec); cudaFree(h->d_pts); cudaFree(h->d_nodes);
+    cudaFree(h->d_color); cudaFree(h->d_pyr); cudaFree(h->d_blur); cudaFree(h->d_rec); cudaFree(h->d_pts); cudaFree(h->d_nodes);
     cudaFree(h->d_iscr); cudaFree(h->d_cellflag); cudaFree(h->d_out); cudaFree(h->d_rec_count); cudaFree(h->d_out_count);
     cudaFree(h->d_status); cudaFree(h->d_counts); cudaFree(h->d_tab); cudaFree(h->d_tiles); cudaFree(h->d_geom);
     cudaFree(h->d_node_off); cudaFree(h->d_cell_off); cudaFree(h->d_kps); cudaFree(h->d_desc);
@@ -585,18 +586,27 @@ static int pipeline_chunk(int w, int ht)
     return c;
 }
 
-extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
-                                  size_t fstride, orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity)
+// Host-buffer batch pipeline.  channels == 1: grey frames (the reference's operator() input).  channels == 3 | 4: colour frames,
+// converted on the device like Tracking::GrabImage* does with cv::cvtColor before the extractor runs (Tracking.cpp:202-227).
+static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
+                              size_t fstride, int channels, int rgb_order, orbx_keypoint* kps_host, uint8_t* desc_host,
+                              int32_t* counts_host, int capacity)
 {
     if (!h || !counts_host || capacity < 0 || (capacity > 0 && (!kps_host || !desc_host))) return ORBB_E_INVALID;
+    if (channels != 1 && channels != 3 && channels != 4) return ORBB_E_INVALID;
+    const size_t CH_ = (size_t)channels;
     if (nframes < 1 || nframes > h->cfg.max_batch) return ORBB_E_INVALID;
     if (w == 0 || ht == 0 || !imgs_host) {              // empty image: silent return (ORBextractor.cpp:1056-1057)
         for (int f = 0; f < nframes; f++) counts_host[f] = 0;
         return ORBB_OK;
     }
-    if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w) return ORBB_E_BAD_SHAPE;
+    if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w * CH_) return ORBB_E_BAD_SHAPE;
     ORBB_CUDA(cudaSetDevice(h->cfg.device));
     cudaStream_t st = h->stream;
+    if (channels > 1 && !h->d_color) {      // colour landing buffer, allocated on first use
+        const int rc = dev_alloc(&h->d_color, (size_t)h->cfg.max_batch * h->cfg.max_width * h->cfg.max_height * 4);
+        if (rc != ORBB_OK) return rc;
+    }
     // H2D straight into the level-0 slots of the pyramid (pitch = geom[0].pitch)
     if (w != h->cur_w || ht != h->cur_h) {
         int rc = setup_geometry(h, w, ht, false);
@@ -664,6 +674,19 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     if (trace) cudaEventRecord(ev_t0, h->s_in);
     for (int c = 0; c < nchunks; c++) {
         const int f0 = cstart[c], nf = cstart[c + 1] - f0;
+        if (channels > 1) {    // colour frames land packed in d_color (pageable sources are staged by the driver)
+            const size_t fbytes = (size_t)w * ht * CH_;
+            if (stride == (size_t)w * CH_ && (nframes == 1 || fstride >= fbytes)) {
+                ORBB_CUDA(cudaMemcpy2DAsync(h->d_color + (size_t)f0 * fbytes, fbytes, imgs_host + (size_t)f0 * fstride,
+                                            nf > 1 ? fstride : fbytes, fbytes, nf, cudaMemcpyHostToDevice, h->s_in));
+            } else {
+                for (int f = f0; f < f0 + nf; f++)
+                    ORBB_CUDA(cudaMemcpy2DAsync(h->d_color + (size_t)f * fbytes, (size_t)w * CH_, imgs_host + (size_t)f * fstride, stride,
+                                                (size_t)w * CH_, ht, cudaMemcpyHostToDevice, h->s_in));
+            }
+            ORBB_CUDA(cudaEventRecord(h->ev_in[c], h->s_in));
+            continue;
+        }
         if (!pinned) {         // stage through pinned memory so the copy is truly asynchronous
             for (int f = f0; f < f0 + nf; f++) {
                 const uint8_t* src = imgs_host + (size_t)f * fstride;
@@ -695,6 +718,12 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
         const int ks = c % h->n_kstreams;
         cudaStream_t kst = ks ? h->s_k[ks - 1] : st;
         ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
+        if (channels > 1) {
+            const size_t fbytes = (size_t)w * ht * CH_;
+            cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nf), 128, 0, kst>>>(h->d_color + (size_t)f0 * fbytes, (long long)((size_t)w * CH_), (long long)fbytes,
+                w, channels, rgb_order, h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
+            ORBB_LAUNCHED();
+        }
         const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, ks, false);   // chunks already overlap each other: side octrees only add launches
         if (rc != ORBB_OK) return rc;
         ORBB_CUDA(cudaEventRecord(h->ev_done[c], kst));
@@ -706,6 +735,12 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
     }
     if (prof) {
         ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_in[nchunks - 1], 0));
+        if (channels > 1) {
+            const size_t fbytes = (size_t)w * ht * CH_;
+            cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nframes), 128, 0, st>>>(h->d_color, (long long)((size_t)w * CH_), (long long)fbytes,
+                w, channels, rgb_order, h->d_pyr + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
+            ORBB_LAUNCHED();
+        }
         const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
         if (rc != ORBB_OK) return rc;
         ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
@@ -740,6 +775,32 @@ extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int 
         }
     }
     return ret;
+}
+
+extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
+                                  size_t fstride, orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity)
+{
+    return extract_batch_impl(h, imgs_host, nframes, w, ht, stride, fstride, 1, 0, kps_host, desc_host, counts_host, capacity);
+}
+
+extern "C" int orbx_extract_batch_color(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
+                                        size_t fstride, int channels, int rgb_order, orbx_keypoint* kps_host, uint8_t* desc_host,
+                                        int32_t* counts_host, int capacity)
+{
+    if (channels != 3 && channels != 4) return ORBB_E_INVALID;
+    return extract_batch_impl(h, imgs_host, nframes, w, ht, stride, fstride, channels, rgb_order ? 1 : 0, kps_host, desc_host, counts_host, capacity);
+}
+
+extern "C" int orbx_cvt_gray_device(const uint8_t* src_dev, int nframes, int w, int ht, size_t src_stride, size_t src_fstride,
+                                    int channels, int rgb_order, uint8_t* dst_dev, size_t dst_stride, size_t dst_fstride, void* stream)
+{
+    if (!src_dev || !dst_dev || nframes < 1 || (channels != 3 && channels != 4)) return ORBB_E_INVALID;
+    if (w < 1 || ht < 1 || src_stride < (size_t)w * channels || dst_stride < (size_t)w) return ORBB_E_BAD_SHAPE;
+    cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nframes), 128, 0, (cudaStream_t)stream>>>(src_dev, (long long)src_stride, (long long)src_fstride,
+        w, channels, rgb_order ? 1 : 0, dst_dev, (long long)dst_stride, (long long)dst_fstride);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    return ORBB_OK;
 }
 
 extern "C" int orbx_extract(orbx_handle* h, const uint8_t* img_host, int w, int ht, size_t stride,

@@ -22,6 +22,44 @@ __constant__ int c_umax[16];          // circular patch row ends (ORBextractor.c
 __constant__ float c_atan[4];         // fastAtan2 polynomial p1,p3,p5,p7 (already scaled to degrees)
 
 // =====================================================================================================
+// cv::cvtColor RGB/BGR/RGBA/BGRA -> GRAY as Tracking::GrabImage* applies it in front of the extractor (Tracking.cpp:202-227,
+// SURVEY 8(f)-4).  OpenCV 4.x 15-bit fixed point: (R*9798 + G*19235 + B*3735 + 2^14) >> 15.  A thread converts four pixels:
+// word loads when the source row allows, one 32-bit store.  HBM-bound: 3-4 bytes read, 1 written per pixel.
+// =====================================================================================================
+__device__ __forceinline__ unsigned cvt_gray_px(unsigned c0, unsigned c1, unsigned c2, int rgb)
+{
+    const unsigned r = rgb ? c0 : c2, b = rgb ? c2 : c0;
+    return (r * 9798u + c1 * 19235u + b * 3735u + 16384u) >> 15;
+}
+
+__global__ void __launch_bounds__(128) cvt_gray_kernel(const uint8_t* __restrict__ src, long long spitch, long long sfstride, int w, int ch, int rgb,
+                                                       uint8_t* __restrict__ dst, long long dpitch, long long dfstride)
+{
+    const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x), y = blockIdx.y, f = blockIdx.z;
+    if (x >= w) return;
+    const uint8_t* s = src + (long long)f * sfstride + (long long)y * spitch + (long long)x * ch;
+    uint8_t* d = dst + (long long)f * dfstride + (long long)y * dpitch + x;
+    const int n = min(4, w - x);
+    unsigned g[4] = {0u, 0u, 0u, 0u};
+    if (n == 4 && ch == 4 && ((uintptr_t)s & 15) == 0) {
+        const uint4 v = *reinterpret_cast<const uint4*>(s);
+        const unsigned p[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) g[i] = cvt_gray_px(p[i] & 255u, (p[i] >> 8) & 255u, (p[i] >> 16) & 255u, rgb);
+    } else if (n == 4 && ch == 3 && ((uintptr_t)s & 3) == 0) {
+        const unsigned a = *reinterpret_cast<const unsigned*>(s), b = *reinterpret_cast<const unsigned*>(s + 4), c = *reinterpret_cast<const unsigned*>(s + 8);
+        g[0] = cvt_gray_px(a & 255u, (a >> 8) & 255u, (a >> 16) & 255u, rgb);
+        g[1] = cvt_gray_px(a >> 24, b & 255u, (b >> 8) & 255u, rgb);
+        g[2] = cvt_gray_px((b >> 16) & 255u, b >> 24, c & 255u, rgb);
+        g[3] = cvt_gray_px((c >> 8) & 255u, (c >> 16) & 255u, c >> 24, rgb);
+    } else {
+        for (int i = 0; i < n; i++) g[i] = cvt_gray_px(s[i * ch], s[i * ch + 1], s[i * ch + 2], rgb);
+    }
+    if (n == 4 && ((uintptr_t)d & 3) == 0) *reinterpret_cast<unsigned*>(d) = g[0] | (g[1] << 8) | (g[2] << 16) | (g[3] << 24);
+    else for (int i = 0; i < n; i++) d[i] = (uint8_t)g[i];
+}
+
+// =====================================================================================================
 // Octree distribution (ORBextractor.cpp:541-770).  Order-free formulation: the reference's result depends on the
 // keypoint ORDER only through "first maximum wins" inside a leaf (:751-767); since vKeys order is always the
 // cell-row-major / pixel-row-major input order (stable partitions, :512-528), the winner is the max-response point

@@ -10,6 +10,10 @@ pinned against outputs of the real implementations, generated here and committed
   ref_extract.npz the reference's own ORBextractor.cpp, compiled unmodified from /root/reference (oracle/_ref), run on
                   seeded synthetic frames: full keypoint + descriptor output, pyramid checksums.
 
+  cv2_cvtcolor.npz  cv2.cvtColor RGB/BGR/RGBA/BGRA -> GRAY (Tracking.cpp:202-227, the SURVEY 8(f)-4 row): a small seeded image
+                  per code plus the sha256 of the gray image of all 2^24 RGB colours.  (python make_golden.py --cvtcolor
+                  regenerates only this file.)
+
 Inputs are regenerated from seeds by synth.py (numpy only), so only outputs are stored.  Usage: python tests/golden/make_golden.py
 """
 import hashlib
@@ -50,6 +54,28 @@ def atan_inputs():
     y[:8] = [0, 0, 1, -1, 5, -5, 0, 3]
     x[:8] = [0, 1, 0, 0, 5, 5, -7, -3]
     return y, x
+
+
+def color_inputs():
+    rng = np.random.default_rng(77)
+    return rng.integers(0, 256, (29, 37, 3), dtype=np.uint8), rng.integers(0, 256, (31, 41, 4), dtype=np.uint8)
+
+
+def all_colours():
+    c = np.arange(1 << 24, dtype=np.uint32)
+    return np.stack([(c >> 16) & 255, (c >> 8) & 255, c & 255], 1).astype(np.uint8).reshape(4096, 4096, 3)
+
+
+def main_cvtcolor():
+    import cv2
+    c3, c4 = color_inputs()
+    out = {"cv2_version": np.array(cv2.__version__),
+           "rgb2gray": cv2.cvtColor(c3, cv2.COLOR_RGB2GRAY), "bgr2gray": cv2.cvtColor(c3, cv2.COLOR_BGR2GRAY),
+           "rgba2gray": cv2.cvtColor(c4, cv2.COLOR_RGBA2GRAY), "bgra2gray": cv2.cvtColor(c4, cv2.COLOR_BGRA2GRAY),
+           "all_rgb_sha": np.array(hashlib.sha256(cv2.cvtColor(all_colours(), cv2.COLOR_RGB2GRAY).tobytes()).hexdigest()),
+           "all_bgr_sha": np.array(hashlib.sha256(cv2.cvtColor(all_colours(), cv2.COLOR_BGR2GRAY).tobytes()).hexdigest())}
+    np.savez_compressed(os.path.join(HERE, "cv2_cvtcolor.npz"), **out)
+    print("cv2_cvtcolor.npz", os.path.getsize(os.path.join(HERE, "cv2_cvtcolor.npz")), "bytes")
 
 
 def main():
@@ -106,4 +132,6 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "--cvtcolor" not in sys.argv:
+        main()
+    main_cvtcolor()

@@ -203,3 +203,61 @@ def test_odd_shapes(gpu, w, h):
     for f in ("x", "y", "size", "response", "octave"):
         assert np.array_equal(k[f], ok[f]), f
     assert np.any(d != od, axis=1).sum() <= max(1, 0.001 * len(d))
+
+
+def _colour_frames(F, w, h, ch, seed):
+    """Colour frames whose channels are differently textured (so the channel order matters)."""
+    from synth import synth
+    out = np.zeros((F, h, w, ch), np.uint8)
+    for f in range(F):
+        for c in range(ch):
+            out[f, :, :, c] = synth(w, h, seed + 10 * f + c)
+    return out
+
+
+@pytest.mark.parametrize("w,h,ch", [(640, 480, 3), (640, 480, 4), (203, 177, 3), (201, 99, 4)])
+def test_colour_frames(gpu, w, h, ch):
+    """SURVEY 8(f)-4: cv::cvtColor (Tracking.cpp:202-227) fused in front of the extractor.  The device conversion is bit-exact
+    against the oracle restatement (pinned to cv2 4.13 by tests/golden/cv2_cvtcolor.npz) and the colour entry point returns
+    exactly what the grey entry point returns on the converted frames, for both channel orders."""
+    import torch, orbb200, pyoracle
+    F = 3
+    col = _colour_frames(F, w, h, ch, 300)
+    ex = orbb200.ORBextractor(600, max_size=(w, h), max_batch=F)
+    for rgb in (True, False):
+        grey = np.stack([pyoracle.cvt_gray(col[f], rgb_order=rgb) for f in range(F)])
+        # the stand-alone device conversion
+        d_src = torch.from_numpy(col).cuda()
+        d_dst = torch.zeros((F, h, w), dtype=torch.uint8, device="cuda")
+        rc = orbb200.lib().orbx_cvt_gray_device(d_src.data_ptr(), F, w, h, w * ch, w * h * ch, ch, 1 if rgb else 0,
+                                                d_dst.data_ptr(), w, w * h, None)
+        assert rc == 0
+        torch.cuda.synchronize()
+        assert np.array_equal(d_dst.cpu().numpy(), grey)
+        # colour batch == grey batch of the converted frames
+        want = ex.extract_batch(grey)
+        got = ex.extract_batch_color(col, rgb_order=rgb)
+        for (k1, d1), (k2, d2) in zip(want, got):
+            assert len(k1) > 50 and k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
+    # the two channel orders really differ
+    assert not np.array_equal(pyoracle.cvt_gray(col[0], True), pyoracle.cvt_gray(col[0], False))
+
+
+def test_colour_frames_strided_rows(gpu):
+    """Row-padded colour frames (stride > w*channels) take the per-frame copy path."""
+    import orbb200, pyoracle
+    w, h, ch, F = 320, 240, 3, 2
+    col = _colour_frames(F, w, h, ch, 400)
+    padded = np.zeros((F, h, w * ch + 24), np.uint8)
+    padded[:, :, :w * ch] = col.reshape(F, h, w * ch)
+    ex = orbb200.ORBextractor(500, max_size=(w, h), max_batch=F)
+    kps = np.zeros((F, 800), orbb200.KP_DTYPE); desc = np.zeros((F, 800, 32), np.uint8); cnt = np.zeros(F, np.int32)
+    rc = orbb200.lib().orbx_extract_batch_color(ex.h, padded.ctypes.data, F, w, h, padded.shape[2], padded.shape[1] * padded.shape[2], ch, 1,
+                                                kps.ctypes.data, desc.ctypes.data, cnt.ctypes.data, 800)
+    assert rc == 0
+    want = ex.extract_batch(np.stack([pyoracle.cvt_gray(col[f], True) for f in range(F)]))
+    for f in range(F):
+        assert kps[f, :cnt[f]].tobytes() == want[f][0].tobytes() and np.array_equal(desc[f, :cnt[f]], want[f][1])
+    # invalid channel counts are rejected
+    assert orbb200.lib().orbx_extract_batch_color(ex.h, padded.ctypes.data, F, w, h, padded.shape[2], 0, 2, 1,
+                                                  kps.ctypes.data, desc.ctypes.data, cnt.ctypes.data, 800) != 0
