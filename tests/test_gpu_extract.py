@@ -50,9 +50,12 @@ def test_final_parity(gpu, w, h, nf, seed):
     assert len(ok) == len(gk)
     for f in ("x", "y", "size", "response", "octave", "class_id"):
         assert np.array_equal(ok[f], gk[f]), f
-    assert np.max(np.abs(ok["angle"] - gk["angle"])) <= 1e-3      # tolerance of BASELINE.json north_star
+    # north_star allows 1e-3 deg on angles and 0.1 % differing descriptor rows (float orientation); on these fixed frames the
+    # kernels reproduce the oracle's float arithmetic exactly (ordered _rn operations, no FMA contraction), so assert equality
+    assert np.max(np.abs(ok["angle"] - gk["angle"])) <= 1e-3
+    assert np.array_equal(ok["angle"], gk["angle"]), "angles are bit-equal on the fixed parity frames"
     bad = np.any(od != gd, axis=1).sum()
-    assert bad <= 0.001 * len(od), f"{bad} of {len(od)} descriptors differ (> 0.1 %)"
+    assert bad == 0, f"{bad} of {len(od)} descriptor rows differ"
 
 
 def test_edge_cases(gpu):
