@@ -230,6 +230,37 @@ int orbm_merge_top2_device(const int32_t* d1_all, const int64_t* idx1_all, const
  * Host arrays; accepted[i] = 0/1. */
 int orbm_ratio_test(const int32_t* d1, const int32_t* d2, int nq, int th_low, float ratio, uint8_t* accepted);
 
+/* -- vocabulary (Frame::ComputeBoW) ------------------------------------------------------- */
+
+/* Device image of a DBoW2 vocabulary tree (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:312-336 Node, :1362-1448
+ * loadFromTextFile).  Nodes are given in the loader's order: node 0 is the root, node i >= 1 names parent[i] < i (children are
+ * appended to their parent in this order), is_leaf[i] = the file's nIsLeaf flag (leaves get consecutive word ids, :1432-1439),
+ * desc = n_nodes x 32 B (row 0 unused), weight = the file's weight column (idf).  weighting: 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY
+ * (BowVector.h); norm: what the scoring object's mustNormalize() asks for, 0 none, 1 L1, 2 L2 (ScoringObject.h; ORBvoc.txt is
+ * "10 6 0 0": TF_IDF + L1_NORM -> weighting 0, norm 1).  A leaf flag that disagrees with "has no children" is rejected. */
+typedef struct orbv_vocab orbv_vocab;
+int orbv_vocab_create(orbv_vocab** out, int k, int L, int n_nodes, const int32_t* parent, const uint8_t* is_leaf,
+                      const uint8_t* desc, const double* weight, int weighting, int norm, int device);
+int orbv_vocab_destroy(orbv_vocab* v);
+int orbv_vocab_words(const orbv_vocab* v);
+
+/* TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup) (:1242-1285) for n descriptors: walk down the tree,
+ * at each level the first child with the smallest FORB::distance; node_id = the node reached at level L - levelsup (0 = root
+ * when that level is <= 0, and also when the leaf is reached above that level, where the reference leaves *nid unset).
+ * node_id may be NULL.  The _device form takes device pointers (desc 16-byte aligned) and a cudaStream_t, no synchronisation. */
+int orbv_transform(const orbv_vocab* v, const uint8_t* desc_host, int n, int levelsup,
+                   int32_t* word_id, double* weight, int32_t* node_id);
+int orbv_transform_device(const orbv_vocab* v, const uint8_t* desc_dev, int n, int levelsup,
+                          int32_t* word_id_dev, double* weight_dev, int32_t* node_id_dev, void* stream);
+
+/* transform(features, BowVector&, FeatureVector&, levelsup) (:1151-1218) = Frame::ComputeBoW (src/Frame.cpp:452-459, levelsup 4).
+ * BowVector: n_bow (word id, value) pairs, ids ascending (std::map order), values accumulated and normalised as the reference
+ * does.  FeatureVector: n_fv node ids ascending with CSR offsets into fv_features (feature indices in insertion order).
+ * Capacities: bow_ids/bow_vals/fv_nodes/fv_features n entries, fv_offsets n + 1. */
+int orbv_compute_bow(const orbv_vocab* v, const uint8_t* desc_host, int n, int levelsup,
+                     int32_t* bow_ids, double* bow_vals, int32_t* n_bow,
+                     int32_t* fv_nodes, int32_t* fv_offsets, int32_t* fv_features, int32_t* n_fv);
+
 /* -- misc ------------------------------------------------------------------------------------------- */
 const char* orbb200_strerror(int code);
 const char* orbb200_last_cuda_error(void);

@@ -2,6 +2,7 @@
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline/reference legs may load this.
 #include "orb_extract_oracle.hpp"
 #include "orb_match_oracle.hpp"
+#include "dbow_oracle.hpp"
 #include <chrono>
 #include <thread>
 
@@ -98,6 +99,44 @@ void orc_bf_top2(const uint8_t* db, long M, const uint8_t* q, int nq, int32_t* d
         th.emplace_back([=]() { bf_top2(db, M, q + (size_t)q0 * 32, q1 - q0, d1 + q0, i1 + q0, d2 + q0); });
     }
     for (auto& t : th) t.join();
+}
+
+// ---- DBoW2 vocabulary descent (Frame::ComputeBoW) ---------------------------------------------
+Vocabulary* orc_vocab_create(int k, int L, int n, const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc, const double* weight,
+                             int weighting, int norm)
+{
+    Vocabulary* v = new Vocabulary();
+    v->build(k, L, n, parent, is_leaf, desc, weight);
+    v->weighting = weighting; v->norm = norm;
+    return v;
+}
+void orc_vocab_destroy(Vocabulary* v) { delete v; }
+void orc_vocab_transform(const Vocabulary* v, const uint8_t* feats, int n, int levelsup, int32_t* word_id, double* weight, int32_t* node_id)
+{
+    for (int i = 0; i < n; i++) {
+        int id, nid; double w;
+        v->transform(feats + (size_t)i * 32, id, w, &nid, levelsup);
+        word_id[i] = id; weight[i] = w; node_id[i] = nid;
+    }
+}
+// BowVector as (ids, values) ascending; FeatureVector as CSR (node ids ascending, offsets, feature indices in insertion order)
+void orc_vocab_bow(const Vocabulary* v, const uint8_t* feats, int n, int levelsup, int32_t* bow_ids, double* bow_vals, int32_t* n_bow,
+                   int32_t* fv_nodes, int32_t* fv_off, int32_t* fv_feat, int32_t* n_fv)
+{
+    std::map<unsigned, double> bv;
+    std::map<unsigned, std::vector<unsigned> > fv;
+    v->transform_all(feats, n, levelsup, bv, fv);
+    int i = 0;
+    for (auto& e : bv) { bow_ids[i] = (int32_t)e.first; bow_vals[i] = e.second; i++; }
+    *n_bow = i;
+    int j = 0, pos = 0;
+    fv_off[0] = 0;
+    for (auto& e : fv) {
+        fv_nodes[j] = (int32_t)e.first;
+        for (unsigned f : e.second) fv_feat[pos++] = (int32_t)f;
+        fv_off[++j] = pos;
+    }
+    *n_fv = j;
 }
 
 struct orc_frame { FrameGrid g; std::vector<KeyPoint> kps; std::vector<uint8_t> desc; };

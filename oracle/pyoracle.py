@@ -23,7 +23,7 @@ assert QUERY_DTYPE.itemsize == 72
 def build(force=False):
     so = os.path.join(_HERE, "liborb_oracle.so")
     srcs = [os.path.join(_HERE, f) for f in ("oracle_capi.cpp", "cv_prims.hpp", "orb_extract_oracle.hpp",
-                                              "orb_match_oracle.hpp", "orb_pattern.inc", "Makefile")]
+                                              "orb_match_oracle.hpp", "dbow_oracle.hpp", "orb_pattern.inc", "Makefile")]
     stale = force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
     if stale:
         subprocess.run(["make", "-C", _HERE, "liborb_oracle.so"], check=True, capture_output=True)
@@ -64,6 +64,11 @@ def lib():
         L.orc_distance_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.orc_distinctive.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_bf_top2.argtypes = [C.c_void_p, C.c_long, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_vocab_create.restype = C.c_void_p
+        L.orc_vocab_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.orc_vocab_destroy.argtypes = [C.c_void_p]
+        L.orc_vocab_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_vocab_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7
         L.orc_frame_create.restype = C.c_void_p
         L.orc_frame_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
         L.orc_frame_destroy.argtypes = [C.c_void_p]
@@ -205,6 +210,38 @@ def bf_top2(db, q, nthreads=1):
     d2 = np.zeros(nq, np.int32)
     lib().orc_bf_top2(_p(db), db.shape[0], _p(q), nq, _p(d1), _p(i1), _p(d2), nthreads)
     return d1, i1, d2
+
+
+class OracleVocabulary:
+    """DBoW2 TemplatedVocabulary (tree + transform) on flattened node arrays, nodes in loadFromTextFile order (oracle)."""
+
+    def __init__(self, k, L, parent, is_leaf, desc, weight, weighting=0, norm=1):
+        self.L_ = lib()
+        self.parent = np.ascontiguousarray(parent, np.int32); self.is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        self.desc = np.ascontiguousarray(desc, np.uint8); self.weight = np.ascontiguousarray(weight, np.float64)
+        self.h = self.L_.orc_vocab_create(k, L, len(self.parent), _p(self.parent), _p(self.is_leaf), _p(self.desc), _p(self.weight),
+                                          weighting, norm)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L_.orc_vocab_destroy(self.h)
+            self.h = None
+
+    def transform(self, feats, levelsup=4):
+        feats = np.ascontiguousarray(feats, np.uint8).reshape(-1, 32)
+        n = len(feats)
+        wid = np.zeros(n, np.int32); w = np.zeros(n, np.float64); nid = np.zeros(n, np.int32)
+        self.L_.orc_vocab_transform(self.h, _p(feats), n, levelsup, _p(wid), _p(w), _p(nid))
+        return wid, w, nid
+
+    def bow(self, feats, levelsup=4):
+        """-> (bow_ids, bow_vals, fv_nodes, fv_offsets, fv_features)"""
+        feats = np.ascontiguousarray(feats, np.uint8).reshape(-1, 32)
+        n = len(feats)
+        ids = np.zeros(n, np.int32); vals = np.zeros(n, np.float64); nb = np.zeros(1, np.int32)
+        fn = np.zeros(n, np.int32); fo = np.zeros(n + 1, np.int32); ff = np.zeros(n, np.int32); nf = np.zeros(1, np.int32)
+        self.L_.orc_vocab_bow(self.h, _p(feats), n, levelsup, _p(ids), _p(vals), _p(nb), _p(fn), _p(fo), _p(ff), _p(nf))
+        return ids[:nb[0]].copy(), vals[:nb[0]].copy(), fn[:nf[0]].copy(), fo[:nf[0] + 1].copy(), ff[:fo[nf[0]]].copy()
 
 
 class OracleFrame:

@@ -50,4 +50,11 @@ struct LevelGeom {
     int dxs_off, dys_off;// offsets into the per-tile first-destination-index tables
 };
 
+// ORBmatcher::DescriptorDistance (ORBmatcher.cpp:1838-1854) / FORB::distance (DBoW2/FORB.cpp:82-102) on two 32-byte rows
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
 }  // namespace orbb

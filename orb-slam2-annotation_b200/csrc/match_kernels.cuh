@@ -16,11 +16,6 @@ namespace orbb {
 constexpr int GRID_COLS = 64, GRID_ROWS = 48;      // Frame.h:37-38
 constexpr int TH_HIGH = 100, TH_LOW = 50;          // ORBmatcher.cpp:37-38
 
-__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
-{
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
 
 __global__ void hamming_pairs_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, int* __restrict__ out)
 {

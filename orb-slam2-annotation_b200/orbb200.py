@@ -29,7 +29,8 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "or
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
-           "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak",
+           "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
+           "orbv_compute_bow", "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak",
            "orbb200_launch_count"]
 
 
@@ -78,6 +79,12 @@ def lib():
         L.orbm_distinctive_descriptors.argtypes = [vp, vp, i32, vp, vp, i32]
         L.orbm_distinctive_descriptors_device.argtypes = [vp, vp, i32, vp, vp, vp]
         L.orbm_frame_create.argtypes = [C.POINTER(vp), vp, vp, i32, f32, f32, f32, f32, i32]
+        L.orbv_vocab_create.argtypes = [C.POINTER(vp), i32, i32, i32, vp, vp, vp, vp, i32, i32, i32]
+        L.orbv_vocab_destroy.argtypes = [vp]
+        L.orbv_vocab_words.argtypes = [vp]
+        L.orbv_transform.argtypes = [vp, vp, i32, i32, vp, vp, vp]
+        L.orbv_transform_device.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp]
+        L.orbv_compute_bow.argtypes = [vp, vp, i32, i32] + [vp] * 7
         L.orbm_frame_destroy.argtypes = [vp]
         L.orbm_window_search.argtypes = [vp, vp, i32, vp, vp, vp, i32]
         L.orbm_search_by_projection_points.argtypes = [vp, vp, vp, i32, f32, vp, vp, C.POINTER(i32)]
@@ -296,6 +303,44 @@ def distinctive_descriptors(desc, offsets, device=0):
     _check(lib().orbm_distinctive_descriptors(_p(desc) if desc.size else None, _p(offsets), n, _p(row), _p(med), device),
            "orbm_distinctive_descriptors")
     return row, med
+
+
+class Vocabulary:
+    """Device image of a DBoW2 vocabulary tree; transform() / bow() = TemplatedVocabulary::transform (Frame::ComputeBoW)."""
+
+    def __init__(self, k, L, parent, is_leaf, desc, weight, weighting=0, norm=1, device=0):
+        self.L = lib()
+        self.h = C.c_void_p()
+        parent = np.ascontiguousarray(parent, np.int32); is_leaf = np.ascontiguousarray(is_leaf, np.uint8)
+        desc = np.ascontiguousarray(desc, np.uint8); weight = np.ascontiguousarray(weight, np.float64)
+        _check(self.L.orbv_vocab_create(C.byref(self.h), k, L, len(parent), _p(parent), _p(is_leaf), _p(desc), _p(weight),
+                                        weighting, norm, device), "orbv_vocab_create")
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orbv_vocab_destroy(self.h)
+            self.h = None
+
+    @property
+    def words(self):
+        return self.L.orbv_vocab_words(self.h)
+
+    def transform(self, feats, levelsup=4):
+        feats = np.ascontiguousarray(feats, np.uint8).reshape(-1, 32)
+        n = len(feats)
+        wid = np.zeros(n, np.int32); w = np.zeros(n, np.float64); nid = np.zeros(n, np.int32)
+        _check(self.L.orbv_transform(self.h, _p(feats) if n else None, n, levelsup, _p(wid), _p(w), _p(nid)), "orbv_transform")
+        return wid, w, nid
+
+    def bow(self, feats, levelsup=4):
+        """-> (bow_ids, bow_vals, fv_nodes, fv_offsets, fv_features)"""
+        feats = np.ascontiguousarray(feats, np.uint8).reshape(-1, 32)
+        n = len(feats)
+        ids = np.zeros(max(n, 1), np.int32); vals = np.zeros(max(n, 1), np.float64); nb = np.zeros(1, np.int32)
+        fn = np.zeros(max(n, 1), np.int32); fo = np.zeros(n + 1, np.int32); ff = np.zeros(max(n, 1), np.int32); nf = np.zeros(1, np.int32)
+        _check(self.L.orbv_compute_bow(self.h, _p(feats) if n else None, n, levelsup, _p(ids), _p(vals), _p(nb), _p(fn), _p(fo), _p(ff), _p(nf)),
+               "orbv_compute_bow")
+        return ids[:nb[0]].copy(), vals[:nb[0]].copy(), fn[:nf[0]].copy(), fo[:nf[0] + 1].copy(), ff[:fo[nf[0]]].copy()
 
 
 class FrameMatcher:

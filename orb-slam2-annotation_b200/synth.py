@@ -84,3 +84,44 @@ def synth_queries(db, nq, seed=43, max_flips=60):
             bits[i, pos] ^= 1
     q[:nhit] = np.packbits(bits, axis=1)
     return q
+
+
+def synth_vocabulary(k=10, L=3, seed=9, stop_fraction=0.05, ragged=False):
+    """Seeded DBoW2-style vocabulary tree in loadFromTextFile order: (parent, is_leaf, desc, weight).
+    Children are noisy copies of their parent's descriptor (so the descent is meaningful), leaf weights are positive idf-like
+    doubles, a few leaves are stopped words (weight 0).  ragged=True makes some inner nodes leaves early and varies the fan-out."""
+    rng = np.random.default_rng(seed)
+    parent = [0]; leaf = [0]; desc = [np.zeros(32, np.uint8)]; weight = [0.0]; level = [0]
+    frontier = [0]
+    root_desc = rng.integers(0, 256, 32, dtype=np.uint8)
+    desc[0] = root_desc
+    while frontier:
+        nxt = []
+        for p in frontier:
+            nch = k if not ragged else int(rng.integers(2, k + 1))
+            for _ in range(nch):
+                d = desc[p].copy()
+                nflip = int(rng.integers(8, 48)) if level[p] == 0 else int(rng.integers(4, 28))
+                for b in rng.integers(0, 256, nflip):
+                    d[b >> 3] ^= np.uint8(1 << (b & 7))
+                nid = len(parent)
+                parent.append(p); desc.append(d); level.append(level[p] + 1)
+                is_leaf = level[p] + 1 == L or (ragged and level[p] + 1 >= 2 and rng.random() < 0.15)
+                leaf.append(1 if is_leaf else 0)
+                weight.append(0.0 if not is_leaf else (0.0 if rng.random() < stop_fraction else float(rng.uniform(0.5, 9.5))))
+                if not is_leaf:
+                    nxt.append(nid)
+        frontier = nxt
+    return (np.asarray(parent, np.int32), np.asarray(leaf, np.uint8), np.stack(desc).astype(np.uint8), np.asarray(weight, np.float64))
+
+
+def synth_vocabulary_features(desc, is_leaf, n, seed=10):
+    """Query descriptors: noisy copies of random leaf descriptors plus some fresh random rows."""
+    rng = np.random.default_rng(seed)
+    leaves = np.flatnonzero(is_leaf)
+    out = desc[rng.choice(leaves, n)].copy()
+    noise = rng.random((n, 32, 8)) < 0.05
+    out ^= np.packbits(noise, axis=2).reshape(n, 32)
+    fresh = rng.random(n) < 0.1
+    out[fresh] = rng.integers(0, 256, (int(fresh.sum()), 32), dtype=np.uint8)
+    return out
