@@ -182,6 +182,18 @@ typedef struct orbm_proj_query {
     float angle;            /* LastFrame.mvKeysUn[i].angle, for the rotation histogram (a11)                */
 } orbm_proj_query;
 
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches) (ORBmatcher.cpp:205-348).
+ * desc_kf / desc_f: mDescriptors of the KeyFrame (n_kf rows) and of the Frame (n_f rows); angle_kf = pKF->mvKeysUn[i].angle,
+ * angle_f = F.mvKeys[i].angle (read only when check_ori); kf_has_mp[i] != 0 iff vpMapPointsKF[i] exists and is not bad
+ * (:233-238).  fv_*: the two FeatureVectors as orbv_compute_bow returns them (node ids ascending, CSR offsets, feature
+ * indices).  Output match_f_to_kf[n_f]: the KeyFrame feature whose MapPoint the reference would store in
+ * vpMapPointMatches[i], or -1; *nmatches = the function's return value. */
+int orbm_search_by_bow(const uint8_t* desc_kf, const float* angle_kf, const uint8_t* kf_has_mp, int n_kf,
+                       const int32_t* fv_kf_nodes, const int32_t* fv_kf_off, const int32_t* fv_kf_feat, int nfv_kf,
+                       const uint8_t* desc_f, const float* angle_f, int n_f,
+                       const int32_t* fv_f_nodes, const int32_t* fv_f_off, const int32_t* fv_f_feat, int nfv_f,
+                       float nnratio, int check_orientation, int32_t* match_f_to_kf, int* nmatches, int device);
+
 /* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (ORBmatcher.cpp:63-155): window candidates and
  * distances on the device, then the reference's order-dependent top-2 / level-aware ratio / already-matched loop on
  * the host.  frame_mp[n] (in/out) is F.mvpMapPoints flattened to ids (-1 = none), frame_mp_obs[n] the matched point's

@@ -139,6 +139,24 @@ void orc_vocab_bow(const Vocabulary* v, const uint8_t* feats, int n, int levelsu
     *n_fv = j;
 }
 
+static std::map<unsigned, std::vector<unsigned> > fv_from_csr(const int32_t* nodes, const int32_t* off, const int32_t* feat, int n)
+{
+    std::map<unsigned, std::vector<unsigned> > fv;
+    for (int j = 0; j < n; j++) fv[(unsigned)nodes[j]] = std::vector<unsigned>(feat + off[j], feat + off[j + 1]);
+    return fv;
+}
+int orc_search_by_bow(const uint8_t* descKF, const float* angleKF, const uint8_t* kf_has_mp,
+                      const int32_t* kn, const int32_t* ko, const int32_t* kf, int nk,
+                      const uint8_t* descF, const float* angleF, int FN, const int32_t* fn, const int32_t* fo, const int32_t* ff, int nf,
+                      float nnratio, int check_ori, int32_t* matches)
+{
+    std::vector<int> m;
+    const int n = SearchByBoW(descKF, angleKF, kf_has_mp, fv_from_csr(kn, ko, kf, nk), descF, angleF, FN, fv_from_csr(fn, fo, ff, nf),
+                              nnratio, check_ori != 0, m);
+    for (int i = 0; i < FN; i++) matches[i] = m[i];
+    return n;
+}
+
 struct orc_frame { FrameGrid g; std::vector<KeyPoint> kps; std::vector<uint8_t> desc; };
 orc_frame* orc_frame_create(const KeyPoint* kps, const uint8_t* desc, int n, float minx, float miny, float maxx, float maxy)
 {

@@ -1,7 +1,7 @@
 // oracle/orb_match_oracle.hpp — TEST INFRASTRUCTURE (CPU oracle), never linked into the product.
 //
 // CPU restatement of the Hamming-matching half of the hot path.  Reference files followed:
-//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :474-590 :1506-1659 :1792-1854
+//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :205-348 (SearchByBoW) :474-590 :1506-1659 :1792-1854
 //   ORB-SLAM2/src/Frame.cpp       :241-257 :379-444 :540-748
 //   ORB-SLAM2/src/MapPoint.cpp    :302-380 (ComputeDistinctiveDescriptors)
 // ORBmatcher.cpp / Frame.cpp cannot be compiled here (they pull in KeyFrame/MapPoint/DBoW2/OpenCV/Eigen),
@@ -13,6 +13,7 @@
 #include <cmath>
 #include <climits>
 #include <vector>
+#include <map>
 #include <algorithm>
 #include "orb_extract_oracle.hpp"
 
@@ -125,6 +126,66 @@ static inline void ComputeThreeMaxima(const std::vector<int>* histo, int L, int&
     }
     if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
     else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+}
+
+// ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (ORBmatcher.cpp:205-348) on flattened arrays.
+// FeatureVectors are std::map<NodeId, vector<unsigned>>; kf_has_mp[i] = "vpMapPointsKF[i] && !isBad()"; the result stores the
+// KeyFrame feature index where the reference stores its MapPoint pointer.
+static inline int SearchByBoW(const uint8_t* descKF, const float* angleKF, const uint8_t* kf_has_mp,
+                              const std::map<unsigned, std::vector<unsigned> >& vFeatVecKF,
+                              const uint8_t* descF, const float* angleF, int FN,
+                              const std::map<unsigned, std::vector<unsigned> >& vFeatVecF,
+                              float mfNNratio, bool mbCheckOrientation, std::vector<int>& vpMapPointMatches)
+{
+    vpMapPointMatches.assign(FN, -1);
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    std::map<unsigned, std::vector<unsigned> >::const_iterator KFit = vFeatVecKF.begin(), Fit = vFeatVecF.begin();
+    const std::map<unsigned, std::vector<unsigned> >::const_iterator KFend = vFeatVecKF.end(), Fend = vFeatVecF.end();
+    while (KFit != KFend && Fit != Fend) {
+        if (KFit->first == Fit->first) {
+            const std::vector<unsigned> vIndicesKF = KFit->second;
+            const std::vector<unsigned> vIndicesF = Fit->second;
+            for (size_t iKF = 0; iKF < vIndicesKF.size(); iKF++) {
+                const unsigned realIdxKF = vIndicesKF[iKF];
+                if (!kf_has_mp[realIdxKF]) continue;
+                const uint8_t* dKF = descKF + (size_t)realIdxKF * 32;
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                for (size_t iF = 0; iF < vIndicesF.size(); iF++) {
+                    const unsigned realIdxF = vIndicesF[iF];
+                    if (vpMapPointMatches[realIdxF] >= 0) continue;
+                    const int dist = DescriptorDistance(dKF, descF + (size_t)realIdxF * 32);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = realIdxF; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 <= TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        vpMapPointMatches[bestIdxF] = (int)realIdxKF;
+                        if (mbCheckOrientation) {
+                            float rot = angleKF[realIdxKF] - angleF[bestIdxF];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back(bestIdxF);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            KFit++; Fit++;
+        } else if (KFit->first < Fit->first) KFit = vFeatVecKF.lower_bound(Fit->first);
+        else Fit = vFeatVecF.lower_bound(KFit->first);
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) { vpMapPointMatches[rotHist[i][j]] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
 }
 
 // Brute-force top-2 with the SearchByBoW update rule (ORBmatcher.cpp:249-275): strict '<' updates,

@@ -69,6 +69,7 @@ def lib():
         L.orc_vocab_destroy.argtypes = [C.c_void_p]
         L.orc_vocab_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_vocab_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7
+        L.orc_search_by_bow.argtypes = [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 2 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.orc_frame_create.restype = C.c_void_p
         L.orc_frame_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
         L.orc_frame_destroy.argtypes = [C.c_void_p]
@@ -242,6 +243,19 @@ class OracleVocabulary:
         fn = np.zeros(n, np.int32); fo = np.zeros(n + 1, np.int32); ff = np.zeros(n, np.int32); nf = np.zeros(1, np.int32)
         self.L_.orc_vocab_bow(self.h, _p(feats), n, levelsup, _p(ids), _p(vals), _p(nb), _p(fn), _p(fo), _p(ff), _p(nf))
         return ids[:nb[0]].copy(), vals[:nb[0]].copy(), fn[:nf[0]].copy(), fo[:nf[0] + 1].copy(), ff[:fo[nf[0]]].copy()
+
+
+def search_by_bow(desc_kf, angle_kf, kf_has_mp, fv_kf, desc_f, angle_f, fv_f, nnratio=0.7, check_ori=True):
+    """ORBmatcher::SearchByBoW(KeyFrame, Frame): fv_* = (nodes, offsets, features) -> (matches[F.N] of KF indices, nmatches)."""
+    desc_kf = np.ascontiguousarray(desc_kf, np.uint8); desc_f = np.ascontiguousarray(desc_f, np.uint8)
+    angle_kf = np.ascontiguousarray(angle_kf, np.float32); angle_f = np.ascontiguousarray(angle_f, np.float32)
+    kf_has_mp = np.ascontiguousarray(kf_has_mp, np.uint8)
+    kn, ko, kf = [np.ascontiguousarray(a, np.int32) for a in fv_kf]
+    fn, fo, ff = [np.ascontiguousarray(a, np.int32) for a in fv_f]
+    out = np.zeros(len(desc_f), np.int32)
+    n = lib().orc_search_by_bow(_p(desc_kf), _p(angle_kf), _p(kf_has_mp), _p(kn), _p(ko), _p(kf), len(kn), _p(desc_f), _p(angle_f), len(desc_f),
+                                _p(fn), _p(fo), _p(ff), len(fn), nnratio, 1 if check_ori else 0, _p(out))
+    return out, n
 
 
 class OracleFrame:

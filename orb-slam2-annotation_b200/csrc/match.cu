@@ -293,6 +293,95 @@ extern "C" int orbm_search_by_projection_frame(const orbm_frame* f, const float*
     return ORBB_OK;
 }
 
+// ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (ORBmatcher.cpp:205-348).  The all-pairs distances of the common
+// vocabulary nodes are computed on the device (bow_join_kernel); the scan that skips already matched Frame features (:243-245) is
+// order dependent and runs on the host exactly as written, followed by the rotation histogram (:313-345).
+extern "C" int orbm_search_by_bow(const uint8_t* desc_kf, const float* angle_kf, const uint8_t* kf_has_mp, int n_kf,
+                                  const int32_t* fv_kf_nodes, const int32_t* fv_kf_off, const int32_t* fv_kf_feat, int nfv_kf,
+                                  const uint8_t* desc_f, const float* angle_f, int n_f,
+                                  const int32_t* fv_f_nodes, const int32_t* fv_f_off, const int32_t* fv_f_feat, int nfv_f,
+                                  float nnratio, int check_ori, int32_t* match_f_to_kf, int* nmatches, int device)
+{
+    if (!nmatches || n_kf < 0 || n_f < 0 || nfv_kf < 0 || nfv_f < 0 || (n_f > 0 && !match_f_to_kf)) return ORBB_E_INVALID;
+    if ((n_kf > 0 && (!desc_kf || !kf_has_mp)) || (n_f > 0 && !desc_f) || (check_ori && ((n_kf > 0 && !angle_kf) || (n_f > 0 && !angle_f)))) return ORBB_E_INVALID;
+    if ((nfv_kf > 0 && (!fv_kf_nodes || !fv_kf_off || !fv_kf_feat)) || (nfv_f > 0 && (!fv_f_nodes || !fv_f_off || !fv_f_feat))) return ORBB_E_INVALID;
+    for (int j = 0; j < nfv_kf; j++) {
+        if (fv_kf_off[j + 1] < fv_kf_off[j] || (j > 0 && fv_kf_nodes[j] <= fv_kf_nodes[j - 1])) return ORBB_E_INVALID;
+        for (int t = fv_kf_off[j]; t < fv_kf_off[j + 1]; t++) if (fv_kf_feat[t] < 0 || fv_kf_feat[t] >= n_kf) return ORBB_E_INVALID;
+    }
+    for (int j = 0; j < nfv_f; j++) {
+        if (fv_f_off[j + 1] < fv_f_off[j] || (j > 0 && fv_f_nodes[j] <= fv_f_nodes[j - 1])) return ORBB_E_INVALID;
+        for (int t = fv_f_off[j]; t < fv_f_off[j + 1]; t++) if (fv_f_feat[t] < 0 || fv_f_feat[t] >= n_f) return ORBB_E_INVALID;
+    }
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    *nmatches = 0;
+    for (int i = 0; i < n_f; i++) match_f_to_kf[i] = -1;
+    // common nodes (the two sorted maps are walked together, :224-310) -> join entries for KeyFrame features that carry a good
+    // MapPoint (:233-238)
+    struct Common { int a, b; };
+    std::vector<Common> common;
+    for (int a = 0, b = 0; a < nfv_kf && b < nfv_f;) {
+        if (fv_kf_nodes[a] == fv_f_nodes[b]) { common.push_back({a, b}); a++; b++; }
+        else if (fv_kf_nodes[a] < fv_f_nodes[b]) a++;
+        else b++;
+    }
+    std::vector<int4> entries;
+    long long total = 0;
+    for (const Common& c : common) {
+        const int nB = fv_f_off[c.b + 1] - fv_f_off[c.b];
+        for (int t = fv_kf_off[c.a]; t < fv_kf_off[c.a + 1]; t++) {
+            const int iA = fv_kf_feat[t];
+            if (!kf_has_mp[iA]) continue;
+            if (total + nB > 0x7fffffffLL) return ORBB_E_CAPACITY;
+            entries.push_back(make_int4(iA, fv_f_off[c.b], nB, (int)total));
+            total += nB;
+        }
+    }
+    std::vector<uint16_t> dist((size_t)total);
+    if (!entries.empty() && total > 0) {
+        DevBuf dA, dB, dF, dE, dD;
+        const int nfeatB = fv_f_off[nfv_f];
+        if ((rc = dA.alloc((size_t)n_kf * 32)) || (rc = dB.alloc((size_t)n_f * 32)) || (rc = dF.alloc((size_t)nfeatB * 4)) ||
+            (rc = dE.alloc(entries.size() * sizeof(int4))) || (rc = dD.alloc((size_t)total * 2))) return rc;
+        ORBB_CUDA(cudaMemcpy(dA.p, desc_kf, (size_t)n_kf * 32, cudaMemcpyHostToDevice));
+        ORBB_CUDA(cudaMemcpy(dB.p, desc_f, (size_t)n_f * 32, cudaMemcpyHostToDevice));
+        ORBB_CUDA(cudaMemcpy(dF.p, fv_f_feat, (size_t)nfeatB * 4, cudaMemcpyHostToDevice));
+        ORBB_CUDA(cudaMemcpy(dE.p, entries.data(), entries.size() * sizeof(int4), cudaMemcpyHostToDevice));
+        bow_join_kernel<<<ceil_div((int)entries.size(), 8), 256>>>(dA.as<uint4>(), dB.as<uint4>(), dF.as<int>(), dE.as<int4>(), (int)entries.size(),
+                                                                   dD.as<uint16_t>());
+        ORBB_LAUNCHED();
+        ORBB_CUDA(cudaGetLastError());
+        ORBB_CUDA(cudaMemcpy(dist.data(), dD.p, (size_t)total * 2, cudaMemcpyDeviceToHost));
+    }
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nm = 0;
+    for (const int4& en : entries) {                                                    // entries are in (node, iKF) order
+        int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+        for (int j = 0; j < en.z; j++) {
+            const int realIdxF = fv_f_feat[en.y + j];
+            if (match_f_to_kf[realIdxF] >= 0) continue;                                 // :243-245
+            const int d = dist[(size_t)en.w + j];
+            if (d < bestDist1) { bestDist2 = bestDist1; bestDist1 = d; bestIdxF = realIdxF; }
+            else if (d < bestDist2) bestDist2 = d;
+        }
+        if (bestDist1 <= TH_LOW && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {   // :264-268
+            match_f_to_kf[bestIdxF] = en.x;
+            if (check_ori) rotHist[rot_bin(angle_kf[en.x], angle_f[bestIdxF])].push_back(bestIdxF);
+            nm++;
+        }
+    }
+    if (check_ori) {                                                                    // :313-345
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int b = 0; b < HISTO_LENGTH; b++)
+            if (b != ind1 && b != ind2 && b != ind3)
+                for (size_t j = 0; j < rotHist[b].size(); j++) { match_f_to_kf[rotHist[b][j]] = -1; nm--; }
+    }
+    *nmatches = nm;
+    return ORBB_OK;
+}
+
 extern "C" int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev_xy, int32_t* m12,
                                               int window, float nnratio, int check_ori, int* nmatches)
 {

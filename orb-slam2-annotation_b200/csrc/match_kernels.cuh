@@ -73,6 +73,25 @@ __global__ void __launch_bounds__(32 * DD_WARPS) distinctive_kernel(const uint4*
 }
 
 // ------------------------------------------------------------------------------------------------------
+// Node join of ORBmatcher::SearchByBoW (ORBmatcher.cpp:224-262): features of two frames that fell into the same vocabulary
+// node are compared all-pairs.  One warp per (common node, A feature) entry: lanes run over the node's B features.
+// entry = {iA, first B slot (index into featB), number of B features, output offset}.
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) bow_join_kernel(const uint4* __restrict__ descA, const uint4* __restrict__ descB, const int* __restrict__ featB,
+                                                       const int4* __restrict__ entries, int nentries, uint16_t* __restrict__ dist)
+{
+    const int lane = threadIdx.x & 31;
+    const int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (e >= nentries) return;
+    const int4 en = entries[e];
+    const uint4 a0 = descA[2 * en.x], a1 = descA[2 * en.x + 1];
+    for (int j = lane; j < en.z; j += 32) {
+        const int iB = featB[en.y + j];
+        dist[en.w + j] = (uint16_t)hamming256(a0, a1, descB[2 * iB], descB[2 * iB + 1]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
 // Frame grid
 // ------------------------------------------------------------------------------------------------------
 struct FrameDev {

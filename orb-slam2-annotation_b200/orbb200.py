@@ -26,7 +26,7 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
            "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
-           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization",
+           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
@@ -89,6 +89,7 @@ def lib():
         L.orbm_window_search.argtypes = [vp, vp, i32, vp, vp, vp, i32]
         L.orbm_search_by_projection_points.argtypes = [vp, vp, vp, i32, f32, vp, vp, C.POINTER(i32)]
         L.orbm_search_by_projection_frame.argtypes = [vp, vp, vp, i32, i32, vp, vp, C.POINTER(i32)]
+        L.orbm_search_by_bow.argtypes = [vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, C.POINTER(i32), i32]
         L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, C.POINTER(i32)]
         L.orbm_stereo_match.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, f32, f32, vp, vp]
         L.orbm_db_create.argtypes = [C.POINTER(vp), C.c_int64, C.c_int64, i32]
@@ -291,6 +292,22 @@ def DescriptorDistance(a, b, device=0):
     out = np.zeros(a.shape[0], np.int32)
     _check(lib().orbm_distance_pairs(_p(a), _p(b), a.shape[0], _p(out), device), "orbm_distance_pairs")
     return out
+
+
+def search_by_bow(desc_kf, angle_kf, kf_has_mp, fv_kf, desc_f, angle_f, fv_f, nnratio=0.7, check_ori=True, device=0):
+    """ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...) (ORBmatcher.cpp:205-348): fv_* = (nodes, offsets, features) as
+    Vocabulary.bow() returns them.  -> (matches[F.N]: KeyFrame feature index or -1, nmatches)."""
+    desc_kf = np.ascontiguousarray(desc_kf, np.uint8); desc_f = np.ascontiguousarray(desc_f, np.uint8)
+    angle_kf = np.ascontiguousarray(angle_kf, np.float32); angle_f = np.ascontiguousarray(angle_f, np.float32)
+    kf_has_mp = np.ascontiguousarray(kf_has_mp, np.uint8)
+    kn, ko, kf = [np.ascontiguousarray(a, np.int32) for a in fv_kf]
+    fn, fo, ff = [np.ascontiguousarray(a, np.int32) for a in fv_f]
+    out = np.zeros(len(desc_f), np.int32)
+    n = C.c_int32()
+    _check(lib().orbm_search_by_bow(_p(desc_kf), _p(angle_kf), _p(kf_has_mp), len(desc_kf), _p(kn), _p(ko), _p(kf), len(kn),
+                                    _p(desc_f), _p(angle_f), len(desc_f), _p(fn), _p(fo), _p(ff), len(fn),
+                                    nnratio, 1 if check_ori else 0, _p(out), C.byref(n), device), "orbm_search_by_bow")
+    return out, n.value
 
 
 def distinctive_descriptors(desc, offsets, device=0):

@@ -137,3 +137,85 @@ def test_vocab_create_rejects_inconsistent_trees():
     assert L.orbv_vocab_create(C.byref(h), 2, 2, 4, p(bad_parent), p(leaf), p(desc), p(w), 0, 1, 0) == orbb200.E_INVALID
     assert L.orbv_vocab_create(C.byref(h), 2, 2, 4, p(parent), p(leaf), p(desc), p(w), 7, 1, 0) == orbb200.E_INVALID
     assert L.orbv_vocab_create(C.byref(h), 2, 2, 1, p(parent), p(leaf), p(desc), p(w), 0, 1, 0) == orbb200.E_INVALID
+
+
+def _bow_pair(seed=31, shift=(3, 1), nf=1000):
+    """Two overlapping views extracted with the CPU oracle, a vocabulary trained around their descriptors (k = 8, L = 4),
+    and both FeatureVectors at levelsup = 2."""
+    import pyoracle
+    from synth import synth
+    w, h = 640, 480
+    big = synth(w + 16, h + 16, seed)
+    cur = big[8:8 + h, 8:8 + w].copy()
+    last = big[8 + shift[1]:8 + shift[1] + h, 8 + shift[0]:8 + shift[0] + w].copy()
+    ex = pyoracle.OracleExtractor(nf)
+    kc, dc = ex.extract(cur)
+    kl, dl = ex.extract(last)
+    # a vocabulary whose nodes are real descriptors: k-ary tree by recursive random seeding (deterministic)
+    rng = np.random.default_rng(seed)
+    pool = np.concatenate([dc, dl])
+    k, L = 8, 4
+    parent, leaf, desc, weight = [0], [0], [np.zeros(32, np.uint8)], [0.0]
+    frontier = [(0, np.arange(len(pool)), 0)]
+    while frontier:
+        nxt = []
+        for nid, members, lvl in frontier:
+            centres = pool[rng.choice(members, k, replace=len(members) < k)]
+            d = (np.unpackbits(pool[members][:, None, :] ^ centres[None, :, :], axis=2)).sum(2)
+            assign = d.argmin(1)
+            for c in range(k):
+                cid = len(parent)
+                parent.append(nid); desc.append(centres[c]); is_leaf = lvl + 1 == L
+                leaf.append(1 if is_leaf else 0); weight.append(float(rng.uniform(0.5, 5.0)) if is_leaf else 0.0)
+                sub = members[assign == c]
+                if not is_leaf:
+                    nxt.append((cid, sub if len(sub) else members[:1], lvl + 1))
+        frontier = nxt
+    voc = (k, L, np.asarray(parent, np.int32), np.asarray(leaf, np.uint8), np.stack(desc), np.asarray(weight))
+    return (kc, dc), (kl, dl), voc
+
+
+def test_oracle_search_by_bow_properties():
+    """The SearchByBoW restatement: every match joins two features of the same node, passes TH_LOW, and no Frame feature is
+    used twice; with all map points bad nothing matches."""
+    import pyoracle
+    (kc, dc), (kl, dl), (k, L, parent, leaf, desc, weight) = _bow_pair()
+    voc = pyoracle.OracleVocabulary(k, L, parent, leaf, desc, weight)
+    fv_kf = voc.bow(dl, 2)[2:]
+    fv_f = voc.bow(dc, 2)[2:]
+    has = np.ones(len(dl), np.uint8)
+    m, n = pyoracle.search_by_bow(dl, kl["angle"], has, fv_kf, dc, kc["angle"], fv_f, 0.7, True)
+    assert n == int((m >= 0).sum()) and n > 100
+    node_of_kf = np.full(len(dl), -1); node_of_f = np.full(len(dc), -1)
+    for j, node in enumerate(fv_kf[0]):
+        node_of_kf[fv_kf[2][fv_kf[1][j]:fv_kf[1][j + 1]]] = node
+    for j, node in enumerate(fv_f[0]):
+        node_of_f[fv_f[2][fv_f[1][j]:fv_f[1][j + 1]]] = node
+    idx = np.flatnonzero(m >= 0)
+    assert np.array_equal(node_of_f[idx], node_of_kf[m[idx]])
+    assert np.all(np.unpackbits(dc[idx] ^ dl[m[idx]], axis=1).sum(1) <= 50)
+    assert len(set(m[idx].tolist())) == len(idx)                      # a KeyFrame feature matches at most one Frame feature
+    m0, n0 = pyoracle.search_by_bow(dl, kl["angle"], np.zeros(len(dl), np.uint8), fv_kf, dc, kc["angle"], fv_f, 0.7, True)
+    assert n0 == 0 and np.all(m0 == -1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("check_ori,ratio", [(True, 0.7), (False, 0.9), (True, 0.6)])
+def test_gpu_search_by_bow(gpu, check_ori, ratio):
+    import orbb200, pyoracle
+    (kc, dc), (kl, dl), (k, L, parent, leaf, desc, weight) = _bow_pair()
+    voc = orbb200.Vocabulary(k, L, parent, leaf, desc, weight)
+    orc = pyoracle.OracleVocabulary(k, L, parent, leaf, desc, weight)
+    fv_kf = voc.bow(dl, 2)[2:]
+    fv_f = voc.bow(dc, 2)[2:]
+    for a, b in zip(fv_kf, orc.bow(dl, 2)[2:]):
+        assert np.array_equal(a, b)
+    rng = np.random.default_rng(5)
+    has = (rng.random(len(dl)) < 0.8).astype(np.uint8)                # some features without a (good) MapPoint
+    want, nw = pyoracle.search_by_bow(dl, kl["angle"], has, fv_kf, dc, kc["angle"], fv_f, ratio, check_ori)
+    got, ng = orbb200.search_by_bow(dl, kl["angle"], has, fv_kf, dc, kc["angle"], fv_f, ratio, check_ori)
+    assert ng == nw and np.array_equal(got, want) and ng > 50
+    # empty feature vectors: no matches, no device work
+    e = (np.zeros(0, np.int32), np.zeros(1, np.int32), np.zeros(0, np.int32))
+    g0, n0 = orbb200.search_by_bow(dl, kl["angle"], has, e, dc, kc["angle"], fv_f, ratio, check_ori)
+    assert n0 == 0 and np.all(g0 == -1)
