@@ -568,7 +568,7 @@ __device__ __forceinline__ void od_load_rows(unsigned (&w)[NIT], const uint8_t* 
 
 __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __grid_constant__ DescArgs a)
 {
-    __shared__ uint32_t patch_s[OD_WARPS][3 * OD_PIT * OD_PW + 2];
+    __shared__ __align__(16) uint32_t patch_s[OD_WARPS][2][3 * OD_PIT * OD_PW + 2];      // two windows per warp: one in use, one in flight
     __shared__ uint32_t absu_s[40];            // |u0+b| packed per byte, indexed by u0 + 18
     const int f = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x < 40) {
@@ -683,31 +683,34 @@ __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __g
 #pragma unroll
     for (int i = 0; i < 16; i++) { px[i] = (float)c_pattern[lane * 32 + 2 * i]; py[i] = (float)c_pattern[lane * 32 + 2 * i + 1]; }
     uint8_t* dout = a.desc + ((long long)f * a.capacity + base) * 32 + lane;
-    uint32_t* ps = patch_s[warp];
-    const uint8_t* pb = reinterpret_cast<const uint8_t*>(ps);
     const int r3 = lane / OD_PW, wc = lane - r3 * OD_PW;           // lanes 30, 31 carry no item
     const bool lane_ok = lane < 3 * OD_PW;
-    unsigned wn[OD_PIT]; int con = 0; float cjn = 0.f, sjn = 0.f;
-    // request keypoint j's blurred window: rows cy-18 .. cy+18, aligned words from (cx-18) & ~3 (the blurred levels are
-    // pitch-aligned buffers of this library)
-    auto request = [&](int j) {
+    int con = 0; float cjn = 0.f, sjn = 0.f;
+    // request keypoint j's blurred window into buffer `buf`: rows cy-18 .. cy+20, aligned words from (cx-18) & ~3 (the blurred
+    // levels are pitch-aligned buffers of this library), global -> shared directly (LDGSTS), one commit group per window
+    auto request = [&](int j, int buf) {
         const uint8_t* bb = (const uint8_t*)__shfl_sync(0xffffffffu, (unsigned long long)bimg, j);
         const int p = __shfl_sync(0xffffffffu, bpitch, j), cx = __shfl_sync(0xffffffffu, kx, j), cy = __shfl_sync(0xffffffffu, ky, j);
         cjn = __shfl_sync(0xffffffffu, ca, j); sjn = __shfl_sync(0xffffffffu, sb, j);
         const int xs = (cx - 18) & ~3;
         con = 18 * (4 * OD_PW) + (cx - xs);                         // window centre inside the staged rows
-        od_load_rows<OD_PIT>(wn, bb + (long long)(cy - 18 + r3) * p + xs + 4 * wc, 3u * (unsigned)p);
-    };
-    request(0);
-    for (int j = 0; j < nvalid; j++) {
-        __syncwarp();                                                   // the previous keypoint's reads are done
         if (lane_ok) {
+            const uint8_t* q = bb + (long long)(cy - 18 + r3) * p + xs + 4 * wc;
+            const unsigned p3 = 3u * (unsigned)p;
+            const unsigned sa = (unsigned)__cvta_generic_to_shared(&patch_s[warp][buf][lane]);
 #pragma unroll
-            for (int it = 0; it < OD_PIT; it++) ps[it * (3 * OD_PW) + lane] = wn[it];
+            for (int it = 0; it < OD_PIT; it++)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + 4u * (unsigned)(it * 3 * OD_PW)), "l"(q + (unsigned long long)it * p3) : "memory");
         }
-        const uint8_t* c = pb + con; const float cj = cjn, sj = sjn;
-        __syncwarp();
-        if (j + 1 < nvalid) request(j + 1);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    request(0, 0);
+    for (int j = 0; j < nvalid; j++) {
+        const uint8_t* c = reinterpret_cast<const uint8_t*>(patch_s[warp][j & 1]) + con;
+        const float cj = cjn, sj = sjn;
+        if (j + 1 < nvalid) { request(j + 1, (j + 1) & 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();                                                   // every lane's part of window j has landed
         int val = 0;
 #pragma unroll
         for (int b = 0; b < 8; b++) {
@@ -719,6 +722,7 @@ __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __g
             val |= (t0 < t1) << b;
         }
         dout[j * 32] = (uint8_t)val;
+        __syncwarp();                                                   // window j is free for request j + 2
     }
 }
 
