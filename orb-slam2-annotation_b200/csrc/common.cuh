@@ -35,6 +35,7 @@ struct LevelGeom {
     int pitch;           // row pitch in bytes inside the pyramid / blur buffers (multiple of 128)
     size_t off;          // byte offset of this level inside one frame's pyramid (and blur) block
     int nCols, nRows, wCell, hCell;   // FAST cell grid (ORBextractor.cpp:781-795); nCols==0 => no FAST on this level
+    unsigned magicW, magicH;          // ceil(2^32 / wCell), ceil(2^32 / hCell): x / wCell == __umulhi(x, magicW) for x < 2^16
     int nIni;            // octree roots (ORBextractor.cpp:545)
     float hX;            // root width as float
     int quota;           // mnFeaturesPerLevel[L]

@@ -137,6 +137,7 @@ static int setup_geometry(orbx_handle* h, int w, int ht, bool allocate_only)
         g.nCols = nCols; g.nRows = nRows;
         g.wCell = nCols ? (int)ceilf(width / nCols) : 1;
         g.hCell = nRows ? (int)ceilf(height / nRows) : 1;
+        g.magicW = (unsigned)((0x100000000ull + g.wCell - 1) / g.wCell); g.magicH = (unsigned)((0x100000000ull + g.hCell - 1) / g.hCell);
         // octree roots (ORBextractor.cpp:545-547)
         int nIni = nCols ? (int)roundf((float)(maxBX - 16) / (float)(maxBY - 16)) : 1;
         if (nIni < 1) nIni = 1;
@@ -463,7 +464,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             a.dst = d_pyr + n.off; a.dst_pitch = n.pitch; a.dst_fstride = (long long)h->pyr_fstride;
         }
         a.fast_on = g.nCols > 0; a.wCell = g.wCell; a.hCell = g.hCell; a.minTh = h->cfg.min_th_fast;
-        a.magicW = (unsigned)((0x100000000ull + g.wCell - 1) / g.wCell); a.magicH = (unsigned)((0x100000000ull + g.hCell - 1) / g.hCell);
+        a.magicW = g.magicW; a.magicH = g.magicH;
         a.rec = d_rec + g.rec_off; a.rec_cap = g.rec_cap; a.rec_fstride = (long long)h->rec_total;
         a.rec_count = d_rec_count + l; a.rec_count_stride = nl;
         for (int i = 0; i < 7; i++) a.q[i] = h->q[i];

@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(NTO) octree_kernel(const __grid_constant__ Oct
     for (int i = tid; i < nraw; i += NTO) {
         const uint32_t r = rec[i];
         const int m = r & 0xff, x = (r >> 8) & 0xfff, y = r >> 20;
-        if (m > a.iniTh) cellflag[((y - 19) / g.hCell) * g.nCols + (x - 19) / g.wCell] = 1;
+        if (m > a.iniTh) cellflag[(int)__umulhi((unsigned)(y - 19), g.magicH) * g.nCols + (int)__umulhi((unsigned)(x - 19), g.magicW)] = 1;
     }
     __syncthreads();
     for (int i = tid; i < ((nraw + NTO - 1) / NTO) * NTO; i += NTO) {
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(NTO) octree_kernel(const __grid_constant__ Oct
         if (i < nraw) {
             r = rec[i];
             const int m = r & 0xff, x = (r >> 8) & 0xfff, y = r >> 20;
-            keep = (m > a.iniTh) || !cellflag[((y - 19) / g.hCell) * g.nCols + (x - 19) / g.wCell];
+            keep = (m > a.iniTh) || !cellflag[(int)__umulhi((unsigned)(y - 19), g.magicH) * g.nCols + (int)__umulhi((unsigned)(x - 19), g.magicW)];
         }
         const unsigned b = __ballot_sync(0xffffffffu, keep);
         int base = 0;
@@ -497,7 +497,7 @@ __global__ void __launch_bounds__(NTO) octree_kernel(const __grid_constant__ Oct
         for (unsigned j = 0; j < nd.w; j++) {
             const uint32_t p = pts[nd.z + j];
             const int m = p & 0xff, x = ((p >> 8) & 0xfff) + 16, y = (p >> 20) + 16;
-            const unsigned long long key = ((unsigned long long)(((y - 19) / g.hCell) * g.nCols + (x - 19) / g.wCell) << 24) | ((unsigned)y << 12) | (unsigned)x;
+            const unsigned long long key = ((unsigned long long)((int)__umulhi((unsigned)(y - 19), g.magicH) * g.nCols + (int)__umulhi((unsigned)(x - 19), g.magicW)) << 24) | ((unsigned)y << 12) | (unsigned)x;
             if (m > bm || (m == bm && key < bkey)) { bm = m; bkey = key; bp = p; }
         }
         out[i] = make_int4((int)((bp >> 8) & 0xfff) + 16, (int)(bp >> 20) + 16, bm - 1, 0);
