@@ -264,3 +264,60 @@ def test_colour_frames_strided_rows(gpu):
     # invalid channel counts are rejected
     assert orbb200.lib().orbx_extract_batch_color(ex.h, padded.ctypes.data, F, w, h, padded.shape[2], 0, 2, 1,
                                                   kps.ctypes.data, desc.ctypes.data, cnt.ctypes.data, 800) != 0
+
+
+def _golden():
+    import importlib.util, os
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(gold, "make_golden.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    return gen, np.load(os.path.join(gold, "ref_extract.npz")), np.load(os.path.join(gold, "cv2_prims.npz"))
+
+
+@pytest.mark.parametrize("w,h,nf,seed", [(320, 240, 500, 21), (203, 177, 300, 22)])
+def test_gpu_equals_reference_golden_full_output(gpu, w, h, nf, seed):
+    """The CUDA path against the committed outputs of the reference's own ORBextractor.cpp (tests/golden/ref_extract.npz,
+    compiled unmodified as oracle/_ref when the fixture was made): keypoints incl. order and angles, descriptors, pyramid."""
+    import hashlib, orbb200
+    from synth import synth
+    gen, refg, _ = _golden()
+    tag = f"{w}x{h}_{nf}_{seed}"
+    ex = orbb200.ORBextractor(nf, max_size=(w, h))
+    k, d = ex(synth(w, h, seed), None)
+    rk, rd = refg[f"kps_{tag}"], refg[f"desc_{tag}"]
+    assert len(k) == len(rk) and len(k) > 100
+    assert gen.kp_exact_bytes(k) == gen.kp_exact_bytes(rk)
+    assert k["angle"].tobytes() == rk["angle"].tobytes()
+    assert np.array_equal(d, rd)
+    for L in range(8):
+        assert hashlib.sha256(ex.pyramid_level(L).tobytes()).hexdigest() == str(refg[f"pyrsha_{tag}"][L]), f"pyramid level {L}"
+
+
+@pytest.mark.parametrize("w,h,nf,seed", [(640, 480, 1000, 1), (1241, 376, 2000, 2), (752, 480, 1200, 3)])
+def test_gpu_equals_reference_golden_config_shapes(gpu, w, h, nf, seed):
+    """C1 / C2 / C3 shapes of BASELINE.json: the CUDA output hashes to the compiled reference's committed checksums."""
+    import hashlib, orbb200
+    from synth import synth
+    gen, refg, _ = _golden()
+    tag = f"{w}x{h}_{nf}_{seed}"
+    k, d = orbb200.ORBextractor(nf, max_size=(w, h))(synth(w, h, seed), None)
+    assert len(k) == int(refg[f"count_{tag}"])
+    assert hashlib.sha256(gen.kp_exact_bytes(k)).hexdigest() == str(refg[f"kpsha_{tag}"])
+    assert k["angle"].tobytes() == refg[f"angles_{tag}"].tobytes()
+    assert hashlib.sha256(d.tobytes()).hexdigest() == str(refg[f"descsha_{tag}"])
+
+
+def test_gpu_pyramid_and_blur_equal_cv2_golden(gpu):
+    """Pyramid levels and blurred levels of the CUDA path against cv2 4.13's own outputs (tests/golden/cv2_prims.npz)."""
+    import orbb200
+    from synth import synth
+    gen, _, cvg = _golden()
+    for (w, h, seed) in gen.PRIM_SHAPES:
+        tag = f"{w}x{h}_{seed}"
+        ex = orbb200.ORBextractor(200, max_size=(w, h))
+        ex(synth(w, h, seed), None)
+        for L in range(8):
+            if L > 0:
+                assert np.array_equal(ex.pyramid_level(L), cvg[f"pyr_{tag}_L{L}"]), f"resize level {L} of {tag}"
+            assert np.array_equal(ex.blurred_level(L), cvg[f"blur_{tag}_L{L}"]), f"blur level {L} of {tag}"
