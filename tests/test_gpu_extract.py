@@ -321,3 +321,27 @@ def test_gpu_pyramid_and_blur_equal_cv2_golden(gpu):
             if L > 0:
                 assert np.array_equal(ex.pyramid_level(L), cvg[f"pyr_{tag}_L{L}"]), f"resize level {L} of {tag}"
             assert np.array_equal(ex.blurred_level(L), cvg[f"blur_{tag}_L{L}"]), f"blur level {L} of {tag}"
+
+
+def test_multi_chunk_pipeline(gpu):
+    """orbx_extract_batch / _color with enough frames for the ramped multi-chunk, multi-stream pipeline (head 16+32, full 64s,
+    tail 32+16 for 300 small frames): every frame equals its single-frame result, pinned and pageable hosts alike."""
+    import torch, orbb200, pyoracle
+    from synth import synth
+    w, h, F, ND = 160, 128, 300, 7
+    distinct = np.stack([synth(w, h, 500 + i) for i in range(ND)])
+    ex1 = orbb200.ORBextractor(150, max_size=(w, h))
+    single = [ex1(distinct[i], None) for i in range(ND)]
+    imgs = distinct[np.arange(F) % ND]
+    exb = orbb200.ORBextractor(150, max_size=(w, h), max_batch=F)
+    for host in (np.ascontiguousarray(imgs), torch.from_numpy(np.ascontiguousarray(imgs)).pin_memory().numpy()):
+        out = exb.extract_batch(host)
+        assert len(out) == F
+        for f in range(F):
+            k, d = out[f]
+            assert k.tobytes() == single[f % ND][0].tobytes() and np.array_equal(d, single[f % ND][1]), f"frame {f}"
+    col = np.stack([imgs, imgs, imgs], axis=3)            # R = G = B = v  ->  grey == v exactly ((9798+19235+3735) v + 2^14) >> 15 = v
+    assert np.array_equal(pyoracle.cvt_gray(col[0], True), imgs[0])
+    out = exb.extract_batch_color(np.ascontiguousarray(col), rgb_order=False)
+    for f in range(F):
+        assert out[f][0].tobytes() == single[f % ND][0].tobytes() and np.array_equal(out[f][1], single[f % ND][1]), f"colour frame {f}"
