@@ -194,6 +194,15 @@ int orbm_search_by_bow(const uint8_t* desc_kf, const float* angle_kf, const uint
                        const int32_t* fv_f_nodes, const int32_t* fv_f_off, const int32_t* fv_f_feat, int nfv_f,
                        float nnratio, int check_orientation, int32_t* match_f_to_kf, int* nmatches, int device);
 
+/* ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12) (ORBmatcher.cpp:604-743), the loop-closing
+ * variant: has_mp1 / has_mp2 flag features whose MapPoint exists and is not bad, angle* = mvKeysUn[i].angle.  Output
+ * match12[n1]: the KeyFrame-2 feature whose MapPoint the reference stores in vpMatches12[i], or -1. */
+int orbm_search_by_bow_kf(const uint8_t* desc1, const float* angle1, const uint8_t* has_mp1, int n1,
+                          const int32_t* fv1_nodes, const int32_t* fv1_off, const int32_t* fv1_feat, int nfv1,
+                          const uint8_t* desc2, const float* angle2, const uint8_t* has_mp2, int n2,
+                          const int32_t* fv2_nodes, const int32_t* fv2_off, const int32_t* fv2_feat, int nfv2,
+                          float nnratio, int check_orientation, int32_t* match12, int* nmatches, int device);
+
 /* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (ORBmatcher.cpp:63-155): window candidates and
  * distances on the device, then the reference's order-dependent top-2 / level-aware ratio / already-matched loop on
  * the host.  frame_mp[n] (in/out) is F.mvpMapPoints flattened to ids (-1 = none), frame_mp_obs[n] the matched point's

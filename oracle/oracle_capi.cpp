@@ -157,6 +157,16 @@ int orc_search_by_bow(const uint8_t* descKF, const float* angleKF, const uint8_t
     return n;
 }
 
+int orc_search_by_bow_kf(const uint8_t* d1, const float* a1, const uint8_t* h1, int n1, const int32_t* n1n, const int32_t* n1o, const int32_t* n1f, int nf1,
+                         const uint8_t* d2, const float* a2, const uint8_t* h2, int n2, const int32_t* n2n, const int32_t* n2o, const int32_t* n2f, int nf2,
+                         float nnratio, int check_ori, int32_t* matches)
+{
+    std::vector<int> m;
+    const int n = SearchByBoW_KF(d1, a1, h1, n1, fv_from_csr(n1n, n1o, n1f, nf1), d2, a2, h2, n2, fv_from_csr(n2n, n2o, n2f, nf2), nnratio, check_ori != 0, m);
+    for (int i = 0; i < n1; i++) matches[i] = m[i];
+    return n;
+}
+
 struct orc_frame { FrameGrid g; std::vector<KeyPoint> kps; std::vector<uint8_t> desc; };
 orc_frame* orc_frame_create(const KeyPoint* kps, const uint8_t* desc, int n, float minx, float miny, float maxx, float maxy)
 {

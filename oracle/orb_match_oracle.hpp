@@ -1,7 +1,7 @@
 // oracle/orb_match_oracle.hpp — TEST INFRASTRUCTURE (CPU oracle), never linked into the product.
 //
 // CPU restatement of the Hamming-matching half of the hot path.  Reference files followed:
-//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :205-348 (SearchByBoW) :474-590 :1506-1659 :1792-1854
+//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :205-348 :604-743 (SearchByBoW) :474-590 :1506-1659 :1792-1854
 //   ORB-SLAM2/src/Frame.cpp       :241-257 :379-444 :540-748
 //   ORB-SLAM2/src/MapPoint.cpp    :302-380 (ComputeDistinctiveDescriptors)
 // ORBmatcher.cpp / Frame.cpp cannot be compiled here (they pull in KeyFrame/MapPoint/DBoW2/OpenCV/Eigen),
@@ -183,6 +183,65 @@ static inline int SearchByBoW(const uint8_t* descKF, const float* angleKF, const
         for (int i = 0; i < HISTO_LENGTH; i++) {
             if (i == ind1 || i == ind2 || i == ind3) continue;
             for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) { vpMapPointMatches[rotHist[i][j]] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+// ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12) (ORBmatcher.cpp:604-743) on flattened
+// arrays: has_mp1/has_mp2 = "MapPoint exists and is not bad"; the result stores the KeyFrame-2 feature index.
+static inline int SearchByBoW_KF(const uint8_t* Descriptors1, const float* angle1, const uint8_t* has_mp1, int n1,
+                                 const std::map<unsigned, std::vector<unsigned> >& vFeatVec1,
+                                 const uint8_t* Descriptors2, const float* angle2, const uint8_t* has_mp2, int n2,
+                                 const std::map<unsigned, std::vector<unsigned> >& vFeatVec2,
+                                 float mfNNratio, bool mbCheckOrientation, std::vector<int>& vpMatches12)
+{
+    vpMatches12.assign(n1, -1);
+    std::vector<bool> vbMatched2(n2, false);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    int nmatches = 0;
+    std::map<unsigned, std::vector<unsigned> >::const_iterator f1it = vFeatVec1.begin(), f2it = vFeatVec2.begin();
+    const std::map<unsigned, std::vector<unsigned> >::const_iterator f1end = vFeatVec1.end(), f2end = vFeatVec2.end();
+    while (f1it != f1end && f2it != f2end) {
+        if (f1it->first == f2it->first) {
+            for (size_t i1 = 0, iend1 = f1it->second.size(); i1 < iend1; i1++) {
+                const size_t idx1 = f1it->second[i1];
+                if (!has_mp1[idx1]) continue;
+                const uint8_t* d1 = Descriptors1 + idx1 * 32;
+                int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+                for (size_t i2 = 0, iend2 = f2it->second.size(); i2 < iend2; i2++) {
+                    const size_t idx2 = f2it->second[i2];
+                    if (vbMatched2[idx2] || !has_mp2[idx2]) continue;
+                    const int dist = DescriptorDistance(d1, Descriptors2 + idx2 * 32);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = (int)idx2; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (bestDist1 < TH_LOW) {
+                    if (static_cast<float>(bestDist1) < mfNNratio * static_cast<float>(bestDist2)) {
+                        vpMatches12[idx1] = bestIdx2;
+                        vbMatched2[bestIdx2] = true;
+                        if (mbCheckOrientation) {
+                            float rot = angle1[idx1] - angle2[bestIdx2];
+                            if (rot < 0.0) rot += 360.0f;
+                            int bin = (int)round(rot * factor);
+                            if (bin == HISTO_LENGTH) bin = 0;
+                            rotHist[bin].push_back((int)idx1);
+                        }
+                        nmatches++;
+                    }
+                }
+            }
+            f1it++; f2it++;
+        } else if (f1it->first < f2it->first) f1it = vFeatVec1.lower_bound(f2it->first);
+        else f2it = vFeatVec2.lower_bound(f1it->first);
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) { vpMatches12[rotHist[i][j]] = -1; nmatches--; }
         }
     }
     return nmatches;

@@ -70,6 +70,7 @@ def lib():
         L.orc_vocab_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_vocab_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7
         L.orc_search_by_bow.argtypes = [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 2 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_float, C.c_int, C.c_void_p]
+        L.orc_search_by_bow_kf.argtypes = ([C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int]) * 2 + [C.c_float, C.c_int, C.c_void_p]
         L.orc_frame_create.restype = C.c_void_p
         L.orc_frame_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
         L.orc_frame_destroy.argtypes = [C.c_void_p]
@@ -255,6 +256,19 @@ def search_by_bow(desc_kf, angle_kf, kf_has_mp, fv_kf, desc_f, angle_f, fv_f, nn
     out = np.zeros(len(desc_f), np.int32)
     n = lib().orc_search_by_bow(_p(desc_kf), _p(angle_kf), _p(kf_has_mp), _p(kn), _p(ko), _p(kf), len(kn), _p(desc_f), _p(angle_f), len(desc_f),
                                 _p(fn), _p(fo), _p(ff), len(fn), nnratio, 1 if check_ori else 0, _p(out))
+    return out, n
+
+
+def search_by_bow_kf(desc1, angle1, has1, fv1, desc2, angle2, has2, fv2, nnratio=0.75, check_ori=True):
+    """ORBmatcher::SearchByBoW(KeyFrame, KeyFrame) -> (matches12[n1] of KF2 indices, nmatches)."""
+    desc1 = np.ascontiguousarray(desc1, np.uint8); desc2 = np.ascontiguousarray(desc2, np.uint8)
+    angle1 = np.ascontiguousarray(angle1, np.float32); angle2 = np.ascontiguousarray(angle2, np.float32)
+    has1 = np.ascontiguousarray(has1, np.uint8); has2 = np.ascontiguousarray(has2, np.uint8)
+    a = [np.ascontiguousarray(x, np.int32) for x in fv1]; b = [np.ascontiguousarray(x, np.int32) for x in fv2]
+    out = np.zeros(len(desc1), np.int32)
+    n = lib().orc_search_by_bow_kf(_p(desc1), _p(angle1), _p(has1), len(desc1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]),
+                                   _p(desc2), _p(angle2), _p(has2), len(desc2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]),
+                                   nnratio, 1 if check_ori else 0, _p(out))
     return out, n
 
 

@@ -293,70 +293,89 @@ extern "C" int orbm_search_by_projection_frame(const orbm_frame* f, const float*
     return ORBB_OK;
 }
 
-// ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vector<MapPoint*>&) (ORBmatcher.cpp:205-348).  The all-pairs distances of the common
-// vocabulary nodes are computed on the device (bow_join_kernel); the scan that skips already matched Frame features (:243-245) is
-// order dependent and runs on the host exactly as written, followed by the rotation histogram (:313-345).
+// ---- ORBmatcher::SearchByBoW ---------------------------------------------------------------------------
+// Shared front half of both SearchByBoW overloads: walk the two FeatureVectors together (the lower_bound dance of :224-310 /
+// :634-720 is a sorted-key intersection), make one join entry per A feature that carries a good MapPoint, and compute the
+// all-pairs distances of every common vocabulary node on the device (bow_join_kernel).  Entries come out in (node, A feature)
+// order, which is the order the reference's loops visit them.
+static int bow_join(const uint8_t* desc_a, const uint8_t* has_a, int n_a, const int32_t* fa_nodes, const int32_t* fa_off, const int32_t* fa_feat, int nfa,
+                    const uint8_t* desc_b, int n_b, const int32_t* fb_nodes, const int32_t* fb_off, const int32_t* fb_feat, int nfb,
+                    int device, std::vector<int4>& entries, std::vector<uint16_t>& dist)
+{
+    if (n_a < 0 || n_b < 0 || nfa < 0 || nfb < 0) return ORBB_E_INVALID;
+    if ((n_a > 0 && (!desc_a || !has_a)) || (n_b > 0 && !desc_b)) return ORBB_E_INVALID;
+    if ((nfa > 0 && (!fa_nodes || !fa_off || !fa_feat)) || (nfb > 0 && (!fb_nodes || !fb_off || !fb_feat))) return ORBB_E_INVALID;
+    for (int j = 0; j < nfa; j++) {
+        if (fa_off[j + 1] < fa_off[j] || (j > 0 && fa_nodes[j] <= fa_nodes[j - 1])) return ORBB_E_INVALID;
+        for (int t = fa_off[j]; t < fa_off[j + 1]; t++) if (fa_feat[t] < 0 || fa_feat[t] >= n_a) return ORBB_E_INVALID;
+    }
+    for (int j = 0; j < nfb; j++) {
+        if (fb_off[j + 1] < fb_off[j] || (j > 0 && fb_nodes[j] <= fb_nodes[j - 1])) return ORBB_E_INVALID;
+        for (int t = fb_off[j]; t < fb_off[j + 1]; t++) if (fb_feat[t] < 0 || fb_feat[t] >= n_b) return ORBB_E_INVALID;
+    }
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    entries.clear();
+    long long total = 0;
+    for (int a = 0, b = 0; a < nfa && b < nfb;) {
+        if (fa_nodes[a] < fb_nodes[b]) { a++; continue; }
+        if (fa_nodes[a] > fb_nodes[b]) { b++; continue; }
+        const int nB = fb_off[b + 1] - fb_off[b];
+        for (int t = fa_off[a]; t < fa_off[a + 1]; t++) {
+            const int iA = fa_feat[t];
+            if (!has_a[iA]) continue;                                                   // :233-238 / :643-647
+            if (total + nB > 0x7fffffffLL) return ORBB_E_CAPACITY;
+            entries.push_back(make_int4(iA, fb_off[b], nB, (int)total));
+            total += nB;
+        }
+        a++; b++;
+    }
+    dist.assign((size_t)total, 0);
+    if (entries.empty() || total == 0) return ORBB_OK;
+    DevBuf dA, dB, dF, dE, dD;
+    const int nfeatB = fb_off[nfb];
+    if ((rc = dA.alloc((size_t)n_a * 32)) || (rc = dB.alloc((size_t)n_b * 32)) || (rc = dF.alloc((size_t)nfeatB * 4)) ||
+        (rc = dE.alloc(entries.size() * sizeof(int4))) || (rc = dD.alloc((size_t)total * 2))) return rc;
+    ORBB_CUDA(cudaMemcpy(dA.p, desc_a, (size_t)n_a * 32, cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(dB.p, desc_b, (size_t)n_b * 32, cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(dF.p, fb_feat, (size_t)nfeatB * 4, cudaMemcpyHostToDevice));
+    ORBB_CUDA(cudaMemcpy(dE.p, entries.data(), entries.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    bow_join_kernel<<<ceil_div((int)entries.size(), 8), 256>>>(dA.as<uint4>(), dB.as<uint4>(), dF.as<int>(), dE.as<int4>(), (int)entries.size(),
+                                                               dD.as<uint16_t>());
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    ORBB_CUDA(cudaMemcpy(dist.data(), dD.p, (size_t)total * 2, cudaMemcpyDeviceToHost));
+    return ORBB_OK;
+}
+
+static void bow_rot_filter(std::vector<int>* rotHist, int32_t* matches, int& nm)          // :313-345 / :722-740
+{
+    int ind1 = -1, ind2 = -1, ind3 = -1;
+    three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+    for (int b = 0; b < HISTO_LENGTH; b++)
+        if (b != ind1 && b != ind2 && b != ind3)
+            for (size_t j = 0; j < rotHist[b].size(); j++) { matches[rotHist[b][j]] = -1; nm--; }
+}
+
+// SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches) (ORBmatcher.cpp:205-348).  The scan that skips already
+// matched Frame features (:243-245) is order dependent and runs on the host exactly as written.
 extern "C" int orbm_search_by_bow(const uint8_t* desc_kf, const float* angle_kf, const uint8_t* kf_has_mp, int n_kf,
                                   const int32_t* fv_kf_nodes, const int32_t* fv_kf_off, const int32_t* fv_kf_feat, int nfv_kf,
                                   const uint8_t* desc_f, const float* angle_f, int n_f,
                                   const int32_t* fv_f_nodes, const int32_t* fv_f_off, const int32_t* fv_f_feat, int nfv_f,
                                   float nnratio, int check_ori, int32_t* match_f_to_kf, int* nmatches, int device)
 {
-    if (!nmatches || n_kf < 0 || n_f < 0 || nfv_kf < 0 || nfv_f < 0 || (n_f > 0 && !match_f_to_kf)) return ORBB_E_INVALID;
-    if ((n_kf > 0 && (!desc_kf || !kf_has_mp)) || (n_f > 0 && !desc_f) || (check_ori && ((n_kf > 0 && !angle_kf) || (n_f > 0 && !angle_f)))) return ORBB_E_INVALID;
-    if ((nfv_kf > 0 && (!fv_kf_nodes || !fv_kf_off || !fv_kf_feat)) || (nfv_f > 0 && (!fv_f_nodes || !fv_f_off || !fv_f_feat))) return ORBB_E_INVALID;
-    for (int j = 0; j < nfv_kf; j++) {
-        if (fv_kf_off[j + 1] < fv_kf_off[j] || (j > 0 && fv_kf_nodes[j] <= fv_kf_nodes[j - 1])) return ORBB_E_INVALID;
-        for (int t = fv_kf_off[j]; t < fv_kf_off[j + 1]; t++) if (fv_kf_feat[t] < 0 || fv_kf_feat[t] >= n_kf) return ORBB_E_INVALID;
-    }
-    for (int j = 0; j < nfv_f; j++) {
-        if (fv_f_off[j + 1] < fv_f_off[j] || (j > 0 && fv_f_nodes[j] <= fv_f_nodes[j - 1])) return ORBB_E_INVALID;
-        for (int t = fv_f_off[j]; t < fv_f_off[j + 1]; t++) if (fv_f_feat[t] < 0 || fv_f_feat[t] >= n_f) return ORBB_E_INVALID;
-    }
-    int rc = check_device(device);
+    if (!nmatches || (n_f > 0 && !match_f_to_kf)) return ORBB_E_INVALID;
+    if (check_ori && ((n_kf > 0 && !angle_kf) || (n_f > 0 && !angle_f))) return ORBB_E_INVALID;
+    std::vector<int4> entries; std::vector<uint16_t> dist;
+    const int rc = bow_join(desc_kf, kf_has_mp, n_kf, fv_kf_nodes, fv_kf_off, fv_kf_feat, nfv_kf, desc_f, n_f, fv_f_nodes, fv_f_off, fv_f_feat, nfv_f,
+                            device, entries, dist);
     if (rc != ORBB_OK) return rc;
     *nmatches = 0;
     for (int i = 0; i < n_f; i++) match_f_to_kf[i] = -1;
-    // common nodes (the two sorted maps are walked together, :224-310) -> join entries for KeyFrame features that carry a good
-    // MapPoint (:233-238)
-    struct Common { int a, b; };
-    std::vector<Common> common;
-    for (int a = 0, b = 0; a < nfv_kf && b < nfv_f;) {
-        if (fv_kf_nodes[a] == fv_f_nodes[b]) { common.push_back({a, b}); a++; b++; }
-        else if (fv_kf_nodes[a] < fv_f_nodes[b]) a++;
-        else b++;
-    }
-    std::vector<int4> entries;
-    long long total = 0;
-    for (const Common& c : common) {
-        const int nB = fv_f_off[c.b + 1] - fv_f_off[c.b];
-        for (int t = fv_kf_off[c.a]; t < fv_kf_off[c.a + 1]; t++) {
-            const int iA = fv_kf_feat[t];
-            if (!kf_has_mp[iA]) continue;
-            if (total + nB > 0x7fffffffLL) return ORBB_E_CAPACITY;
-            entries.push_back(make_int4(iA, fv_f_off[c.b], nB, (int)total));
-            total += nB;
-        }
-    }
-    std::vector<uint16_t> dist((size_t)total);
-    if (!entries.empty() && total > 0) {
-        DevBuf dA, dB, dF, dE, dD;
-        const int nfeatB = fv_f_off[nfv_f];
-        if ((rc = dA.alloc((size_t)n_kf * 32)) || (rc = dB.alloc((size_t)n_f * 32)) || (rc = dF.alloc((size_t)nfeatB * 4)) ||
-            (rc = dE.alloc(entries.size() * sizeof(int4))) || (rc = dD.alloc((size_t)total * 2))) return rc;
-        ORBB_CUDA(cudaMemcpy(dA.p, desc_kf, (size_t)n_kf * 32, cudaMemcpyHostToDevice));
-        ORBB_CUDA(cudaMemcpy(dB.p, desc_f, (size_t)n_f * 32, cudaMemcpyHostToDevice));
-        ORBB_CUDA(cudaMemcpy(dF.p, fv_f_feat, (size_t)nfeatB * 4, cudaMemcpyHostToDevice));
-        ORBB_CUDA(cudaMemcpy(dE.p, entries.data(), entries.size() * sizeof(int4), cudaMemcpyHostToDevice));
-        bow_join_kernel<<<ceil_div((int)entries.size(), 8), 256>>>(dA.as<uint4>(), dB.as<uint4>(), dF.as<int>(), dE.as<int4>(), (int)entries.size(),
-                                                                   dD.as<uint16_t>());
-        ORBB_LAUNCHED();
-        ORBB_CUDA(cudaGetLastError());
-        ORBB_CUDA(cudaMemcpy(dist.data(), dD.p, (size_t)total * 2, cudaMemcpyDeviceToHost));
-    }
     std::vector<int> rotHist[HISTO_LENGTH];
     int nm = 0;
-    for (const int4& en : entries) {                                                    // entries are in (node, iKF) order
+    for (const int4& en : entries) {
         int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
         for (int j = 0; j < en.z; j++) {
             const int realIdxF = fv_f_feat[en.y + j];
@@ -371,13 +390,46 @@ extern "C" int orbm_search_by_bow(const uint8_t* desc_kf, const float* angle_kf,
             nm++;
         }
     }
-    if (check_ori) {                                                                    // :313-345
-        int ind1 = -1, ind2 = -1, ind3 = -1;
-        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
-        for (int b = 0; b < HISTO_LENGTH; b++)
-            if (b != ind1 && b != ind2 && b != ind3)
-                for (size_t j = 0; j < rotHist[b].size(); j++) { match_f_to_kf[rotHist[b][j]] = -1; nm--; }
+    if (check_ori) bow_rot_filter(rotHist, match_f_to_kf, nm);
+    *nmatches = nm;
+    return ORBB_OK;
+}
+
+// SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, vector<MapPoint*>& vpMatches12) (ORBmatcher.cpp:604-743): both sides need a good
+// MapPoint (:643-647, :660-666), KeyFrame-2 features are used once (vbMatched2, :662, :691), strict bestDist1 < TH_LOW (:686).
+extern "C" int orbm_search_by_bow_kf(const uint8_t* desc1, const float* angle1, const uint8_t* has_mp1, int n1,
+                                     const int32_t* fv1_nodes, const int32_t* fv1_off, const int32_t* fv1_feat, int nfv1,
+                                     const uint8_t* desc2, const float* angle2, const uint8_t* has_mp2, int n2,
+                                     const int32_t* fv2_nodes, const int32_t* fv2_off, const int32_t* fv2_feat, int nfv2,
+                                     float nnratio, int check_ori, int32_t* match12, int* nmatches, int device)
+{
+    if (!nmatches || (n1 > 0 && !match12) || (n2 > 0 && !has_mp2)) return ORBB_E_INVALID;
+    if (check_ori && ((n1 > 0 && !angle1) || (n2 > 0 && !angle2))) return ORBB_E_INVALID;
+    std::vector<int4> entries; std::vector<uint16_t> dist;
+    const int rc = bow_join(desc1, has_mp1, n1, fv1_nodes, fv1_off, fv1_feat, nfv1, desc2, n2, fv2_nodes, fv2_off, fv2_feat, nfv2, device, entries, dist);
+    if (rc != ORBB_OK) return rc;
+    *nmatches = 0;
+    for (int i = 0; i < n1; i++) match12[i] = -1;
+    std::vector<uint8_t> vbMatched2((size_t)n2, 0);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nm = 0;
+    for (const int4& en : entries) {
+        int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+        for (int j = 0; j < en.z; j++) {
+            const int idx2 = fv2_feat[en.y + j];
+            if (vbMatched2[idx2] || !has_mp2[idx2]) continue;                           // :660-666
+            const int d = dist[(size_t)en.w + j];
+            if (d < bestDist1) { bestDist2 = bestDist1; bestDist1 = d; bestIdx2 = idx2; }
+            else if (d < bestDist2) bestDist2 = d;
+        }
+        if (bestDist1 < TH_LOW && static_cast<float>(bestDist1) < nnratio * static_cast<float>(bestDist2)) {    // :686-688
+            match12[en.x] = bestIdx2;
+            vbMatched2[bestIdx2] = 1;
+            if (check_ori) rotHist[rot_bin(angle1[en.x], angle2[bestIdx2])].push_back(en.x);
+            nm++;
+        }
     }
+    if (check_ori) bow_rot_filter(rotHist, match12, nm);
     *nmatches = nm;
     return ORBB_OK;
 }

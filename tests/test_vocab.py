@@ -219,3 +219,21 @@ def test_gpu_search_by_bow(gpu, check_ori, ratio):
     e = (np.zeros(0, np.int32), np.zeros(1, np.int32), np.zeros(0, np.int32))
     g0, n0 = orbb200.search_by_bow(dl, kl["angle"], has, e, dc, kc["angle"], fv_f, ratio, check_ori)
     assert n0 == 0 and np.all(g0 == -1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("check_ori,ratio", [(True, 0.75), (False, 0.9)])
+def test_gpu_search_by_bow_keyframes(gpu, check_ori, ratio):
+    """ORBmatcher::SearchByBoW(KeyFrame, KeyFrame) (ORBmatcher.cpp:604-743): MapPoint flags on both sides, vbMatched2."""
+    import orbb200, pyoracle
+    (kc, dc), (kl, dl), (k, L, parent, leaf, desc, weight) = _bow_pair(seed=33)
+    voc = orbb200.Vocabulary(k, L, parent, leaf, desc, weight)
+    fv1 = voc.bow(dl, 2)[2:]
+    fv2 = voc.bow(dc, 2)[2:]
+    rng = np.random.default_rng(6)
+    has1 = (rng.random(len(dl)) < 0.7).astype(np.uint8); has2 = (rng.random(len(dc)) < 0.7).astype(np.uint8)
+    want, nw = pyoracle.search_by_bow_kf(dl, kl["angle"], has1, fv1, dc, kc["angle"], has2, fv2, ratio, check_ori)
+    got, ng = orbb200.search_by_bow_kf(dl, kl["angle"], has1, fv1, dc, kc["angle"], has2, fv2, ratio, check_ori)
+    assert ng == nw and np.array_equal(got, want) and ng > 30
+    idx = np.flatnonzero(got >= 0)
+    assert np.all(has1[idx] == 1) and np.all(has2[got[idx]] == 1) and len(set(got[idx].tolist())) == len(idx)
