@@ -182,6 +182,25 @@ typedef struct orbm_proj_query {
     float angle;            /* LastFrame.mvKeysUn[i].angle, for the rotation histogram (a11)                */
 } orbm_proj_query;
 
+/* the relocalisation, loop-closing and fusion variants.  The caller projects (pose algebra,
+ * PredictScale, frustum tests) exactly as the reference does and hands over one orbm_proj_query per surviving MapPoint:
+ * q.u, q.v, q.r = th * mvScaleFactors[nPredictedLevel], q.min_level / q.max_level = the octave window of the variant.
+ *
+ * orbm_search_by_projection_reloc: SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound,
+ *   th, ORBdist) (ORBmatcher.cpp:1661-1789): level window [p-1, p+1]; frame_mp[i] >= 0 marks Frame features that already have a
+ *   MapPoint (:1727-1728) and receives pq[].id on a match; max_dist = ORBdist; angle = pKF->mvKeysUn[i].angle.
+ * orbm_search_by_projection_loop: SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints,
+ *   vector<MapPoint*>& vpMatched, th) (:352-472): level window [p-1, p]; matched[i] >= 0 = vpMatched[i] set, receives pq[].id.
+ * orbm_fuse_best: the search of Fuse(KeyFrame*, const vector<MapPoint*>&, th) (:962-1115: pass mvuRight, mvInvLevelSigma2 and
+ *   q.u_right = ur for the chi-square gate, max_dist = TH_LOW), of Fuse(KeyFrame*, cv::Mat Scw, ...) (:1119-1251: gate off =
+ *   inv_level_sigma2 NULL, TH_LOW) and of each direction of SearchBySim3 (:1253-1500: gate off, TH_HIGH).  best_idx[i] = the
+ *   KeyFrame feature the reference selects for point i, or -1; Replace / AddObservation / the Sim3 cross-check stay with the caller. */
+int orbm_search_by_projection_reloc(const orbm_frame* f, const orbm_proj_query* q_host, int nq, int max_dist, int check_orientation,
+                                    int32_t* frame_mp, int* nmatches);
+int orbm_search_by_projection_loop(const orbm_frame* f, const orbm_proj_query* q_host, int nq, int32_t* matched, int* nmatches);
+int orbm_fuse_best(const orbm_frame* f, const orbm_proj_query* q_host, int nq, const float* mvuRight_host,
+                   const float* inv_level_sigma2, int max_dist, int32_t* best_idx, int32_t* best_dist);
+
 /* ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, vector<MapPoint*>& vpMapPointMatches) (ORBmatcher.cpp:205-348).
  * desc_kf / desc_f: mDescriptors of the KeyFrame (n_kf rows) and of the Frame (n_f rows); angle_kf = pKF->mvKeysUn[i].angle,
  * angle_f = F.mvKeys[i].angle (read only when check_ori); kf_has_mp[i] != 0 iff vpMapPointsKF[i] exists and is not bad

@@ -214,6 +214,29 @@ int orc_search_last_frame(orc_frame* f, const float* mvuRight, const ProjQuery* 
     std::copy(mp.begin(), mp.end(), frameMP); std::copy(ob.begin(), ob.end(), frameMPObs);
     return n;
 }
+int orc_search_reloc(orc_frame* f, const ProjQuery* qs, int nq, int orbdist, int checkOri, int* frameMP)
+{
+    std::vector<ProjQuery> q(qs, qs + nq);
+    std::vector<int> mp(frameMP, frameMP + f->g.N);
+    int n = SearchByProjection_Reloc(f->g, q, orbdist, checkOri != 0, mp);
+    std::copy(mp.begin(), mp.end(), frameMP);
+    return n;
+}
+int orc_search_loop(orc_frame* f, const ProjQuery* qs, int nq, int* matched)
+{
+    std::vector<ProjQuery> q(qs, qs + nq);
+    std::vector<int> m(matched, matched + f->g.N);
+    int n = SearchByProjection_Loop(f->g, q, m);
+    std::copy(m.begin(), m.end(), matched);
+    return n;
+}
+void orc_fuse_best(orc_frame* f, const ProjQuery* qs, int nq, const float* mvuRight, const float* invSigma2, int gate, int maxDist, int* bestIdx, int* bestDist)
+{
+    std::vector<ProjQuery> q(qs, qs + nq);
+    std::vector<int> bi, bd;
+    FuseBest(f->g, q, mvuRight, invSigma2, gate != 0, maxDist, bi, bd);
+    std::copy(bi.begin(), bi.end(), bestIdx); std::copy(bd.begin(), bd.end(), bestDist);
+}
 int orc_search_for_initialization(orc_frame* f1, orc_frame* f2, float* prevMatchedXY, int* vnMatches12, int windowSize, float nnratio, int checkOri)
 {
     std::vector<float> pm(prevMatchedXY, prevMatchedXY + 2 * f1->g.N);

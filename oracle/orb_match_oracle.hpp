@@ -1,7 +1,7 @@
 // oracle/orb_match_oracle.hpp — TEST INFRASTRUCTURE (CPU oracle), never linked into the product.
 //
 // CPU restatement of the Hamming-matching half of the hot path.  Reference files followed:
-//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :205-348 :604-743 (SearchByBoW) :474-590 :1506-1659 :1792-1854
+//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :205-348 :604-743 (SearchByBoW) :352-472 :962-1251 (Fuse) :1253-1500 (SearchBySim3) :1661-1789 :474-590 :1506-1659 :1792-1854
 //   ORB-SLAM2/src/Frame.cpp       :241-257 :379-444 :540-748
 //   ORB-SLAM2/src/MapPoint.cpp    :302-380 (ComputeDistinctiveDescriptors)
 // ORBmatcher.cpp / Frame.cpp cannot be compiled here (they pull in KeyFrame/MapPoint/DBoW2/OpenCV/Eigen),
@@ -352,6 +352,110 @@ static inline int SearchByProjection_LastFrame(const FrameGrid& F, const float* 
                 for (size_t j = 0; j < rotHist[i].size(); j++) { frameMP[rotHist[i][j]] = -1; nmatches--; }
     }
     return nmatches;
+}
+
+// SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, th, ORBdist)
+// (ORBmatcher.cpp:1661-1789) after the projection step.  frameMP[i] = id of CurrentFrame.mvpMapPoints[i] or -1.
+static inline int SearchByProjection_Reloc(const FrameGrid& F, const std::vector<ProjQuery>& qs, int ORBdist, bool checkOri,
+                                           std::vector<int>& frameMP)
+{
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    std::vector<int> vIndices2;
+    for (size_t i = 0; i < qs.size(); i++) {
+        const ProjQuery& q = qs[i];
+        F.GetFeaturesInArea(q.u, q.v, q.r, q.minLevel, q.maxLevel, vIndices2);
+        if (vIndices2.empty()) continue;
+        int bestDist = 256, bestIdx2 = -1;
+        for (int i2 : vIndices2) {
+            if (frameMP[i2] >= 0) continue;
+            const int dist = DescriptorDistance(q.desc, F.desc + (size_t)i2 * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = i2; }
+        }
+        if (bestDist <= ORBdist) {
+            frameMP[bestIdx2] = q.id;
+            nmatches++;
+            if (checkOri) {
+                float rot = q.angle - F.kps[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) { frameMP[rotHist[i][j]] = -1; nmatches--; }
+    }
+    return nmatches;
+}
+
+// SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, vector<MapPoint*>& vpMatched, th)
+// (ORBmatcher.cpp:352-472) after the projection step: KeyFrame::GetFeaturesInArea(u, v, radius) has no level filter
+// (KeyFrame.cpp:694-735), the level test follows in the loop.  q.maxLevel carries nPredictedLevel.
+static inline int SearchByProjection_Loop(const FrameGrid& KF, const std::vector<ProjQuery>& qs, std::vector<int>& vpMatched)
+{
+    int nmatches = 0;
+    std::vector<int> vIndices;
+    for (size_t iMP = 0; iMP < qs.size(); iMP++) {
+        const ProjQuery& q = qs[iMP];
+        const int nPredictedLevel = q.maxLevel;
+        KF.GetFeaturesInArea(q.u, q.v, q.r, -1, -1, vIndices);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (int idx : vIndices) {
+            if (vpMatched[idx] >= 0) continue;
+            const int kpLevel = KF.kps[idx].octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            const int dist = DescriptorDistance(q.desc, KF.desc + (size_t)idx * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestDist <= TH_LOW) { vpMatched[bestIdx] = q.id; nmatches++; }
+    }
+    return nmatches;
+}
+
+// The per-point search of Fuse(KeyFrame*, const vector<MapPoint*>&, th) (ORBmatcher.cpp:1025-1085, gate = true),
+// Fuse(KeyFrame*, cv::Mat Scw, ...) (:1195-1225) and SearchBySim3 (:1343-1377, :1423-1457) (gate = false).
+static inline void FuseBest(const FrameGrid& KF, const std::vector<ProjQuery>& qs, const float* mvuRight, const float* mvInvLevelSigma2,
+                            bool gate, int maxDist, std::vector<int>& bestIdxOut, std::vector<int>& bestDistOut)
+{
+    bestIdxOut.assign(qs.size(), -1); bestDistOut.assign(qs.size(), -1);
+    std::vector<int> vIndices;
+    for (size_t i = 0; i < qs.size(); i++) {
+        const ProjQuery& q = qs[i];
+        const int nPredictedLevel = q.maxLevel;
+        const float u = q.u, v = q.v, ur = q.uR;
+        KF.GetFeaturesInArea(u, v, q.r, -1, -1, vIndices);
+        if (vIndices.empty()) continue;
+        int bestDist = 256, bestIdx = -1;
+        for (int idx : vIndices) {
+            const KeyPoint& kp = KF.kps[idx];
+            const int kpLevel = kp.octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            if (gate) {
+                if (mvuRight && mvuRight[idx] >= 0) {
+                    const float kpx = kp.x, kpy = kp.y, kpr = mvuRight[idx];
+                    const float ex = u - kpx, ey = v - kpy, er = ur - kpr;
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * mvInvLevelSigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float kpx = kp.x, kpy = kp.y;
+                    const float ex = u - kpx, ey = v - kpy;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * mvInvLevelSigma2[kpLevel] > 5.99) continue;
+                }
+            }
+            const int dist = DescriptorDistance(q.desc, KF.desc + (size_t)idx * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx = idx; }
+        }
+        if (bestIdx >= 0 && bestDist <= maxDist) { bestIdxOut[i] = bestIdx; bestDistOut[i] = bestDist; }
+    }
 }
 
 // ORBmatcher::SearchForInitialization (ORBmatcher.cpp:474-590)

@@ -69,6 +69,9 @@ def lib():
         L.orc_vocab_destroy.argtypes = [C.c_void_p]
         L.orc_vocab_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_vocab_bow.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7
+        L.orc_search_reloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.orc_search_loop.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orc_fuse_best.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_search_by_bow.argtypes = [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 2 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.orc_search_by_bow_kf.argtypes = ([C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int]) * 2 + [C.c_float, C.c_int, C.c_void_p]
         L.orc_frame_create.restype = C.c_void_p
@@ -317,6 +320,27 @@ class OracleFrame:
         ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
         n = self.L.orc_search_last_frame(self.h, _p(ur), _p(q), len(q), int(check_ori), _p(mp), _p(ob))
         return n, mp, ob
+
+
+    def search_reloc(self, queries, orbdist, check_ori, frame_mp):
+        q = np.ascontiguousarray(queries, QUERY_DTYPE)
+        mp = np.ascontiguousarray(frame_mp, np.int32).copy()
+        n = self.L.orc_search_reloc(self.h, _p(q), len(q), orbdist, int(check_ori), _p(mp))
+        return n, mp
+
+    def search_loop(self, queries, matched):
+        q = np.ascontiguousarray(queries, QUERY_DTYPE)
+        m = np.ascontiguousarray(matched, np.int32).copy()
+        n = self.L.orc_search_loop(self.h, _p(q), len(q), _p(m))
+        return n, m
+
+    def fuse_best(self, queries, uright, inv_sigma2, gate, max_dist):
+        q = np.ascontiguousarray(queries, QUERY_DTYPE)
+        ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+        s2 = None if inv_sigma2 is None else np.ascontiguousarray(inv_sigma2, np.float32)
+        bi = np.zeros(len(q), np.int32); bd = np.zeros(len(q), np.int32)
+        self.L.orc_fuse_best(self.h, _p(q), len(q), _p(ur), _p(s2), int(gate), max_dist, _p(bi), _p(bd))
+        return bi, bd
 
 
 def search_for_initialization(f1, f2, prev_matched, window=100, nnratio=0.9, check_ori=True):

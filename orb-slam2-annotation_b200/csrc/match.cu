@@ -293,6 +293,116 @@ extern "C" int orbm_search_by_projection_frame(const orbm_frame* f, const float*
     return ORBB_OK;
 }
 
+// ---- relocalisation / loop-closing / fusion variants --------------------------
+// They all project on the host (pose algebra, PredictScale) and share the device window search; only the candidate gates and
+// the bookkeeping differ.
+
+// SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, th, ORBdist) (ORBmatcher.cpp:1661-1789):
+// a candidate is skipped when the Frame feature already has a MapPoint (:1727-1728), best distance <= ORBdist (:1742).
+extern "C" int orbm_search_by_projection_reloc(const orbm_frame* f, const orbm_proj_query* pq, int nq, int max_dist, int check_ori,
+                                               int32_t* frame_mp, int* nmatches)
+{
+    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && !frame_mp)) return ORBB_E_INVALID;
+    *nmatches = 0;
+    if (nq == 0) return ORBB_OK;
+    std::vector<orbm_query> q(nq);
+    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
+    std::vector<int> offs, idx, dist;
+    const int rc = run_window_search(f, q, offs, idx, dist);
+    if (rc != ORBB_OK) return rc;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nm = 0;
+    for (int i = 0; i < nq; i++) {
+        int bestDist = 256, bestIdx2 = -1;
+        for (int c = offs[i]; c < offs[i + 1]; c++) {
+            const int i2 = idx[c];
+            if (frame_mp[i2] >= 0) continue;                                            // :1727-1728
+            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx2 = i2; }
+        }
+        if (bestDist <= max_dist) {                                                     // :1742-1760
+            frame_mp[bestIdx2] = pq[i].id;
+            nm++;
+            if (check_ori) rotHist[rot_bin(pq[i].angle, f->h_kps[bestIdx2].angle)].push_back(bestIdx2);
+        }
+    }
+    if (check_ori) {                                                                    // :1766-1786
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int b = 0; b < HISTO_LENGTH; b++)
+            if (b != ind1 && b != ind2 && b != ind3)
+                for (size_t j = 0; j < rotHist[b].size(); j++) { frame_mp[rotHist[b][j]] = -1; nm--; }
+    }
+    *nmatches = nm;
+    return ORBB_OK;
+}
+
+// SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, vector<MapPoint*>& vpMatched, th)
+// (ORBmatcher.cpp:352-472): KeyFrame::GetFeaturesInArea has no level filter, the level gate [p-1, p] follows (:441-444) — the
+// same set as a window query with that level range; already matched features are skipped (:438-439); best <= TH_LOW (:457).
+extern "C" int orbm_search_by_projection_loop(const orbm_frame* f, const orbm_proj_query* pq, int nq, int32_t* matched, int* nmatches)
+{
+    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && !matched)) return ORBB_E_INVALID;
+    *nmatches = 0;
+    if (nq == 0) return ORBB_OK;
+    std::vector<orbm_query> q(nq);
+    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
+    std::vector<int> offs, idx, dist;
+    const int rc = run_window_search(f, q, offs, idx, dist);
+    if (rc != ORBB_OK) return rc;
+    int nm = 0;
+    for (int i = 0; i < nq; i++) {
+        int bestDist = 256, bestIdx = -1;
+        for (int c = offs[i]; c < offs[i + 1]; c++) {
+            const int k = idx[c];
+            if (matched[k] >= 0) continue;
+            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx = k; }
+        }
+        if (bestDist <= TH_LOW) { matched[bestIdx] = pq[i].id; nm++; }
+    }
+    *nmatches = nm;
+    return ORBB_OK;
+}
+
+// The per-point search of Fuse(KeyFrame*, const vector<MapPoint*>&, th) (ORBmatcher.cpp:962-1115; chi-square reprojection gate
+// :1053-1078), Fuse(KeyFrame*, cv::Mat Scw, ...) (:1119-1251, no gate) and of each direction of SearchBySim3 (:1253-1500, no gate,
+// TH_HIGH): first candidate with the smallest distance among those passing the level range of the query and, when
+// inv_level_sigma2 is given, the gate; best_idx = -1 unless best distance <= max_dist.  Queries do not interact.
+extern "C" int orbm_fuse_best(const orbm_frame* f, const orbm_proj_query* pq, int nq, const float* uright, const float* inv_level_sigma2,
+                              int max_dist, int32_t* best_idx, int32_t* best_dist)
+{
+    if (!f || nq < 0 || (nq > 0 && (!pq || !best_idx))) return ORBB_E_INVALID;
+    if (nq == 0) return ORBB_OK;
+    std::vector<orbm_query> q(nq);
+    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
+    std::vector<int> offs, idx, dist;
+    const int rc = run_window_search(f, q, offs, idx, dist);
+    if (rc != ORBB_OK) return rc;
+    for (int i = 0; i < nq; i++) {
+        const float u = pq[i].q.u, v = pq[i].q.v, ur = pq[i].u_right;
+        int bestDist = 256, bestIdx = -1;
+        for (int c = offs[i]; c < offs[i + 1]; c++) {
+            const int k = idx[c];
+            if (inv_level_sigma2) {
+                const orbx_keypoint& kp = f->h_kps[k];
+                const float ex = u - kp.x, ey = v - kp.y;
+                if (uright && uright[k] >= 0) {                                         // :1053-1066
+                    const float er = ur - uright[k];
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * inv_level_sigma2[kp.octave] > 7.8) continue;
+                } else {                                                                // :1067-1078
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * inv_level_sigma2[kp.octave] > 5.99) continue;
+                }
+            }
+            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx = k; }
+        }
+        const bool ok = bestIdx >= 0 && bestDist <= max_dist;
+        best_idx[i] = ok ? bestIdx : -1;
+        if (best_dist) best_dist[i] = ok ? bestDist : -1;
+    }
+    return ORBB_OK;
+}
+
 // ---- ORBmatcher::SearchByBoW ---------------------------------------------------------------------------
 // Shared front half of both SearchByBoW overloads: walk the two FeatureVectors together (the lower_bound dance of :224-310 /
 // :634-720 is a sorted-key intersection), make one join entry per A feature that carries a good MapPoint, and compute the

@@ -26,7 +26,7 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
            "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
-           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf",
+           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
@@ -91,6 +91,9 @@ def lib():
         L.orbm_search_by_projection_frame.argtypes = [vp, vp, vp, i32, i32, vp, vp, C.POINTER(i32)]
         L.orbm_search_by_bow.argtypes = [vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, C.POINTER(i32), i32]
         L.orbm_search_by_bow_kf.argtypes = [vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, C.POINTER(i32), i32]
+        L.orbm_search_by_projection_reloc.argtypes = [vp, vp, i32, i32, i32, vp, C.POINTER(i32)]
+        L.orbm_search_by_projection_loop.argtypes = [vp, vp, i32, vp, C.POINTER(i32)]
+        L.orbm_fuse_best.argtypes = [vp, vp, i32, vp, vp, i32, vp, vp]
         L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, C.POINTER(i32)]
         L.orbm_stereo_match.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, f32, f32, vp, vp]
         L.orbm_db_create.argtypes = [C.POINTER(vp), C.c_int64, C.c_int64, i32]
@@ -442,6 +445,32 @@ class ORBmatcher:
         _check(self.L.orbm_search_by_projection_frame(frame.h, _p(ur), _p(q), len(q), int(self.mbCheckOrientation), _p(mp), _p(ob), C.byref(n)),
                "orbm_search_by_projection_frame")
         return n.value, mp, ob
+
+    def SearchByProjection_reloc(self, frame, proj_queries, frame_mp, ORBdist):
+        """SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (ORBmatcher.cpp:1661-1789)."""
+        q = np.ascontiguousarray(proj_queries, PROJ_QUERY_DTYPE)
+        mp = np.ascontiguousarray(frame_mp, np.int32).copy()
+        n = C.c_int()
+        _check(self.L.orbm_search_by_projection_reloc(frame.h, _p(q), len(q), ORBdist, int(self.mbCheckOrientation), _p(mp), C.byref(n)),
+               "orbm_search_by_projection_reloc")
+        return n.value, mp
+
+    def SearchByProjection_loop(self, frame, proj_queries, matched):
+        """SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (ORBmatcher.cpp:352-472)."""
+        q = np.ascontiguousarray(proj_queries, PROJ_QUERY_DTYPE)
+        m = np.ascontiguousarray(matched, np.int32).copy()
+        n = C.c_int()
+        _check(self.L.orbm_search_by_projection_loop(frame.h, _p(q), len(q), _p(m), C.byref(n)), "orbm_search_by_projection_loop")
+        return n.value, m
+
+    def FuseBest(self, frame, proj_queries, mvuRight, inv_level_sigma2, max_dist):
+        """Per-point search of Fuse / Fuse(Scw) / SearchBySim3 (ORBmatcher.cpp:962-1500): (best_idx, best_dist)."""
+        q = np.ascontiguousarray(proj_queries, PROJ_QUERY_DTYPE)
+        ur = None if mvuRight is None else np.ascontiguousarray(mvuRight, np.float32)
+        s2 = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
+        bi = np.zeros(len(q), np.int32); bd = np.zeros(len(q), np.int32)
+        _check(self.L.orbm_fuse_best(frame.h, _p(q), len(q), _p(ur), _p(s2), max_dist, _p(bi), _p(bd)), "orbm_fuse_best")
+        return bi, bd
 
     def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
         pm = np.ascontiguousarray(vbPrevMatched, np.float32).copy()

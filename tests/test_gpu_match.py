@@ -302,3 +302,62 @@ def test_distinctive_descriptors_map_scale(gpu):
     want_row, want_med = pyoracle.distinctive_descriptors(desc, off)
     got_row, got_med = orbb200.distinctive_descriptors(desc, off)
     assert np.array_equal(got_row, want_row) and np.array_equal(got_med, want_med)
+
+
+def test_search_by_projection_reloc_and_loop(gpu):
+    """the relocalisation (ORBmatcher.cpp:1661-1789) and loop-closing (:352-472) SearchByProjection overloads."""
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=14)
+    rng = np.random.default_rng(10)
+    h, w = cur.shape
+    F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h)); O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    for th, orbdist, check in [(10.0, 100, True), (3.0, 64, True), (10.0, 100, False)]:
+        q = _queries(kl, dl, scale, th, (3, 1), rng, "pm1")                       # GetFeaturesInArea(u, v, radius, p-1, p+1)
+        mp0 = np.full(len(kc), -1, np.int32); mp0[::13] = 5555                    # features that already have a MapPoint
+        n, mp = orbb200.ORBmatcher(0.9, check).SearchByProjection_reloc(F, q, mp0, orbdist)
+        on, omp = O.search_reloc(_to_oracle_queries(q), orbdist, check, mp0)
+        assert n == on and np.array_equal(mp, omp) and n > 0.2 * len(kl)
+    for th in (4.0, 10.0):
+        q = _queries(kl, dl, scale, th, (3, 1), rng, "pred")                      # level gate [p-1, p]
+        m0 = np.full(len(kc), -1, np.int32); m0[3::11] = 4444
+        n, m = orbb200.ORBmatcher().SearchByProjection_loop(F, q, m0)
+        on, om = O.search_loop(_to_oracle_queries(q), m0)
+        assert n == on and np.array_equal(m, om) and n > 0.2 * len(kl)
+
+
+def test_fuse_and_sim3_best(gpu):
+    """the per-point search of Fuse (chi-square gate, mono and stereo), Fuse(Scw) and SearchBySim3."""
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=15)
+    rng = np.random.default_rng(11)
+    h, w = cur.shape
+    F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h)); O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    sigma2 = (scale.astype(np.float32) ** 2).astype(np.float32)
+    inv_s2 = (np.float32(1.0) / sigma2).astype(np.float32)
+    ur = np.where(rng.random(len(kc)) < 0.5, kc["x"] - rng.uniform(0, 30, len(kc)), -1).astype(np.float32)
+    q = _queries(kl, dl, scale, 3.0, (3, 1), rng, "pred")
+    q["q"]["u"] += rng.normal(0, 1.5, len(q)).astype(np.float32)                   # reprojection noise: the gate really cuts
+    q["q"]["v"] += rng.normal(0, 1.5, len(q)).astype(np.float32)
+    q["u_right"] = q["q"]["u"] - 12.0
+    oq = _to_oracle_queries(q)
+    m = orbb200.ORBmatcher()
+    cases = [(ur, inv_s2, True, 50), (None, inv_s2, True, 50), (None, None, False, 50), (None, None, False, 100)]
+    seen = []
+    for uright, s2, gate, maxd in cases:
+        bi, bd = m.FuseBest(F, q, uright, s2, maxd)
+        obi, obd = O.fuse_best(oq, uright, s2 if s2 is not None else inv_s2, gate, maxd)
+        assert np.array_equal(bi, obi) and np.array_equal(bd, obd)
+        assert (bi >= 0).sum() > 0.2 * len(kl)
+        seen.append(int((bi >= 0).sum()))
+    assert seen[0] <= seen[2] <= seen[3]                                           # gates and thresholds only remove matches
+    # SearchBySim3's mutual check (ORBmatcher.cpp:1478-1495) on two directions of best matches
+    q21 = _queries(kc, dc, scale, 7.5, (-3, -1), rng, "pred")
+    F2 = orbb200.FrameMatcher(kl, dl, (0, 0, w, h)); O2 = pyoracle.OracleFrame(kl, dl, (0, 0, w, h))
+    q12 = _queries(kl, dl, scale, 7.5, (3, 1), rng, "pred")
+    m1, _ = m.FuseBest(F, q12, None, None, 100)        # KF1 points searched in KF2 (= cur)
+    m2, _ = m.FuseBest(F2, q21, None, None, 100)       # KF2 points searched in KF1 (= last)
+    o1, _ = O.fuse_best(_to_oracle_queries(q12), None, inv_s2, False, 100)
+    o2, _ = O2.fuse_best(_to_oracle_queries(q21), None, inv_s2, False, 100)
+    assert np.array_equal(m1, o1) and np.array_equal(m2, o2)
+    mutual = [(i1, m1[i1]) for i1 in range(len(m1)) if m1[i1] >= 0 and m2[m1[i1]] == i1]
+    assert len(mutual) > 0.2 * len(kl)
