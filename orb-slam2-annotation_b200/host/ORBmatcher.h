@@ -132,6 +132,58 @@ public:
         return n;
     }
 
+    // src/ORBmatcher.cpp:1661-1789 (relocalisation): frameMapPointIds[i] >= 0 <=> CurrentFrame.mvpMapPoints[i] is set.
+    int SearchByProjectionReloc(const DeviceFrame& Current, const std::vector<orbm_proj_query>& q, int ORBdist,
+                                std::vector<int32_t>& frameMapPointIds) const
+    {
+        int n = 0;
+        orbm_check(orbm_search_by_projection_reloc(Current.get(), q.data(), (int)q.size(), ORBdist, mbCheckOrientation ? 1 : 0,
+                                                   frameMapPointIds.data(), &n), "orbm_search_by_projection_reloc");
+        return n;
+    }
+    // src/ORBmatcher.cpp:352-472 (loop closing, Sim3-projected points): vpMatchedIds[i] >= 0 <=> vpMatched[i] is set.
+    int SearchByProjectionLoop(const DeviceFrame& KF, const std::vector<orbm_proj_query>& q, std::vector<int32_t>& vpMatchedIds) const
+    {
+        int n = 0;
+        orbm_check(orbm_search_by_projection_loop(KF.get(), q.data(), (int)q.size(), vpMatchedIds.data(), &n), "orbm_search_by_projection_loop");
+        return n;
+    }
+    // The per-point search of Fuse (src/ORBmatcher.cpp:962-1115 with the chi-square gate, :1119-1251 without) and of each direction
+    // of SearchBySim3 (:1253-1500, maxDist = TH_HIGH): bestIdx[i] = feature of KF selected for point i, or -1.
+    void FuseBest(const DeviceFrame& KF, const std::vector<orbm_proj_query>& q, const std::vector<float>* mvuRight,
+                  const std::vector<float>* mvInvLevelSigma2, int maxDist, std::vector<int32_t>& bestIdx) const
+    {
+        bestIdx.assign(q.size(), -1);
+        orbm_check(orbm_fuse_best(KF.get(), q.data(), (int)q.size(), mvuRight ? mvuRight->data() : nullptr,
+                                  mvInvLevelSigma2 ? mvInvLevelSigma2->data() : nullptr, maxDist, bestIdx.data(), nullptr), "orbm_fuse_best");
+    }
+    // src/ORBmatcher.cpp:205-348 and :604-743 on flattened FeatureVectors (node ids ascending, CSR offsets, feature indices) as
+    // orbv_compute_bow returns them.  hasMapPoint[i] != 0 <=> the feature's MapPoint exists and is not bad.
+    struct FeatVec { std::vector<int32_t> nodes, offsets, features; };
+    int SearchByBoW(const cv::Mat& descKF, const std::vector<float>& angleKF, const std::vector<uint8_t>& hasMapPointKF, const FeatVec& fvKF,
+                    const cv::Mat& descF, const std::vector<float>& angleF, const FeatVec& fvF, std::vector<int32_t>& matchFtoKF, int device = 0) const
+    {
+        int n = 0;
+        matchFtoKF.assign(descF.rows, -1);
+        orbm_check(orbm_search_by_bow(descKF.ptr(0), angleKF.data(), hasMapPointKF.data(), descKF.rows, fvKF.nodes.data(), fvKF.offsets.data(),
+                                      fvKF.features.data(), (int)fvKF.nodes.size(), descF.ptr(0), angleF.data(), descF.rows, fvF.nodes.data(),
+                                      fvF.offsets.data(), fvF.features.data(), (int)fvF.nodes.size(), mfNNratio, mbCheckOrientation ? 1 : 0,
+                                      matchFtoKF.data(), &n, device), "orbm_search_by_bow");
+        return n;
+    }
+    int SearchByBoW(const cv::Mat& desc1, const std::vector<float>& angle1, const std::vector<uint8_t>& hasMapPoint1, const FeatVec& fv1,
+                    const cv::Mat& desc2, const std::vector<float>& angle2, const std::vector<uint8_t>& hasMapPoint2, const FeatVec& fv2,
+                    std::vector<int32_t>& match12, int device = 0) const
+    {
+        int n = 0;
+        match12.assign(desc1.rows, -1);
+        orbm_check(orbm_search_by_bow_kf(desc1.ptr(0), angle1.data(), hasMapPoint1.data(), desc1.rows, fv1.nodes.data(), fv1.offsets.data(),
+                                         fv1.features.data(), (int)fv1.nodes.size(), desc2.ptr(0), angle2.data(), hasMapPoint2.data(), desc2.rows,
+                                         fv2.nodes.data(), fv2.offsets.data(), fv2.features.data(), (int)fv2.nodes.size(), mfNNratio,
+                                         mbCheckOrientation ? 1 : 0, match12.data(), &n, device), "orbm_search_by_bow_kf");
+        return n;
+    }
+
     static const int TH_LOW = 50;         // src/ORBmatcher.cpp:37-39
     static const int TH_HIGH = 100;
     static const int HISTO_LENGTH = 30;
