@@ -103,6 +103,20 @@ int orbx_extract_batch_color(orbx_handle* h, const uint8_t* imgs_host, int nfram
 int orbx_cvt_gray_device(const uint8_t* src_dev, int nframes, int w, int h_, size_t src_stride, size_t src_frame_stride,
                          int channels, int rgb_order, uint8_t* dst_dev, size_t dst_stride, size_t dst_frame_stride, void* stream);
 
+/* Stereo rectification in front of the extractor: the stereo examples call
+ * cv::remap(imLeft, imLeftRect, M1l, M2l, cv::INTER_LINEAR) with the CV_32F maps of cv::initUndistortRectifyMap before
+ * SLAM.TrackStereo (Examples/Stereo/stereo_euroc.cc:174-185).  orbx_set_rectification stores one camera's maps (dst_w x dst_h
+ * floats each, giving for every rectified pixel its source position in the src_w x src_h raw frame) in the handle, converted to
+ * cv::remap's fixed point; NULL maps clear it.  orbx_extract_batch_rectified = cv::remap on the device (INTER_LINEAR,
+ * BORDER_CONSTANT 0, arithmetic of OpenCV 4.x) followed by orbx_extract_batch on the rectified frames; raw frames are
+ * src_w x src_h bytes with the given strides.  orbx_remap_device rectifies device frames and synchronises the stream. */
+int orbx_set_rectification(orbx_handle* h, const float* mapx_host, const float* mapy_host, int dst_w, int dst_h, int src_w, int src_h);
+int orbx_extract_batch_rectified(orbx_handle* h, const uint8_t* raw_host, int nframes, size_t stride_bytes, size_t frame_stride_bytes,
+                                 orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity);
+int orbx_remap_device(const uint8_t* src_dev, int nframes, int src_w, int src_h, size_t src_stride, size_t src_frame_stride,
+                      const float* mapx_host, const float* mapy_host, int dst_w, int dst_h,
+                      uint8_t* dst_dev, size_t dst_stride, size_t dst_frame_stride, void* stream);
+
 /* Blocks until the handle's stream is idle; returns the first asynchronous error, and ORBB_E_CAPACITY if an
  * internal candidate buffer overflowed during the last extraction. */
 int orbx_sync(orbx_handle* h);

@@ -14,6 +14,7 @@
 //   cvRound                      :83,117-122,1128 -> cv_round
 // and, for the SURVEY 8(f)-4 "next" row (ORB-SLAM2/src/Tracking.cpp:202-227, 233-250, 264-281):
 //   cv::cvtColor RGB/BGR/RGBA/BGRA -> GRAY    -> cvt_gray_u8
+//   cv::remap INTER_LINEAR (stereo rectification, Examples/Stereo/stereo_euroc.cc:174-185) -> remap_linear_u8
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -47,6 +48,35 @@ static inline void cvt_gray_u8(const uint8_t* src, int w, int h, size_t sstride,
             d[x] = (uint8_t)((r * RY + g * GY + b * BY + (1 << (shift - 1))) >> shift);
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------
+// cv::remap(src, dst, map1, map2, cv::INTER_LINEAR) for CV_8UC1 with CV_32FC1 maps and the default BORDER_CONSTANT (0)
+// (OpenCV imgproc/imgwarp.cpp: maps are converted to fixed point with INTER_BITS = 5, sx = cvRound(mapx * 32), integer part
+// sx >> 5 saturated to short, fraction sx & 31; BilinearTab_i weights are (32-fx)(32-fy)*32 etc. — products of 1/32 steps are
+// exact, so the table needs no fix-up — and the result is (sum w*p + 2^14) >> 15).  Checked against cv2 4.13
+// (tests/golden/cv2_remap.npz).
+// ---------------------------------------------------------------------------------------
+static inline void remap_linear_u8(const uint8_t* src, int sw, int sh, size_t sstride, const float* mapx, const float* mapy,
+                                   uint8_t* dst, int dw, int dh, size_t dstride)
+{
+    for (int y = 0; y < dh; y++)
+        for (int x = 0; x < dw; x++) {
+            const int sx = cv_round(mapx[(size_t)y * dw + x] * 32.f), sy = cv_round(mapy[(size_t)y * dw + x] * 32.f);
+            int ix = sx >> 5, iy = sy >> 5;
+            ix = ix < -32768 ? -32768 : (ix > 32767 ? 32767 : ix);
+            iy = iy < -32768 ? -32768 : (iy > 32767 ? 32767 : iy);
+            const int fx = sx & 31, fy = sy & 31;
+            int acc = 0;
+            for (int dy = 0; dy < 2; dy++)
+                for (int dx = 0; dx < 2; dx++) {
+                    const int xx = ix + dx, yy = iy + dy;
+                    const int p = (xx >= 0 && xx < sw && yy >= 0 && yy < sh) ? src[(size_t)yy * sstride + xx] : 0;
+                    const int w = (dx ? fx : 32 - fx) * (dy ? fy : 32 - fy) * 32;
+                    acc += w * p;
+                }
+            dst[(size_t)y * dstride + x] = (uint8_t)((acc + (1 << 14)) >> 15);
+        }
 }
 
 // ---------------------------------------------------------------------------------------

@@ -66,6 +66,7 @@ void orc_level_kps(orc_ctx* c, int level, KeyPoint* out)
 
 // ---- primitives (for the cv2 pinning tests) ---------------------------------------------
 void orc_resize(const uint8_t* src, int sw, int sh, uint8_t* dst, int dw, int dh) { cvp::resize_linear_u8(src, sw, sh, sw, dst, dw, dh, dw); }
+void orc_remap(const uint8_t* src, int sw, int sh, const float* mapx, const float* mapy, uint8_t* dst, int dw, int dh) { cvp::remap_linear_u8(src, sw, sh, sw, mapx, mapy, dst, dw, dh, dw); }
 void orc_cvt_gray(const uint8_t* src, int w, int h, int channels, int rgb_order, uint8_t* dst) { cvp::cvt_gray_u8(src, w, h, (size_t)w * channels, channels, rgb_order != 0, dst, w); }
 void orc_blur(const uint8_t* src, int w, int h, uint8_t* dst, int legacy) { cvp::gaussian_blur7_u8(src, w, h, w, dst, w, legacy != 0); }
 int orc_fast(const uint8_t* img, int w, int h, int th, int* xys, int cap)

@@ -58,6 +58,7 @@ def lib():
         L.orc_level_kps.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.orc_resize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int]
         L.orc_blur.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_remap.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         L.orc_cvt_gray.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.orc_fast.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.orc_fast_atan2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
@@ -153,6 +154,16 @@ def resize(src, dw, dh):
     dst = np.zeros((dh, dw), np.uint8)
     lib().orc_resize(_p(src), src.shape[1], src.shape[0], _p(dst), dw, dh)
     return dst
+
+
+def remap(src, mapx, mapy):
+    """cv::remap(src, dst, mapx, mapy, INTER_LINEAR) (BORDER_CONSTANT 0) of a u8 image with float32 maps."""
+    src = np.ascontiguousarray(src, np.uint8)
+    mapx = np.ascontiguousarray(mapx, np.float32); mapy = np.ascontiguousarray(mapy, np.float32)
+    dh, dw = mapx.shape
+    out = np.zeros((dh, dw), np.uint8)
+    lib().orc_remap(_p(src), src.shape[1], src.shape[0], _p(mapx), _p(mapy), _p(out), dw, dh)
+    return out
 
 
 def cvt_gray(src, rgb_order=True):

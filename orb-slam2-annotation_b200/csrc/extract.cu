@@ -65,7 +65,9 @@ struct orbx_handle {
     orbx_keypoint* d_kps = nullptr;
     // pinned staging
     uint8_t *h_img = nullptr, *h_desc = nullptr;
-    uint8_t* d_color = nullptr;          // colour frames of orbx_extract_batch_color (allocated on first use)
+    uint8_t* d_color = nullptr;          // colour / raw frames of orbx_extract_batch_color / _rectified (allocated on first use)
+    int2* d_map = nullptr;               // rectification map in cv::remap's fixed point {cvRound(mapx*32), cvRound(mapy*32)}
+    int map_w = 0, map_h = 0, map_sw = 0, map_sh = 0;
     orbx_keypoint* h_kps = nullptr;
     int *h_counts = nullptr, *h_status = nullptr;
     // optional per-kernel timing (bench.py roofline): events around each kernel class
@@ -360,7 +362,7 @@ extern "C" int orbx_destroy(orbx_handle* h)
     if (!h) return ORBB_E_INVALID;
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    cudaFree(h->d_color); cudaFree(h->d_pyr); cudaFree(h->d_blur); cudaFree(h->d_rec); cudaFree(h->d_pts); cudaFree(h->d_nodes);
+    cudaFree(h->d_color); cudaFree(h->d_map); cudaFree(h->d_pyr); cudaFree(h->d_blur); cudaFree(h->d_rec); cudaFree(h->d_pts); cudaFree(h->d_nodes);
     cudaFree(h->d_iscr); cudaFree(h->d_cellflag); cudaFree(h->d_out); cudaFree(h->d_rec_count); cudaFree(h->d_out_count);
     cudaFree(h->d_status); cudaFree(h->d_counts); cudaFree(h->d_tab); cudaFree(h->d_tiles); cudaFree(h->d_geom);
     cudaFree(h->d_node_off); cudaFree(h->d_cell_off); cudaFree(h->d_kps); cudaFree(h->d_desc);
@@ -590,21 +592,26 @@ static int pipeline_chunk(int w, int ht)
 // Host-buffer batch pipeline.  channels == 1: grey frames (the reference's operator() input).  channels == 3 | 4: colour frames,
 // converted on the device like Tracking::GrabImage* does with cv::cvtColor before the extractor runs (Tracking.cpp:202-227).
 static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
-                              size_t fstride, int channels, int rgb_order, orbx_keypoint* kps_host, uint8_t* desc_host,
+                              size_t fstride, int channels, int rgb_order, int raw_w, int raw_h, orbx_keypoint* kps_host, uint8_t* desc_host,
                               int32_t* counts_host, int capacity)
 {
     if (!h || !counts_host || capacity < 0 || (capacity > 0 && (!kps_host || !desc_host))) return ORBB_E_INVALID;
     if (channels != 1 && channels != 3 && channels != 4) return ORBB_E_INVALID;
     const size_t CH_ = (size_t)channels;
+    const bool remap = raw_w > 0;           // raw camera frames of raw_w x raw_h, rectified on the device into w x ht (orbx_set_rectification)
+    if (remap && (channels != 1 || raw_h < 1 || !h || !h->d_map || h->map_w != w || h->map_h != ht || h->map_sw != raw_w || h->map_sh != raw_h)) return ORBB_E_STATE;
+    const int in_w = remap ? raw_w : w, in_h = remap ? raw_h : ht;     // what crosses PCIe
+    const bool staged = channels > 1 || remap;
     if (nframes < 1 || nframes > h->cfg.max_batch) return ORBB_E_INVALID;
     if (w == 0 || ht == 0 || !imgs_host) {              // empty image: silent return (ORBextractor.cpp:1056-1057)
         for (int f = 0; f < nframes; f++) counts_host[f] = 0;
         return ORBB_OK;
     }
-    if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w * CH_) return ORBB_E_BAD_SHAPE;
+    if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)in_w * CH_) return ORBB_E_BAD_SHAPE;
+    if (remap && (size_t)in_w * in_h > 4 * (size_t)h->cfg.max_width * h->cfg.max_height) return ORBB_E_BAD_SHAPE;
     ORBB_CUDA(cudaSetDevice(h->cfg.device));
     cudaStream_t st = h->stream;
-    if (channels > 1 && !h->d_color) {      // colour landing buffer, allocated on first use
+    if (staged && !h->d_color) {      // colour landing buffer, allocated on first use
         const int rc = dev_alloc(&h->d_color, (size_t)h->cfg.max_batch * h->cfg.max_width * h->cfg.max_height * 4);
         if (rc != ORBB_OK) return rc;
     }
@@ -675,15 +682,15 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
     if (trace) cudaEventRecord(ev_t0, h->s_in);
     for (int c = 0; c < nchunks; c++) {
         const int f0 = cstart[c], nf = cstart[c + 1] - f0;
-        if (channels > 1) {    // colour frames land packed in d_color (pageable sources are staged by the driver)
-            const size_t fbytes = (size_t)w * ht * CH_;
-            if (stride == (size_t)w * CH_ && (nframes == 1 || fstride >= fbytes)) {
+        if (staged) {          // colour / raw frames land packed in d_color (pageable sources are staged by the driver)
+            const size_t fbytes = (size_t)in_w * in_h * CH_;
+            if (stride == (size_t)in_w * CH_ && (nframes == 1 || fstride >= fbytes)) {
                 ORBB_CUDA(cudaMemcpy2DAsync(h->d_color + (size_t)f0 * fbytes, fbytes, imgs_host + (size_t)f0 * fstride,
                                             nf > 1 ? fstride : fbytes, fbytes, nf, cudaMemcpyHostToDevice, h->s_in));
             } else {
                 for (int f = f0; f < f0 + nf; f++)
-                    ORBB_CUDA(cudaMemcpy2DAsync(h->d_color + (size_t)f * fbytes, (size_t)w * CH_, imgs_host + (size_t)f * fstride, stride,
-                                                (size_t)w * CH_, ht, cudaMemcpyHostToDevice, h->s_in));
+                    ORBB_CUDA(cudaMemcpy2DAsync(h->d_color + (size_t)f * fbytes, (size_t)in_w * CH_, imgs_host + (size_t)f * fstride, stride,
+                                                (size_t)in_w * CH_, in_h, cudaMemcpyHostToDevice, h->s_in));
             }
             ORBB_CUDA(cudaEventRecord(h->ev_in[c], h->s_in));
             continue;
@@ -719,7 +726,12 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
         const int ks = c % h->n_kstreams;
         cudaStream_t kst = ks ? h->s_k[ks - 1] : st;
         ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
-        if (channels > 1) {
+        if (remap) {
+            const size_t fbytes = (size_t)in_w * in_h;
+            remap_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nf), 128, 0, kst>>>(h->d_color + (size_t)f0 * fbytes, (long long)in_w, (long long)fbytes, in_w, in_h,
+                h->d_map, w, h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
+            ORBB_LAUNCHED();
+        } else if (channels > 1) {
             const size_t fbytes = (size_t)w * ht * CH_;
             cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nf), 128, 0, kst>>>(h->d_color + (size_t)f0 * fbytes, (long long)((size_t)w * CH_), (long long)fbytes,
                 w, channels, rgb_order, h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
@@ -736,7 +748,11 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
     }
     if (prof) {
         ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_in[nchunks - 1], 0));
-        if (channels > 1) {
+        if (remap) {
+            remap_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nframes), 128, 0, st>>>(h->d_color, (long long)in_w, (long long)((size_t)in_w * in_h), in_w, in_h,
+                h->d_map, w, h->d_pyr + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
+            ORBB_LAUNCHED();
+        } else if (channels > 1) {
             const size_t fbytes = (size_t)w * ht * CH_;
             cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nframes), 128, 0, st>>>(h->d_color, (long long)((size_t)w * CH_), (long long)fbytes,
                 w, channels, rgb_order, h->d_pyr + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
@@ -781,7 +797,7 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
 extern "C" int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
                                   size_t fstride, orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity)
 {
-    return extract_batch_impl(h, imgs_host, nframes, w, ht, stride, fstride, 1, 0, kps_host, desc_host, counts_host, capacity);
+    return extract_batch_impl(h, imgs_host, nframes, w, ht, stride, fstride, 1, 0, 0, 0, kps_host, desc_host, counts_host, capacity);
 }
 
 extern "C" int orbx_extract_batch_color(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int ht, size_t stride,
@@ -789,7 +805,66 @@ extern "C" int orbx_extract_batch_color(orbx_handle* h, const uint8_t* imgs_host
                                         int32_t* counts_host, int capacity)
 {
     if (channels != 3 && channels != 4) return ORBB_E_INVALID;
-    return extract_batch_impl(h, imgs_host, nframes, w, ht, stride, fstride, channels, rgb_order ? 1 : 0, kps_host, desc_host, counts_host, capacity);
+    return extract_batch_impl(h, imgs_host, nframes, w, ht, stride, fstride, channels, rgb_order ? 1 : 0, 0, 0, kps_host, desc_host, counts_host, capacity);
+}
+
+// cv::remap's conversion of float maps to fixed point (imgproc/imgwarp.cpp, INTER_BITS = 5): cvRound(map * 32), round half to even.
+static void fixed_point_map(const float* mapx, const float* mapy, size_t n, std::vector<int2>& out)
+{
+    out.resize(n);
+    for (size_t i = 0; i < n; i++) out[i] = make_int2((int)nearbyintf(mapx[i] * 32.f), (int)nearbyintf(mapy[i] * 32.f));
+}
+
+extern "C" int orbx_set_rectification(orbx_handle* h, const float* mapx_host, const float* mapy_host, int dst_w, int dst_h, int src_w, int src_h)
+{
+    if (!h) return ORBB_E_INVALID;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    ORBB_CUDA(cudaStreamSynchronize(h->stream));
+    if (!mapx_host && !mapy_host) {             // clear
+        cudaFree(h->d_map); h->d_map = nullptr; h->map_w = h->map_h = h->map_sw = h->map_sh = 0;
+        return ORBB_OK;
+    }
+    if (!mapx_host || !mapy_host) return ORBB_E_INVALID;
+    if (dst_w < 1 || dst_h < 1 || src_w < 1 || src_h < 1 || dst_w > h->cfg.max_width || dst_h > h->cfg.max_height) return ORBB_E_BAD_SHAPE;
+    std::vector<int2> m;
+    fixed_point_map(mapx_host, mapy_host, (size_t)dst_w * dst_h, m);
+    cudaFree(h->d_map); h->d_map = nullptr;
+    const int rc = dev_alloc(&h->d_map, m.size());
+    if (rc != ORBB_OK) return rc;
+    ORBB_CUDA(cudaMemcpy(h->d_map, m.data(), m.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    h->map_w = dst_w; h->map_h = dst_h; h->map_sw = src_w; h->map_sh = src_h;
+    return ORBB_OK;
+}
+
+extern "C" int orbx_extract_batch_rectified(orbx_handle* h, const uint8_t* raw_host, int nframes, size_t stride, size_t fstride,
+                                            orbx_keypoint* kps_host, uint8_t* desc_host, int32_t* counts_host, int capacity)
+{
+    if (!h) return ORBB_E_INVALID;
+    if (!h->d_map) return ORBB_E_STATE;
+    return extract_batch_impl(h, raw_host, nframes, h->map_w, h->map_h, stride, fstride, 1, 0, h->map_sw, h->map_sh, kps_host, desc_host, counts_host, capacity);
+}
+
+extern "C" int orbx_remap_device(const uint8_t* src_dev, int nframes, int src_w, int src_h, size_t src_stride, size_t src_fstride,
+                                 const float* mapx_host, const float* mapy_host, int dst_w, int dst_h,
+                                 uint8_t* dst_dev, size_t dst_stride, size_t dst_fstride, void* stream)
+{
+    if (!src_dev || !dst_dev || !mapx_host || !mapy_host || nframes < 1) return ORBB_E_INVALID;
+    if (src_w < 1 || src_h < 1 || dst_w < 1 || dst_h < 1 || src_stride < (size_t)src_w || dst_stride < (size_t)dst_w) return ORBB_E_BAD_SHAPE;
+    std::vector<int2> m;
+    fixed_point_map(mapx_host, mapy_host, (size_t)dst_w * dst_h, m);
+    int2* d_map = nullptr;
+    ORBB_CUDA(cudaMalloc((void**)&d_map, m.size() * sizeof(int2)));
+    cudaError_t e = cudaMemcpyAsync(d_map, m.data(), m.size() * sizeof(int2), cudaMemcpyHostToDevice, (cudaStream_t)stream);
+    if (e == cudaSuccess) {
+        remap_kernel<<<dim3(ceil_div(dst_w, 4 * 128), dst_h, nframes), 128, 0, (cudaStream_t)stream>>>(src_dev, (long long)src_stride, (long long)src_fstride,
+            src_w, src_h, d_map, dst_w, dst_dev, (long long)dst_stride, (long long)dst_fstride);
+        ORBB_LAUNCHED();
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)stream);      // the temporary map must outlive the kernel
+    cudaFree(d_map);
+    if (e != cudaSuccess) { set_cuda_error(e, "orbx_remap_device"); return ORBB_E_CUDA; }
+    return ORBB_OK;
 }
 
 extern "C" int orbx_cvt_gray_device(const uint8_t* src_dev, int nframes, int w, int ht, size_t src_stride, size_t src_fstride,

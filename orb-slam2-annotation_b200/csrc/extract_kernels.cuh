@@ -60,6 +60,38 @@ __global__ void __launch_bounds__(128) cvt_gray_kernel(const uint8_t* __restrict
 }
 
 // =====================================================================================================
+// cv::remap(src, dst, map1, map2, INTER_LINEAR), BORDER_CONSTANT 0 — stereo rectification in front of the extractor
+// (Examples/Stereo/stereo_euroc.cc:174-185).  The map arrives in cv::remap's own fixed point (1/32 pixel); the
+// bilinear weights (32-fx)(32-fy)*32 ... sum to 2^15; out = (sum w*p + 2^14) >> 15.  A thread produces four pixels and one
+// 32-bit store; the map (8 B per pixel, shared by all frames of the batch) stays in L2.
+// =====================================================================================================
+__global__ void __launch_bounds__(128) remap_kernel(const uint8_t* __restrict__ src, long long spitch, long long sfstride, int sw, int sh,
+                                                    const int2* __restrict__ map, int dw, uint8_t* __restrict__ dst, long long dpitch, long long dfstride)
+{
+    const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x), y = blockIdx.y, f = blockIdx.z;
+    if (x >= dw) return;
+    const uint8_t* s = src + (long long)f * sfstride;
+    uint8_t* d = dst + (long long)f * dfstride + (long long)y * dpitch + x;
+    const int n = min(4, dw - x);
+    unsigned g[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if (i >= n) break;
+        const int2 m = __ldg(map + (long long)y * dw + x + i);
+        const int ix = max(-32768, min(32767, m.x >> 5)), iy = max(-32768, min(32767, m.y >> 5));
+        const int fx = m.x & 31, fy = m.y & 31;
+        const bool x0 = ix >= 0 && ix < sw, x1 = ix + 1 >= 0 && ix + 1 < sw, y0 = iy >= 0 && iy < sh, y1 = iy + 1 >= 0 && iy + 1 < sh;
+        const uint8_t* r0 = s + (long long)iy * spitch + ix;
+        const uint8_t* r1 = r0 + spitch;
+        const int p00 = (x0 && y0) ? r0[0] : 0, p01 = (x1 && y0) ? r0[1] : 0, p10 = (x0 && y1) ? r1[0] : 0, p11 = (x1 && y1) ? r1[1] : 0;
+        const int acc = ((32 - fx) * (32 - fy) * p00 + fx * (32 - fy) * p01 + (32 - fx) * fy * p10 + fx * fy * p11) * 32;
+        g[i] = (unsigned)((acc + (1 << 14)) >> 15);
+    }
+    if (n == 4 && ((uintptr_t)d & 3) == 0) *reinterpret_cast<unsigned*>(d) = g[0] | (g[1] << 8) | (g[2] << 16) | (g[3] << 24);
+    else for (int i = 0; i < n; i++) d[i] = (uint8_t)g[i];
+}
+
+// =====================================================================================================
 // Octree distribution (ORBextractor.cpp:541-770).  Order-free formulation: the reference's result depends on the
 // keypoint ORDER only through "first maximum wins" inside a leaf (:751-767); since vKeys order is always the
 // cell-row-major / pixel-row-major input order (stable partitions, :512-528), the winner is the max-response point

@@ -25,7 +25,7 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 # every symbol include/orbb200.h declares (tests check the .so exports all of them)
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
            "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
-           "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
+           "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbx_set_rectification", "orbx_extract_batch_rectified", "orbx_remap_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
@@ -68,6 +68,9 @@ def lib():
         L.orbx_extract_batch.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32]
         L.orbx_extract_batch_color.argtypes = [vp, vp, i32, i32, i32, sz, sz, i32, i32, vp, vp, vp, i32]
         L.orbx_cvt_gray_device.argtypes = [vp, i32, i32, i32, sz, sz, i32, i32, vp, sz, sz, vp]
+        L.orbx_set_rectification.argtypes = [vp, vp, vp, i32, i32, i32, i32]
+        L.orbx_extract_batch_rectified.argtypes = [vp, vp, i32, sz, sz, vp, vp, vp, i32]
+        L.orbx_remap_device.argtypes = [vp, i32, i32, i32, sz, sz, vp, vp, i32, i32, vp, sz, sz, vp]
         L.orbx_sync.argtypes = [vp]
         L.orbx_set_profiling.argtypes = [vp, i32]
         L.orbx_get_profile.argtypes = [vp, vp, C.POINTER(i32)]
@@ -236,6 +239,26 @@ class ORBextractor:
         counts = np.zeros(F, np.int32)
         _check(self.L.orbx_extract_batch_color(self.h, _p(images), F, w, h, w * ch, w * h * ch, ch, 1 if rgb_order else 0,
                                                _p(kps), _p(desc), _p(counts), cap), "orbx_extract_batch_color")
+        return [(kps[f, :counts[f]].copy(), desc[f, :counts[f]].copy()) for f in range(F)]
+
+    def set_rectification(self, mapx, mapy, src_size):
+        """Store cv::initUndistortRectifyMap's CV_32F maps (dst_h x dst_w each) for raw frames of src_size = (w, h); None clears."""
+        if mapx is None:
+            _check(self.L.orbx_set_rectification(self.h, None, None, 0, 0, 0, 0), "orbx_set_rectification")
+            return
+        mapx = np.ascontiguousarray(mapx, np.float32); mapy = np.ascontiguousarray(mapy, np.float32)
+        dh, dw = mapx.shape
+        _check(self.L.orbx_set_rectification(self.h, _p(mapx), _p(mapy), dw, dh, src_size[0], src_size[1]), "orbx_set_rectification")
+
+    def extract_batch_rectified(self, raw, capacity=None):
+        """raw: (F, src_h, src_w) uint8 host frames; cv::remap INTER_LINEAR on the device (stereo_euroc.cc:174-185), then extract."""
+        raw = np.ascontiguousarray(raw, np.uint8)
+        F, h, w = raw.shape
+        cap = capacity or self.default_capacity
+        kps = np.zeros((F, cap), KP_DTYPE)
+        desc = np.zeros((F, cap, 32), np.uint8)
+        counts = np.zeros(F, np.int32)
+        _check(self.L.orbx_extract_batch_rectified(self.h, _p(raw), F, w, w * h, _p(kps), _p(desc), _p(counts), cap), "orbx_extract_batch_rectified")
         return [(kps[f, :counts[f]].copy(), desc[f, :counts[f]].copy()) for f in range(F)]
 
     def extract_batch_device(self, imgs_ptr, F, w, h, stride, fstride, kps_ptr, desc_ptr, counts_ptr, capacity):

@@ -14,6 +14,10 @@ pinned against outputs of the real implementations, generated here and committed
                   per code plus the sha256 of the gray image of all 2^24 RGB colours.  (python make_golden.py --cvtcolor
                   regenerates only this file.)
 
+  cv2_remap.npz   cv2.remap INTER_LINEAR with float maps (stereo rectification, Examples/Stereo/stereo_euroc.cc:174-185): a
+                  rectification-like map (cv2.initUndistortRectifyMap of a distorted pinhole camera) and a hostile map (fractions
+                  on every 1/32 step, out-of-range and negative coordinates).  (python make_golden.py --remap regenerates it.)
+
 Inputs are regenerated from seeds by synth.py (numpy only), so only outputs are stored.  Usage: python tests/golden/make_golden.py
 """
 import hashlib
@@ -78,6 +82,37 @@ def main_cvtcolor():
     print("cv2_cvtcolor.npz", os.path.getsize(os.path.join(HERE, "cv2_cvtcolor.npz")), "bytes")
 
 
+def remap_inputs():
+    """(image, [(mapx, mapy), ...]) — maps are regenerated here, not stored: pure numpy / float32 formulas."""
+    img = synth(188, 120, 31)
+    h, w = img.shape
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    rng = np.random.default_rng(32)
+    hostile_x = (xx + rng.integers(-40, 40, (h, w)).astype(np.float32) / np.float32(32) * rng.integers(0, 33, (h, w)).astype(np.float32) - np.float32(3)).astype(np.float32)
+    hostile_y = (yy + rng.integers(-40, 40, (h, w)).astype(np.float32) / np.float32(32) * rng.integers(0, 33, (h, w)).astype(np.float32) + np.float32(2)).astype(np.float32)
+    hostile_x[::7, ::5] = np.float32(-1.5); hostile_y[::11, ::3] = np.float32(h + 0.25); hostile_x[3::9, 1::4] = np.float32(w - 1 + 0.5)
+    return img, hostile_x, hostile_y
+
+
+def rectify_maps(cv2, w, h):
+    K = np.array([[0.61 * w, 0, 0.49 * w], [0, 0.61 * w, 0.52 * h], [0, 0, 1]], np.float64)
+    D = np.array([-0.28, 0.07, 0.0002, 0.00002, 0.0], np.float64)
+    R = cv2.Rodrigues(np.array([0.01, -0.02, 0.005]))[0]
+    P = np.array([[0.58 * w, 0, 0.5 * w, 0], [0, 0.58 * w, 0.5 * h, 0], [0, 0, 1, 0]], np.float64)
+    return cv2.initUndistortRectifyMap(K, D, R, P[:3, :3], (w, h), cv2.CV_32F)
+
+
+def main_remap():
+    import cv2
+    img, hx, hy = remap_inputs()
+    h, w = img.shape
+    rx, ry = rectify_maps(cv2, w, h)
+    out = {"cv2_version": np.array(cv2.__version__), "rect_mapx": rx, "rect_mapy": ry,
+           "rect_out": cv2.remap(img, rx, ry, cv2.INTER_LINEAR), "hostile_out": cv2.remap(img, hx, hy, cv2.INTER_LINEAR)}
+    np.savez_compressed(os.path.join(HERE, "cv2_remap.npz"), **out)
+    print("cv2_remap.npz", os.path.getsize(os.path.join(HERE, "cv2_remap.npz")), "bytes")
+
+
 def main():
     import cv2
     cv2.setNumThreads(1)
@@ -132,6 +167,9 @@ def main():
 
 
 if __name__ == "__main__":
-    if "--cvtcolor" not in sys.argv:
+    if "--cvtcolor" not in sys.argv and "--remap" not in sys.argv:
         main()
-    main_cvtcolor()
+    if "--remap" not in sys.argv:
+        main_cvtcolor()
+    if "--cvtcolor" not in sys.argv:
+        main_remap()

@@ -345,3 +345,40 @@ def test_multi_chunk_pipeline(gpu):
     out = exb.extract_batch_color(np.ascontiguousarray(col), rgb_order=False)
     for f in range(F):
         assert out[f][0].tobytes() == single[f % ND][0].tobytes() and np.array_equal(out[f][1], single[f % ND][1]), f"colour frame {f}"
+
+
+def test_rectified_frames(gpu):
+    """SURVEY 8(f)-4, second half: cv::remap (stereo rectification, stereo_euroc.cc:174-185) on the device.  The device remap is
+    bit-equal to cv2's committed output and to the oracle restatement; the rectified entry point returns exactly what the grey
+    entry point returns on the oracle-rectified frames (raw frames larger than the rectified ones, several frames)."""
+    import torch, orbb200, pyoracle
+    from synth import synth
+    gen, _, _ = _golden()
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cv2_remap.npz"))
+    img, hx, hy = gen.remap_inputs()
+    h, w = img.shape
+    for mx, my, want in ((g["rect_mapx"], g["rect_mapy"], g["rect_out"]), (hx, hy, g["hostile_out"])):
+        d_src = torch.from_numpy(img).cuda(); d_dst = torch.zeros((h, w), dtype=torch.uint8, device="cuda")
+        rc = orbb200.lib().orbx_remap_device(d_src.data_ptr(), 1, w, h, w, w * h, mx.ctypes.data, my.ctypes.data, w, h, d_dst.data_ptr(), w, w * h, None)
+        assert rc == 0
+        assert np.array_equal(d_dst.cpu().numpy(), want)
+    # a camera-sized case: raw 800x520 frames rectified into 752x480
+    sw, sh, dw, dh, F = 800, 520, 752, 480, 3
+    raw = np.stack([synth(sw, sh, 600 + i) for i in range(F)])
+    yy, xx = np.mgrid[0:dh, 0:dw].astype(np.float32)
+    cx, cy = np.float32(dw / 2), np.float32(dh / 2)
+    r2 = ((xx - cx) ** 2 + (yy - cy) ** 2) / np.float32(dw * dw)
+    mapx = (xx + 24 + (xx - cx) * (np.float32(0.08) * r2)).astype(np.float32)
+    mapy = (yy + 20 + (yy - cy) * (np.float32(0.08) * r2)).astype(np.float32)
+    rect = np.stack([pyoracle.remap(raw[f], mapx, mapy) for f in range(F)])
+    ex = orbb200.ORBextractor(1200, max_size=(dw, dh), max_batch=F)
+    want = ex.extract_batch(rect)
+    ex.set_rectification(mapx, mapy, (sw, sh))
+    got = ex.extract_batch_rectified(raw)
+    for (k1, d1), (k2, d2) in zip(want, got):
+        assert len(k1) > 500 and k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
+    assert np.array_equal(ex.pyramid_level(0, frame=1), rect[1])       # mImGray the caller keeps = the rectified frame
+    ex.set_rectification(None, None, None)
+    kps = np.zeros((F, 10), orbb200.KP_DTYPE); desc = np.zeros((F, 10, 32), np.uint8); cnt = np.zeros(F, np.int32)
+    assert orbb200.lib().orbx_extract_batch_rectified(ex.h, raw.ctypes.data, F, sw, sw * sh, kps.ctypes.data, desc.ctypes.data, cnt.ctypes.data, 10) == orbb200.E_STATE
