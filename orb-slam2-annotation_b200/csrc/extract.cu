@@ -705,12 +705,7 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
         }
         const uint8_t* cbase = pinned ? imgs_host : h->h_img;
         const size_t cstride = pinned ? stride : (size_t)w, cfstride = pinned ? fstride : (size_t)w * ht;
-        static const int h2d_mode = getenv("ORBB_H2D_MODE") ? atoi(getenv("ORBB_H2D_MODE")) : 0;
-        if (packed && h2d_mode == 1) {
-            for (int f = f0; f < f0 + nf; f++)
-                ORBB_CUDA(cudaMemcpyAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, cbase + (size_t)f * cfstride, (size_t)w * ht,
-                                          cudaMemcpyHostToDevice, h->s_in));
-        } else if (packed) {
+        if (packed) {
             ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, h->pyr_fstride, cbase + (size_t)f0 * cfstride,
                                         nf > 1 ? cfstride : (size_t)w * ht, (size_t)w * ht, nf, cudaMemcpyHostToDevice, h->s_in));
         } else {

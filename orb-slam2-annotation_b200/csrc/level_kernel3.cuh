@@ -57,12 +57,6 @@ __device__ __forceinline__ int l3_reflect101(int p, int n)
     return min(max(p, 0), n - 1);
 }
 
-// per byte: bit 7 set where x > t (0 <= t <= 126); other bits are garbage (callers mask with 0x80808080)
-__device__ __forceinline__ unsigned l3_gt_raw(unsigned x, unsigned t1 /* (t+1) * 0x01010101 */)
-{
-    return (((x & 0x7f7f7f7fu) | 0x80808080u) - t1) | x;
-}
-
 // Threshold-independent FAST arc score m = max over the 16 arcs of 9 contiguous ring pixels of
 // max(min(v - p_k), min(p_k - v)); cv::FAST's response is m - 1 and a pixel is a corner at threshold t iff m > t.
 // Both polarities ride in one register as biased u16 halves: lo = 256 + v - p_k, hi = 256 - v + p_k.

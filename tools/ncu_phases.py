@@ -27,7 +27,6 @@ for (ln, text), a in agg.items():
     if body and ln >= marks[0][1] and ln < marks[-1][1]:
         for i in range(len(marks) - 1):
             if marks[i][1] <= ln < marks[i + 1][1]: add(marks[i][0], a)
-    elif body and find('l3_gt_raw(unsigned') <= ln <= find('l3_gt_raw(unsigned') + 3: add('reject', a)
     elif body and find('l3_arc_score(const') <= ln <= find('l3_arc_score(const') + 24: add('score', a)
     elif body and find('l3_reflect101(int') <= ln <= find('l3_reflect101(int') + 5: add('stage', a)
     elif body and find('l3_pack4(int') <= ln <= find('l3_pack4(int') + 3: add('blur', a)
