@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
         unsigned m0 = 0, m1 = 0;                                  // private candidate flags: 4 bits per row, rows it = 0..7 | 8
         constexpr int NIT = (TH + 2 + NW - 1) / NW;
         static_assert(NIT <= 9, "candidate masks hold 9 rows per warp");
-#pragma unroll 3
+#pragma unroll 9
         for (int it = 0; it < NIT; it++) {                                           // (partly rolled: instruction-cache footprint)
             const int s = warp - 1 + NW * it;
             const int gy = y0 + s;
