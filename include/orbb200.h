@@ -196,6 +196,18 @@ typedef struct orbm_proj_query {
     float angle;            /* LastFrame.mvKeysUn[i].angle, for the rotation histogram (a11)                */
 } orbm_proj_query;
 
+/* ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, vector<pair<size_t,size_t>>& vMatchedPairs,
+ * const bool bOnlyStereo) (ORBmatcher.cpp:755-927).  kps_un* = mvKeysUn, uright* = mvuRight (may be NULL for monocular KeyFrames
+ * unless only_stereo), has_mp*[i] != 0 iff GetMapPoint(i) is set; F12 = the fundamental matrix, 9 floats row-major; (ex, ey) = the
+ * epipole of KeyFrame 1 in KeyFrame 2 as computed at :763-769; scale_factors2 = pKF2->mvScaleFactors, level_sigma2_2 =
+ * pKF2->mvLevelSigma2.  match12[n1] = vMatches12 (KeyFrame-2 feature or -1): vMatchedPairs is its list of (i, match12[i]). */
+int orbm_search_for_triangulation(const uint8_t* desc1, const orbx_keypoint* kps_un1, const float* uright1, const uint8_t* has_mp1, int n1,
+                                  const int32_t* fv1_nodes, const int32_t* fv1_off, const int32_t* fv1_feat, int nfv1,
+                                  const uint8_t* desc2, const orbx_keypoint* kps_un2, const float* uright2, const uint8_t* has_mp2, int n2,
+                                  const int32_t* fv2_nodes, const int32_t* fv2_off, const int32_t* fv2_feat, int nfv2,
+                                  const float* F12, float ex, float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                  int only_stereo, int check_orientation, int32_t* match12, int* nmatches, int device);
+
 /* the relocalisation, loop-closing and fusion variants.  The caller projects (pose algebra,
  * PredictScale, frustum tests) exactly as the reference does and hands over one orbm_proj_query per surviving MapPoint:
  * q.u, q.v, q.r = th * mvScaleFactors[nPredictedLevel], q.min_level / q.max_level = the octave window of the variant.

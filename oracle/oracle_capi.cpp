@@ -168,6 +168,17 @@ int orc_search_by_bow_kf(const uint8_t* d1, const float* a1, const uint8_t* h1, 
     return n;
 }
 
+int orc_search_for_triangulation(const uint8_t* d1, const KeyPoint* k1, const float* ur1, const uint8_t* h1, int n1, const int32_t* a0, const int32_t* a1, const int32_t* a2, int na,
+                                 const uint8_t* d2, const KeyPoint* k2, const float* ur2, const uint8_t* h2, int n2, const int32_t* b0, const int32_t* b1, const int32_t* b2, int nb,
+                                 const float* F12, float ex, float ey, const float* sf2, const float* ls2, int onlyStereo, int checkOri, int32_t* matches)
+{
+    std::vector<int> m;
+    const int n = SearchForTriangulation(d1, k1, ur1, h1, n1, fv_from_csr(a0, a1, a2, na), d2, k2, ur2, h2, n2, fv_from_csr(b0, b1, b2, nb),
+                                         F12, ex, ey, sf2, ls2, onlyStereo != 0, checkOri != 0, m);
+    for (int i = 0; i < n1; i++) matches[i] = m[i];
+    return n;
+}
+
 struct orc_frame { FrameGrid g; std::vector<KeyPoint> kps; std::vector<uint8_t> desc; };
 orc_frame* orc_frame_create(const KeyPoint* kps, const uint8_t* desc, int n, float minx, float miny, float maxx, float maxy)
 {

@@ -1,7 +1,7 @@
 // oracle/orb_match_oracle.hpp — TEST INFRASTRUCTURE (CPU oracle), never linked into the product.
 //
 // CPU restatement of the Hamming-matching half of the hot path.  Reference files followed:
-//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :205-348 :604-743 (SearchByBoW) :352-472 :962-1251 (Fuse) :1253-1500 (SearchBySim3) :1661-1789 :474-590 :1506-1659 :1792-1854
+//   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :166-190 :205-348 :604-743 (SearchByBoW) :755-927 (SearchForTriangulation) :352-472 :962-1251 (Fuse) :1253-1500 (SearchBySim3) :1661-1789 :474-590 :1506-1659 :1792-1854
 //   ORB-SLAM2/src/Frame.cpp       :241-257 :379-444 :540-748
 //   ORB-SLAM2/src/MapPoint.cpp    :302-380 (ComputeDistinctiveDescriptors)
 // ORBmatcher.cpp / Frame.cpp cannot be compiled here (they pull in KeyFrame/MapPoint/DBoW2/OpenCV/Eigen),
@@ -242,6 +242,87 @@ static inline int SearchByBoW_KF(const uint8_t* Descriptors1, const float* angle
         for (int i = 0; i < HISTO_LENGTH; i++) {
             if (i == ind1 || i == ind2 || i == ind3) continue;
             for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) { vpMatches12[rotHist[i][j]] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
+// ORBmatcher::CheckDistEpipolarLine (ORBmatcher.cpp:166-190); F12 row-major.
+static inline bool CheckDistEpipolarLine(const KeyPoint& kp1, const KeyPoint& kp2, const float* F12, const float* mvLevelSigma2_2)
+{
+    const float a = kp1.x * F12[0 * 3 + 0] + kp1.y * F12[1 * 3 + 0] + F12[2 * 3 + 0];
+    const float b = kp1.x * F12[0 * 3 + 1] + kp1.y * F12[1 * 3 + 1] + F12[2 * 3 + 1];
+    const float c = kp1.x * F12[0 * 3 + 2] + kp1.y * F12[1 * 3 + 2] + F12[2 * 3 + 2];
+    const float num = a * kp2.x + b * kp2.y + c;
+    const float den = a * a + b * b;
+    if (den == 0) return false;
+    const float dsqr = num * num / den;
+    return dsqr < 3.84 * mvLevelSigma2_2[kp2.octave];
+}
+
+// ORBmatcher::SearchForTriangulation (ORBmatcher.cpp:755-927) on flattened arrays; hasMP* = GetMapPoint(i) != NULL.
+static inline int SearchForTriangulation(const uint8_t* desc1, const KeyPoint* kps1, const float* mvuRight1, const uint8_t* hasMP1, int N1,
+                                         const std::map<unsigned, std::vector<unsigned> >& vFeatVec1,
+                                         const uint8_t* desc2, const KeyPoint* kps2, const float* mvuRight2, const uint8_t* hasMP2, int N2,
+                                         const std::map<unsigned, std::vector<unsigned> >& vFeatVec2,
+                                         const float* F12, float ex, float ey, const float* mvScaleFactors2, const float* mvLevelSigma2_2,
+                                         bool bOnlyStereo, bool mbCheckOrientation, std::vector<int>& vMatches12)
+{
+    int nmatches = 0;
+    std::vector<bool> vbMatched2(N2, false);
+    vMatches12.assign(N1, -1);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = HISTO_LENGTH / 360.0f;
+    std::map<unsigned, std::vector<unsigned> >::const_iterator f1it = vFeatVec1.begin(), f2it = vFeatVec2.begin();
+    const std::map<unsigned, std::vector<unsigned> >::const_iterator f1end = vFeatVec1.end(), f2end = vFeatVec2.end();
+    while (f1it != f1end && f2it != f2end) {
+        if (f1it->first == f2it->first) {
+            for (size_t i1 = 0, iend1 = f1it->second.size(); i1 < iend1; i1++) {
+                const size_t idx1 = f1it->second[i1];
+                if (hasMP1[idx1]) continue;
+                const bool bStereo1 = mvuRight1 && mvuRight1[idx1] >= 0;
+                if (bOnlyStereo) if (!bStereo1) continue;
+                const KeyPoint& kp1 = kps1[idx1];
+                const uint8_t* d1 = desc1 + idx1 * 32;
+                int bestDist = TH_LOW, bestIdx2 = -1;
+                for (size_t i2 = 0, iend2 = f2it->second.size(); i2 < iend2; i2++) {
+                    size_t idx2 = f2it->second[i2];
+                    if (vbMatched2[idx2] || hasMP2[idx2]) continue;
+                    const bool bStereo2 = mvuRight2 && mvuRight2[idx2] >= 0;
+                    if (bOnlyStereo) if (!bStereo2) continue;
+                    const int dist = DescriptorDistance(d1, desc2 + idx2 * 32);
+                    if (dist > TH_LOW || dist > bestDist) continue;
+                    const KeyPoint& kp2 = kps2[idx2];
+                    if (!bStereo1 && !bStereo2) {
+                        const float distex = ex - kp2.x, distey = ey - kp2.y;
+                        if (distex * distex + distey * distey < 100 * mvScaleFactors2[kp2.octave]) continue;
+                    }
+                    if (CheckDistEpipolarLine(kp1, kp2, F12, mvLevelSigma2_2)) { bestIdx2 = (int)idx2; bestDist = dist; }
+                }
+                if (bestIdx2 >= 0) {
+                    const KeyPoint& kp2 = kps2[bestIdx2];
+                    vMatches12[idx1] = bestIdx2;
+                    vbMatched2[bestIdx2] = true;
+                    nmatches++;
+                    if (mbCheckOrientation) {
+                        float rot = kp1.angle - kp2.angle;
+                        if (rot < 0.0) rot += 360.0f;
+                        int bin = (int)round(rot * factor);
+                        if (bin == HISTO_LENGTH) bin = 0;
+                        rotHist[bin].push_back((int)idx1);
+                    }
+                }
+            }
+            f1it++; f2it++;
+        } else if (f1it->first < f2it->first) f1it = vFeatVec1.lower_bound(f2it->first);
+        else f2it = vFeatVec2.lower_bound(f1it->first);
+    }
+    if (mbCheckOrientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        ComputeThreeMaxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0, jend = rotHist[i].size(); j < jend; j++) { vMatches12[rotHist[i][j]] = -1; nmatches--; }
         }
     }
     return nmatches;

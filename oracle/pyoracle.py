@@ -75,6 +75,7 @@ def lib():
         L.orc_fuse_best.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_search_by_bow.argtypes = [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 2 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int, C.c_float, C.c_int, C.c_void_p]
         L.orc_search_by_bow_kf.argtypes = ([C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int]) * 2 + [C.c_float, C.c_int, C.c_void_p]
+        L.orc_search_for_triangulation.argtypes = ([C.c_void_p] * 4 + [C.c_int] + [C.c_void_p] * 3 + [C.c_int]) * 2 + [C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.orc_frame_create.restype = C.c_void_p
         L.orc_frame_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]
         L.orc_frame_destroy.argtypes = [C.c_void_p]
@@ -283,6 +284,21 @@ def search_by_bow_kf(desc1, angle1, has1, fv1, desc2, angle2, has2, fv2, nnratio
     n = lib().orc_search_by_bow_kf(_p(desc1), _p(angle1), _p(has1), len(desc1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]),
                                    _p(desc2), _p(angle2), _p(has2), len(desc2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]),
                                    nnratio, 1 if check_ori else 0, _p(out))
+    return out, n
+
+
+def search_for_triangulation(desc1, kps1, ur1, has1, fv1, desc2, kps2, ur2, has2, fv2, F12, ex, ey, sf2, ls2, only_stereo=False, check_ori=True):
+    """ORBmatcher::SearchForTriangulation -> (vMatches12[n1], nmatches)."""
+    desc1 = np.ascontiguousarray(desc1, np.uint8); desc2 = np.ascontiguousarray(desc2, np.uint8)
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    ur1 = None if ur1 is None else np.ascontiguousarray(ur1, np.float32); ur2 = None if ur2 is None else np.ascontiguousarray(ur2, np.float32)
+    has1 = np.ascontiguousarray(has1, np.uint8); has2 = np.ascontiguousarray(has2, np.uint8)
+    a = [np.ascontiguousarray(x, np.int32) for x in fv1]; b = [np.ascontiguousarray(x, np.int32) for x in fv2]
+    F12 = np.ascontiguousarray(F12, np.float32); sf2 = np.ascontiguousarray(sf2, np.float32); ls2 = np.ascontiguousarray(ls2, np.float32)
+    out = np.zeros(len(desc1), np.int32)
+    n = lib().orc_search_for_triangulation(_p(desc1), _p(kps1), _p(ur1), _p(has1), len(desc1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]),
+                                           _p(desc2), _p(kps2), _p(ur2), _p(has2), len(desc2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]),
+                                           _p(F12), float(ex), float(ey), _p(sf2), _p(ls2), int(only_stereo), int(check_ori), _p(out))
     return out, n
 
 

@@ -544,6 +544,75 @@ extern "C" int orbm_search_by_bow_kf(const uint8_t* desc1, const float* angle1, 
     return ORBB_OK;
 }
 
+// ORBmatcher::CheckDistEpipolarLine (ORBmatcher.cpp:166-190): F12 row-major 3x3 floats.
+static bool check_dist_epipolar_line(const orbx_keypoint& kp1, const orbx_keypoint& kp2, const float* F12, const float* level_sigma2_2)
+{
+    const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+    const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+    const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+    const float num = a * kp2.x + b * kp2.y + c;
+    const float den = a * a + b * b;
+    if (den == 0) return false;
+    const float dsqr = num * num / den;
+    return dsqr < 3.84 * level_sigma2_2[kp2.octave];
+}
+
+// ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, vector<pair<size_t,size_t>>& vMatchedPairs,
+// bOnlyStereo) (ORBmatcher.cpp:755-927): features WITHOUT a MapPoint on both sides (:793-796, :815-818), optional stereo-only,
+// dist <= TH_LOW and <= the best so far (:829-830), the epipole proximity test for mono pairs (:834-840), the epipolar-line test
+// (:842-846), vbMatched2, rotation histogram.  Distances of the common vocabulary nodes come from the device join.
+extern "C" int orbm_search_for_triangulation(const uint8_t* desc1, const orbx_keypoint* kps_un1, const float* uright1, const uint8_t* has_mp1, int n1,
+                                             const int32_t* fv1_nodes, const int32_t* fv1_off, const int32_t* fv1_feat, int nfv1,
+                                             const uint8_t* desc2, const orbx_keypoint* kps_un2, const float* uright2, const uint8_t* has_mp2, int n2,
+                                             const int32_t* fv2_nodes, const int32_t* fv2_off, const int32_t* fv2_feat, int nfv2,
+                                             const float* F12, float ex, float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                             int only_stereo, int check_ori, int32_t* match12, int* nmatches, int device)
+{
+    if (!nmatches || !F12 || !scale_factors2 || !level_sigma2_2 || (n1 > 0 && (!match12 || !kps_un1 || !has_mp1)) || (n2 > 0 && (!kps_un2 || !has_mp2)))
+        return ORBB_E_INVALID;
+    if (only_stereo && ((n1 > 0 && !uright1) || (n2 > 0 && !uright2))) return ORBB_E_INVALID;
+    // KeyFrame-1 features that take part: no MapPoint yet, and stereo when bOnlyStereo (:793-802)
+    std::vector<uint8_t> a_ok((size_t)(n1 > 0 ? n1 : 0));
+    for (int i = 0; i < n1; i++) a_ok[i] = (!has_mp1[i] && (!only_stereo || uright1[i] >= 0)) ? 1 : 0;
+    std::vector<int4> entries; std::vector<uint16_t> dist;
+    const int rc = bow_join(desc1, a_ok.data(), n1, fv1_nodes, fv1_off, fv1_feat, nfv1, desc2, n2, fv2_nodes, fv2_off, fv2_feat, nfv2, device, entries, dist);
+    if (rc != ORBB_OK) return rc;
+    *nmatches = 0;
+    for (int i = 0; i < n1; i++) match12[i] = -1;
+    std::vector<uint8_t> vbMatched2((size_t)n2, 0);
+    std::vector<int> rotHist[HISTO_LENGTH];
+    int nm = 0;
+    for (const int4& en : entries) {
+        const int idx1 = en.x;
+        const bool bStereo1 = uright1 && uright1[idx1] >= 0;
+        const orbx_keypoint& kp1 = kps_un1[idx1];
+        int bestDist = TH_LOW, bestIdx2 = -1;
+        for (int j = 0; j < en.z; j++) {
+            const int idx2 = fv2_feat[en.y + j];
+            if (vbMatched2[idx2] || has_mp2[idx2]) continue;                            // :815-818
+            const bool bStereo2 = uright2 && uright2[idx2] >= 0;
+            if (only_stereo && !bStereo2) continue;
+            const int d = dist[(size_t)en.w + j];
+            if (d > TH_LOW || d > bestDist) continue;                                   // :829-830
+            const orbx_keypoint& kp2 = kps_un2[idx2];
+            if (!bStereo1 && !bStereo2) {                                               // :834-840
+                const float distex = ex - kp2.x, distey = ey - kp2.y;
+                if (distex * distex + distey * distey < 100 * scale_factors2[kp2.octave]) continue;
+            }
+            if (check_dist_epipolar_line(kp1, kp2, F12, level_sigma2_2)) { bestIdx2 = idx2; bestDist = d; }
+        }
+        if (bestIdx2 >= 0) {
+            match12[idx1] = bestIdx2;
+            vbMatched2[bestIdx2] = 1;
+            nm++;
+            if (check_ori) rotHist[rot_bin(kp1.angle, kps_un2[bestIdx2].angle)].push_back(idx1);
+        }
+    }
+    if (check_ori) bow_rot_filter(rotHist, match12, nm);
+    *nmatches = nm;
+    return ORBB_OK;
+}
+
 extern "C" int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev_xy, int32_t* m12,
                                               int window, float nnratio, int check_ori, int* nmatches)
 {

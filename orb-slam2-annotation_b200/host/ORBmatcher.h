@@ -184,6 +184,30 @@ public:
         return n;
     }
 
+    // src/ORBmatcher.cpp:755-927: candidates are features without a MapPoint; F12 is the 3x3 fundamental matrix row-major (the CV_32F cv::Mat's data), (ex, ey) the
+    // projection of KF1's camera centre in KF2 (computed by the caller as the reference does at :765-772).  Returns the pair list.
+    int SearchForTriangulation(const cv::Mat& desc1, const std::vector<cv::KeyPoint>& keysUn1, const std::vector<float>& uRight1,
+                               const std::vector<uint8_t>& hasMapPoint1, const FeatVec& fv1, const cv::Mat& desc2,
+                               const std::vector<cv::KeyPoint>& keysUn2, const std::vector<float>& uRight2,
+                               const std::vector<uint8_t>& hasMapPoint2, const FeatVec& fv2, const float F12[9], float ex, float ey,
+                               const std::vector<float>& scaleFactors2, const std::vector<float>& levelSigma2_2,
+                               std::vector<std::pair<size_t, size_t> >& vMatchedPairs, bool bOnlyStereo, int device = 0) const
+    {
+        int n = 0;
+        std::vector<int32_t> m12(desc1.rows, -1);
+        orbm_check(orbm_search_for_triangulation(desc1.ptr(0), (const orbx_keypoint*)keysUn1.data(), uRight1.empty() ? nullptr : uRight1.data(), hasMapPoint1.data(),
+                                                 desc1.rows, fv1.nodes.data(), fv1.offsets.data(), fv1.features.data(), (int)fv1.nodes.size(),
+                                                 desc2.ptr(0), (const orbx_keypoint*)keysUn2.data(), uRight2.empty() ? nullptr : uRight2.data(), hasMapPoint2.data(),
+                                                 desc2.rows, fv2.nodes.data(), fv2.offsets.data(), fv2.features.data(), (int)fv2.nodes.size(), F12,
+                                                 ex, ey, scaleFactors2.data(), levelSigma2_2.data(), bOnlyStereo ? 1 : 0,
+                                                 mbCheckOrientation ? 1 : 0, m12.data(), &n, device), "orbm_search_for_triangulation");
+        vMatchedPairs.clear();
+        vMatchedPairs.reserve(n);
+        for (size_t i = 0; i < m12.size(); i++)           // :917-923
+            if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair(i, (size_t)m12[i]));
+        return n;
+    }
+
     static const int TH_LOW = 50;         // src/ORBmatcher.cpp:37-39
     static const int TH_HIGH = 100;
     static const int HISTO_LENGTH = 30;

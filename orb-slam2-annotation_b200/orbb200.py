@@ -26,7 +26,7 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
            "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbx_set_rectification", "orbx_extract_batch_rectified", "orbx_remap_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
-           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
+           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
@@ -97,6 +97,7 @@ def lib():
         L.orbm_search_by_projection_reloc.argtypes = [vp, vp, i32, i32, i32, vp, C.POINTER(i32)]
         L.orbm_search_by_projection_loop.argtypes = [vp, vp, i32, vp, C.POINTER(i32)]
         L.orbm_fuse_best.argtypes = [vp, vp, i32, vp, vp, i32, vp, vp]
+        L.orbm_search_for_triangulation.argtypes = ([vp] * 4 + [i32] + [vp] * 3 + [i32]) * 2 + [vp, f32, f32, vp, vp, i32, i32, vp, C.POINTER(i32), i32]
         L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, C.POINTER(i32)]
         L.orbm_stereo_match.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, f32, f32, vp, vp]
         L.orbm_db_create.argtypes = [C.POINTER(vp), C.c_int64, C.c_int64, i32]
@@ -348,6 +349,23 @@ def search_by_bow_kf(desc1, angle1, has1, fv1, desc2, angle2, has2, fv2, nnratio
     _check(lib().orbm_search_by_bow_kf(_p(desc1), _p(angle1), _p(has1), len(desc1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]),
                                        _p(desc2), _p(angle2), _p(has2), len(desc2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]),
                                        nnratio, 1 if check_ori else 0, _p(out), C.byref(n), device), "orbm_search_by_bow_kf")
+    return out, n.value
+
+
+def search_for_triangulation(desc1, kps1, ur1, has1, fv1, desc2, kps2, ur2, has2, fv2, F12, ex, ey, sf2, ls2, only_stereo=False, check_ori=True, device=0):
+    """ORBmatcher::SearchForTriangulation (ORBmatcher.cpp:755-927) -> (vMatches12[n1], nmatches)."""
+    desc1 = np.ascontiguousarray(desc1, np.uint8); desc2 = np.ascontiguousarray(desc2, np.uint8)
+    kps1 = np.ascontiguousarray(kps1, KP_DTYPE); kps2 = np.ascontiguousarray(kps2, KP_DTYPE)
+    ur1 = None if ur1 is None else np.ascontiguousarray(ur1, np.float32); ur2 = None if ur2 is None else np.ascontiguousarray(ur2, np.float32)
+    has1 = np.ascontiguousarray(has1, np.uint8); has2 = np.ascontiguousarray(has2, np.uint8)
+    a = [np.ascontiguousarray(x, np.int32) for x in fv1]; b = [np.ascontiguousarray(x, np.int32) for x in fv2]
+    F12 = np.ascontiguousarray(F12, np.float32); sf2 = np.ascontiguousarray(sf2, np.float32); ls2 = np.ascontiguousarray(ls2, np.float32)
+    out = np.zeros(len(desc1), np.int32)
+    n = C.c_int32()
+    _check(lib().orbm_search_for_triangulation(_p(desc1), _p(kps1), _p(ur1), _p(has1), len(desc1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]),
+                                               _p(desc2), _p(kps2), _p(ur2), _p(has2), len(desc2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]),
+                                               _p(F12), float(ex), float(ey), _p(sf2), _p(ls2), int(only_stereo), int(check_ori), _p(out),
+                                               C.byref(n), device), "orbm_search_for_triangulation")
     return out, n.value
 
 

@@ -237,3 +237,31 @@ def test_gpu_search_by_bow_keyframes(gpu, check_ori, ratio):
     assert ng == nw and np.array_equal(got, want) and ng > 30
     idx = np.flatnonzero(got >= 0)
     assert np.all(has1[idx] == 1) and np.all(has2[got[idx]] == 1) and len(set(got[idx].tolist())) == len(idx)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("only_stereo,check_ori", [(False, True), (True, True), (False, False)])
+def test_gpu_search_for_triangulation(gpu, only_stereo, check_ori):
+    """ORBmatcher::SearchForTriangulation (ORBmatcher.cpp:755-927).  The second view is the first translated by (3, 1) px, so the
+    fundamental matrix of a pure image-plane translation F12 = [t]x, t = (3, 1, 0), puts true matches on their epipolar lines."""
+    import orbb200, pyoracle
+    (kc, dc), (kl, dl), (k, L, parent, leaf, desc, weight) = _bow_pair(seed=35)
+    voc = orbb200.Vocabulary(k, L, parent, leaf, desc, weight)
+    fv1 = voc.bow(dl, 2)[2:]; fv2 = voc.bow(dc, 2)[2:]
+    rng = np.random.default_rng(7)
+    has1 = (rng.random(len(dl)) < 0.3).astype(np.uint8); has2 = (rng.random(len(dc)) < 0.3).astype(np.uint8)   # already triangulated
+    ur1 = np.where(rng.random(len(dl)) < 0.5, kl["x"] - 10, -1).astype(np.float32)
+    ur2 = np.where(rng.random(len(dc)) < 0.5, kc["x"] - 10, -1).astype(np.float32)
+    F12 = np.asarray([[0, 0, 1], [0, 0, -3], [-1, 3, 0]], np.float32)
+    sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32); ls2 = (sf * sf).astype(np.float32)
+    ex, ey = 200.0, 150.0                                  # an epipole inside the image: nearby mono candidates are rejected
+    want, nw = pyoracle.search_for_triangulation(dl, kl, ur1, has1, fv1, dc, kc, ur2, has2, fv2, F12, ex, ey, sf, ls2, only_stereo, check_ori)
+    got, ng = orbb200.search_for_triangulation(dl, kl, ur1, has1, fv1, dc, kc, ur2, has2, fv2, F12, ex, ey, sf, ls2, only_stereo, check_ori)
+    assert ng == nw and np.array_equal(got, want) and ng > 30
+    idx = np.flatnonzero(got >= 0)
+    assert np.all(has1[idx] == 0) and np.all(has2[got[idx]] == 0)
+    if only_stereo:
+        assert np.all(ur1[idx] >= 0) and np.all(ur2[got[idx]] >= 0)
+    # most accepted pairs are the true correspondences (x2 = x1 + (3, 1))
+    dx = kc["x"][got[idx]] - kl["x"][idx]; dy = kc["y"][got[idx]] - kl["y"][idx]
+    assert np.mean((np.abs(dx - 3) < 1.5) & (np.abs(dy - 1) < 1.5)) > 0.5
