@@ -167,6 +167,10 @@ int orbm_distinctive_descriptors_device(const uint8_t* desc_dev, const int64_t* 
 typedef struct orbm_frame orbm_frame;
 int orbm_frame_create(orbm_frame** out, const orbx_keypoint* kps_un_host, const uint8_t* desc_host, int n,
                       float min_x, float min_y, float max_x, float max_y, int device);
+/* The same from device arrays (e.g. the outputs of orbx_extract_batch_device after undistortion): copies and grid build are
+ * queued on `stream`, nothing visits the host. */
+int orbm_frame_create_device(orbm_frame** out, const orbx_keypoint* kps_un_dev, const uint8_t* desc_dev, int n,
+                             float min_x, float min_y, float max_x, float max_y, int device, void* stream);
 int orbm_frame_destroy(orbm_frame* f);
 
 /* One projected query: what every SearchByProjection variant hands to GetFeaturesInArea + DescriptorDistance
@@ -249,8 +253,8 @@ int orbm_search_by_bow_kf(const uint8_t* desc1, const float* angle1, const uint8
                           float nnratio, int check_orientation, int32_t* match12, int* nmatches, int device);
 
 /* ORBmatcher::SearchByProjection(Frame&, const vector<MapPoint*>&, th) (ORBmatcher.cpp:63-155): window candidates and
- * distances on the device, then the reference's order-dependent top-2 / level-aware ratio / already-matched loop on
- * the host.  frame_mp[n] (in/out) is F.mvpMapPoints flattened to ids (-1 = none), frame_mp_obs[n] the matched point's
+ * distances on the device, then the reference's order-dependent top-2 / level-aware ratio / already-matched loop, also
+ * on the device (see the _device forms below; this host-pointer form uploads, runs them and reads the state back).  frame_mp[n] (in/out) is F.mvpMapPoints flattened to ids (-1 = none), frame_mp_obs[n] the matched point's
  * Observations()>0.  mvuRight_host may be NULL (monocular).  Queries are the visible, non-bad map points in order. */
 int orbm_search_by_projection_points(const orbm_frame* f, const float* mvuRight_host, const orbm_proj_query* q_host, int nq,
                                      float nnratio, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches);
@@ -258,6 +262,18 @@ int orbm_search_by_projection_points(const orbm_frame* f, const float* mvuRight_
  * projection step: top-1 <= TH_HIGH, already-matched skips, rotation histogram (ComputeThreeMaxima :1792-1833). */
 int orbm_search_by_projection_frame(const orbm_frame* f, const float* mvuRight_host, const orbm_proj_query* q_host, int nq,
                                     int check_orientation, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches);
+/* Device-resident forms of the two calls above: queries, mvuRight (or NULL), the Frame's match state and the two
+ * result scalars all live on the device; window search AND the order-dependent resolve run there (the reference's sequential
+ * "skip slots that already hold an observed MapPoint" rule is evaluated as a parallel fixed-point iteration that reproduces the
+ * sequential result exactly), queued on `stream` with no host synchronisation.  *status_dev = ORBB_OK, or ORBB_E_CAPACITY when the
+ * windows held more than cand_capacity candidates in total (0 = 64*nq + 1024), in which case the state is left untouched.
+ * Calls that share one orbm_frame share its workspace: the caller serialises them (they are the Tracking thread's calls). */
+int orbm_search_by_projection_points_device(const orbm_frame* f, const float* mvuRight_dev, const orbm_proj_query* q_dev, int nq,
+                                            float nnratio, int32_t* frame_mp_dev, int32_t* frame_mp_obs_dev, int32_t* nmatches_dev,
+                                            int32_t* status_dev, int cand_capacity, void* stream);
+int orbm_search_by_projection_frame_device(const orbm_frame* f, const float* mvuRight_dev, const orbm_proj_query* q_dev, int nq,
+                                           int check_orientation, int32_t* frame_mp_dev, int32_t* frame_mp_obs_dev, int32_t* nmatches_dev,
+                                           int32_t* status_dev, int cand_capacity, void* stream);
 /* ORBmatcher::SearchForInitialization (ORBmatcher.cpp:474-590): level-0 keypoints of f1 against f2 in a window around
  * prev_matched_xy (in/out, 2*n1 floats); matches12_out[n1] = index in f2 or -1. */
 int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev_matched_xy, int32_t* matches12_out,

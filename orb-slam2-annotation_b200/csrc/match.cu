@@ -14,8 +14,15 @@ namespace {
 
 struct DevBuf {
     void* p = nullptr;
+    size_t cap = 0;
     ~DevBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { ORBB_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); return ORBB_OK; }
+    int alloc(size_t bytes) { ORBB_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); cap = bytes ? bytes : 16; return ORBB_OK; }
+    int reserve(size_t bytes)           // grow-only; contents are not kept
+    {
+        if (bytes <= cap) return ORBB_OK;
+        if (p) { ORBB_CUDA(cudaFree(p)); p = nullptr; cap = 0; }
+        return alloc(bytes + bytes / 4);
+    }
     template <typename T> T* as() { return (T*)p; }
 };
 
@@ -91,13 +98,31 @@ extern "C" int orbm_distinctive_descriptors(const uint8_t* desc_host, const int6
 struct orbm_frame {
     int device = 0, n = 0;
     FrameDev f{};
-    std::vector<orbx_keypoint> h_kps;      // host copies for the order-dependent resolution loops
-    std::vector<uint8_t> h_desc;
+    // host copies for the order-dependent resolution loops that stay on the host (reloc / loop / fuse / initialisation);
+    // a frame built from device arrays fetches them on first use
+    mutable std::vector<orbx_keypoint> h_kps;
+    mutable std::vector<uint8_t> h_desc;
+    mutable bool host_valid = false;
     DevBuf kps, desc, cell_of, cell_start, cell_items, cursor;
+    // workspace of the device resolve (orbm_search_by_projection_*_device); calls on one frame are serialised by the caller
+    mutable DevBuf ws_counts, ws_offs, ws_idx, ws_dist, ws_choice, ws_taker, ws_uright, ws_mp, ws_obs, ws_scalars;
 };
 
-extern "C" int orbm_frame_create(orbm_frame** out, const orbx_keypoint* kps, const uint8_t* desc, int n,
-                                 float min_x, float min_y, float max_x, float max_y, int device)
+static int frame_host_copies(const orbm_frame* fr)
+{
+    if (fr->host_valid) return ORBB_OK;
+    fr->h_kps.resize(fr->n); fr->h_desc.resize((size_t)fr->n * 32);
+    if (fr->n > 0) {
+        ORBB_CUDA(cudaMemcpy(fr->h_kps.data(), fr->kps.p, (size_t)fr->n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost));
+        ORBB_CUDA(cudaMemcpy(fr->h_desc.data(), fr->desc.p, (size_t)fr->n * 32, cudaMemcpyDeviceToHost));
+    }
+    fr->host_valid = true;
+    return ORBB_OK;
+}
+
+// kind = cudaMemcpyHostToDevice: the classic entry point (synchronous); cudaMemcpyDeviceToDevice: everything is queued on `stream`.
+static int frame_create_impl(orbm_frame** out, const orbx_keypoint* kps, const uint8_t* desc, int n,
+                             float min_x, float min_y, float max_x, float max_y, int device, cudaMemcpyKind kind, cudaStream_t st)
 {
     if (!out || n < 0 || (n > 0 && (!kps || !desc)) || !(max_x > min_x) || !(max_y > min_y)) return ORBB_E_INVALID;
     *out = nullptr;
@@ -106,7 +131,11 @@ extern "C" int orbm_frame_create(orbm_frame** out, const orbx_keypoint* kps, con
     orbm_frame* fr = new (std::nothrow) orbm_frame();
     if (!fr) return ORBB_E_NOMEM;
     fr->device = device; fr->n = n;
-    if (n > 0) { fr->h_kps.assign(kps, kps + n); fr->h_desc.assign(desc, desc + (size_t)n * 32); }
+    const bool from_host = kind == cudaMemcpyHostToDevice;
+    if (from_host) {
+        if (n > 0) { fr->h_kps.assign(kps, kps + n); fr->h_desc.assign(desc, desc + (size_t)n * 32); }
+        fr->host_valid = true;
+    }
     const int NC = GRID_COLS * GRID_ROWS;
     if ((rc = fr->kps.alloc((size_t)n * sizeof(orbx_keypoint))) || (rc = fr->desc.alloc((size_t)n * 32)) ||
         (rc = fr->cell_of.alloc((size_t)n * 4)) || (rc = fr->cell_start.alloc((size_t)(NC + 1) * 4)) ||
@@ -120,20 +149,32 @@ extern "C" int orbm_frame_create(orbm_frame** out, const orbx_keypoint* kps, con
     f.cell_of = fr->cell_of.as<int>(); f.cell_start = fr->cell_start.as<int>(); f.cell_items = fr->cell_items.as<int>();
     auto fail = [&](int code) { delete fr; return code; };
     if (n > 0) {
-        if (cudaMemcpy(fr->kps.p, kps, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice) != cudaSuccess) return fail(ORBB_E_CUDA);
-        if (cudaMemcpy(fr->desc.p, desc, (size_t)n * 32, cudaMemcpyHostToDevice) != cudaSuccess) return fail(ORBB_E_CUDA);
+        if (cudaMemcpyAsync(fr->kps.p, kps, (size_t)n * sizeof(orbx_keypoint), kind, st) != cudaSuccess) return fail(ORBB_E_CUDA);
+        if (cudaMemcpyAsync(fr->desc.p, desc, (size_t)n * 32, kind, st) != cudaSuccess) return fail(ORBB_E_CUDA);
     }
-    if (cudaMemset(fr->cursor.p, 0, (size_t)NC * 4) != cudaSuccess) return fail(ORBB_E_CUDA);
-    if (n > 0) { grid_assign_kernel<<<ceil_div(n, 256), 256>>>(f, fr->cursor.as<int>()); ORBB_LAUNCHED(); }
-    grid_scan_kernel<<<1, 1024>>>(fr->cursor.as<int>(), f.cell_start); ORBB_LAUNCHED();
+    if (cudaMemsetAsync(fr->cursor.p, 0, (size_t)NC * 4, st) != cudaSuccess) return fail(ORBB_E_CUDA);
+    if (n > 0) { grid_assign_kernel<<<ceil_div(n, 256), 256, 0, st>>>(f, fr->cursor.as<int>()); ORBB_LAUNCHED(); }
+    grid_scan_kernel<<<1, 1024, 0, st>>>(fr->cursor.as<int>(), f.cell_start); ORBB_LAUNCHED();
     if (n > 0) {
-        grid_fill_kernel<<<ceil_div(n, 256), 256>>>(f, fr->cursor.as<int>()); ORBB_LAUNCHED();
-        grid_sort_kernel<<<ceil_div(NC, 256), 256>>>(f); ORBB_LAUNCHED();
+        grid_fill_kernel<<<ceil_div(n, 256), 256, 0, st>>>(f, fr->cursor.as<int>()); ORBB_LAUNCHED();
+        grid_sort_kernel<<<ceil_div(NC, 256), 256, 0, st>>>(f); ORBB_LAUNCHED();
     }
-    cudaError_t e = cudaDeviceSynchronize();
+    cudaError_t e = from_host ? cudaStreamSynchronize(st) : cudaGetLastError();
     if (e != cudaSuccess) { set_cuda_error(e, "orbm_frame_create"); return fail(ORBB_E_CUDA); }
     *out = fr;
     return ORBB_OK;
+}
+
+extern "C" int orbm_frame_create(orbm_frame** out, const orbx_keypoint* kps, const uint8_t* desc, int n,
+                                 float min_x, float min_y, float max_x, float max_y, int device)
+{
+    return frame_create_impl(out, kps, desc, n, min_x, min_y, max_x, max_y, device, cudaMemcpyHostToDevice, 0);
+}
+
+extern "C" int orbm_frame_create_device(orbm_frame** out, const orbx_keypoint* kps_dev, const uint8_t* desc_dev, int n,
+                                        float min_x, float min_y, float max_x, float max_y, int device, void* stream)
+{
+    return frame_create_impl(out, kps_dev, desc_dev, n, min_x, min_y, max_x, max_y, device, cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
 }
 
 extern "C" int orbm_frame_destroy(orbm_frame* f)
@@ -156,11 +197,11 @@ extern "C" int orbm_window_search(const orbm_frame* fr, const orbm_query* q_host
         (rc = idx.alloc((size_t)cap * 4)) || (rc = dist.alloc((size_t)cap * 4))) return rc;
     ORBB_CUDA(cudaMemcpy(q.p, q_host, (size_t)nq * sizeof(orbm_query), cudaMemcpyHostToDevice));
     const int wpb = 8;
-    window_search_kernel<false><<<ceil_div(nq, wpb), wpb * 32>>>(fr->f, q.as<orbm_query>(), nq, counts.as<int>(), nullptr, nullptr, nullptr, 0);
+    window_search_kernel<false><<<ceil_div(nq, wpb), wpb * 32>>>(fr->f, q.p, sizeof(orbm_query), nq, counts.as<int>(), nullptr, nullptr, nullptr, 0);
     ORBB_LAUNCHED();
     excl_scan_kernel<<<1, 1024>>>(counts.as<int>(), offs.as<int>(), nq);
     ORBB_LAUNCHED();
-    window_search_kernel<true><<<ceil_div(nq, wpb), wpb * 32>>>(fr->f, q.as<orbm_query>(), nq, nullptr, offs.as<int>(), idx.as<int>(), dist.as<int>(), cap);
+    window_search_kernel<true><<<ceil_div(nq, wpb), wpb * 32>>>(fr->f, q.p, sizeof(orbm_query), nq, nullptr, offs.as<int>(), idx.as<int>(), dist.as<int>(), cap);
     ORBB_LAUNCHED();
     ORBB_CUDA(cudaGetLastError());
     ORBB_CUDA(cudaMemcpy(offs_host, offs.p, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost));
@@ -182,6 +223,8 @@ int run_window_search(const orbm_frame* f, const std::vector<orbm_query>& q, std
 {
     const int nq = (int)q.size();
     offs.assign(nq + 1, 0);
+    int rc0 = check_device(f->device);
+    if (rc0 != ORBB_OK || (rc0 = frame_host_copies(f)) != ORBB_OK) return rc0;    // the callers' resolve loops read h_kps
     int cap = 64 * nq + 1024;
     for (int attempt = 0; attempt < 2; attempt++) {
         idx.resize(cap); dist.resize(cap);
@@ -217,80 +260,110 @@ inline int rot_bin(float a1, float a2)
 }
 }  // namespace
 
-extern "C" int orbm_search_by_projection_points(const orbm_frame* f, const float* uright, const orbm_proj_query* pq, int nq,
-                                                float nnratio, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches)
+// ---- SearchByProjection(Frame&, vector<MapPoint*>) / (Frame&, const Frame&): candidates AND resolve on the device ------------
+// (SURVEY 8(f)-1).  Everything is queued on `st`; nothing is read back here.
+static int resolve_on_device(const orbm_frame* fr, int mode, const float* uright_dev, const orbm_proj_query* q_dev, int nq, float nnratio,
+                             int check_ori, int32_t* frame_mp_dev, int32_t* frame_mp_obs_dev, int32_t* nmatches_dev, int32_t* status_dev,
+                             int32_t* rounds_dev, int cand_capacity, cudaStream_t st)
+{
+    const int cap = cand_capacity > 0 ? cand_capacity : 64 * nq + 1024;
+    int rc;
+    if ((rc = fr->ws_counts.reserve((size_t)nq * 4)) ||
+        (rc = fr->ws_offs.reserve((size_t)(nq + 1) * 4)) || (rc = fr->ws_idx.reserve((size_t)cap * 4)) ||
+        (rc = fr->ws_dist.reserve((size_t)cap * 4)) || (rc = fr->ws_choice.reserve((size_t)nq * 4)) ||
+        (rc = fr->ws_taker.reserve((size_t)fr->n * 4))) return rc;
+    const int wpb = 8;
+    window_search_kernel<false><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, fr->ws_counts.as<int>(), nullptr, nullptr, nullptr, 0);
+    ORBB_LAUNCHED();
+    excl_scan_kernel<<<1, 1024, 0, st>>>(fr->ws_counts.as<int>(), fr->ws_offs.as<int>(), nq); ORBB_LAUNCHED();
+    window_search_kernel<true><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, nullptr, fr->ws_offs.as<int>(), fr->ws_idx.as<int>(),
+                                                                     fr->ws_dist.as<int>(), cap);
+    ORBB_LAUNCHED();
+    ResolveArgs a{};
+    a.f = fr->f; a.q = q_dev; a.nq = nq; a.offs = fr->ws_offs.as<int>(); a.idx = fr->ws_idx.as<int>(); a.dist = fr->ws_dist.as<int>(); a.cap = cap;
+    a.uright = uright_dev; a.nnratio = nnratio; a.check_ori = check_ori; a.frame_mp = frame_mp_dev; a.frame_mp_obs = frame_mp_obs_dev;
+    a.choice = fr->ws_choice.as<int>(); a.taker = fr->ws_taker.as<int>(); a.nmatches = nmatches_dev; a.status = status_dev; a.rounds = rounds_dev;
+    if (mode == 0) resolve_projection_kernel<0><<<1, 1024, 0, st>>>(a); else resolve_projection_kernel<1><<<1, 1024, 0, st>>>(a);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    return ORBB_OK;
+}
+
+extern "C" int orbm_search_by_projection_points_device(const orbm_frame* f, const float* mvuRight_dev, const orbm_proj_query* q_dev, int nq, float nnratio,
+                                                       int32_t* frame_mp_dev, int32_t* frame_mp_obs_dev, int32_t* nmatches_dev, int32_t* status_dev,
+                                                       int cand_capacity, void* stream)
+{
+    if (!f || nq <= 0 || !q_dev || !nmatches_dev || !status_dev || (f->n > 0 && (!frame_mp_dev || !frame_mp_obs_dev))) return ORBB_E_INVALID;
+    const int rc = check_device(f->device);
+    if (rc != ORBB_OK) return rc;
+    return resolve_on_device(f, 0, mvuRight_dev, q_dev, nq, nnratio, 0, frame_mp_dev, frame_mp_obs_dev, nmatches_dev, status_dev, nullptr, cand_capacity,
+                             (cudaStream_t)stream);
+}
+
+extern "C" int orbm_search_by_projection_frame_device(const orbm_frame* f, const float* mvuRight_dev, const orbm_proj_query* q_dev, int nq, int check_ori,
+                                                      int32_t* frame_mp_dev, int32_t* frame_mp_obs_dev, int32_t* nmatches_dev, int32_t* status_dev,
+                                                      int cand_capacity, void* stream)
+{
+    if (!f || nq <= 0 || !q_dev || !nmatches_dev || !status_dev || (f->n > 0 && (!frame_mp_dev || !frame_mp_obs_dev))) return ORBB_E_INVALID;
+    const int rc = check_device(f->device);
+    if (rc != ORBB_OK) return rc;
+    return resolve_on_device(f, 1, mvuRight_dev, q_dev, nq, 0.f, check_ori, frame_mp_dev, frame_mp_obs_dev, nmatches_dev, status_dev, nullptr, cand_capacity,
+                             (cudaStream_t)stream);
+}
+
+// Host-pointer forms: upload the queries and the Frame's match state, run the device path, read the state back.
+static int search_projection_host(const orbm_frame* f, int mode, const float* uright, const orbm_proj_query* pq, int nq, float nnratio, int check_ori,
+                                  int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches)
 {
     if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && (!frame_mp || !frame_mp_obs))) return ORBB_E_INVALID;
     *nmatches = 0;
-    if (nq == 0) return ORBB_OK;
-    std::vector<orbm_query> q(nq);
-    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
-    std::vector<int> offs, idx, dist;
-    const int rc = run_window_search(f, q, offs, idx, dist);
+    int rc = check_device(f->device);
     if (rc != ORBB_OK) return rc;
-    int nm = 0;
-    for (int i = 0; i < nq; i++) {
-        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
-        for (int c = offs[i]; c < offs[i + 1]; c++) {
-            const int k = idx[c];
-            if (frame_mp[k] >= 0 && frame_mp_obs[k] > 0) continue;                       // :112-114
-            if (uright && uright[k] > 0) {                                              // :116-121
-                const float er = fabsf(pq[i].u_right - uright[k]);
-                if (er > pq[i].max_err_right) continue;
-            }
-            const int d = dist[c];
-            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestLevel2 = bestLevel; bestLevel = f->h_kps[k].octave; bestIdx = k; }
-            else if (d < bestDist2) { bestLevel2 = f->h_kps[k].octave; bestDist2 = d; }
+    if (nq == 0) return ORBB_OK;
+    const size_t nb = (size_t)f->n * 4;
+    DevBuf q;
+    if ((rc = q.alloc((size_t)nq * sizeof(orbm_proj_query))) || (rc = f->ws_mp.reserve(nb)) || (rc = f->ws_obs.reserve(nb)) ||
+        (rc = f->ws_scalars.reserve(16)) || (uright && (rc = f->ws_uright.reserve(nb)))) return rc;
+    ORBB_CUDA(cudaMemcpy(q.p, pq, (size_t)nq * sizeof(orbm_proj_query), cudaMemcpyHostToDevice));
+    if (uright && f->n > 0) ORBB_CUDA(cudaMemcpy(f->ws_uright.p, uright, nb, cudaMemcpyHostToDevice));
+    int32_t* sc = f->ws_scalars.as<int32_t>();
+    int cap = 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        if (f->n > 0) {
+            ORBB_CUDA(cudaMemcpy(f->ws_mp.p, frame_mp, nb, cudaMemcpyHostToDevice));
+            ORBB_CUDA(cudaMemcpy(f->ws_obs.p, frame_mp_obs, nb, cudaMemcpyHostToDevice));
         }
-        if (bestDist <= TH_HIGH) {                                                      // :142-151
-            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
-            frame_mp[bestIdx] = pq[i].id; frame_mp_obs[bestIdx] = pq[i].has_obs;
-            nm++;
+        rc = resolve_on_device(f, mode, uright ? f->ws_uright.as<float>() : nullptr, q.as<orbm_proj_query>(), nq, nnratio, check_ori,
+                               f->ws_mp.as<int32_t>(), f->ws_obs.as<int32_t>(), sc, sc + 1, sc + 2, cap, 0);
+        if (rc != ORBB_OK) return rc;
+        int32_t h[3] = {0, 0, 0};
+        ORBB_CUDA(cudaMemcpy(h, sc, sizeof(h), cudaMemcpyDeviceToHost));
+        if (h[1] == ORBB_E_CAPACITY && attempt == 0) {            // more candidates than the default budget: size it exactly
+            ORBB_CUDA(cudaMemcpy(&cap, f->ws_offs.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
+            cap += 16;
+            continue;
         }
+        if (h[1] != ORBB_OK) return h[1];
+        *nmatches = h[0];
+        if (f->n > 0) {
+            ORBB_CUDA(cudaMemcpy(frame_mp, f->ws_mp.p, nb, cudaMemcpyDeviceToHost));
+            ORBB_CUDA(cudaMemcpy(frame_mp_obs, f->ws_obs.p, nb, cudaMemcpyDeviceToHost));
+        }
+        return ORBB_OK;
     }
-    *nmatches = nm;
-    return ORBB_OK;
+    return ORBB_E_CAPACITY;
+}
+
+extern "C" int orbm_search_by_projection_points(const orbm_frame* f, const float* uright, const orbm_proj_query* pq, int nq,
+                                                float nnratio, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches)
+{
+    return search_projection_host(f, 0, uright, pq, nq, nnratio, 0, frame_mp, frame_mp_obs, nmatches);
 }
 
 extern "C" int orbm_search_by_projection_frame(const orbm_frame* f, const float* uright, const orbm_proj_query* pq, int nq,
                                                int check_ori, int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches)
 {
-    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && (!frame_mp || !frame_mp_obs))) return ORBB_E_INVALID;
-    *nmatches = 0;
-    if (nq == 0) return ORBB_OK;
-    std::vector<orbm_query> q(nq);
-    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
-    std::vector<int> offs, idx, dist;
-    const int rc = run_window_search(f, q, offs, idx, dist);
-    if (rc != ORBB_OK) return rc;
-    std::vector<int> rotHist[HISTO_LENGTH];
-    int nm = 0;
-    for (int i = 0; i < nq; i++) {
-        int bestDist = 256, bestIdx2 = -1;
-        for (int c = offs[i]; c < offs[i + 1]; c++) {
-            const int k = idx[c];
-            if (frame_mp[k] >= 0 && frame_mp_obs[k] > 0) continue;                       // :1590-1592
-            if (uright && uright[k] > 0) {                                              // :1594-1601
-                const float er = fabsf(pq[i].u_right - uright[k]);
-                if (er > pq[i].max_err_right) continue;
-            }
-            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx2 = k; }
-        }
-        if (bestDist <= TH_HIGH) {                                                      // :1615-1632
-            frame_mp[bestIdx2] = pq[i].id; frame_mp_obs[bestIdx2] = pq[i].has_obs;
-            nm++;
-            if (check_ori) rotHist[rot_bin(pq[i].angle, f->h_kps[bestIdx2].angle)].push_back(bestIdx2);
-        }
-    }
-    if (check_ori) {                                                                    // :1636-1656
-        int ind1 = -1, ind2 = -1, ind3 = -1;
-        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
-        for (int b = 0; b < HISTO_LENGTH; b++)
-            if (b != ind1 && b != ind2 && b != ind3)
-                for (size_t j = 0; j < rotHist[b].size(); j++) { frame_mp[rotHist[b][j]] = -1; nm--; }
-    }
-    *nmatches = nm;
-    return ORBB_OK;
+    return search_projection_host(f, 1, uright, pq, nq, 0.f, check_ori, frame_mp, frame_mp_obs, nmatches);
 }
 
 // ---- relocalisation / loop-closing / fusion variants --------------------------
@@ -620,6 +693,8 @@ extern "C" int orbm_search_for_initialization(const orbm_frame* f1, const orbm_f
     *nmatches = 0;
     const int n1 = f1->n, n2 = f2->n;
     for (int i = 0; i < n1; i++) m12[i] = -1;
+    int rc0 = check_device(f1->device);
+    if (rc0 != ORBB_OK || (rc0 = frame_host_copies(f1)) != ORBB_OK || (rc0 = frame_host_copies(f2)) != ORBB_OK) return rc0;
     // level-0 keypoints of F1 are the queries (:490-494)
     std::vector<orbm_query> q; std::vector<int> qi;
     for (int i = 0; i < n1; i++) {

@@ -160,14 +160,14 @@ __global__ void grid_sort_kernel(FrameDev f)
 // GetFeaturesInArea + DescriptorDistance.  One warp per query; FILL=false counts, FILL=true writes.
 // ------------------------------------------------------------------------------------------------------
 template <bool FILL>
-__global__ void window_search_kernel(FrameDev f, const orbm_query* __restrict__ qs, int nq,
+__global__ void window_search_kernel(FrameDev f, const void* __restrict__ qs, size_t qstride, int nq,   // records that START with an orbm_query
                                      int* __restrict__ counts, const int* __restrict__ offsets,
                                      int* __restrict__ cand_idx, int* __restrict__ cand_dist, int cap)
 {
     const int lane = threadIdx.x & 31;
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (qi >= nq) return;
-    const orbm_query& q = qs[qi];
+    const orbm_query& q = *reinterpret_cast<const orbm_query*>(static_cast<const char*>(qs) + (size_t)qi * qstride);
     const float x = q.u, y = q.v, r = q.r;
     const int minLevel = q.min_level, maxLevel = q.max_level;
     int total = 0;
@@ -241,6 +241,141 @@ __global__ void excl_scan_kernel(const int* __restrict__ in, int* __restrict__ o
         __syncthreads();
     }
     if (threadIdx.x == 0) out[n] = carry;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Device resolve of ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>, th) (MODE 0, ORBmatcher.cpp:63-155) and
+// SearchByProjection(Frame& Current, const Frame& Last, th, bMono) (MODE 1, :1506-1659) on the candidate CSR of
+// window_search_kernel (no candidate list travels to the host).
+//
+// The reference walks the queries in order; query i skips every candidate whose Frame slot already holds a MapPoint with
+// Observations() > 0 (:112-114, :1590-1592), and its own match, written into the slot, is such a point for the queries after
+// it.  So choice(i) depends only on the choices of queries j < i: the sequence of choices is the unique fixed point of
+//     choice(i) = best candidate k of i with  !(initially taken(k))  and  !(exists j < i: choice(j) == k and has_obs(j)).
+// One CTA iterates it in parallel (thread per query; taker[k] = min such j by atomicMin) until no choice changes; after round
+// r the first r queries are final, and dependency chains are a handful long in practice.  Slot k finally holds the LAST query
+// that chose it (a point without observations does not block and is overwritten, as in the reference), nmatches counts every
+// accepted query (:150, :1618), and MODE 1's rotation histogram (:1620-1656, ComputeThreeMaxima :1792-1833) then clears the
+// slots of the queries outside the three dominant bins.
+// ------------------------------------------------------------------------------------------------------
+struct ResolveArgs {
+    FrameDev f;
+    const orbm_proj_query* q; int nq;
+    const int* offs; const int* idx; const int* dist; int cap;     // candidate CSR (offs[nq] > cap: overflow, nothing is written)
+    const float* uright;                                           // mvuRight or nullptr
+    float nnratio; int check_ori;
+    int* frame_mp; int* frame_mp_obs;                              // [f.n] in/out
+    int* choice;                                                   // [nq] scratch
+    int* taker;                                                    // [f.n] scratch
+    int* nmatches; int* status; int* rounds;                       // device scalars (rounds may be nullptr)
+};
+
+template <int MODE>
+__device__ __forceinline__ int resolve_choose(const ResolveArgs& a, int i)
+{
+    const orbm_proj_query& pq = a.q[i];
+    const float ur = pq.u_right, maxer = pq.max_err_right;
+    int bestDist = 256, bestDist2 = 256, bestLevel = -1, bestLevel2 = -1, bestIdx = -1;
+    for (int c = a.offs[i], e = a.offs[i + 1]; c < e; c++) {
+        const int k = a.idx[c];
+        if ((a.frame_mp[k] >= 0 && a.frame_mp_obs[k] > 0) || a.taker[k] < i) continue;
+        if (a.uright) {
+            const float urk = a.uright[k];
+            if (urk > 0 && fabsf(__fsub_rn(ur, urk)) > maxer) continue;
+        }
+        const int d = a.dist[c];
+        if (MODE == 0) {
+            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestLevel2 = bestLevel; bestLevel = a.f.kps[k].octave; bestIdx = k; }
+            else if (d < bestDist2) { bestLevel2 = a.f.kps[k].octave; bestDist2 = d; }
+        } else if (d < bestDist) { bestDist = d; bestIdx = k; }
+    }
+    if (bestDist > TH_HIGH) return -1;
+    if (MODE == 0 && bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(a.nnratio, (float)bestDist2)) return -1;
+    return bestIdx;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_constant__ ResolveArgs a)
+{
+    __shared__ int changed_s, nm_s, hist_s[30], ind_s[3];
+    const int tid = threadIdx.x, nt = blockDim.x;
+    if (a.offs[a.nq] > a.cap) { if (tid == 0) { *a.status = ORBB_E_CAPACITY; *a.nmatches = 0; } return; }
+    for (int i = tid; i < a.nq; i += nt) a.choice[i] = -2;
+    for (int k = tid; k < a.f.n; k += nt) a.taker[k] = 0x7fffffff;
+    if (tid == 0) { nm_s = 0; changed_s = 0; }
+    if (tid < 30) hist_s[tid] = 0;
+    __syncthreads();
+    int rounds = 0;
+    for (;;) {
+        bool changed = false;
+        for (int i = tid; i < a.nq; i += nt) {
+            const int c = resolve_choose<MODE>(a, i);
+            if (c != a.choice[i]) { a.choice[i] = c; changed = true; }
+        }
+        if (changed) changed_s = 1;
+        __syncthreads();
+        const int any = changed_s;
+        rounds++;
+        for (int k = tid; k < a.f.n; k += nt) a.taker[k] = 0x7fffffff;
+        __syncthreads();
+        if (!any) break;
+        if (tid == 0) changed_s = 0;
+        for (int i = tid; i < a.nq; i += nt) {
+            const int c = a.choice[i];
+            if (c >= 0 && a.q[i].has_obs > 0) atomicMin(&a.taker[c], i);
+        }
+        __syncthreads();
+    }
+    // slot k <- the last query that chose it; taker is reused as "last chooser" (reset to INT_MAX above: store -i-1 as min)
+    for (int i = tid; i < a.nq; i += nt) {
+        const int c = a.choice[i];
+        if (c >= 0) atomicMin(&a.taker[c], -i - 1);
+    }
+    __syncthreads();
+    int mine = 0;
+    for (int i = tid; i < a.nq; i += nt) {
+        const int c = a.choice[i];
+        if (c < 0) continue;
+        mine++;
+        if (a.taker[c] == -i - 1) { a.frame_mp[c] = a.q[i].id; a.frame_mp_obs[c] = a.q[i].has_obs; }
+        if (MODE == 1 && a.check_ori) {
+            float rot = __fsub_rn(a.q[i].angle, a.f.kps[c].angle);
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            int bin = (int)roundf(__fmul_rn(rot, 30 / 360.0f));
+            if (bin == 30) bin = 0;
+            atomicAdd(&hist_s[bin], 1);
+        }
+    }
+    if (mine) atomicAdd(&nm_s, mine);
+    __syncthreads();
+    if (MODE == 1 && a.check_ori) {
+        if (tid == 0) {                                     // ComputeThreeMaxima
+            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+            for (int b = 0; b < 30; b++) {
+                const int s = hist_s[b];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = b; }
+                else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = b; }
+                else if (s > max3) { max3 = s; ind3 = b; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) ind3 = -1;
+            ind_s[0] = ind1; ind_s[1] = ind2; ind_s[2] = ind3;
+        }
+        __syncthreads();
+        int gone = 0;
+        for (int i = tid; i < a.nq; i += nt) {
+            const int c = a.choice[i];
+            if (c < 0) continue;
+            float rot = __fsub_rn(a.q[i].angle, a.f.kps[c].angle);
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            int bin = (int)roundf(__fmul_rn(rot, 30 / 360.0f));
+            if (bin == 30) bin = 0;
+            if (bin != ind_s[0] && bin != ind_s[1] && bin != ind_s[2]) { a.frame_mp[c] = -1; gone++; }
+        }
+        if (gone) atomicSub(&nm_s, gone);
+        __syncthreads();
+    }
+    if (tid == 0) { *a.nmatches = nm_s; *a.status = ORBB_OK; if (a.rounds) *a.rounds = rounds; }
 }
 
 // ------------------------------------------------------------------------------------------------------

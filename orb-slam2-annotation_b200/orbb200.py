@@ -26,7 +26,8 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
            "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbx_set_rectification", "orbx_extract_batch_rectified", "orbx_remap_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
-           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
+           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_frame_create_device",
+           "orbm_search_by_projection_points_device", "orbm_search_by_projection_frame_device", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
@@ -90,6 +91,9 @@ def lib():
         L.orbv_compute_bow.argtypes = [vp, vp, i32, i32] + [vp] * 7
         L.orbm_frame_destroy.argtypes = [vp]
         L.orbm_window_search.argtypes = [vp, vp, i32, vp, vp, vp, i32]
+        L.orbm_frame_create_device.argtypes = [C.POINTER(vp), vp, vp, i32, f32, f32, f32, f32, i32, vp]
+        L.orbm_search_by_projection_points_device.argtypes = [vp, vp, vp, i32, f32, vp, vp, vp, vp, i32, vp]
+        L.orbm_search_by_projection_frame_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp, i32, vp]
         L.orbm_search_by_projection_points.argtypes = [vp, vp, vp, i32, f32, vp, vp, C.POINTER(i32)]
         L.orbm_search_by_projection_frame.argtypes = [vp, vp, vp, i32, i32, vp, vp, C.POINTER(i32)]
         L.orbm_search_by_bow.argtypes = [vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, C.POINTER(i32), i32]
@@ -431,6 +435,16 @@ class FrameMatcher:
         _check(self.L.orbm_frame_create(C.byref(self.h), _p(self.kps), _p(self.desc), self.n,
                                         *[float(b) for b in bounds], device), "orbm_frame_create")
 
+    @classmethod
+    def from_device(cls, kps_un_ptr, desc_ptr, n, bounds, device=0, stream=0):
+        """orbm_frame_create_device: kps_un_ptr / desc_ptr are device addresses (ints); nothing visits the host."""
+        self = cls.__new__(cls)
+        self.L = lib(); self.n = int(n); self.kps = None; self.desc = None
+        self.h = C.c_void_p()
+        _check(self.L.orbm_frame_create_device(C.byref(self.h), C.c_void_p(kps_un_ptr), C.c_void_p(desc_ptr), self.n,
+                                               *[float(b) for b in bounds], device, C.c_void_p(stream)), "orbm_frame_create_device")
+        return self
+
     def close(self):
         if getattr(self, "h", None) and self.h.value:
             self.L.orbm_frame_destroy(self.h)
@@ -486,6 +500,18 @@ class ORBmatcher:
         _check(self.L.orbm_search_by_projection_frame(frame.h, _p(ur), _p(q), len(q), int(self.mbCheckOrientation), _p(mp), _p(ob), C.byref(n)),
                "orbm_search_by_projection_frame")
         return n.value, mp, ob
+
+    def SearchByProjection_device(self, mode, frame, q_ptr, nq, mp_ptr, obs_ptr, nmatches_ptr, status_ptr, uright_ptr=0, cand_capacity=0, stream=0):
+        """orbm_search_by_projection_{points,frame}_device on raw device addresses (mode "points" | "frame"); asynchronous."""
+        vp = C.c_void_p
+        if mode == "points":
+            _check(self.L.orbm_search_by_projection_points_device(frame.h, vp(uright_ptr), vp(q_ptr), nq, self.mfNNratio, vp(mp_ptr), vp(obs_ptr),
+                                                                  vp(nmatches_ptr), vp(status_ptr), cand_capacity, vp(stream)),
+                   "orbm_search_by_projection_points_device")
+        else:
+            _check(self.L.orbm_search_by_projection_frame_device(frame.h, vp(uright_ptr), vp(q_ptr), nq, int(self.mbCheckOrientation), vp(mp_ptr),
+                                                                 vp(obs_ptr), vp(nmatches_ptr), vp(status_ptr), cand_capacity, vp(stream)),
+                   "orbm_search_by_projection_frame_device")
 
     def SearchByProjection_reloc(self, frame, proj_queries, frame_mp, ORBdist):
         """SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (ORBmatcher.cpp:1661-1789)."""

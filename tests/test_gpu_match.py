@@ -361,3 +361,91 @@ def test_fuse_and_sim3_best(gpu):
     assert np.array_equal(m1, o1) and np.array_equal(m2, o2)
     mutual = [(i1, m1[i1]) for i1 in range(len(m1)) if m1[i1] >= 0 and m2[m1[i1]] == i1]
     assert len(mutual) > 0.2 * len(kl)
+
+
+def _contended(kl, dl, scale, rng, reps, th, levels):
+    """Every last-frame point `reps` times in shuffled order with a wide window: many queries compete for the same Frame slots, so
+    the reference's sequential already-matched rule (ORBmatcher.cpp:112-114, :1590-1592) decides most of the outcome."""
+    q = _queries(kl, dl, scale, th, (3, 1), rng, levels)
+    q = np.concatenate([q] * reps)
+    q = q[rng.permutation(len(q))]
+    q["id"] = np.arange(len(q))
+    q["has_obs"] = (rng.random(len(q)) < 0.7).astype(np.int32)
+    flip = rng.random(len(q)) < 0.5                      # perturb half of the descriptors so that the rivals' best slots differ
+    bits = rng.integers(0, 256, (len(q), 32), dtype=np.uint8) & rng.integers(0, 256, (len(q), 32), dtype=np.uint8) & rng.integers(0, 256, (len(q), 32), dtype=np.uint8)
+    q["q"]["desc"][flip] ^= bits[flip]
+    return q
+
+
+@pytest.mark.parametrize("mode", ["frame", "points"])
+def test_search_by_projection_contended_order_dependence(gpu, mode):
+    """The device resolve (parallel fixed point) against the sequential reference loop under heavy slot contention."""
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=14)
+    rng = np.random.default_rng(21)
+    h, w = cur.shape
+    F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h)); O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    ur = np.where(rng.random(len(kc)) < 0.5, kc["x"] - rng.uniform(0, 30, len(kc)), -1).astype(np.float32)
+    for reps, th in [(3, 15.0), (6, 40.0)]:
+        q = _contended(kl, dl, scale, rng, reps, th, "pm1" if mode == "frame" else "pred")
+        mp0 = np.full(len(kc), -1, np.int32); ob0 = np.zeros(len(kc), np.int32)
+        mp0[::17] = 9999; ob0[::17] = 1; mp0[5::23] = 7777
+        for uright in (None, ur):
+            if mode == "frame":
+                n, mp, ob = orbb200.ORBmatcher(0.9, True).SearchByProjection_frame(F, q, mp0, ob0, uright)
+                on, omp, oob = O.search_last_frame(_to_oracle_queries(q), True, mp0, ob0, uright)
+            else:
+                n, mp, ob = orbb200.ORBmatcher(0.8).SearchByProjection_points(F, q, mp0, ob0, uright)
+                on, omp, oob = O.search_local_points(_to_oracle_queries(q), 0.8, mp0, ob0, uright)
+            assert n == on and np.array_equal(mp, omp)
+            assert np.array_equal(ob, oob)
+            assert n > 200
+    # candidate overflow of the default budget is retried with the exact size (reps=6, th=40 above exceeds 64*nq+1024 or not; force it)
+    q = _contended(kl, dl, scale, rng, 2, 200.0, "pm1")
+    q["q"]["min_level"] = -1; q["q"]["max_level"] = -1
+    n, mp, ob = orbb200.ORBmatcher(0.9, True).SearchByProjection_frame(F, q, mp0, ob0, None)
+    on, omp, oob = O.search_last_frame(_to_oracle_queries(q), True, mp0, ob0, None)
+    assert n == on and np.array_equal(mp, omp)
+
+
+def test_search_by_projection_device_resident(gpu):
+    """Frame built from device arrays, queries / state / results on the device, no host round trip in between."""
+    import torch
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=15)
+    rng = np.random.default_rng(22)
+    h, w = cur.shape
+    dev = torch.device("cuda:0")
+    t_k = torch.from_numpy(kc.view(np.uint8).reshape(len(kc), -1).copy()).to(dev); t_d = torch.from_numpy(dc.copy()).to(dev)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        F = orbb200.FrameMatcher.from_device(t_k.data_ptr(), t_d.data_ptr(), len(kc), (0, 0, w, h), 0, st.cuda_stream)
+        O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+        for mode, levels in (("frame", "pm1"), ("points", "pred")):
+            q = _contended(kl, dl, scale, rng, 2, 15.0, levels)
+            mp0 = np.full(len(kc), -1, np.int32); ob0 = np.zeros(len(kc), np.int32)
+            mp0[::17] = 9999; ob0[::17] = 1
+            t_q = torch.from_numpy(q.view(np.uint8).reshape(len(q), -1).copy()).to(dev, non_blocking=True)
+            t_mp = torch.from_numpy(mp0.copy()).to(dev); t_ob = torch.from_numpy(ob0.copy()).to(dev)
+            t_sc = torch.zeros(2, dtype=torch.int32, device=dev)
+            orbb200.ORBmatcher(0.8, True).SearchByProjection_device(mode, F, t_q.data_ptr(), len(q), t_mp.data_ptr(), t_ob.data_ptr(), t_sc.data_ptr(),
+                                                                    t_sc.data_ptr() + 4, stream=st.cuda_stream)
+            st.synchronize()
+            n, status = t_sc.cpu().tolist()
+            if mode == "frame":
+                on, omp, oob = O.search_last_frame(_to_oracle_queries(q), True, mp0, ob0, None)
+            else:
+                on, omp, oob = O.search_local_points(_to_oracle_queries(q), 0.8, mp0, ob0, None)
+            assert status == 0 and n == on and np.array_equal(t_mp.cpu().numpy(), omp)
+        # a budget that is too small reports ORBB_E_CAPACITY in *status_dev and leaves the state untouched
+        t_mp = torch.from_numpy(mp0.copy()).to(dev)
+        orbb200.ORBmatcher(0.8, True).SearchByProjection_device("frame", F, t_q.data_ptr(), len(q), t_mp.data_ptr(), t_ob.data_ptr(), t_sc.data_ptr(),
+                                                                t_sc.data_ptr() + 4, cand_capacity=8, stream=st.cuda_stream)
+        st.synchronize()
+        assert t_sc.cpu().tolist()[1] == orbb200.E_CAPACITY and np.array_equal(t_mp.cpu().numpy(), mp0)
+        # the host-resolve entry points still work on a device-built frame (host copies are fetched on first use)
+        qq = _queries(kl, dl, scale, 10.0, (3, 1), rng, "pm1")
+        n1, m1 = orbb200.ORBmatcher(0.9, True).SearchByProjection_reloc(F, qq, np.full(len(kc), -1, np.int32), 100)
+        n2, m2 = O.search_reloc(_to_oracle_queries(qq), 100, True, np.full(len(kc), -1, np.int32))
+        assert n1 == n2 and np.array_equal(m1, m2)
+    F.close()
