@@ -161,6 +161,18 @@ int orbm_distinctive_descriptors(const uint8_t* desc_host, const int64_t* offset
 int orbm_distinctive_descriptors_device(const uint8_t* desc_dev, const int64_t* offsets_dev, int npoints,
                                         int32_t* best_row_dev, int32_t* best_median_dev, void* stream);
 
+/* Frame::UndistortKeyPoints (Frame.cpp:462-496): mvKeysUn = mvKeys with (x, y) replaced by cv::undistortPoints(pts, mK, mDistCoef,
+ * cv::Mat(), mK); a plain copy when mDistCoef(0) == 0.  K4 = {fx, fy, cx, cy} (mK), dist = mDistCoef with ndist = 4, 5, 8 or 12
+ * coefficients (k1 k2 p1 p2 [k3 [k4 k5 k6 [s1..s4]]]).  OpenCV 4.x arithmetic (double, five iterations), bit-equal to cv2 4.13
+ * (tests/golden/cv2_undistort.npz).  The _device form works on device arrays of any length (a whole batch of frames that share one
+ * calibration) and is queued on `stream`; in and out may be the same array.
+ * orbm_image_bounds: Frame::ComputeImageBounds (Frame.cpp:498-536) -> {mnMinX, mnMinY, mnMaxX, mnMaxY}. */
+int orbm_undistort_keypoints(const orbx_keypoint* kps_host, int n, const float* K4, const float* dist, int ndist,
+                             orbx_keypoint* kps_un_host, int device);
+int orbm_undistort_keypoints_device(const orbx_keypoint* kps_dev, int n, const float* K4, const float* dist, int ndist,
+                                    orbx_keypoint* kps_un_dev, int device, void* stream);
+int orbm_image_bounds(int cols, int rows, const float* K4, const float* dist, int ndist, float* bounds4, int device);
+
 /* A Frame's matching state on the device: undistorted keypoints (mvKeysUn), descriptors (mDescriptors) and the
  * 64x48 bucket grid of Frame::AssignFeaturesToGrid / PosInGrid (Frame.cpp:241-257, :434-444), built on device
  * in insertion order.  Bounds are Frame::mnMinX/mnMinY/mnMaxX/mnMaxY. */

@@ -283,4 +283,38 @@ static inline float fast_atan2(float y, float x)
     return a;
 }
 
+// cv::undistortPoints(src, dst, K, D, noArray(), P = K) for CV_32FC2 points, OpenCV 4.x (imgproc/src/undistort.dispatch.cpp,
+// cvUndistortPointsInternal; the 6-argument overload uses TermCriteria(MAX_ITER, 5, 0.01), i.e. exactly five fixed-point iterations).
+// All arithmetic is double on operands converted from float; R = identity and P = K make RR = K exactly; no tilt (k[12], k[13] = 0).
+// dist holds nd = 4, 5 or 8 coefficients (k1 k2 p1 p2 [k3 [k4 k5 k6]]).  Pinned against cv2 4.13 (tests/golden/cv2_undistort.npz).
+static inline void undistort_points_f32(const float* src_xy, int n, float fxf, float fyf, float cxf, float cyf, const float* dist, int nd, float* dst_xy)
+{
+    double k[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < nd && i < 14; i++) k[i] = (double)dist[i];
+    const double fx = fxf, fy = fyf, cx = cxf, cy = cyf, ifx = 1. / fx, ify = 1. / fy;
+    for (int i = 0; i < n; i++) {
+        double x = src_xy[2 * i], y = src_xy[2 * i + 1];
+        const double u = x, v = y;
+        x = (x - cx) * ifx;
+        y = (y - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; j++) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = fx * x + 0.0 * y + cx;
+        const double yy = 0.0 * x + fy * y + cy;
+        const double ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+        dst_xy[2 * i] = (float)(xx * ww);
+        dst_xy[2 * i + 1] = (float)(yy * ww);
+    }
+}
+
 }  // namespace cvp
+
+

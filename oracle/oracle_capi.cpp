@@ -68,6 +68,27 @@ void orc_level_kps(orc_ctx* c, int level, KeyPoint* out)
 void orc_resize(const uint8_t* src, int sw, int sh, uint8_t* dst, int dw, int dh) { cvp::resize_linear_u8(src, sw, sh, sw, dst, dw, dh, dw); }
 void orc_remap(const uint8_t* src, int sw, int sh, const float* mapx, const float* mapy, uint8_t* dst, int dw, int dh) { cvp::remap_linear_u8(src, sw, sh, sw, mapx, mapy, dst, dw, dh, dw); }
 void orc_cvt_gray(const uint8_t* src, int w, int h, int channels, int rgb_order, uint8_t* dst) { cvp::cvt_gray_u8(src, w, h, (size_t)w * channels, channels, rgb_order != 0, dst, w); }
+void orc_undistort_points(const float* src_xy, int n, const float* K4, const float* dist, int nd, float* dst_xy) { cvp::undistort_points_f32(src_xy, n, K4[0], K4[1], K4[2], K4[3], dist, nd, dst_xy); }
+// Frame::UndistortKeyPoints (Frame.cpp:462-496): copy when mDistCoef(0) == 0, else cv::undistortPoints on the (x, y) pairs.
+void orc_undistort_keypoints(const KeyPoint* kps, int n, const float* K4, const float* dist, int nd, KeyPoint* out)
+{
+    for (int i = 0; i < n; i++) out[i] = kps[i];
+    if (dist[0] == 0.0) return;
+    std::vector<float> xy(2 * (size_t)n + 2), un(2 * (size_t)n + 2);
+    for (int i = 0; i < n; i++) { xy[2 * i] = kps[i].x; xy[2 * i + 1] = kps[i].y; }
+    cvp::undistort_points_f32(xy.data(), n, K4[0], K4[1], K4[2], K4[3], dist, nd, un.data());
+    for (int i = 0; i < n; i++) { out[i].x = un[2 * i]; out[i].y = un[2 * i + 1]; }
+}
+// Frame::ComputeImageBounds (Frame.cpp:498-536) -> {mnMinX, mnMinY, mnMaxX, mnMaxY}
+void orc_image_bounds(int cols, int rows, const float* K4, const float* dist, int nd, float* b)
+{
+    if (dist[0] != 0.0) {
+        const float c[8] = {0.f, 0.f, (float)cols, 0.f, 0.f, (float)rows, (float)cols, (float)rows};
+        float u[8];
+        cvp::undistort_points_f32(c, 4, K4[0], K4[1], K4[2], K4[3], dist, nd, u);
+        b[0] = std::min(u[0], u[4]); b[2] = std::max(u[2], u[6]); b[1] = std::min(u[1], u[3]); b[3] = std::max(u[5], u[7]);
+    } else { b[0] = 0.0f; b[2] = (float)cols; b[1] = 0.0f; b[3] = (float)rows; }
+}
 void orc_blur(const uint8_t* src, int w, int h, uint8_t* dst, int legacy) { cvp::gaussian_blur7_u8(src, w, h, w, dst, w, legacy != 0); }
 int orc_fast(const uint8_t* img, int w, int h, int th, int* xys, int cap)
 {

@@ -302,6 +302,30 @@ def search_for_triangulation(desc1, kps1, ur1, has1, fv1, desc2, kps2, ur2, has2
     return out, n
 
 
+def undistort_points(xy, K4, dist):
+    """cv::undistortPoints(xy, K, dist, noArray(), K) on float32 (n, 2)."""
+    xy = np.ascontiguousarray(xy, np.float32); K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    out = np.zeros_like(xy)
+    lib().orc_undistort_points(_p(xy), len(xy), _p(K4), _p(dist), len(dist), _p(out))
+    return out
+
+
+def undistort_keypoints(kps, K4, dist):
+    """Frame::UndistortKeyPoints -> mvKeysUn."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE); K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    out = np.zeros_like(kps)
+    lib().orc_undistort_keypoints(_p(kps), len(kps), _p(K4), _p(dist), len(dist), _p(out))
+    return out
+
+
+def image_bounds(cols, rows, K4, dist):
+    """Frame::ComputeImageBounds -> (mnMinX, mnMinY, mnMaxX, mnMaxY) float32."""
+    K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    b = np.zeros(4, np.float32)
+    lib().orc_image_bounds(int(cols), int(rows), _p(K4), _p(dist), len(dist), _p(b))
+    return b
+
+
 class OracleFrame:
     """Frame grid + GetFeaturesInArea + the Search* loops on flattened arrays (oracle)."""
 

@@ -94,6 +94,69 @@ extern "C" int orbm_distinctive_descriptors(const uint8_t* desc_host, const int6
     return ORBB_OK;
 }
 
+// ---- Frame::UndistortKeyPoints / ComputeImageBounds (Frame.cpp:462-536) ----------------------------------------------------
+static int undistort_args(const float* K4, const float* dist, int ndist, UndistortArgs& a)
+{
+    if (!K4 || !dist || (ndist != 4 && ndist != 5 && ndist != 8 && ndist != 12) || K4[0] == 0.f || K4[1] == 0.f) return ORBB_E_INVALID;
+    a.fx = K4[0]; a.fy = K4[1]; a.cx = K4[2]; a.cy = K4[3];
+    a.ifx = 1. / a.fx; a.ify = 1. / a.fy;
+    for (int i = 0; i < 12; i++) a.k[i] = i < ndist ? (double)dist[i] : 0.0;
+    a.identity = dist[0] == 0.0;                            // Frame.cpp:465
+    return ORBB_OK;
+}
+
+extern "C" int orbm_undistort_keypoints_device(const orbx_keypoint* kps_dev, int n, const float* K4, const float* dist, int ndist,
+                                               orbx_keypoint* kps_un_dev, int device, void* stream)
+{
+    UndistortArgs a;
+    if (n < 0 || (n > 0 && (!kps_dev || !kps_un_dev)) || undistort_args(K4, dist, ndist, a) != ORBB_OK) return ORBB_E_INVALID;
+    const int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    if (n == 0) return ORBB_OK;
+    undistort_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(kps_dev, kps_un_dev, n, a);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    return ORBB_OK;
+}
+
+extern "C" int orbm_undistort_keypoints(const orbx_keypoint* kps_host, int n, const float* K4, const float* dist, int ndist,
+                                        orbx_keypoint* kps_un_host, int device)
+{
+    UndistortArgs a;
+    if (n < 0 || (n > 0 && (!kps_host || !kps_un_host)) || undistort_args(K4, dist, ndist, a) != ORBB_OK) return ORBB_E_INVALID;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    if (n == 0) return ORBB_OK;
+    DevBuf in, out;
+    if ((rc = in.alloc((size_t)n * sizeof(orbx_keypoint))) || (rc = out.alloc((size_t)n * sizeof(orbx_keypoint)))) return rc;
+    ORBB_CUDA(cudaMemcpy(in.p, kps_host, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
+    undistort_kernel<<<ceil_div(n, 256), 256>>>(in.as<orbx_keypoint>(), out.as<orbx_keypoint>(), n, a);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    ORBB_CUDA(cudaMemcpy(kps_un_host, out.p, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost));
+    return ORBB_OK;
+}
+
+extern "C" int orbm_image_bounds(int cols, int rows, const float* K4, const float* dist, int ndist, float* bounds4, int device)
+{
+    UndistortArgs a;
+    if (cols <= 0 || rows <= 0 || !bounds4 || undistort_args(K4, dist, ndist, a) != ORBB_OK) return ORBB_E_INVALID;
+    if (a.identity) {                                        // Frame.cpp:527-533; no device work
+        const int rc = check_device(device);
+        if (rc != ORBB_OK) return rc;
+        bounds4[0] = 0.0f; bounds4[1] = 0.0f; bounds4[2] = (float)cols; bounds4[3] = (float)rows;
+        return ORBB_OK;
+    }
+    orbx_keypoint c[4], u[4];
+    memset(c, 0, sizeof(c));
+    c[1].x = (float)cols; c[2].y = (float)rows; c[3].x = (float)cols; c[3].y = (float)rows;       // :504-511
+    const int rc = orbm_undistort_keypoints(c, 4, K4, dist, ndist, u, device);
+    if (rc != ORBB_OK) return rc;
+    bounds4[0] = std::min(u[0].x, u[2].x); bounds4[2] = std::max(u[1].x, u[3].x);                   // :518-521
+    bounds4[1] = std::min(u[0].y, u[1].y); bounds4[3] = std::max(u[2].y, u[3].y);
+    return ORBB_OK;
+}
+
 // ---- frame -------------------------------------------------------------------------------------------
 struct orbm_frame {
     int device = 0, n = 0;

@@ -92,6 +92,56 @@ __global__ void __launch_bounds__(256) bow_join_kernel(const uint4* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------------
+// Frame::UndistortKeyPoints (Frame.cpp:462-496) = cv::undistortPoints(pts, K, D, noArray(), K) on the keypoint coordinates.
+// OpenCV 4.x (cvUndistortPointsInternal): double arithmetic on float inputs, five fixed-point iterations of the Brown model
+// (TermCriteria(MAX_ITER, 5, 0.01) of the 6-argument overload), the icdist < 0 escape, then re-projection with P = K.  Every
+// operation is an explicit round-to-nearest intrinsic so that no multiply-add is contracted: bit-equal to cv2 4.13.
+// ------------------------------------------------------------------------------------------------------
+struct UndistortArgs {
+    double fx, fy, cx, cy, ifx, ify;
+    double k[12];
+    int identity;          // mDistCoef(0) == 0: mvKeysUn = mvKeys
+};
+
+__global__ void __launch_bounds__(256) undistort_kernel(const orbx_keypoint* in, orbx_keypoint* out, int n,   // in == out allowed
+                                                         const __grid_constant__ UndistortArgs a)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    orbx_keypoint kp = in[i];
+    if (!a.identity) {
+#define DM(p, q) __dmul_rn((p), (q))
+#define DA(p, q) __dadd_rn((p), (q))
+#define DS(p, q) __dsub_rn((p), (q))
+        const double u = (double)kp.x, v = (double)kp.y;
+        double x = DM(DS(u, a.cx), a.ifx), y = DM(DS(v, a.cy), a.ify);
+        const double x0 = x, y0 = y;
+        const double* k = a.k;
+#pragma unroll 1
+        for (int j = 0; j < 5; j++) {
+            const double r2 = DA(DM(x, x), DM(y, y));
+            const double num = DA(1.0, DM(DA(DM(DA(DM(k[7], r2), k[6]), r2), k[5]), r2));
+            const double den = DA(1.0, DM(DA(DM(DA(DM(k[4], r2), k[1]), r2), k[0]), r2));
+            const double icdist = __ddiv_rn(num, den);
+            if (icdist < 0) { x = DM(DS(u, a.cx), a.ifx); y = DM(DS(v, a.cy), a.ify); break; }
+            const double deltaX = DA(DA(DA(DM(DM(DM(2.0, k[2]), x), y), DM(k[3], DA(r2, DM(DM(2.0, x), x)))), DM(k[8], r2)), DM(DM(k[9], r2), r2));
+            const double deltaY = DA(DA(DA(DM(k[2], DA(r2, DM(DM(2.0, y), y))), DM(DM(DM(2.0, k[3]), x), y)), DM(k[10], r2)), DM(DM(k[11], r2), r2));
+            x = DM(DS(x0, deltaX), icdist);
+            y = DM(DS(y0, deltaY), icdist);
+        }
+        const double xx = DA(DA(DM(a.fx, x), DM(0.0, y)), a.cx);
+        const double yy = DA(DA(DM(0.0, x), DM(a.fy, y)), a.cy);
+        const double ww = __ddiv_rn(1.0, DA(DA(DM(0.0, x), DM(0.0, y)), 1.0));
+        kp.x = (float)DM(xx, ww);
+        kp.y = (float)DM(yy, ww);
+#undef DM
+#undef DA
+#undef DS
+    }
+    out[i] = kp;
+}
+
+// ------------------------------------------------------------------------------------------------------
 // Frame grid
 // ------------------------------------------------------------------------------------------------------
 struct FrameDev {

@@ -30,6 +30,22 @@ inline void orbm_check(int rc, const char* where)
     throw MatcherDeviceError(rc, msg);
 }
 
+// Frame::UndistortKeyPoints / ComputeImageBounds (src/Frame.cpp:462-536).  K4 = {fx, fy, cx, cy}; distCoef = mDistCoef (4, 5, 8 or 12 floats).
+inline void UndistortKeyPoints(const std::vector<cv::KeyPoint>& mvKeys, const float K4[4], const std::vector<float>& distCoef,
+                               std::vector<cv::KeyPoint>& mvKeysUn, int device = 0)
+{
+    mvKeysUn.resize(mvKeys.size());
+    orbm_check(orbm_undistort_keypoints((const orbx_keypoint*)mvKeys.data(), (int)mvKeys.size(), K4, distCoef.data(), (int)distCoef.size(),
+                                        (orbx_keypoint*)mvKeysUn.data(), device), "orbm_undistort_keypoints");
+}
+inline void ComputeImageBounds(int cols, int rows, const float K4[4], const std::vector<float>& distCoef, float& mnMinX, float& mnMinY,
+                               float& mnMaxX, float& mnMaxY, int device = 0)
+{
+    float b[4];
+    orbm_check(orbm_image_bounds(cols, rows, K4, distCoef.data(), (int)distCoef.size(), b, device), "orbm_image_bounds");
+    mnMinX = b[0]; mnMinY = b[1]; mnMaxX = b[2]; mnMaxY = b[3];
+}
+
 // Device image of a Frame's matching state: mvKeysUn, mDescriptors and the 64x48 grid (src/Frame.cc:241-257).
 class DeviceFrame {
 public:

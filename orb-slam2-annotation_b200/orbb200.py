@@ -26,7 +26,7 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
            "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbx_set_rectification", "orbx_extract_batch_rectified", "orbx_remap_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
-           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_frame_create_device",
+           "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_frame_create_device", "orbm_undistort_keypoints", "orbm_undistort_keypoints_device", "orbm_image_bounds",
            "orbm_search_by_projection_points_device", "orbm_search_by_projection_frame_device", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
@@ -91,6 +91,9 @@ def lib():
         L.orbv_compute_bow.argtypes = [vp, vp, i32, i32] + [vp] * 7
         L.orbm_frame_destroy.argtypes = [vp]
         L.orbm_window_search.argtypes = [vp, vp, i32, vp, vp, vp, i32]
+        L.orbm_undistort_keypoints.argtypes = [vp, i32, vp, vp, i32, vp, i32]
+        L.orbm_undistort_keypoints_device.argtypes = [vp, i32, vp, vp, i32, vp, i32, vp]
+        L.orbm_image_bounds.argtypes = [i32, i32, vp, vp, i32, vp, i32]
         L.orbm_frame_create_device.argtypes = [C.POINTER(vp), vp, vp, i32, f32, f32, f32, f32, i32, vp]
         L.orbm_search_by_projection_points_device.argtypes = [vp, vp, vp, i32, f32, vp, vp, vp, vp, i32, vp]
         L.orbm_search_by_projection_frame_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp, i32, vp]
@@ -371,6 +374,28 @@ def search_for_triangulation(desc1, kps1, ur1, has1, fv1, desc2, kps2, ur2, has2
                                                _p(F12), float(ex), float(ey), _p(sf2), _p(ls2), int(only_stereo), int(check_ori), _p(out),
                                                C.byref(n), device), "orbm_search_for_triangulation")
     return out, n.value
+
+
+def undistort_keypoints(kps, K4, dist, device=0):
+    """Frame::UndistortKeyPoints (Frame.cpp:462-496) -> mvKeysUn."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE); K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    out = np.zeros_like(kps)
+    _check(lib().orbm_undistort_keypoints(_p(kps), len(kps), _p(K4), _p(dist), len(dist), _p(out), device), "orbm_undistort_keypoints")
+    return out
+
+
+def undistort_keypoints_device(kps_ptr, n, K4, dist, out_ptr, device=0, stream=0):
+    K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    _check(lib().orbm_undistort_keypoints_device(C.c_void_p(kps_ptr), n, _p(K4), _p(dist), len(dist), C.c_void_p(out_ptr), device, C.c_void_p(stream)),
+           "orbm_undistort_keypoints_device")
+
+
+def image_bounds(cols, rows, K4, dist, device=0):
+    """Frame::ComputeImageBounds (Frame.cpp:498-536) -> float32 (mnMinX, mnMinY, mnMaxX, mnMaxY)."""
+    K4 = np.ascontiguousarray(K4, np.float32); dist = np.ascontiguousarray(dist, np.float32)
+    b = np.zeros(4, np.float32)
+    _check(lib().orbm_image_bounds(int(cols), int(rows), _p(K4), _p(dist), len(dist), _p(b), device), "orbm_image_bounds")
+    return b
 
 
 def distinctive_descriptors(desc, offsets, device=0):

@@ -18,6 +18,10 @@ pinned against outputs of the real implementations, generated here and committed
                   rectification-like map (cv2.initUndistortRectifyMap of a distorted pinhole camera) and a hostile map (fractions
                   on every 1/32 step, out-of-range and negative coordinates).  (python make_golden.py --remap regenerates it.)
 
+  cv2_undistort.npz  cv2.undistortPoints(pts, K, D, None, K) (Frame::UndistortKeyPoints / ComputeImageBounds, Frame.cpp:462-536): the
+                  EuRoC, TUM1 and a strong 5/8-coefficient calibration on seeded points inside and far outside the image (the
+                  icdist < 0 branch included).  (python make_golden.py --undistort regenerates it.)
+
 Inputs are regenerated from seeds by synth.py (numpy only), so only outputs are stored.  Usage: python tests/golden/make_golden.py
 """
 import hashlib
@@ -113,6 +117,33 @@ def main_remap():
     print("cv2_remap.npz", os.path.getsize(os.path.join(HERE, "cv2_remap.npz")), "bytes")
 
 
+def undistort_cases():
+    """(name, K4 = fx fy cx cy, dist, w, h): ORB-SLAM2's shipped calibrations (Examples/Monocular/EuRoC.yaml, TUM1.yaml) + hostile ones."""
+    return [("euroc", [458.654, 457.296, 367.215, 248.375], [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], 752, 480),
+            ("tum1", [517.306408, 516.469215, 318.643040, 255.313989], [0.262383, -0.953104, -0.005358, 0.002628, 1.163314], 640, 480),
+            ("strong8", [300.0, 310.0, 320.0, 240.0], [-0.45, 0.31, 0.004, -0.003, -0.12, 0.02, -0.01, 0.005], 640, 480),
+            ("barrel", [200.0, 200.0, 320.0, 240.0], [-0.9, 0.2, 0.0, 0.0], 640, 480)]
+
+
+def undistort_points_in(w, h, seed):
+    rng = np.random.default_rng(seed)
+    inside = np.stack([rng.uniform(0, w, 3000), rng.uniform(0, h, 3000)], 1)
+    grid = np.stack(np.meshgrid(np.arange(0, w + 1, 40.0), np.arange(0, h + 1, 40.0)), -1).reshape(-1, 2)     # integer pixels, corners included
+    far = np.stack([rng.uniform(-3 * w, 4 * w, 500), rng.uniform(-3 * h, 4 * h, 500)], 1)                   # far outside: icdist < 0 happens
+    return np.concatenate([inside, grid, far]).astype(np.float32)
+
+
+def main_undistort():
+    import cv2
+    out = {"cv2_version": np.array(cv2.__version__)}
+    for i, (name, K4, D, w, h) in enumerate(undistort_cases()):
+        K = np.array([[K4[0], 0, K4[2]], [0, K4[1], K4[3]], [0, 0, 1]], np.float32)
+        pts = undistort_points_in(w, h, 300 + i)
+        out[name] = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, np.array(D, np.float32), None, K).reshape(-1, 2)
+    np.savez_compressed(os.path.join(HERE, "cv2_undistort.npz"), **out)
+    print("cv2_undistort.npz", os.path.getsize(os.path.join(HERE, "cv2_undistort.npz")), "bytes")
+
+
 def main():
     import cv2
     cv2.setNumThreads(1)
@@ -167,9 +198,12 @@ def main():
 
 
 if __name__ == "__main__":
-    if "--cvtcolor" not in sys.argv and "--remap" not in sys.argv:
+    only = [a for a in ("--cvtcolor", "--remap", "--undistort") if a in sys.argv]
+    if not only:
         main()
-    if "--remap" not in sys.argv:
+    if not only or "--cvtcolor" in only:
         main_cvtcolor()
-    if "--cvtcolor" not in sys.argv:
+    if not only or "--remap" in only:
         main_remap()
+    if not only or "--undistort" in only:
+        main_undistort()

@@ -449,3 +449,78 @@ def test_search_by_projection_device_resident(gpu):
         n2, m2 = O.search_reloc(_to_oracle_queries(qq), 100, True, np.full(len(kc), -1, np.int32))
         assert n1 == n2 and np.array_equal(m1, m2)
     F.close()
+
+
+def test_undistort_keypoints_and_image_bounds(gpu):
+    """Frame::UndistortKeyPoints / ComputeImageBounds (Frame.cpp:462-536) on the device: bit-equal to cv2 4.13 (golden) and the oracle."""
+    import os, sys
+    import orbb200, pyoracle
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, gold)
+    import make_golden as GEN
+    g = np.load(os.path.join(gold, "cv2_undistort.npz"))
+    rng = np.random.default_rng(3)
+    for i, (name, K4, D, w, h) in enumerate(GEN.undistort_cases()):
+        pts = GEN.undistort_points_in(w, h, 300 + i)
+        kps = np.zeros(len(pts), orbb200.KP_DTYPE)
+        kps["x"] = pts[:, 0]; kps["y"] = pts[:, 1]
+        kps["angle"] = rng.uniform(0, 360, len(pts)); kps["octave"] = rng.integers(0, 8, len(pts)); kps["response"] = rng.uniform(0, 200, len(pts))
+        un = orbb200.undistort_keypoints(kps, K4, D)
+        got = np.stack([un["x"], un["y"]], 1)
+        assert np.array_equal(got.view(np.uint32), g[name].view(np.uint32)), name
+        for f in ("size", "angle", "response", "octave", "class_id"):
+            assert np.array_equal(un[f], kps[f])
+        assert np.array_equal(un.view(np.uint8), pyoracle.undistort_keypoints(kps, K4, D).view(np.uint8))
+        assert np.array_equal(orbb200.image_bounds(w, h, K4, D), pyoracle.image_bounds(w, h, K4, D))
+    # mDistCoef(0) == 0: copy, bounds = the image rectangle (even when later coefficients are set, as the reference does)
+    K4 = [458.654, 457.296, 367.215, 248.375]
+    un = orbb200.undistort_keypoints(kps, K4, [0, 0.2, 0, 0])
+    assert np.array_equal(un.view(np.uint8), kps.view(np.uint8))
+    assert orbb200.image_bounds(752, 480, K4, [0, 0.2, 0, 0]).tolist() == [0, 0, 752, 480]
+    assert len(orbb200.undistort_keypoints(kps[:0], K4, [0.1, 0, 0, 0])) == 0
+    with pytest.raises(orbb200.OrbError):
+        orbb200.undistort_keypoints(kps, K4, [0.1, 0, 0])                          # 3 coefficients: not a calibration OpenCV accepts
+
+
+def test_tracked_frame_stays_on_device(gpu):
+    """SURVEY 8(f)-1 end to end: extract (device) -> undistort (device, in place) -> grid (device) -> SearchByProjection candidates and
+    resolve (device).  Only the final match state is read back; every stage equals the oracle chain."""
+    import torch
+    import orbb200, pyoracle
+    from synth import synth
+    w, h, nf = 752, 480, 1200
+    K4 = [458.654, 457.296, 367.215, 248.375]; D = [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05]
+    big = synth(w + 16, h + 16, 31)
+    cur = big[8:8 + h, 8:8 + w].copy(); last = big[9:9 + h, 11:11 + w].copy()
+    oex = pyoracle.OracleExtractor(nf)
+    kc, dc = oex.extract(cur); kl, dl = oex.extract(last)
+    scale = oex.tables()["scale"]
+    kcu = pyoracle.undistort_keypoints(kc, K4, D); klu = pyoracle.undistort_keypoints(kl, K4, D)
+    bounds = pyoracle.image_bounds(w, h, K4, D)
+    rng = np.random.default_rng(5)
+    q = _queries(klu, dl, scale, 15.0, (3, 1), rng, "pm1")
+    mp0 = np.full(len(kc), -1, np.int32); ob0 = np.zeros(len(kc), np.int32)
+    on, omp, oob = pyoracle.OracleFrame(kcu, dc, bounds).search_last_frame(_to_oracle_queries(q), True, mp0, ob0, None)
+
+    dev = torch.device("cuda:0")
+    ex = orbb200.ORBextractor(nf, max_size=(w, h))
+    cap = 2 * nf
+    t_img = torch.from_numpy(cur).to(dev)
+    t_k = torch.zeros(cap * 28, dtype=torch.uint8, device=dev); t_d = torch.zeros(cap * 32, dtype=torch.uint8, device=dev)
+    t_n = torch.zeros(1, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    ex.extract_batch_device(t_img.data_ptr(), 1, w, h, w, w * h, t_k.data_ptr(), t_d.data_ptr(), t_n.data_ptr(), cap)
+    st = ex.stream()
+    n = len(kc)                              # the one scalar a real caller would read (or size the grid for `capacity`)
+    orbb200.undistort_keypoints_device(t_k.data_ptr(), n, K4, D, t_k.data_ptr(), 0, st)
+    F = orbb200.FrameMatcher.from_device(t_k.data_ptr(), t_d.data_ptr(), n, orbb200.image_bounds(w, h, K4, D), 0, st)
+    ex.sync()
+    assert int(t_n.cpu()[0]) == n
+    t_q = torch.from_numpy(q.view(np.uint8).reshape(len(q), -1).copy()).to(dev)
+    t_mp = torch.from_numpy(mp0.copy()).to(dev); t_ob = torch.from_numpy(ob0.copy()).to(dev); t_sc = torch.zeros(2, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    orbb200.ORBmatcher(0.9, True).SearchByProjection_device("frame", F, t_q.data_ptr(), len(q), t_mp.data_ptr(), t_ob.data_ptr(), t_sc.data_ptr(),
+                                                            t_sc.data_ptr() + 4, stream=st)
+    ex.sync()
+    assert t_sc.cpu().tolist() == [on, 0] and np.array_equal(t_mp.cpu().numpy(), omp) and on > 300
+    F.close()
