@@ -728,8 +728,8 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
             ORBB_LAUNCHED();
         } else if (channels > 1) {
             const size_t fbytes = (size_t)w * ht * CH_;
-            cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nf), 128, 0, kst>>>(h->d_color + (size_t)f0 * fbytes, (long long)((size_t)w * CH_), (long long)fbytes,
-                w, channels, rgb_order, h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
+            launch_cvt_gray(h->d_color + (size_t)f0 * fbytes, (long long)((size_t)w * CH_), (long long)fbytes, w, ht, channels, rgb_order,
+                            h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, (long long)dpitch0, (long long)h->pyr_fstride, nf, kst);
             ORBB_LAUNCHED();
         }
         const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, ks, false);   // chunks already overlap each other: side octrees only add launches
@@ -749,8 +749,8 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
             ORBB_LAUNCHED();
         } else if (channels > 1) {
             const size_t fbytes = (size_t)w * ht * CH_;
-            cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nframes), 128, 0, st>>>(h->d_color, (long long)((size_t)w * CH_), (long long)fbytes,
-                w, channels, rgb_order, h->d_pyr + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
+            launch_cvt_gray(h->d_color, (long long)((size_t)w * CH_), (long long)fbytes, w, ht, channels, rgb_order, h->d_pyr + g0.off,
+                            (long long)dpitch0, (long long)h->pyr_fstride, nframes, st);
             ORBB_LAUNCHED();
         }
         const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap);
@@ -867,8 +867,8 @@ extern "C" int orbx_cvt_gray_device(const uint8_t* src_dev, int nframes, int w, 
 {
     if (!src_dev || !dst_dev || nframes < 1 || (channels != 3 && channels != 4)) return ORBB_E_INVALID;
     if (w < 1 || ht < 1 || src_stride < (size_t)w * channels || dst_stride < (size_t)w) return ORBB_E_BAD_SHAPE;
-    cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nframes), 128, 0, (cudaStream_t)stream>>>(src_dev, (long long)src_stride, (long long)src_fstride,
-        w, channels, rgb_order ? 1 : 0, dst_dev, (long long)dst_stride, (long long)dst_fstride);
+    launch_cvt_gray(src_dev, (long long)src_stride, (long long)src_fstride, w, ht, channels, rgb_order ? 1 : 0, dst_dev, (long long)dst_stride,
+                    (long long)dst_fstride, nframes, (cudaStream_t)stream);
     ORBB_LAUNCHED();
     ORBB_CUDA(cudaGetLastError());
     return ORBB_OK;

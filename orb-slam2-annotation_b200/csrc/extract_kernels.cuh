@@ -59,6 +59,62 @@ __global__ void __launch_bounds__(128) cvt_gray_kernel(const uint8_t* __restrict
     else for (int i = 0; i < n; i++) d[i] = (uint8_t)g[i];
 }
 
+// Frames whose rows are contiguous on both sides (source pitch = w*CH, destination pitch = w, 16-byte aligned frame bases): the frame
+// is one flat array.  A thread converts 16 pixels: CH 128-bit loads, one 128-bit store; a CTA covers 4096 pixels.
+template <int CH>
+__global__ void __launch_bounds__(256) cvt_gray_flat_kernel(const uint8_t* __restrict__ src, long long sfstride, int npix, int rgb,
+                                                            uint8_t* __restrict__ dst, long long dfstride)
+{
+    const int f = blockIdx.y;
+    const uint8_t* s = src + (long long)f * sfstride;
+    uint8_t* d = dst + (long long)f * dfstride;
+    const int p0 = 16 * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (p0 >= npix) return;
+    if (p0 + 16 <= npix) {
+        unsigned in[4 * CH];
+#pragma unroll
+        for (int i = 0; i < CH; i++) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(s + (long long)p0 * CH) + i);
+            in[4 * i] = v.x; in[4 * i + 1] = v.y; in[4 * i + 2] = v.z; in[4 * i + 3] = v.w;
+        }
+        unsigned out[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            unsigned g[4];
+            if (CH == 4) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) { const unsigned v = in[4 * j + i]; g[i] = cvt_gray_px(v & 255u, (v >> 8) & 255u, (v >> 16) & 255u, rgb); }
+            } else {
+                const unsigned a = in[3 * j], b = in[3 * j + 1], c = in[3 * j + 2];
+                g[0] = cvt_gray_px(a & 255u, (a >> 8) & 255u, (a >> 16) & 255u, rgb);
+                g[1] = cvt_gray_px(a >> 24, b & 255u, (b >> 8) & 255u, rgb);
+                g[2] = cvt_gray_px((b >> 16) & 255u, b >> 24, c & 255u, rgb);
+                g[3] = cvt_gray_px((c >> 8) & 255u, (c >> 16) & 255u, c >> 24, rgb);
+            }
+            out[j] = g[0] | (g[1] << 8) | (g[2] << 16) | (g[3] << 24);
+        }
+        *reinterpret_cast<uint4*>(d + p0) = make_uint4(out[0], out[1], out[2], out[3]);
+    } else {
+        for (int p = p0; p < npix; p++) d[p] = (uint8_t)cvt_gray_px(s[(long long)p * CH], s[(long long)p * CH + 1], s[(long long)p * CH + 2], rgb);
+    }
+}
+
+// picks the flat kernel when the layout allows it, the row kernel otherwise
+static inline void launch_cvt_gray(const uint8_t* src, long long spitch, long long sfstride, int w, int ht, int ch, int rgb,
+                                   uint8_t* dst, long long dpitch, long long dfstride, int nf, cudaStream_t st)
+{
+    const long long npix = (long long)w * ht;
+    const bool flat = spitch == (long long)w * ch && dpitch == w && npix < (1ll << 30) && (((uintptr_t)src | (uintptr_t)dst) & 15) == 0 &&
+                      (nf == 1 || ((sfstride | dfstride) & 15) == 0);
+    if (flat) {
+        const dim3 grid((unsigned)((npix + 16 * 256 - 1) / (16 * 256)), nf);
+        if (ch == 3) cvt_gray_flat_kernel<3><<<grid, 256, 0, st>>>(src, sfstride, (int)npix, rgb, dst, dfstride);
+        else cvt_gray_flat_kernel<4><<<grid, 256, 0, st>>>(src, sfstride, (int)npix, rgb, dst, dfstride);
+    } else {
+        cvt_gray_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nf), 128, 0, st>>>(src, spitch, sfstride, w, ch, rgb, dst, dpitch, dfstride);
+    }
+}
+
 // =====================================================================================================
 // cv::remap(src, dst, map1, map2, INTER_LINEAR), BORDER_CONSTANT 0 — stereo rectification in front of the extractor
 // (Examples/Stereo/stereo_euroc.cc:174-185).  The map arrives in cv::remap's own fixed point (1/32 pixel); the

@@ -336,17 +336,20 @@ static int resolve_on_device(const orbm_frame* fr, int mode, const float* uright
         (rc = fr->ws_dist.reserve((size_t)cap * 4)) || (rc = fr->ws_choice.reserve((size_t)nq * 4)) ||
         (rc = fr->ws_taker.reserve((size_t)fr->n * 4))) return rc;
     const int wpb = 8;
-    window_search_kernel<false><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, fr->ws_counts.as<int>(), nullptr, nullptr, nullptr, 0);
+    const WindowFilter flt{frame_mp_dev, frame_mp_obs_dev, uright_dev};
+    window_search_kernel<false, true><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, fr->ws_counts.as<int>(), nullptr, nullptr,
+                                                                            nullptr, 0, flt);
     ORBB_LAUNCHED();
     excl_scan_kernel<<<1, 1024, 0, st>>>(fr->ws_counts.as<int>(), fr->ws_offs.as<int>(), nq); ORBB_LAUNCHED();
-    window_search_kernel<true><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, nullptr, fr->ws_offs.as<int>(), fr->ws_idx.as<int>(),
-                                                                     fr->ws_dist.as<int>(), cap);
+    window_search_kernel<true, true><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, nullptr, fr->ws_offs.as<int>(),
+                                                                           fr->ws_idx.as<int>(), fr->ws_dist.as<int>(), cap, flt);
     ORBB_LAUNCHED();
     ResolveArgs a{};
     a.f = fr->f; a.q = q_dev; a.nq = nq; a.offs = fr->ws_offs.as<int>(); a.idx = fr->ws_idx.as<int>(); a.dist = fr->ws_dist.as<int>(); a.cap = cap;
     a.uright = uright_dev; a.nnratio = nnratio; a.check_ori = check_ori; a.frame_mp = frame_mp_dev; a.frame_mp_obs = frame_mp_obs_dev;
     a.choice = fr->ws_choice.as<int>(); a.taker = fr->ws_taker.as<int>(); a.nmatches = nmatches_dev; a.status = status_dev; a.rounds = rounds_dev;
-    if (mode == 0) resolve_projection_kernel<0><<<1, 1024, 0, st>>>(a); else resolve_projection_kernel<1><<<1, 1024, 0, st>>>(a);
+    const size_t smem = fr->n <= RESOLVE_SMEM_SLOTS ? (size_t)fr->n * 4 : 0;
+    if (mode == 0) resolve_projection_kernel<0><<<1, 1024, smem, st>>>(a); else resolve_projection_kernel<1><<<1, 1024, smem, st>>>(a);
     ORBB_LAUNCHED();
     ORBB_CUDA(cudaGetLastError());
     return ORBB_OK;

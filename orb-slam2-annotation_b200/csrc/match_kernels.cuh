@@ -209,10 +209,15 @@ __global__ void grid_sort_kernel(FrameDev f)
 // ------------------------------------------------------------------------------------------------------
 // GetFeaturesInArea + DescriptorDistance.  One warp per query; FILL=false counts, FILL=true writes.
 // ------------------------------------------------------------------------------------------------------
-template <bool FILL>
+// FILTER (the device resolve): records are orbm_proj_query; candidates that can never be chosen — the Frame slot already holds a
+// MapPoint with observations (ORBmatcher.cpp:112-114, :1590-1592) or the stereo gate fails (:116-121, :1594-1601) — are dropped
+// here, where the lanes of the warp test them in parallel, and cand_dist carries the candidate's octave in bits 16+.
+struct WindowFilter { const int* frame_mp; const int* frame_mp_obs; const float* uright; };
+
+template <bool FILL, bool FILTER = false>
 __global__ void window_search_kernel(FrameDev f, const void* __restrict__ qs, size_t qstride, int nq,   // records that START with an orbm_query
                                      int* __restrict__ counts, const int* __restrict__ offsets,
-                                     int* __restrict__ cand_idx, int* __restrict__ cand_dist, int cap)
+                                     int* __restrict__ cand_idx, int* __restrict__ cand_dist, int cap, WindowFilter flt = WindowFilter{})
 {
     const int lane = threadIdx.x & 31;
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -240,7 +245,7 @@ __global__ void window_search_kernel(FrameDev f, const void* __restrict__ qs, si
             const int b = f.cell_start[ix * GRID_ROWS + nMinCellY], e = f.cell_start[ix * GRID_ROWS + nMaxCellY + 1];
             for (int base = b; base < e; base += 32) {
                 const int j = base + lane;
-                bool ok = false; int idx = -1;
+                bool ok = false; int idx = -1, oct = 0;
                 if (j < e) {
                     idx = f.cell_items[j];
                     const orbx_keypoint kp = f.kps[idx];
@@ -251,13 +256,23 @@ __global__ void window_search_kernel(FrameDev f, const void* __restrict__ qs, si
                     }
                     const float dx = __fsub_rn(kp.x, x), dy = __fsub_rn(kp.y, y);
                     if (!(fabsf(dx) < r && fabsf(dy) < r)) ok = false;
+                    oct = kp.octave;
+                    if (FILTER && ok) {
+                        const orbm_proj_query& pq = reinterpret_cast<const orbm_proj_query&>(q);
+                        if (flt.frame_mp[idx] >= 0 && flt.frame_mp_obs[idx] > 0) ok = false;
+                        if (flt.uright) {
+                            const float urk = flt.uright[idx];
+                            if (urk > 0 && fabsf(__fsub_rn(pq.u_right, urk)) > pq.max_err_right) ok = false;
+                        }
+                    }
                 }
                 const unsigned bal = __ballot_sync(0xffffffffu, ok);
                 if (FILL && ok) {
                     const int pos = obase + total + __popc(bal & ((1u << lane) - 1));
                     if (pos < cap) {
                         cand_idx[pos] = idx;
-                        cand_dist[pos] = hamming256(q0, q1, f.desc[2 * idx], f.desc[2 * idx + 1]);
+                        const int d = hamming256(q0, q1, f.desc[2 * idx], f.desc[2 * idx + 1]);
+                        cand_dist[pos] = FILTER ? (d | (oct << 16)) : d;
                     }
                 }
                 total += __popc(bal);
@@ -320,24 +335,28 @@ struct ResolveArgs {
     int* nmatches; int* status; int* rounds;                       // device scalars (rounds may be nullptr)
 };
 
+constexpr int RESOLVE_SMEM_SLOTS = 12 * 1024;       // taker table in shared memory up to this many Frame features (48 KB)
+
 template <int MODE>
-__device__ __forceinline__ int resolve_choose(const ResolveArgs& a, int i)
+__device__ __forceinline__ int resolve_choose(const ResolveArgs& a, const int* __restrict__ taker, int i)
 {
-    const orbm_proj_query& pq = a.q[i];
-    const float ur = pq.u_right, maxer = pq.max_err_right;
     int bestDist = 256, bestDist2 = 256, bestLevel = -1, bestLevel2 = -1, bestIdx = -1;
-    for (int c = a.offs[i], e = a.offs[i + 1]; c < e; c++) {
-        const int k = a.idx[c];
-        if ((a.frame_mp[k] >= 0 && a.frame_mp_obs[k] > 0) || a.taker[k] < i) continue;
-        if (a.uright) {
-            const float urk = a.uright[k];
-            if (urk > 0 && fabsf(__fsub_rn(ur, urk)) > maxer) continue;
+    const int e = a.offs[i + 1];
+    for (int c0 = a.offs[i]; c0 < e; c0 += 4) {          // four candidates' loads in flight, then the reference's sequential update
+        int k[4], pd[4], tk[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) { const int c = min(c0 + j, e - 1); k[j] = a.idx[c]; pd[j] = a.dist[c]; }
+#pragma unroll
+        for (int j = 0; j < 4; j++) tk[j] = taker[k[j]];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (c0 + j >= e || tk[j] < i) continue;
+            const int d = pd[j] & 0xffff, oct = pd[j] >> 16;
+            if (MODE == 0) {
+                if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestLevel2 = bestLevel; bestLevel = oct; bestIdx = k[j]; }
+                else if (d < bestDist2) { bestLevel2 = oct; bestDist2 = d; }
+            } else if (d < bestDist) { bestDist = d; bestIdx = k[j]; }
         }
-        const int d = a.dist[c];
-        if (MODE == 0) {
-            if (d < bestDist) { bestDist2 = bestDist; bestDist = d; bestLevel2 = bestLevel; bestLevel = a.f.kps[k].octave; bestIdx = k; }
-            else if (d < bestDist2) { bestLevel2 = a.f.kps[k].octave; bestDist2 = d; }
-        } else if (d < bestDist) { bestDist = d; bestIdx = k; }
     }
     if (bestDist > TH_HIGH) return -1;
     if (MODE == 0 && bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(a.nnratio, (float)bestDist2)) return -1;
@@ -347,11 +366,13 @@ __device__ __forceinline__ int resolve_choose(const ResolveArgs& a, int i)
 template <int MODE>
 __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_constant__ ResolveArgs a)
 {
+    extern __shared__ int taker_s[];
     __shared__ int changed_s, nm_s, hist_s[30], ind_s[3];
     const int tid = threadIdx.x, nt = blockDim.x;
     if (a.offs[a.nq] > a.cap) { if (tid == 0) { *a.status = ORBB_E_CAPACITY; *a.nmatches = 0; } return; }
+    int* taker = a.f.n <= RESOLVE_SMEM_SLOTS ? taker_s : a.taker;
     for (int i = tid; i < a.nq; i += nt) a.choice[i] = -2;
-    for (int k = tid; k < a.f.n; k += nt) a.taker[k] = 0x7fffffff;
+    for (int k = tid; k < a.f.n; k += nt) taker[k] = 0x7fffffff;
     if (tid == 0) { nm_s = 0; changed_s = 0; }
     if (tid < 30) hist_s[tid] = 0;
     __syncthreads();
@@ -359,27 +380,27 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
     for (;;) {
         bool changed = false;
         for (int i = tid; i < a.nq; i += nt) {
-            const int c = resolve_choose<MODE>(a, i);
+            const int c = resolve_choose<MODE>(a, taker, i);
             if (c != a.choice[i]) { a.choice[i] = c; changed = true; }
         }
         if (changed) changed_s = 1;
         __syncthreads();
         const int any = changed_s;
         rounds++;
-        for (int k = tid; k < a.f.n; k += nt) a.taker[k] = 0x7fffffff;
+        for (int k = tid; k < a.f.n; k += nt) taker[k] = 0x7fffffff;
         __syncthreads();
         if (!any) break;
         if (tid == 0) changed_s = 0;
         for (int i = tid; i < a.nq; i += nt) {
             const int c = a.choice[i];
-            if (c >= 0 && a.q[i].has_obs > 0) atomicMin(&a.taker[c], i);
+            if (c >= 0 && a.q[i].has_obs > 0) atomicMin(&taker[c], i);
         }
         __syncthreads();
     }
     // slot k <- the last query that chose it; taker is reused as "last chooser" (reset to INT_MAX above: store -i-1 as min)
     for (int i = tid; i < a.nq; i += nt) {
         const int c = a.choice[i];
-        if (c >= 0) atomicMin(&a.taker[c], -i - 1);
+        if (c >= 0) atomicMin(&taker[c], -i - 1);
     }
     __syncthreads();
     int mine = 0;
@@ -387,7 +408,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
         const int c = a.choice[i];
         if (c < 0) continue;
         mine++;
-        if (a.taker[c] == -i - 1) { a.frame_mp[c] = a.q[i].id; a.frame_mp_obs[c] = a.q[i].has_obs; }
+        if (taker[c] == -i - 1) { a.frame_mp[c] = a.q[i].id; a.frame_mp_obs[c] = a.q[i].has_obs; }
         if (MODE == 1 && a.check_ori) {
             float rot = __fsub_rn(a.q[i].angle, a.f.kps[c].angle);
             if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
