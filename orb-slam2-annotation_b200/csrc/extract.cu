@@ -723,8 +723,8 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
         ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
         if (remap) {
             const size_t fbytes = (size_t)in_w * in_h;
-            remap_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nf), 128, 0, kst>>>(h->d_color + (size_t)f0 * fbytes, (long long)in_w, (long long)fbytes, in_w, in_h,
-                h->d_map, w, h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
+            launch_remap(h->d_color + (size_t)f0 * fbytes, (long long)in_w, (long long)fbytes, in_w, in_h, h->d_map, w, ht,
+                         h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, (long long)dpitch0, (long long)h->pyr_fstride, nf, kst);
             ORBB_LAUNCHED();
         } else if (channels > 1) {
             const size_t fbytes = (size_t)w * ht * CH_;
@@ -744,8 +744,8 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
     if (prof) {
         ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_in[nchunks - 1], 0));
         if (remap) {
-            remap_kernel<<<dim3(ceil_div(w, 4 * 128), ht, nframes), 128, 0, st>>>(h->d_color, (long long)in_w, (long long)((size_t)in_w * in_h), in_w, in_h,
-                h->d_map, w, h->d_pyr + g0.off, (long long)dpitch0, (long long)h->pyr_fstride);
+            launch_remap(h->d_color, (long long)in_w, (long long)((size_t)in_w * in_h), in_w, in_h, h->d_map, w, ht, h->d_pyr + g0.off,
+                         (long long)dpitch0, (long long)h->pyr_fstride, nframes, st);
             ORBB_LAUNCHED();
         } else if (channels > 1) {
             const size_t fbytes = (size_t)w * ht * CH_;
@@ -851,8 +851,8 @@ extern "C" int orbx_remap_device(const uint8_t* src_dev, int nframes, int src_w,
     ORBB_CUDA(cudaMalloc((void**)&d_map, m.size() * sizeof(int2)));
     cudaError_t e = cudaMemcpyAsync(d_map, m.data(), m.size() * sizeof(int2), cudaMemcpyHostToDevice, (cudaStream_t)stream);
     if (e == cudaSuccess) {
-        remap_kernel<<<dim3(ceil_div(dst_w, 4 * 128), dst_h, nframes), 128, 0, (cudaStream_t)stream>>>(src_dev, (long long)src_stride, (long long)src_fstride,
-            src_w, src_h, d_map, dst_w, dst_dev, (long long)dst_stride, (long long)dst_fstride);
+        launch_remap(src_dev, (long long)src_stride, (long long)src_fstride, src_w, src_h, d_map, dst_w, dst_h, dst_dev, (long long)dst_stride,
+                     (long long)dst_fstride, nframes, (cudaStream_t)stream);
         ORBB_LAUNCHED();
         e = cudaGetLastError();
     }

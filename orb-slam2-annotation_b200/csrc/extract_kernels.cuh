@@ -121,30 +121,116 @@ static inline void launch_cvt_gray(const uint8_t* src, long long spitch, long lo
 // bilinear weights (32-fx)(32-fy)*32 ... sum to 2^15; out = (sum w*p + 2^14) >> 15.  A thread produces four pixels and one
 // 32-bit store; the map (8 B per pixel, shared by all frames of the batch) stays in L2.
 // =====================================================================================================
-__global__ void __launch_bounds__(128) remap_kernel(const uint8_t* __restrict__ src, long long spitch, long long sfstride, int sw, int sh,
-                                                    const int2* __restrict__ map, int dw, uint8_t* __restrict__ dst, long long dpitch, long long dfstride)
+// FLAT (dw % 4 == 0): the destination frame is walked as one array of 4-pixel groups (grid = groups x frames), so that CTAs are
+// full whatever the row length; otherwise one CTA row per image row.
+template <bool FLAT>
+__global__ void __launch_bounds__(256) remap_kernel(const uint8_t* __restrict__ src, long long spitch, long long sfstride, int sw, int sh,
+                                                    const int2* __restrict__ map, int dw, int dh, uint8_t* __restrict__ dst, long long dpitch, long long dfstride,
+                                                    unsigned gpr_magic)
 {
-    const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x), y = blockIdx.y, f = blockIdx.z;
-    if (x >= dw) return;
+    int x, y, f;
+    if (FLAT) {                                   // host guarantees: groups * (dw / 4) < 2^32 (magic division exact), frames < 2 GB
+        const int g = blockIdx.x * blockDim.x + threadIdx.x, gpr = dw >> 2;
+        y = (int)__umulhi((unsigned)g, gpr_magic); x = 4 * (g - y * gpr); f = blockIdx.y;
+        if (y >= dh) return;
+    } else {
+        x = 4 * (blockIdx.x * blockDim.x + threadIdx.x); y = blockIdx.y; f = blockIdx.z;
+        if (x >= dw) return;
+    }
     const uint8_t* s = src + (long long)f * sfstride;
-    uint8_t* d = dst + (long long)f * dfstride + (long long)y * dpitch + x;
+    uint8_t* d = FLAT ? dst + (long long)f * dfstride + (unsigned)(y * (int)dpitch + x) : dst + (long long)f * dfstride + (long long)y * dpitch + x;
     const int n = min(4, dw - x);
     unsigned g[4] = {0u, 0u, 0u, 0u};
+    int2 m[4];
+    const int2* mp = FLAT ? map + (unsigned)(y * dw + x) : map + (long long)y * dw + x;
+    if (FLAT) {                                  // x % 4 == 0 and dw % 4 == 0: the four map entries are one aligned 32-byte run
+        const int4 a = __ldg(reinterpret_cast<const int4*>(mp)), b = __ldg(reinterpret_cast<const int4*>(mp) + 1);
+        m[0] = make_int2(a.x, a.y); m[1] = make_int2(a.z, a.w); m[2] = make_int2(b.x, b.y); m[3] = make_int2(b.z, b.w);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; i++) m[i] = i < n ? __ldg(mp + i) : make_int2(0, 0);
+    }
+    const unsigned sp32 = (unsigned)spitch;
+    const bool small = FLAT;                     // 32-bit source offsets (checked by launch_remap)
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         if (i >= n) break;
-        const int2 m = __ldg(map + (long long)y * dw + x + i);
-        const int ix = max(-32768, min(32767, m.x >> 5)), iy = max(-32768, min(32767, m.y >> 5));
-        const int fx = m.x & 31, fy = m.y & 31;
-        const bool x0 = ix >= 0 && ix < sw, x1 = ix + 1 >= 0 && ix + 1 < sw, y0 = iy >= 0 && iy < sh, y1 = iy + 1 >= 0 && iy + 1 < sh;
-        const uint8_t* r0 = s + (long long)iy * spitch + ix;
-        const uint8_t* r1 = r0 + spitch;
-        const int p00 = (x0 && y0) ? r0[0] : 0, p01 = (x1 && y0) ? r0[1] : 0, p10 = (x0 && y1) ? r1[0] : 0, p11 = (x1 && y1) ? r1[1] : 0;
-        const int acc = ((32 - fx) * (32 - fy) * p00 + fx * (32 - fy) * p01 + (32 - fx) * fy * p10 + fx * fy * p11) * 32;
-        g[i] = (unsigned)((acc + (1 << 14)) >> 15);
+        const int ix = m[i].x >> 5, iy = m[i].y >> 5;
+        const int fx = m[i].x & 31, fy = m[i].y & 31;
+        if (small && (unsigned)ix < (unsigned)(sw - 1) && (unsigned)iy < (unsigned)(sh - 1)) {
+            // all four taps inside the source: sum of (32-fx)(32-fy)*32 ... products, factored (exact integer arithmetic)
+            const uint8_t* r0 = s + ((unsigned)iy * sp32 + (unsigned)ix);
+            const int p00 = r0[0], p01 = r0[1], p10 = r0[sp32], p11 = r0[sp32 + 1];
+            const int top = p00 * (32 - fx) + p01 * fx, bot = p10 * (32 - fx) + p11 * fx;
+            g[i] = (unsigned)((top * (32 - fy) + bot * fy + 512) >> 10);
+        } else {
+            const int cx = max(-32768, min(32767, ix)), cy = max(-32768, min(32767, iy));
+            const bool x0 = cx >= 0 && cx < sw, x1 = cx + 1 >= 0 && cx + 1 < sw, y0 = cy >= 0 && cy < sh, y1 = cy + 1 >= 0 && cy + 1 < sh;
+            const uint8_t* r0 = s + (long long)cy * spitch + cx;
+            const uint8_t* r1 = r0 + spitch;
+            const int p00 = (x0 && y0) ? r0[0] : 0, p01 = (x1 && y0) ? r0[1] : 0, p10 = (x0 && y1) ? r1[0] : 0, p11 = (x1 && y1) ? r1[1] : 0;
+            const int acc = ((32 - fx) * (32 - fy) * p00 + fx * (32 - fy) * p01 + (32 - fx) * fy * p10 + fx * fy * p11) * 32;
+            g[i] = (unsigned)((acc + (1 << 14)) >> 15);
+        }
     }
     if (n == 4 && ((uintptr_t)d & 3) == 0) *reinterpret_cast<unsigned*>(d) = g[0] | (g[1] << 8) | (g[2] << 16) | (g[3] << 24);
     else for (int i = 0; i < n; i++) d[i] = (uint8_t)g[i];
+}
+
+// Lane-consecutive variant (frames below 2 GB): a warp covers 128 consecutive destination pixels of the flattened frame, lane l
+// takes pixels l, l+32, l+64, l+96, so that a warp's map loads are contiguous 256-byte runs and its source taps fall into one or
+// two cache lines per load instruction (the L1 data pipe, not HBM, bounds this gather).  magic = ceil(2^32 / dw).
+__global__ void __launch_bounds__(256) remap_lanes_kernel(const uint8_t* __restrict__ src, unsigned spitch, long long sfstride, int sw, int sh,
+                                                          const int2* __restrict__ map, int dw, int npix, uint8_t* __restrict__ dst, unsigned dpitch,
+                                                          long long dfstride, unsigned magic)
+{
+    const int lane = threadIdx.x & 31;
+    const int base = 128 * (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) + lane;
+    const uint8_t* s = src + (long long)blockIdx.y * sfstride;
+    uint8_t* d = dst + (long long)blockIdx.y * dfstride;
+    int2 m[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) m[i] = base + 32 * i < npix ? __ldg(map + base + 32 * i) : make_int2(-64, -64);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int p = base + 32 * i;
+        if (p >= npix) break;
+        const int ix = m[i].x >> 5, iy = m[i].y >> 5, fx = m[i].x & 31, fy = m[i].y & 31;
+        unsigned g;
+        if ((unsigned)ix < (unsigned)(sw - 1) && (unsigned)iy < (unsigned)(sh - 1)) {
+            const uint8_t* r0 = s + ((unsigned)iy * spitch + (unsigned)ix);
+            const int p00 = r0[0], p01 = r0[1], p10 = r0[spitch], p11 = r0[spitch + 1];
+            const int top = p00 * (32 - fx) + p01 * fx, bot = p10 * (32 - fx) + p11 * fx;
+            g = (unsigned)((top * (32 - fy) + bot * fy + 512) >> 10);
+        } else {
+            const int cx = max(-32768, min(32767, ix)), cy = max(-32768, min(32767, iy));
+            const bool x0 = cx >= 0 && cx < sw, x1 = cx + 1 >= 0 && cx + 1 < sw, y0 = cy >= 0 && cy < sh, y1 = cy + 1 >= 0 && cy + 1 < sh;
+            const uint8_t* r0 = s + (long long)cy * spitch + cx;
+            const uint8_t* r1 = r0 + spitch;
+            const int p00 = (x0 && y0) ? r0[0] : 0, p01 = (x1 && y0) ? r0[1] : 0, p10 = (x0 && y1) ? r1[0] : 0, p11 = (x1 && y1) ? r1[1] : 0;
+            const int acc = ((32 - fx) * (32 - fy) * p00 + fx * (32 - fy) * p01 + (32 - fx) * fy * p10 + fx * fy * p11) * 32;
+            g = (unsigned)((acc + (1 << 14)) >> 15);
+        }
+        const unsigned y = __umulhi((unsigned)p, magic), x = (unsigned)p - y * (unsigned)dw;
+        d[y * dpitch + x] = (uint8_t)g;
+    }
+}
+
+static inline void launch_remap(const uint8_t* src, long long spitch, long long sfstride, int sw, int sh, const int2* map, int dw, int dh,
+                                uint8_t* dst, long long dpitch, long long dfstride, int nf, cudaStream_t st)
+{
+    const long long npix = (long long)dw * dh;
+    if ((npix + 1024) * dw < (1ll << 32) && (long long)sh * spitch < (1ll << 31) && (long long)dh * dpitch < (1ll << 31)) {
+        const unsigned magic = (unsigned)(((1ull << 32) + (unsigned)dw - 1) / (unsigned)dw);
+        remap_lanes_kernel<<<dim3((unsigned)((npix + 1023) / 1024), nf), 256, 0, st>>>(src, (unsigned)spitch, sfstride, sw, sh, map, dw, (int)npix, dst,
+                                                                                   (unsigned)dpitch, dfstride, magic);
+    } else if ((dw & 3) == 0 && ((long long)(dw >> 2) * dh + 256) * (dw >> 2) < (1ll << 32) && (long long)sh * spitch < (1ll << 31) &&
+               (long long)dh * dpitch < (1ll << 31)) {
+        const long long groups = (long long)(dw >> 2) * dh;
+        const unsigned magic = (unsigned)(((1ull << 32) + (unsigned)(dw >> 2) - 1) / (unsigned)(dw >> 2));
+        remap_kernel<true><<<dim3((unsigned)((groups + 255) / 256), nf), 256, 0, st>>>(src, spitch, sfstride, sw, sh, map, dw, dh, dst, dpitch, dfstride, magic);
+    } else
+        remap_kernel<false><<<dim3(ceil_div(dw, 4 * 128), dh, nf), 128, 0, st>>>(src, spitch, sfstride, sw, sh, map, dw, dh, dst, dpitch, dfstride, 0u);
 }
 
 // =====================================================================================================

@@ -1,14 +1,8 @@
 #!/bin/bash
-# One GPU call: parity tests, bench line, ncu launch list, ncu full capture of the level kernel (smallest workload).
+# round-end confirmation: full GPU suite, smoke, bench (both arms), secondary rows
 set -x
-mkdir -p gpurun_out
-nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
-timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
-tail -5 gpurun_out/pytest_gpu.log
-timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
-cat gpurun_out/bench.json
-timeout 300 python tools/prof_extract.py 3 --match > gpurun_out/plain.log 2>&1 &&
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python tools/prof_extract.py 3 --match > gpurun_out/ncu_launch.log 2>&1
-echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:level_kernel -s 8 -c 3 -o gpurun_out/prof_level python tools/prof_extract.py 2 > gpurun_out/ncu_full.log 2>&1
-echo "ncu full rc=$?"
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
+timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo bench rc=$?
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo ref rc=$?
+timeout 500 python tools/bench_rows.py > gpurun_out/rows.json 2> gpurun_out/rows.err; echo rows rc=$?
