@@ -470,7 +470,8 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         a.rec = d_rec + g.rec_off; a.rec_cap = g.rec_cap; a.rec_fstride = (long long)h->rec_total;
         a.rec_count = d_rec_count + l; a.rec_count_stride = nl;
         for (int i = 0; i < 7; i++) a.q[i] = h->q[i];
-        a.legacy = h->cfg.blur_legacy ? 1 : 0;
+        l3_blur_taps(a.q, a.kq);
+        const bool legacy = h->cfg.blur_legacy != 0;
         {   // quick-reject threshold t' = 2^k - 1 <= minTh (k >= 1); minTh == 0 disables the reject
             int k = 0;
             while ((2 << k) - 1 <= h->cfg.min_th_fast && k < 7) k++;
@@ -478,10 +479,12 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         }
         if (h->l3_warps == 8) {
             dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, 8 * L3_RG), nframes);
-            level3_kernel<8><<<grid, 256, 0, st>>>(a);
+            if (legacy) level3_kernel<8, true><<<grid, 256, 0, st>>>(a);
+            else level3_kernel<8, false><<<grid, 256, 0, st>>>(a);
         } else {
             dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, 4 * L3_RG), nframes);
-            level3_kernel<4><<<grid, 128, 0, st>>>(a);
+            if (legacy) level3_kernel<4, true><<<grid, 128, 0, st>>>(a);
+            else level3_kernel<4, false><<<grid, 128, 0, st>>>(a);
         }
         ORBB_LAUNCHED();
         if (has_next && !fused_resize) {

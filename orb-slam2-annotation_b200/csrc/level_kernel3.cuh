@@ -47,8 +47,17 @@ struct Level3Args {
     uint32_t* rec; int rec_cap; long long rec_fstride;      // raw FAST records  y<<20 | x<<8 | m
     int* rec_count; int rec_count_stride;
     int q[7];                                               // Q8 blur kernel
-    int legacy;                                             // 1: kernel sums to 257 -> the result needs a clamp
+    unsigned kq[8];                                         // horizontal-pass tap words KA..KH (l3_blur_taps), packed by the host
 };
+
+// Tap words of the horizontal blur pass: byte pairs multiply the (even | odd) u16 halves of the left / own / right word.
+inline void l3_blur_taps(const int* q, unsigned* k)
+{
+    auto pack = [](int b0, int b1, int b2, int b3) { return (unsigned)b0 | ((unsigned)b1 << 8) | ((unsigned)b2 << 16) | ((unsigned)b3 << 24); };
+    const int q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];
+    k[0] = pack(q0, q2, 0, q1); k[1] = pack(q3, q1, q2, q0); k[2] = pack(0, q0, 0, q1); k[3] = pack(q2, q2, q3, q1);
+    k[4] = pack(q0, 0, q1, 0);  k[5] = pack(q1, q3, q2, q2); k[6] = pack(q0, q2, q1, q3); k[7] = pack(q2, q0, q1, 0);
+}
 
 __device__ __forceinline__ int l3_reflect101(int p, int n)
 {
@@ -85,20 +94,17 @@ __device__ __forceinline__ int l3_arc_score(const uint8_t* c)
     return (int)max(best & 0xffffu, best >> 16) - 256;
 }
 
-__device__ __forceinline__ unsigned l3_pack4(int b0, int b1, int b2, int b3)
-{
-    return (unsigned)b0 | ((unsigned)b1 << 8) | ((unsigned)b2 << 16) | ((unsigned)b3 << 24);
-}
-
-template <int NW>
+// LEGACY: the Q8 kernel of OpenCV <= 3.3 sums to 257, so the rounded result needs a clamp (default kernel: it is byte 2 of the sum).
+template <int NW, bool LEGACY>
 __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const __grid_constant__ Level3Args a)
 {
     constexpr int TH = L3_RG * NW, SMH = TH + 8, SCH = TH + 2, NT = 32 * NW;
     constexpr int QCAP = SCH * 122;                      // every scored pixel a candidate (uniform-noise images)
     constexpr unsigned FULL = 0xffffffffu;
-    __shared__ __align__(128) uint32_t tws[SMH * L3_SP]; // tile + halo, 4 pixels per word (TMA destination)
+    __shared__ __align__(128) uint32_t tws[(SMH + NW - 2) * L3_SP];   // tile + halo, 4 pixels per word (TMA destination: SMH rows); the
+                                                                      // FAST row window of the last warp reads NW - 2 rows past it (masked)
     __shared__ __align__(8) unsigned long long mbar;      // completion barrier of the bulk tensor copy
-    __shared__ __align__(4) uint8_t sc[SCH * L3_SCP];    // arc scores (> minTh) of the tile's pixels + 1-px ring
+    __shared__ __align__(16) uint8_t sc[SCH * L3_SCP];   // arc scores (> minTh) of the tile's pixels + 1-px ring
     __shared__ uint16_t queue[QCAP];
     __shared__ int s_qn;
 
@@ -112,7 +118,9 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
     const uint8_t* tb = reinterpret_cast<const uint8_t*>(tw);
     if (tid == 0) s_qn = 0;
 
-    for (int i = tid; i < SCH * L3_SCP / 4; i += NT) reinterpret_cast<uint32_t*>(sc)[i] = 0;     // visible after the next barrier
+#pragma unroll
+    for (int i = 0; i < (SCH * L3_SCP / 16 + NT - 1) / NT; i++)                                  // visible after the next barrier
+        if (i * NT + tid < SCH * L3_SCP / 16) reinterpret_cast<uint4*>(sc)[i * NT + tid] = make_uint4(0u, 0u, 0u, 0u);
 
     // ---- 1. stage tile + halo (128 bytes x SMH rows, lane = word column).  Normal case: ONE bulk tensor copy (TMA) issued by
     //         thread 0 lands the box [(x0-4) & ~15, +144) x [y0-4, y0+TH+4) of frame f in shared memory (out-of-image bytes arrive as
@@ -198,9 +206,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
             O[i] = __byte_perm(w, 0u, 0x4341);
         }
         const unsigned q0 = a.q[0], q1 = a.q[1], q2 = a.q[2], q3 = a.q[3];      // symmetric kernel (checked by the host)
-        const unsigned KA = l3_pack4(q0, q2, 0, q1), KB = l3_pack4(q3, q1, q2, q0), KC = l3_pack4(0, q0, 0, q1);
-        const unsigned KD = l3_pack4(q2, q2, q3, q1), KE = l3_pack4(q0, 0, q1, 0), KF = l3_pack4(q1, q3, q2, q2);
-        const unsigned KG = l3_pack4(q0, q2, q1, q3), KH = l3_pack4(q2, q0, q1, 0);
+        const unsigned KA = a.kq[0], KB = a.kq[1], KC = a.kq[2], KD = a.kq[3], KE = a.kq[4], KF = a.kq[5], KG = a.kq[6], KH = a.kq[7];
         const int gx = x0 - 4 + 4 * lane;
         const bool store_lane = lane >= 1 && lane <= L3_OWNW && gx < a.w;
         uint8_t* __restrict__ bp = a.blur + (long long)f * a.blur_fstride + (long long)(y0 + ry0) * a.blur_pitch + gx;
@@ -219,7 +225,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
             r2 = __dp2a_lo(rO, KE, r2);
             unsigned r3 = __dp2a_lo(VE, KG, 32768u); r3 = __dp2a_hi(VO, KG, r3); r3 = __dp2a_lo(rE, KH, r3); r3 = __dp2a_hi(rO, KH, r3);
             unsigned o;
-            if (!a.legacy) {        // sums < 2^24: the rounded result is byte 2
+            if (!LEGACY) {          // sums < 2^24: the rounded result is byte 2
                 o = __byte_perm(__byte_perm(r0, r1, 0x0062), __byte_perm(r2, r3, 0x0062), 0x5410);
             } else {
                 o = min(r0 >> 16, 255u) | (min(r1 >> 16, 255u) << 8) | (min(r2 >> 16, 255u) << 16) | (min(r3 >> 16, 255u) << 24);
@@ -288,43 +294,65 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
             if (lo > 0) valid &= 0xffffffffu << (8 * lo);
             if (hi < 3) valid &= 0xffffffffu >> (8 * (3 - hi));
         }
+        // Each warp scans 9 CONSECUTIVE score-map rows s = 9 * warp - 1 + it (the last warp has fewer), so the staged rows slide
+        // through registers: a row is loaded once (own word + both neighbours) and its +-2-pixel and +-3-pixel shifted views are
+        // formed once, whichever of the five roles (centre, +-2, +-3) it plays for the rows around it.
+        constexpr int RPW9 = 9;
+        static_assert(RPW9 * NW >= TH + 2, "9 rows per warp cover the tile and its ring");
+        const int sb = RPW9 * warp - 1;                           // first score-map row of this warp (tile row index)
+        unsigned rowok = 0;                                       // bit it: row sb + it is a scored row of the image
+#pragma unroll
+        for (int it = 0; it < RPW9; it++) {
+            const int s = sb + it, gy = y0 + s;
+            if (s <= TH && gy >= 19 && gy <= a.h - 20) rowok |= 1u << it;
+        }
         unsigned m0 = 0, m1 = 0;                                  // private candidate flags: 4 bits per row, rows it = 0..7 | 8
-        constexpr int NIT = (TH + 2 + NW - 1) / NW;
-        static_assert(NIT <= 9, "candidate masks hold 9 rows per warp");
-#pragma unroll 9
-        for (int it = 0; it < NIT; it++) {                                           // (partly rolled: instruction-cache footprint)
-            const int s = warp - 1 + NW * it;
-            const int gy = y0 + s;
-            if (s > TH || gy < 19 || gy > a.h - 20) continue;                        // warp-uniform
-            const uint32_t* rowp = tw + (s + 4) * L3_SP + lane;
-            const unsigned V = rowp[0], Lw = rowp[-1], Rw = rowp[1];
-            const unsigned Vd = rowp[2 * L3_SP], Ld = rowp[2 * L3_SP - 1], Rd = rowp[2 * L3_SP + 1];
-            const unsigned Vu = rowp[-2 * L3_SP], Lu = rowp[-2 * L3_SP - 1], Ru = rowp[-2 * L3_SP + 1];
-            // any 9-arc contains two ADJACENT ones of the axis four  0 (0,+3), 4 (+3,0), 8 (0,-3), 12 (-3,0)
-            // and two adjacent ones of the diagonal four             2 (+2,+2), 6 (+2,-2), 10 (-2,-2), 14 (-2,+2)
-            const unsigned p08 = (__vabsdiffu4(V, rowp[3 * L3_SP]) | __vabsdiffu4(V, rowp[-3 * L3_SP])) & M;
-            const unsigned p4c = (__vabsdiffu4(V, __funnelshift_r(V, Rw, 24)) | __vabsdiffu4(V, __funnelshift_r(Lw, V, 8))) & M;
-            const unsigned p2a = (__vabsdiffu4(V, __funnelshift_r(Vd, Rd, 16)) | __vabsdiffu4(V, __funnelshift_r(Lu, Vu, 16))) & M;
-            const unsigned p6e = (__vabsdiffu4(V, __funnelshift_r(Vu, Ru, 16)) | __vabsdiffu4(V, __funnelshift_r(Ld, Vd, 16))) & M;
-            unsigned cand = ((p08 >> 1) + C) & ((p4c >> 1) + C) & ((p2a >> 1) + C) & ((p6e >> 1) + C) & valid;
-            if (a.qmask == 0) cand = valid;                                          // minTh == 0: no quick reject possible
-            const unsigned nib = (((cand >> 7) * 0x00204081u) >> 21) & 15u;
-            if (it < 8) m0 |= nib << (4 * (it & 7)); else m1 = nib;
+        if (rowok) {                                              // warp-uniform
+            const uint32_t* rp = tw + (sb + 1) * L3_SP + lane;   // staged row j of the window = tile row sb - 3 + j
+            unsigned Vw[7], Aw[7] = {}, Bw[7] = {};              // sliding window: own word, +2-pixel view, -2-pixel view
+#pragma unroll
+            for (int j = 0; j < 6; j++) {
+                const unsigned V = rp[j * L3_SP];
+                Vw[j] = V;
+                if (j >= 1) { Aw[j] = __funnelshift_r(V, rp[j * L3_SP + 1], 16); Bw[j] = __funnelshift_r(rp[j * L3_SP - 1], V, 16); }
+            }
+#pragma unroll
+            for (int it = 0; it < RPW9; it++) {
+                // window slots: 0 = row -3, 1 = row -2, 3 = centre, 5 = row +2, 6 = row +3 (entered now)
+                Vw[6] = rp[(it + 6) * L3_SP];
+                const unsigned V5 = Vw[5];
+                if (it > 0) { Aw[5] = __funnelshift_r(V5, rp[(it + 5) * L3_SP + 1], 16); Bw[5] = __funnelshift_r(rp[(it + 5) * L3_SP - 1], V5, 16); }
+                const unsigned V = Vw[3];
+                const unsigned Cw = __funnelshift_r(V, rp[(it + 3) * L3_SP + 1], 24), Dw = __funnelshift_r(rp[(it + 3) * L3_SP - 1], V, 8);
+                // any 9-arc contains two ADJACENT ones of the axis four  0 (0,+3), 4 (+3,0), 8 (0,-3), 12 (-3,0)
+                // and two adjacent ones of the diagonal four             2 (+2,+2), 6 (+2,-2), 10 (-2,-2), 14 (-2,+2)
+                const unsigned p08 = (__vabsdiffu4(V, Vw[6]) | __vabsdiffu4(V, Vw[0])) & M;
+                const unsigned p4c = (__vabsdiffu4(V, Cw) | __vabsdiffu4(V, Dw)) & M;
+                const unsigned p2a = (__vabsdiffu4(V, Aw[5]) | __vabsdiffu4(V, Bw[1])) & M;
+                const unsigned p6e = (__vabsdiffu4(V, Aw[1]) | __vabsdiffu4(V, Bw[5])) & M;
+                unsigned cand = ((p08 >> 1) + C) & ((p4c >> 1) + C) & ((p2a >> 1) + C) & ((p6e >> 1) + C) & valid;
+                if (a.qmask == 0) cand = valid;                                      // minTh == 0: no quick reject possible
+                if (!((rowok >> it) & 1u)) cand = 0;
+                const unsigned nib = (((cand >> 7) * 0x00204081u) >> 21) & 15u;
+                if (it < 8) m0 |= nib << (4 * (it & 7)); else m1 = nib;
+#pragma unroll
+                for (int j = 0; j < 6; j++) { Vw[j] = Vw[j + 1]; Aw[j] = Aw[j + 1]; Bw[j] = Bw[j + 1]; }
+            }
         }
         // each lane appends its own candidates: one shared atomic per lane, no warp scan (queue order is irrelevant)
         const int n = __popc(m0) + __popc(m1);
         if (n) {
             int slot = atomicAdd(&s_qn, n);
-            const int pbase = warp * L3_SCP + 4 * lane;          // position of (row s = warp - 1, byte 0): (s + 1) * SCP + 4 * lane
-            while (m0) {
+            const int pbase = (sb + 1) * L3_SCP + 4 * lane;      // position of (row sb, byte 0 of this lane's word)
+            while (m0) {                                          // bit t = 4 * it + byte  ->  pbase + it * L3_SCP + byte
                 const int t = __ffs((int)m0) - 1;
                 m0 &= m0 - 1;
-                queue[slot++] = (uint16_t)(pbase + (t >> 2) * (NW * L3_SCP) + (t & 3));
+                queue[slot++] = (uint16_t)(pbase + (((t << 5) | t) & 0x383));
             }
             while (m1) {
                 const int t = __ffs((int)m1) - 1;
                 m1 &= m1 - 1;
-                queue[slot++] = (uint16_t)(pbase + 8 * (NW * L3_SCP) + t);
+                queue[slot++] = (uint16_t)(pbase + 8 * L3_SCP + t);
             }
         }
     }
