@@ -443,6 +443,10 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
     oa.node_off = h->d_node_off; oa.cell_off = h->d_cell_off;
     oa.out = d_out; oa.out_fstride = (long long)h->out_total;
     oa.out_count = d_out_count; oa.status = d_status;
+    static const bool tl_on = getenv("ORBB_TIMELINE") != nullptr;     // debugging aid: device timeline of one call on stderr
+    static cudaEvent_t tl[2 + 2 * ORBB_MAX_LEVELS + 1];
+    if (tl_on && !tl[0]) for (auto& e : tl) ORBB_CUDA(cudaEventCreate(&e));
+    if (tl_on) ORBB_CUDA(cudaEventRecord(tl[0], st));
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[0], st));
     for (int l = 0; l < nl; l++) {
         const LevelGeom& g = h->geom[l];
@@ -500,7 +504,9 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             oa.level0 = l;
             octree_kernel<<<dim3(1, nframes), NTO, 0, side>>>(oa);
             ORBB_LAUNCHED();
+            if (tl_on) ORBB_CUDA(cudaEventRecord(tl[2 + ORBB_MAX_LEVELS + l], side));
         }
+        if (tl_on) ORBB_CUDA(cudaEventRecord(tl[2 + l], st));
     }
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[1], st));
     if (!overlap) {
@@ -524,6 +530,15 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         const int maxk = capacity < (int)h->out_total ? capacity : (int)h->out_total;
         orient_desc_kernel<<<dim3(ceil_div(maxk > 0 ? maxk : 1, 256), nframes), 256, 0, st>>>(a);
         ORBB_LAUNCHED();
+    }
+    if (tl_on) {
+        ORBB_CUDA(cudaEventRecord(tl[1], st));
+        ORBB_CUDA(cudaEventSynchronize(tl[1]));
+        float ms = 0;
+        fprintf(stderr, "[timeline] frames %d:", nframes);
+        for (int l = 0; l < nl; l++) { cudaEventElapsedTime(&ms, tl[0], tl[2 + l]); fprintf(stderr, " L%d %.3f", l, ms); }
+        if (overlap) for (int l = 0; l < nl; l++) { cudaEventElapsedTime(&ms, tl[0], tl[2 + ORBB_MAX_LEVELS + l]); fprintf(stderr, " O%d %.3f", l, ms); }
+        cudaEventElapsedTime(&ms, tl[0], tl[1]); fprintf(stderr, " end %.3f\n", ms);
     }
     if (h->profiling) {
         ORBB_CUDA(cudaEventRecord(h->ev[3], st));
