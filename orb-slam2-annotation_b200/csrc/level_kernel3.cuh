@@ -84,13 +84,18 @@ __device__ __forceinline__ int l3_arc_score(const uint8_t* c)
     unsigned a3[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) a3[k] = __vimin3_u16x2(X[k], X[(k + 1) & 15], X[(k + 2) & 15]);
-    unsigned best = 0;
+    // arcs k and k + 3 share a3[k+3], a3[k+6]:  max(a9[k], a9[k+3]) = min(a3[k+3], a3[k+6], max(a3[k], a3[k+9])); the eight pairs
+    // (k, k + 3), k = 0, 6, 12, 2, 8, 14, 4, 10 cover the sixteen arcs
+    unsigned pv[8];
 #pragma unroll
-    for (int k = 0; k < 16; k += 2) {
-        const unsigned a9 = __vimin3_u16x2(a3[k], a3[(k + 3) & 15], a3[(k + 6) & 15]);
-        const unsigned b9 = __vimin3_u16x2(a3[k + 1], a3[(k + 4) & 15], a3[(k + 7) & 15]);
-        best = __vimax3_u16x2(best, a9, b9);
+    for (int i = 0; i < 8; i++) {
+        const int k = (6 * i) & 15;
+        pv[i] = __vimin3_u16x2(a3[(k + 3) & 15], a3[(k + 6) & 15], __vmaxu2(a3[k], a3[(k + 9) & 15]));
     }
+    unsigned best = __vimax3_u16x2(pv[0], pv[1], pv[2]);
+    best = __vimax3_u16x2(best, pv[3], pv[4]);
+    best = __vimax3_u16x2(best, pv[5], pv[6]);
+    best = __vmaxu2(best, pv[7]);
     return (int)max(best & 0xffffu, best >> 16) - 256;
 }
 

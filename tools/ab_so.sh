@@ -1,13 +1,19 @@
 #!/bin/bash
-# A/B of alternative builds: ab_so.sh v2 v4 ...  (orb-slam2-annotation_b200/liborbb200_<v>.so), then the default build
+# A/B of alternative builds: ab_so.sh v2 v4 ...  (orb-slam2-annotation_b200/liborbb200_<v>.so), then the default build; a name of the
+# form ENV=val runs the default build with that environment variable
 cd orb-slam2-annotation_b200
 cp liborbb200.so /tmp/orig.so
 for v in "$@" orig; do
-  if [ $v = orig ]; then cp /tmp/orig.so liborbb200.so; else cp liborbb200_$v.so liborbb200.so; fi
+  E=""
+  case $v in
+    orig) cp /tmp/orig.so liborbb200.so;;
+    *=*) cp /tmp/orig.so liborbb200.so; E=$v;;
+    *) cp liborbb200_$v.so liborbb200.so;;
+  esac
   cd ..
-  python -m pytest tests/test_gpu_extract.py -m gpu -x -q 2>&1 | tail -1
-  python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_$v.json 2>gpurun_out/bench_$v.err
+  env $E python -m pytest tests/test_gpu_extract.py -m gpu -x -q 2>&1 | tail -1
+  env $E python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_ab.json 2>gpurun_out/bench_ab.err
   python -c "
-import json;d=json.load(open('gpurun_out/bench_$v.json'));print('$v value',round(d['value']),'e2e',round(d['e2e']['value']),'share',d['roofline']['step_share'])"
+import json;d=json.load(open('gpurun_out/bench_ab.json'));print('$v value',round(d['value']),'e2e',round(d['e2e']['value']),'share',{k:round(x,4) for k,x in d['roofline']['step_share'].items()})"
   cd orb-slam2-annotation_b200
 done

@@ -68,6 +68,44 @@ def tdev(a):
 st = torch.cuda.Stream()
 S = st.cuda_stream
 
+# ---- a1-a8 at the other config shapes (C2 KITTI, C3 EuRoC, C4 4K): device-resident batches, step shares by CUDA events ----------
+def level_pixels(w, h, nl=8, sf=1.2):
+    sc = np.float32(1.0); P = []
+    for l in range(nl):
+        inv = np.float32(1.0) / sc
+        P.append(int(np.rint(np.float32(w) * inv)) * int(np.rint(np.float32(h) * inv)))
+        sc = np.float32(np.float64(sc) * np.float64(np.float32(sf)))
+    return P
+
+
+for name, (w, h, nf, F, cap) in {"C2 KITTI 1241x376 / 2000 kp": (1241, 376, 2000, 256, 2560), "C3 EuRoC 752x480 / 1200 kp": (752, 480, 1200, 512, 1536),
+                                 "C4 4K 3840x2160 / 8000 kp": (3840, 2160, 8000, 16, 9216)}.items():
+    nd = 4 if w > 2000 else 16
+    distinct = np.stack([synth(w, h, 5000 + i) for i in range(nd)])
+    frames = torch.from_numpy(np.ascontiguousarray(np.tile(distinct, (F // nd, 1, 1)))).to(dev)
+    ex = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), max_batch=F)
+    est = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    kps = torch.zeros((F, cap, 7), dtype=torch.float32, device=dev); desc = torch.zeros((F, cap, 32), dtype=torch.uint8, device=dev)
+    cnt = torch.zeros(F, dtype=torch.int32, device=dev)
+    step = lambda: ex.extract_batch_device(frames.data_ptr(), F, w, h, w, w * h, kps.data_ptr(), desc.data_ptr(), cnt.data_ptr(), cap)
+    ms = gpu_ms(step, est, iters=10)
+    ex.sync()
+    nkp = float(cnt.float().mean().item())
+    ex.set_profiling(True)
+    for _ in range(3):
+        step()
+    prof = ex.get_profile(); ex.set_profiling(False)
+    P = level_pixels(w, h)
+    lvl_bytes = 3 * sum(P) - P[0] - P[-1]
+    lvl_ms = prof["level_ms"] / prof["calls"]
+    oe = pyoracle.RefExtractor(nf) if pyoracle.ref_lib() is not None else pyoracle.OracleExtractor(nf)
+    tc = cpu_s(lambda: oe.extract(distinct[0]), 1.0)
+    rows[f"extract {name} (a1-a8)"] = {"workload": f"{F} frames device-resident, {nd} distinct synthetic frames tiled", "gpu_ms": ms, "frames_per_s": F / ms * 1e3,
+                                      "keypoints_per_frame": nkp, "step_share_ms": {k: prof[k] / prof["calls"] for k in ("level_ms", "octree_ms", "desc_ms")},
+                                      "level_kernels_algorithmic_GBps": lvl_bytes * F / lvl_ms / 1e6, "level_kernels_hbm_frac": lvl_bytes * F / lvl_ms / 1e6 / HBM,
+                                      "cpu_reference_frames_per_s_1_thread": 1 / tc, "parity": "tests/test_gpu_extract.py (same shapes)"}
+    del frames, kps, desc, cnt, ex
+
 # ---- f4: cvtColor, 512 BGR VGA frames (bigger than L2) -----------------------------------------------------------------
 F, w, h = 512, 640, 480
 rng = np.random.default_rng(1)
