@@ -35,6 +35,8 @@ struct orbx_handle {
     int n_kstreams = 4;
     // per kernel stream: a side stream on which the octree of level L runs while the main stream works on levels L+1..
     cudaStream_t s_side[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t s_side2[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // odd levels' octrees
+    cudaEvent_t ev_side2[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_side[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> ev_lvl[8];
     bool oct_overlap = true;
@@ -334,6 +336,8 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
     for (int i = 0; i < 8; i++) {
         ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_side[i], cudaStreamNonBlocking));
         ORBB_CUDA(cudaEventCreateWithFlags(&h->ev_side[i], cudaEventDisableTiming));
+        ORBB_CUDA(cudaStreamCreateWithFlags(&h->s_side2[i], cudaStreamNonBlocking));
+        ORBB_CUDA(cudaEventCreateWithFlags(&h->ev_side2[i], cudaEventDisableTiming));
     }
     if (getenv("ORBB_NO_OCT_OVERLAP")) h->oct_overlap = false;
     if (const char* e = getenv("ORBB_KSTREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 8) h->n_kstreams = v; }
@@ -375,6 +379,8 @@ extern "C" int orbx_destroy(orbx_handle* h)
     for (int i = 0; i < 7; i++) if (h->s_k[i]) cudaStreamDestroy(h->s_k[i]);
     for (int i = 0; i < 8; i++) {
         if (h->s_side[i]) cudaStreamDestroy(h->s_side[i]);
+        if (h->s_side2[i]) cudaStreamDestroy(h->s_side2[i]);
+        if (h->ev_side2[i]) cudaEventDestroy(h->ev_side2[i]);
         if (h->ev_side[i]) cudaEventDestroy(h->ev_side[i]);
         for (cudaEvent_t e : h->ev_lvl[i]) cudaEventDestroy(e);
     }
@@ -413,9 +419,10 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
     }
     const int nl = h->nlevels;
     cudaStream_t st = slot ? h->s_k[slot - 1] : h->stream;
-    cudaStream_t side = h->s_side[slot];
+    cudaStream_t side = h->s_side[slot], side2 = h->s_side2[slot];
     // the octree of a level only needs that level's FAST records: it runs beside the next levels' kernels (not while profiling:
-    // the per-kernel-class event times are taken with the classes back to back)
+    // the per-kernel-class event times are taken with the classes back to back).  Even and odd levels use two side streams, so
+    // a long octree (level 0 of a large frame, few frames per launch) does not hold up the octrees of the levels after it.
     const bool overlap = h->oct_overlap && side_octree && !h->profiling;
     while ((int)h->ev_lvl[slot].size() < nl) {
         cudaEvent_t e;
@@ -499,12 +506,13 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             ORBB_LAUNCHED();
         }
         if (overlap) {
+            cudaStream_t sl = (l & 1) ? side2 : side;
             ORBB_CUDA(cudaEventRecord(h->ev_lvl[slot][l], st));
-            ORBB_CUDA(cudaStreamWaitEvent(side, h->ev_lvl[slot][l], 0));
+            ORBB_CUDA(cudaStreamWaitEvent(sl, h->ev_lvl[slot][l], 0));
             oa.level0 = l;
-            octree_kernel<<<dim3(1, nframes), NTO, 0, side>>>(oa);
+            octree_kernel<<<dim3(1, nframes), NTO, 0, sl>>>(oa);
             ORBB_LAUNCHED();
-            if (tl_on) ORBB_CUDA(cudaEventRecord(tl[2 + ORBB_MAX_LEVELS + l], side));
+            if (tl_on) ORBB_CUDA(cudaEventRecord(tl[2 + ORBB_MAX_LEVELS + l], sl));
         }
         if (tl_on) ORBB_CUDA(cudaEventRecord(tl[2 + l], st));
     }
@@ -515,6 +523,10 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
     } else {
         ORBB_CUDA(cudaEventRecord(h->ev_side[slot], side));
         ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_side[slot], 0));
+        if (nl > 1) {
+            ORBB_CUDA(cudaEventRecord(h->ev_side2[slot], side2));
+            ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_side2[slot], 0));
+        }
     }
     if (h->profiling) ORBB_CUDA(cudaEventRecord(h->ev[2], st));
     {

@@ -79,7 +79,7 @@ def level_pixels(w, h, nl=8, sf=1.2):
 
 
 for name, (w, h, nf, F, cap) in {"C2 KITTI 1241x376 / 2000 kp": (1241, 376, 2000, 256, 2560), "C3 EuRoC 752x480 / 1200 kp": (752, 480, 1200, 512, 1536),
-                                 "C4 4K 3840x2160 / 8000 kp": (3840, 2160, 8000, 16, 9216)}.items():
+                                 "C4 4K 3840x2160 / 8000 kp": (3840, 2160, 8000, 64, 9216)}.items():
     nd = 4 if w > 2000 else 16
     distinct = np.stack([synth(w, h, 5000 + i) for i in range(nd)])
     frames = torch.from_numpy(np.ascontiguousarray(np.tile(distinct, (F // nd, 1, 1)))).to(dev)
