@@ -362,6 +362,9 @@ int orbb200_device_count(void);
 /* Measured throughput (1e9 POPC.32 per second) of a register-only __popc loop on `device`: the roofline
  * denominator for the matching kernels. */
 int orbb200_measure_popc_peak(int device, double* gpopc_per_s);
+/* Measured throughput (int8 TOPS, 2 x multiply-adds) of a register-only mma.sync.m16n8k32 (IMMA) loop on `device`: the
+ * tensor-pipe denominator of the brute-force top-2 kernel, where one 256-bit comparison is 512 int8 operations. */
+int orbb200_measure_imma_peak(int device, double* int8_tops);
 /* Number of kernel launches issued by this library since load (bench.py's gpu_launches claim). */
 uint64_t orbb200_launch_count(void);
 

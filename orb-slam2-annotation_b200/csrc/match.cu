@@ -882,7 +882,7 @@ extern "C" int orbm_db_create(orbm_db** out, int64_t capacity_rows, int64_t row_
     if (!db) return ORBB_E_NOMEM;
     db->device = device; db->capacity = capacity_rows; db->row_offset = row_offset;
     const char* v = getenv("ORBB_BF_VARIANT");
-    db->variant = v ? atoi(v) : 1;
+    db->variant = v ? atoi(v) : 2;            // 2: tensor cores (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
     if (cudaMalloc((void**)&db->d_rows, (size_t)(capacity_rows > 0 ? capacity_rows : 1) * 32) != cudaSuccess) {
         set_cuda_error(cudaGetLastError(), "orbm_db_create: cudaMalloc");
         delete db;
@@ -919,8 +919,8 @@ static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nc
 {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, db->device);
-    const int qtiles = ceil_div(nq, BF_QTILE);
-    int target = ceil_div(sms * 4, qtiles);                         // ~4 CTAs per SM in flight
+    const int qtiles = ceil_div(nq, db->variant == 2 ? BM_QTILE : BF_QTILE);
+    int target = ceil_div(sms * 4, qtiles);                         // ~4 CTAs per SM in flight (variant 2: two waves of two)
     long long rpc = (db->rows + target - 1) / target;
     rpc = (rpc + BF_ROWS - 1) / BF_ROWS * BF_ROWS;
     if (rpc < BF_ROWS) rpc = BF_ROWS;
@@ -966,8 +966,9 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
     BfArgs a;
     a.db = db->d_rows; a.nrows = db->rows; a.q = (const uint4*)q_dev; a.nq = nq;
     a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = db->d_k1; a.part_k2 = db->d_k2;
-    dim3 grid(ceil_div(nq, BF_QTILE), nchunks);
+    dim3 grid(ceil_div(nq, db->variant == 2 ? BM_QTILE : BF_QTILE), nchunks);
     if (db->variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
+    else if (db->variant == 2) bf_top2_mma_kernel<<<grid, BM_THREADS, 0, st>>>(a);
     else bf_top2_kernel<1><<<grid, BF_THREADS, 0, st>>>(a);
     ORBB_LAUNCHED();
     bf_merge_chunks_kernel<<<ceil_div(nq, 256), 256, 0, st>>>(db->d_k1, db->d_k2, nchunks, nq, rpc, db->row_offset, d1, (long long*)i1, d2);
@@ -1041,5 +1042,36 @@ extern "C" int orbb200_measure_popc_peak(int device, double* gpopc_per_s)
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     *gpopc_per_s = best;
+    return ORBB_OK;
+}
+
+// Measured throughput (1e12 int8 multiply-adds x 2 per second) of a register-only mma.sync.m16n8k32 loop: the tensor-pipe
+// denominator of the brute-force top-2 kernel (one 256-bit comparison = 512 int8 operations).
+extern "C" int orbb200_measure_imma_peak(int device, double* int8_tops)
+{
+    if (!int8_tops) return ORBB_E_INVALID;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    DevBuf o;
+    const int blocks = sms * 4, threads = 256, iters = 4096;
+    if ((rc = o.alloc((size_t)blocks * threads * 4))) return rc;
+    cudaEvent_t e0, e1;
+    ORBB_CUDA(cudaEventCreate(&e0)); ORBB_CUDA(cudaEventCreate(&e1));
+    double best = 0;
+    for (int rep = 0; rep < 5; rep++) {
+        ORBB_CUDA(cudaEventRecord(e0));
+        imma_peak_kernel<<<blocks, threads>>>(o.as<int>(), iters, 12345u + rep);
+        ORBB_LAUNCHED();
+        ORBB_CUDA(cudaEventRecord(e1));
+        ORBB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ORBB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double tops = (double)blocks * (threads / 32) * iters * 8 * (2.0 * 16 * 8 * 32) / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tops > best) best = tops;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *int8_tops = best;
     return ORBB_OK;
 }

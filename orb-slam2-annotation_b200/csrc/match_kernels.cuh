@@ -691,6 +691,160 @@ __global__ void __launch_bounds__(BF_THREADS) bf_top2_kernel(const __grid_consta
     }
 }
 
+// ------------------------------------------------------------------------------------------------------
+// Brute-force top-2 on the tensor cores (variant 2).  For descriptors q, d of 256 bits:
+//     hamming(q, d) = |q| - sum_k a_k * b_k      with a_k = +1 / -1 for query bit 1 / 0 and b_k = database bit (0 / 1),
+// so a 16 x 8 block of distances is eight mma.sync.m16n8k32.s8.u8 (IMMA) instructions.  The b1 XOR-POPC mma the reference
+// algorithm suggests does not exist on sm_100a (ptxas emulates it with ~170 instructions around IMMA), the integer pipe tops
+// out at ~0.65 T comparisons/s (ham_csa above), and the legacy IMMA path measures 1144 int8 TOPS on B200 = 2.2 T comparisons/s
+// (tools/micro/imma_rate.cu).
+//   * a CTA owns 256 queries: each warp keeps its 32 queries as A fragments in registers (+1 / -1 bytes, all eight k-steps);
+//   * database rows arrive 128 at a time (cp.async, double buffered), are expanded bit -> byte in shared memory (bit p of a
+//     row = byte p: the k order of the instruction is irrelevant as long as A and B agree) and read as 8-byte B fragments;
+//   * the accumulators are filtered against the per-row threshold (max of the lane's two columns >= |q| - current second
+//     distance); only the rare pair that can enter the top-2 builds its key (dist << 23 | row) and updates (k1, k2);
+//   * the four lanes that share a query row merge their partial top-2 with shuffles at the end.
+// Output: the same per-(chunk, query) packed keys as bf_top2_kernel, merged by bf_merge_chunks_kernel.
+// ------------------------------------------------------------------------------------------------------
+constexpr int BM_THREADS = 256;
+constexpr int BM_QTILE = 256;                  // queries per CTA: 8 warps x 2 m-tiles x 16 rows
+constexpr int BM_ROWS = 128;                   // database rows per stage
+constexpr int BM_PITCH = 288;                  // bytes per expanded row in shared memory (256 + 32: conflict-free 8-byte fragment loads)
+
+__device__ __forceinline__ unsigned bm_spread01(unsigned nib)       // 4 bits -> 4 bytes of 0 / 1
+{
+    return (nib * 0x00204081u) & 0x01010101u;
+}
+__device__ __forceinline__ unsigned bm_spread_pm1(unsigned nib)     // 4 bits -> 4 bytes of +1 (0x01) / -1 (0xff)
+{
+    return ~(bm_spread01(nib) * 0xfeu);
+}
+__device__ __forceinline__ void bm_mma(int (&c)[4], const unsigned (&a)[4], const uint2& b)
+{
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
+}
+
+__global__ void __launch_bounds__(BM_THREADS, 2) bf_top2_mma_kernel(const __grid_constant__ BfArgs a)
+{
+    __shared__ __align__(16) uint8_t Bs[BM_ROWS * BM_PITCH];      // expanded stage
+    __shared__ uint4 raw[2][BM_ROWS * 2];                         // packed rows in flight
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int chunk = blockIdx.y;
+    const long long r_begin = (long long)chunk * a.rows_per_chunk;
+    const long long r_end = min(a.nrows, r_begin + a.rows_per_chunk);
+    const int nrows = (int)(r_end - r_begin);
+
+    // ---- queries -> A fragments: row (i, h) = blockIdx.x * 256 + warp * 32 + 16 i + g + 8 h ----
+    unsigned A[2][8][4];
+    int pq[2][2], thr[2][2];
+    unsigned k1[2][2], k2[2][2];
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int qi = blockIdx.x * BM_QTILE + warp * 32 + 16 * i + g + 8 * h;
+            uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0;
+            if (qi < a.nq) { v0 = a.q[2 * qi]; v1 = a.q[2 * qi + 1]; }
+            const unsigned w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            int pc = 0;
+#pragma unroll
+            for (int s = 0; s < 8; s++) {
+                pc += __popc(w[s]);
+                const unsigned byte = (w[s] >> (8 * t)) & 0xffu;            // bits s*32 + 8 t .. + 7
+                A[i][s][h] = qi < a.nq ? bm_spread_pm1(byte & 15u) : 0u;        // k = 4 t + 0..3 of the k-step
+                A[i][s][2 + h] = qi < a.nq ? bm_spread_pm1(byte >> 4) : 0u;     // k = 16 + 4 t + 0..3
+            }
+            pq[i][h] = pc;
+            k1[i][h] = 0xffffffffu; k2[i][h] = 0xffffffffu;
+            thr[i][h] = qi < a.nq ? pc - 511 : 0x7fffffff;                  // nothing yet: every row passes / padding rows: none
+        }
+    }
+
+    const int nstages = (nrows + BM_ROWS - 1) / BM_ROWS;
+    auto load_stage = [&](int s, int buf) {                       // 128 rows x 32 B = 256 uint4: one 16-byte cp.async per thread
+        const long long row = r_begin + (long long)s * BM_ROWS + (tid >> 1);
+        const uint4* src = a.db + (row < r_end ? row * 2 + (tid & 1) : 0);
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(&raw[buf][tid]);
+        const int bytes = row < r_end ? 16 : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+        asm volatile("cp.async.commit_group;");
+    };
+    if (nstages > 0) load_stage(0, 0);
+    for (int s = 0; s < nstages; s++) {
+        const int buf = s & 1;
+        if (s + 1 < nstages) { load_stage(s + 1, buf ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();                                          // stage s has landed; the previous stage's fragments are consumed
+        // ---- expand: packed word (row, wd) -> 32 bytes at row * PITCH + 32 wd ----
+        {
+            const unsigned* rw = reinterpret_cast<const unsigned*>(raw[buf]);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int e = tid + BM_THREADS * j;
+                const unsigned wv = rw[e];
+                uint4* dst = reinterpret_cast<uint4*>(Bs + (e >> 3) * BM_PITCH + (e & 7) * 32);
+                dst[0] = make_uint4(bm_spread01(wv & 15u), bm_spread01((wv >> 4) & 15u), bm_spread01((wv >> 8) & 15u), bm_spread01((wv >> 12) & 15u));
+                dst[1] = make_uint4(bm_spread01((wv >> 16) & 15u), bm_spread01((wv >> 20) & 15u), bm_spread01((wv >> 24) & 15u), bm_spread01(wv >> 28));
+            }
+        }
+        __syncthreads();
+        // ---- 16 n-tiles of 8 rows: 2 x 8 IMMA each, threshold filter, rare exact update ----
+        const int sbase = s * BM_ROWS + 2 * t;                    // chunk row of this lane's first column in n-tile 0
+#pragma unroll 2
+        for (int j = 0; j < BM_ROWS / 8; j++) {
+            const uint8_t* bp = Bs + (8 * j + g) * BM_PITCH + 8 * t;
+            uint2 b[8];
+#pragma unroll
+            for (int ks = 0; ks < 8; ks++) b[ks] = *reinterpret_cast<const uint2*>(bp + 32 * ks);
+            int c[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+#pragma unroll
+            for (int ks = 0; ks < 8; ks++) {
+                bm_mma(c[0], A[0][ks], b[ks]);
+                bm_mma(c[1], A[1][ks], b[ks]);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                if (max(c[i][0], c[i][1]) >= thr[i][0] || max(c[i][2], c[i][3]) >= thr[i][1]) {
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        if (thr[i][h] == 0x7fffffff) continue;                     // padding query row
+#pragma unroll
+                        for (int jj = 0; jj < 2; jj++) {
+                            const int idx = sbase + 8 * j + jj;
+                            if (idx < nrows) {
+                                const unsigned key = ((unsigned)(pq[i][h] - c[i][2 * h + jj]) << BF_IDX_BITS) | (unsigned)idx;
+                                k2[i][h] = min(k2[i][h], max(k1[i][h], key));
+                                k1[i][h] = min(k1[i][h], key);
+                            }
+                        }
+                        thr[i][h] = pq[i][h] - (int)(k2[i][h] >> BF_IDX_BITS);
+                    }
+                }
+            }
+        }
+    }
+    // ---- the four lanes of a query row merge their partial top-2 ----
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            unsigned x1 = k1[i][h], x2 = k2[i][h];
+#pragma unroll
+            for (int o = 1; o <= 2; o <<= 1) {
+                const unsigned y1 = __shfl_xor_sync(0xffffffffu, x1, o), y2 = __shfl_xor_sync(0xffffffffu, x2, o);
+                x2 = min(max(x1, y1), min(x2, y2));
+                x1 = min(x1, y1);
+            }
+            const int qi = blockIdx.x * BM_QTILE + warp * 32 + 16 * i + g + 8 * h;
+            if (t == 0 && qi < a.nq) {
+                a.part_k1[(long long)chunk * a.nq + qi] = x1;
+                a.part_k2[(long long)chunk * a.nq + qi] = x2;
+            }
+        }
+    }
+}
+
 // Merge the per-chunk keys in ascending chunk (= ascending row) order: sequential-scan semantics.
 __global__ void bf_merge_chunks_kernel(const unsigned* __restrict__ k1, const unsigned* __restrict__ k2, int nchunks, int nq,
                                        long long rows_per_chunk, long long row_offset,
@@ -741,6 +895,23 @@ __global__ void popc_peak_kernel(unsigned* out, int iters, unsigned seed)
 #pragma unroll
     for (int j = 0; j < 8; j++) s += acc[j];
     if (s == 0x12345678u) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+
+// register-only IMMA (mma.sync.m16n8k32 int8) throughput probe: the tensor-pipe denominator of bf_top2_mma_kernel
+__global__ void __launch_bounds__(256) imma_peak_kernel(int* out, int iters, unsigned seed)
+{
+    unsigned fa[4] = {seed * (threadIdx.x + 1), seed * 3u + threadIdx.x, seed * 5u ^ threadIdx.x, seed * 7u + 2u * threadIdx.x};
+    const uint2 fb = make_uint2(seed * 11u + threadIdx.x, seed * 13u ^ threadIdx.x);
+    int c[8][4] = {};
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) bm_mma(c[j], fa, fb);
+    }
+    int s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) s += c[j][0] + c[j][1] + c[j][2] + c[j][3];
+    if (s == 0x12345678) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
 }  // namespace orbb

@@ -31,7 +31,7 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "or
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
-           "orbv_compute_bow", "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak",
+           "orbv_compute_bow", "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak", "orbb200_measure_imma_peak",
            "orbb200_launch_count"]
 
 
@@ -121,6 +121,7 @@ def lib():
         L.orbb200_strerror.restype = C.c_char_p
         L.orbb200_last_cuda_error.restype = C.c_char_p
         L.orbb200_measure_popc_peak.argtypes = [i32, C.POINTER(C.c_double)]
+        L.orbb200_measure_imma_peak.argtypes = [i32, C.POINTER(C.c_double)]
         L.orbb200_launch_count.restype = C.c_uint64
         _lib = L
     return _lib
@@ -146,6 +147,12 @@ def launch_count():
 def popc_peak(device=0):
     v = C.c_double()
     _check(lib().orbb200_measure_popc_peak(device, C.byref(v)), "orbb200_measure_popc_peak")
+    return v.value
+
+
+def imma_peak(device=0):
+    v = C.c_double()
+    _check(lib().orbb200_measure_imma_peak(device, C.byref(v)), "orbb200_measure_imma_peak")
     return v.value
 
 
