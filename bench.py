@@ -331,10 +331,12 @@ def run_ours(args, rank, world, local_rank):
     hamming = {"metric": "bf_top2_gcmp_per_s", "value": gcmp, "unit": "Gcmp/s", "ms_per_step": ms_match / Km, "steps": Km,
                "workload": f"{NQ} queries x {DB_ROWS} rows per GPU, top-2 + merge" + (" + NCCL all-gather" if world > 1 else ""),
                "gpu_launches": int(match_launches),
-               "kernel": "bf_top2_mma_kernel: hamming = |q| - sum(+-1 query bits x 0/1 database bits), mma.sync.m16n8k32.s8.u8 (IMMA), "
-                         "threshold-filtered top-2 update",
-               "roofline": {"bound": "tensor", "achieved": tops, "peak": imma_peak, "unit": "int8 TOP/s", "frac": tops / imma_peak,
-                            "peak_source": "measured register-only mma.sync.m16n8k32 loop on this GPU (orbb200_measure_imma_peak)",
+               "kernel": "bf_top2_tc_kernel: hamming = |q| - sum(+-1 query bits x 0/1 database bits), tcgen05.mma kind::i8 128x128x32, "
+                         "accumulators in TMEM, threshold-filtered top-2 update",
+               "roofline": {"bound": "tensor", "achieved": tops, "peak": 4 * imma_peak, "unit": "int8 TOP/s", "frac": tops / (4 * imma_peak),
+                            "peak_source": "4 x the measured register-only mma.sync.m16n8k32 rate on this GPU (orbb200_measure_imma_peak: the legacy "
+                                           "path runs at a quarter of the tcgen05 int8 rate; nominal dense int8 4500 TOP/s)",
+                            "legacy_imma_peak": imma_peak,
                             "popc_equivalent": {"achieved": 8 * gcmp / world, "peak": popc_peak, "unit": "Gpopc/s", "frac": 8 * gcmp / world / popc_peak,
                                                 "note": "what the integer-pipe formulation (8 POPC.32 per comparison) would need: the measured "
                                                         "register-only __popc rate caps that design at frac <= 1.6 (carry-save adders, 5 POPC)"}}}

@@ -882,7 +882,8 @@ extern "C" int orbm_db_create(orbm_db** out, int64_t capacity_rows, int64_t row_
     if (!db) return ORBB_E_NOMEM;
     db->device = device; db->capacity = capacity_rows; db->row_offset = row_offset;
     const char* v = getenv("ORBB_BF_VARIANT");
-    db->variant = v ? atoi(v) : 2;            // 2: tensor cores (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
+    db->variant = v ? atoi(v) : 3;            // 3: tcgen05 / TMEM, 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
+    if (db->variant < 0 || db->variant > 3) db->variant = 3;
     if (cudaMalloc((void**)&db->d_rows, (size_t)(capacity_rows > 0 ? capacity_rows : 1) * 32) != cudaSuccess) {
         set_cuda_error(cudaGetLastError(), "orbm_db_create: cudaMalloc");
         delete db;
@@ -919,8 +920,8 @@ static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nc
 {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, db->device);
-    const int qtiles = ceil_div(nq, db->variant == 2 ? BM_QTILE : BF_QTILE);
-    int target = ceil_div(sms * 4, qtiles);                         // ~4 CTAs per SM in flight (variant 2: two waves of two)
+    const int qtiles = ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE);
+    int target = ceil_div(sms * (db->variant == 3 ? 2 : 4), qtiles);                         // ~4 CTAs per SM in flight (variant 2: two waves of two)
     long long rpc = (db->rows + target - 1) / target;
     rpc = (rpc + BF_ROWS - 1) / BF_ROWS * BF_ROWS;
     if (rpc < BF_ROWS) rpc = BF_ROWS;
@@ -966,8 +967,13 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
     BfArgs a;
     a.db = db->d_rows; a.nrows = db->rows; a.q = (const uint4*)q_dev; a.nq = nq;
     a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = db->d_k1; a.part_k2 = db->d_k2;
-    dim3 grid(ceil_div(nq, db->variant == 2 ? BM_QTILE : BF_QTILE), nchunks);
-    if (db->variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
+    dim3 grid(ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE), nchunks);
+    if (db->variant == 3) {
+        static bool attr_set = false;
+        if (!attr_set) { ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM)); attr_set = true; }
+        bf_top2_tc_kernel<<<grid, BT_THREADS, BT_SMEM, st>>>(a);
+    }
+    else if (db->variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
     else if (db->variant == 2) bf_top2_mma_kernel<<<grid, BM_THREADS, 0, st>>>(a);
     else bf_top2_kernel<1><<<grid, BF_THREADS, 0, st>>>(a);
     ORBB_LAUNCHED();

@@ -845,6 +845,213 @@ __global__ void __launch_bounds__(BM_THREADS, 2) bf_top2_mma_kernel(const __grid
     }
 }
 
+// ------------------------------------------------------------------------------------------------------
+// Brute-force top-2 with tcgen05 (variant 3): the same restatement as bf_top2_mma_kernel (hamming = |q| - sum a.b, a = +-1, b = 0/1)
+// on the 5th-generation tensor cores.  tcgen05.mma.kind::i8, M = 128 queries x N = 128 rows x K = 32 bits per instruction, both
+// operands in shared memory (K-major, no swizzle: 8-row x 16-byte core matrices, LBO = 128 B between the two K chunks of an
+// instruction, SBO = 2048 B between 8-row groups), int32 accumulators in TMEM.
+//   * a CTA owns 256 queries = two A tiles of 32 KB, expanded once; one CTA per SM (all 512 TMEM columns: 2 stages x 2 tiles x 128);
+//   * per stage of 128 rows: all warps expand the packed rows into the B tile of that stage, one thread issues the 16 MMAs of the
+//     stage and commits them to an mbarrier; meanwhile all warps read the PREVIOUS stage's accumulators (tcgen05.ld 32x32b.x32:
+//     a thread owns one query row and 64 of the 128 columns), filter them against the row threshold and update (k1, k2);
+//   * one __syncthreads per stage; MMA of stage s overlaps the epilogue of stage s-1 and the expansion of stage s+1.
+// ------------------------------------------------------------------------------------------------------
+constexpr int BT_THREADS = 256;
+constexpr int BT_QTILE = 256;
+constexpr int BT_ROWS = 128;
+constexpr int BT_TILE_BYTES = 128 * 256;                 // one 128 x 256-byte operand tile
+constexpr int BT_SMEM = 4 * BT_TILE_BYTES + 2 * BT_ROWS * 32 + 2048;     // A0 A1 B0 B1 | raw x 2 | merge scratch: 141312 B
+
+__device__ __forceinline__ unsigned long long bt_desc(unsigned smem_addr)
+{
+    // start address >> 4 | LBO (128 B) >> 4 at bit 16 | SBO (2048 B) >> 4 at bit 32 | descriptor version 1 at bit 46 | no swizzle
+    return (unsigned long long)((smem_addr & 0x3ffffu) >> 4) | (8ull << 16) | (128ull << 32) | (1ull << 46);
+}
+// canonical K-major byte offset of (row r, byte p) inside a 128-row x 256-byte tile
+__device__ __forceinline__ unsigned bt_off(unsigned r, unsigned p)
+{
+    return (r >> 3) * 2048u + (p >> 4) * 128u + (r & 7u) * 16u + (p & 15u);
+}
+__device__ __forceinline__ void bt_wait(unsigned mbar, unsigned parity)
+{
+    unsigned done = 0;
+    while (!done)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
+}
+#define BT_LD32(r, taddr)                                                                                                                  \
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23," \
+                 "%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"                                                                                \
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),  \
+                   "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),    \
+                   "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),    \
+                   "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                                                                      \
+                 : "r"(taddr))
+
+__global__ void __launch_bounds__(BT_THREADS, 1) bf_top2_tc_kernel(const __grid_constant__ BfArgs a)
+{
+    extern __shared__ __align__(128) uint8_t bt_smem[];
+    __shared__ __align__(8) unsigned long long mbar[2];
+    __shared__ unsigned tmem_base_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, quarter = warp & 3, half = warp >> 2;
+    const int chunk = blockIdx.y;
+    const long long r_begin = (long long)chunk * a.rows_per_chunk;
+    const long long r_end = min(a.nrows, r_begin + a.rows_per_chunk);
+    const int nrows = (int)(r_end - r_begin);
+    uint8_t* const As = bt_smem;
+    uint8_t* const Bs = bt_smem + 2 * BT_TILE_BYTES;
+    uint4* const raw = reinterpret_cast<uint4*>(bt_smem + 4 * BT_TILE_BYTES);            // [2][256]
+    unsigned* const scratch = reinterpret_cast<unsigned*>(bt_smem + 4 * BT_TILE_BYTES + 2 * BT_ROWS * 32);
+    const unsigned As_addr = (unsigned)__cvta_generic_to_shared(As), Bs_addr = (unsigned)__cvta_generic_to_shared(Bs);
+    const unsigned mbar_addr = (unsigned)__cvta_generic_to_shared(&mbar[0]);
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((unsigned)__cvta_generic_to_shared(&tmem_base_s)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_addr));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_addr + 8));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // ---- A tiles: 256 queries x 256 bytes of +1 / -1, canonical K-major layout; consecutive lanes write consecutive rows ----
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int i = tid + BT_THREADS * j;
+        const int r8 = i & 7, wd = (i >> 3) & 7, row256 = (i >> 6) * 8 + r8;
+        const int qi = blockIdx.x * BT_QTILE + row256;
+        const bool ok = qi < a.nq;
+        const unsigned w = ok ? reinterpret_cast<const unsigned*>(a.q)[(long long)qi * 8 + wd] : 0u;
+        uint4 lo, hi;
+        lo.x = bm_spread_pm1(w & 15u); lo.y = bm_spread_pm1((w >> 4) & 15u); lo.z = bm_spread_pm1((w >> 8) & 15u); lo.w = bm_spread_pm1((w >> 12) & 15u);
+        hi.x = bm_spread_pm1((w >> 16) & 15u); hi.y = bm_spread_pm1((w >> 20) & 15u); hi.z = bm_spread_pm1((w >> 24) & 15u); hi.w = bm_spread_pm1(w >> 28);
+        if (!ok) { lo = make_uint4(0, 0, 0, 0); hi = lo; }
+        uint8_t* dst = As + (row256 >> 7) * BT_TILE_BYTES + bt_off(row256 & 127, wd * 32);
+        *reinterpret_cast<uint4*>(dst) = lo;
+        *reinterpret_cast<uint4*>(dst + 128) = hi;
+    }
+    // ---- this thread's query rows: row = 32 quarter + lane of both tiles; it sees columns [64 half, 64 half + 64) of every stage ----
+    const int row = 32 * quarter + lane;
+    int pq[2], thr[2];
+    unsigned k1[2], k2[2];
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++) {
+        const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
+        int pc = 0;
+        if (qi < a.nq) {
+            const uint4 v0 = a.q[2 * qi], v1 = a.q[2 * qi + 1];
+            pc = __popc(v0.x) + __popc(v0.y) + __popc(v0.z) + __popc(v0.w) + __popc(v1.x) + __popc(v1.y) + __popc(v1.z) + __popc(v1.w);
+        }
+        pq[mt] = pc; k1[mt] = 0xffffffffu; k2[mt] = 0xffffffffu;
+        thr[mt] = qi < a.nq ? pc - 511 : 0x7fffffff;
+    }
+    // ---- packed rows: every thread copies and later expands its own 16 bytes (half a row); lanes 0-7 take 8 consecutive rows ----
+    const int my_row = (tid & ~15) / 2 + (tid & 7), my_half = (tid >> 3) & 1;
+    const int nstages = (nrows + BT_ROWS - 1) / BT_ROWS;
+    auto load_stage = [&](int s, int buf) {
+        const long long grow = r_begin + (long long)s * BT_ROWS + my_row;
+        const uint4* src = a.db + (grow < r_end ? grow * 2 + my_half : 0);
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(&raw[buf * BT_THREADS + tid]);
+        const int bytes = grow < r_end ? 16 : 0;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+        asm volatile("cp.async.commit_group;");
+    };
+    if (nstages > 0) load_stage(0, 0);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                          // the A tiles are read by the tensor core
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = tmem_base_s;
+    // instruction descriptor: D = s32 (2 << 4), A = s8 (1 << 7), B = u8 (0 << 10), both K-major, N = 128 (16 << 17), M = 128 (8 << 24)
+    constexpr unsigned IDESC = (2u << 4) | (1u << 7) | (16u << 17) | (8u << 24);
+
+    for (int it = 0; it <= nstages; it++) {
+        const int buf = it & 1;
+        if (it < nstages) {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            const uint4 rv = raw[buf * BT_THREADS + tid];
+            if (it + 1 < nstages) load_stage(it + 1, buf ^ 1);
+            const unsigned wv[4] = {rv.x, rv.y, rv.z, rv.w};
+            uint8_t* dst = Bs + buf * BT_TILE_BYTES + bt_off(my_row, my_half * 128);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const unsigned w = wv[j];
+                *reinterpret_cast<uint4*>(dst + 256 * j) = make_uint4(bm_spread01(w & 15u), bm_spread01((w >> 4) & 15u), bm_spread01((w >> 8) & 15u), bm_spread01((w >> 12) & 15u));
+                *reinterpret_cast<uint4*>(dst + 256 * j + 128) = make_uint4(bm_spread01((w >> 16) & 15u), bm_spread01((w >> 20) & 15u), bm_spread01((w >> 24) & 15u), bm_spread01(w >> 28));
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (it < nstages && tid == 0) {
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+#pragma unroll
+                for (int ks = 0; ks < 8; ks++) {
+                    const unsigned long long ad = bt_desc(As_addr + mt * BT_TILE_BYTES + ks * 256), bd = bt_desc(Bs_addr + buf * BT_TILE_BYTES + ks * 256);
+                    const unsigned acc = ks > 0 ? 1u : 0u;
+                    asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p; }"
+                                 ::"r"(tmem + (unsigned)((buf * 2 + mt) * 128)), "l"(ad), "l"(bd), "r"(IDESC), "r"(acc), "r"(0u) : "memory");
+                }
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mbar_addr + 8u * buf) : "memory");
+        }
+        if (it >= 1) {
+            const int e = it - 1, eb = e & 1;
+            bt_wait(mbar_addr + 8u * eb, (unsigned)((e >> 1) & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int cbase = e * BT_ROWS + 64 * half;                 // chunk row of this thread's first column
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+#pragma unroll
+                for (int part = 0; part < 2; part++) {
+                    int v[32];
+                    BT_LD32(v, tmem + ((unsigned)(32 * quarter) << 16) + (unsigned)((eb * 2 + mt) * 128 + 64 * half + 32 * part));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    int m = v[0];
+#pragma unroll
+                    for (int c = 1; c < 32; c++) m = max(m, v[c]);
+                    if (m >= thr[mt]) {
+#pragma unroll
+                        for (int c = 0; c < 32; c++) {
+                            const int idx = cbase + 32 * part + c;
+                            if (v[c] >= thr[mt] && idx < nrows) {
+                                const unsigned key = ((unsigned)(pq[mt] - v[c]) << BF_IDX_BITS) | (unsigned)idx;
+                                k2[mt] = min(k2[mt], max(k1[mt], key));
+                                k1[mt] = min(k1[mt], key);
+                                thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+    // ---- the two warps that share a query row (column halves) merge; release TMEM ----
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    if (half == 1) {
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) { scratch[(mt * 128 + row) * 2] = k1[mt]; scratch[(mt * 128 + row) * 2 + 1] = k2[mt]; }
+    }
+    __syncthreads();
+    if (half == 0) {
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) {
+            const unsigned y1 = scratch[(mt * 128 + row) * 2], y2 = scratch[(mt * 128 + row) * 2 + 1];
+            const unsigned x2 = min(max(k1[mt], y1), min(k2[mt], y2)), x1 = min(k1[mt], y1);
+            const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
+            if (qi < a.nq) {
+                a.part_k1[(long long)chunk * a.nq + qi] = x1;
+                a.part_k2[(long long)chunk * a.nq + qi] = x2;
+            }
+        }
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
 // Merge the per-chunk keys in ascending chunk (= ascending row) order: sequential-scan semantics.
 __global__ void bf_merge_chunks_kernel(const unsigned* __restrict__ k1, const unsigned* __restrict__ k2, int nchunks, int nq,
                                        long long rows_per_chunk, long long row_offset,
