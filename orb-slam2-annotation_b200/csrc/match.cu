@@ -970,8 +970,14 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
     dim3 grid(ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE), nchunks);
     if (db->variant == 3) {
         static bool attr_set = false;
-        if (!attr_set) { ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM)); attr_set = true; }
-        bf_top2_tc_kernel<<<grid, BT_THREADS, BT_SMEM, st>>>(a);
+        static const int nt = getenv("ORBB_BT_THREADS") ? atoi(getenv("ORBB_BT_THREADS")) : 1024;
+        if (!attr_set) {
+            ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM));
+            ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM));
+            attr_set = true;
+        }
+        if (nt == 512) bf_top2_tc_kernel<512><<<grid, 512, BT_SMEM, st>>>(a);
+        else bf_top2_tc_kernel<1024><<<grid, 1024, BT_SMEM, st>>>(a);
     }
     else if (db->variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
     else if (db->variant == 2) bf_top2_mma_kernel<<<grid, BM_THREADS, 0, st>>>(a);

@@ -856,11 +856,10 @@ __global__ void __launch_bounds__(BM_THREADS, 2) bf_top2_mma_kernel(const __grid
 //     a thread owns one query row and 64 of the 128 columns), filter them against the row threshold and update (k1, k2);
 //   * one __syncthreads per stage; MMA of stage s overlaps the epilogue of stage s-1 and the expansion of stage s+1.
 // ------------------------------------------------------------------------------------------------------
-constexpr int BT_THREADS = 256;
 constexpr int BT_QTILE = 256;
 constexpr int BT_ROWS = 128;
 constexpr int BT_TILE_BYTES = 128 * 256;                 // one 128 x 256-byte operand tile
-constexpr int BT_SMEM = 4 * BT_TILE_BYTES + 2 * BT_ROWS * 32 + 2048;     // A0 A1 B0 B1 | raw x 2 | merge scratch: 141312 B
+constexpr int BT_SMEM = 4 * BT_TILE_BYTES + 2 * BT_ROWS * 32;            // A0 A1 B0 B1 | packed rows x 2: 139264 B
 
 __device__ __forceinline__ unsigned long long bt_desc(unsigned smem_addr)
 {
@@ -887,20 +886,29 @@ __device__ __forceinline__ void bt_wait(unsigned mbar, unsigned parity)
                    "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                                                                      \
                  : "r"(taddr))
 
-__global__ void __launch_bounds__(BT_THREADS, 1) bf_top2_tc_kernel(const __grid_constant__ BfArgs a)
+#define BT_LD16(r, taddr)                                                                                                                  \
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"                  \
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),  \
+                   "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])                                            \
+                 : "r"(taddr))
+
+// NT threads: NT / 128 warps share a TMEM lane quarter and split the 128 columns of a stage; a thread expands 1024 / NT packed words.
+template <int NT>
+__global__ void __launch_bounds__(NT, 1) bf_top2_tc_kernel(const __grid_constant__ BfArgs a)
 {
+    constexpr int CG = NT / 128, COLS = 128 / CG, WPT = 1024 / NT;       // column groups, columns per thread, packed words per thread
+    static_assert(NT == 512 || NT == 1024, "512 or 1024 threads");
     extern __shared__ __align__(128) uint8_t bt_smem[];
     __shared__ __align__(8) unsigned long long mbar[2];
     __shared__ unsigned tmem_base_s;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, quarter = warp & 3, half = warp >> 2;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, quarter = warp & 3, cg = warp >> 2;
     const int chunk = blockIdx.y;
     const long long r_begin = (long long)chunk * a.rows_per_chunk;
     const long long r_end = min(a.nrows, r_begin + a.rows_per_chunk);
     const int nrows = (int)(r_end - r_begin);
     uint8_t* const As = bt_smem;
     uint8_t* const Bs = bt_smem + 2 * BT_TILE_BYTES;
-    uint4* const raw = reinterpret_cast<uint4*>(bt_smem + 4 * BT_TILE_BYTES);            // [2][256]
-    unsigned* const scratch = reinterpret_cast<unsigned*>(bt_smem + 4 * BT_TILE_BYTES + 2 * BT_ROWS * 32);
+    unsigned* const raw = reinterpret_cast<unsigned*>(bt_smem + 4 * BT_TILE_BYTES);       // [2][1024] packed words, a thread's own WPT
     const unsigned As_addr = (unsigned)__cvta_generic_to_shared(As), Bs_addr = (unsigned)__cvta_generic_to_shared(Bs);
     const unsigned mbar_addr = (unsigned)__cvta_generic_to_shared(&mbar[0]);
 
@@ -915,8 +923,8 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bf_top2_tc_kernel(const __grid_
     }
     // ---- A tiles: 256 queries x 256 bytes of +1 / -1, canonical K-major layout; consecutive lanes write consecutive rows ----
 #pragma unroll
-    for (int j = 0; j < 8; j++) {
-        const int i = tid + BT_THREADS * j;
+    for (int j = 0; j < 2048 / NT; j++) {
+        const int i = tid + NT * j;
         const int r8 = i & 7, wd = (i >> 3) & 7, row256 = (i >> 6) * 8 + r8;
         const int qi = blockIdx.x * BT_QTILE + row256;
         const bool ok = qi < a.nq;
@@ -929,7 +937,7 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bf_top2_tc_kernel(const __grid_
         *reinterpret_cast<uint4*>(dst) = lo;
         *reinterpret_cast<uint4*>(dst + 128) = hi;
     }
-    // ---- this thread's query rows: row = 32 quarter + lane of both tiles; it sees columns [64 half, 64 half + 64) of every stage ----
+    // ---- this thread's query rows: row = 32 quarter + lane of both tiles; it sees columns [COLS cg, COLS cg + COLS) of every stage ----
     const int row = 32 * quarter + lane;
     int pq[2], thr[2];
     unsigned k1[2], k2[2];
@@ -944,15 +952,16 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bf_top2_tc_kernel(const __grid_
         pq[mt] = pc; k1[mt] = 0xffffffffu; k2[mt] = 0xffffffffu;
         thr[mt] = qi < a.nq ? pc - 511 : 0x7fffffff;
     }
-    // ---- packed rows: every thread copies and later expands its own 16 bytes (half a row); lanes 0-7 take 8 consecutive rows ----
-    const int my_row = (tid & ~15) / 2 + (tid & 7), my_half = (tid >> 3) & 1;
+    // ---- packed rows: every thread copies and later expands its own WPT words; 8 consecutive lanes take 8 consecutive rows ----
+    const int my_row = (tid >> (WPT == 1 ? 6 : 5)) * 8 + (tid & 7), my_wd = WPT == 1 ? (tid >> 3) & 7 : 2 * ((tid >> 3) & 3);
     const int nstages = (nrows + BT_ROWS - 1) / BT_ROWS;
     auto load_stage = [&](int s, int buf) {
         const long long grow = r_begin + (long long)s * BT_ROWS + my_row;
-        const uint4* src = a.db + (grow < r_end ? grow * 2 + my_half : 0);
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(&raw[buf * BT_THREADS + tid]);
-        const int bytes = grow < r_end ? 16 : 0;
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+        const unsigned* src = reinterpret_cast<const unsigned*>(a.db) + (grow < r_end ? grow * 8 + my_wd : 0);
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(&raw[buf * 1024 + tid * WPT]);
+        const int bytes = grow < r_end ? 4 * WPT : 0;
+        if (WPT == 1) asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+        else asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(bytes));
         asm volatile("cp.async.commit_group;");
     };
     if (nstages > 0) load_stage(0, 0);
@@ -968,12 +977,13 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bf_top2_tc_kernel(const __grid_
         const int buf = it & 1;
         if (it < nstages) {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
-            const uint4 rv = raw[buf * BT_THREADS + tid];
-            if (it + 1 < nstages) load_stage(it + 1, buf ^ 1);
-            const unsigned wv[4] = {rv.x, rv.y, rv.z, rv.w};
-            uint8_t* dst = Bs + buf * BT_TILE_BYTES + bt_off(my_row, my_half * 128);
+            unsigned wv[WPT];
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
+            for (int j = 0; j < WPT; j++) wv[j] = raw[buf * 1024 + tid * WPT + j];
+            if (it + 1 < nstages) load_stage(it + 1, buf ^ 1);
+            uint8_t* dst = Bs + buf * BT_TILE_BYTES + bt_off(my_row, my_wd * 32);
+#pragma unroll
+            for (int j = 0; j < WPT; j++) {
                 const unsigned w = wv[j];
                 *reinterpret_cast<uint4*>(dst + 256 * j) = make_uint4(bm_spread01(w & 15u), bm_spread01((w >> 4) & 15u), bm_spread01((w >> 8) & 15u), bm_spread01((w >> 12) & 15u));
                 *reinterpret_cast<uint4*>(dst + 256 * j + 128) = make_uint4(bm_spread01((w >> 16) & 15u), bm_spread01((w >> 20) & 15u), bm_spread01((w >> 24) & 15u), bm_spread01(w >> 28));
@@ -1000,45 +1010,51 @@ __global__ void __launch_bounds__(BT_THREADS, 1) bf_top2_tc_kernel(const __grid_
             const int e = it - 1, eb = e & 1;
             bt_wait(mbar_addr + 8u * eb, (unsigned)((e >> 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int cbase = e * BT_ROWS + 64 * half;                 // chunk row of this thread's first column
+            const int cbase = e * BT_ROWS + COLS * cg;                 // chunk row of this thread's first column
+            int v[2][COLS];
 #pragma unroll
             for (int mt = 0; mt < 2; mt++) {
+                const unsigned ta = tmem + ((unsigned)(32 * quarter) << 16) + (unsigned)((eb * 2 + mt) * 128 + COLS * cg);
+                if (COLS == 32) { BT_LD32(v[mt], ta); } else { BT_LD16(v[mt], ta); }
+            }
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-                for (int part = 0; part < 2; part++) {
-                    int v[32];
-                    BT_LD32(v, tmem + ((unsigned)(32 * quarter) << 16) + (unsigned)((eb * 2 + mt) * 128 + 64 * half + 32 * part));
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    int m = v[0];
+            for (int mt = 0; mt < 2; mt++) {
+                int m = __vimax3_s32(v[mt][0], v[mt][1], v[mt][2]);
 #pragma unroll
-                    for (int c = 1; c < 32; c++) m = max(m, v[c]);
-                    if (m >= thr[mt]) {
+                for (int c = 3; c + 1 < COLS; c += 2) m = __vimax3_s32(m, v[mt][c], v[mt][c + 1]);
+                m = max(m, v[mt][COLS - 1]);
+                if (m >= thr[mt]) {
 #pragma unroll
-                        for (int c = 0; c < 32; c++) {
-                            const int idx = cbase + 32 * part + c;
-                            if (v[c] >= thr[mt] && idx < nrows) {
-                                const unsigned key = ((unsigned)(pq[mt] - v[c]) << BF_IDX_BITS) | (unsigned)idx;
-                                k2[mt] = min(k2[mt], max(k1[mt], key));
-                                k1[mt] = min(k1[mt], key);
-                                thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
-                            }
+                    for (int c = 0; c < COLS; c++) {
+                        const int idx = cbase + c;
+                        if (v[mt][c] >= thr[mt] && idx < nrows) {
+                            const unsigned key = ((unsigned)(pq[mt] - v[mt][c]) << BF_IDX_BITS) | (unsigned)idx;
+                            k2[mt] = min(k2[mt], max(k1[mt], key));
+                            k1[mt] = min(k1[mt], key);
+                            thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
                         }
                     }
                 }
             }
         }
     }
-    // ---- the two warps that share a query row (column halves) merge; release TMEM ----
+    // ---- the CG warps that share a query row (column groups) merge through shared memory (the B tiles are free now); release TMEM ----
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    if (half == 1) {
-#pragma unroll
-        for (int mt = 0; mt < 2; mt++) { scratch[(mt * 128 + row) * 2] = k1[mt]; scratch[(mt * 128 + row) * 2 + 1] = k2[mt]; }
-    }
     __syncthreads();
-    if (half == 0) {
+    unsigned* const scratch = reinterpret_cast<unsigned*>(Bs);         // [CG][2][128][2]
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++) { scratch[((cg * 2 + mt) * 128 + row) * 2] = k1[mt]; scratch[((cg * 2 + mt) * 128 + row) * 2 + 1] = k2[mt]; }
+    __syncthreads();
+    if (cg == 0) {
 #pragma unroll
         for (int mt = 0; mt < 2; mt++) {
-            const unsigned y1 = scratch[(mt * 128 + row) * 2], y2 = scratch[(mt * 128 + row) * 2 + 1];
-            const unsigned x2 = min(max(k1[mt], y1), min(k2[mt], y2)), x1 = min(k1[mt], y1);
+            unsigned x1 = k1[mt], x2 = k2[mt];
+            for (int g = 1; g < CG; g++) {
+                const unsigned y1 = scratch[((g * 2 + mt) * 128 + row) * 2], y2 = scratch[((g * 2 + mt) * 128 + row) * 2 + 1];
+                x2 = min(max(x1, y1), min(x2, y2));
+                x1 = min(x1, y1);
+            }
             const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
             if (qi < a.nq) {
                 a.part_k1[(long long)chunk * a.nq + qi] = x1;
