@@ -972,6 +972,7 @@ __global__ void __launch_bounds__(NT, 1) bf_top2_tc_kernel(const __grid_constant
     const unsigned tmem = tmem_base_s;
     // instruction descriptor: D = s32 (2 << 4), A = s8 (1 << 7), B = u8 (0 << 10), both K-major, N = 128 (16 << 17), M = 128 (8 << 24)
     constexpr unsigned IDESC = (2u << 4) | (1u << 7) | (16u << 17) | (8u << 24);
+    const unsigned long long adesc0 = bt_desc(As_addr), bdesc0 = bt_desc(Bs_addr);
 
     for (int it = 0; it <= nstages; it++) {
         const int buf = it & 1;
@@ -994,14 +995,19 @@ __global__ void __launch_bounds__(NT, 1) bf_top2_tc_kernel(const __grid_constant
         __syncthreads();
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         if (it < nstages && tid == 0) {
+            // descriptors differ only in the start-address field (16-byte units): + 2048 per tile, + 16 per k-step
+            const unsigned long long bd0 = bdesc0 + (unsigned long long)(buf * (BT_TILE_BYTES >> 4));
 #pragma unroll
             for (int mt = 0; mt < 2; mt++) {
 #pragma unroll
                 for (int ks = 0; ks < 8; ks++) {
-                    const unsigned long long ad = bt_desc(As_addr + mt * BT_TILE_BYTES + ks * 256), bd = bt_desc(Bs_addr + buf * BT_TILE_BYTES + ks * 256);
-                    const unsigned acc = ks > 0 ? 1u : 0u;
-                    asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p; }"
-                                 ::"r"(tmem + (unsigned)((buf * 2 + mt) * 128)), "l"(ad), "l"(bd), "r"(IDESC), "r"(acc), "r"(0u) : "memory");
+                    const unsigned long long ad = adesc0 + (unsigned long long)(mt * (BT_TILE_BYTES >> 4) + ks * 16), bd = bd0 + (unsigned long long)(ks * 16);
+                    if (ks == 0)
+                        asm volatile("{ .reg .pred p; setp.ne.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
+                                     ::"r"(tmem + (unsigned)((buf * 2 + mt) * 128)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
+                    else
+                        asm volatile("{ .reg .pred p; setp.eq.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
+                                     ::"r"(tmem + (unsigned)((buf * 2 + mt) * 128)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
                 }
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mbar_addr + 8u * buf) : "memory");
