@@ -882,8 +882,8 @@ extern "C" int orbm_db_create(orbm_db** out, int64_t capacity_rows, int64_t row_
     if (!db) return ORBB_E_NOMEM;
     db->device = device; db->capacity = capacity_rows; db->row_offset = row_offset;
     const char* v = getenv("ORBB_BF_VARIANT");
-    db->variant = v ? atoi(v) : 3;            // 3: tcgen05 / TMEM, 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
-    if (db->variant < 0 || db->variant > 3) db->variant = 3;
+    db->variant = v ? atoi(v) : 4;            // 4: tcgen05 / TMEM warp-specialised, 3: tcgen05 bulk-synchronous, 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
+    if (db->variant < 0 || db->variant > 4) db->variant = 4;
     if (cudaMalloc((void**)&db->d_rows, (size_t)(capacity_rows > 0 ? capacity_rows : 1) * 32) != cudaSuccess) {
         set_cuda_error(cudaGetLastError(), "orbm_db_create: cudaMalloc");
         delete db;
@@ -921,7 +921,7 @@ static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nc
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, db->device);
     const int qtiles = ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE);
-    int target = ceil_div(sms * (db->variant == 3 ? 2 : 4), qtiles);                         // ~4 CTAs per SM in flight (variant 2: two waves of two)
+    int target = ceil_div(sms * (db->variant >= 3 ? 2 : 4), qtiles);                         // ~4 CTAs per SM in flight (variant 2: two waves of two)
     long long rpc = (db->rows + target - 1) / target;
     rpc = (rpc + BF_ROWS - 1) / BF_ROWS * BF_ROWS;
     if (rpc < BF_ROWS) rpc = BF_ROWS;
@@ -968,7 +968,12 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
     a.db = db->d_rows; a.nrows = db->rows; a.q = (const uint4*)q_dev; a.nq = nq;
     a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = db->d_k1; a.part_k2 = db->d_k2;
     dim3 grid(ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE), nchunks);
-    if (db->variant == 3) {
+    if (db->variant == 4) {
+        static bool attr4_set = false;
+        if (!attr4_set) { ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BW_SMEM)); attr4_set = true; }
+        bf_top2_tcws_kernel<<<grid, BW_THREADS, BW_SMEM, st>>>(a);
+    }
+    else if (db->variant == 3) {
         static bool attr_set = false;
         static const int nt = getenv("ORBB_BT_THREADS") ? atoi(getenv("ORBB_BT_THREADS")) : 1024;
         if (!attr_set) {
