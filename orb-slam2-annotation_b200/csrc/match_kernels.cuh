@@ -1099,6 +1099,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcws_kernel(const __gri
     extern __shared__ __align__(128) uint8_t bt_smem[];
     __shared__ __align__(8) unsigned long long bars[2 * BW_STAGES + 4];      // full[S] | empty[S] | accfull[2] | accempty[2]
     __shared__ unsigned tmem_base_s;
+    __shared__ int thr_s[2 * 128];                                          // per query row: tightest threshold any of its four consumer threads holds
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int chunk = blockIdx.y;
     const long long r_begin = (long long)chunk * a.rows_per_chunk;
@@ -1127,6 +1128,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcws_kernel(const __gri
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (tid < 256) thr_s[tid] = -100000;
     // ---- A tiles: 256 queries x 256 bytes of +1 / -1, canonical K-major layout; consecutive lanes write consecutive rows ----
     for (int i = tid; i < 2048; i += BW_THREADS) {
         const int r8 = i & 7, wd = (i >> 3) & 7, row256 = (i >> 6) * 8 + r8;
@@ -1234,21 +1236,33 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcws_kernel(const __gri
             const int cbase = e * BT_ROWS + 32 * cg;
 #pragma unroll
             for (int mt = 0; mt < 2; mt++) {
-                int mx = __vimax3_s32(v[mt][0], v[mt][1], v[mt][2]);
+                // the four threads of a row see disjoint columns; each publishes its threshold, the row uses the tightest one: an
+                // element above ANY thread's second distance cannot enter the row's top-2
+                thr[mt] = max(thr[mt], thr_s[mt * 128 + row]);
+                int gm[4];
 #pragma unroll
-                for (int c = 3; c + 1 < 32; c += 2) mx = __vimax3_s32(mx, v[mt][c], v[mt][c + 1]);
-                mx = max(mx, v[mt][31]);
-                if (mx >= thr[mt]) {
+                for (int q = 0; q < 4; q++) {
+                    int t3 = __vimax3_s32(v[mt][8 * q], v[mt][8 * q + 1], v[mt][8 * q + 2]);
+                    t3 = __vimax3_s32(t3, v[mt][8 * q + 3], v[mt][8 * q + 4]);
+                    t3 = __vimax3_s32(t3, v[mt][8 * q + 5], v[mt][8 * q + 6]);
+                    gm[q] = max(t3, v[mt][8 * q + 7]);
+                }
+                if (max(__vimax3_s32(gm[0], gm[1], gm[2]), gm[3]) >= thr[mt]) {
 #pragma unroll
-                    for (int c = 0; c < 32; c++) {
-                        const int idx = cbase + c;
-                        if (v[mt][c] >= thr[mt] && idx < nrows) {
-                            const unsigned key = ((unsigned)(pq[mt] - v[mt][c]) << BF_IDX_BITS) | (unsigned)idx;
-                            k2[mt] = min(k2[mt], max(k1[mt], key));
-                            k1[mt] = min(k1[mt], key);
-                            thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
+                    for (int q = 0; q < 4; q++) {
+                        if (gm[q] < thr[mt]) continue;
+#pragma unroll
+                        for (int c = 8 * q; c < 8 * q + 8; c++) {
+                            const int idx = cbase + c;
+                            if (v[mt][c] >= thr[mt] && idx < nrows) {
+                                const unsigned key = ((unsigned)(pq[mt] - v[mt][c]) << BF_IDX_BITS) | (unsigned)idx;
+                                k2[mt] = min(k2[mt], max(k1[mt], key));
+                                k1[mt] = min(k1[mt], key);
+                                thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
+                            }
                         }
                     }
+                    if (thr[mt] != 0x7fffffff) atomicMax(&thr_s[mt * 128 + row], thr[mt]);
                 }
             }
         }
