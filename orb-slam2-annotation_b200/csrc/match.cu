@@ -968,20 +968,19 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
     a.db = db->d_rows; a.nrows = db->rows; a.q = (const uint4*)q_dev; a.nq = nq;
     a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = db->d_k1; a.part_k2 = db->d_k2;
     dim3 grid(ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE), nchunks);
-    if (db->variant == 4) {
-        static bool attr4_set = false;
-        if (!attr4_set) { ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BW_SMEM)); attr4_set = true; }
-        bf_top2_tcws_kernel<<<grid, BW_THREADS, BW_SMEM, st>>>(a);
-    }
-    else if (db->variant == 3) {
-        static bool attr_set = false;
-        static const int nt = getenv("ORBB_BT_THREADS") ? atoi(getenv("ORBB_BT_THREADS")) : 1024;
-        if (!attr_set) {
+    if (db->variant >= 3) {
+        // more than 48 KB of dynamic shared memory is an opt-in per device
+        static bool attr_set[64] = {};
+        const int dv = db->device & 63;
+        if (!attr_set[dv]) {
+            ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BW_SMEM));
             ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM));
             ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM));
-            attr_set = true;
+            attr_set[dv] = true;
         }
-        if (nt == 512) bf_top2_tc_kernel<512><<<grid, 512, BT_SMEM, st>>>(a);
+        static const int nt = getenv("ORBB_BT_THREADS") ? atoi(getenv("ORBB_BT_THREADS")) : 1024;
+        if (db->variant == 4) bf_top2_tcws_kernel<<<grid, BW_THREADS, BW_SMEM, st>>>(a);
+        else if (nt == 512) bf_top2_tc_kernel<512><<<grid, 512, BT_SMEM, st>>>(a);
         else bf_top2_tc_kernel<1024><<<grid, 1024, BT_SMEM, st>>>(a);
     }
     else if (db->variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
