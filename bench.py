@@ -152,7 +152,7 @@ def run_reference(args, rank, world):
             "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "hamming": {"metric": "bf_top2_gcmp_per_s", "value": gcmp, "unit": "Gcmp/s", "cores": nthreads},
             "wall_s": time.perf_counter() - t_all}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args, rank, world, local_rank):
@@ -361,12 +361,26 @@ def run_ours(args, rank, world, local_rank):
                            "l2": "inputs 157 MB/step/GPU > 126 MB L2 and ~2 GB of intermediates rewritten every step",
                            "parallelism": f"frames sharded across {world} GPU(s), no collective; DB row-sharded, one NCCL all-gather"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "hamming": hamming}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_OUT_FD = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else that libraries print (NCCL's version banner,
+    warnings) was redirected to stderr at start-up."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_OUT_FD if _OUT_FD is not None else 1, data)
+
+
 def main():
+    global _OUT_FD
+    sys.stdout.flush()
+    _OUT_FD = os.dup(1)
+    os.dup2(2, 1)                       # C-level and Python-level prints of libraries -> stderr
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
