@@ -377,10 +377,6 @@ def emit(line):
 
 
 def main():
-    global _OUT_FD
-    sys.stdout.flush()
-    _OUT_FD = os.dup(1)
-    os.dup2(2, 1)                       # C-level and Python-level prints of libraries -> stderr
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -397,6 +393,10 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1",
                "--master-port", "29517", os.path.abspath(__file__)] + sys.argv[1:]
         sys.exit(subprocess.call(cmd))
+    global _OUT_FD
+    sys.stdout.flush()
+    _OUT_FD = os.dup(1)
+    os.dup2(2, 1)                       # C-level and Python-level prints of libraries -> stderr
     if args.impl == "reference":
         run_reference(args, rank, world)
     else:
