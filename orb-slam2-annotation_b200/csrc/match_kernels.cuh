@@ -1084,10 +1084,17 @@ __global__ void __launch_bounds__(NT, 1) bf_top2_tc_kernel(const __grid_constant
 //   * 16 CONSUMER warps (4 per TMEM lane quarter, 32 columns each) wait accfull[b], pull the accumulators into registers
 //     (tcgen05.ld), release the buffer (accempty[b] <- one arrive per consumer warp) and only then filter / update the top-2.
 // ------------------------------------------------------------------------------------------------------
-constexpr int BW_STAGES = 3;
+#ifndef BW_STAGES_X
+#define BW_STAGES_X 3
+#endif
+#ifndef BW_PGROUPS_X
+#define BW_PGROUPS_X 2
+#endif
+constexpr int BW_STAGES = BW_STAGES_X;
+constexpr int BW_PGROUPS = BW_PGROUPS_X;                  // producer groups working on alternate stages
 constexpr int BW_PROD_WARPS = 8, BW_CONS_WARPS = 16;
 constexpr int BW_THREADS = 32 * (BW_PROD_WARPS + BW_CONS_WARPS + 1);                 // 800
-constexpr int BW_SMEM = (2 + BW_STAGES) * BT_TILE_BYTES + 2 * BT_ROWS * 32;         // A0 A1 | B ring | packed rows x 2: 172032 B
+constexpr int BW_SMEM = (2 + BW_STAGES) * BT_TILE_BYTES + BW_PGROUPS * 2 * BT_ROWS * 32;         // A0 A1 | B ring | packed rows x 2: 172032 B
 
 __device__ __forceinline__ void bw_arrive(unsigned mbar)
 {
@@ -1119,7 +1126,7 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcws_kernel(const __gri
     }
     if (tid == 0) {
         for (int s = 0; s < BW_STAGES; s++) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(BW_PROD_WARPS));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(BW_PROD_WARPS / BW_PGROUPS));
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty0 + 8 * s));
         }
         for (int b = 0; b < 2; b++) {
@@ -1155,30 +1162,43 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcws_kernel(const __gri
     const int quarter = warp & 3, cg = (warp - BW_PROD_WARPS) >> 2, row = 32 * quarter + lane;
 
     if (warp < BW_PROD_WARPS) {
-        // ================= producers: packed rows -> B ring =================
-        const int my_row = (tid & ~15) / 2 + (tid & 7), my_half = (tid >> 3) & 1;
+        // ================= producers: packed rows -> B ring; BW_PGROUPS groups of warps take alternate stages =================
+        constexpr int GT = 32 * BW_PROD_WARPS / BW_PGROUPS;      // threads per group
+        constexpr int U4 = 256 / GT;                             // 16-byte pieces per thread and stage (1: half a row, 2: a whole row)
+        const int pg = tid / GT, t = tid % GT;
+        const int my_row = U4 == 1 ? (t & ~15) / 2 + (t & 7) : (t >> 3) * 8 + (t & 7), my_half = U4 == 1 ? (t >> 3) & 1 : 0;
+        uint4* const myraw = raw + pg * 512;                      // [2][GT * U4] own slots
         auto load_stage = [&](int s, int buf) {
             const long long grow = r_begin + (long long)s * BT_ROWS + my_row;
-            const uint4* src = a.db + (grow < r_end ? grow * 2 + my_half : 0);
-            const unsigned dst = (unsigned)__cvta_generic_to_shared(&raw[buf * 256 + tid]);
-            const int bytes = grow < r_end ? 16 : 0;
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+#pragma unroll
+            for (int u = 0; u < U4; u++) {
+                const uint4* src = a.db + (grow < r_end ? grow * 2 + my_half + u : 0);
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(&myraw[buf * 256 + t * U4 + u]);
+                const int bytes = grow < r_end ? 16 : 0;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+            }
             asm volatile("cp.async.commit_group;");
         };
-        if (nstages > 0) load_stage(0, 0);
-        for (int it = 0; it < nstages; it++) {
+        if (pg < nstages) load_stage(pg, 0);
+        int k = 0;                                               // this group's stage counter
+        for (int it = pg; it < nstages; it += BW_PGROUPS, k++) {
             const int s = it % BW_STAGES, n = it / BW_STAGES;
             asm volatile("cp.async.wait_group 0;" ::: "memory");
-            const uint4 rv = raw[(it & 1) * 256 + tid];
-            if (it + 1 < nstages) load_stage(it + 1, (it + 1) & 1);
+            uint4 rv[U4];
+#pragma unroll
+            for (int u = 0; u < U4; u++) rv[u] = myraw[(k & 1) * 256 + t * U4 + u];
+            if (it + BW_PGROUPS < nstages) load_stage(it + BW_PGROUPS, (k + 1) & 1);
             if (it >= BW_STAGES) bt_wait(empty0 + 8 * s, (unsigned)((n - 1) & 1));      // the MMAs that read this tile have completed
-            const unsigned wv[4] = {rv.x, rv.y, rv.z, rv.w};
             uint8_t* dst = Bs + s * BT_TILE_BYTES + bt_off(my_row, my_half * 128);
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const unsigned w = wv[j];
-                *reinterpret_cast<uint4*>(dst + 256 * j) = make_uint4(bm_spread01(w & 15u), bm_spread01((w >> 4) & 15u), bm_spread01((w >> 8) & 15u), bm_spread01((w >> 12) & 15u));
-                *reinterpret_cast<uint4*>(dst + 256 * j + 128) = make_uint4(bm_spread01((w >> 16) & 15u), bm_spread01((w >> 20) & 15u), bm_spread01((w >> 24) & 15u), bm_spread01(w >> 28));
+            for (int u = 0; u < U4; u++) {
+                const unsigned wv[4] = {rv[u].x, rv[u].y, rv[u].z, rv[u].w};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const unsigned w = wv[j];
+                    *reinterpret_cast<uint4*>(dst + 1024 * u + 256 * j) = make_uint4(bm_spread01(w & 15u), bm_spread01((w >> 4) & 15u), bm_spread01((w >> 8) & 15u), bm_spread01((w >> 12) & 15u));
+                    *reinterpret_cast<uint4*>(dst + 1024 * u + 256 * j + 128) = make_uint4(bm_spread01((w >> 16) & 15u), bm_spread01((w >> 20) & 15u), bm_spread01((w >> 24) & 15u), bm_spread01(w >> 28));
+                }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
