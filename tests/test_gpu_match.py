@@ -178,6 +178,31 @@ def test_bf_top2_small_and_edges(gpu):
     assert len(orbb200.DescriptorDB(4).top2(q[:0])[0]) == 0
 
 
+@pytest.mark.parametrize("variant", ["0", "1", "2", "3", "4"])
+def test_bf_top2_every_kernel_variant(gpu, variant, monkeypatch):
+    """Every brute-force kernel (plain POPC, carry-save integer pipe, legacy mma.sync IMMA, tcgen05 bulk-synchronous, tcgen05
+    warp-specialised = default) against the oracle: duplicates (first index wins, d2 == d1), all-zero and all-one descriptors
+    (|q| = 0 / 256: the extremes of hamming = |q| - sum a.b), ragged query and row counts around the 128-row stage and the
+    256-query tile, and row counts that leave empty trailing chunks."""
+    import orbb200, pyoracle
+    from synth import synth_descriptor_db, synth_queries
+    monkeypatch.setenv("ORBB_BF_VARIANT", variant)
+    db = synth_descriptor_db(70_001, seed=11)
+    db[5] = 0; db[6] = 255; db[60_000] = db[321]; db[69_999] = db[321]
+    q = synth_queries(db, 515, seed=12)
+    q[0] = db[321]; q[1] = 0; q[2] = 255; q[3] = db[70_000]
+    for nq, nrows in ((515, 70_001), (1, 70_001), (256, 129), (257, 128), (300, 1), (64, 383), (515, 33_000)):
+        D = orbb200.DescriptorDB(max(nrows, 1)); D.append(db[:nrows])
+        d1, i1, d2 = D.top2(q[:nq])
+        o1, oi, o2 = pyoracle.bf_top2(db[:nrows], q[:nq], nthreads=8)
+        assert np.array_equal(d1, o1) and np.array_equal(i1, oi) and np.array_equal(d2, o2), (variant, nq, nrows)
+        D.close()
+    D = orbb200.DescriptorDB(70_001); D.append(db)
+    d1, i1, d2 = D.top2(q)
+    assert d1[0] == 0 and i1[0] == 321 and d2[0] == 0 and d1[1] == 0 and i1[1] == 5 and d1[2] == 0 and i1[2] == 6 and i1[3] == 70_000
+    D.close()
+
+
 def test_bf_top2_sharded_merge_equals_single(gpu):
     """Shard the DB into contiguous ranges, merge per-shard top-2 on the device (the post-all-gather step):
     identical to the unsharded scan and to the oracle."""
