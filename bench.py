@@ -331,7 +331,7 @@ def run_ours(args, rank, world, local_rank):
     hamming = {"metric": "bf_top2_gcmp_per_s", "value": gcmp, "unit": "Gcmp/s", "ms_per_step": ms_match / Km, "steps": Km,
                "workload": f"{NQ} queries x {DB_ROWS} rows per GPU, top-2 + merge" + (" + NCCL all-gather" if world > 1 else ""),
                "gpu_launches": int(match_launches),
-               "kernel": "bf_top2_tcws_kernel: hamming = |q| - sum(+-1 query bits x 0/1 database bits), tcgen05.mma kind::i8 128x128x32, "
+               "kernel": "bf_top2_tcn_kernel: hamming = |q| - sum(+-1 query bits x 0/1 database bits), tcgen05.mma kind::i8 128x256x32, warp-specialised, "
                          "accumulators in TMEM, threshold-filtered top-2 update",
                "roofline": {"bound": "tensor", "achieved": tops, "peak": 4 * imma_peak, "unit": "int8 TOP/s", "frac": tops / (4 * imma_peak),
                             "peak_source": "4 x the measured register-only mma.sync.m16n8k32 rate on this GPU (orbb200_measure_imma_peak: the legacy "

@@ -882,8 +882,8 @@ extern "C" int orbm_db_create(orbm_db** out, int64_t capacity_rows, int64_t row_
     if (!db) return ORBB_E_NOMEM;
     db->device = device; db->capacity = capacity_rows; db->row_offset = row_offset;
     const char* v = getenv("ORBB_BF_VARIANT");
-    db->variant = v ? atoi(v) : 4;            // 4: tcgen05 / TMEM warp-specialised, 3: tcgen05 bulk-synchronous, 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
-    if (db->variant < 0 || db->variant > 4) db->variant = 4;
+    db->variant = v ? atoi(v) : 5;            // 5: tcgen05 / TMEM warp-specialised with N = 256 MMAs, 4: the same with N = 128, 3: tcgen05 bulk-synchronous, 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
+    if (db->variant < 0 || db->variant > 5) db->variant = 5;
     if (cudaMalloc((void**)&db->d_rows, (size_t)(capacity_rows > 0 ? capacity_rows : 1) * 32) != cudaSuccess) {
         set_cuda_error(cudaGetLastError(), "orbm_db_create: cudaMalloc");
         delete db;
@@ -923,7 +923,7 @@ static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nc
     const int qtiles = ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE);
     int target = ceil_div(sms * (db->variant >= 3 ? 2 : 4), qtiles);                         // ~4 CTAs per SM in flight (variant 2: two waves of two)
     long long rpc = (db->rows + target - 1) / target;
-    rpc = (rpc + BF_ROWS - 1) / BF_ROWS * BF_ROWS;
+    rpc = (rpc + 255) / 256 * 256;                                  // a multiple of every kernel's stage size
     if (rpc < BF_ROWS) rpc = BF_ROWS;
     if (rpc > (1ll << BF_IDX_BITS)) rpc = 1ll << BF_IDX_BITS;
     *rows_per_chunk = rpc;
@@ -974,12 +974,14 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
         const int dv = db->device & 63;
         if (!attr_set[dv]) {
             ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BW_SMEM));
+            ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_SMEM));
             ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM));
             ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM));
             attr_set[dv] = true;
         }
         static const int nt = getenv("ORBB_BT_THREADS") ? atoi(getenv("ORBB_BT_THREADS")) : 1024;
-        if (db->variant == 4) bf_top2_tcws_kernel<<<grid, BW_THREADS, BW_SMEM, st>>>(a);
+        if (db->variant == 5) bf_top2_tcn_kernel<<<grid, BW_THREADS, BN_SMEM, st>>>(a);
+        else if (db->variant == 4) bf_top2_tcws_kernel<<<grid, BW_THREADS, BW_SMEM, st>>>(a);
         else if (nt == 512) bf_top2_tc_kernel<512><<<grid, 512, BT_SMEM, st>>>(a);
         else bf_top2_tc_kernel<1024><<<grid, 1024, BT_SMEM, st>>>(a);
     }

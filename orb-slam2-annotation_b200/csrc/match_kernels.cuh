@@ -1319,6 +1319,229 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcws_kernel(const __gri
     }
 }
 
+// ------------------------------------------------------------------------------------------------------
+// Variant 5: the warp-specialised kernel with N = 256 MMAs.  A stage is 256 database rows (B tile 64 KB, ring of two); each query
+// tile has ONE 256-column accumulator, so the two tiles of a stage double-buffer each other: tile 1 is multiplied while tile 0 is
+// consumed.  Shared-memory reads of the tensor core drop from 1024 to 768 bytes per row and CTA, and there are half as many stage
+// hand-overs and MMA instructions.
+// ------------------------------------------------------------------------------------------------------
+constexpr int BN_ROWS = 256, BN_STAGES = 2;
+constexpr int BN_BTILE = BN_ROWS * 256;
+constexpr int BN_SMEM = 2 * BT_TILE_BYTES + BN_STAGES * BN_BTILE + 2 * BN_ROWS * 32;     // 212992 B
+
+__global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcn_kernel(const __grid_constant__ BfArgs a)
+{
+    extern __shared__ __align__(128) uint8_t bt_smem[];
+    __shared__ __align__(8) unsigned long long bars[2 * BN_STAGES + 4];      // full[S] | empty[S] | accfull[2] | accempty[2]
+    __shared__ unsigned tmem_base_s;
+    __shared__ int thr_s[2 * 128];                                          // per query row: tightest threshold any of its four consumer threads holds
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int chunk = blockIdx.y;
+    const long long r_begin = (long long)chunk * a.rows_per_chunk;
+    const long long r_end = min(a.nrows, r_begin + a.rows_per_chunk);
+    const int nrows = (int)(r_end - r_begin);
+    const int nstages = (nrows + BN_ROWS - 1) / BN_ROWS;
+    uint8_t* const As = bt_smem;
+    uint8_t* const Bs = bt_smem + 2 * BT_TILE_BYTES;
+    uint4* const raw = reinterpret_cast<uint4*>(bt_smem + 2 * BT_TILE_BYTES + BN_STAGES * BN_BTILE);      // [2][256][2], a producer thread's own slots
+    const unsigned As_addr = (unsigned)__cvta_generic_to_shared(As), Bs_addr = (unsigned)__cvta_generic_to_shared(Bs);
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
+    const unsigned full0 = bar0, empty0 = bar0 + 8 * BN_STAGES, accfull0 = bar0 + 16 * BN_STAGES, accempty0 = accfull0 + 16;
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((unsigned)__cvta_generic_to_shared(&tmem_base_s)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 0) {
+        for (int s = 0; s < BN_STAGES; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(BW_PROD_WARPS));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty0 + 8 * s));
+        }
+        for (int b = 0; b < 2; b++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(accfull0 + 8 * b));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(accempty0 + 8 * b), "r"(BW_CONS_WARPS));
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 256) thr_s[tid] = -100000;
+    // ---- A tiles: 256 queries x 256 bytes of +1 / -1, canonical K-major layout; consecutive lanes write consecutive rows ----
+    for (int i = tid; i < 2048; i += BW_THREADS) {
+        const int r8 = i & 7, wd = (i >> 3) & 7, row256 = (i >> 6) * 8 + r8;
+        const int qi = blockIdx.x * BT_QTILE + row256;
+        const bool ok = qi < a.nq;
+        const unsigned w = ok ? reinterpret_cast<const unsigned*>(a.q)[(long long)qi * 8 + wd] : 0u;
+        uint4 lo, hi;
+        lo.x = bm_spread_pm1(w & 15u); lo.y = bm_spread_pm1((w >> 4) & 15u); lo.z = bm_spread_pm1((w >> 8) & 15u); lo.w = bm_spread_pm1((w >> 12) & 15u);
+        hi.x = bm_spread_pm1((w >> 16) & 15u); hi.y = bm_spread_pm1((w >> 20) & 15u); hi.z = bm_spread_pm1((w >> 24) & 15u); hi.w = bm_spread_pm1(w >> 28);
+        if (!ok) { lo = make_uint4(0, 0, 0, 0); hi = lo; }
+        uint8_t* dst = As + (row256 >> 7) * BT_TILE_BYTES + bt_off(row256 & 127, wd * 32);
+        *reinterpret_cast<uint4*>(dst) = lo;
+        *reinterpret_cast<uint4*>(dst + 128) = hi;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                          // the A tiles are read by the tensor core
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = tmem_base_s;
+    constexpr unsigned IDESC = (2u << 4) | (1u << 7) | (32u << 17) | (8u << 24);      // N = 256
+
+    int pq[2] = {0, 0}, thr[2] = {0x7fffffff, 0x7fffffff};
+    unsigned k1[2] = {0xffffffffu, 0xffffffffu}, k2[2] = {0xffffffffu, 0xffffffffu};
+    const int quarter = warp & 3, cg = (warp - BW_PROD_WARPS) >> 2, row = 32 * quarter + lane;
+
+    if (warp < BW_PROD_WARPS) {
+        // ================= producers: 256 packed rows -> B ring; thread t owns row t of every stage (two 16-byte copies) =================
+        auto load_stage = [&](int s, int buf) {
+            const long long grow = r_begin + (long long)s * BN_ROWS + tid;
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                const uint4* src = a.db + (grow < r_end ? grow * 2 + u : 0);
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(&raw[(buf * 256 + tid) * 2 + u]);
+                const int bytes = grow < r_end ? 16 : 0;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+            }
+            asm volatile("cp.async.commit_group;");
+        };
+        if (nstages > 0) load_stage(0, 0);
+        for (int it = 0; it < nstages; it++) {
+            const int s = it % BN_STAGES, n = it / BN_STAGES;
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            uint4 rv[2];
+            rv[0] = raw[((it & 1) * 256 + tid) * 2]; rv[1] = raw[((it & 1) * 256 + tid) * 2 + 1];
+            if (it + 1 < nstages) load_stage(it + 1, (it + 1) & 1);
+            if (it >= BN_STAGES) bt_wait(empty0 + 8 * s, (unsigned)((n - 1) & 1));      // the MMAs that read this tile have completed
+            uint8_t* dst = Bs + s * BN_BTILE + bt_off(tid, 0);
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                const unsigned wv[4] = {rv[u].x, rv[u].y, rv[u].z, rv[u].w};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const unsigned w = wv[j];
+                    *reinterpret_cast<uint4*>(dst + 1024 * u + 256 * j) = make_uint4(bm_spread01(w & 15u), bm_spread01((w >> 4) & 15u), bm_spread01((w >> 8) & 15u), bm_spread01((w >> 12) & 15u));
+                    *reinterpret_cast<uint4*>(dst + 1024 * u + 256 * j + 128) = make_uint4(bm_spread01((w >> 16) & 15u), bm_spread01((w >> 20) & 15u), bm_spread01((w >> 24) & 15u), bm_spread01(w >> 28));
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) bw_arrive(full0 + 8 * s);
+        }
+    } else if (warp == BW_PROD_WARPS + BW_CONS_WARPS) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            // accumulator buffer = query tile: 256 columns each; tile 1 of a stage is multiplied while tile 0 is being consumed
+            const unsigned long long adesc0 = bt_desc(As_addr), bdesc0 = bt_desc(Bs_addr);
+            for (int it = 0; it < nstages; it++) {
+                const int s = it % BN_STAGES, n = it / BN_STAGES;
+                bt_wait(full0 + 8 * s, (unsigned)(n & 1));
+                const unsigned long long bd0 = bdesc0 + (unsigned long long)(s * (BN_BTILE >> 4));
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    if (it >= 1) bt_wait(accempty0 + 8 * mt, (unsigned)((it - 1) & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                    for (int ks = 0; ks < 8; ks++) {
+                        const unsigned long long ad = adesc0 + (unsigned long long)(mt * (BT_TILE_BYTES >> 4) + ks * 16), bd = bd0 + (unsigned long long)(ks * 16);
+                        if (ks == 0)
+                            asm volatile("{ .reg .pred p; setp.ne.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
+                                         ::"r"(tmem + (unsigned)(mt * 256)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
+                        else
+                            asm volatile("{ .reg .pred p; setp.eq.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
+                                         ::"r"(tmem + (unsigned)(mt * 256)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
+                    }
+                    if (mt == 1) asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(empty0 + 8u * s) : "memory");
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(accfull0 + 8u * mt) : "memory");
+                }
+            }
+        }
+    } else {
+        // ================= consumers: accumulators -> top-2 =================
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) {
+            const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
+            if (qi < a.nq) {
+                const uint4 v0 = a.q[2 * qi], v1 = a.q[2 * qi + 1];
+                pq[mt] = __popc(v0.x) + __popc(v0.y) + __popc(v0.z) + __popc(v0.w) + __popc(v1.x) + __popc(v1.y) + __popc(v1.z) + __popc(v1.w);
+                thr[mt] = pq[mt] - 511;
+            }
+        }
+        for (int e = 0; e < nstages; e++) {
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+                bt_wait(accfull0 + 8 * mt, (unsigned)(e & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                thr[mt] = max(thr[mt], thr_s[mt * 128 + row]);
+#pragma unroll
+                for (int part = 0; part < 2; part++) {                // this warp's 64 columns of the tile, 32 at a time
+                    int v[32];
+                    BT_LD32(v, tmem + ((unsigned)(32 * quarter) << 16) + (unsigned)(mt * 256 + 64 * cg + 32 * part));
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (part == 1) {
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        __syncwarp();
+                        if (lane == 0) bw_arrive(accempty0 + 8 * mt);     // the tile's buffer can be overwritten: the values are in registers
+                    }
+                    const int cbase = e * BN_ROWS + 64 * cg + 32 * part;
+                    int gm[4];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        int t3 = __vimax3_s32(v[8 * q], v[8 * q + 1], v[8 * q + 2]);
+                        t3 = __vimax3_s32(t3, v[8 * q + 3], v[8 * q + 4]);
+                        t3 = __vimax3_s32(t3, v[8 * q + 5], v[8 * q + 6]);
+                        gm[q] = max(t3, v[8 * q + 7]);
+                    }
+                    if (max(__vimax3_s32(gm[0], gm[1], gm[2]), gm[3]) >= thr[mt]) {
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            if (gm[q] < thr[mt]) continue;
+#pragma unroll
+                            for (int c = 8 * q; c < 8 * q + 8; c++) {
+                                const int idx = cbase + c;
+                                if (v[c] >= thr[mt] && idx < nrows) {
+                                    const unsigned key = ((unsigned)(pq[mt] - v[c]) << BF_IDX_BITS) | (unsigned)idx;
+                                    k2[mt] = min(k2[mt], max(k1[mt], key));
+                                    k1[mt] = min(k1[mt], key);
+                                    thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
+                                }
+                            }
+                        }
+                        if (thr[mt] != 0x7fffffff) atomicMax(&thr_s[mt * 128 + row], thr[mt]);
+                    }
+                }
+            }
+        }
+    }
+    // ---- merge the four column groups of a query row through shared memory (the B ring is free: every MMA has been consumed) ----
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    unsigned* const scratch = reinterpret_cast<unsigned*>(Bs);         // [4][2][128][2]
+    const bool consumer = warp >= BW_PROD_WARPS && warp < BW_PROD_WARPS + BW_CONS_WARPS;
+    if (consumer) {
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) { scratch[((cg * 2 + mt) * 128 + row) * 2] = k1[mt]; scratch[((cg * 2 + mt) * 128 + row) * 2 + 1] = k2[mt]; }
+    }
+    __syncthreads();
+    if (consumer && cg == 0) {
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) {
+            unsigned x1 = k1[mt], x2 = k2[mt];
+            for (int g = 1; g < 4; g++) {
+                const unsigned y1 = scratch[((g * 2 + mt) * 128 + row) * 2], y2 = scratch[((g * 2 + mt) * 128 + row) * 2 + 1];
+                x2 = min(max(x1, y1), min(x2, y2));
+                x1 = min(x1, y1);
+            }
+            const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
+            if (qi < a.nq) {
+                a.part_k1[(long long)chunk * a.nq + qi] = x1;
+                a.part_k2[(long long)chunk * a.nq + qi] = x2;
+            }
+        }
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
 // Merge the per-chunk keys in ascending chunk (= ascending row) order: sequential-scan semantics.
 __global__ void bf_merge_chunks_kernel(const unsigned* __restrict__ k1, const unsigned* __restrict__ k2, int nchunks, int nq,
                                        long long rows_per_chunk, long long row_offset,

@@ -178,10 +178,10 @@ def test_bf_top2_small_and_edges(gpu):
     assert len(orbb200.DescriptorDB(4).top2(q[:0])[0]) == 0
 
 
-@pytest.mark.parametrize("variant", ["0", "1", "2", "3", "4"])
+@pytest.mark.parametrize("variant", ["0", "1", "2", "3", "4", "5"])
 def test_bf_top2_every_kernel_variant(gpu, variant, monkeypatch):
     """Every brute-force kernel (plain POPC, carry-save integer pipe, legacy mma.sync IMMA, tcgen05 bulk-synchronous, tcgen05
-    warp-specialised = default) against the oracle: duplicates (first index wins, d2 == d1), all-zero and all-one descriptors
+    warp-specialised with N = 128 and with N = 256 MMAs = default) against the oracle: duplicates (first index wins, d2 == d1), all-zero and all-one descriptors
     (|q| = 0 / 256: the extremes of hamming = |q| - sum a.b), ragged query and row counts around the 128-row stage and the
     256-query tile, and row counts that leave empty trailing chunks."""
     import orbb200, pyoracle
@@ -191,7 +191,7 @@ def test_bf_top2_every_kernel_variant(gpu, variant, monkeypatch):
     db[5] = 0; db[6] = 255; db[60_000] = db[321]; db[69_999] = db[321]
     q = synth_queries(db, 515, seed=12)
     q[0] = db[321]; q[1] = 0; q[2] = 255; q[3] = db[70_000]
-    for nq, nrows in ((515, 70_001), (1, 70_001), (256, 129), (257, 128), (300, 1), (64, 383), (515, 33_000)):
+    for nq, nrows in ((515, 70_001), (1, 70_001), (256, 129), (257, 128), (300, 1), (64, 383), (64, 255), (300, 257), (515, 33_000)):
         D = orbb200.DescriptorDB(max(nrows, 1)); D.append(db[:nrows])
         d1, i1, d2 = D.top2(q[:nq])
         o1, oi, o2 = pyoracle.bf_top2(db[:nrows], q[:nq], nthreads=8)
