@@ -882,8 +882,8 @@ extern "C" int orbm_db_create(orbm_db** out, int64_t capacity_rows, int64_t row_
     if (!db) return ORBB_E_NOMEM;
     db->device = device; db->capacity = capacity_rows; db->row_offset = row_offset;
     const char* v = getenv("ORBB_BF_VARIANT");
-    db->variant = v ? atoi(v) : 5;            // 5: tcgen05 / TMEM warp-specialised with N = 256 MMAs, 4: the same with N = 128, 3: tcgen05 bulk-synchronous, 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
-    if (db->variant < 0 || db->variant > 5) db->variant = 5;
+    db->variant = v ? atoi(v) : 3;            // 3: tcgen05 / TMEM (warp-specialised, N = 256 MMAs), 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
+    if (db->variant < 0 || db->variant > 3) db->variant = 3;
     if (cudaMalloc((void**)&db->d_rows, (size_t)(capacity_rows > 0 ? capacity_rows : 1) * 32) != cudaSuccess) {
         set_cuda_error(cudaGetLastError(), "orbm_db_create: cudaMalloc");
         delete db;
@@ -973,17 +973,10 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
         static bool attr_set[64] = {};
         const int dv = db->device & 63;
         if (!attr_set[dv]) {
-            ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcws_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BW_SMEM));
             ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_SMEM));
-            ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM));
-            ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, BT_SMEM));
             attr_set[dv] = true;
         }
-        static const int nt = getenv("ORBB_BT_THREADS") ? atoi(getenv("ORBB_BT_THREADS")) : 1024;
-        if (db->variant == 5) bf_top2_tcn_kernel<<<grid, BW_THREADS, BN_SMEM, st>>>(a);
-        else if (db->variant == 4) bf_top2_tcws_kernel<<<grid, BW_THREADS, BW_SMEM, st>>>(a);
-        else if (nt == 512) bf_top2_tc_kernel<512><<<grid, 512, BT_SMEM, st>>>(a);
-        else bf_top2_tc_kernel<1024><<<grid, 1024, BT_SMEM, st>>>(a);
+        bf_top2_tcn_kernel<<<grid, BW_THREADS, BN_SMEM, st>>>(a);
     }
     else if (db->variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
     else if (db->variant == 2) bf_top2_mma_kernel<<<grid, BM_THREADS, 0, st>>>(a);

@@ -846,20 +846,29 @@ __global__ void __launch_bounds__(BM_THREADS, 2) bf_top2_mma_kernel(const __grid
 }
 
 // ------------------------------------------------------------------------------------------------------
-// Brute-force top-2 with tcgen05 (variant 3): the same restatement as bf_top2_mma_kernel (hamming = |q| - sum a.b, a = +-1, b = 0/1)
-// on the 5th-generation tensor cores.  tcgen05.mma.kind::i8, M = 128 queries x N = 128 rows x K = 32 bits per instruction, both
-// operands in shared memory (K-major, no swizzle: 8-row x 16-byte core matrices, LBO = 128 B between the two K chunks of an
-// instruction, SBO = 2048 B between 8-row groups), int32 accumulators in TMEM.
-//   * a CTA owns 256 queries = two A tiles of 32 KB, expanded once; one CTA per SM (all 512 TMEM columns: 2 stages x 2 tiles x 128);
-//   * per stage of 128 rows: all warps expand the packed rows into the B tile of that stage, one thread issues the 16 MMAs of the
-//     stage and commits them to an mbarrier; meanwhile all warps read the PREVIOUS stage's accumulators (tcgen05.ld 32x32b.x32:
-//     a thread owns one query row and 64 of the 128 columns), filter them against the row threshold and update (k1, k2);
-//   * one __syncthreads per stage; MMA of stage s overlaps the epilogue of stage s-1 and the expansion of stage s+1.
+// Brute-force top-2 on the 5th-generation tensor cores (default).  The same restatement as bf_top2_mma_kernel (hamming = |q| - sum a.b,
+// a = +-1 query bits, b = 0 / 1 database bits) issued as tcgen05.mma.kind::i8, M = 128 queries x N = 256 rows x K = 32 bits per
+// instruction, both operands in shared memory (K-major, no swizzle: 8-row x 16-byte core matrices, LBO = 128 B between the two K chunks
+// of an instruction, SBO = 2048 B between 8-row groups), int32 accumulators in TMEM.
+//   * a CTA owns 256 queries = two A tiles of 32 KB (+1 / -1 bytes), expanded once; one CTA per SM (all 512 TMEM columns);
+//   * a stage is 256 database rows = one 64 KB B tile (ring of two).  Each query tile has ONE 256-column accumulator, so the two tiles of
+//     a stage double-buffer each other: tile 1 is multiplied while tile 0 is consumed.  (N = 256 rather than 128 because with both
+//     operands in shared memory the kernel sits at the 128 B/clk shared-memory port before the tensor pipe: 768 instead of 1024 bytes
+//     read per row and CTA.)
+// The three activities of a stage run as independent pipelines coupled only by mbarriers; no block barrier inside the scan:
+//   * 8 PRODUCER warps: thread t copies packed row t of the stage (cp.async, own slots) and expands it bit -> byte into the B tile;
+//     full[s] <- one arrive per producer warp;  a tile is reused when empty[s] <- tcgen05.commit of the MMAs that read it;
+//   * 1 MMA warp (one lane) waits full[s] and accempty[t], issues the 8 k-steps of tile t and commits them to accfull[t] (and to
+//     empty[s] after tile 1);
+//   * 16 CONSUMER warps (4 per TMEM lane quarter, 64 columns each, a thread = one query row) wait accfull[t], pull the accumulators
+//     into registers (tcgen05.ld), release the buffer (accempty[t] <- one arrive per consumer warp) and filter them against the row
+//     threshold |q| - (current second distance); only a pair that can still enter the top-2 builds its key and updates (k1, k2).  The
+//     four threads of a row publish their threshold with a shared-memory atomicMax: an element above ANY thread's second distance
+//     cannot enter the row's top-2.
+// Output: the same per-(chunk, query) packed keys as bf_top2_kernel, merged by bf_merge_chunks_kernel.
 // ------------------------------------------------------------------------------------------------------
-constexpr int BT_QTILE = 256;
-constexpr int BT_ROWS = 128;
-constexpr int BT_TILE_BYTES = 128 * 256;                 // one 128 x 256-byte operand tile
-constexpr int BT_SMEM = 4 * BT_TILE_BYTES + 2 * BT_ROWS * 32;            // A0 A1 B0 B1 | packed rows x 2: 139264 B
+constexpr int BT_QTILE = 256;                            // queries per CTA
+constexpr int BT_TILE_BYTES = 128 * 256;                 // one 128-row x 256-byte operand tile
 
 __device__ __forceinline__ unsigned long long bt_desc(unsigned smem_addr)
 {
@@ -886,445 +895,13 @@ __device__ __forceinline__ void bt_wait(unsigned mbar, unsigned parity)
                    "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                                                                      \
                  : "r"(taddr))
 
-#define BT_LD16(r, taddr)                                                                                                                  \
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"                  \
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),  \
-                   "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])                                            \
-                 : "r"(taddr))
-
-// NT threads: NT / 128 warps share a TMEM lane quarter and split the 128 columns of a stage; a thread expands 1024 / NT packed words.
-template <int NT>
-__global__ void __launch_bounds__(NT, 1) bf_top2_tc_kernel(const __grid_constant__ BfArgs a)
-{
-    constexpr int CG = NT / 128, COLS = 128 / CG, WPT = 1024 / NT;       // column groups, columns per thread, packed words per thread
-    static_assert(NT == 512 || NT == 1024, "512 or 1024 threads");
-    extern __shared__ __align__(128) uint8_t bt_smem[];
-    __shared__ __align__(8) unsigned long long mbar[2];
-    __shared__ unsigned tmem_base_s;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, quarter = warp & 3, cg = warp >> 2;
-    const int chunk = blockIdx.y;
-    const long long r_begin = (long long)chunk * a.rows_per_chunk;
-    const long long r_end = min(a.nrows, r_begin + a.rows_per_chunk);
-    const int nrows = (int)(r_end - r_begin);
-    uint8_t* const As = bt_smem;
-    uint8_t* const Bs = bt_smem + 2 * BT_TILE_BYTES;
-    unsigned* const raw = reinterpret_cast<unsigned*>(bt_smem + 4 * BT_TILE_BYTES);       // [2][1024] packed words, a thread's own WPT
-    const unsigned As_addr = (unsigned)__cvta_generic_to_shared(As), Bs_addr = (unsigned)__cvta_generic_to_shared(Bs);
-    const unsigned mbar_addr = (unsigned)__cvta_generic_to_shared(&mbar[0]);
-
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((unsigned)__cvta_generic_to_shared(&tmem_base_s)) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
-    if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_addr));
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar_addr + 8));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    // ---- A tiles: 256 queries x 256 bytes of +1 / -1, canonical K-major layout; consecutive lanes write consecutive rows ----
-#pragma unroll
-    for (int j = 0; j < 2048 / NT; j++) {
-        const int i = tid + NT * j;
-        const int r8 = i & 7, wd = (i >> 3) & 7, row256 = (i >> 6) * 8 + r8;
-        const int qi = blockIdx.x * BT_QTILE + row256;
-        const bool ok = qi < a.nq;
-        const unsigned w = ok ? reinterpret_cast<const unsigned*>(a.q)[(long long)qi * 8 + wd] : 0u;
-        uint4 lo, hi;
-        lo.x = bm_spread_pm1(w & 15u); lo.y = bm_spread_pm1((w >> 4) & 15u); lo.z = bm_spread_pm1((w >> 8) & 15u); lo.w = bm_spread_pm1((w >> 12) & 15u);
-        hi.x = bm_spread_pm1((w >> 16) & 15u); hi.y = bm_spread_pm1((w >> 20) & 15u); hi.z = bm_spread_pm1((w >> 24) & 15u); hi.w = bm_spread_pm1(w >> 28);
-        if (!ok) { lo = make_uint4(0, 0, 0, 0); hi = lo; }
-        uint8_t* dst = As + (row256 >> 7) * BT_TILE_BYTES + bt_off(row256 & 127, wd * 32);
-        *reinterpret_cast<uint4*>(dst) = lo;
-        *reinterpret_cast<uint4*>(dst + 128) = hi;
-    }
-    // ---- this thread's query rows: row = 32 quarter + lane of both tiles; it sees columns [COLS cg, COLS cg + COLS) of every stage ----
-    const int row = 32 * quarter + lane;
-    int pq[2], thr[2];
-    unsigned k1[2], k2[2];
-#pragma unroll
-    for (int mt = 0; mt < 2; mt++) {
-        const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
-        int pc = 0;
-        if (qi < a.nq) {
-            const uint4 v0 = a.q[2 * qi], v1 = a.q[2 * qi + 1];
-            pc = __popc(v0.x) + __popc(v0.y) + __popc(v0.z) + __popc(v0.w) + __popc(v1.x) + __popc(v1.y) + __popc(v1.z) + __popc(v1.w);
-        }
-        pq[mt] = pc; k1[mt] = 0xffffffffu; k2[mt] = 0xffffffffu;
-        thr[mt] = qi < a.nq ? pc - 511 : 0x7fffffff;
-    }
-    // ---- packed rows: every thread copies and later expands its own WPT words; 8 consecutive lanes take 8 consecutive rows ----
-    const int my_row = (tid >> (WPT == 1 ? 6 : 5)) * 8 + (tid & 7), my_wd = WPT == 1 ? (tid >> 3) & 7 : 2 * ((tid >> 3) & 3);
-    const int nstages = (nrows + BT_ROWS - 1) / BT_ROWS;
-    auto load_stage = [&](int s, int buf) {
-        const long long grow = r_begin + (long long)s * BT_ROWS + my_row;
-        const unsigned* src = reinterpret_cast<const unsigned*>(a.db) + (grow < r_end ? grow * 8 + my_wd : 0);
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(&raw[buf * 1024 + tid * WPT]);
-        const int bytes = grow < r_end ? 4 * WPT : 0;
-        if (WPT == 1) asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(bytes));
-        else asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(bytes));
-        asm volatile("cp.async.commit_group;");
-    };
-    if (nstages > 0) load_stage(0, 0);
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                          // the A tiles are read by the tensor core
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const unsigned tmem = tmem_base_s;
-    // instruction descriptor: D = s32 (2 << 4), A = s8 (1 << 7), B = u8 (0 << 10), both K-major, N = 128 (16 << 17), M = 128 (8 << 24)
-    constexpr unsigned IDESC = (2u << 4) | (1u << 7) | (16u << 17) | (8u << 24);
-    const unsigned long long adesc0 = bt_desc(As_addr), bdesc0 = bt_desc(Bs_addr);
-
-    for (int it = 0; it <= nstages; it++) {
-        const int buf = it & 1;
-        if (it < nstages) {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-            unsigned wv[WPT];
-#pragma unroll
-            for (int j = 0; j < WPT; j++) wv[j] = raw[buf * 1024 + tid * WPT + j];
-            if (it + 1 < nstages) load_stage(it + 1, buf ^ 1);
-            uint8_t* dst = Bs + buf * BT_TILE_BYTES + bt_off(my_row, my_wd * 32);
-#pragma unroll
-            for (int j = 0; j < WPT; j++) {
-                const unsigned w = wv[j];
-                *reinterpret_cast<uint4*>(dst + 256 * j) = make_uint4(bm_spread01(w & 15u), bm_spread01((w >> 4) & 15u), bm_spread01((w >> 8) & 15u), bm_spread01((w >> 12) & 15u));
-                *reinterpret_cast<uint4*>(dst + 256 * j + 128) = make_uint4(bm_spread01((w >> 16) & 15u), bm_spread01((w >> 20) & 15u), bm_spread01((w >> 24) & 15u), bm_spread01(w >> 28));
-            }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        }
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        if (it < nstages && tid == 0) {
-            // descriptors differ only in the start-address field (16-byte units): + 2048 per tile, + 16 per k-step
-            const unsigned long long bd0 = bdesc0 + (unsigned long long)(buf * (BT_TILE_BYTES >> 4));
-#pragma unroll
-            for (int mt = 0; mt < 2; mt++) {
-#pragma unroll
-                for (int ks = 0; ks < 8; ks++) {
-                    const unsigned long long ad = adesc0 + (unsigned long long)(mt * (BT_TILE_BYTES >> 4) + ks * 16), bd = bd0 + (unsigned long long)(ks * 16);
-                    if (ks == 0)
-                        asm volatile("{ .reg .pred p; setp.ne.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
-                                     ::"r"(tmem + (unsigned)((buf * 2 + mt) * 128)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
-                    else
-                        asm volatile("{ .reg .pred p; setp.eq.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
-                                     ::"r"(tmem + (unsigned)((buf * 2 + mt) * 128)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
-                }
-            }
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mbar_addr + 8u * buf) : "memory");
-        }
-        if (it >= 1) {
-            const int e = it - 1, eb = e & 1;
-            bt_wait(mbar_addr + 8u * eb, (unsigned)((e >> 1) & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int cbase = e * BT_ROWS + COLS * cg;                 // chunk row of this thread's first column
-            int v[2][COLS];
-#pragma unroll
-            for (int mt = 0; mt < 2; mt++) {
-                const unsigned ta = tmem + ((unsigned)(32 * quarter) << 16) + (unsigned)((eb * 2 + mt) * 128 + COLS * cg);
-                if (COLS == 32) { BT_LD32(v[mt], ta); } else { BT_LD16(v[mt], ta); }
-            }
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-            for (int mt = 0; mt < 2; mt++) {
-                int m = __vimax3_s32(v[mt][0], v[mt][1], v[mt][2]);
-#pragma unroll
-                for (int c = 3; c + 1 < COLS; c += 2) m = __vimax3_s32(m, v[mt][c], v[mt][c + 1]);
-                m = max(m, v[mt][COLS - 1]);
-                if (m >= thr[mt]) {
-#pragma unroll
-                    for (int c = 0; c < COLS; c++) {
-                        const int idx = cbase + c;
-                        if (v[mt][c] >= thr[mt] && idx < nrows) {
-                            const unsigned key = ((unsigned)(pq[mt] - v[mt][c]) << BF_IDX_BITS) | (unsigned)idx;
-                            k2[mt] = min(k2[mt], max(k1[mt], key));
-                            k1[mt] = min(k1[mt], key);
-                            thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
-                        }
-                    }
-                }
-            }
-        }
-    }
-    // ---- the CG warps that share a query row (column groups) merge through shared memory (the B tiles are free now); release TMEM ----
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    unsigned* const scratch = reinterpret_cast<unsigned*>(Bs);         // [CG][2][128][2]
-#pragma unroll
-    for (int mt = 0; mt < 2; mt++) { scratch[((cg * 2 + mt) * 128 + row) * 2] = k1[mt]; scratch[((cg * 2 + mt) * 128 + row) * 2 + 1] = k2[mt]; }
-    __syncthreads();
-    if (cg == 0) {
-#pragma unroll
-        for (int mt = 0; mt < 2; mt++) {
-            unsigned x1 = k1[mt], x2 = k2[mt];
-            for (int g = 1; g < CG; g++) {
-                const unsigned y1 = scratch[((g * 2 + mt) * 128 + row) * 2], y2 = scratch[((g * 2 + mt) * 128 + row) * 2 + 1];
-                x2 = min(max(x1, y1), min(x2, y2));
-                x1 = min(x1, y1);
-            }
-            const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
-            if (qi < a.nq) {
-                a.part_k1[(long long)chunk * a.nq + qi] = x1;
-                a.part_k2[(long long)chunk * a.nq + qi] = x2;
-            }
-        }
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
-    }
-}
-
-// ------------------------------------------------------------------------------------------------------
-// Warp-specialised version of the tcgen05 kernel (variant 4): the three activities of a stage run as independent pipelines
-// coupled only by mbarriers, so no warp waits at a block barrier for the slowest activity:
-//   * 8 PRODUCER warps copy the packed rows (cp.async, own slots) and expand them into a ring of BW_STAGES B tiles;
-//     full[s] <- one arrive per producer warp;  they reuse a tile when empty[s] <- tcgen05.commit of the MMAs that read it;
-//   * 1 MMA warp (one lane) waits full[s] and accempty[b], issues the 16 tcgen05.mma of the stage into accumulator buffer b and
-//     commits them to empty[s] and accfull[b];
-//   * 16 CONSUMER warps (4 per TMEM lane quarter, 32 columns each) wait accfull[b], pull the accumulators into registers
-//     (tcgen05.ld), release the buffer (accempty[b] <- one arrive per consumer warp) and only then filter / update the top-2.
-// ------------------------------------------------------------------------------------------------------
-#ifndef BW_STAGES_X
-#define BW_STAGES_X 3
-#endif
-#ifndef BW_PGROUPS_X
-#define BW_PGROUPS_X 2
-#endif
-constexpr int BW_STAGES = BW_STAGES_X;
-constexpr int BW_PGROUPS = BW_PGROUPS_X;                  // producer groups working on alternate stages
 constexpr int BW_PROD_WARPS = 8, BW_CONS_WARPS = 16;
 constexpr int BW_THREADS = 32 * (BW_PROD_WARPS + BW_CONS_WARPS + 1);                 // 800
-constexpr int BW_SMEM = (2 + BW_STAGES) * BT_TILE_BYTES + BW_PGROUPS * 2 * BT_ROWS * 32;         // A0 A1 | B ring | packed rows x 2: 172032 B
 
 __device__ __forceinline__ void bw_arrive(unsigned mbar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(mbar) : "memory");
 }
-
-__global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcws_kernel(const __grid_constant__ BfArgs a)
-{
-    extern __shared__ __align__(128) uint8_t bt_smem[];
-    __shared__ __align__(8) unsigned long long bars[2 * BW_STAGES + 4];      // full[S] | empty[S] | accfull[2] | accempty[2]
-    __shared__ unsigned tmem_base_s;
-    __shared__ int thr_s[2 * 128];                                          // per query row: tightest threshold any of its four consumer threads holds
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int chunk = blockIdx.y;
-    const long long r_begin = (long long)chunk * a.rows_per_chunk;
-    const long long r_end = min(a.nrows, r_begin + a.rows_per_chunk);
-    const int nrows = (int)(r_end - r_begin);
-    const int nstages = (nrows + BT_ROWS - 1) / BT_ROWS;
-    uint8_t* const As = bt_smem;
-    uint8_t* const Bs = bt_smem + 2 * BT_TILE_BYTES;
-    uint4* const raw = reinterpret_cast<uint4*>(bt_smem + (2 + BW_STAGES) * BT_TILE_BYTES);      // [2][256], a producer thread's own slot
-    const unsigned As_addr = (unsigned)__cvta_generic_to_shared(As), Bs_addr = (unsigned)__cvta_generic_to_shared(Bs);
-    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
-    const unsigned full0 = bar0, empty0 = bar0 + 8 * BW_STAGES, accfull0 = bar0 + 16 * BW_STAGES, accempty0 = accfull0 + 16;
-
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((unsigned)__cvta_generic_to_shared(&tmem_base_s)) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    }
-    if (tid == 0) {
-        for (int s = 0; s < BW_STAGES; s++) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(BW_PROD_WARPS / BW_PGROUPS));
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty0 + 8 * s));
-        }
-        for (int b = 0; b < 2; b++) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(accfull0 + 8 * b));
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(accempty0 + 8 * b), "r"(BW_CONS_WARPS));
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (tid < 256) thr_s[tid] = -100000;
-    // ---- A tiles: 256 queries x 256 bytes of +1 / -1, canonical K-major layout; consecutive lanes write consecutive rows ----
-    for (int i = tid; i < 2048; i += BW_THREADS) {
-        const int r8 = i & 7, wd = (i >> 3) & 7, row256 = (i >> 6) * 8 + r8;
-        const int qi = blockIdx.x * BT_QTILE + row256;
-        const bool ok = qi < a.nq;
-        const unsigned w = ok ? reinterpret_cast<const unsigned*>(a.q)[(long long)qi * 8 + wd] : 0u;
-        uint4 lo, hi;
-        lo.x = bm_spread_pm1(w & 15u); lo.y = bm_spread_pm1((w >> 4) & 15u); lo.z = bm_spread_pm1((w >> 8) & 15u); lo.w = bm_spread_pm1((w >> 12) & 15u);
-        hi.x = bm_spread_pm1((w >> 16) & 15u); hi.y = bm_spread_pm1((w >> 20) & 15u); hi.z = bm_spread_pm1((w >> 24) & 15u); hi.w = bm_spread_pm1(w >> 28);
-        if (!ok) { lo = make_uint4(0, 0, 0, 0); hi = lo; }
-        uint8_t* dst = As + (row256 >> 7) * BT_TILE_BYTES + bt_off(row256 & 127, wd * 32);
-        *reinterpret_cast<uint4*>(dst) = lo;
-        *reinterpret_cast<uint4*>(dst + 128) = hi;
-    }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");                          // the A tiles are read by the tensor core
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const unsigned tmem = tmem_base_s;
-    constexpr unsigned IDESC = (2u << 4) | (1u << 7) | (16u << 17) | (8u << 24);
-
-    int pq[2] = {0, 0}, thr[2] = {0x7fffffff, 0x7fffffff};
-    unsigned k1[2] = {0xffffffffu, 0xffffffffu}, k2[2] = {0xffffffffu, 0xffffffffu};
-    const int quarter = warp & 3, cg = (warp - BW_PROD_WARPS) >> 2, row = 32 * quarter + lane;
-
-    if (warp < BW_PROD_WARPS) {
-        // ================= producers: packed rows -> B ring; BW_PGROUPS groups of warps take alternate stages =================
-        constexpr int GT = 32 * BW_PROD_WARPS / BW_PGROUPS;      // threads per group
-        constexpr int U4 = 256 / GT;                             // 16-byte pieces per thread and stage (1: half a row, 2: a whole row)
-        const int pg = tid / GT, t = tid % GT;
-        const int my_row = U4 == 1 ? (t & ~15) / 2 + (t & 7) : (t >> 3) * 8 + (t & 7), my_half = U4 == 1 ? (t >> 3) & 1 : 0;
-        uint4* const myraw = raw + pg * 512;                      // [2][GT * U4] own slots
-        auto load_stage = [&](int s, int buf) {
-            const long long grow = r_begin + (long long)s * BT_ROWS + my_row;
-#pragma unroll
-            for (int u = 0; u < U4; u++) {
-                const uint4* src = a.db + (grow < r_end ? grow * 2 + my_half + u : 0);
-                const unsigned dst = (unsigned)__cvta_generic_to_shared(&myraw[buf * 256 + t * U4 + u]);
-                const int bytes = grow < r_end ? 16 : 0;
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
-            }
-            asm volatile("cp.async.commit_group;");
-        };
-        if (pg < nstages) load_stage(pg, 0);
-        int k = 0;                                               // this group's stage counter
-        for (int it = pg; it < nstages; it += BW_PGROUPS, k++) {
-            const int s = it % BW_STAGES, n = it / BW_STAGES;
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-            uint4 rv[U4];
-#pragma unroll
-            for (int u = 0; u < U4; u++) rv[u] = myraw[(k & 1) * 256 + t * U4 + u];
-            if (it + BW_PGROUPS < nstages) load_stage(it + BW_PGROUPS, (k + 1) & 1);
-            if (it >= BW_STAGES) bt_wait(empty0 + 8 * s, (unsigned)((n - 1) & 1));      // the MMAs that read this tile have completed
-            uint8_t* dst = Bs + s * BT_TILE_BYTES + bt_off(my_row, my_half * 128);
-#pragma unroll
-            for (int u = 0; u < U4; u++) {
-                const unsigned wv[4] = {rv[u].x, rv[u].y, rv[u].z, rv[u].w};
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const unsigned w = wv[j];
-                    *reinterpret_cast<uint4*>(dst + 1024 * u + 256 * j) = make_uint4(bm_spread01(w & 15u), bm_spread01((w >> 4) & 15u), bm_spread01((w >> 8) & 15u), bm_spread01((w >> 12) & 15u));
-                    *reinterpret_cast<uint4*>(dst + 1024 * u + 256 * j + 128) = make_uint4(bm_spread01((w >> 16) & 15u), bm_spread01((w >> 20) & 15u), bm_spread01((w >> 24) & 15u), bm_spread01(w >> 28));
-                }
-            }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) bw_arrive(full0 + 8 * s);
-        }
-    } else if (warp == BW_PROD_WARPS + BW_CONS_WARPS) {
-        // ================= MMA issuer =================
-        if (lane == 0) {
-            const unsigned long long adesc0 = bt_desc(As_addr), bdesc0 = bt_desc(Bs_addr);
-            for (int it = 0; it < nstages; it++) {
-                const int s = it % BW_STAGES, n = it / BW_STAGES, b = it & 1, m = it >> 1;
-                bt_wait(full0 + 8 * s, (unsigned)(n & 1));
-                if (it >= 2) bt_wait(accempty0 + 8 * b, (unsigned)((m - 1) & 1));
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const unsigned long long bd0 = bdesc0 + (unsigned long long)(s * (BT_TILE_BYTES >> 4));
-#pragma unroll
-                for (int mt = 0; mt < 2; mt++) {
-#pragma unroll
-                    for (int ks = 0; ks < 8; ks++) {
-                        const unsigned long long ad = adesc0 + (unsigned long long)(mt * (BT_TILE_BYTES >> 4) + ks * 16), bd = bd0 + (unsigned long long)(ks * 16);
-                        if (ks == 0)
-                            asm volatile("{ .reg .pred p; setp.ne.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
-                                         ::"r"(tmem + (unsigned)((b * 2 + mt) * 128)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
-                        else
-                            asm volatile("{ .reg .pred p; setp.eq.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
-                                         ::"r"(tmem + (unsigned)((b * 2 + mt) * 128)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
-                    }
-                }
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(empty0 + 8u * s) : "memory");
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(accfull0 + 8u * b) : "memory");
-            }
-        }
-    } else {
-        // ================= consumers: accumulators -> top-2 =================
-#pragma unroll
-        for (int mt = 0; mt < 2; mt++) {
-            const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
-            if (qi < a.nq) {
-                const uint4 v0 = a.q[2 * qi], v1 = a.q[2 * qi + 1];
-                pq[mt] = __popc(v0.x) + __popc(v0.y) + __popc(v0.z) + __popc(v0.w) + __popc(v1.x) + __popc(v1.y) + __popc(v1.z) + __popc(v1.w);
-                thr[mt] = pq[mt] - 511;
-            }
-        }
-        for (int e = 0; e < nstages; e++) {
-            const int b = e & 1, m = e >> 1;
-            bt_wait(accfull0 + 8 * b, (unsigned)(m & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            int v[2][32];
-#pragma unroll
-            for (int mt = 0; mt < 2; mt++) BT_LD32(v[mt], tmem + ((unsigned)(32 * quarter) << 16) + (unsigned)((b * 2 + mt) * 128 + 32 * cg));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) bw_arrive(accempty0 + 8 * b);                  // the buffer can be overwritten: the values are in registers
-            const int cbase = e * BT_ROWS + 32 * cg;
-#pragma unroll
-            for (int mt = 0; mt < 2; mt++) {
-                // the four threads of a row see disjoint columns; each publishes its threshold, the row uses the tightest one: an
-                // element above ANY thread's second distance cannot enter the row's top-2
-                thr[mt] = max(thr[mt], thr_s[mt * 128 + row]);
-                int gm[4];
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    int t3 = __vimax3_s32(v[mt][8 * q], v[mt][8 * q + 1], v[mt][8 * q + 2]);
-                    t3 = __vimax3_s32(t3, v[mt][8 * q + 3], v[mt][8 * q + 4]);
-                    t3 = __vimax3_s32(t3, v[mt][8 * q + 5], v[mt][8 * q + 6]);
-                    gm[q] = max(t3, v[mt][8 * q + 7]);
-                }
-                if (max(__vimax3_s32(gm[0], gm[1], gm[2]), gm[3]) >= thr[mt]) {
-#pragma unroll
-                    for (int q = 0; q < 4; q++) {
-                        if (gm[q] < thr[mt]) continue;
-#pragma unroll
-                        for (int c = 8 * q; c < 8 * q + 8; c++) {
-                            const int idx = cbase + c;
-                            if (v[mt][c] >= thr[mt] && idx < nrows) {
-                                const unsigned key = ((unsigned)(pq[mt] - v[mt][c]) << BF_IDX_BITS) | (unsigned)idx;
-                                k2[mt] = min(k2[mt], max(k1[mt], key));
-                                k1[mt] = min(k1[mt], key);
-                                thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
-                            }
-                        }
-                    }
-                    if (thr[mt] != 0x7fffffff) atomicMax(&thr_s[mt * 128 + row], thr[mt]);
-                }
-            }
-        }
-    }
-    // ---- merge the four column groups of a query row through shared memory (the B ring is free: every MMA has been consumed) ----
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    unsigned* const scratch = reinterpret_cast<unsigned*>(Bs);         // [4][2][128][2]
-    const bool consumer = warp >= BW_PROD_WARPS && warp < BW_PROD_WARPS + BW_CONS_WARPS;
-    if (consumer) {
-#pragma unroll
-        for (int mt = 0; mt < 2; mt++) { scratch[((cg * 2 + mt) * 128 + row) * 2] = k1[mt]; scratch[((cg * 2 + mt) * 128 + row) * 2 + 1] = k2[mt]; }
-    }
-    __syncthreads();
-    if (consumer && cg == 0) {
-#pragma unroll
-        for (int mt = 0; mt < 2; mt++) {
-            unsigned x1 = k1[mt], x2 = k2[mt];
-            for (int g = 1; g < 4; g++) {
-                const unsigned y1 = scratch[((g * 2 + mt) * 128 + row) * 2], y2 = scratch[((g * 2 + mt) * 128 + row) * 2 + 1];
-                x2 = min(max(x1, y1), min(x2, y2));
-                x1 = min(x1, y1);
-            }
-            const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
-            if (qi < a.nq) {
-                a.part_k1[(long long)chunk * a.nq + qi] = x1;
-                a.part_k2[(long long)chunk * a.nq + qi] = x2;
-            }
-        }
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
-    }
-}
-
-// ------------------------------------------------------------------------------------------------------
-// Variant 5: the warp-specialised kernel with N = 256 MMAs.  A stage is 256 database rows (B tile 64 KB, ring of two); each query
-// tile has ONE 256-column accumulator, so the two tiles of a stage double-buffer each other: tile 1 is multiplied while tile 0 is
-// consumed.  Shared-memory reads of the tensor core drop from 1024 to 768 bytes per row and CTA, and there are half as many stage
-// hand-overs and MMA instructions.
-// ------------------------------------------------------------------------------------------------------
 constexpr int BN_ROWS = 256, BN_STAGES = 2;
 constexpr int BN_BTILE = BN_ROWS * 256;
 constexpr int BN_SMEM = 2 * BT_TILE_BYTES + BN_STAGES * BN_BTILE + 2 * BN_ROWS * 32;     // 212992 B

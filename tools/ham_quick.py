@@ -10,7 +10,7 @@ q = torch.randint(0, 256, (NQ, 32), dtype=torch.uint8, device="cuda", generator=
 q[: NQ // 2] = db[torch.randint(0, ROWS, (NQ // 2,), device="cuda", generator=g)]
 q[: NQ // 2, :3] ^= 0x55
 res = {}
-for var in (os.environ.get("ORBB_BF_VARIANT", "5"), "1"):
+for var in (os.environ.get("ORBB_BF_VARIANT", "3"), "1"):
     os.environ["ORBB_BF_VARIANT"] = var
     D = orbb200.DescriptorDB(ROWS); D.append_device(db.data_ptr(), ROWS)
     d1 = torch.empty(NQ, dtype=torch.int32, device="cuda"); i1 = torch.empty(NQ, dtype=torch.int64, device="cuda"); d2 = torch.empty(NQ, dtype=torch.int32, device="cuda")
