@@ -78,7 +78,7 @@ std::vector<cv::Mat> Converter::toDescriptorVector(const cv::Mat& Descriptors)
 
 // ---- call trace (linker --wrap) --------------------------------------------------------------------------------------------
 namespace {
-struct TraceEvent { int kind; float x, y, r; int a, b; const void* obj; };   // kind 0 Frame::GFA, 1 KeyFrame::GFA, 2 KeyFrame::GetMapPoint
+struct TraceEvent { int kind; float x, y, r; int a, b; const void* obj; };   // kind 0 Frame::GFA, 1 KeyFrame::GFA, 2 KeyFrame::GetMapPoint, 3 MapPoint::GetWorldPos, 4 MapPoint::isBad, 5 MapPoint::PredictScale
 std::vector<TraceEvent> g_trace;
 bool g_trace_on = false;
 }
@@ -100,6 +100,36 @@ MapPoint* __wrap__ZN9ORB_SLAM28KeyFrame11GetMapPointERKm(KeyFrame* self, const s
 {
     if (g_trace_on) g_trace.push_back(TraceEvent{2, 0, 0, 0, (int)idx, 0, self});
     return __real__ZN9ORB_SLAM28KeyFrame11GetMapPointERKm(self, idx);
+}
+// MapPoint::GetWorldPos / isBad: called once per candidate point before its projection, so the event that precedes a
+// GetFeaturesInArea event names the MapPoint the window belongs to (kind 3 / 4, obj = the MapPoint).
+cv::Mat __real__ZN9ORB_SLAM28MapPoint11GetWorldPosEv(MapPoint*);
+cv::Mat __wrap__ZN9ORB_SLAM28MapPoint11GetWorldPosEv(MapPoint* self)
+{
+    if (g_trace_on) g_trace.push_back(TraceEvent{3, 0, 0, 0, 0, 0, self});
+    return __real__ZN9ORB_SLAM28MapPoint11GetWorldPosEv(self);
+}
+// MapPoint::PredictScale: kind 5, x = the distance passed in, a = the level returned (the [p-1, p] gate of the KeyFrame variants
+// is applied inside ORBmatcher.cpp's candidate loop and is otherwise invisible)
+int __real__ZN9ORB_SLAM28MapPoint12PredictScaleERKfPNS_5FrameE(MapPoint*, const float&, Frame*);
+int __wrap__ZN9ORB_SLAM28MapPoint12PredictScaleERKfPNS_5FrameE(MapPoint* self, const float& d, Frame* f)
+{
+    const int r = __real__ZN9ORB_SLAM28MapPoint12PredictScaleERKfPNS_5FrameE(self, d, f);
+    if (g_trace_on) g_trace.push_back(TraceEvent{5, d, 0, 0, r, 0, self});
+    return r;
+}
+int __real__ZN9ORB_SLAM28MapPoint12PredictScaleERKfPNS_8KeyFrameE(MapPoint*, const float&, KeyFrame*);
+int __wrap__ZN9ORB_SLAM28MapPoint12PredictScaleERKfPNS_8KeyFrameE(MapPoint* self, const float& d, KeyFrame* f)
+{
+    const int r = __real__ZN9ORB_SLAM28MapPoint12PredictScaleERKfPNS_8KeyFrameE(self, d, f);
+    if (g_trace_on) g_trace.push_back(TraceEvent{5, d, 0, 0, r, 0, self});
+    return r;
+}
+bool __real__ZN9ORB_SLAM28MapPoint5isBadEv(MapPoint*);
+bool __wrap__ZN9ORB_SLAM28MapPoint5isBadEv(MapPoint* self)
+{
+    if (g_trace_on) g_trace.push_back(TraceEvent{4, 0, 0, 0, 0, 0, self});
+    return __real__ZN9ORB_SLAM28MapPoint5isBadEv(self);
 }
 }
 
@@ -320,6 +350,7 @@ void* rm_mappoints_create(void* map, void* refkf, int n, const float* pos, const
     }
     return s;
 }
+void rm_mappoints_ptrs(void* s, uint64_t* out) { MapPointSet* m = (MapPointSet*)s; for (size_t i = 0; i < m->v.size(); i++) out[i] = (uint64_t)(uintptr_t)m->v[i]; }
 int rm_mappoints_n(void* s) { return (int)((MapPointSet*)s)->v.size(); }
 // what Frame::isInFrustum (Frame.cpp:305-372) leaves on each MapPoint for SearchByProjection(F, vpMapPoints, th)
 void rm_mappoints_set_track(void* sp, const uint8_t* inView, const float* projX, const float* projY, const float* projXR,
