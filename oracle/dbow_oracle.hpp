@@ -8,8 +8,10 @@
 //   ORB-SLAM2/Thirdparty/DBoW2/DBoW2/BowVector.cpp           addWeight, addIfNotExist, normalize
 //   ORB-SLAM2/Thirdparty/DBoW2/DBoW2/FeatureVector.cpp       addFeature
 //   ORB-SLAM2/Thirdparty/DBoW2/DBoW2/FORB.cpp :82-102        distance (twin of ORBmatcher::DescriptorDistance)
-// The reference ships no vocabulary file (Vocabulary/ holds only bin_vocabulary.cpp) and no tests: parity for this row is
-// pinned by a second, independent numpy statement in tests/ on seeded synthetic trees ("parity unpinned" by the reference).
+// PINNED: the reference ships no vocabulary file (Vocabulary/ holds only bin_vocabulary.cpp) and no tests, so the vendored DBoW2 itself
+// was compiled unmodified (oracle/_ref/liborb_refmatch.so) and run on a seeded vocabulary written in its loadFromTextFile format:
+// tests/golden/ref_match.npz cases "vocab", "bow", "triang_*" (tests/test_ref_match_golden.py); a second, independent numpy statement
+// in tests/test_vocab.py covers more tree shapes.
 #pragma once
 #include <cstdint>
 #include <cmath>

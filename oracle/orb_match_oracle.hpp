@@ -4,9 +4,11 @@
 //   ORB-SLAM2/src/ORBmatcher.cpp  :37-39 (constants) :63-155 :166-190 :205-348 :604-743 (SearchByBoW) :755-927 (SearchForTriangulation) :352-472 :962-1251 (Fuse) :1253-1500 (SearchBySim3) :1661-1789 :474-590 :1506-1659 :1792-1854
 //   ORB-SLAM2/src/Frame.cpp       :241-257 :379-444 :540-748
 //   ORB-SLAM2/src/MapPoint.cpp    :302-380 (ComputeDistinctiveDescriptors)
-// ORBmatcher.cpp / Frame.cpp cannot be compiled here (they pull in KeyFrame/MapPoint/DBoW2/OpenCV/Eigen),
-// and the reference has no tests or golden vectors for them: parity for this half is "unpinned" beyond
-// DescriptorDistance (checked against numpy popcount) and hand-built known-answer cases in tests/.
+// PINNED: the reference ships no tests or golden vectors for these functions, so the reference itself was run here —
+// ORBmatcher.cpp, Frame.cpp, KeyFrame.cpp, MapPoint.cpp, Map.cpp and the vendored DBoW2 compile UNMODIFIED over oracle/cvshim into
+// oracle/_ref/liborb_refmatch.so (oracle/Makefile `refmatch`, harness oracle/refmatch_capi.cpp) — and its outputs on seeded scenes
+// are committed as tests/golden/ref_match.npz (generator tests/golden/make_golden_match.py).  tests/test_ref_match_golden.py checks
+// every function below against that fixture bit for bit (and the CUDA path against the same fixture under -m gpu).
 // MapPoint*/Frame bookkeeping is flattened to plain arrays; the control flow follows the reference.
 #pragma once
 #include <cstdint>

@@ -33,6 +33,8 @@ def build(force=False):
         rsrcs = [s for s in rsrcs if os.path.exists(s)]
         if rsrcs and (force or not os.path.exists(ref) or any(os.path.getmtime(s) > os.path.getmtime(ref) for s in rsrcs)):
             subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
+        import pyrefmatch                       # the matcher half of the reference (oracle/_ref/liborb_refmatch.so)
+        pyrefmatch.build(force)
     return so
 
 

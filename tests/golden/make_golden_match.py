@@ -167,9 +167,10 @@ def stereo_scene(seed, nf=1200, shift=(4, 0)):
     return Fc, Fl, R.Frame.statics()
 
 
-def put_frame(case, name, F, st):
-    put(case, **{f"{name}_kps": F.kps, f"{name}_kps_un": F.kps_un, f"{name}_desc": F.desc, f"{name}_u_right": F.u_right,
-                 f"{name}_depth": F.depth})
+def put_frame(case, name, F, st, raw=False):
+    put(case, **{f"{name}_kps_un": F.kps_un, f"{name}_desc": F.desc, f"{name}_u_right": F.u_right})
+    if raw:
+        put(case, **{f"{name}_kps": F.kps})
     put(case, bounds=np.array([st["min_x"], st["min_y"], st["max_x"], st["max_y"]], f32), scale=F.scale, inv_sigma2=F.inv_sigma2,
         sigma2=F.sigma2)
 
@@ -202,7 +203,7 @@ def case_frame_basics():
     """f1 / a15: UndistortKeyPoints, ComputeImageBounds, AssignFeaturesToGrid, GetFeaturesInArea of the reference's Frame."""
     cur, last, Fc, Fl, st = mono_scene(101)
     rng = np.random.default_rng(1)
-    put_frame("frame", "f", Fc, st)
+    put_frame("frame", "f", Fc, st, raw=True)
     off, idx = Fc.grid()
     nwin = 400
     win = np.zeros((nwin, 5), f32)
@@ -557,7 +558,213 @@ def case_initialization():
         assert nm > 100, (name, nm)
 
 
-CASES = [case_frame_basics, case_stereo, case_local_points, case_last_frame, case_reloc, case_loop, case_fuse, case_sim3, case_initialization]
+
+# ---- vocabulary, BoW, triangulation, distinctive descriptors -----------------------------------------------------------------------
+def build_vocab(pool, k, L, rng, stop_fraction=0.03):
+    """A ragged vocabulary tree over real descriptors, in loadFromTextFile order: a node's children are k of the descriptors assigned
+    to it (padded with perturbed copies), the pool is split by nearest child, nodes with < 2 descriptors become leaves early."""
+    bits = np.unpackbits(pool, axis=1).astype(np.int16)
+    parent = [0]; leaf = [0]; desc = [np.zeros(32, np.uint8)]; weight = [0.0]
+    frontier = [(0, np.arange(len(pool)), 0)]
+    while frontier:
+        nxt = []
+        for node, members, lvl in frontier:
+            cent = []
+            pick = rng.permutation(members)[:k] if len(members) else []
+            for m in pick:
+                cent.append(pool[m].copy())
+            while len(cent) < k:
+                d = (cent[0] if cent else desc[node]).copy()
+                for b in rng.integers(0, 256, 20):
+                    d[b >> 3] ^= np.uint8(1 << (b & 7))
+                cent.append(d)
+            cb = np.unpackbits(np.stack(cent), axis=1).astype(np.int16)
+            assign = np.argmin((bits[members][:, None, :] != cb[None, :, :]).sum(2), axis=1) if len(members) else np.zeros(0, np.int64)
+            for c in range(k):
+                nid = len(parent)
+                mem = members[assign == c]
+                is_leaf = lvl + 1 == L or (lvl + 1 >= 2 and len(mem) < 2)
+                parent.append(node); desc.append(cent[c]); leaf.append(1 if is_leaf else 0)
+                weight.append(0.0 if not is_leaf else (0.0 if rng.random() < stop_fraction else float(rng.uniform(0.5, 9.5))))
+                if not is_leaf:
+                    nxt.append((nid, mem, lvl + 1))
+        frontier = nxt
+    return np.asarray(parent, np.int32), np.asarray(leaf, np.uint8), np.stack(desc).astype(np.uint8), np.asarray(weight, np.float64)
+
+
+def write_vocab_txt(path, k, L, parent, leaf, desc, weight):
+    """The text format of TemplatedVocabulary::loadFromTextFile (:1362-1448): header "k L scoring weighting", then one line per node
+    "parent isLeaf d0 .. d31 weight"; no trailing newline (the loader's eof loop would add a bogus node)."""
+    lines = [f"{k} {L} 0 0"]
+    for i in range(1, len(parent)):
+        lines.append(f"{parent[i]} {leaf[i]} " + " ".join(str(int(b)) for b in desc[i]) + f" {float(weight[i])!r}")
+    with open(path, "w") as f:
+        f.write("\n".join(lines))
+
+
+def bow_scene(seed, stereo, k=4, L=6):
+    """Frames with a vocabulary built from their own descriptors; returns the frames (BoW computed by the reference) and the tree."""
+    rng = np.random.default_rng(seed)
+    if stereo:
+        Fc0, Fl0, _ = stereo_scene(seed)
+    else:
+        _, _, Fc0, Fl0, _ = mono_scene(seed)
+    pool = np.concatenate([Fc0.desc, Fl0.desc])
+    parent, leaf, desc, weight = build_vocab(pool, k, L, rng)
+    tmp = os.path.join(tempfile.gettempdir(), f"orbb_voc_{seed}.txt")
+    write_vocab_txt(tmp, k, L, parent, leaf, desc, weight)
+    voc = R.Vocabulary(tmp)
+    assert voc.size() == int(leaf.sum())
+    return voc, (k, L, parent, leaf, desc, weight), rng
+
+
+def frames_with_voc(seed, stereo, voc):
+    R.reset()
+    if stereo:
+        L_, Rt = synth_stereo(752 + 16, 480 + 16, seed)
+        crop = lambda im, dx, dy: im[8 + dy:488 + dy, 8 + dx:760 + dx].copy()
+        exL, exR = R.Extractor(1200), R.Extractor(1200)
+        Fc = R.Frame.stereo(crop(L_, 0, 0), crop(Rt, 0, 0), exL, exR, voc, STEREO_K4, [0, 0, 0, 0], STEREO_BF)
+        Fl = R.Frame.stereo(crop(L_, 4, 0), crop(Rt, 4, 0), exL, exR, voc, STEREO_K4, [0, 0, 0, 0], STEREO_BF)
+    else:
+        big = synth(640 + 16, 480 + 16, seed)
+        ex = R.Extractor(1000)
+        Fc = R.Frame.mono(big[8:488, 8:648].copy(), ex, voc, MONO_K4, MONO_DIST)
+        Fl = R.Frame.mono(big[9:489, 11:651].copy(), ex, voc, MONO_K4, MONO_DIST)
+    return Fc, Fl, R.Frame.statics()
+
+
+def put_fv(case, name, bow):
+    ids, vals, fn, fo, ff = bow
+    put(case, **{f"{name}_bow_ids": ids, f"{name}_bow_vals": vals, f"{name}_fv_nodes": fn, f"{name}_fv_off": fo, f"{name}_fv_feat": ff})
+
+
+def case_vocab():
+    """f2: TemplatedVocabulary::transform (single feature, several levelsup) and Frame::ComputeBoW (transform of a whole frame)."""
+    voc, (k, L, parent, leaf, desc, weight), rng = bow_scene(111, False)
+    Fc, Fl, st = frames_with_voc(111, False, voc)
+    put("vocab", k=k, L=L, parent=parent, is_leaf=leaf, desc=desc, weight=weight, feats=Fc.desc)
+    for lu in (0, 2, 4, 7):
+        wid, w, nid = voc.transform(Fc.desc, lu)
+        put("vocab", **{f"word_lu{lu}": wid, f"weight_lu{lu}": w, f"node_lu{lu}": nid})
+    put_fv("vocab", "frame", Fc.compute_bow())
+    put_fv("vocab", "direct_lu2", voc.bow(Fc.desc, 2))
+    assert len(OUT["vocab/frame_fv_nodes"]) >= 4
+
+
+def case_bow():
+    """f2: SearchByBoW(KeyFrame*, Frame&, ...) and SearchByBoW(KeyFrame*, KeyFrame*, ...) with BoW vectors computed by the reference."""
+    voc, (k, L, parent, leaf, desc, weight), rng = bow_scene(112, False)
+    Fc, Fl, st = frames_with_voc(112, False, voc)
+    bow_c = Fc.compute_bow(); bow_l = Fl.compute_bow()
+    Fc.set_pose(pose(0, 0, 0, [0, 0, 0])); Fl.set_pose(pose(0, 0, 0, [0, 0, 0]))
+    map_ = R.Map()
+    kfl = R.KeyFrame(Fl, map_); kfc = R.KeyFrame(Fc, map_)
+    nl, nc = Fl.N, Fc.N
+    pts = R.MapPoints(map_, kfl, np.zeros((nl + nc, 3), f32), np.concatenate([Fl.desc, Fc.desc]), None, None, None, None)
+    il = np.where(rng.random(nl) < 0.8, np.arange(nl), -1).astype(np.int32)
+    ic = np.where(rng.random(nc) < 0.8, nl + np.arange(nc), -1).astype(np.int32)
+    kfl.set_mappoints(pts, il, True); kfc.set_mappoints(pts, ic, True)
+    for b in (il[il >= 0][5::40]).tolist() + (ic[ic >= 0][7::40]).tolist():
+        pts.set_bad(b)
+    bad = pts.is_bad()
+    has_l = ((il >= 0) & (bad[np.maximum(il, 0)] == 0)).astype(np.uint8)
+    has_c = ((ic >= 0) & (bad[np.maximum(ic, 0)] == 0)).astype(np.uint8)
+    put("bow", k=k, L=L, parent=parent, is_leaf=leaf, desc=desc, weight=weight, kf_desc=Fl.desc, kf_angle=Fl.kps_un["angle"], kf_has_mp=has_l,
+        f_desc=Fc.desc, f_angle=Fc.kps["angle"], f_angle_un=Fc.kps_un["angle"], f_has_mp=has_c)
+    put_fv("bow", "kf", bow_l); put_fv("bow", "f", bow_c)
+    for nnratio, check in ((0.7, True), (0.9, False)):
+        n, m = R.search_by_bow_kf_frame(kfl, Fc, pts, nnratio, check)
+        assert np.all((m == -1) | ((m >= 0) & (m < nl)))             # KeyFrame Fl's points are 0 .. nl-1 = its feature indices
+        put("bow", **{f"kf_f_matches_{int(nnratio * 10)}_{int(check)}": m, f"kf_f_n_{int(nnratio * 10)}_{int(check)}": n})
+        assert n > 100, n
+        n, m = R.search_by_bow_kf_kf(kfl, kfc, pts, nnratio, check)
+        m = np.where(m >= 0, m - nl, -1).astype(np.int32)           # KeyFrame Fc's point nl + j sits on its feature j
+        put("bow", **{f"kf_kf_matches_{int(nnratio * 10)}_{int(check)}": m, f"kf_kf_n_{int(nnratio * 10)}_{int(check)}": n})
+        assert n > 100, n
+
+
+def skew(t):
+    return np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]])
+
+
+def case_triangulation():
+    """f2: SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (:755-927) — monocular KeyFrames, and stereo ones
+    with and without bOnlyStereo.  F12 as LocalMapping::ComputeF12 builds it (K1^-T [t12]x R12 K2^-1)."""
+    for name, stereo, only in [("triang_mono", False, False), ("triang_stereo", True, False), ("triang_only_stereo", True, True)]:
+        voc, (k, L, parent, leaf, desc, weight), rng = bow_scene(113 if not stereo else 114, stereo)
+        Fc, Fl, st = frames_with_voc(113 if not stereo else 114, stereo, voc)
+        b1 = Fl.compute_bow(); b2 = Fc.compute_bow()
+        K4 = STEREO_K4 if stereo else MONO_K4
+        shift = (4, 0) if stereo else (3, 1)
+        Z = 8.0
+        T1 = pose(0, 0, 0, [0, 0, 0])
+        # Current (KF2) sees every Last (KF1) feature at +shift: camera 2 sits at -shift*Z/f of camera 1, plus a small advance so the epipole is finite
+        T2 = pose(0, 0, 0, [shift[0] * Z / K4[0], shift[1] * Z / K4[1], -0.02])
+        Fl.set_pose(T1); Fc.set_pose(T2)
+        map_ = R.Map()
+        kf1 = R.KeyFrame(Fl, map_); kf2 = R.KeyFrame(Fc, map_)
+        n1, n2 = Fl.N, Fc.N
+        pts = R.MapPoints(map_, kf1, np.zeros((n1 + n2, 3), f32), np.concatenate([Fl.desc, Fc.desc]), None, None, None, None)
+        i1 = np.where(rng.random(n1) < 0.3, np.arange(n1), -1).astype(np.int32)       # features that already have a MapPoint are skipped
+        i2 = np.where(rng.random(n2) < 0.3, n1 + np.arange(n2), -1).astype(np.int32)
+        kf1.set_mappoints(pts, i1, True); kf2.set_mappoints(pts, i2, True)
+        R1, t1, O1 = kf1.pose(); R2, t2, O2 = kf2.pose()
+        R12 = R1.astype(np.float64) @ R2.astype(np.float64).T
+        t12 = -R12 @ t2.astype(np.float64) + t1.astype(np.float64)
+        Km = np.array([[K4[0], 0, K4[2]], [0, K4[1], K4[3]], [0, 0, 1]])
+        F12 = (np.linalg.inv(Km).T @ skew(t12) @ R12 @ np.linalg.inv(Km)).astype(f32)
+        n, pairs = R.search_for_triangulation(kf1, kf2, F12, only, 0.6, False)
+        # the epipole of KeyFrame 1 in KeyFrame 2 (:763-769), float32 in the reference's order
+        C2 = (mat3(R2, O1[None, :])[0] + t2).astype(f32)
+        invz = f32(1.0) / C2[2]
+        ex = f32(f32(f32(st["fx"] * C2[0]) * invz) + st["cx"]); ey = f32(f32(f32(st["fy"] * C2[1]) * invz) + st["cy"])
+        m12 = np.full(n1, -1, np.int32); m12[pairs[:, 0]] = pairs[:, 1]
+        put(name, k=k, L=L, only_stereo=int(only), F12=F12, ex=ex, ey=ey, match12=m12, pairs=pairs, nmatches=n,
+            kf1_desc=Fl.desc, kf1_kps_un=Fl.kps_un, kf1_u_right=Fl.u_right, kf1_has_mp=(i1 >= 0).astype(np.uint8),
+            kf2_desc=Fc.desc, kf2_kps_un=Fc.kps_un, kf2_u_right=Fc.u_right, kf2_has_mp=(i2 >= 0).astype(np.uint8),
+            scale=Fc.scale, sigma2=Fc.sigma2)
+        put_fv(name, "kf1", b1); put_fv(name, "kf2", b2)
+        assert n > 40, (name, n)
+
+
+def case_distinctive():
+    """f3: MapPoint::ComputeDistinctiveDescriptors (MapPoint.cpp:302-380) on points observed in 1 .. 9 KeyFrames; rows are listed in
+    the order the reference walks mObservations (a std::map keyed by KeyFrame*, i.e. by address)."""
+    R.reset()
+    rng = np.random.default_rng(115)
+    ex = R.Extractor(500)
+    big = synth(640 + 32, 480 + 32, 115)
+    map_ = R.Map()
+    kfs = []
+    for i in range(9):
+        F = R.Frame.mono(big[8 + i:488 + i, 8 + 2 * i:648 + 2 * i].copy(), ex, None, MONO_K4, [0, 0, 0, 0])
+        F.set_pose(pose(0, 0, 0, [0, 0, 0]))
+        kfs.append((R.KeyFrame(F, map_), F))
+    npts = 300
+    pts = R.MapPoints(map_, kfs[0][0], np.zeros((npts, 3), f32), np.zeros((npts, 32), np.uint8), None, None, None, None)
+    for p in range(npts):
+        nk = int(rng.integers(1, 10))
+        for j in rng.permutation(9)[:nk]:
+            kf, F = kfs[j]
+            # the feature nearest to where the point would be in that view (views are shifted crops), or a random one (a wrong association)
+            idx = int(rng.integers(0, F.N)) if rng.random() < 0.15 else int(np.argmin((F.kps["x"] - (F.kps["x"][p % F.N] if j == 0 else kfs[0][1].kps["x"][p % kfs[0][1].N] - 2 * j)) ** 2 +
+                                                                                          (F.kps["y"] - (kfs[0][1].kps["y"][p % kfs[0][1].N] - j)) ** 2))
+            pts.add_observation(p, kf, idx)
+    kf_of = {kf.h: j for j, (kf, F) in enumerate(kfs)}
+    rows, off, want = [], [0], []
+    for p in range(npts):
+        okfs, oidx = pts.observations(p)
+        for kfp, fi in zip(okfs, oidx):
+            rows.append(kfs[kf_of[int(kfp)]][1].desc[fi])
+        off.append(len(rows))
+        want.append(pts.distinctive(p))
+    rows = np.stack(rows); want = np.stack(want)
+    put("distinctive", rows=rows, offsets=np.asarray(off, np.int64), best_desc=want)
+
+
+CASES = [case_frame_basics, case_stereo, case_local_points, case_last_frame, case_reloc, case_loop, case_fuse, case_sim3, case_initialization, case_vocab, case_bow,
+         case_triangulation, case_distinctive]
 
 
 def main():

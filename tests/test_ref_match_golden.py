@@ -140,7 +140,7 @@ def test_fixture_is_reference_generated(G):
     assert os.path.exists(os.path.join(HERE, "..", "oracle", "refmatch_capi.cpp"))
     cases = {k.split("/")[0] for k in G.files}
     for need in ("frame", "stereo", "local_points_th1", "last_frame_mono", "last_frame_fwd", "last_frame_bwd", "reloc_th10", "loop_th10",
-                 "fuse_stereo", "fuse_mono", "fuse_sim3", "sim3", "init_w100"):
+                 "fuse_stereo", "fuse_mono", "fuse_sim3", "sim3", "init_w100", "vocab", "bow", "triang_mono", "triang_only_stereo", "distinctive"):
         assert need in cases, need
 
 
@@ -252,3 +252,66 @@ def test_search_for_initialization(be, G, case):
     n, m12, pm = be.initialization(F1, F2, g["prev_in"], int(g["window"]), float(g["nnratio"]), bool(g["check_ori"]))
     assert n == int(g["nmatches"]) and np.array_equal(m12, g["matches12"])
     assert np.array_equal(np.asarray(pm, np.float32).reshape(-1, 2).view(np.uint32), g["prev_out"].view(np.uint32))
+
+
+# ---- f2 / f3: vocabulary, BoW searches, triangulation, distinctive descriptors ---------------------------------------------------
+def _mod(be):
+    return be.O if be.name == "oracle" else be.B
+
+
+def _voc(be, g):
+    m = _mod(be)
+    cls = m.OracleVocabulary if be.name == "oracle" else m.Vocabulary
+    return cls(int(g["k"]), int(g["L"]), g["parent"], g["is_leaf"], g["desc"], g["weight"])
+
+
+def _fv(g, name):
+    return (g[name + "_fv_nodes"], g[name + "_fv_off"], g[name + "_fv_feat"])
+
+
+def test_vocabulary_transform_and_compute_bow(be, G):
+    """f2: TemplatedVocabulary::transform (:1242-1285) per feature for levelsup 0 / 2 / 4 / 7 and Frame::ComputeBoW (Frame.cpp:452-459:
+    BowVector doubles and FeatureVector as the reference's loadFromTextFile'd vocabulary produced them)."""
+    g = _case(G, "vocab")
+    voc = _voc(be, g)
+    for lu in (0, 2, 4, 7):
+        wid, w, nid = voc.transform(g["feats"], lu)
+        assert np.array_equal(wid, g[f"word_lu{lu}"]) and np.array_equal(w.view(np.uint64), g[f"weight_lu{lu}"].view(np.uint64))
+        assert np.array_equal(nid, g[f"node_lu{lu}"]), lu
+    for name, lu in (("frame", 4), ("direct_lu2", 2)):
+        ids, vals, fn, fo, ff = voc.bow(g["feats"], lu)
+        assert np.array_equal(ids, g[name + "_bow_ids"]) and np.array_equal(np.asarray(vals).view(np.uint64), g[name + "_bow_vals"].view(np.uint64))
+        assert np.array_equal(fn, g[name + "_fv_nodes"]) and np.array_equal(fo, g[name + "_fv_off"]) and np.array_equal(ff, g[name + "_fv_feat"])
+
+
+@pytest.mark.parametrize("nnratio,check", [(0.7, True), (0.9, False)])
+def test_search_by_bow(be, G, nnratio, check):
+    """f2: SearchByBoW(KeyFrame*, Frame&, ...) (:205-348) and SearchByBoW(KeyFrame*, KeyFrame*, ...) (:604-743)."""
+    g = _case(G, "bow")
+    m = _mod(be)
+    tag = f"{int(nnratio * 10)}_{int(check)}"
+    out, n = m.search_by_bow(g["kf_desc"], g["kf_angle"], g["kf_has_mp"], _fv(g, "kf"), g["f_desc"], g["f_angle"], _fv(g, "f"), nnratio, check)
+    assert n == int(g["kf_f_n_" + tag]) and np.array_equal(out, g["kf_f_matches_" + tag])
+    out, n = m.search_by_bow_kf(g["kf_desc"], g["kf_angle"], g["kf_has_mp"], _fv(g, "kf"), g["f_desc"], g["f_angle_un"], g["f_has_mp"], _fv(g, "f"),
+                                nnratio, check)
+    assert n == int(g["kf_kf_n_" + tag]) and np.array_equal(out, g["kf_kf_matches_" + tag])
+
+
+@pytest.mark.parametrize("case", ["triang_mono", "triang_stereo", "triang_only_stereo"])
+def test_search_for_triangulation(be, G, case):
+    """f2: SearchForTriangulation (:755-927) with CheckDistEpipolarLine (:166-190)."""
+    g = _case(G, case)
+    m = _mod(be)
+    out, n = m.search_for_triangulation(g["kf1_desc"], g["kf1_kps_un"], g["kf1_u_right"], g["kf1_has_mp"], _fv(g, "kf1"),
+                                        g["kf2_desc"], g["kf2_kps_un"], g["kf2_u_right"], g["kf2_has_mp"], _fv(g, "kf2"),
+                                        g["F12"], float(g["ex"]), float(g["ey"]), g["scale"], g["sigma2"], bool(g["only_stereo"]), False)
+    assert n == int(g["nmatches"]) and np.array_equal(out, g["match12"])
+
+
+def test_distinctive_descriptors(be, G):
+    """f3: MapPoint::ComputeDistinctiveDescriptors (MapPoint.cpp:302-380): the descriptor the reference stored per point."""
+    g = _case(G, "distinctive")
+    row, med = _mod(be).distinctive_descriptors(g["rows"], g["offsets"])
+    off = g["offsets"]
+    got = g["rows"][off[:-1] + row]
+    assert np.all(row >= 0) and np.array_equal(got, g["best_desc"])
