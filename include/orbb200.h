@@ -311,10 +311,13 @@ int orbm_db_destroy(orbm_db* db);
 int64_t orbm_db_rows(const orbm_db* db);
 
 /* Host queries in, host results out: d1[i] best distance, idx1[i] GLOBAL row index of the best (first on ties),
- * d2[i] second-best distance (256 when the shard has < 2 rows; d1 = 256, idx1 = -1 when it has none). */
-int orbm_bf_top2(const orbm_db* db, const uint8_t* q_host, int nq, int32_t* d1_host, int64_t* idx1_host, int32_t* d2_host);
+ * d2[i] second-best distance (256 when the shard has < 2 rows; d1 = 256, idx1 = -1 when it has none).
+ * A search uses (and may grow) scratch owned by the database object, so the handle is not const and calls on ONE orbm_db must be
+ * serialised by the caller, also across streams; concurrent searchers each create their own orbm_db (rows can be shared by
+ * appending from the same device buffer). */
+int orbm_bf_top2(orbm_db* db, const uint8_t* q_host, int nq, int32_t* d1_host, int64_t* idx1_host, int32_t* d2_host);
 /* Device queries / device results, asynchronous on `stream` (cudaStream_t, may be NULL). */
-int orbm_bf_top2_device(const orbm_db* db, const uint8_t* q_dev, int nq, int32_t* d1_dev, int64_t* idx1_dev,
+int orbm_bf_top2_device(orbm_db* db, const uint8_t* q_dev, int nq, int32_t* d1_dev, int64_t* idx1_dev,
                         int32_t* d2_dev, void* stream);
 /* Merge of G per-shard results laid out [g][nq] (shards ordered by ascending row range) into the global top-2
  *  — the step that follows the NCCL all-gather.  Device pointers, asynchronous on `stream`. */

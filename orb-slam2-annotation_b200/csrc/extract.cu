@@ -203,6 +203,21 @@ static int upload_geometry(orbx_handle* h)
     return ORBB_OK;
 }
 
+// Per-shape geometry of the handle, rebuilt when the frame shape changes.  setup_geometry writes h->geom[] in place, so a rejected
+// shape (ORBB_E_BAD_SHAPE) leaves it partly overwritten: the current shape is invalidated first and only set again on success, so
+// the next call with the previous, valid shape rebuilds and re-uploads instead of running on the rejected shape's tables.
+static int ensure_geometry(orbx_handle* h, int w, int ht)
+{
+    if (w == h->cur_w && ht == h->cur_h) return ORBB_OK;
+    h->cur_w = h->cur_h = 0;
+    int rc = setup_geometry(h, w, ht, false);
+    if (rc != ORBB_OK) return rc;
+    rc = upload_geometry(h);
+    if (rc != ORBB_OK) return rc;
+    h->cur_w = w; h->cur_h = ht;
+    return ORBB_OK;
+}
+
 static std::mutex g_const_mu;
 static bool g_const_done[64] = {false};
 
@@ -410,13 +425,7 @@ extern "C" int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_sc
 static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int nframes, int w, int ht, size_t stride, size_t fstride,
                            orbx_keypoint* kps_dev0, uint8_t* desc_dev0, int32_t* counts_dev0, int capacity, int slot = 0, bool side_octree = true)
 {
-    if (w != h->cur_w || ht != h->cur_h) {
-        int rc = setup_geometry(h, w, ht, false);
-        if (rc != ORBB_OK) return rc;
-        rc = upload_geometry(h);
-        if (rc != ORBB_OK) return rc;
-        h->cur_w = w; h->cur_h = ht;
-    }
+    { const int rc = ensure_geometry(h, w, ht); if (rc != ORBB_OK) return rc; }
     const int nl = h->nlevels;
     cudaStream_t st = slot ? h->s_k[slot - 1] : h->stream;
     cudaStream_t side = h->s_side[slot], side2 = h->s_side2[slot];
@@ -646,13 +655,7 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
         if (rc != ORBB_OK) return rc;
     }
     // H2D straight into the level-0 slots of the pyramid (pitch = geom[0].pitch)
-    if (w != h->cur_w || ht != h->cur_h) {
-        int rc = setup_geometry(h, w, ht, false);
-        if (rc != ORBB_OK) return rc;
-        rc = upload_geometry(h);
-        if (rc != ORBB_OK) return rc;
-        h->cur_w = w; h->cur_h = ht;
-    }
+    { const int rc = ensure_geometry(h, w, ht); if (rc != ORBB_OK) return rc; }
     const LevelGeom& g0 = h->geom[0];
     cudaPointerAttributes attr;
     const bool pinned = cudaPointerGetAttributes(&attr, imgs_host) == cudaSuccess && attr.type == cudaMemoryTypeHost;

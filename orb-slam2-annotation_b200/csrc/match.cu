@@ -2,6 +2,7 @@
 // Replaces the Hamming core of ORB_SLAM2::ORBmatcher / Frame (reference src/ORBmatcher.cpp, src/Frame.cpp).
 #include "match_kernels.cuh"
 #include <stdlib.h>
+#include <atomic>
 
 using namespace orbb;
 
@@ -169,11 +170,24 @@ struct orbm_frame {
     DevBuf kps, desc, cell_of, cell_start, cell_items, cursor;
     // workspace of the device resolve (orbm_search_by_projection_*_device); calls on one frame are serialised by the caller
     mutable DevBuf ws_counts, ws_offs, ws_idx, ws_dist, ws_choice, ws_taker, ws_uright, ws_mp, ws_obs, ws_scalars;
+    // recorded after the copies and grid kernels of orbm_frame_create_device on the caller's stream: the host-pointer entry points
+    // run on the legacy default stream, which does not order against cudaStreamNonBlocking streams, so they wait on it first
+    cudaEvent_t ready = nullptr;
+    ~orbm_frame() { if (ready) cudaEventDestroy(ready); }
 };
+
+// Host-form entry points: block until a frame built by orbm_frame_create_device is complete.
+static int frame_wait_ready(const orbm_frame* fr)
+{
+    if (fr->ready) ORBB_CUDA(cudaEventSynchronize(fr->ready));
+    return ORBB_OK;
+}
 
 static int frame_host_copies(const orbm_frame* fr)
 {
     if (fr->host_valid) return ORBB_OK;
+    int rcw = frame_wait_ready(fr);
+    if (rcw != ORBB_OK) return rcw;
     fr->h_kps.resize(fr->n); fr->h_desc.resize((size_t)fr->n * 32);
     if (fr->n > 0) {
         ORBB_CUDA(cudaMemcpy(fr->h_kps.data(), fr->kps.p, (size_t)fr->n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost));
@@ -223,6 +237,10 @@ static int frame_create_impl(orbm_frame** out, const orbx_keypoint* kps, const u
         grid_sort_kernel<<<ceil_div(NC, 256), 256, 0, st>>>(f); ORBB_LAUNCHED();
     }
     cudaError_t e = from_host ? cudaStreamSynchronize(st) : cudaGetLastError();
+    if (e == cudaSuccess && !from_host) {
+        e = cudaEventCreateWithFlags(&fr->ready, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventRecord(fr->ready, st);
+    }
     if (e != cudaSuccess) { set_cuda_error(e, "orbm_frame_create"); return fail(ORBB_E_CUDA); }
     *out = fr;
     return ORBB_OK;
@@ -253,7 +271,7 @@ extern "C" int orbm_window_search(const orbm_frame* fr, const orbm_query* q_host
 {
     if (!fr || nq < 0 || !offs_host || cap < 0 || (nq > 0 && !q_host) || (cap > 0 && (!idx_host || !dist_host))) return ORBB_E_INVALID;
     int rc = check_device(fr->device);
-    if (rc != ORBB_OK) return rc;
+    if (rc != ORBB_OK || (rc = frame_wait_ready(fr)) != ORBB_OK) return rc;
     if (nq == 0) { offs_host[0] = 0; return ORBB_OK; }
     DevBuf q, counts, offs, idx, dist;
     if ((rc = q.alloc((size_t)nq * sizeof(orbm_query))) || (rc = counts.alloc((size_t)nq * 4)) || (rc = offs.alloc((size_t)(nq + 1) * 4)) ||
@@ -331,6 +349,7 @@ static int resolve_on_device(const orbm_frame* fr, int mode, const float* uright
 {
     const int cap = cand_capacity > 0 ? cand_capacity : 64 * nq + 1024;
     int rc;
+    if (fr->ready) ORBB_CUDA(cudaStreamWaitEvent(st, fr->ready, 0));      // the frame may have been built on another stream
     if ((rc = fr->ws_counts.reserve((size_t)nq * 4)) ||
         (rc = fr->ws_offs.reserve((size_t)(nq + 1) * 4)) || (rc = fr->ws_idx.reserve((size_t)cap * 4)) ||
         (rc = fr->ws_dist.reserve((size_t)cap * 4)) || (rc = fr->ws_choice.reserve((size_t)nq * 4)) ||
@@ -458,7 +477,7 @@ extern "C" int orbm_search_by_projection_reloc(const orbm_frame* f, const orbm_p
             if (frame_mp[i2] >= 0) continue;                                            // :1727-1728
             if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx2 = i2; }
         }
-        if (bestDist <= max_dist) {                                                     // :1742-1760
+        if (bestIdx2 >= 0 && bestDist <= max_dist) {                                    // :1742-1760 (the guard keeps max_dist >= 256 in bounds)
             frame_mp[bestIdx2] = pq[i].id;
             nm++;
             if (check_ori) rotHist[rot_bin(pq[i].angle, f->h_kps[bestIdx2].angle)].push_back(bestIdx2);
@@ -953,9 +972,10 @@ static int db_reserve(orbm_db* db, int nq, int nchunks)
     return ORBB_OK;
 }
 
-extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int nq, int32_t* d1, int64_t* i1, int32_t* d2, void* stream)
+// A search writes the database's per-chunk partial-key scratch (and may grow it): not const, and calls on one orbm_db are
+// serialised by the caller (include/orbb200.h).
+extern "C" int orbm_bf_top2_device(orbm_db* db, const uint8_t* q_dev, int nq, int32_t* d1, int64_t* i1, int32_t* d2, void* stream)
 {
-    orbm_db* db = const_cast<orbm_db*>(cdb);
     if (!db || nq < 0 || (nq > 0 && (!q_dev || !d1 || !i1 || !d2))) return ORBB_E_INVALID;
     if (nq == 0) return ORBB_OK;
     ORBB_CUDA(cudaSetDevice(db->device));
@@ -970,11 +990,11 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
     dim3 grid(ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE), nchunks);
     if (db->variant >= 3) {
         // more than 48 KB of dynamic shared memory is an opt-in per device
-        static bool attr_set[64] = {};
+        static std::atomic<bool> attr_set[64];                   // setting it twice is harmless; the flag only saves the call
         const int dv = db->device & 63;
-        if (!attr_set[dv]) {
+        if (!attr_set[dv].load(std::memory_order_acquire)) {
             ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_SMEM));
-            attr_set[dv] = true;
+            attr_set[dv].store(true, std::memory_order_release);
         }
         bf_top2_tcn_kernel<<<grid, BW_THREADS, BN_SMEM, st>>>(a);
     }
@@ -988,9 +1008,8 @@ extern "C" int orbm_bf_top2_device(const orbm_db* cdb, const uint8_t* q_dev, int
     return ORBB_OK;
 }
 
-extern "C" int orbm_bf_top2(const orbm_db* cdb, const uint8_t* q_host, int nq, int32_t* d1, int64_t* i1, int32_t* d2)
+extern "C" int orbm_bf_top2(orbm_db* db, const uint8_t* q_host, int nq, int32_t* d1, int64_t* i1, int32_t* d2)
 {
-    orbm_db* db = const_cast<orbm_db*>(cdb);
     if (!db || nq < 0 || (nq > 0 && (!q_host || !d1 || !i1 || !d2))) return ORBB_E_INVALID;
     if (nq == 0) return ORBB_OK;
     ORBB_CUDA(cudaSetDevice(db->device));

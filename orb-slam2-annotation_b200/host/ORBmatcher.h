@@ -93,7 +93,7 @@ public:
         d1.resize(nq); idx1.resize(nq); d2.resize(nq);
         orbm_check(orbm_bf_top2(db_, q.data(), nq, d1.data(), idx1.data(), d2.data()), "orbm_bf_top2");
     }
-    const orbm_db* get() const { return db_; }
+    orbm_db* get() const { return db_; }
 
 private:
     orbm_db* db_;

@@ -548,3 +548,44 @@ def test_tracked_frame_stays_on_device(gpu):
     ex.sync()
     assert t_sc.cpu().tolist() == [on, 0] and np.array_equal(t_mp.cpu().numpy(), omp) and on > 300
     F.close()
+
+
+def test_host_form_search_waits_for_device_built_frame(gpu):
+    """orbm_frame_create_device queues its copies and grid kernels on the caller's non-blocking stream; the
+    host-pointer entry points run on the legacy default stream, which does not order against it.  They must wait on the frame's
+    'ready' event themselves: no explicit synchronisation here, and a long kernel is queued first so the race would be lost."""
+    import torch
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=16)
+    rng = np.random.default_rng(23)
+    h, w = cur.shape
+    dev = torch.device("cuda:0")
+    t_k = torch.from_numpy(kc.view(np.uint8).reshape(len(kc), -1).copy()).to(dev); t_d = torch.from_numpy(dc.copy()).to(dev)
+    big = torch.empty(1 << 28, dtype=torch.float32, device=dev)
+    torch.cuda.synchronize()
+    st = torch.cuda.Stream()                       # cudaStreamNonBlocking
+    O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    q = _queries(kl, dl, scale, 10.0, (3, 1), rng, "pm1")
+    with torch.cuda.stream(st):
+        for _ in range(20):
+            big.mul_(1.0001)                       # ~ tens of ms of work ahead of the frame build on `st`
+        F = orbb200.FrameMatcher.from_device(t_k.data_ptr(), t_d.data_ptr(), len(kc), (0, 0, w, h), 0, st.cuda_stream)
+    offs, idx, dist = F.window_search(q["q"])                                       # host form, default stream, no sync in between
+    oo, oi, od = O.window_search(_to_oracle_queries(q))
+    assert np.array_equal(offs, oo) and np.array_equal(idx, oi) and np.array_equal(dist, od)
+    n1, m1 = orbb200.ORBmatcher(0.9, True).SearchByProjection_reloc(F, q, np.full(len(kc), -1, np.int32), 100)
+    n2, m2 = O.search_reloc(_to_oracle_queries(q), 100, True, np.full(len(kc), -1, np.int32))
+    assert n1 == n2 and np.array_equal(m1, m2)
+    F.close()
+
+
+def test_reloc_max_dist_above_255_stays_in_bounds(gpu):
+    """with max_dist >= 256 a query without any unfiltered candidate must not write frame_mp[-1]."""
+    import orbb200
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=16)
+    h, w = cur.shape
+    F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h))
+    q = _queries(kl, dl, scale, 10.0, (3, 1), np.random.default_rng(1), "pm1")
+    mp0 = np.zeros(len(kc), np.int32)                                              # every feature already has a MapPoint
+    n, mp = orbb200.ORBmatcher(0.9, True).SearchByProjection_reloc(F, q, mp0, 300)
+    assert n == 0 and np.array_equal(mp, mp0)
