@@ -319,6 +319,19 @@ int orbm_bf_top2(orbm_db* db, const uint8_t* q_host, int nq, int32_t* d1_host, i
 /* Device queries / device results, asynchronous on `stream` (cudaStream_t, may be NULL). */
 int orbm_bf_top2_device(orbm_db* db, const uint8_t* q_dev, int nq, int32_t* d1_dev, int64_t* idx1_dev,
                         int32_t* d2_dev, void* stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The same scan and chunk merge as orbm_bf_top2_device over rows
+ * the CALLER holds on the device (rows_dev: nrows x 32 B, 16-byte aligned; global row index = row_offset + i), with the per-chunk
+ * partial keys in a file-scope static device array of liborbb200 (4 MiB, held by every GPU that loads the library until exit)
+ * instead of scratch owned by an orbm_db.  Calls no cudaMalloc / cudaFree and no allocating library routine.
+ * Limits: nq <= ORBM_NOALLOC_MAX_QUERIES; the scan is split into at most ORBM_NOALLOC_MAX_KEYS / nq chunks of at most 2^23 rows, so
+ * nrows <= (ORBM_NOALLOC_MAX_KEYS / nq) * 2^23; beyond either limit ORBB_E_CAPACITY is returned (text in orbb200_last_cuda_error)
+ * and nothing is launched.  Every call on one device shares the array: calls that overlap on the GPU (two streams, two threads)
+ * race; serialise them.  Asynchronous on `stream`; outputs are device pointers as in orbm_bf_top2_device. */
+#define ORBM_NOALLOC_MAX_QUERIES 4096
+#define ORBM_NOALLOC_MAX_KEYS (1 << 19)
+int orbm_bf_top2_noalloc(const uint8_t* rows_dev, int64_t nrows, int64_t row_offset, const uint8_t* q_dev, int nq,
+                         int32_t* d1_dev, int64_t* idx1_dev, int32_t* d2_dev, int device, void* stream);
 /* Merge of G per-shard results laid out [g][nq] (shards ordered by ascending row range) into the global top-2
  *  — the step that follows the NCCL all-gather.  Device pointers, asynchronous on `stream`. */
 int orbm_merge_top2_device(const int32_t* d1_all, const int64_t* idx1_all, const int32_t* d2_all, int nshards, int nq,

@@ -1026,6 +1026,80 @@ extern "C" int orbm_bf_top2(orbm_db* db, const uint8_t* q_host, int nq, int32_t*
     return ORBB_OK;
 }
 
+// ---- brute-force top-2 without any allocation ---------------------------------------------------------
+// Same scan + chunk merge as orbm_bf_top2_device, for callers that cannot call cudaMalloc (CUDA graph capture, serving loops): the
+// per-(chunk, query) partial keys live in ONE file-scope device array that every device holding this library keeps until exit.
+// Every call on a device shares it: calls that overlap on the GPU race (see include/orbb200.h).
+constexpr int BF_NOALLOC_MAX_NQ = 4096;                   // queries per call
+constexpr int BF_NOALLOC_MAX_KEYS = 1 << 19;              // nq * nchunks partial keys per array (2 MiB each, 4 MiB in total)
+static __device__ __align__(256) unsigned g_bf_noalloc_scratch[2 * BF_NOALLOC_MAX_KEYS];
+
+// The array's name is only a host-side stand-in: the device address comes from cudaGetSymbolAddress, once per device, with that
+// device current.
+static int bf_noalloc_scratch(int device, unsigned** out)
+{
+    static std::mutex mu;
+    static unsigned* ptr[64] = {};
+    if (device < 0 || device >= 64) return ORBB_E_INVALID;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[device]) {
+        ORBB_CUDA(cudaSetDevice(device));
+        unsigned* p = nullptr;
+        ORBB_CUDA(cudaGetSymbolAddress((void**)&p, g_bf_noalloc_scratch));
+        // more than 48 KB of dynamic shared memory is an opt-in per device (not an allocation)
+        ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tcn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_SMEM));
+        ptr[device] = p;
+    }
+    *out = ptr[device];
+    return ORBB_OK;
+}
+
+extern "C" int orbm_bf_top2_noalloc(const uint8_t* rows_dev, int64_t nrows, int64_t row_offset, const uint8_t* q_dev, int nq,
+                                    int32_t* d1, int64_t* i1, int32_t* d2, int device, void* stream)
+{
+    if (nrows < 0 || row_offset < 0 || nq < 0 || (nrows > 0 && !rows_dev) || (nq > 0 && (!q_dev || !d1 || !i1 || !d2))) return ORBB_E_INVALID;
+    if (((uintptr_t)rows_dev | (uintptr_t)q_dev) & 15) return ORBB_E_INVALID;            // 16-byte row loads
+    if (nq > BF_NOALLOC_MAX_NQ) {
+        set_cuda_error(cudaErrorInvalidValue, "orbm_bf_top2_noalloc: nq exceeds ORBM_NOALLOC_MAX_QUERIES (4096)");
+        return ORBB_E_CAPACITY;
+    }
+    if (nq == 0) return ORBB_OK;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    unsigned* scratch = nullptr;
+    if ((rc = bf_noalloc_scratch(device, &scratch)) != ORBB_OK) return rc;
+    // chunking as db_plan does for the tcgen05 kernel (two CTAs per SM over all query tiles), then capped by the scratch size
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const int qtiles = ceil_div(nq, BM_QTILE);
+    int target = ceil_div(sms * 2, qtiles);
+    if ((long long)target * nq > BF_NOALLOC_MAX_KEYS) target = BF_NOALLOC_MAX_KEYS / nq;
+    long long rpc = (nrows + target - 1) / target;
+    rpc = (rpc + 255) / 256 * 256;
+    if (rpc < BF_ROWS) rpc = BF_ROWS;
+    if (rpc > (1ll << BF_IDX_BITS)) rpc = 1ll << BF_IDX_BITS;
+    const long long nchunks_ll = nrows > 0 ? (nrows + rpc - 1) / rpc : 1;
+    if (nchunks_ll * nq > BF_NOALLOC_MAX_KEYS) {
+        set_cuda_error(cudaErrorInvalidValue, "orbm_bf_top2_noalloc: nrows x nq exceeds the static scratch (2^19 partial keys of <= 2^23 rows each)");
+        return ORBB_E_CAPACITY;
+    }
+    const int nchunks = (int)nchunks_ll;
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned* k1 = scratch; unsigned* k2 = scratch + BF_NOALLOC_MAX_KEYS;
+    // the array keeps the previous call's keys: start both halves of this call's region at "no row" (0xffffffff)
+    ORBB_CUDA(cudaMemsetAsync(k1, 0xff, (size_t)nchunks * nq * 4, st));
+    ORBB_CUDA(cudaMemsetAsync(k2, 0xff, (size_t)nchunks * nq * 4, st));
+    BfArgs a;
+    a.db = (const uint4*)rows_dev; a.nrows = nrows; a.q = (const uint4*)q_dev; a.nq = nq;
+    a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = k1; a.part_k2 = k2;
+    bf_top2_tcn_kernel<<<dim3(qtiles, nchunks), BW_THREADS, BN_SMEM, st>>>(a);
+    ORBB_LAUNCHED();
+    bf_merge_chunks_kernel<<<ceil_div(nq, 256), 256, 0, st>>>(k1, k2, nchunks, nq, rpc, row_offset, d1, (long long*)i1, d2);
+    ORBB_LAUNCHED();
+    ORBB_CUDA(cudaGetLastError());
+    return ORBB_OK;
+}
+
 extern "C" int orbm_merge_top2_device(const int32_t* d1_all, const int64_t* i1_all, const int32_t* d2_all, int G, int nq,
                                       int32_t* d1, int64_t* i1, int32_t* d2, void* stream)
 {

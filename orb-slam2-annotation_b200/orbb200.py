@@ -20,6 +20,7 @@ PROJ_QUERY_DTYPE = np.dtype([("q", QUERY_DTYPE), ("u_right", "<f4"), ("max_err_r
 assert KP_DTYPE.itemsize == 28 and QUERY_DTYPE.itemsize == 52 and PROJ_QUERY_DTYPE.itemsize == 72
 
 OK, E_INVALID, E_CUDA, E_CAPACITY, E_BAD_SHAPE, E_NOMEM, E_STATE = 0, -1, -2, -3, -4, -5, -6
+NOALLOC_MAX_QUERIES, NOALLOC_MAX_KEYS = 4096, 1 << 19      # ORBM_NOALLOC_MAX_QUERIES / _KEYS of include/orbb200.h
 STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 
 # every symbol include/orbb200.h declares (tests check the .so exports all of them)
@@ -29,7 +30,7 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "or
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_frame_create_device", "orbm_undistort_keypoints", "orbm_undistort_keypoints_device", "orbm_image_bounds",
            "orbm_search_by_projection_points_device", "orbm_search_by_projection_frame_device", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
-           "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_merge_top2_device", "orbm_ratio_test",
+           "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_bf_top2_noalloc", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
            "orbv_compute_bow", "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak", "orbb200_measure_imma_peak",
            "orbb200_launch_count"]
@@ -115,6 +116,7 @@ def lib():
         L.orbm_db_rows.restype = C.c_int64
         L.orbm_bf_top2.argtypes = [vp, vp, i32, vp, vp, vp]
         L.orbm_bf_top2_device.argtypes = [vp, vp, i32, vp, vp, vp, vp]
+        L.orbm_bf_top2_noalloc.argtypes = [vp, C.c_int64, C.c_int64, vp, i32, vp, vp, vp, i32, vp]
         L.orbm_merge_top2_device.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, vp]
         L.orbm_ratio_test.argtypes = [vp, vp, i32, i32, f32, vp]
         L.orbb200_strerror.argtypes = [i32]
@@ -631,6 +633,12 @@ class DescriptorDB:
     def top2_device(self, q_ptr, nq, d1_ptr, i1_ptr, d2_ptr, stream=0):
         _check(self.L.orbm_bf_top2_device(self.h, _p(q_ptr), nq, _p(d1_ptr), _p(i1_ptr), _p(d2_ptr), _p(stream) if stream else None),
                "orbm_bf_top2_device")
+
+
+def bf_top2_noalloc(rows_ptr, nrows, row_offset, q_ptr, nq, d1_ptr, i1_ptr, d2_ptr, device=0, stream=0):
+    """orbm_bf_top2_noalloc: device pointers in and out, scratch in the library's static device array (no allocation)."""
+    _check(lib().orbm_bf_top2_noalloc(_p(rows_ptr), nrows, row_offset, _p(q_ptr), nq, _p(d1_ptr), _p(i1_ptr), _p(d2_ptr), device,
+                                      _p(stream) if stream else None), "orbm_bf_top2_noalloc")
 
 
 def merge_top2_device(d1_all, i1_all, d2_all, nshards, nq, d1, i1, d2, stream=0):
