@@ -155,6 +155,293 @@ def run_reference(args, rank, world):
     emit(line)
 
 
+def _pcts(us):
+    us = sorted(us)
+    return {"p50_us": us[len(us) // 2], "p99_us": us[min(len(us) - 1, int(0.99 * len(us)))], "min_us": us[0], "calls": len(us)}
+
+
+def measure_latency(local_rank, dev):
+    """Config 1 as BASELINE.json words it: ONE synthetic 640x480 frame through the call Frame::ExtractORB makes (Frame.cpp:259-265 ->
+    orbx_extract: H2D, kernels, D2H, sync), and the same launch sequence device-resident with plain launches vs one CUDA graph."""
+    import ctypes as C
+    import numpy as np
+    import torch
+    import orbb200
+    from synth import synth
+    L = orbb200.lib()
+    img = synth(W, H, 4242)
+    ex = orbb200.ORBextractor(NFEAT, 1.2, 8, 20, 7, max_size=(W, H), max_batch=1, device=local_rank)
+    kps = np.zeros(CAPACITY, orbb200.KP_DTYPE); desc = np.zeros((CAPACITY, 32), np.uint8); n = C.c_int()
+    pin = torch.from_numpy(img.copy()).pin_memory()
+    pk = torch.zeros((CAPACITY, 7), dtype=torch.float32).pin_memory(); pd = torch.zeros((CAPACITY, 32), dtype=torch.uint8).pin_memory()
+
+    def call_pageable():
+        rc = L.orbx_extract(ex.h, img.ctypes.data_as(C.c_void_p), W, H, W, kps.ctypes.data_as(C.c_void_p), desc.ctypes.data_as(C.c_void_p), CAPACITY, C.byref(n))
+        assert rc == 0, rc
+
+    def call_pinned():
+        rc = L.orbx_extract(ex.h, C.c_void_p(pin.data_ptr()), W, H, W, C.c_void_p(pk.data_ptr()), C.c_void_p(pd.data_ptr()), CAPACITY, C.byref(n))
+        assert rc == 0, rc
+
+    dimg = pin.to(dev)
+    dk = torch.zeros((CAPACITY, 7), dtype=torch.float32, device=dev); dd = torch.zeros((CAPACITY, 32), dtype=torch.uint8, device=dev)
+    dc = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def call_device():
+        ex.extract_batch_device(dimg.data_ptr(), 1, W, H, W, W * H, dk.data_ptr(), dd.data_ptr(), dc.data_ptr(), CAPACITY)
+        ex.sync()
+
+    def timed(fn, calls=300, warm=20):
+        for _ in range(warm):
+            fn()
+        us = []
+        for _ in range(calls):
+            t0 = time.perf_counter(); fn(); us.append((time.perf_counter() - t0) * 1e6)
+        return _pcts(us)
+
+    out = {"workload": "one 640x480 synthetic frame, 1000 kp (BASELINE.json configs[0])",
+           "orbx_extract_pageable_host": timed(call_pageable), "keypoints": 0}
+    out["keypoints"] = int(n.value)
+    out["orbx_extract_pinned_host"] = timed(call_pinned)
+    out["device_resident_plain_launches"] = timed(call_device)
+    ref_cnt = int(dc.item()); ref_desc = dd.clone()
+    ex.graph_capture(dimg.data_ptr(), 1, W, H, W, W * H, dk.data_ptr(), dd.data_ptr(), dc.data_ptr(), CAPACITY)
+    dd.zero_(); dc.zero_()
+
+    def call_graph():
+        ex.graph_launch()
+        ex.sync()
+    out["device_resident_cuda_graph"] = timed(call_graph)
+    out["graph_equals_plain"] = bool(int(dc.item()) == ref_cnt and torch.equal(dd, ref_desc))
+    # the kernels alone (CUDA events around 50 graph replays, no host in between)
+    st = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(st)
+    for _ in range(50):
+        ex.graph_launch()
+    e1.record(st)
+    ex.sync()
+    out["gpu_us_per_frame_back_to_back_graphs"] = e0.elapsed_time(e1) * 1e3 / 50
+    return out
+
+
+def measure_link_floor(world, dev, barrier, max_over_ranks, h2d_bytes, d2h_bytes, frames):
+    """What the host can move: every rank copies one step's input bytes H2D and one step's result bytes D2H from / to pinned memory
+    on two streams at the same time, all ranks concurrently.  e2e can not beat frames / this time."""
+    import torch
+    hin = torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory(); din = torch.empty(h2d_bytes, dtype=torch.uint8, device=dev)
+    hout = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory(); dout = torch.empty(d2h_bytes, dtype=torch.uint8, device=dev)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def go(n):
+        for _ in range(n):
+            with torch.cuda.stream(s1):
+                din.copy_(hin, non_blocking=True)
+            with torch.cuda.stream(s2):
+                hout.copy_(dout, non_blocking=True)
+        s1.synchronize(); s2.synchronize()
+    go(2)
+    barrier()
+    t0 = time.perf_counter()
+    iters = 6
+    go(iters)
+    barrier()
+    dt = max_over_ranks(time.perf_counter() - t0)
+    return {"frames_per_s": world * frames * iters / dt, "h2d_GBps_per_gpu": h2d_bytes * iters / dt / 1e9, "d2h_GBps_per_gpu": d2h_bytes * iters / dt / 1e9,
+            "what": f"{world} rank(s) x (H2D {h2d_bytes} B + D2H {d2h_bytes} B) per step from pinned memory, both directions and all ranks at once"}
+
+
+def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
+    """Driver-timed rows for BASELINE.json configs[1..3] (C2 KITTI stereo pair, C3 EuRoC batch, C4 4K batch).  Frames shard over
+    ranks with no collective; every row is the whole job (all ranks), device-timed with CUDA events, max over ranks."""
+    import ctypes as C
+    import numpy as np
+    import torch
+    import orbb200
+    from synth import synth
+    L = orbb200.lib()
+    rows = {}
+
+    def batch_row(w, h, nf, F, cap, nd, iters, seed):
+        distinct = np.stack([synth(w, h, seed + 100 * rank + i) for i in range(nd)])
+        frames = torch.from_numpy(np.ascontiguousarray(np.tile(distinct, (F // nd, 1, 1)))).to(dev)
+        ex = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), max_batch=F, device=local_rank)
+        st = torch.cuda.ExternalStream(ex.stream(), device=dev)
+        kps = torch.zeros((F, cap, 7), dtype=torch.float32, device=dev); desc = torch.zeros((F, cap, 32), dtype=torch.uint8, device=dev)
+        cnt = torch.zeros(F, dtype=torch.int32, device=dev)
+        step = lambda: ex.extract_batch_device(frames.data_ptr(), F, w, h, w, w * h, kps.data_ptr(), desc.data_ptr(), cnt.data_ptr(), cap)
+        for _ in range(3):
+            step()
+        ex.sync(); barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(iters):
+            step()
+        e1.record(st)
+        ex.sync(); barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1)) / iters
+        ex.set_profiling(True)
+        for _ in range(2):
+            step()
+        prof = ex.get_profile(); ex.set_profiling(False)
+        sc = np.float32(1.0); P = []
+        for l in range(8):
+            inv = np.float32(1.0) / sc
+            P.append(int(np.rint(np.float32(w) * inv)) * int(np.rint(np.float32(h) * inv)))
+            sc = np.float32(np.float64(sc) * np.float64(np.float32(1.2)))
+        lvl_bytes = 3 * sum(P) - P[0] - P[-1]
+        lvl_ms = prof["level_ms"] / prof["calls"]
+        peak, _ = measured_peaks()
+        nkp = float(cnt.float().mean().item())
+        return {"frames_per_s": world * F / ms * 1e3, "ms_per_step": ms, "frames_per_step_per_gpu": F, "steps": iters, "keypoints_per_frame": nkp,
+                "keypoints_per_s": world * F * nkp / ms * 1e3, "distinct_frames": nd,
+                "step_share_ms": {k: prof[k] / prof["calls"] for k in ("level_ms", "octree_ms", "desc_ms")},
+                "level_kernels_hbm_frac": lvl_bytes * F / lvl_ms / 1e6 / peak}
+
+    rows["C3_euroc_752x480_1200kp_batch"] = batch_row(752, 480, 1200, 512, 1536, 16, 6, 7000)
+    rows["C4_4k_3840x2160_8000kp_batch"] = batch_row(3840, 2160, 8000, 64, 9216, 2, 5, 9000)
+    rows["C2_kitti_1241x376_2000kp_batch"] = batch_row(1241, 376, 2000, 256, 2560, 8, 6, 8000)
+    torch.cuda.empty_cache()
+
+    # ---- C2 pair pipeline through the host-pointer C ABI: extract L, extract R, ComputeStereoMatches, SearchByProjection(last frame) ----
+    w, h, nf, cap = 1241, 376, 2000, 2560
+    big = synth(w + 80, h + 16, 8100 + rank)
+    pairs = []
+    for (ox, oy) in ((8, 8), (11, 9)):                      # two consecutive stereo pairs: the camera moved by (3, 1) pixels
+        left = big[oy:oy + h, ox + 40:ox + 40 + w].copy()
+        right = big[oy:oy + h, ox + 28:ox + 28 + w].copy()  # constant 12-px disparity
+        pairs.append((left, right))
+    exL = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
+    exR = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
+    scale = exL.GetScaleFactors()
+    bufs = [dict(kL=np.zeros(cap, orbb200.KP_DTYPE), dL=np.zeros((cap, 32), np.uint8), kR=np.zeros(cap, orbb200.KP_DTYPE), dR=np.zeros((cap, 32), np.uint8),
+                 ur=np.zeros(cap, np.float32), dp=np.zeros(cap, np.float32), mp=np.zeros(cap, np.int32), ob=np.zeros(cap, np.int32)) for _ in range(2)]
+    vp = C.c_void_p
+    ptr = lambda a: a.ctypes.data_as(vp)
+    mbf, bounds = 386.1448, (0.0, 0.0, float(w), float(h))
+    nL, nR, nm = C.c_int(), C.c_int(), C.c_int()
+    stats = {"stereo": 0, "proj": 0, "kp": 0}
+
+    def one_pair(i, queries):
+        b = bufs[i & 1]; left, right = pairs[i & 1]
+        assert L.orbx_extract(exL.h, ptr(left), w, h, w, ptr(b["kL"]), ptr(b["dL"]), cap, C.byref(nL)) == 0
+        assert L.orbx_extract(exR.h, ptr(right), w, h, w, ptr(b["kR"]), ptr(b["dR"]), cap, C.byref(nR)) == 0
+        assert L.orbm_stereo_match(exL.h, exR.h, ptr(b["kL"]), ptr(b["dL"]), nL.value, ptr(b["kR"]), ptr(b["dR"]), nR.value,
+                                   C.c_float(mbf), C.c_float(0.0), ptr(b["ur"]), ptr(b["dp"])) == 0
+        fh = vp()
+        assert L.orbm_frame_create(C.byref(fh), ptr(b["kL"]), ptr(b["dL"]), nL.value, *[C.c_float(x) for x in bounds], local_rank) == 0
+        if queries is not None:
+            b["mp"][:nL.value] = -1; b["ob"][:nL.value] = 0
+            assert L.orbm_search_by_projection_frame(fh, ptr(b["ur"]), ptr(queries), len(queries), 1, ptr(b["mp"]), ptr(b["ob"]), C.byref(nm)) == 0
+            stats["proj"] += nm.value
+        L.orbm_frame_destroy(fh)
+        stats["stereo"] += int((b["ur"][:nL.value] > 0).sum()); stats["kp"] += nL.value + nR.value
+
+    def queries_from(b, n, dx, dy):                        # the previous left frame's keypoints projected into the current one
+        q = np.zeros(n, orbb200.PROJ_QUERY_DTYPE)
+        k = b["kL"][:n]
+        q["q"]["u"] = k["x"] + dx; q["q"]["v"] = k["y"] + dy; q["q"]["r"] = 15.0 * scale[k["octave"]]
+        q["q"]["min_level"] = k["octave"] - 1; q["q"]["max_level"] = k["octave"] + 1; q["q"]["desc"] = b["dL"][:n]
+        q["u_right"] = q["q"]["u"] - 12.0; q["max_err_right"] = 15.0 * scale[k["octave"]]
+        q["id"] = np.arange(n); q["has_obs"] = 1; q["angle"] = k["angle"]
+        return q
+    one_pair(0, None); n0 = nL.value
+    one_pair(1, None); n1 = nL.value
+    qs = [queries_from(bufs[1], n1, 3.0, 1.0), queries_from(bufs[0], n0, -3.0, -1.0)]     # queries for pair 0 come from pair 1 and vice versa
+    for i in range(4):
+        one_pair(i, qs[i & 1])
+    stats.update(stereo=0, proj=0, kp=0)
+    barrier()
+    npairs = 40
+    t0 = time.perf_counter()
+    for i in range(npairs):
+        one_pair(i, qs[i & 1])
+    torch.cuda.synchronize(); barrier()
+    dt = max_over_ranks(time.perf_counter() - t0)
+    rows["C2_kitti_stereo_pair_pipeline"] = {
+        "pairs_per_s": world * npairs / dt, "frames_per_s": 2 * world * npairs / dt, "ms_per_pair": dt / npairs * 1e3,
+        "stereo_matches_per_s": world * stats["stereo"] / dt, "projection_matches_per_s": world * stats["proj"] / dt,
+        "matches_per_s": world * (stats["stereo"] + stats["proj"]) / dt, "keypoints_per_frame": stats["kp"] / (2 * npairs),
+        "stereo_matches_per_pair": stats["stereo"] / npairs, "projection_matches_per_pair": stats["proj"] / npairs,
+        "api": "per pair on one host thread, host pointers: orbx_extract (L) + orbx_extract (R) + orbm_stereo_match + orbm_frame_create + "
+               "orbm_search_by_projection_frame + orbm_frame_destroy; wall clock, H2D/D2H inside every call"}
+    return rows
+
+
+def measure_c5_strong(rank, world, local_rank, dev, stream, barrier, max_over_ranks):
+    """BASELINE.json configs[4] as stated: 2000 queries x 10 M rows IN TOTAL, rows block-sharded over the ranks (1.25 M per GPU at N = 8),
+    per-shard top-2 merged after ONE packed NCCL all-gather (sharding.ShardedDescriptorDB / gather_top2); the merged result is checked."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import orbb200
+    import sharding
+    S = sharding.ShardedDescriptorDB(DB_ROWS, local_rank)
+    nrows = S.end - S.begin
+    g = torch.Generator(device=dev); g.manual_seed(4242 + rank)
+    shard = torch.randint(0, 256, (nrows, 32), dtype=torch.uint8, device=dev, generator=g)
+    S.append_device(shard)
+    rng = np.random.default_rng(99)                                   # the same on every rank
+    nh = NQ // 2
+    planted = np.sort(rng.choice(DB_ROWS, nh, replace=False))
+    mine = (planted >= S.begin) & (planted < S.end)
+    rows = torch.zeros((nh, 32), dtype=torch.int32, device=dev)
+    if mine.any():
+        rows[torch.from_numpy(np.flatnonzero(mine)).to(dev)] = shard[torch.from_numpy(planted[mine] - S.begin).to(dev)].to(torch.int32)
+    if world > 1:
+        dist.all_reduce(rows)                                         # every planted row is owned by exactly one rank
+    base = rows.to(torch.uint8).cpu().numpy()
+    bits = np.unpackbits(base, axis=1)
+    flips = rng.integers(0, 61, nh)
+    for i in range(nh):
+        if flips[i]:
+            bits[i, rng.choice(256, int(flips[i]), replace=False)] ^= 1
+    q = rng.integers(0, 256, (NQ, 32), dtype=np.uint8)
+    q[:nh] = np.packbits(bits, axis=1)
+    qd = torch.from_numpy(q).to(dev)
+    del shard
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    ea, eb, ec = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    d1 = torch.empty(NQ, dtype=torch.int32, device=dev); i1 = torch.empty(NQ, dtype=torch.int64, device=dev); d2 = torch.empty(NQ, dtype=torch.int32, device=dev)
+
+    def step():
+        """scan of the local shard | packed all-gather + merge"""
+        S.db.top2_device(qd.data_ptr(), NQ, d1.data_ptr(), i1.data_ptr(), d2.data_ptr(), stream.cuda_stream)
+        eb.record(stream)
+        if world > 1:
+            d1a, i1a, d2a = sharding.gather_top2(d1, i1, d2)
+            orbb200.merge_top2_device(d1a.data_ptr(), i1a.data_ptr(), d2a.data_ptr(), world, NQ, d1.data_ptr(), i1.data_ptr(), d2.data_ptr(), stream.cuda_stream)
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            step()
+    barrier()
+    iters, ms_scan, ms_all = 10, 0.0, 0.0
+    l0 = orbb200.launch_count()
+    for _ in range(iters):
+        with torch.cuda.stream(stream):
+            flush.zero_()
+            if world > 1:
+                dist.barrier()                  # ranks start the step together: the gather then measures the exchange, not the skew
+            ea.record(stream)
+            step()
+            ec.record(stream)
+        stream.synchronize()
+        ms_scan += ea.elapsed_time(eb); ms_all += ea.elapsed_time(ec)
+    barrier()
+    launches = orbb200.launch_count() - l0
+    ms_all = max_over_ranks(ms_all) / iters; ms_scan = max_over_ranks(ms_scan) / iters
+    r1, ri, r2 = d1.cpu().numpy(), i1.cpu().numpy(), d2.cpu().numpy()
+    ok = bool(np.array_equal(r1[:nh], flips) and np.array_equal(ri[:nh], planted) and np.all(r1 <= r2) and np.all((ri >= 0) & (ri < DB_ROWS)))
+    if not ok:
+        raise AssertionError("C5-strong: merged top-2 of the planted queries is wrong")
+    return {"metric": "bf_top2_gcmp_per_s", "value": NQ * DB_ROWS / (ms_all * 1e-3) / 1e9, "unit": "Gcmp/s", "scaling": "strong",
+            "workload": f"{NQ} queries x {DB_ROWS} rows in total = {nrows} rows per GPU on {world} GPU(s)", "ms_per_step": ms_all,
+            "scan_ms": ms_scan, "gather_merge_ms": ms_all - ms_scan, "limiter": "scan" if ms_scan > ms_all - ms_scan else "all-gather + merge",
+            "steps": iters, "gpu_launches": int(launches), "queries_per_s": NQ / (ms_all * 1e-3),
+            "exchange": "one all_gather_into_tensor of 16 B per query (sharding.gather_top2) + bf_merge_shards_kernel" if world > 1 else "none (one shard)",
+            "merge_checked": ok}
+
+
 def run_ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -280,6 +567,8 @@ def run_ours(args, rank, world, local_rank):
            "api": f"orbx_extract_batch (pinned host frames -> host keypoints+descriptors), {NH} handles on {NH} host threads, "
                   "alternate batches in flight"}
     del exs[1:]
+    e2e["link_floor"] = measure_link_floor(world, dev, barrier, max_over_ranks, e2e["h2d_bytes_per_step"], e2e["d2h_bytes_per_step"], B)
+    e2e["frac_of_link_floor"] = e2e["value"] / e2e["link_floor"]["frames_per_s"]
 
     # ---------------- Hamming: brute-force top-2, 2000 queries x 10 M rows per GPU ----------------
     g = torch.Generator(device=dev); g.manual_seed(42 + rank)
@@ -327,19 +616,29 @@ def run_ours(args, rank, world, local_rank):
     gcmp = world * NQ * DB_ROWS * Km / (ms_match * 1e-3) / 1e9
     popc_peak = orbb200.popc_peak(local_rank)
     imma_peak = orbb200.imma_peak(local_rank)
+    tc_peak = orbb200.tcgen05_i8_peak(local_rank)
     tops = 512 * gcmp / world / 1e3                     # one 256-bit comparison = 256 int8 multiply-adds on the tensor pipe
     hamming = {"metric": "bf_top2_gcmp_per_s", "value": gcmp, "unit": "Gcmp/s", "ms_per_step": ms_match / Km, "steps": Km,
                "workload": f"{NQ} queries x {DB_ROWS} rows per GPU, top-2 + merge" + (" + NCCL all-gather" if world > 1 else ""),
                "gpu_launches": int(match_launches),
                "kernel": "bf_top2_tcn_kernel: hamming = |q| - sum(+-1 query bits x 0/1 database bits), tcgen05.mma kind::i8 128x256x32, warp-specialised, "
                          "accumulators in TMEM, threshold-filtered top-2 update",
-               "roofline": {"bound": "tensor", "achieved": tops, "peak": 4 * imma_peak, "unit": "int8 TOP/s", "frac": tops / (4 * imma_peak),
-                            "peak_source": "4 x the measured register-only mma.sync.m16n8k32 rate on this GPU (orbb200_measure_imma_peak: the legacy "
-                                           "path runs at a quarter of the tcgen05 int8 rate; nominal dense int8 4500 TOP/s)",
+               "roofline": {"bound": "tensor", "achieved": tops, "peak": tc_peak, "unit": "int8 TOP/s", "frac": tops / tc_peak,
+                            "peak_source": "measured on this GPU: orbb200_measure_tcgen05_i8_peak = tcgen05.mma kind::i8 128x256x32 back to back from "
+                                           "shared-memory operands into TMEM, one CTA per SM, no producers or consumers (nominal dense int8 4500 TOP/s)",
+                            "inferred_peak_4x_legacy_imma": 4 * imma_peak, "frac_of_inferred": tops / (4 * imma_peak),
                             "legacy_imma_peak": imma_peak,
                             "popc_equivalent": {"achieved": 8 * gcmp / world, "peak": popc_peak, "unit": "Gpopc/s", "frac": 8 * gcmp / world / popc_peak,
                                                 "note": "what the integer-pipe formulation (8 POPC.32 per comparison) would need: the measured "
                                                         "register-only __popc rate caps that design at frac <= 1.6 (carry-save adders, 5 POPC)"}}}
+
+    del D, flush
+    torch.cuda.empty_cache()
+    c5 = measure_c5_strong(rank, world, local_rank, dev, stream, barrier, max_over_ranks)
+    torch.cuda.empty_cache()
+    configs = None if args.no_configs else measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks)
+    latency = measure_latency(local_rank, dev) if (rank == 0 and not args.no_configs) else None
+    barrier()
 
     # ---------------- CPU baseline (rank 0, N = 1 only): bounded sample on the host cores ----------------
     cpu = None
@@ -360,7 +659,8 @@ def run_ours(args, rank, world, local_rank):
                            "frames_per_step_per_gpu": B, "keypoints_per_frame": nkp,
                            "l2": "inputs 157 MB/step/GPU > 126 MB L2 and ~2 GB of intermediates rewritten every step",
                            "parallelism": f"frames sharded across {world} GPU(s), no collective; DB row-sharded, one NCCL all-gather"},
-                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "hamming": hamming}
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "hamming": hamming,
+                "configs": dict(configs or {}, C5_strong_10M_rows_total=c5), "merge_checked": c5["merge_checked"], "latency": latency}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
@@ -383,6 +683,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C2/C3/C4 rows and the single-frame latency (headline + Hamming only)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))

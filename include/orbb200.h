@@ -85,6 +85,15 @@ int orbx_extract_batch_device(orbx_handle* h, const uint8_t* imgs_dev, int nfram
                               size_t stride_bytes, size_t frame_stride_bytes,
                               orbx_keypoint* kps_dev, uint8_t* desc_dev, int32_t* counts_dev, int capacity);
 
+/* The launch sequence of orbx_extract_batch_device captured once as a CUDA graph and replayed with one launch: for the caller of
+ * Frame::ExtractORB (Frame.cpp:259-265), which extracts ONE frame at a time on the tracking thread's latency path, from fixed
+ * device buffers.  orbx_graph_capture bakes the pointers, shape and capacity given into the handle's graph (replacing an earlier
+ * one); orbx_graph_launch replays it on the handle's stream (asynchronous; orbx_sync as usual).  ORBB_E_STATE while profiling
+ * is on or before a capture. */
+int orbx_graph_capture(orbx_handle* h, const uint8_t* imgs_dev, int nframes, int w, int h_, size_t stride_bytes,
+                       size_t frame_stride_bytes, orbx_keypoint* kps_dev, uint8_t* desc_dev, int32_t* counts_dev, int capacity);
+int orbx_graph_launch(orbx_handle* h);
+
 /* Host-buffer batch: pinned or pageable host frames in, host results out (one H2D copy per batch, one D2H).
  * counts_host[f] receives each frame's keypoint count. */
 int orbx_extract_batch(orbx_handle* h, const uint8_t* imgs_host, int nframes, int w, int h_,
@@ -381,6 +390,9 @@ int orbb200_measure_popc_peak(int device, double* gpopc_per_s);
 /* Measured throughput (int8 TOPS, 2 x multiply-adds) of a register-only mma.sync.m16n8k32 (IMMA) loop on `device`: the
  * tensor-pipe denominator of the brute-force top-2 kernel, where one 256-bit comparison is 512 int8 operations. */
 int orbb200_measure_imma_peak(int device, double* int8_tops);
+/* Measured throughput (int8 TOPS) of tcgen05.mma kind::i8 128x256x32 issued back to back from shared-memory operands into TMEM
+ * accumulators, one CTA per SM, nothing else running: the measured tensor-pipe denominator of bf_top2_tcn_kernel's roofline. */
+int orbb200_measure_tcgen05_i8_peak(int device, double* int8_tops);
 /* Number of kernel launches issued by this library since load (bench.py's gpu_launches claim). */
 uint64_t orbb200_launch_count(void);
 

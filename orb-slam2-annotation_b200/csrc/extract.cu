@@ -81,6 +81,9 @@ struct orbx_handle {
     int last_frames = 0;
     const uint8_t* last_src = nullptr; long long last_src_pitch = 0, last_src_fstride = 0;
     const orbx_keypoint* last_kps_dev = nullptr; int last_capacity = 0;
+    // orbx_graph_capture: the launch sequence of one device-resident extraction as an executable CUDA graph
+    cudaGraphExec_t graph_exec = nullptr;
+    int graph_frames = 0;
 };
 
 static void level_sizes(const orbx_handle* h, int w, int ht, int* lw, int* lh)
@@ -399,6 +402,7 @@ extern "C" int orbx_destroy(orbx_handle* h)
         if (h->ev_side[i]) cudaEventDestroy(h->ev_side[i]);
         for (cudaEvent_t e : h->ev_lvl[i]) cudaEventDestroy(e);
     }
+    if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBB_OK;
@@ -583,6 +587,52 @@ extern "C" int orbx_extract_batch_device(orbx_handle* h, const uint8_t* imgs_dev
     if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w) return ORBB_E_BAD_SHAPE;
     ORBB_CUDA(cudaSetDevice(h->cfg.device));
     return enqueue_extract(h, imgs_dev, 0, nframes, w, ht, stride, fstride, kps_dev, desc_dev, counts_dev, capacity);
+}
+
+// The launch sequence of orbx_extract_batch_device (2 memsets, the level kernels, the octrees on their side streams, the
+// orientation + descriptor kernel) captured once as a CUDA graph: a tracking thread that extracts one frame at a time from fixed
+// device buffers replays it with a single launch instead of ~25 runtime calls (Frame::ExtractORB, Frame.cpp:259-265, is on the
+// latency path of every frame).  The graph bakes in the pointers, the shape and the capacity given here.
+extern "C" int orbx_graph_capture(orbx_handle* h, const uint8_t* imgs_dev, int nframes, int w, int ht, size_t stride, size_t fstride,
+                                  orbx_keypoint* kps_dev, uint8_t* desc_dev, int32_t* counts_dev, int capacity)
+{
+    if (!h || !imgs_dev || !kps_dev || !desc_dev || !counts_dev || capacity < 1) return ORBB_E_INVALID;
+    if (nframes < 1 || nframes > h->cfg.max_batch) return ORBB_E_INVALID;
+    if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w) return ORBB_E_BAD_SHAPE;
+    if (h->profiling) return ORBB_E_STATE;                      // the profiling path synchronises: not capturable
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    { const int rc = ensure_geometry(h, w, ht); if (rc != ORBB_OK) return rc; }     // table uploads happen outside the capture
+    while ((int)h->ev_lvl[0].size() < h->nlevels) {
+        cudaEvent_t e;
+        ORBB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->ev_lvl[0].push_back(e);
+    }
+    ORBB_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->graph_exec) { cudaGraphExecDestroy(h->graph_exec); h->graph_exec = nullptr; h->graph_frames = 0; }
+    ORBB_CUDA(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    const uint64_t launched = g_launches.load();
+    const int rc = enqueue_extract(h, imgs_dev, 0, nframes, w, ht, stride, fstride, kps_dev, desc_dev, counts_dev, capacity);
+    g_launches.store(launched);                                 // captured, not launched
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(h->stream, &graph);
+    if (rc != ORBB_OK) { if (graph) cudaGraphDestroy(graph); cudaGetLastError(); return rc; }
+    ORBB_CUDA(ce);
+    const cudaError_t ci = cudaGraphInstantiate(&h->graph_exec, graph, 0);
+    cudaGraphDestroy(graph);
+    ORBB_CUDA(ci);
+    h->graph_frames = nframes;
+    return ORBB_OK;
+}
+
+extern "C" int orbx_graph_launch(orbx_handle* h)
+{
+    if (!h) return ORBB_E_INVALID;
+    if (!h->graph_exec) return ORBB_E_STATE;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    ORBB_CUDA(cudaGraphLaunch(h->graph_exec, h->stream));
+    g_launches.fetch_add((uint64_t)(2 * h->nlevels + 1), std::memory_order_relaxed);      // level + octree kernels, descriptors
+    h->last_frames = h->graph_frames;
+    return ORBB_OK;
 }
 
 extern "C" int orbx_sync(orbx_handle* h)

@@ -1179,3 +1179,34 @@ extern "C" int orbb200_measure_imma_peak(int device, double* int8_tops)
     *int8_tops = best;
     return ORBB_OK;
 }
+
+// Measured tcgen05.mma kind::i8 rate (int8 TOP/s, 2 x multiply-adds) of the 128 x 256 x 32 shape the scan kernel issues, operands in
+// shared memory, accumulators in TMEM, nothing else running: the denominator of the brute-force top-2 roofline.
+extern "C" int orbb200_measure_tcgen05_i8_peak(int device, double* int8_tops)
+{
+    if (!int8_tops) return ORBB_E_INVALID;
+    int rc = check_device(device);
+    if (rc != ORBB_OK) return rc;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    ORBB_CUDA(cudaFuncSetAttribute(tc_i8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TCP_SMEM));
+    cudaEvent_t e0, e1;
+    ORBB_CUDA(cudaEventCreate(&e0)); ORBB_CUDA(cudaEventCreate(&e1));
+    const int groups = 4096;                                  // x 16 MMAs of 2 * 128 * 256 * 32 operations per CTA
+    double best = 0;
+    for (int rep = 0; rep < 5; rep++) {
+        ORBB_CUDA(cudaEventRecord(e0));
+        tc_i8_peak_kernel<<<sms, 128, TCP_SMEM>>>(groups, nullptr);
+        ORBB_LAUNCHED();
+        ORBB_CUDA(cudaEventRecord(e1));
+        ORBB_CUDA(cudaEventSynchronize(e1));
+        float ms = 0;
+        ORBB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double tops = (double)sms * groups * 16 * (2.0 * 128 * 256 * 32) / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tops > best) best = tops;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    ORBB_CUDA(cudaGetLastError());
+    *int8_tops = best;
+    return ORBB_OK;
+}

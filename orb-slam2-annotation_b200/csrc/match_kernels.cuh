@@ -1119,6 +1119,65 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcn_kernel(const __grid
     }
 }
 
+// Roofline probe: tcgen05.mma kind::i8 128 x 256 x 32 back to back from static shared-memory operands into the two accumulators the
+// scan kernel uses — no producers, no consumers, no global memory.  One CTA per SM, one issuing thread; groups of 16 MMAs are
+// committed to an mbarrier and the issuer stays two groups ahead of the tensor pipe.
+constexpr int TCP_SMEM = BT_TILE_BYTES + BN_BTILE;          // one A tile + one 256-row B tile = 96 KB
+__global__ void __launch_bounds__(128, 1) tc_i8_peak_kernel(int groups, int* sink)
+{
+    extern __shared__ __align__(128) uint8_t tp_smem[];
+    __shared__ __align__(8) unsigned long long bars[2];
+    __shared__ unsigned tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < TCP_SMEM / 4; i += 128) reinterpret_cast<unsigned*>(tp_smem)[i] = 0x01010101u;
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((unsigned)__cvta_generic_to_shared(&tmem_base_s)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = tmem_base_s;
+    constexpr unsigned IDESC = (2u << 4) | (1u << 7) | (32u << 17) | (8u << 24);      // s32 accumulate, u8 x s8 ... as bf_top2_tcn_kernel, N = 256
+    if (tid == 0) {
+        const unsigned long long adesc0 = bt_desc((unsigned)__cvta_generic_to_shared(tp_smem));
+        const unsigned long long bdesc0 = bt_desc((unsigned)__cvta_generic_to_shared(tp_smem + BT_TILE_BYTES));
+        for (int g = 0; g < groups; g++) {
+            if (g >= 2) bt_wait(bar0 + 8 * (g & 1), (unsigned)(((g >> 1) - 1) & 1));
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+#pragma unroll
+                for (int ks = 0; ks < 8; ks++) {
+                    const unsigned long long ad = adesc0 + (unsigned long long)(ks * 16), bd = bdesc0 + (unsigned long long)(ks * 16);
+                    if (ks == 0)
+                        asm volatile("{ .reg .pred p; setp.ne.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
+                                     ::"r"(tmem + (unsigned)(mt * 256)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
+                    else
+                        asm volatile("{ .reg .pred p; setp.eq.b32 p, 0, 0; tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%4, %4, %4, %4}, p; }"
+                                     ::"r"(tmem + (unsigned)(mt * 256)), "l"(ad), "l"(bd), "r"(IDESC), "r"(0u) : "memory");
+                }
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar0 + 8u * (g & 1)) : "memory");
+        }
+        for (int g = max(groups - 2, 0); g < groups; g++) bt_wait(bar0 + 8 * (g & 1), (unsigned)((g >> 1) & 1));
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (sink && groups < 0) sink[blockIdx.x] = (int)tmem;
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
 // Merge the per-chunk keys in ascending chunk (= ascending row) order: sequential-scan semantics.
 __global__ void bf_merge_chunks_kernel(const unsigned* __restrict__ k1, const unsigned* __restrict__ k2, int nchunks, int nq,
                                        long long rows_per_chunk, long long row_offset,

@@ -25,14 +25,14 @@ STAGE_BLUR, STAGE_FASTKPS, STAGE_LEVELKPS = 1, 2, 3
 
 # every symbol include/orbb200.h declares (tests check the .so exports all of them)
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "orbx_extract_batch_device",
-           "orbx_extract_batch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
+           "orbx_extract_batch", "orbx_graph_capture", "orbx_graph_launch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbx_set_rectification", "orbx_extract_batch_rectified", "orbx_remap_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_frame_create_device", "orbm_undistort_keypoints", "orbm_undistort_keypoints_device", "orbm_image_bounds",
            "orbm_search_by_projection_points_device", "orbm_search_by_projection_frame_device", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_bf_top2_noalloc", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
-           "orbv_compute_bow", "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak", "orbb200_measure_imma_peak",
+           "orbv_compute_bow", "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak", "orbb200_measure_imma_peak", "orbb200_measure_tcgen05_i8_peak",
            "orbb200_launch_count"]
 
 
@@ -67,6 +67,8 @@ def lib():
         L.orbx_get_tables.argtypes = [vp] + [vp] * 6
         L.orbx_extract.argtypes = [vp, vp, i32, i32, sz, vp, vp, i32, C.POINTER(i32)]
         L.orbx_extract_batch_device.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32]
+        L.orbx_graph_capture.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32]
+        L.orbx_graph_launch.argtypes = [vp]
         L.orbx_extract_batch.argtypes = [vp, vp, i32, i32, i32, sz, sz, vp, vp, vp, i32]
         L.orbx_extract_batch_color.argtypes = [vp, vp, i32, i32, i32, sz, sz, i32, i32, vp, vp, vp, i32]
         L.orbx_cvt_gray_device.argtypes = [vp, i32, i32, i32, sz, sz, i32, i32, vp, sz, sz, vp]
@@ -124,6 +126,7 @@ def lib():
         L.orbb200_last_cuda_error.restype = C.c_char_p
         L.orbb200_measure_popc_peak.argtypes = [i32, C.POINTER(C.c_double)]
         L.orbb200_measure_imma_peak.argtypes = [i32, C.POINTER(C.c_double)]
+        L.orbb200_measure_tcgen05_i8_peak.argtypes = [i32, C.POINTER(C.c_double)]
         L.orbb200_launch_count.restype = C.c_uint64
         _lib = L
     return _lib
@@ -155,6 +158,12 @@ def popc_peak(device=0):
 def imma_peak(device=0):
     v = C.c_double()
     _check(lib().orbb200_measure_imma_peak(device, C.byref(v)), "orbb200_measure_imma_peak")
+    return v.value
+
+
+def tcgen05_i8_peak(device=0):
+    v = C.c_double()
+    _check(lib().orbb200_measure_tcgen05_i8_peak(device, C.byref(v)), "orbb200_measure_tcgen05_i8_peak")
     return v.value
 
 
@@ -282,6 +291,14 @@ class ORBextractor:
         """Raw device-pointer entry (ints): asynchronous on the handle's stream."""
         _check(self.L.orbx_extract_batch_device(self.h, _p(imgs_ptr), F, w, h, stride, fstride, _p(kps_ptr),
                                                 _p(desc_ptr), _p(counts_ptr), capacity), "orbx_extract_batch_device")
+
+    def graph_capture(self, imgs_ptr, F, w, h, stride, fstride, kps_ptr, desc_ptr, counts_ptr, capacity):
+        """Capture the launch sequence of extract_batch_device on these buffers as a CUDA graph (orbx_graph_capture)."""
+        _check(self.L.orbx_graph_capture(self.h, _p(imgs_ptr), F, w, h, stride, fstride, _p(kps_ptr), _p(desc_ptr), _p(counts_ptr), capacity),
+               "orbx_graph_capture")
+
+    def graph_launch(self):
+        _check(self.L.orbx_graph_launch(self.h), "orbx_graph_launch")
 
     def sync(self):
         _check(self.L.orbx_sync(self.h), "orbx_sync")

@@ -389,3 +389,32 @@ def test_rectified_frames(gpu):
     ex.set_rectification(None, None, None)
     kps = np.zeros((F, 10), orbb200.KP_DTYPE); desc = np.zeros((F, 10, 32), np.uint8); cnt = np.zeros(F, np.int32)
     assert orbb200.lib().orbx_extract_batch_rectified(ex.h, raw.ctypes.data, F, sw, sw * sh, kps.ctypes.data, desc.ctypes.data, cnt.ctypes.data, 10) == orbb200.E_STATE
+
+
+def test_cuda_graph_replay_equals_plain_launches(gpu):
+    """orbx_graph_capture / orbx_graph_launch: the captured launch sequence gives the same keypoints and descriptors as
+    orbx_extract_batch_device on the same buffers, on replays with new image content, and reports its state errors."""
+    import torch, orbb200
+    from synth import synth
+    W, H, CAP, B = 640, 480, 1280, 2
+    ex = orbb200.ORBextractor(1000, max_size=(W, H), max_batch=B)
+    assert ex.L.orbx_graph_launch(ex.h) == orbb200.E_STATE                  # nothing captured yet
+    imgs = torch.from_numpy(np.stack([synth(W, H, 71), synth(W, H, 72)])).cuda()
+    k = torch.zeros((B, CAP, 7), device="cuda"); d = torch.zeros((B, CAP, 32), dtype=torch.uint8, device="cuda"); c = torch.zeros(B, dtype=torch.int32, device="cuda")
+    ex.graph_capture(imgs.data_ptr(), B, W, H, W, W * H, k.data_ptr(), d.data_ptr(), c.data_ptr(), CAP)
+    for seeds in ((71, 72), (73, 74)):
+        imgs.copy_(torch.from_numpy(np.stack([synth(W, H, s) for s in seeds])).cuda())
+        torch.cuda.synchronize()
+        ex.extract_batch_device(imgs.data_ptr(), B, W, H, W, W * H, k.data_ptr(), d.data_ptr(), c.data_ptr(), CAP)
+        ex.sync()
+        rk, rd, rc = k.clone(), d.clone(), c.clone()
+        k.zero_(); d.zero_(); c.zero_()
+        torch.cuda.synchronize()
+        ex.graph_launch(); ex.sync()
+        assert torch.equal(c, rc) and int(c.min()) >= 1000
+        for f in range(B):
+            n = int(c[f])
+            assert torch.equal(k[f, :n].view(torch.int32), rk[f, :n].view(torch.int32)) and torch.equal(d[f, :n], rd[f, :n])      # bit patterns: class_id -1 reads as NaN
+    ex.set_profiling(True)
+    assert ex.L.orbx_graph_capture(ex.h, orbb200._p(imgs.data_ptr()), B, W, H, W, W * H, orbb200._p(k.data_ptr()), orbb200._p(d.data_ptr()),
+                                   orbb200._p(c.data_ptr()), CAP) == orbb200.E_STATE

@@ -589,3 +589,13 @@ def test_reloc_max_dist_above_255_stays_in_bounds(gpu):
     mp0 = np.zeros(len(kc), np.int32)                                              # every feature already has a MapPoint
     n, mp = orbb200.ORBmatcher(0.9, True).SearchByProjection_reloc(F, q, mp0, 300)
     assert n == 0 and np.array_equal(mp, mp0)
+
+
+def test_tensor_peak_probes(gpu):
+    """The roofline denominators are measured, not assumed: the tcgen05 kind::i8 probe must land between the legacy mma.sync
+    rate and a loose ceiling above the nominal 4.5 POP/s."""
+    import orbb200
+    legacy = orbb200.imma_peak(0)
+    tc = orbb200.tcgen05_i8_peak(0)
+    assert 500 < legacy < 2500
+    assert 2 * legacy < tc < 6000, (legacy, tc)
