@@ -500,6 +500,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             int k = 0;
             while ((2 << k) - 1 <= h->cfg.min_th_fast && k < 7) k++;
             if (k >= 1) { a.qmask = ((0xffu << k) & 0xffu) * 0x01010101u; a.qadd = (0x80u - (1u << (k - 1))) * 0x01010101u; }
+            else { a.qmask = 0; a.qadd = 0x80808080u; }           // every valid pixel passes
         }
         if (h->l3_warps == 8) {
             dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, 8 * L3_RG), nframes);

@@ -101,7 +101,10 @@ __device__ __forceinline__ int l3_arc_score(const uint8_t* c)
 
 // LEGACY: the Q8 kernel of OpenCV <= 3.3 sums to 257, so the rounded result needs a clamp (default kernel: it is byte 2 of the sum).
 template <int NW, bool LEGACY>
-__global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const __grid_constant__ Level3Args a)
+#ifndef L3_MINB
+#define L3_MINB 8
+#endif
+__global__ void __launch_bounds__(32 * NW, NW == 4 ? L3_MINB : L3_MINB / 2) level3_kernel(const __grid_constant__ Level3Args a)
 {
     constexpr int TH = L3_RG * NW, SMH = TH + 8, SCH = TH + 2, NT = 32 * NW;
     constexpr int QCAP = SCH * 122;                      // every scored pixel a candidate (uniform-noise images)
@@ -311,7 +314,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
             const int s = sb + it, gy = y0 + s;
             if (s <= TH && gy >= 19 && gy <= a.h - 20) rowok |= 1u << it;
         }
-        unsigned m0 = 0, m1 = 0;                                  // private candidate flags: 4 bits per row, rows it = 0..7 | 8
+        // private candidate flags: byte b of m0 holds rows it = 0..7 of pixel b (bit it), m1 holds row 8 at bit 7 of byte b
+        unsigned m0 = 0, m1 = 0;
         if (rowok) {                                              // warp-uniform
             const uint32_t* rp = tw + (sb + 1) * L3_SP + lane;   // staged row j of the window = tile row sb - 3 + j
             unsigned Vw[7], Aw[7] = {}, Bw[7] = {};              // sliding window: own word, +2-pixel view, -2-pixel view
@@ -335,29 +339,30 @@ __global__ void __launch_bounds__(32 * NW, NW == 4 ? 8 : 4) level3_kernel(const 
                 const unsigned p4c = (__vabsdiffu4(V, Cw) | __vabsdiffu4(V, Dw)) & M;
                 const unsigned p2a = (__vabsdiffu4(V, Aw[5]) | __vabsdiffu4(V, Bw[1])) & M;
                 const unsigned p6e = (__vabsdiffu4(V, Aw[1]) | __vabsdiffu4(V, Bw[5])) & M;
-                unsigned cand = ((p08 >> 1) + C) & ((p4c >> 1) + C) & ((p2a >> 1) + C) & ((p6e >> 1) + C) & valid;
-                if (a.qmask == 0) cand = valid;                                      // minTh == 0: no quick reject possible
-                if (!((rowok >> it) & 1u)) cand = 0;
-                const unsigned nib = (((cand >> 7) * 0x00204081u) >> 21) & 15u;
-                if (it < 8) m0 |= nib << (4 * (it & 7)); else m1 = nib;
+                // minTh == 0: the host passes M = 0, C = 0x80 per byte, so every valid pixel is a candidate
+                const unsigned cand = ((p08 >> 1) + C) & ((p4c >> 1) + C) & ((p2a >> 1) + C) & ((p6e >> 1) + C) & valid;
+                if (it < 8) m0 = (m0 >> 1) + cand;               // after row 7: bit it of byte b = row it (no carry: bit 7 of m0 >> 1 is byte b + 1's
+                else m1 = cand;                                   // bit 0, which only fills on the eighth shift)
 #pragma unroll
                 for (int j = 0; j < 6; j++) { Vw[j] = Vw[j + 1]; Aw[j] = Aw[j + 1]; Bw[j] = Bw[j + 1]; }
             }
+            m0 &= (rowok & 0xffu) * 0x01010101u;                  // rows outside the scored range (image border tiles)
+            if (!(rowok & 0x100u)) m1 = 0;
         }
         // each lane appends its own candidates: one shared atomic per lane, no warp scan (queue order is irrelevant)
         const int n = __popc(m0) + __popc(m1);
         if (n) {
             int slot = atomicAdd(&s_qn, n);
             const int pbase = (sb + 1) * L3_SCP + 4 * lane;      // position of (row sb, byte 0 of this lane's word)
-            while (m0) {                                          // bit t = 4 * it + byte  ->  pbase + it * L3_SCP + byte
+            while (m0) {                                          // bit t = 8 * byte + it  ->  pbase + it * L3_SCP + byte
                 const int t = __ffs((int)m0) - 1;
                 m0 &= m0 - 1;
-                queue[slot++] = (uint16_t)(pbase + (((t << 5) | t) & 0x383));
+                queue[slot++] = (uint16_t)(pbase + ((t & 7) << 7) + (t >> 3));
             }
-            while (m1) {
+            while (m1) {                                          // bit t = 8 * byte + 7
                 const int t = __ffs((int)m1) - 1;
                 m1 &= m1 - 1;
-                queue[slot++] = (uint16_t)(pbase + 8 * L3_SCP + t);
+                queue[slot++] = (uint16_t)(pbase + 8 * L3_SCP + (t >> 3));
             }
         }
     }
