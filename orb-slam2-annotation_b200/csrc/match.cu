@@ -901,8 +901,8 @@ extern "C" int orbm_db_create(orbm_db** out, int64_t capacity_rows, int64_t row_
     if (!db) return ORBB_E_NOMEM;
     db->device = device; db->capacity = capacity_rows; db->row_offset = row_offset;
     const char* v = getenv("ORBB_BF_VARIANT");
-    db->variant = v ? atoi(v) : 3;            // 3: tcgen05 / TMEM (warp-specialised, N = 256 MMAs), 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
-    if (db->variant < 0 || db->variant > 3) db->variant = 3;
+    db->variant = v ? atoi(v) : -1;           // -1 (default): 4 when a call has more than 256 queries, else 3; 4: tcgen05 on a CTA pair (cta_group::2, 512 queries per pair), 3: tcgen05 / TMEM (warp-specialised, N = 256 MMAs), 2: legacy mma.sync (IMMA), 1: integer pipe with carry-save adders, 0: plain XOR + POPC
+    if (db->variant < 0 || db->variant > 4) db->variant = -1;
     if (cudaMalloc((void**)&db->d_rows, (size_t)(capacity_rows > 0 ? capacity_rows : 1) * 32) != cudaSuccess) {
         set_cuda_error(cudaGetLastError(), "orbm_db_create: cudaMalloc");
         delete db;
@@ -935,12 +935,21 @@ static int db_append(orbm_db* db, const uint8_t* rows, int64_t n, cudaMemcpyKind
 extern "C" int orbm_db_append(orbm_db* db, const uint8_t* rows_host, int64_t n) { return db_append(db, rows_host, n, cudaMemcpyHostToDevice); }
 extern "C" int orbm_db_append_device(orbm_db* db, const uint8_t* rows_dev, int64_t n) { return db_append(db, rows_dev, n, cudaMemcpyDeviceToDevice); }
 
+// Kernel of one search: ORBB_BF_VARIANT when given, else the CTA-pair kernel for wide, long scans (its 512-query tile and its
+// longer prologue pay off above 256 queries and about two million rows) and the single-CTA tcgen05 kernel otherwise.
+static int bf_variant(const orbm_db* db, int nq)
+{
+    if (db->variant >= 0) return db->variant;
+    return (nq > 256 && db->rows >= 2000000) ? 4 : 3;
+}
+
 static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nchunks)
 {
+    const int variant = bf_variant(db, nq);
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, db->device);
-    const int qtiles = ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE);
-    int target = ceil_div(sms * (db->variant >= 3 ? 2 : 4), qtiles);                         // ~4 CTAs per SM in flight (variant 2: two waves of two)
+    const int qtiles = ceil_div(nq, variant >= 4 ? B2_QTILE : variant >= 2 ? BM_QTILE : BF_QTILE);
+    int target = ceil_div(variant >= 4 ? sms : sms * (variant == 3 ? 2 : 4), qtiles);      // two waves (variant 4: of sms / 2 CTA pairs); integer-pipe kernels: ~4 CTAs per SM in flight
     long long rpc = (db->rows + target - 1) / target;
     rpc = (rpc + 255) / 256 * 256;                                  // a multiple of every kernel's stage size
     if (rpc < BF_ROWS) rpc = BF_ROWS;
@@ -987,8 +996,18 @@ extern "C" int orbm_bf_top2_device(orbm_db* db, const uint8_t* q_dev, int nq, in
     BfArgs a;
     a.db = db->d_rows; a.nrows = db->rows; a.q = (const uint4*)q_dev; a.nq = nq;
     a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = db->d_k1; a.part_k2 = db->d_k2;
-    dim3 grid(ceil_div(nq, db->variant >= 2 ? BM_QTILE : BF_QTILE), nchunks);
-    if (db->variant >= 3) {
+    const int variant = bf_variant(db, nq);
+    dim3 grid(ceil_div(nq, variant >= 2 ? BM_QTILE : BF_QTILE), nchunks);
+    if (variant == 4) {
+        static std::atomic<bool> attr2_set[64];
+        const int dv = db->device & 63;
+        if (!attr2_set[dv].load(std::memory_order_acquire)) {
+            ORBB_CUDA(cudaFuncSetAttribute(bf_top2_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, B2_SMEM));
+            attr2_set[dv].store(true, std::memory_order_release);
+        }
+        bf_top2_tc2_kernel<<<dim3(2 * ceil_div(nq, B2_QTILE), nchunks), B2_THREADS, B2_SMEM, st>>>(a);      // clusters of 2 along x
+    }
+    else if (variant == 3) {
         // more than 48 KB of dynamic shared memory is an opt-in per device
         static std::atomic<bool> attr_set[64];                   // setting it twice is harmless; the flag only saves the call
         const int dv = db->device & 63;
@@ -998,8 +1017,8 @@ extern "C" int orbm_bf_top2_device(orbm_db* db, const uint8_t* q_dev, int nq, in
         }
         bf_top2_tcn_kernel<<<grid, BW_THREADS, BN_SMEM, st>>>(a);
     }
-    else if (db->variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
-    else if (db->variant == 2) bf_top2_mma_kernel<<<grid, BM_THREADS, 0, st>>>(a);
+    else if (variant == 0) bf_top2_kernel<0><<<grid, BF_THREADS, 0, st>>>(a);
+    else if (variant == 2) bf_top2_mma_kernel<<<grid, BM_THREADS, 0, st>>>(a);
     else bf_top2_kernel<1><<<grid, BF_THREADS, 0, st>>>(a);
     ORBB_LAUNCHED();
     bf_merge_chunks_kernel<<<ceil_div(nq, 256), 256, 0, st>>>(db->d_k1, db->d_k2, nchunks, nq, rpc, db->row_offset, d1, (long long*)i1, d2);
@@ -1189,20 +1208,24 @@ extern "C" int orbb200_measure_tcgen05_i8_peak(int device, double* int8_tops)
     if (rc != ORBB_OK) return rc;
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const bool pair = getenv("ORBB_PEAK_PAIR") != nullptr;             // experiment: the same probe with cta_group::2 on CTA pairs
     ORBB_CUDA(cudaFuncSetAttribute(tc_i8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TCP_SMEM));
+    ORBB_CUDA(cudaFuncSetAttribute(tc2_i8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TCP_SMEM));
     cudaEvent_t e0, e1;
     ORBB_CUDA(cudaEventCreate(&e0)); ORBB_CUDA(cudaEventCreate(&e1));
     const int groups = 4096;                                  // x 16 MMAs of 2 * 128 * 256 * 32 operations per CTA
     double best = 0;
     for (int rep = 0; rep < 5; rep++) {
         ORBB_CUDA(cudaEventRecord(e0));
-        tc_i8_peak_kernel<<<sms, 128, TCP_SMEM>>>(groups, nullptr);
+        const int ncols = getenv("ORBB_PEAK_N") ? atoi(getenv("ORBB_PEAK_N")) : 256;
+        if (pair) tc2_i8_peak_kernel<<<sms & ~1, 128, TCP_SMEM>>>(groups, ncols);      // each MMA is twice the work: same operations per CTA
+        else tc_i8_peak_kernel<<<sms, 128, TCP_SMEM>>>(groups, nullptr);
         ORBB_LAUNCHED();
         ORBB_CUDA(cudaEventRecord(e1));
         ORBB_CUDA(cudaEventSynchronize(e1));
         float ms = 0;
         ORBB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-        const double tops = (double)sms * groups * 16 * (2.0 * 128 * 256 * 32) / (ms * 1e-3) / 1e12;
+        const double tops = (double)sms * groups * 16 * (2.0 * 128 * (pair && getenv("ORBB_PEAK_N") ? atoi(getenv("ORBB_PEAK_N")) : 256) * 32) / (ms * 1e-3) / 1e12;
         if (rep > 0 && tops > best) best = tops;
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);

@@ -1119,6 +1119,280 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcn_kernel(const __grid
     }
 }
 
+// ------------------------------------------------------------------------------------------------------
+// Brute-force top-2 on a CTA PAIR (thread-block cluster of 2, tcgen05 cta_group::2): one MMA is 256 queries x 256 rows x 32 bits, each
+// CTA holding 128 of its query rows (A) and staging 128 of the stage's 256 database rows (B); the tensor cores exchange the B
+// halves themselves.  A pair keeps two such query sets (512 queries) resident, so every expanded row feeds 512 queries instead of
+// 256: per multiply-add, half the bit -> byte expansion work and a third of the shared-memory operand reads of bf_top2_tcn_kernel
+// (which is level between the shared-memory port and the tensor pipe).  Roles per CTA are those of bf_top2_tcn_kernel; only the
+// leader CTA's MMA thread issues.  Cross-CTA protocol: producers and consumers of BOTH CTAs arrive on the LEADER's full / accempty
+// barriers (mapa + mbarrier.arrive.release.cluster); tcgen05.commit multicasts to the empty / accfull barriers of both CTAs.
+// Output: the same per-(chunk, query) packed keys as the other kernels.
+// ------------------------------------------------------------------------------------------------------
+constexpr int B2_QTILE = 512;                            // queries per CTA pair
+constexpr int B2_STAGES = 4;
+constexpr int B2_BTILE = 128 * 256;                      // one CTA's half of a 256-row stage, expanded
+constexpr int B2_SMEM = 2 * BT_TILE_BYTES + B2_STAGES * B2_BTILE + 2 * 256 * 16;      // 204800 B
+constexpr int B2_PROD_WARPS = 2;                         // 64 producer threads: two database rows each per stage
+constexpr int B2_THREADS = 32 * (B2_PROD_WARPS + BW_CONS_WARPS + 1);               // 608: leaves 96 registers per thread (the consumers hold 64 accumulator columns)
+
+// Wait on a local barrier.  CTA-scope acquire on purpose: what the barriers of this kernel order is shared memory written for / TMEM
+// read by the tensor cores, never global data of the peer, and a cluster-scope acquire makes ptxas invalidate the whole L1
+// (CCTL.IVALL) after every successful wait, twice on the accumulator hand-over path.  A protocol bug traps instead of hanging the GPU.
+__device__ __forceinline__ void b2_wait(unsigned mbar, unsigned parity)
+{
+    unsigned done = 0;
+    for (unsigned spin = 0; !done; spin++) {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(mbar), "r"(parity) : "memory");
+        if (spin > (1u << 27)) __trap();
+    }
+}
+__device__ __forceinline__ void b2_arrive_leader(unsigned mbar_local)              // arrive on the barrier at this offset in CTA 0 of the cluster
+{
+    unsigned remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(remote) : "r"(mbar_local));
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+
+__device__ __forceinline__ void b2_arrive_leader_relaxed(unsigned mbar_local)     // no data to publish (the TMEM reads have completed)
+{
+    unsigned remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(remote) : "r"(mbar_local));
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(B2_THREADS, 1) bf_top2_tc2_kernel(const __grid_constant__ BfArgs a)
+{
+    extern __shared__ __align__(128) uint8_t bt_smem[];
+    __shared__ __align__(8) unsigned long long bars[2 * B2_STAGES + 4];      // full[S] | empty[S] | accfull[2] | accempty[2]
+    __shared__ unsigned tmem_base_s;
+    __shared__ int thr_s[2 * 128];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    const int chunk = blockIdx.y;
+    const int qbase = (blockIdx.x >> 1) * B2_QTILE + 128 * (int)rank;          // query of (set mt, row) = qbase + 256 * mt + row
+    const long long r_begin = (long long)chunk * a.rows_per_chunk;
+    const long long r_end = min(a.nrows, r_begin + a.rows_per_chunk);
+    const int nrows = (int)(r_end - r_begin);
+    const int nstages = (nrows + 255) / 256;
+    uint8_t* const As = bt_smem;
+    uint8_t* const Bs = bt_smem + 2 * BT_TILE_BYTES;
+    uint4* const raw = reinterpret_cast<uint4*>(bt_smem + 2 * BT_TILE_BYTES + B2_STAGES * B2_BTILE);      // [2][256]
+    const unsigned As_addr = (unsigned)__cvta_generic_to_shared(As), Bs_addr = (unsigned)__cvta_generic_to_shared(Bs);
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
+    const unsigned full0 = bar0, empty0 = bar0 + 8 * B2_STAGES, accfull0 = bar0 + 16 * B2_STAGES, accempty0 = accfull0 + 16;
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((unsigned)__cvta_generic_to_shared(&tmem_base_s)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    if (tid == 0) {
+        for (int s = 0; s < B2_STAGES; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(2 * B2_PROD_WARPS));     // both CTAs' producer warps
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(empty0 + 8 * s));
+        }
+        for (int b = 0; b < 2; b++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(accfull0 + 8 * b));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(accempty0 + 8 * b), "r"(2 * BW_CONS_WARPS));  // both CTAs' consumer warps
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 256) thr_s[tid] = -100000;
+    // ---- A tiles: this CTA's 128 rows of both query sets, +1 / -1 bytes, canonical K-major layout ----
+    for (int i = tid; i < 2048; i += B2_THREADS) {
+        const int r8 = i & 7, wd = (i >> 3) & 7, row256 = (i >> 6) * 8 + r8;
+        const int qi = qbase + 256 * (row256 >> 7) + (row256 & 127);
+        const bool ok = qi < a.nq;
+        const unsigned w = ok ? reinterpret_cast<const unsigned*>(a.q)[(long long)qi * 8 + wd] : 0u;
+        uint4 lo, hi;
+        lo.x = bm_spread_pm1(w & 15u); lo.y = bm_spread_pm1((w >> 4) & 15u); lo.z = bm_spread_pm1((w >> 8) & 15u); lo.w = bm_spread_pm1((w >> 12) & 15u);
+        hi.x = bm_spread_pm1((w >> 16) & 15u); hi.y = bm_spread_pm1((w >> 20) & 15u); hi.z = bm_spread_pm1((w >> 24) & 15u); hi.w = bm_spread_pm1(w >> 28);
+        if (!ok) { lo = make_uint4(0, 0, 0, 0); hi = lo; }
+        uint8_t* dst = As + (row256 >> 7) * BT_TILE_BYTES + bt_off(row256 & 127, wd * 32);
+        *reinterpret_cast<uint4*>(dst) = lo;
+        *reinterpret_cast<uint4*>(dst + 128) = hi;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    // both CTAs' barriers, A tiles and TMEM exist before anyone arrives remotely or the leader issues
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = tmem_base_s;
+    constexpr unsigned IDESC = (2u << 4) | (1u << 7) | (32u << 17) | (16u << 24);     // s32 accumulators, A signed / B unsigned 8 bit, N = 256, M = 256
+
+    int pq[2] = {0, 0}, thr[2] = {0x7fffffff, 0x7fffffff};
+    unsigned k1[2] = {0xffffffffu, 0xffffffffu}, k2[2] = {0xffffffffu, 0xffffffffu};
+    const int quarter = warp & 3, cg = (warp - B2_PROD_WARPS) >> 2, row = 32 * quarter + lane;
+
+    if (warp < B2_PROD_WARPS) {
+        // ================= producers: this CTA's 128 rows of every stage; thread t owns rows t and t + 64 (four 16-byte copies) =================
+        auto load_stage = [&](int s, int buf) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const long long grow = r_begin + (long long)s * 256 + 128 * (int)rank + tid + 64 * h;
+#pragma unroll
+                for (int u = 0; u < 2; u++) {
+                    const uint4* src = a.db + (grow < r_end ? grow * 2 + u : 0);
+                    const unsigned dst = (unsigned)__cvta_generic_to_shared(&raw[(buf * 128 + tid + 64 * h) * 2 + u]);
+                    const int bytes = grow < r_end ? 16 : 0;
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes));
+                }
+            }
+            asm volatile("cp.async.commit_group;");
+        };
+        if (nstages > 0) load_stage(0, 0);
+        for (int it = 0; it < nstages; it++) {
+            const int s = it % B2_STAGES, n = it / B2_STAGES;
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            uint4 rv[4];
+#pragma unroll
+            for (int h = 0; h < 2; h++) { rv[2 * h] = raw[((it & 1) * 128 + tid + 64 * h) * 2]; rv[2 * h + 1] = raw[((it & 1) * 128 + tid + 64 * h) * 2 + 1]; }
+            if (it + 1 < nstages) load_stage(it + 1, (it + 1) & 1);
+            if (it >= B2_STAGES) b2_wait(empty0 + 8 * s, (unsigned)((n - 1) & 1));      // the MMAs that read this tile have completed
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                uint8_t* dst = Bs + s * B2_BTILE + bt_off(tid + 64 * h, 0);
+#pragma unroll
+                for (int u = 0; u < 2; u++) {
+                    const unsigned wv[4] = {rv[2 * h + u].x, rv[2 * h + u].y, rv[2 * h + u].z, rv[2 * h + u].w};
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const unsigned w = wv[j];
+                        *reinterpret_cast<uint4*>(dst + 1024 * u + 256 * j) = make_uint4(bm_spread01(w & 15u), bm_spread01((w >> 4) & 15u), bm_spread01((w >> 8) & 15u), bm_spread01((w >> 12) & 15u));
+                        *reinterpret_cast<uint4*>(dst + 1024 * u + 256 * j + 128) = make_uint4(bm_spread01((w >> 16) & 15u), bm_spread01((w >> 20) & 15u), bm_spread01((w >> 24) & 15u), bm_spread01(w >> 28));
+                    }
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) b2_arrive_leader(full0 + 8 * s);
+        }
+    } else if (warp == B2_PROD_WARPS + BW_CONS_WARPS) {
+        // ================= MMA issuer: leader CTA only =================
+        if (rank == 0 && lane == 0) {
+            const unsigned long long adesc0 = bt_desc(As_addr), bdesc0 = bt_desc(Bs_addr);
+            for (int it = 0; it < nstages; it++) {
+                const int s = it % B2_STAGES, n = it / B2_STAGES;
+                b2_wait(full0 + 8 * s, (unsigned)(n & 1));
+                const unsigned long long bd0 = bdesc0 + (unsigned long long)(s * (B2_BTILE >> 4));
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    if (it >= 1) b2_wait(accempty0 + 8 * mt, (unsigned)((it - 1) & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                    for (int ks = 0; ks < 8; ks++) {
+                        const unsigned long long ad = adesc0 + (unsigned long long)(mt * (BT_TILE_BYTES >> 4) + ks * 16), bd = bd0 + (unsigned long long)(ks * 16);
+                        if (ks == 0)
+                            asm volatile("{ .reg .pred p; setp.ne.b32 p, 0, 0; tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p; }"
+                                         ::"r"(tmem + (unsigned)(mt * 256)), "l"(ad), "l"(bd), "r"(IDESC) : "memory");
+                        else
+                            asm volatile("{ .reg .pred p; setp.eq.b32 p, 0, 0; tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p; }"
+                                         ::"r"(tmem + (unsigned)(mt * 256)), "l"(ad), "l"(bd), "r"(IDESC) : "memory");
+                    }
+                    // (the last uses of a stage are not followed by a refill: no empty signal, so nothing arrives at a CTA that is leaving)
+                    if (mt == 1 && it + B2_STAGES < nstages)
+                        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(empty0 + 8u * s), "h"((unsigned short)3) : "memory");
+                    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(accfull0 + 8u * mt), "h"((unsigned short)3) : "memory");
+                }
+            }
+        }
+    } else {
+        // ================= consumers: this CTA's 128 query rows of both sets =================
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) {
+            const int qi = qbase + 256 * mt + row;
+            if (qi < a.nq) {
+                const uint4 v0 = a.q[2 * qi], v1 = a.q[2 * qi + 1];
+                pq[mt] = __popc(v0.x) + __popc(v0.y) + __popc(v0.z) + __popc(v0.w) + __popc(v1.x) + __popc(v1.y) + __popc(v1.z) + __popc(v1.w);
+                thr[mt] = pq[mt] - 511;
+            }
+        }
+        for (int e = 0; e < nstages; e++) {
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+                b2_wait(accfull0 + 8 * mt, (unsigned)(e & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                // this warp's 64 columns of the set: both loads in flight, one wait, and the buffer is handed back before any filtering
+                // (.pack::16b loads, two columns per register, were tried: the TMEM read gets slower, not faster)
+                int vv[2][32];
+                BT_LD32(vv[0], tmem + ((unsigned)(32 * quarter) << 16) + (unsigned)(mt * 256 + 64 * cg));
+                BT_LD32(vv[1], tmem + ((unsigned)(32 * quarter) << 16) + (unsigned)(mt * 256 + 64 * cg + 32));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) b2_arrive_leader_relaxed(accempty0 + 8 * mt);       // nothing to publish: the TMEM reads have completed
+                thr[mt] = max(thr[mt], thr_s[mt * 128 + row]);
+#pragma unroll
+                for (int part = 0; part < 2; part++) {
+                    const int (&v)[32] = vv[part];
+                    const int cbase = e * 256 + 64 * cg + 32 * part;
+                    int gm[4];
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        int t3 = __vimax3_s32(v[8 * q], v[8 * q + 1], v[8 * q + 2]);
+                        t3 = __vimax3_s32(t3, v[8 * q + 3], v[8 * q + 4]);
+                        t3 = __vimax3_s32(t3, v[8 * q + 5], v[8 * q + 6]);
+                        gm[q] = max(t3, v[8 * q + 7]);
+                    }
+                    if (max(__vimax3_s32(gm[0], gm[1], gm[2]), gm[3]) >= thr[mt]) {
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            if (gm[q] < thr[mt]) continue;
+#pragma unroll
+                            for (int c = 8 * q; c < 8 * q + 8; c++) {
+                                const int idx = cbase + c;
+                                if (v[c] >= thr[mt] && idx < nrows) {
+                                    const unsigned key = ((unsigned)(pq[mt] - v[c]) << BF_IDX_BITS) | (unsigned)idx;
+                                    k2[mt] = min(k2[mt], max(k1[mt], key));
+                                    k1[mt] = min(k1[mt], key);
+                                    thr[mt] = pq[mt] - (int)(k2[mt] >> BF_IDX_BITS);
+                                }
+                            }
+                        }
+                        if (thr[mt] != 0x7fffffff) atomicMax(&thr_s[mt * 128 + row], thr[mt]);
+                    }
+                }
+            }
+        }
+    }
+    // ---- merge the four column groups of a query row through shared memory.  The B ring is free only once BOTH CTAs have consumed
+    //      every MMA (the peer's tensor core reads this CTA's half): cluster barrier first ----
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    unsigned* const scratch = reinterpret_cast<unsigned*>(Bs);         // [4][2][128][2]
+    const bool consumer = warp >= B2_PROD_WARPS && warp < B2_PROD_WARPS + BW_CONS_WARPS;
+    if (consumer) {
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) { scratch[((cg * 2 + mt) * 128 + row) * 2] = k1[mt]; scratch[((cg * 2 + mt) * 128 + row) * 2 + 1] = k2[mt]; }
+    }
+    __syncthreads();
+    if (consumer && cg == 0) {
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) {
+            unsigned x1 = k1[mt], x2 = k2[mt];
+            for (int g = 1; g < 4; g++) {
+                const unsigned y1 = scratch[((g * 2 + mt) * 128 + row) * 2], y2 = scratch[((g * 2 + mt) * 128 + row) * 2 + 1];
+                x2 = min(max(x1, y1), min(x2, y2));
+                x1 = min(x1, y1);
+            }
+            const int qi = qbase + 256 * mt + row;
+            if (qi < a.nq) {
+                a.part_k1[(long long)chunk * a.nq + qi] = x1;
+                a.part_k2[(long long)chunk * a.nq + qi] = x2;
+            }
+        }
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
 // Roofline probe: tcgen05.mma kind::i8 128 x 256 x 32 back to back from static shared-memory operands into the two accumulators the
 // scan kernel uses — no producers, no consumers, no global memory.  One CTA per SM, one issuing thread; groups of 16 MMAs are
 // committed to an mbarrier and the issuer stays two groups ahead of the tensor pipe.
@@ -1175,6 +1449,69 @@ __global__ void __launch_bounds__(128, 1) tc_i8_peak_kernel(int groups, int* sin
     if (warp == 0) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+    }
+}
+
+// The same probe on CTA pairs: tcgen05.mma cta_group::2 kind::i8 256 x 256 x 32 (each CTA 128 A rows and 128 B rows in shared memory),
+// issued by the leader, completion multicast to both CTAs.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1) tc2_i8_peak_kernel(int groups, int ncols)
+{
+    extern __shared__ __align__(128) uint8_t tp_smem[];
+    __shared__ __align__(8) unsigned long long bars[2];
+    __shared__ unsigned tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    unsigned rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    for (int i = tid; i < (BT_TILE_BYTES + B2_BTILE) / 4; i += 128) reinterpret_cast<unsigned*>(tp_smem)[i] = 0x01010101u;
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((unsigned)__cvta_generic_to_shared(&tmem_base_s)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const unsigned tmem = tmem_base_s;
+    const unsigned IDESC = (2u << 4) | (1u << 7) | ((unsigned)(ncols >> 3) << 17) | (16u << 24);
+    const int nbuf = 512 / ncols;
+    if (tid == 0 && rank == 0) {
+        const unsigned long long adesc0 = bt_desc((unsigned)__cvta_generic_to_shared(tp_smem));
+        const unsigned long long bdesc0 = bt_desc((unsigned)__cvta_generic_to_shared(tp_smem + BT_TILE_BYTES));
+        for (int g = 0; g < groups; g++) {
+            if (g >= 2) b2_wait(bar0 + 8 * (g & 1), (unsigned)(((g >> 1) - 1) & 1));
+#pragma unroll
+            for (int mt = 0; mt < 2; mt++) {
+                const unsigned dcol = (unsigned)(((2 * g + mt) % nbuf) * ncols);
+#pragma unroll
+                for (int ks = 0; ks < 8; ks++) {
+                    const unsigned long long ad = adesc0 + (unsigned long long)(ks * 16), bd = bdesc0 + (unsigned long long)(ks * 16);
+                    if (ks == 0)
+                        asm volatile("{ .reg .pred p; setp.ne.b32 p, 0, 0; tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p; }"
+                                     ::"r"(tmem + dcol), "l"(ad), "l"(bd), "r"(IDESC) : "memory");
+                    else
+                        asm volatile("{ .reg .pred p; setp.eq.b32 p, 0, 0; tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p; }"
+                                     ::"r"(tmem + dcol), "l"(ad), "l"(bd), "r"(IDESC) : "memory");
+                }
+            }
+            asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar0 + 8u * (g & 1)), "h"((unsigned short)1) : "memory");
+        }
+        for (int g = max(groups - 2, 0); g < groups; g++) b2_wait(bar0 + 8 * (g & 1), (unsigned)((g >> 1) & 1));
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (warp == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
     }
 }
 

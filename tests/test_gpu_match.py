@@ -178,9 +178,9 @@ def test_bf_top2_small_and_edges(gpu):
     assert len(orbb200.DescriptorDB(4).top2(q[:0])[0]) == 0
 
 
-@pytest.mark.parametrize("variant", ["0", "1", "2", "3"])
+@pytest.mark.parametrize("variant", ["0", "1", "2", "3", "4"])
 def test_bf_top2_every_kernel_variant(gpu, variant, monkeypatch):
-    """Every brute-force kernel (plain POPC, carry-save integer pipe, legacy mma.sync IMMA, tcgen05 + TMEM = default) against the oracle: duplicates (first index wins, d2 == d1), all-zero and all-one descriptors
+    """Every brute-force kernel (plain POPC, carry-save integer pipe, legacy mma.sync IMMA, tcgen05 + TMEM on one CTA, tcgen05 cta_group::2 on a CTA pair) against the oracle: duplicates (first index wins, d2 == d1), all-zero and all-one descriptors
     (|q| = 0 / 256: the extremes of hamming = |q| - sum a.b), ragged query and row counts around the 128-row stage and the
     256-query tile, and row counts that leave empty trailing chunks."""
     import orbb200, pyoracle
