@@ -26,6 +26,16 @@ void set_cuda_error(cudaError_t e, const char* what);
 
 #define ORBB_LAUNCHED() (::orbb::g_launches.fetch_add(1, std::memory_order_relaxed))
 
+// Scratch allocator of the matcher / vocabulary entry points: device blocks are cached per device in power-of-two size classes, so the
+// per-frame calls (orbm_frame_create, orbm_window_search, the Search* functions, orbm_stereo_match ...) stop calling cudaMalloc /
+// cudaFree after their first use - those calls serialise the device and cost ~100 us per frame on the tracking thread.
+// A block is handed back only when no queued work can still touch it (the host-pointer entry points synchronise before they return;
+// orbm_frame_destroy synchronises the streams the frame was used on).  Blocks above 64 MiB and anything beyond 1 GiB cached per
+// device go straight to cudaMalloc / cudaFree.  Defined in extract.cu.
+void* scratch_alloc(size_t bytes, size_t* granted);      // nullptr on failure (the CUDA error is recorded)
+void scratch_free(void* p, size_t granted);
+void scratch_trim(void);                                 // cudaFree everything cached on the current device
+
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

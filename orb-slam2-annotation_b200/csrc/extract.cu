@@ -9,6 +9,68 @@ namespace orbb {
 std::atomic<uint64_t> g_launches{0};
 static std::mutex g_err_mu;
 static char g_err[512] = "";
+namespace {
+struct ScratchCache {
+    static constexpr int NDEV = 64, NCLASS = 27;          // classes 2^8 .. 2^26 bytes
+    std::mutex mu;
+    std::vector<void*> free_[NDEV][NCLASS];
+    size_t cached[NDEV] = {};
+};
+ScratchCache& scratch_cache() { static ScratchCache* c = new ScratchCache(); return *c; }      // never destroyed: outlives every handle
+int scratch_class(size_t bytes) { int c = 8; while (((size_t)1 << c) < bytes) c++; return c; }
+}  // namespace
+
+void* scratch_alloc(size_t bytes, size_t* granted)
+{
+    if (bytes < 256) bytes = 256;
+    int dev = 0;
+    void* p = nullptr;
+    if (cudaGetDevice(&dev) == cudaSuccess && dev < ScratchCache::NDEV && bytes <= ((size_t)1 << 26)) {
+        const int c = scratch_class(bytes);
+        ScratchCache& sc = scratch_cache();
+        {
+            std::lock_guard<std::mutex> lk(sc.mu);
+            std::vector<void*>& v = sc.free_[dev][c];
+            if (!v.empty()) { p = v.back(); v.pop_back(); sc.cached[dev] -= (size_t)1 << c; }
+        }
+        *granted = (size_t)1 << c;
+        if (p) return p;
+        bytes = *granted;
+    } else {
+        *granted = bytes;
+    }
+    const cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) { set_cuda_error(e, "cudaMalloc (scratch)"); cudaGetLastError(); return nullptr; }
+    return p;
+}
+
+void scratch_free(void* p, size_t granted)
+{
+    if (!p) return;
+    int dev = 0;
+    const bool pow2 = granted >= 256 && (granted & (granted - 1)) == 0 && granted <= ((size_t)1 << 26);
+    if (pow2 && cudaGetDevice(&dev) == cudaSuccess && dev < ScratchCache::NDEV) {
+        ScratchCache& sc = scratch_cache();
+        std::lock_guard<std::mutex> lk(sc.mu);
+        if (sc.cached[dev] + granted <= ((size_t)1 << 30)) {
+            sc.free_[dev][scratch_class(granted)].push_back(p);
+            sc.cached[dev] += granted;
+            return;
+        }
+    }
+    cudaFree(p);
+}
+
+void scratch_trim(void)
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev >= ScratchCache::NDEV) return;
+    ScratchCache& sc = scratch_cache();
+    std::lock_guard<std::mutex> lk(sc.mu);
+    for (auto& v : sc.free_[dev]) { for (void* p : v) cudaFree(p); v.clear(); }
+    sc.cached[dev] = 0;
+}
+
 void set_cuda_error(cudaError_t e, const char* what)
 {
     std::lock_guard<std::mutex> lk(g_err_mu);

@@ -13,15 +13,19 @@ extern "C" int orbx__pyramid_view(orbx_handle* h, const LevelGeom** geom_host, c
 
 namespace {
 
+// Device scratch from the library's block cache (common.cuh): no cudaMalloc / cudaFree on the per-frame paths after warm-up.
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
-    ~DevBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { ORBB_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); cap = bytes ? bytes : 16; return ORBB_OK; }
+    ~DevBuf() { if (p) scratch_free(p, cap); }
+    int alloc(size_t bytes) { p = scratch_alloc(bytes ? bytes : 16, &cap); if (!p) { cap = 0; return ORBB_E_NOMEM; } return ORBB_OK; }
     int reserve(size_t bytes)           // grow-only; contents are not kept
     {
         if (bytes <= cap) return ORBB_OK;
-        if (p) { ORBB_CUDA(cudaFree(p)); p = nullptr; cap = 0; }
+        if (p) {                        // queued work may still use the old block, and the cache may hand it to another stream: drain first (rare)
+            ORBB_CUDA(cudaDeviceSynchronize());
+            scratch_free(p, cap); p = nullptr; cap = 0;
+        }
         return alloc(bytes + bytes / 4);
     }
     template <typename T> T* as() { return (T*)p; }
@@ -173,6 +177,8 @@ struct orbm_frame {
     // recorded after the copies and grid kernels of orbm_frame_create_device on the caller's stream: the host-pointer entry points
     // run on the legacy default stream, which does not order against cudaStreamNonBlocking streams, so they wait on it first
     cudaEvent_t ready = nullptr;
+    // streams that may still hold queued work on this frame's buffers: drained by orbm_frame_destroy before the blocks go back to the cache
+    mutable cudaStream_t s_create = nullptr, s_last = nullptr;
     ~orbm_frame() { if (ready) cudaEventDestroy(ready); }
 };
 
@@ -207,7 +213,7 @@ static int frame_create_impl(orbm_frame** out, const orbx_keypoint* kps, const u
     if (rc != ORBB_OK) return rc;
     orbm_frame* fr = new (std::nothrow) orbm_frame();
     if (!fr) return ORBB_E_NOMEM;
-    fr->device = device; fr->n = n;
+    fr->device = device; fr->n = n; fr->s_create = st; fr->s_last = st;
     const bool from_host = kind == cudaMemcpyHostToDevice;
     if (from_host) {
         if (n > 0) { fr->h_kps.assign(kps, kps + n); fr->h_desc.assign(desc, desc + (size_t)n * 32); }
@@ -262,6 +268,10 @@ extern "C" int orbm_frame_destroy(orbm_frame* f)
 {
     if (!f) return ORBB_E_INVALID;
     cudaSetDevice(f->device);
+    // asynchronous searches may still be queued (cudaFree used to wait for them implicitly; the block cache does not)
+    cudaStreamSynchronize(f->s_create);
+    if (f->s_last != f->s_create) cudaStreamSynchronize(f->s_last);
+    cudaGetLastError();                 // a stream the caller already destroyed is not an error here
     delete f;
     return ORBB_OK;
 }
@@ -350,6 +360,8 @@ static int resolve_on_device(const orbm_frame* fr, int mode, const float* uright
     const int cap = cand_capacity > 0 ? cand_capacity : 64 * nq + 1024;
     int rc;
     if (fr->ready) ORBB_CUDA(cudaStreamWaitEvent(st, fr->ready, 0));      // the frame may have been built on another stream
+    if (fr->s_last != st && fr->s_last != fr->s_create) cudaStreamSynchronize(fr->s_last);       // a third stream: keep only two to drain at destroy
+    fr->s_last = st;
     if ((rc = fr->ws_counts.reserve((size_t)nq * 4)) ||
         (rc = fr->ws_offs.reserve((size_t)(nq + 1) * 4)) || (rc = fr->ws_idx.reserve((size_t)cap * 4)) ||
         (rc = fr->ws_dist.reserve((size_t)cap * 4)) || (rc = fr->ws_choice.reserve((size_t)nq * 4)) ||

@@ -55,10 +55,11 @@ __global__ void __launch_bounds__(32 * VT_WARPS) vocab_transform_kernel(const Vo
     }
 }
 
-struct DevBuf {
+struct DevBuf {                       // blocks come from the library's scratch cache (common.cuh): the per-frame transform calls do not cudaMalloc
     void* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { ORBB_CUDA(cudaMalloc(&p, bytes ? bytes : 16)); return ORBB_OK; }
+    size_t cap = 0;
+    ~DevBuf() { if (p) scratch_free(p, cap); }
+    int alloc(size_t bytes) { p = scratch_alloc(bytes ? bytes : 16, &cap); if (!p) { cap = 0; return ORBB_E_NOMEM; } return ORBB_OK; }
     template <typename T> T* as() { return (T*)p; }
 };
 
@@ -128,6 +129,7 @@ extern "C" int orbv_vocab_destroy(orbv_vocab* v)
 {
     if (!v) return ORBB_OK;
     cudaSetDevice(v->device);
+    cudaDeviceSynchronize();            // orbv_transform_device calls may still be queued (cudaFree used to wait for them; the block cache does not)
     delete v;
     return ORBB_OK;
 }
