@@ -311,60 +311,75 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
         left = big[oy:oy + h, ox + 40:ox + 40 + w].copy()
         right = big[oy:oy + h, ox + 28:ox + 28 + w].copy()  # constant 12-px disparity
         pairs.append((left, right))
-    exL = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
-    exR = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
-    scale = exL.GetScaleFactors()
-    bufs = [dict(kL=np.zeros(cap, orbb200.KP_DTYPE), dL=np.zeros((cap, 32), np.uint8), kR=np.zeros(cap, orbb200.KP_DTYPE), dR=np.zeros((cap, 32), np.uint8),
-                 ur=np.zeros(cap, np.float32), dp=np.zeros(cap, np.float32), mp=np.zeros(cap, np.int32), ob=np.zeros(cap, np.int32)) for _ in range(2)]
     vp = C.c_void_p
     ptr = lambda a: a.ctypes.data_as(vp)
     mbf, bounds = 386.1448, (0.0, 0.0, float(w), float(h))
-    nL, nR, nm = C.c_int(), C.c_int(), C.c_int()
-    stats = {"stereo": 0, "proj": 0, "kp": 0}
 
-    def one_pair(i, queries):
-        b = bufs[i & 1]; left, right = pairs[i & 1]
-        assert L.orbx_extract(exL.h, ptr(left), w, h, w, ptr(b["kL"]), ptr(b["dL"]), cap, C.byref(nL)) == 0
-        assert L.orbx_extract(exR.h, ptr(right), w, h, w, ptr(b["kR"]), ptr(b["dR"]), cap, C.byref(nR)) == 0
-        assert L.orbm_stereo_match(exL.h, exR.h, ptr(b["kL"]), ptr(b["dL"]), nL.value, ptr(b["kR"]), ptr(b["dR"]), nR.value,
-                                   C.c_float(mbf), C.c_float(0.0), ptr(b["ur"]), ptr(b["dp"])) == 0
-        fh = vp()
-        assert L.orbm_frame_create(C.byref(fh), ptr(b["kL"]), ptr(b["dL"]), nL.value, *[C.c_float(x) for x in bounds], local_rank) == 0
-        if queries is not None:
-            b["mp"][:nL.value] = -1; b["ob"][:nL.value] = 0
-            assert L.orbm_search_by_projection_frame(fh, ptr(b["ur"]), ptr(queries), len(queries), 1, ptr(b["mp"]), ptr(b["ob"]), C.byref(nm)) == 0
-            stats["proj"] += nm.value
-        L.orbm_frame_destroy(fh)
-        stats["stereo"] += int((b["ur"][:nL.value] > 0).sum()); stats["kp"] += nL.value + nR.value
+    class Pipeline:
+        """One tracking thread's state: two extractor handles (left / right camera) and its host buffers."""
 
-    def queries_from(b, n, dx, dy):                        # the previous left frame's keypoints projected into the current one
-        q = np.zeros(n, orbb200.PROJ_QUERY_DTYPE)
-        k = b["kL"][:n]
-        q["q"]["u"] = k["x"] + dx; q["q"]["v"] = k["y"] + dy; q["q"]["r"] = 15.0 * scale[k["octave"]]
-        q["q"]["min_level"] = k["octave"] - 1; q["q"]["max_level"] = k["octave"] + 1; q["q"]["desc"] = b["dL"][:n]
-        q["u_right"] = q["q"]["u"] - 12.0; q["max_err_right"] = 15.0 * scale[k["octave"]]
-        q["id"] = np.arange(n); q["has_obs"] = 1; q["angle"] = k["angle"]
-        return q
-    one_pair(0, None); n0 = nL.value
-    one_pair(1, None); n1 = nL.value
-    qs = [queries_from(bufs[1], n1, 3.0, 1.0), queries_from(bufs[0], n0, -3.0, -1.0)]     # queries for pair 0 come from pair 1 and vice versa
-    for i in range(4):
-        one_pair(i, qs[i & 1])
-    stats.update(stereo=0, proj=0, kp=0)
-    barrier()
-    npairs = 40
-    t0 = time.perf_counter()
-    for i in range(npairs):
-        one_pair(i, qs[i & 1])
-    torch.cuda.synchronize(); barrier()
-    dt = max_over_ranks(time.perf_counter() - t0)
-    rows["C2_kitti_stereo_pair_pipeline"] = {
-        "pairs_per_s": world * npairs / dt, "frames_per_s": 2 * world * npairs / dt, "ms_per_pair": dt / npairs * 1e3,
-        "stereo_matches_per_s": world * stats["stereo"] / dt, "projection_matches_per_s": world * stats["proj"] / dt,
-        "matches_per_s": world * (stats["stereo"] + stats["proj"]) / dt, "keypoints_per_frame": stats["kp"] / (2 * npairs),
-        "stereo_matches_per_pair": stats["stereo"] / npairs, "projection_matches_per_pair": stats["proj"] / npairs,
-        "api": "per pair on one host thread, host pointers: orbx_extract (L) + orbx_extract (R) + orbm_stereo_match + orbm_frame_create + "
-               "orbm_search_by_projection_frame + orbm_frame_destroy; wall clock, H2D/D2H inside every call"}
+        def __init__(self):
+            self.exL = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
+            self.exR = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
+            self.scale = self.exL.GetScaleFactors()
+            self.bufs = [dict(kL=np.zeros(cap, orbb200.KP_DTYPE), dL=np.zeros((cap, 32), np.uint8), kR=np.zeros(cap, orbb200.KP_DTYPE), dR=np.zeros((cap, 32), np.uint8),
+                              ur=np.zeros(cap, np.float32), dp=np.zeros(cap, np.float32), mp=np.zeros(cap, np.int32), ob=np.zeros(cap, np.int32)) for _ in range(2)]
+            self.nL, self.nR, self.nm = C.c_int(), C.c_int(), C.c_int()
+            self.stats = {"stereo": 0, "proj": 0, "kp": 0}
+            self.one_pair(0, None); n0 = self.nL.value
+            self.one_pair(1, None); n1 = self.nL.value
+            self.qs = [self.queries_from(self.bufs[1], n1, 3.0, 1.0), self.queries_from(self.bufs[0], n0, -3.0, -1.0)]   # queries for pair 0 come from pair 1 and vice versa
+            for i in range(4):
+                self.one_pair(i, self.qs[i & 1])
+            self.stats.update(stereo=0, proj=0, kp=0)
+
+        def one_pair(self, i, queries):
+            b = self.bufs[i & 1]; left, right = pairs[i & 1]
+            nL, nR, nm = self.nL, self.nR, self.nm
+            assert L.orbx_extract(self.exL.h, ptr(left), w, h, w, ptr(b["kL"]), ptr(b["dL"]), cap, C.byref(nL)) == 0
+            assert L.orbx_extract(self.exR.h, ptr(right), w, h, w, ptr(b["kR"]), ptr(b["dR"]), cap, C.byref(nR)) == 0
+            assert L.orbm_stereo_match(self.exL.h, self.exR.h, ptr(b["kL"]), ptr(b["dL"]), nL.value, ptr(b["kR"]), ptr(b["dR"]), nR.value,
+                                       C.c_float(mbf), C.c_float(0.0), ptr(b["ur"]), ptr(b["dp"])) == 0
+            fh = vp()
+            assert L.orbm_frame_create(C.byref(fh), ptr(b["kL"]), ptr(b["dL"]), nL.value, *[C.c_float(x) for x in bounds], local_rank) == 0
+            if queries is not None:
+                b["mp"][:nL.value] = -1; b["ob"][:nL.value] = 0
+                assert L.orbm_search_by_projection_frame(fh, ptr(b["ur"]), ptr(queries), len(queries), 1, ptr(b["mp"]), ptr(b["ob"]), C.byref(nm)) == 0
+                self.stats["proj"] += nm.value
+            L.orbm_frame_destroy(fh)
+            self.stats["stereo"] += int((b["ur"][:nL.value] > 0).sum()); self.stats["kp"] += nL.value + nR.value
+
+        def queries_from(self, b, n, dx, dy):                  # the previous left frame's keypoints projected into the current one
+            q = np.zeros(n, orbb200.PROJ_QUERY_DTYPE)
+            k = b["kL"][:n]
+            q["q"]["u"] = k["x"] + dx; q["q"]["v"] = k["y"] + dy; q["q"]["r"] = 15.0 * self.scale[k["octave"]]
+            q["q"]["min_level"] = k["octave"] - 1; q["q"]["max_level"] = k["octave"] + 1; q["q"]["desc"] = b["dL"][:n]
+            q["u_right"] = q["q"]["u"] - 12.0; q["max_err_right"] = 15.0 * self.scale[k["octave"]]
+            q["id"] = np.arange(n); q["has_obs"] = 1; q["angle"] = k["angle"]
+            return q
+
+        def run(self, npairs):
+            for i in range(npairs):
+                self.one_pair(i, self.qs[i & 1])
+
+    api = ("per pair, host pointers: orbx_extract (L) + orbx_extract (R) + orbm_stereo_match + orbm_frame_create + orbm_search_by_projection_frame + "
+           "orbm_frame_destroy; wall clock, H2D/D2H inside every call")
+    for nthreads, npairs in ((1, 40), (4, 40)):
+        pipes = [Pipeline() for _ in range(nthreads)]
+        barrier()
+        t0 = time.perf_counter()
+        th = [threading.Thread(target=p_.run, args=(npairs,)) for p_ in pipes]
+        [t.start() for t in th]; [t.join() for t in th]
+        torch.cuda.synchronize(); barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        st_ = {k: sum(p_.stats[k] for p_ in pipes) for k in ("stereo", "proj", "kp")}
+        tot = nthreads * npairs
+        rows["C2_kitti_stereo_pair_pipeline" + ("" if nthreads == 1 else f"_{nthreads}_host_threads")] = {
+            "pairs_per_s": world * tot / dt, "frames_per_s": 2 * world * tot / dt, "ms_per_pair_per_thread": dt / npairs * 1e3, "host_threads_per_gpu": nthreads,
+            "stereo_matches_per_s": world * st_["stereo"] / dt, "projection_matches_per_s": world * st_["proj"] / dt,
+            "matches_per_s": world * (st_["stereo"] + st_["proj"]) / dt, "keypoints_per_frame": st_["kp"] / (2 * tot),
+            "stereo_matches_per_pair": st_["stereo"] / tot, "projection_matches_per_pair": st_["proj"] / tot, "api": api}
+        del pipes
     return rows
 
 
