@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 #include "orbb_cv.h"
+#include "ORBextractor.h"
 #include "../../include/orbb200.h"
 
 namespace ORB_SLAM2 {
@@ -99,19 +100,39 @@ private:
     orbm_db* db_;
 };
 
+// Frame::ComputeStereoMatches (src/Frame.cpp:540-748) on the device: reads both extractors' pyramids in HBM (their last operator()
+// call), so SetPyramidDownload(false) is enough for stereo frames.  mb = the member value at call time (0 in the reference's stereo
+// constructor).  Fills mvuRight / mvDepth (-1 = no match).
+inline void ComputeStereoMatches(ORBextractor& left, ORBextractor& right, const std::vector<cv::KeyPoint>& mvKeys, const cv::Mat& mDescriptors,
+                                 const std::vector<cv::KeyPoint>& mvKeysRight, const cv::Mat& mDescriptorsRight, float mbf, float mb,
+                                 std::vector<float>& mvuRight, std::vector<float>& mvDepth)
+{
+    const int nL = (int)mvKeys.size(), nR = (int)mvKeysRight.size();
+    std::vector<uint8_t> dL((size_t)nL * 32), dR((size_t)nR * 32);
+    for (int i = 0; i < nL; i++) memcpy(&dL[(size_t)i * 32], mDescriptors.ptr(i), 32);
+    for (int i = 0; i < nR; i++) memcpy(&dR[(size_t)i * 32], mDescriptorsRight.ptr(i), 32);
+    mvuRight.assign(nL, -1.0f); mvDepth.assign(nL, -1.0f);
+    orbm_check(orbm_stereo_match(left.Handle(), right.Handle(), (const orbx_keypoint*)mvKeys.data(), dL.data(), nL,
+                                 (const orbx_keypoint*)mvKeysRight.data(), dR.data(), nR, mbf, mb, mvuRight.data(), mvDepth.data()), "orbm_stereo_match");
+}
+
 class ORBmatcher {
 public:
     ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
 
-    // include/ORBmatcher.h:45, src/ORBmatcher.cpp:1838-1854.  Routed to the device like everything else in this mirror (no
-    // host arithmetic); per-pair callers outside the hot path (MapPoint::ComputeDistinctiveDescriptors, SearchByBoW) should
-    // keep the reference's own static function or batch their pairs through DescriptorDistances().
+    // include/ORBmatcher.h:45, src/ORBmatcher.cpp:1838-1854.  Routed to the device like everything else in this mirror (no host
+    // arithmetic), so ONE pair costs a kernel launch and three copies: a caller that keeps the reference's per-pair loops
+    // (Frame::ComputeStereoMatches, src/Frame.cpp:632; MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cpp:345) would run
+    // ~10^4 times slower than the reference.  Those two loops are whole entry points here: ComputeStereoMatches() below
+    // (orbm_stereo_match) and orbm_distinctive_descriptors; any other set of pairs goes through DescriptorDistances() in one call.
+    [[deprecated("one device round trip per pair: batch with ORBmatcher::DescriptorDistances, or use ComputeStereoMatches / orbm_distinctive_descriptors")]]
     static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b, int device = 0)
     {
         int32_t d = -1;
         orbm_check(orbm_distance_pairs(a.ptr(0), b.ptr(0), 1, &d, device), "orbm_distance_pairs");
         return d;
     }
+    // n pairs (a[i], b[i]) of 32-byte descriptors in one launch
     static void DescriptorDistances(const uint8_t* a, const uint8_t* b, int n, int32_t* out, int device = 0)
     {
         orbm_check(orbm_distance_pairs(a, b, n, out, device), "orbm_distance_pairs");

@@ -1,9 +1,12 @@
 // host_selftest.cc — exercises the C++ host mirror (ORB_SLAM2::ORBextractor / ORBmatcher) exactly as Frame.cc does.
 //   host_selftest                       no arguments: API/table checks; with no CUDA device it must fail loudly (exit 0)
 //   host_selftest W H in.raw out.bin    extract in.raw (W x H, 8-bit) and write n, keypoints, descriptors, level sizes
+//   host_selftest match in.bin out.bin  run the ORBmatcher mirror (SearchByProjection x2, SearchForInitialization, ComputeStereoMatches,
+//                                       DescriptorDistances) on dumped inputs; tests/test_host_mirror.py compares with the oracle
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <stdexcept>
 #include "ORBextractor.h"
 #include "ORBmatcher.h"
 
@@ -36,14 +39,94 @@ static int api_checks()
     if (kps.empty() || desc.rows != (int)kps.size() || desc.cols != 32) return 7;
     if ((int)ex.mvImagePyramid.size() != 8 || ex.mvImagePyramid[1].cols != 533 || ex.mvImagePyramid[7].rows != 134) return 8;
     if (memcmp(ex.mvImagePyramid[0].ptr(5), img.ptr(5), 640)) return 9;
-    int d = ORBmatcher::DescriptorDistance(desc.row(0), desc.row(0));
+    int32_t d = -1;
+    ORBmatcher::DescriptorDistances(desc.ptr(0), desc.ptr(0), 1, &d);
     if (d != 0) return 10;
     printf("device path ok: %zu keypoints\n", kps.size());
     return 0;
 }
 
+namespace {
+struct Reader {
+    FILE* f;
+    template <typename T> void get(T* p, size_t n) { if (n && fread(p, sizeof(T), n, f) != n) throw std::runtime_error("short input file"); }
+    int i32() { int v; get(&v, 1); return v; }
+    float f32() { float v; get(&v, 1); return v; }
+};
+cv::Mat rows32(const std::vector<uint8_t>& d, int n)
+{
+    cv::Mat m(n > 0 ? n : 1, 32, CV_8U);
+    for (int i = 0; i < n; i++) memcpy(m.ptr(i), &d[(size_t)i * 32], 32);
+    m.rows = n;
+    return m;
+}
+}  // namespace
+
+// The matcher half of the mirror, driven like Tracking / Initializer / Frame drive the reference classes.
+static int match_mode(const char* in, const char* outp)
+{
+    Reader r{fopen(in, "rb")};
+    if (!r.f) { fprintf(stderr, "cannot read %s\n", in); return 2; }
+    const int w = r.i32(), h = r.i32(), n1 = r.i32(), n2 = r.i32(), nq = r.i32(), nf = r.i32();
+    std::vector<cv::KeyPoint> k1(n1), k2(n2);
+    std::vector<uint8_t> d1((size_t)n1 * 32), d2((size_t)n2 * 32);
+    r.get(k1.data(), n1); r.get(d1.data(), d1.size()); r.get(k2.data(), n2); r.get(d2.data(), d2.size());
+    std::vector<float> ur2(n2); r.get(ur2.data(), n2);
+    std::vector<orbm_proj_query> q(nq); r.get(q.data(), nq);
+    std::vector<int32_t> mp0(n2), ob0(n2); r.get(mp0.data(), n2); r.get(ob0.data(), n2);
+    std::vector<cv::Point2f> prev(n1); r.get(prev.data(), n1);
+    cv::Mat imL(h, w, CV_8U), imR(h, w, CV_8U);
+    r.get(imL.ptr(0), (size_t)w * h); r.get(imR.ptr(0), (size_t)w * h);
+    const float mbf = r.f32();
+    fclose(r.f);
+    FILE* o = fopen(outp, "wb");
+    auto put = [&](const void* p, size_t bytes) { fwrite(p, 1, bytes, o); };
+
+    const cv::Mat D1 = rows32(d1, n1), D2 = rows32(d2, n2);
+    DeviceFrame F1(k1, D1, 0.f, 0.f, (float)w, (float)h), F2(k2, D2, 0.f, 0.f, (float)w, (float)h);
+    {   // Tracking::TrackWithMotionModel -> SearchByProjection(CurrentFrame, LastFrame, th, mono) (src/ORBmatcher.cpp:1506)
+        std::vector<int32_t> mp = mp0, ob = ob0;
+        const int n = ORBmatcher(0.9f, true).SearchByProjectionLastFrame(F2, &ur2, q, mp, ob);
+        put(&n, 4); put(mp.data(), 4 * (size_t)n2); put(ob.data(), 4 * (size_t)n2);
+    }
+    {   // Tracking::SearchLocalPoints -> SearchByProjection(CurrentFrame, vpMapPoints, th) (:63)
+        std::vector<int32_t> mp = mp0, ob = ob0;
+        const int n = ORBmatcher(0.8f).SearchByProjection(F2, &ur2, q, mp, ob);
+        put(&n, 4); put(mp.data(), 4 * (size_t)n2); put(ob.data(), 4 * (size_t)n2);
+    }
+    {   // Tracking::MonocularInitialization -> SearchForInitialization(mInitialFrame, mCurrentFrame, mvbPrevMatched, mvIniMatches, 100) (:474)
+        std::vector<int> m12;
+        std::vector<cv::Point2f> pm = prev;
+        const int n = ORBmatcher(0.9f, true).SearchForInitialization(F1, F2, pm, m12, 100);
+        put(&n, 4); put(m12.data(), 4 * (size_t)n1); put(pm.data(), 8 * (size_t)n1);
+    }
+    {   // Frame::Frame (stereo): two extractors, then ComputeStereoMatches (src/Frame.cpp:84-100, :540)
+        ORBextractor exL(nf, 1.2f, 8, 20, 7), exR(nf, 1.2f, 8, 20, 7);
+        exL.SetPyramidDownload(false); exR.SetPyramidDownload(false);
+        std::vector<cv::KeyPoint> kL, kR;
+        cv::Mat dL, dR;
+        exL(imL, cv::Mat(), kL, dL); exR(imR, cv::Mat(), kR, dR);
+        std::vector<float> uR, depth;
+        ComputeStereoMatches(exL, exR, kL, dL, kR, dR, mbf, 0.0f, uR, depth);
+        const int n = (int)kL.size();
+        put(&n, 4); put(uR.data(), 4 * (size_t)n); put(depth.data(), 4 * (size_t)n);
+    }
+    {   // batched distances: row i of frame 1 against row i of frame 2
+        const int n = n1 < n2 ? n1 : n2;
+        std::vector<int32_t> dist(n);
+        ORBmatcher::DescriptorDistances(d1.data(), d2.data(), n, dist.data());
+        put(&n, 4); put(dist.data(), 4 * (size_t)n);
+    }
+    fclose(o);
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
+    if (argc == 4 && !strcmp(argv[1], "match")) {
+        try { return match_mode(argv[2], argv[3]); }
+        catch (const std::exception& e) { fprintf(stderr, "host_selftest match: %s\n", e.what()); return 3; }
+    }
     if (argc < 5) { const int rc = api_checks(); if (rc) fprintf(stderr, "host_selftest: check %d failed\n", rc); return rc; }
     const int W = atoi(argv[1]), H = atoi(argv[2]);
     const int nf = argc > 5 ? atoi(argv[5]) : 1000;

@@ -50,3 +50,69 @@ def test_host_mirror_extract_equals_oracle(gpu, tmp_path, w, h, nf, seed):
         lw, lh = np.frombuffer(buf, np.int32, 2, off); off += 8
         lvl = np.frombuffer(buf, np.uint8, lw * lh, off).reshape(lh, lw); off += lw * lh
         assert np.array_equal(lvl, orc.level_image(L)), f"mvImagePyramid[{L}]"
+
+
+@pytest.mark.gpu
+def test_host_mirror_matcher_equals_oracle(gpu, tmp_path):
+    """The C++ ORBmatcher mirror driven the way Tracking / Initializer / Frame drive the reference class: both SearchByProjection
+    overloads, SearchForInitialization, ComputeStereoMatches (two ORBextractor mirrors + orbm_stereo_match) and the batched
+    DescriptorDistances, on dumped inputs; every output equals the CPU oracle's."""
+    import orbb200, pyoracle
+    from synth import synth, synth_stereo
+    w, h, nf = 640, 480, 1000
+    big = synth(w + 16, h + 16, 31)
+    cur = big[8:8 + h, 8:8 + w].copy(); last = big[9:9 + h, 11:11 + w].copy()
+    ex = pyoracle.OracleExtractor(nf)
+    k2, d2 = ex.extract(cur); k1, d1 = ex.extract(last)
+    scale = ex.tables()["scale"]
+    rng = np.random.default_rng(5)
+    q = np.zeros(len(k1), orbb200.PROJ_QUERY_DTYPE)
+    q["q"]["u"] = k1["x"] + 3; q["q"]["v"] = k1["y"] + 1; q["q"]["r"] = 15.0 * scale[k1["octave"]]
+    q["q"]["min_level"] = k1["octave"] - 1; q["q"]["max_level"] = k1["octave"] + 1; q["q"]["desc"] = d1
+    q["u_right"] = q["q"]["u"] - rng.uniform(0, 30, len(k1)).astype(np.float32); q["max_err_right"] = q["q"]["r"]
+    q["id"] = np.arange(len(k1)); q["has_obs"] = (rng.random(len(k1)) < 0.9).astype(np.int32); q["angle"] = k1["angle"]
+    ur2 = np.where(rng.random(len(k2)) < 0.5, k2["x"] - rng.uniform(0, 30, len(k2)), -1).astype(np.float32)
+    mp0 = np.full(len(k2), -1, np.int32); ob0 = np.zeros(len(k2), np.int32)
+    mp0[::17] = 9999; ob0[::17] = 1; mp0[5::23] = 7777
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    L, R = synth_stereo(w, h, 22)
+    mbf = np.float32(47.90639384423901)
+    src, out = tmp_path / "match_in.bin", tmp_path / "match_out.bin"
+    with open(src, "wb") as f:
+        f.write(np.array([w, h, len(k1), len(k2), len(q), nf], np.int32).tobytes())
+        for a in (k1, d1, k2, d2, ur2, q, mp0, ob0, prev, L, R, np.array([mbf], np.float32)):
+            f.write(np.ascontiguousarray(a).tobytes())
+    r = subprocess.run([_exe(), "match", str(src), str(out)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    buf = out.read_bytes(); off = 0
+
+    def take(dtype, n):
+        nonlocal off
+        a = np.frombuffer(buf, dtype, n, off); off += a.nbytes
+        return a
+    oq = np.zeros(len(q), pyoracle.QUERY_DTYPE)
+    oq["u"] = q["q"]["u"]; oq["v"] = q["q"]["v"]; oq["r"] = q["q"]["r"]; oq["minLevel"] = q["q"]["min_level"]; oq["maxLevel"] = q["q"]["max_level"]
+    oq["desc"] = q["q"]["desc"]; oq["uR"] = q["u_right"]; oq["maxErrR"] = q["max_err_right"]; oq["id"] = q["id"]; oq["hasObs"] = q["has_obs"]; oq["angle"] = q["angle"]
+    O1 = pyoracle.OracleFrame(k1, d1, (0, 0, w, h)); O2 = pyoracle.OracleFrame(k2, d2, (0, 0, w, h))
+    n = int(take(np.int32, 1)[0]); mp = take(np.int32, len(k2)); ob = take(np.int32, len(k2))
+    on, omp, oob = O2.search_last_frame(oq, True, mp0, ob0, ur2)
+    assert n == on and np.array_equal(mp, omp) and np.array_equal(ob, oob) and n > 300
+    n = int(take(np.int32, 1)[0]); mp = take(np.int32, len(k2)); ob = take(np.int32, len(k2))
+    on, omp, oob = O2.search_local_points(oq, 0.8, mp0, ob0, ur2)
+    assert n == on and np.array_equal(mp, omp) and np.array_equal(ob, oob) and n > 100
+    n = int(take(np.int32, 1)[0]); m12 = take(np.int32, len(k1)); pm = take(np.float32, 2 * len(k1))
+    on, om12, opm = pyoracle.search_for_initialization(O1, O2, prev, 100, 0.9, True)
+    assert n == on and np.array_equal(m12, om12) and np.array_equal(pm, opm.reshape(-1)) and n > 100
+    oL, oR = pyoracle.OracleExtractor(nf), pyoracle.OracleExtractor(nf)
+    okL, _ = oL.extract(L); oR.extract(R)
+    nL = int(take(np.int32, 1)[0]); ur = take(np.float32, nL); dp = take(np.float32, nL)
+    with np.errstate(divide="ignore"):
+        our, odp, _, _ = pyoracle.stereo_match(oL, oR, float(mbf), 0.0)
+    assert nL == len(okL) and np.array_equal(ur, our) and np.array_equal(dp, odp) and (ur >= 0).sum() > 0.2 * nL
+    npairs = int(take(np.int32, 1)[0]); dist = take(np.int32, npairs)
+    m = min(len(k1), len(k2))
+    assert npairs == m and np.array_equal(dist, pyoracle.distance_pairs(d1[:m], d2[:m]))
+    # the batched form gives the per-pair results of orbm_distance_pairs with n = 1 (the deprecated single-pair form)
+    single = np.array([orbb200.DescriptorDistance(d1[i:i + 1], d2[i:i + 1])[0] for i in range(8)])
+    assert np.array_equal(single, dist[:8])
+    assert off == len(buf)
