@@ -1,9 +1,9 @@
 // extract_kernels.cuh — sm_100a kernels of the ORB extractor hot path.
 //
-//   level_kernel     : one launch per pyramid level, grid = (tiles_x, tiles_y, frames).  A CTA stages a 64x32 tile of
-//                      level L (+4 px halo) in shared memory ONCE and produces from it (a) the 7x7 sigma-2 blurred level
-//                      (ORBextractor.cpp:1097-1098), (b) the FAST-9-16 arc score, cell-local 3x3 NMS and the ini/min
-//                      threshold candidates (ORBextractor.cpp:797-838), (c) the bilinear-resized tile of level L+1
+//   level3_kernel    : (level_kernel3.cuh) one launch per pyramid level, grid = (tiles_x, tiles_y, frames).  A CTA of 4 (or 8) warps stages a
+//                      120 x 32 (120 x 64) pixel tile of level L plus a 4-pixel halo in shared memory ONCE, by one bulk tensor copy (TMA), and
+//                      produces from it (a) the 7x7 sigma-2 blurred level (ORBextractor.cpp:1097-1098), (b) the FAST-9-16 arc score, cell-local
+//                      3x3 NMS and the raw corner records (ORBextractor.cpp:797-838), (c) its part of level L+1 by bilinear resize
 //                      (ORBextractor.cpp:1136).  Level L is therefore read from HBM once.
 //   octree_kernel    : DistributeOctTree (ORBextractor.cpp:541-770), one CTA per (level, frame).
 //   orient_desc_kernel: IC_Angle (ORBextractor.cpp:79-106) + computeOrbDescriptor (:110-149) + the coordinate scaling

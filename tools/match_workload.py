@@ -1,5 +1,5 @@
 """Guided-matching workload at the C2 shape (KITTI 1241x376, 2000 kp): stereo matching, tracked-frame search (window search + device
-resolve), grid build.  For ncu (tools/gpu_ncu_match.sh) and for CUDA-event timing of the kernel families (prints one JSON object)."""
+resolve), grid build.  For ncu (tools/gpu.sh ncu-match) and for CUDA-event timing of the kernel families (prints one JSON object)."""
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "orb-slam2-annotation_b200")]
