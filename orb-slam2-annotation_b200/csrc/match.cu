@@ -900,6 +900,7 @@ struct orbm_db {
     int nq_cap = 0, chunk_cap = 0;
     uint4* d_q = nullptr; unsigned *d_k1 = nullptr, *d_k2 = nullptr;
     int *d_d1 = nullptr, *d_d2 = nullptr; long long* d_i1 = nullptr;
+    int* d_bound = nullptr;                    // [nq_cap] cross-chunk second-best bound of the CTA-pair kernel
     int variant = 0;
 };
 
@@ -928,7 +929,7 @@ extern "C" int orbm_db_destroy(orbm_db* db)
 {
     if (!db) return ORBB_E_INVALID;
     cudaSetDevice(db->device);
-    cudaFree(db->d_rows); cudaFree(db->d_q); cudaFree(db->d_k1); cudaFree(db->d_k2); cudaFree(db->d_d1); cudaFree(db->d_d2); cudaFree(db->d_i1);
+    cudaFree(db->d_rows); cudaFree(db->d_q); cudaFree(db->d_k1); cudaFree(db->d_k2); cudaFree(db->d_d1); cudaFree(db->d_d2); cudaFree(db->d_i1); cudaFree(db->d_bound);
     delete db;
     return ORBB_OK;
 }
@@ -947,12 +948,12 @@ static int db_append(orbm_db* db, const uint8_t* rows, int64_t n, cudaMemcpyKind
 extern "C" int orbm_db_append(orbm_db* db, const uint8_t* rows_host, int64_t n) { return db_append(db, rows_host, n, cudaMemcpyHostToDevice); }
 extern "C" int orbm_db_append_device(orbm_db* db, const uint8_t* rows_dev, int64_t n) { return db_append(db, rows_dev, n, cudaMemcpyDeviceToDevice); }
 
-// Kernel of one search: ORBB_BF_VARIANT when given, else the CTA-pair kernel for wide, long scans (its 512-query tile and its
-// longer prologue pay off above 256 queries and about two million rows) and the single-CTA tcgen05 kernel otherwise.
+// Kernel of one search: ORBB_BF_VARIANT when given, else the CTA-pair kernel when its 512-query tile is more than half used (measured
+// ahead of the single-CTA kernel from 300 queries x 100 k rows upwards) and the single-CTA tcgen05 kernel otherwise.
 static int bf_variant(const orbm_db* db, int nq)
 {
     if (db->variant >= 0) return db->variant;
-    return (nq > 256 && db->rows >= 2000000) ? 4 : 3;
+    return (nq > 256 && db->rows >= 65536) ? 4 : 3;
 }
 
 static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nchunks)
@@ -961,6 +962,13 @@ static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nc
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, db->device);
     const int qtiles = ceil_div(nq, variant >= 4 ? B2_QTILE : variant >= 2 ? BM_QTILE : BF_QTILE);
+    static const int waves4 = getenv("ORBB_BF_WAVES") ? atoi(getenv("ORBB_BF_WAVES")) : 1;
+    if (variant >= 4 && waves4 == 1) {          // one wave of at most sms / 2 CTA pairs (whole query tiles): 2.72 ms against 2.80 ms in two waves (ORBB_BF_WAVES=2)
+        int t1 = (sms / 2) / qtiles; if (t1 < 1) t1 = 1;
+        long long rpc1 = (db->rows + t1 - 1) / t1; rpc1 = (rpc1 + 255) / 256 * 256;
+        if (rpc1 < BF_ROWS) rpc1 = BF_ROWS;
+        if (rpc1 <= (1ll << BF_IDX_BITS)) { *rows_per_chunk = rpc1; *nchunks = (int)((db->rows + rpc1 - 1) / rpc1); if (*nchunks < 1) *nchunks = 1; return ORBB_OK; }
+    }
     int target = ceil_div(variant >= 4 ? sms : sms * (variant == 3 ? 2 : 4), qtiles);      // two waves (variant 4: of sms / 2 CTA pairs); integer-pipe kernels: ~4 CTAs per SM in flight
     long long rpc = (db->rows + target - 1) / target;
     rpc = (rpc + 255) / 256 * 256;                                  // a multiple of every kernel's stage size
@@ -975,12 +983,13 @@ static int db_plan(const orbm_db* db, int nq, long long* rows_per_chunk, int* nc
 static int db_reserve(orbm_db* db, int nq, int nchunks)
 {
     if (nq > db->nq_cap) {
-        cudaFree(db->d_q); cudaFree(db->d_d1); cudaFree(db->d_d2); cudaFree(db->d_i1);
-        db->d_q = nullptr; db->d_d1 = db->d_d2 = nullptr; db->d_i1 = nullptr; db->nq_cap = 0;
+        cudaFree(db->d_q); cudaFree(db->d_d1); cudaFree(db->d_d2); cudaFree(db->d_i1); cudaFree(db->d_bound);
+        db->d_q = nullptr; db->d_d1 = db->d_d2 = nullptr; db->d_i1 = nullptr; db->d_bound = nullptr; db->nq_cap = 0;
         ORBB_CUDA(cudaMalloc((void**)&db->d_q, (size_t)nq * 32));
         ORBB_CUDA(cudaMalloc((void**)&db->d_d1, (size_t)nq * 4));
         ORBB_CUDA(cudaMalloc((void**)&db->d_d2, (size_t)nq * 4));
         ORBB_CUDA(cudaMalloc((void**)&db->d_i1, (size_t)nq * 8));
+        ORBB_CUDA(cudaMalloc((void**)&db->d_bound, (size_t)nq * 4));
         db->nq_cap = nq;
         db->chunk_cap = 0;
     }
@@ -1007,8 +1016,10 @@ extern "C" int orbm_bf_top2_device(orbm_db* db, const uint8_t* q_dev, int nq, in
     cudaStream_t st = (cudaStream_t)stream;
     BfArgs a;
     a.db = db->d_rows; a.nrows = db->rows; a.q = (const uint4*)q_dev; a.nq = nq;
-    a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = db->d_k1; a.part_k2 = db->d_k2;
+    a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = db->d_k1; a.part_k2 = db->d_k2; a.bound_d2 = nullptr;
     const int variant = bf_variant(db, nq);
+    static const bool share = getenv("ORBB_BF_NO_BOUND") == nullptr;                 // experiment knob: chunks do not share their bounds
+    if (share && variant >= 3) { a.bound_d2 = db->d_bound; ORBB_CUDA(cudaMemsetAsync(db->d_bound, 0x7f, (size_t)nq * 4, st)); }      // 0x7f7f7f7f: no bound yet
     dim3 grid(ceil_div(nq, variant >= 2 ? BM_QTILE : BF_QTILE), nchunks);
     if (variant == 4) {
         static std::atomic<bool> attr2_set[64];
@@ -1122,7 +1133,7 @@ extern "C" int orbm_bf_top2_noalloc(const uint8_t* rows_dev, int64_t nrows, int6
     ORBB_CUDA(cudaMemsetAsync(k2, 0xff, (size_t)nchunks * nq * 4, st));
     BfArgs a;
     a.db = (const uint4*)rows_dev; a.nrows = nrows; a.q = (const uint4*)q_dev; a.nq = nq;
-    a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = k1; a.part_k2 = k2;
+    a.rows_per_chunk = rpc; a.nchunks = nchunks; a.part_k1 = k1; a.part_k2 = k2; a.bound_d2 = nullptr;
     bf_top2_tcn_kernel<<<dim3(qtiles, nchunks), BW_THREADS, BN_SMEM, st>>>(a);
     ORBB_LAUNCHED();
     bf_merge_chunks_kernel<<<ceil_div(nq, 256), 256, 0, st>>>(k1, k2, nchunks, nq, rpc, row_offset, d1, (long long*)i1, d2);
@@ -1245,3 +1256,8 @@ extern "C" int orbb200_measure_tcgen05_i8_peak(int device, double* int8_tops)
     *int8_tops = best;
     return ORBB_OK;
 }
+
+#ifdef B2_TIMING
+extern "C" int orbb200__b2_gtiming(long long* out) { return cudaMemcpyFromSymbol(out, g_b2_g, sizeof(long long) * 2 * 32 * 2 * 8) == cudaSuccess ? 0 : -2; }
+extern "C" int orbb200__b2_timing(long long* out) { return cudaMemcpyFromSymbol(out, g_b2_t, sizeof(long long) * 32 * 2 * 8) == cudaSuccess ? 0 : -2; }
+#endif

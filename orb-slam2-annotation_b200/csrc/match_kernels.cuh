@@ -622,6 +622,7 @@ struct BfArgs {
     const uint4* q; int nq;
     long long rows_per_chunk; int nchunks;
     unsigned* part_k1; unsigned* part_k2;      // [nchunks][nq] packed keys
+    int* bound_d2;                             // [nq] or null: smallest second-best distance any chunk has published (bf_top2_tc2_kernel)
 };
 
 template <int VARIANT>
@@ -1042,6 +1043,16 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcn_kernel(const __grid
             }
         }
         for (int e = 0; e < nstages; e++) {
+            if (a.bound_d2 && (e & 15) == 0 && cg == 0) {              // chunks share their second-best bounds: see bf_top2_tc2_kernel
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    const int qi = blockIdx.x * BT_QTILE + 128 * mt + row;
+                    if (qi < a.nq) {
+                        const int g = __ldcg(a.bound_d2 + qi);
+                        if (g < 512) atomicMax(&thr_s[mt * 128 + row], pq[mt] - g);
+                    }
+                }
+            }
 #pragma unroll
             for (int mt = 0; mt < 2; mt++) {
                 bt_wait(accfull0 + 8 * mt, (unsigned)(e & 1));
@@ -1081,7 +1092,10 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcn_kernel(const __grid
                                 }
                             }
                         }
-                        if (thr[mt] != 0x7fffffff) atomicMax(&thr_s[mt * 128 + row], thr[mt]);
+                        if (thr[mt] != 0x7fffffff) {
+                            atomicMax(&thr_s[mt * 128 + row], thr[mt]);
+                            if (a.bound_d2 && k2[mt] != 0xffffffffu) atomicMin(a.bound_d2 + blockIdx.x * BT_QTILE + 128 * mt + row, (int)(k2[mt] >> BF_IDX_BITS));
+                        }
                     }
                 }
             }
@@ -1129,6 +1143,9 @@ __global__ void __launch_bounds__(BW_THREADS, 1) bf_top2_tcn_kernel(const __grid
 // barriers (mapa + mbarrier.arrive.release.cluster); tcgen05.commit multicasts to the empty / accfull barriers of both CTAs.
 // Output: the same per-(chunk, query) packed keys as the other kernels.
 // ------------------------------------------------------------------------------------------------------
+#ifndef B2_REFRESH
+#define B2_REFRESH 15
+#endif
 constexpr int B2_QTILE = 512;                            // queries per CTA pair
 constexpr int B2_STAGES = 4;
 constexpr int B2_BTILE = 128 * 256;                      // one CTA's half of a 256-row stage, expanded
@@ -1161,6 +1178,15 @@ __device__ __forceinline__ void b2_arrive_leader_relaxed(unsigned mbar_local)   
     asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
 }
 
+#ifdef B2_TIMING
+// diagnostic build only: clock64 stamps of the hand-over chain in the leader CTA of cluster (0, 0), stages 64..95
+__device__ long long g_b2_t[32][2][8];
+__device__ __forceinline__ long long b2_gt() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+__device__ long long g_b2_g[2][32][2][8];       // [cta rank] globaltimer stamps (ns)
+#define B2_STAMP(it, mt, slot) do { if (blockIdx.x < 2 && blockIdx.y == 0 && (it) >= 64 && (it) < 96) { if (blockIdx.x == 0) g_b2_t[(it) - 64][mt][slot] = clock64(); g_b2_g[blockIdx.x][(it) - 64][mt][slot] = b2_gt(); } } while (0)
+#else
+#define B2_STAMP(it, mt, slot) do {} while (0)
+#endif
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(B2_THREADS, 1) bf_top2_tc2_kernel(const __grid_constant__ BfArgs a)
 {
     extern __shared__ __align__(128) uint8_t bt_smem[];
@@ -1280,7 +1306,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(B2_THREADS, 1) bf_to
                 const unsigned long long bd0 = bdesc0 + (unsigned long long)(s * (B2_BTILE >> 4));
 #pragma unroll
                 for (int mt = 0; mt < 2; mt++) {
+                    B2_STAMP(it, mt, 0);                                   // issuer reaches the accempty wait
                     if (it >= 1) b2_wait(accempty0 + 8 * mt, (unsigned)((it - 1) & 1));
+                    B2_STAMP(it, mt, 1);                                   // buffer free
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
                     for (int ks = 0; ks < 8; ks++) {
@@ -1296,6 +1324,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(B2_THREADS, 1) bf_to
                     if (mt == 1 && it + B2_STAGES < nstages)
                         asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(empty0 + 8u * s), "h"((unsigned short)3) : "memory");
                     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(accfull0 + 8u * mt), "h"((unsigned short)3) : "memory");
+                    B2_STAMP(it, mt, 2);                                   // the set's MMAs and commits are issued
                 }
             }
         }
@@ -1311,9 +1340,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(B2_THREADS, 1) bf_to
             }
         }
         for (int e = 0; e < nstages; e++) {
+            // Chunks share their progress: a row farther from the query than a second-best distance ANY chunk has already found cannot be in
+            // the merged top-2 (strictly farther: ties stay, so "first index wins" is untouched), so every chunk starts from - and keeps
+            // refreshing - the tightest published bound instead of re-learning its thresholds from scratch (with 270 k-row chunks 15 % of
+            // the warp-level filter steps otherwise take the divergent update path, and one late warp delays the accumulator hand-over).
+            if (a.bound_d2 && (e & B2_REFRESH) == 0 && cg == 0) {
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    const int qi = qbase + 256 * mt + row;
+                    if (qi < a.nq) {
+                        const int g = __ldcg(a.bound_d2 + qi);
+                        if (g < 512) atomicMax(&thr_s[mt * 128 + row], pq[mt] - g);
+                    }
+                }
+            }
 #pragma unroll
             for (int mt = 0; mt < 2; mt++) {
+                if (warp == B2_PROD_WARPS && lane == 0) B2_STAMP(e, mt, 3);       // consumer warp 0 starts waiting for the set
                 b2_wait(accfull0 + 8 * mt, (unsigned)(e & 1));
+                if (warp == B2_PROD_WARPS && lane == 0) B2_STAMP(e, mt, 4);       // ... sees it complete
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 // this warp's 64 columns of the set: both loads in flight, one wait, and the buffer is handed back before any filtering
                 // (.pack::16b loads, two columns per register, were tried: the TMEM read gets slower, not faster)
@@ -1323,6 +1368,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(B2_THREADS, 1) bf_to
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
+                if (warp == B2_PROD_WARPS && lane == 0) B2_STAMP(e, mt, 5);       // ... has its 64 columns in registers
+                if (warp == B2_PROD_WARPS + 15 && lane == 0) B2_STAMP(e, mt, 6);  // the last consumer warp likewise
                 if (lane == 0) b2_arrive_leader_relaxed(accempty0 + 8 * mt);       // nothing to publish: the TMEM reads have completed
                 thr[mt] = max(thr[mt], thr_s[mt * 128 + row]);
 #pragma unroll
@@ -1352,7 +1399,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(B2_THREADS, 1) bf_to
                                 }
                             }
                         }
-                        if (thr[mt] != 0x7fffffff) atomicMax(&thr_s[mt * 128 + row], thr[mt]);
+                        if (thr[mt] != 0x7fffffff) {
+                            atomicMax(&thr_s[mt * 128 + row], thr[mt]);
+                            if (a.bound_d2 && k2[mt] != 0xffffffffu) atomicMin(a.bound_d2 + qbase + 256 * mt + row, (int)(k2[mt] >> BF_IDX_BITS));
+                        }
                     }
                 }
             }
