@@ -259,29 +259,38 @@ def measure_latency(local_rank, dev):
 
 
 def measure_link_floor(world, dev, barrier, max_over_ranks, h2d_bytes, d2h_bytes, frames):
-    """What the host can move: every rank copies one step's input bytes H2D and one step's result bytes D2H from / to pinned memory
-    on two streams at the same time, all ranks concurrently.  e2e can not beat frames / this time."""
+    """What the host can move: every rank copies one step's input bytes H2D and one step's result bytes D2H from / to pinned memory, each
+    direction split over two streams (as the two handles of the e2e loop do), both directions and all ranks at the same time; best of three
+    passes.  e2e can not beat frames / this time by more than the probe's own imperfection."""
     import torch
     hin = torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory(); din = torch.empty(h2d_bytes, dtype=torch.uint8, device=dev)
     hout = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory(); dout = torch.empty(d2h_bytes, dtype=torch.uint8, device=dev)
-    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    streams = [torch.cuda.Stream(dev) for _ in range(4)]
+    hi, ho = h2d_bytes // 2, d2h_bytes // 2
 
     def go(n):
         for _ in range(n):
-            with torch.cuda.stream(s1):
-                din.copy_(hin, non_blocking=True)
-            with torch.cuda.stream(s2):
-                hout.copy_(dout, non_blocking=True)
-        s1.synchronize(); s2.synchronize()
+            with torch.cuda.stream(streams[0]):
+                din[:hi].copy_(hin[:hi], non_blocking=True)
+            with torch.cuda.stream(streams[1]):
+                din[hi:].copy_(hin[hi:], non_blocking=True)
+            with torch.cuda.stream(streams[2]):
+                hout[:ho].copy_(dout[:ho], non_blocking=True)
+            with torch.cuda.stream(streams[3]):
+                hout[ho:].copy_(dout[ho:], non_blocking=True)
+        for st in streams:
+            st.synchronize()
     go(2)
-    barrier()
-    t0 = time.perf_counter()
-    iters = 6
-    go(iters)
-    barrier()
-    dt = max_over_ranks(time.perf_counter() - t0)
-    return {"frames_per_s": world * frames * iters / dt, "h2d_GBps_per_gpu": h2d_bytes * iters / dt / 1e9, "d2h_GBps_per_gpu": d2h_bytes * iters / dt / 1e9,
-            "what": f"{world} rank(s) x (H2D {h2d_bytes} B + D2H {d2h_bytes} B) per step from pinned memory, both directions and all ranks at once"}
+    iters, best = 5, None
+    for _ in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        go(iters)
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        best = dt if best is None else min(best, dt)
+    return {"frames_per_s": world * frames * iters / best, "h2d_GBps_per_gpu": h2d_bytes * iters / best / 1e9, "d2h_GBps_per_gpu": d2h_bytes * iters / best / 1e9,
+            "what": f"{world} rank(s) x (H2D {h2d_bytes} B + D2H {d2h_bytes} B) per step from pinned memory, two streams per direction, both directions and all ranks at once, best of 3"}
 
 
 def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):

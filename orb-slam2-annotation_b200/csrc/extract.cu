@@ -107,7 +107,9 @@ struct orbx_handle {
     float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS], sigma2[ORBB_MAX_LEVELS], inv_sigma2[ORBB_MAX_LEVELS];
     int per_level[ORBB_MAX_LEVELS], umax[16];
     int q[7];
-    int l3_warps = 4;          // warps per level-kernel CTA (tile = 120 x 8*warps pixels)
+    int l3_warps = 4;          // warps per level-kernel CTA (tile = 120 x 8*warps pixels); ORBB_L3_WARPS = 2 | 4 | 8
+    bool l3_warps_forced = false;
+    int sm_count = 148;
     float factorPI;
     // geometry for the current image shape
     int cur_w = 0, cur_h = 0;
@@ -145,7 +147,7 @@ struct orbx_handle {
     const orbx_keypoint* last_kps_dev = nullptr; int last_capacity = 0;
     // orbx_graph_capture: the launch sequence of one device-resident extraction as an executable CUDA graph
     cudaGraphExec_t graph_exec = nullptr;
-    int graph_frames = 0;
+    int graph_frames = 0, graph_kernels = 0;
 };
 
 static void level_sizes(const orbx_handle* h, int w, int ht, int* lw, int* lh)
@@ -399,7 +401,7 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
         for (int i = 0; i < 7; i++) h->q[i] = cfg->blur_legacy ? QL[i] : Q[i];
     }
     h->factorPI = (float)(3.14159265358979323846 / 180.f);
-    { const char* e = getenv("ORBB_L3_WARPS"); if (e && atoi(e) == 8) h->l3_warps = 8; }
+    { const char* e = getenv("ORBB_L3_WARPS"); if (e && (atoi(e) == 8 || atoi(e) == 2 || atoi(e) == 4)) { h->l3_warps = atoi(e); h->l3_warps_forced = true; } }
 
     int rc = setup_geometry(h, cfg->max_width, cfg->max_height, true);
     if (rc != ORBB_OK) { delete h; return rc; }
@@ -423,6 +425,7 @@ extern "C" int orbx_create(const orbx_config* cfg, orbx_handle** out)
         ORBB_CUDA(cudaStreamCreateWithPriority(&h->s_side2[i], cudaStreamNonBlocking, prio_hi));
         ORBB_CUDA(cudaEventCreateWithFlags(&h->ev_side2[i], cudaEventDisableTiming));
     }
+    cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
     if (getenv("ORBB_NO_OCT_OVERLAP")) h->oct_overlap = false;
     if (const char* e = getenv("ORBB_KSTREAMS")) { const int v = atoi(e); if (v >= 1 && v <= 8) h->n_kstreams = v; }
     ok(dev_alloc(&h->d_pyr, B * h->cap_pyr)); ok(dev_alloc(&h->d_blur, B * h->cap_pyr));
@@ -542,7 +545,9 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         else { a.src = d_pyr + g.off; a.src_pitch = g.pitch; a.src_fstride = (long long)h->pyr_fstride; }
         a.w = g.w; a.h = g.h;
         a.status = d_status;
-        a.use_tma = encode_level_tmap(&a.tmap, a.src, g.w, g.h, nframes, (size_t)a.src_pitch, (size_t)a.src_fstride, 8 * h->l3_warps + 8) ? 1 : 0;
+        const int nw = h->l3_warps;          // (half-height tiles, ORBB_L3_WARPS=2, do not shorten a single frame's chain: 209 vs 207 us; neither does building the
+                                             //  pyramid first with a light resize kernel and running the levels side by side on eight streams: 242 vs 179 us)
+        a.use_tma = encode_level_tmap(&a.tmap, a.src, g.w, g.h, nframes, (size_t)a.src_pitch, (size_t)a.src_fstride, 8 * nw + 8) ? 1 : 0;
         a.blur = d_blur + g.off; a.blur_pitch = g.pitch; a.blur_fstride = (long long)h->pyr_fstride;
         const bool has_next = l + 1 < nl;
         // the fused resize needs the 4 source columns of a destination word inside the 4-pixel halo: scale <= 1.25
@@ -568,13 +573,11 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             if (k >= 1) { a.qmask = ((0xffu << k) & 0xffu) * 0x01010101u; a.qadd = (0x80u - (1u << (k - 1))) * 0x01010101u; }
             else { a.qmask = 0; a.qadd = 0x80808080u; }           // every valid pixel passes
         }
-        if (h->l3_warps == 8) {
-            dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, 8 * L3_RG), nframes);
-            if (legacy) level3_kernel<8, true><<<grid, 256, 0, st>>>(a);
-            else level3_kernel<8, false><<<grid, 256, 0, st>>>(a);
-        } else {
-            dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, 4 * L3_RG), nframes);
-            if (legacy) level3_kernel<4, true><<<grid, 128, 0, st>>>(a);
+        {
+            dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, nw * L3_RG), nframes);
+            if (nw == 8) { if (legacy) level3_kernel<8, true><<<grid, 256, 0, st>>>(a); else level3_kernel<8, false><<<grid, 256, 0, st>>>(a); }
+            else if (nw == 2) { if (legacy) level3_kernel<2, true><<<grid, 64, 0, st>>>(a); else level3_kernel<2, false><<<grid, 64, 0, st>>>(a); }
+            else if (legacy) level3_kernel<4, true><<<grid, 128, 0, st>>>(a);
             else level3_kernel<4, false><<<grid, 128, 0, st>>>(a);
         }
         ORBB_LAUNCHED();
@@ -620,7 +623,11 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         a.kps = kps_dev; a.desc = desc_dev; a.counts = counts_dev; a.capacity = capacity;
         a.factorPI = h->factorPI;
         const int maxk = capacity < (int)h->out_total ? capacity : (int)h->out_total;
-        orient_desc_kernel<<<dim3(ceil_div(maxk > 0 ? maxk : 1, 256), nframes), 256, 0, st>>>(a);
+        // a warp walks its keypoints one after the other (~1.5 us each): with few frames in the launch, fewer keypoints per warp
+        // shorten that serial chain (one 1000-keypoint frame: 49 -> 12 us) at no cost, the SMs being mostly idle
+        a.kpw = 32;
+        while (a.kpw > 4 && (long long)ceil_div(maxk > 0 ? maxk : 1, a.kpw) * nframes < 16ll * h->sm_count) a.kpw >>= 1;
+        orient_desc_kernel<<<dim3(ceil_div(ceil_div(maxk > 0 ? maxk : 1, a.kpw), OD_WARPS), nframes), 32 * OD_WARPS, 0, st>>>(a);
         ORBB_LAUNCHED();
     }
     if (tl_on) {
@@ -679,6 +686,7 @@ extern "C" int orbx_graph_capture(orbx_handle* h, const uint8_t* imgs_dev, int n
     ORBB_CUDA(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
     const uint64_t launched = g_launches.load();
     const int rc = enqueue_extract(h, imgs_dev, 0, nframes, w, ht, stride, fstride, kps_dev, desc_dev, counts_dev, capacity);
+    h->graph_kernels = (int)(g_launches.load() - launched);
     g_launches.store(launched);                                 // captured, not launched
     cudaGraph_t graph = nullptr;
     const cudaError_t ce = cudaStreamEndCapture(h->stream, &graph);
@@ -697,7 +705,7 @@ extern "C" int orbx_graph_launch(orbx_handle* h)
     if (!h->graph_exec) return ORBB_E_STATE;
     ORBB_CUDA(cudaSetDevice(h->cfg.device));
     ORBB_CUDA(cudaGraphLaunch(h->graph_exec, h->stream));
-    g_launches.fetch_add((uint64_t)(2 * h->nlevels + 1), std::memory_order_relaxed);      // level + octree kernels, descriptors
+    g_launches.fetch_add((uint64_t)h->graph_kernels, std::memory_order_relaxed);          // the kernels one replay launches
     h->last_frames = h->graph_frames;
     return ORBB_OK;
 }

@@ -690,6 +690,7 @@ struct DescArgs {
     const int4* lvl; long long lvl_fstride; const int* lvl_count;  // octree output
     orbx_keypoint* kps; uint8_t* desc; int* counts; int capacity;  // final output, frame f at f*capacity
     float factorPI;
+    int kpw;                                                       // keypoints per warp: 32 for full batches, fewer when a launch would not fill the GPU
 };
 
 __device__ __forceinline__ float fast_atan2_deg(float y, float x)
@@ -751,7 +752,7 @@ __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __g
     }
     __syncthreads();
     const int wid = blockIdx.x * OD_WARPS + warp;
-    const int base = wid * 32;
+    const int base = wid * a.kpw;
     const int* cnt = a.lvl_count + (long long)f * a.nlevels;
     // own keypoint: (level, index) from the per-level counts
     const int slot = base + lane;
@@ -763,7 +764,7 @@ __global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __g
     }
     const int total = acc;
     if (wid == 0 && lane == 0) a.counts[f] = total;
-    const int nvalid = min(min(total, a.capacity) - base, 32);      // keypoints handled by this warp
+    const int nvalid = min(min(total, a.capacity) - base, a.kpw);   // keypoints handled by this warp
     if (nvalid <= 0) return;
     const bool mine = lane < nvalid;
     int kx = 0, ky = 0, kresp = 0, pitch = 0, bpitch = 0;

@@ -104,7 +104,7 @@ template <int NW, bool LEGACY>
 #ifndef L3_MINB
 #define L3_MINB 8
 #endif
-__global__ void __launch_bounds__(32 * NW, NW == 4 ? L3_MINB : L3_MINB / 2) level3_kernel(const __grid_constant__ Level3Args a)
+__global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) level3_kernel(const __grid_constant__ Level3Args a)
 {
     constexpr int TH = L3_RG * NW, SMH = TH + 8, SCH = TH + 2, NT = 32 * NW;
     constexpr int QCAP = SCH * 122;                      // every scored pixel a candidate (uniform-noise images)
