@@ -249,6 +249,13 @@ int orbm_search_for_triangulation(const uint8_t* desc1, const orbx_keypoint* kps
 int orbm_search_by_projection_reloc(const orbm_frame* f, const orbm_proj_query* q_host, int nq, int max_dist, int check_orientation,
                                     int32_t* frame_mp, int* nmatches);
 int orbm_search_by_projection_loop(const orbm_frame* f, const orbm_proj_query* q_host, int nq, int32_t* matched, int* nmatches);
+/* Device-resident form of the two calls above (they are this call plus the copies): queries and the slot array (frame_mp / vpMatched as
+ * ids, -1 = empty) live on the device, window search and the order-dependent resolve ("a slot that holds a MapPoint is skipped", so every
+ * accepted match blocks its slot for the later queries: evaluated as the parallel fixed-point iteration of the a10 / a11 resolve) run
+ * there, queued on `stream` without host synchronisation.  Relocalisation: max_dist = ORBdist, check_orientation = mbCheckOrientation;
+ * loop closing: max_dist = TH_LOW (50), check_orientation = 0.  *status_dev / cand_capacity as in orbm_search_by_projection_points_device. */
+int orbm_search_by_projection_reloc_device(const orbm_frame* f, const orbm_proj_query* q_dev, int nq, int max_dist, int check_orientation,
+                                           int32_t* frame_mp_dev, int32_t* nmatches_dev, int32_t* status_dev, int cand_capacity, void* stream);
 int orbm_fuse_best(const orbm_frame* f, const orbm_proj_query* q_host, int nq, const float* mvuRight_host,
                    const float* inv_level_sigma2, int max_dist, int32_t* best_idx, int32_t* best_dist);
 

@@ -355,7 +355,7 @@ inline int rot_bin(float a1, float a2)
 // (SURVEY 8(f)-1).  Everything is queued on `st`; nothing is read back here.
 static int resolve_on_device(const orbm_frame* fr, int mode, const float* uright_dev, const orbm_proj_query* q_dev, int nq, float nnratio,
                              int check_ori, int32_t* frame_mp_dev, int32_t* frame_mp_obs_dev, int32_t* nmatches_dev, int32_t* status_dev,
-                             int32_t* rounds_dev, int cand_capacity, cudaStream_t st)
+                             int32_t* rounds_dev, int cand_capacity, cudaStream_t st, int max_dist = 100 /* TH_HIGH */)
 {
     const int cap = cand_capacity > 0 ? cand_capacity : 64 * nq + 1024;
     int rc;
@@ -377,10 +377,12 @@ static int resolve_on_device(const orbm_frame* fr, int mode, const float* uright
     ORBB_LAUNCHED();
     ResolveArgs a{};
     a.f = fr->f; a.q = q_dev; a.nq = nq; a.offs = fr->ws_offs.as<int>(); a.idx = fr->ws_idx.as<int>(); a.dist = fr->ws_dist.as<int>(); a.cap = cap;
-    a.uright = uright_dev; a.nnratio = nnratio; a.check_ori = check_ori; a.frame_mp = frame_mp_dev; a.frame_mp_obs = frame_mp_obs_dev;
+    a.uright = uright_dev; a.nnratio = nnratio; a.check_ori = check_ori; a.max_dist = max_dist; a.frame_mp = frame_mp_dev; a.frame_mp_obs = frame_mp_obs_dev;
     a.choice = fr->ws_choice.as<int>(); a.taker = fr->ws_taker.as<int>(); a.nmatches = nmatches_dev; a.status = status_dev; a.rounds = rounds_dev;
     const size_t smem = fr->n <= RESOLVE_SMEM_SLOTS ? (size_t)fr->n * 4 : 0;
-    if (mode == 0) resolve_projection_kernel<0><<<1, 1024, smem, st>>>(a); else resolve_projection_kernel<1><<<1, 1024, smem, st>>>(a);
+    if (mode == 0) resolve_projection_kernel<0><<<1, 1024, smem, st>>>(a);
+    else if (mode == 1) resolve_projection_kernel<1><<<1, 1024, smem, st>>>(a);
+    else resolve_projection_kernel<2><<<1, 1024, smem, st>>>(a);
     ORBB_LAUNCHED();
     ORBB_CUDA(cudaGetLastError());
     return ORBB_OK;
@@ -410,9 +412,9 @@ extern "C" int orbm_search_by_projection_frame_device(const orbm_frame* f, const
 
 // Host-pointer forms: upload the queries and the Frame's match state, run the device path, read the state back.
 static int search_projection_host(const orbm_frame* f, int mode, const float* uright, const orbm_proj_query* pq, int nq, float nnratio, int check_ori,
-                                  int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches)
+                                  int32_t* frame_mp, int32_t* frame_mp_obs, int* nmatches, int max_dist = 100 /* TH_HIGH */)
 {
-    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && (!frame_mp || !frame_mp_obs))) return ORBB_E_INVALID;
+    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && (!frame_mp || (mode != 2 && !frame_mp_obs)))) return ORBB_E_INVALID;
     *nmatches = 0;
     int rc = check_device(f->device);
     if (rc != ORBB_OK) return rc;
@@ -428,10 +430,10 @@ static int search_projection_host(const orbm_frame* f, int mode, const float* ur
     for (int attempt = 0; attempt < 2; attempt++) {
         if (f->n > 0) {
             ORBB_CUDA(cudaMemcpy(f->ws_mp.p, frame_mp, nb, cudaMemcpyHostToDevice));
-            ORBB_CUDA(cudaMemcpy(f->ws_obs.p, frame_mp_obs, nb, cudaMemcpyHostToDevice));
+            if (frame_mp_obs) ORBB_CUDA(cudaMemcpy(f->ws_obs.p, frame_mp_obs, nb, cudaMemcpyHostToDevice));
         }
         rc = resolve_on_device(f, mode, uright ? f->ws_uright.as<float>() : nullptr, q.as<orbm_proj_query>(), nq, nnratio, check_ori,
-                               f->ws_mp.as<int32_t>(), f->ws_obs.as<int32_t>(), sc, sc + 1, sc + 2, cap, 0);
+                               f->ws_mp.as<int32_t>(), frame_mp_obs ? f->ws_obs.as<int32_t>() : nullptr, sc, sc + 1, sc + 2, cap, 0, max_dist);
         if (rc != ORBB_OK) return rc;
         int32_t h[3] = {0, 0, 0};
         ORBB_CUDA(cudaMemcpy(h, sc, sizeof(h), cudaMemcpyDeviceToHost));
@@ -444,7 +446,7 @@ static int search_projection_host(const orbm_frame* f, int mode, const float* ur
         *nmatches = h[0];
         if (f->n > 0) {
             ORBB_CUDA(cudaMemcpy(frame_mp, f->ws_mp.p, nb, cudaMemcpyDeviceToHost));
-            ORBB_CUDA(cudaMemcpy(frame_mp_obs, f->ws_obs.p, nb, cudaMemcpyDeviceToHost));
+            if (frame_mp_obs) ORBB_CUDA(cudaMemcpy(frame_mp_obs, f->ws_obs.p, nb, cudaMemcpyDeviceToHost));
         }
         return ORBB_OK;
     }
@@ -472,65 +474,30 @@ extern "C" int orbm_search_by_projection_frame(const orbm_frame* f, const float*
 extern "C" int orbm_search_by_projection_reloc(const orbm_frame* f, const orbm_proj_query* pq, int nq, int max_dist, int check_ori,
                                                int32_t* frame_mp, int* nmatches)
 {
-    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && !frame_mp)) return ORBB_E_INVALID;
-    *nmatches = 0;
-    if (nq == 0) return ORBB_OK;
-    std::vector<orbm_query> q(nq);
-    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
-    std::vector<int> offs, idx, dist;
-    const int rc = run_window_search(f, q, offs, idx, dist);
+    if (max_dist < 0) return ORBB_E_INVALID;
+    // window search + resolve on the device (resolve_projection_kernel<2>: every occupied slot is skipped, any accepted match blocks its slot
+    // for the later queries, best <= ORBdist, rotation histogram :1766-1786); a query without candidates never matches, whatever max_dist
+    return search_projection_host(f, 2, nullptr, pq, nq, 0.f, check_ori, frame_mp, nullptr, nmatches, max_dist > 255 ? 255 : max_dist);
+}
+
+// The same with device arrays, queued on `stream` without host synchronisation (include/orbb200.h).
+extern "C" int orbm_search_by_projection_reloc_device(const orbm_frame* f, const orbm_proj_query* q_dev, int nq, int max_dist, int check_ori,
+                                                      int32_t* frame_mp_dev, int32_t* nmatches_dev, int32_t* status_dev, int cand_capacity, void* stream)
+{
+    if (!f || nq <= 0 || max_dist < 0 || !q_dev || !nmatches_dev || !status_dev || (f->n > 0 && !frame_mp_dev)) return ORBB_E_INVALID;
+    const int rc = check_device(f->device);
     if (rc != ORBB_OK) return rc;
-    std::vector<int> rotHist[HISTO_LENGTH];
-    int nm = 0;
-    for (int i = 0; i < nq; i++) {
-        int bestDist = 256, bestIdx2 = -1;
-        for (int c = offs[i]; c < offs[i + 1]; c++) {
-            const int i2 = idx[c];
-            if (frame_mp[i2] >= 0) continue;                                            // :1727-1728
-            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx2 = i2; }
-        }
-        if (bestIdx2 >= 0 && bestDist <= max_dist) {                                    // :1742-1760 (the guard keeps max_dist >= 256 in bounds)
-            frame_mp[bestIdx2] = pq[i].id;
-            nm++;
-            if (check_ori) rotHist[rot_bin(pq[i].angle, f->h_kps[bestIdx2].angle)].push_back(bestIdx2);
-        }
-    }
-    if (check_ori) {                                                                    // :1766-1786
-        int ind1 = -1, ind2 = -1, ind3 = -1;
-        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
-        for (int b = 0; b < HISTO_LENGTH; b++)
-            if (b != ind1 && b != ind2 && b != ind3)
-                for (size_t j = 0; j < rotHist[b].size(); j++) { frame_mp[rotHist[b][j]] = -1; nm--; }
-    }
-    *nmatches = nm;
-    return ORBB_OK;
+    return resolve_on_device(f, 2, nullptr, q_dev, nq, 0.f, check_ori, frame_mp_dev, nullptr, nmatches_dev, status_dev, nullptr, cand_capacity,
+                             (cudaStream_t)stream, max_dist > 255 ? 255 : max_dist);
 }
 
 // SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints, vector<MapPoint*>& vpMatched, th)
-// (ORBmatcher.cpp:352-472): KeyFrame::GetFeaturesInArea has no level filter, the level gate [p-1, p] follows (:441-444) — the
-// same set as a window query with that level range; already matched features are skipped (:438-439); best <= TH_LOW (:457).
+// (ORBmatcher.cpp:352-472): KeyFrame::GetFeaturesInArea has no level filter, the level gate [p-1, p] follows (:441-444) - the
+// same set as a window query with that level range; already matched features are skipped (:438-439); best <= TH_LOW (:457); no
+// orientation check.  The relocalisation resolve with those parameters.
 extern "C" int orbm_search_by_projection_loop(const orbm_frame* f, const orbm_proj_query* pq, int nq, int32_t* matched, int* nmatches)
 {
-    if (!f || nq < 0 || !nmatches || (nq > 0 && !pq) || (f->n > 0 && !matched)) return ORBB_E_INVALID;
-    *nmatches = 0;
-    if (nq == 0) return ORBB_OK;
-    std::vector<orbm_query> q(nq);
-    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
-    std::vector<int> offs, idx, dist;
-    const int rc = run_window_search(f, q, offs, idx, dist);
-    if (rc != ORBB_OK) return rc;
-    int nm = 0;
-    for (int i = 0; i < nq; i++) {
-        int bestDist = 256, bestIdx = -1;
-        for (int c = offs[i]; c < offs[i + 1]; c++) {
-            const int k = idx[c];
-            if (matched[k] >= 0) continue;
-            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx = k; }
-        }
-        if (bestDist <= TH_LOW) { matched[bestIdx] = pq[i].id; nm++; }
-    }
-    *nmatches = nm;
-    return ORBB_OK;
+    return search_projection_host(f, 2, nullptr, pq, nq, 0.f, 0, matched, nullptr, nmatches, TH_LOW);
 }
 
 // The per-point search of Fuse(KeyFrame*, const vector<MapPoint*>&, th) (ORBmatcher.cpp:962-1115; chi-square reprojection gate

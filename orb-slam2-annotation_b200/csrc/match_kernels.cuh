@@ -212,6 +212,8 @@ __global__ void grid_sort_kernel(FrameDev f)
 // FILTER (the device resolve): records are orbm_proj_query; candidates that can never be chosen — the Frame slot already holds a
 // MapPoint with observations (ORBmatcher.cpp:112-114, :1590-1592) or the stereo gate fails (:116-121, :1594-1601) — are dropped
 // here, where the lanes of the warp test them in parallel, and cand_dist carries the candidate's octave in bits 16+.
+// frame_mp_obs == nullptr: every slot that already holds a MapPoint is skipped (relocalisation / loop-closing overloads, ORBmatcher.cpp
+// :1727-1728, :438-439); else only slots whose MapPoint has observations (:1590-1592, :107-109)
 struct WindowFilter { const int* frame_mp; const int* frame_mp_obs; const float* uright; };
 
 template <bool FILL, bool FILTER = false>
@@ -259,7 +261,7 @@ __global__ void window_search_kernel(FrameDev f, const void* __restrict__ qs, si
                     oct = kp.octave;
                     if (FILTER && ok) {
                         const orbm_proj_query& pq = reinterpret_cast<const orbm_proj_query&>(q);
-                        if (flt.frame_mp[idx] >= 0 && flt.frame_mp_obs[idx] > 0) ok = false;
+                        if (flt.frame_mp[idx] >= 0 && (!flt.frame_mp_obs || flt.frame_mp_obs[idx] > 0)) ok = false;
                         if (flt.uright) {
                             const float urk = flt.uright[idx];
                             if (urk > 0 && fabsf(__fsub_rn(pq.u_right, urk)) > pq.max_err_right) ok = false;
@@ -329,7 +331,8 @@ struct ResolveArgs {
     const int* offs; const int* idx; const int* dist; int cap;     // candidate CSR (offs[nq] > cap: overflow, nothing is written)
     const float* uright;                                           // mvuRight or nullptr
     float nnratio; int check_ori;
-    int* frame_mp; int* frame_mp_obs;                              // [f.n] in/out
+    int max_dist;                                                  // accept best <= max_dist: TH_HIGH (a10, a11), ORBdist (reloc), TH_LOW (loop)
+    int* frame_mp; int* frame_mp_obs;                              // [f.n] in/out (frame_mp_obs null in MODE 2)
     int* choice;                                                   // [nq] scratch
     int* taker;                                                    // [f.n] scratch
     int* nmatches; int* status; int* rounds;                       // device scalars (rounds may be nullptr)
@@ -358,7 +361,7 @@ __device__ __forceinline__ int resolve_choose(const ResolveArgs& a, const int* _
             } else if (d < bestDist) { bestDist = d; bestIdx = k[j]; }
         }
     }
-    if (bestDist > TH_HIGH) return -1;
+    if (bestIdx < 0 || bestDist > a.max_dist) return -1;
     if (MODE == 0 && bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(a.nnratio, (float)bestDist2)) return -1;
     return bestIdx;
 }
@@ -393,7 +396,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
         if (tid == 0) changed_s = 0;
         for (int i = tid; i < a.nq; i += nt) {
             const int c = a.choice[i];
-            if (c >= 0 && a.q[i].has_obs > 0) atomicMin(&taker[c], i);
+            if (c >= 0 && (MODE == 2 || a.q[i].has_obs > 0)) atomicMin(&taker[c], i);      // MODE 2: any MapPoint blocks the slot for later queries
         }
         __syncthreads();
     }
@@ -408,8 +411,8 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
         const int c = a.choice[i];
         if (c < 0) continue;
         mine++;
-        if (taker[c] == -i - 1) { a.frame_mp[c] = a.q[i].id; a.frame_mp_obs[c] = a.q[i].has_obs; }
-        if (MODE == 1 && a.check_ori) {
+        if (taker[c] == -i - 1) { a.frame_mp[c] = a.q[i].id; if (MODE != 2) a.frame_mp_obs[c] = a.q[i].has_obs; }
+        if (MODE >= 1 && a.check_ori) {
             float rot = __fsub_rn(a.q[i].angle, a.f.kps[c].angle);
             if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
             int bin = (int)roundf(__fmul_rn(rot, 30 / 360.0f));
@@ -419,7 +422,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
     }
     if (mine) atomicAdd(&nm_s, mine);
     __syncthreads();
-    if (MODE == 1 && a.check_ori) {
+    if (MODE >= 1 && a.check_ori) {
         if (tid == 0) {                                     // ComputeThreeMaxima
             int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
             for (int b = 0; b < 30; b++) {

@@ -28,7 +28,7 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "or
            "orbx_extract_batch", "orbx_graph_capture", "orbx_graph_launch", "orbx_sync", "orbx_set_profiling", "orbx_get_profile", "orbx_stream", "orbx_pyramid_level", "orbx_debug_stage",
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbx_set_rectification", "orbx_extract_batch_rectified", "orbx_remap_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_frame_create_device", "orbm_undistort_keypoints", "orbm_undistort_keypoints_device", "orbm_image_bounds",
-           "orbm_search_by_projection_points_device", "orbm_search_by_projection_frame_device", "orbm_search_by_projection_reloc", "orbm_search_by_projection_loop", "orbm_fuse_best",
+           "orbm_search_by_projection_points_device", "orbm_search_by_projection_frame_device", "orbm_search_by_projection_reloc", "orbm_search_by_projection_reloc_device", "orbm_search_by_projection_loop", "orbm_fuse_best",
            "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_bf_top2_noalloc", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
@@ -105,6 +105,7 @@ def lib():
         L.orbm_search_by_bow.argtypes = [vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, C.POINTER(i32), i32]
         L.orbm_search_by_bow_kf.argtypes = [vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, vp, i32, vp, vp, vp, i32, f32, i32, vp, C.POINTER(i32), i32]
         L.orbm_search_by_projection_reloc.argtypes = [vp, vp, i32, i32, i32, vp, C.POINTER(i32)]
+        L.orbm_search_by_projection_reloc_device.argtypes = [vp, vp, i32, i32, i32, vp, vp, vp, i32, vp]
         L.orbm_search_by_projection_loop.argtypes = [vp, vp, i32, vp, C.POINTER(i32)]
         L.orbm_fuse_best.argtypes = [vp, vp, i32, vp, vp, i32, vp, vp]
         L.orbm_search_for_triangulation.argtypes = ([vp] * 4 + [i32] + [vp] * 3 + [i32]) * 2 + [vp, f32, f32, vp, vp, i32, i32, vp, C.POINTER(i32), i32]

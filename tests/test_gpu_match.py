@@ -599,3 +599,33 @@ def test_tensor_peak_probes(gpu):
     tc = orbb200.tcgen05_i8_peak(0)
     assert 500 < legacy < 2500
     assert 2 * legacy < tc < 6000, (legacy, tc)
+
+
+def test_reloc_and_loop_resolve_on_device(gpu):
+    """orbm_search_by_projection_reloc_device: queries and the slot array stay on the device, window search and the order-dependent resolve
+    (every accepted match blocks its slot for the later queries) run there without host synchronisation.  Wide windows make many queries
+    compete for the same features; the result must equal the sequential oracle loop, for the relocalisation parameters (ORBdist,
+    orientation check) and the loop-closing ones (TH_LOW, no orientation check)."""
+    import ctypes as C
+    import torch, orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=16)
+    rng = np.random.default_rng(12)
+    h, w = cur.shape
+    F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h)); O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    L = orbb200.lib()
+    st = torch.cuda.Stream()
+    for th, maxd, check, levels in [(40.0, 100, True, "pm1"), (25.0, 64, False, "pm1"), (40.0, 50, False, "pred")]:
+        q = _queries(kl, dl, scale, th, (3, 1), rng, levels)
+        mp0 = np.full(len(kc), -1, np.int32); mp0[::13] = 5555
+        on, omp = (O.search_reloc(_to_oracle_queries(q), maxd, check, mp0) if levels == "pm1" else O.search_loop(_to_oracle_queries(q), mp0))
+        with torch.cuda.stream(st):
+            qd = torch.from_numpy(q.view(np.uint8).reshape(-1).copy()).cuda()
+            mpd = torch.from_numpy(mp0.copy()).cuda()
+            sc = torch.zeros(2, dtype=torch.int32, device="cuda")
+            rc = L.orbm_search_by_projection_reloc_device(F.h, C.c_void_p(qd.data_ptr()), len(q), maxd, int(check), C.c_void_p(mpd.data_ptr()),
+                                                          C.c_void_p(sc.data_ptr()), C.c_void_p(sc.data_ptr() + 4), 0, C.c_void_p(st.cuda_stream))
+            assert rc == 0
+        st.synchronize()
+        n, status = sc.cpu().tolist()
+        assert status == 0 and n == on and np.array_equal(mpd.cpu().numpy(), omp), (th, maxd, check, levels)
+        assert n > 0.2 * len(kl)
