@@ -509,35 +509,47 @@ extern "C" int orbm_fuse_best(const orbm_frame* f, const orbm_proj_query* pq, in
 {
     if (!f || nq < 0 || (nq > 0 && (!pq || !best_idx))) return ORBB_E_INVALID;
     if (nq == 0) return ORBB_OK;
-    std::vector<orbm_query> q(nq);
-    for (int i = 0; i < nq; i++) q[i] = pq[i].q;
-    std::vector<int> offs, idx, dist;
-    const int rc = run_window_search(f, q, offs, idx, dist);
-    if (rc != ORBB_OK) return rc;
-    for (int i = 0; i < nq; i++) {
-        const float u = pq[i].q.u, v = pq[i].q.v, ur = pq[i].u_right;
-        int bestDist = 256, bestIdx = -1;
-        for (int c = offs[i]; c < offs[i + 1]; c++) {
-            const int k = idx[c];
-            if (inv_level_sigma2) {
-                const orbx_keypoint& kp = f->h_kps[k];
-                const float ex = u - kp.x, ey = v - kp.y;
-                if (uright && uright[k] >= 0) {                                         // :1053-1066
-                    const float er = ur - uright[k];
-                    const float e2 = ex * ex + ey * ey + er * er;
-                    if (e2 * inv_level_sigma2[kp.octave] > 7.8) continue;
-                } else {                                                                // :1067-1078
-                    const float e2 = ex * ex + ey * ey;
-                    if (e2 * inv_level_sigma2[kp.octave] > 5.99) continue;
-                }
-            }
-            if (dist[c] < bestDist) { bestDist = dist[c]; bestIdx = k; }
-        }
-        const bool ok = bestIdx >= 0 && bestDist <= max_dist;
-        best_idx[i] = ok ? bestIdx : -1;
-        if (best_dist) best_dist[i] = ok ? bestDist : -1;
+    int rc = check_device(f->device);
+    if (rc != ORBB_OK || (rc = frame_wait_ready(f)) != ORBB_OK) return rc;
+    // window search and the per-point selection on the device (fuse_best_kernel); only best_idx / best_dist come back
+    int nlev = 0;
+    if (inv_level_sigma2) {                               // the caller's table has one entry per pyramid level: upload as many as the frame's octaves need
+        if ((rc = frame_host_copies(f)) != ORBB_OK) return rc;
+        for (int k = 0; k < f->n; k++) nlev = std::max(nlev, f->h_kps[k].octave + 1);
+        if (nlev > 64) return ORBB_E_INVALID;
     }
-    return ORBB_OK;
+    DevBuf q, counts, offs, idx, dist, dur, dsig, dbi, dbd;
+    const size_t nb = (size_t)f->n * 4;
+    if ((rc = q.alloc((size_t)nq * sizeof(orbm_proj_query))) || (rc = counts.alloc((size_t)nq * 4)) || (rc = offs.alloc((size_t)(nq + 1) * 4)) ||
+        (rc = dbi.alloc((size_t)nq * 4)) || (rc = dbd.alloc((size_t)nq * 4)) || (uright && inv_level_sigma2 && (rc = dur.alloc(nb))) ||
+        (nlev > 0 && (rc = dsig.alloc((size_t)nlev * 4)))) return rc;
+    ORBB_CUDA(cudaMemcpy(q.p, pq, (size_t)nq * sizeof(orbm_proj_query), cudaMemcpyHostToDevice));
+    if (dur.p && f->n > 0) ORBB_CUDA(cudaMemcpy(dur.p, uright, nb, cudaMemcpyHostToDevice));
+    if (dsig.p) ORBB_CUDA(cudaMemcpy(dsig.p, inv_level_sigma2, (size_t)nlev * 4, cudaMemcpyHostToDevice));
+    const int wpb = 8;
+    window_search_kernel<false><<<ceil_div(nq, wpb), wpb * 32>>>(f->f, q.p, sizeof(orbm_proj_query), nq, counts.as<int>(), nullptr, nullptr, nullptr, 0);
+    ORBB_LAUNCHED();
+    excl_scan_kernel<<<1, 1024>>>(counts.as<int>(), offs.as<int>(), nq);
+    ORBB_LAUNCHED();
+    int cap = 64 * nq + 1024;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        if ((rc = idx.reserve((size_t)cap * 4)) || (rc = dist.reserve((size_t)cap * 4))) return rc;
+        window_search_kernel<true><<<ceil_div(nq, wpb), wpb * 32>>>(f->f, q.p, sizeof(orbm_proj_query), nq, nullptr, offs.as<int>(), idx.as<int>(), dist.as<int>(), cap);
+        ORBB_LAUNCHED();
+        fuse_best_kernel<<<ceil_div(nq, 128), 128>>>(f->f, q.as<orbm_proj_query>(), nq, offs.as<int>(), idx.as<int>(), dist.as<int>(), cap,
+                                                    dur.p ? dur.as<float>() : nullptr, dsig.p ? dsig.as<float>() : nullptr, max_dist, dbi.as<int>(), dbd.as<int>());
+        ORBB_LAUNCHED();
+        ORBB_CUDA(cudaGetLastError());
+        int total = 0;
+        ORBB_CUDA(cudaMemcpy(&total, offs.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
+        if (total <= cap) {
+            ORBB_CUDA(cudaMemcpy(best_idx, dbi.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+            if (best_dist) ORBB_CUDA(cudaMemcpy(best_dist, dbd.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+            return ORBB_OK;
+        }
+        cap = total + 16;                                 // more candidates than the default budget: size it exactly
+    }
+    return ORBB_E_CAPACITY;
 }
 
 // ---- ORBmatcher::SearchByBoW ---------------------------------------------------------------------------

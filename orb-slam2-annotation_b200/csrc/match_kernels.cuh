@@ -452,6 +452,40 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
     if (tid == 0) { *a.nmatches = nm_s; *a.status = ORBB_OK; if (a.rounds) *a.rounds = rounds; }
 }
 
+// The per-point search of Fuse / SearchBySim3 (ORBmatcher.cpp:962-1115, :1119-1251, :1253-1500) on the candidate CSR: queries do not
+// interact, a thread owns one projected MapPoint.  First candidate (in GetFeaturesInArea order) with the smallest distance among those that
+// pass the chi-square reprojection gate when inv_level_sigma2 is given (:1053-1078: three degrees of freedom, 7.8, when the feature has a
+// right coordinate, else two, 5.99; float products, double comparison as in the reference); -1 unless best <= max_dist.
+__global__ void fuse_best_kernel(FrameDev f, const orbm_proj_query* __restrict__ q, int nq, const int* __restrict__ offs, const int* __restrict__ idx,
+                                 const int* __restrict__ dist, int cap, const float* __restrict__ uright, const float* __restrict__ inv_level_sigma2,
+                                 int max_dist, int* __restrict__ best_idx, int* __restrict__ best_dist)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq || offs[nq] > cap) return;                 // overflow: the host repeats the call with the exact capacity
+    const float u = q[i].q.u, v = q[i].q.v, ur = q[i].u_right;
+    int bestDist = 256, bestIdx = -1;
+    for (int c = offs[i]; c < offs[i + 1]; c++) {
+        const int k = idx[c];
+        if (inv_level_sigma2) {
+            const orbx_keypoint kp = f.kps[k];
+            const float ex = __fsub_rn(u, kp.x), ey = __fsub_rn(v, kp.y);
+            if (uright && uright[k] >= 0) {
+                const float er = __fsub_rn(ur, uright[k]);
+                const float e2 = __fadd_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)), __fmul_rn(er, er));
+                if ((double)__fmul_rn(e2, inv_level_sigma2[kp.octave]) > 7.8) continue;
+            } else {
+                const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                if ((double)__fmul_rn(e2, inv_level_sigma2[kp.octave]) > 5.99) continue;
+            }
+        }
+        const int d = dist[c];
+        if (d < bestDist) { bestDist = d; bestIdx = k; }
+    }
+    const bool ok = bestIdx >= 0 && bestDist <= max_dist;
+    best_idx[i] = ok ? bestIdx : -1;
+    if (best_dist) best_dist[i] = ok ? bestDist : -1;
+}
+
 // ------------------------------------------------------------------------------------------------------
 // Stereo (Frame.cpp:540-748)
 // ------------------------------------------------------------------------------------------------------
