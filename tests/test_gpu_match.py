@@ -629,3 +629,41 @@ def test_reloc_and_loop_resolve_on_device(gpu):
         n, status = sc.cpu().tolist()
         assert status == 0 and n == on and np.array_equal(mpd.cpu().numpy(), omp), (th, maxd, check, levels)
         assert n > 0.2 * len(kl)
+
+
+def test_matcher_entry_points_from_concurrent_host_threads(gpu):
+    """The reference calls the matcher from several threads (Tracking, LocalMapping, LoopClosing).  The host-pointer entry points run on
+    per-thread default streams and take their scratch from the library's shared block cache: four threads hammer frame creation, both
+    SearchByProjection forms, the relocalisation form, Fuse and descriptor distances at once; every result must equal the oracle's."""
+    import threading
+    import orbb200, pyoracle
+    (cur, kc, dc), (last, kl, dl), scale = _frames(seed=17)
+    h, w = cur.shape
+    O = pyoracle.OracleFrame(kc, dc, (0, 0, w, h))
+    rng = np.random.default_rng(13)
+    q = _queries(kl, dl, scale, 15.0, (3, 1), rng)
+    oq = _to_oracle_queries(q)
+    mp0 = np.full(len(kc), -1, np.int32); ob0 = np.zeros(len(kc), np.int32); mp0[::17] = 9999; ob0[::17] = 1
+    exp_frame = O.search_last_frame(oq, True, mp0, ob0, None)
+    exp_pts = O.search_local_points(oq, 0.8, mp0, ob0, None)
+    exp_reloc = O.search_reloc(oq, 100, True, mp0)
+    exp_dist = pyoracle.distance_pairs(dc[:500], dl[:500])
+    errs = []
+
+    def work(t):
+        try:
+            for it in range(12):
+                F = orbb200.FrameMatcher(kc, dc, (0, 0, w, h))
+                n, mp, ob = orbb200.ORBmatcher(0.9, True).SearchByProjection_frame(F, q, mp0, ob0, None)
+                assert n == exp_frame[0] and np.array_equal(mp, exp_frame[1]) and np.array_equal(ob, exp_frame[2]), ("frame", t, it)
+                n, mp, ob = orbb200.ORBmatcher(0.8).SearchByProjection_points(F, q, mp0, ob0, None)
+                assert n == exp_pts[0] and np.array_equal(mp, exp_pts[1]), ("points", t, it)
+                n, mp = orbb200.ORBmatcher(0.9, True).SearchByProjection_reloc(F, q, mp0, 100)
+                assert n == exp_reloc[0] and np.array_equal(mp, exp_reloc[1]), ("reloc", t, it)
+                assert np.array_equal(orbb200.DescriptorDistance(dc[:500], dl[:500]), exp_dist), ("dist", t, it)
+                F.close()
+        except Exception as e:          # surfaced after join
+            errs.append(e)
+    th = [threading.Thread(target=work, args=(t,)) for t in range(4)]
+    [t.start() for t in th]; [t.join() for t in th]
+    assert not errs, errs[0]
