@@ -640,17 +640,16 @@ def run_ours(args, rank, world, local_rank):
     qd = torch.from_numpy(qh).to(dev)
     d1 = torch.empty(NQ, dtype=torch.int32, device=dev); i1 = torch.empty(NQ, dtype=torch.int64, device=dev); d2 = torch.empty(NQ, dtype=torch.int32, device=dev)
     if world > 1:
-        d1a = torch.empty((world, NQ), dtype=torch.int32, device=dev); i1a = torch.empty((world, NQ), dtype=torch.int64, device=dev)
-        d2a = torch.empty((world, NQ), dtype=torch.int32, device=dev)
+        import sharding
         m1 = torch.empty_like(d1); mi = torch.empty_like(i1); m2 = torch.empty_like(d2)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 
     def step_match():
         with torch.cuda.stream(stream):
             D.top2_device(qd.data_ptr(), NQ, d1.data_ptr(), i1.data_ptr(), d2.data_ptr(), stream.cuda_stream)
-            if world > 1:       # the one real exchange step: all-gather the per-shard (d1, idx1, d2), merge on every rank
-                dist.all_gather_into_tensor(d1a, d1); dist.all_gather_into_tensor(i1a, i1); dist.all_gather_into_tensor(d2a, d2)
-                orbb200.merge_top2_device(d1a.data_ptr(), i1a.data_ptr(), d2a.data_ptr(), world, NQ, m1.data_ptr(), mi.data_ptr(), m2.data_ptr(),
+            if world > 1:       # the one real exchange step: ONE packed all-gather of the per-shard (d1, idx1, d2) (16 B per query), merge on every rank
+                g1, gi, g2 = sharding.gather_top2(d1, i1, d2)
+                orbb200.merge_top2_device(g1.data_ptr(), gi.data_ptr(), g2.data_ptr(), world, NQ, m1.data_ptr(), mi.data_ptr(), m2.data_ptr(),
                                           stream.cuda_stream)
     for _ in range(3):
         step_match()

@@ -741,7 +741,10 @@ __device__ __forceinline__ void od_load_rows(unsigned (&w)[NIT], const uint8_t* 
     for (int it = 0; it < NIT; it++) w[it] = __ldg(reinterpret_cast<const unsigned*>(q + (unsigned long long)it * p3));
 }
 
-__global__ void __launch_bounds__(32 * OD_WARPS, 3) orient_desc_kernel(const __grid_constant__ DescArgs a)
+#ifndef OD_MINB
+#define OD_MINB 3
+#endif
+__global__ void __launch_bounds__(32 * OD_WARPS, OD_MINB) orient_desc_kernel(const __grid_constant__ DescArgs a)
 {
     __shared__ __align__(16) uint32_t patch_s[OD_WARPS][2][3 * OD_PIT * OD_PW + 2];      // two windows per warp: one in use, one in flight
     __shared__ uint32_t absu_s[40];            // |u0+b| packed per byte, indexed by u0 + 18

@@ -12,7 +12,7 @@ for v in "$@" orig; do
   esac
   cd ..
   env $E python -m pytest tests/test_gpu_extract.py -m gpu -x -q 2>&1 | tail -1
-  env $E python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_ab.json 2>gpurun_out/bench_ab.err
+  env $E python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-configs > gpurun_out/bench_ab.json 2>gpurun_out/bench_ab.err
   python -c "
 import json;d=json.load(open('gpurun_out/bench_ab.json'));print('$v value',round(d['value']),'e2e',round(d['e2e']['value']),'share',{k:round(x,4) for k,x in d['roofline']['step_share'].items()})"
   cd orb-slam2-annotation_b200
