@@ -12,6 +12,7 @@ N > 1   : launched by torch.distributed.run, one rank per GPU; frames shard with
 import argparse
 import json
 import os
+import queue
 import statistics
 import sys
 import threading
@@ -368,6 +369,8 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
                               ur=np.zeros(cap, np.float32), dp=np.zeros(cap, np.float32), mp=np.zeros(cap, np.int32), ob=np.zeros(cap, np.int32)) for _ in range(2)]
             self.nL, self.nR, self.nm = C.c_int(), C.c_int(), C.c_int()
             self.stats = {"stereo": 0, "proj": 0, "kp": 0}
+            self.right_job, self.right_done = queue.Queue(), queue.Queue()
+            threading.Thread(target=self._right_worker, daemon=True).start()
             self.one_pair(0, None); n0 = self.nL.value
             self.one_pair(1, None); n1 = self.nL.value
             self.qs = [self.queries_from(self.bufs[1], n1, 3.0, 1.0), self.queries_from(self.bufs[0], n0, -3.0, -1.0)]   # queries for pair 0 come from pair 1 and vice versa
@@ -375,11 +378,24 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
                 self.one_pair(i, self.qs[i & 1])
             self.stats.update(stereo=0, proj=0, kp=0)
 
+        def _right_worker(self):
+            while True:
+                job = self.right_job.get()
+                if job is None:
+                    return
+                right, b = job
+                self.right_done.put(L.orbx_extract(self.exR.h, ptr(right), w, h, w, ptr(b["kR"]), ptr(b["dR"]), cap, C.byref(self.nR)))
+
+        def close(self):
+            self.right_job.put(None)
+
         def one_pair(self, i, queries):
             b = self.bufs[i & 1]; left, right = pairs[i & 1]
             nL, nR, nm = self.nL, self.nR, self.nm
+            # the reference extracts the two images on two threads (Frame.cpp:84-87: threadLeft / threadRight): so does this pipeline
+            self.right_job.put((right, b))
             assert L.orbx_extract(self.exL.h, ptr(left), w, h, w, ptr(b["kL"]), ptr(b["dL"]), cap, C.byref(nL)) == 0
-            assert L.orbx_extract(self.exR.h, ptr(right), w, h, w, ptr(b["kR"]), ptr(b["dR"]), cap, C.byref(nR)) == 0
+            assert self.right_done.get() == 0
             assert L.orbm_stereo_match(self.exL.h, self.exR.h, ptr(b["kL"]), ptr(b["dL"]), nL.value, ptr(b["kR"]), ptr(b["dR"]), nR.value,
                                        C.c_float(mbf), C.c_float(0.0), ptr(b["ur"]), ptr(b["dp"])) == 0
             fh = vp()
@@ -404,7 +420,7 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
             for i in range(npairs):
                 self.one_pair(i, self.qs[i & 1])
 
-    api = ("per pair, host pointers: orbx_extract (L) + orbx_extract (R) + orbm_stereo_match + orbm_frame_create + orbm_search_by_projection_frame + "
+    api = ("per pair, host pointers: orbx_extract (L) and orbx_extract (R) on two threads as in Frame.cpp:84-87, then orbm_stereo_match + orbm_frame_create + orbm_search_by_projection_frame + "
            "orbm_frame_destroy; wall clock, H2D/D2H inside every call")
     for nthreads, npairs in ((1, 40), (4, 40)):
         pipes = [Pipeline() for _ in range(nthreads)]
@@ -421,6 +437,8 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
             "stereo_matches_per_s": world * st_["stereo"] / dt, "projection_matches_per_s": world * st_["proj"] / dt,
             "matches_per_s": world * (st_["stereo"] + st_["proj"]) / dt, "keypoints_per_frame": st_["kp"] / (2 * tot),
             "stereo_matches_per_pair": st_["stereo"] / tot, "projection_matches_per_pair": st_["proj"] / tot, "api": api}
+        for p_ in pipes:
+            p_.close()
         del pipes
     return rows
 
