@@ -667,3 +667,24 @@ def test_matcher_entry_points_from_concurrent_host_threads(gpu):
     th = [threading.Thread(target=work, args=(t,)) for t in range(4)]
     [t.start() for t in th]; [t.join() for t in th]
     assert not errs, errs[0]
+
+
+@pytest.mark.parametrize("variant", ["3", "4"])
+def test_bf_top2_ties_across_chunks(gpu, variant, monkeypatch):
+    """Chunks of one scan share their second-best bounds: only rows STRICTLY farther than a published bound may be dropped.  A database of
+    long runs of identical rows makes every chunk hold exact ties of the global best and second best: the first index must win, d2 == d1,
+    whatever chunk finishes first."""
+    import orbb200, pyoracle
+    monkeypatch.setenv("ORBB_BF_VARIANT", variant)
+    rng = np.random.default_rng(31)
+    base = rng.integers(0, 256, (7, 32), dtype=np.uint8)
+    db = np.repeat(base, 60_000, axis=0)                                  # 420 k rows: 7 runs of identical rows
+    db[::4999] = rng.integers(0, 256, (len(db[::4999]), 32), dtype=np.uint8)
+    q = rng.integers(0, 256, (700, 32), dtype=np.uint8)
+    q[:7] = base; q[7:14] = base ^ np.uint8(1)
+    D = orbb200.DescriptorDB(len(db)); D.append(db)
+    d1, i1, d2 = D.top2(q)
+    o1, oi, o2 = pyoracle.bf_top2(db, q, nthreads=8)
+    assert np.array_equal(d1, o1) and np.array_equal(i1, oi) and np.array_equal(d2, o2)
+    assert np.all(d1[:7] == 0) and np.all(d2[:7] == 0)
+    D.close()
