@@ -361,16 +361,22 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
     class Pipeline:
         """One tracking thread's state: two extractor handles (left / right camera) and its host buffers."""
 
-        def __init__(self):
-            self.exL = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
-            self.exR = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
+        def __init__(self, fused=False):
+            self.fused = fused
+            if fused:                # Frame::Frame (stereo) as one call: both images are one two-frame batch of one handle
+                self.exL = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), max_batch=2, device=local_rank)
+                self.one_pair = self.one_pair_fused
+            else:
+                self.exL = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
+                self.exR = orbb200.ORBextractor(nf, 1.2, 8, 20, 7, max_size=(w, h), device=local_rank)
             self.scale = self.exL.GetScaleFactors()
             self.bufs = [dict(kL=np.zeros(cap, orbb200.KP_DTYPE), dL=np.zeros((cap, 32), np.uint8), kR=np.zeros(cap, orbb200.KP_DTYPE), dR=np.zeros((cap, 32), np.uint8),
                               ur=np.zeros(cap, np.float32), dp=np.zeros(cap, np.float32), mp=np.zeros(cap, np.int32), ob=np.zeros(cap, np.int32)) for _ in range(2)]
             self.nL, self.nR, self.nm = C.c_int(), C.c_int(), C.c_int()
             self.stats = {"stereo": 0, "proj": 0, "kp": 0}
             self.right_job, self.right_done = queue.Queue(), queue.Queue()
-            threading.Thread(target=self._right_worker, daemon=True).start()
+            if not fused:
+                threading.Thread(target=self._right_worker, daemon=True).start()
             self.one_pair(0, None); n0 = self.nL.value
             self.one_pair(1, None); n1 = self.nL.value
             self.qs = [self.queries_from(self.bufs[1], n1, 3.0, 1.0), self.queries_from(self.bufs[0], n0, -3.0, -1.0)]   # queries for pair 0 come from pair 1 and vice versa
@@ -407,6 +413,19 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
             L.orbm_frame_destroy(fh)
             self.stats["stereo"] += int((b["ur"][:nL.value] > 0).sum()); self.stats["kp"] += nL.value + nR.value
 
+        def one_pair_fused(self, i, queries):
+            b = self.bufs[i & 1]; left, right = pairs[i & 1]
+            nL, nR, nm = self.nL, self.nR, self.nm
+            fh = vp()
+            assert L.orbm_stereo_frame_create(self.exL.h, ptr(left), ptr(right), w, h, w, C.c_float(mbf), C.c_float(0.0), *[C.c_float(x) for x in bounds], C.byref(fh),
+                                              ptr(b["kL"]), ptr(b["dL"]), C.byref(nL), ptr(b["kR"]), ptr(b["dR"]), C.byref(nR), cap, ptr(b["ur"]), ptr(b["dp"])) == 0
+            if queries is not None:
+                b["mp"][:nL.value] = -1; b["ob"][:nL.value] = 0
+                assert L.orbm_search_by_projection_frame(fh, orbb200.URIGHT_OF_FRAME, ptr(queries), len(queries), 1, ptr(b["mp"]), ptr(b["ob"]), C.byref(nm)) == 0
+                self.stats["proj"] += nm.value
+            L.orbm_frame_destroy(fh)
+            self.stats["stereo"] += int((b["ur"][:nL.value] > 0).sum()); self.stats["kp"] += nL.value + nR.value
+
         def queries_from(self, b, n, dx, dy):                  # the previous left frame's keypoints projected into the current one
             q = np.zeros(n, orbb200.PROJ_QUERY_DTYPE)
             k = b["kL"][:n]
@@ -420,10 +439,12 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
             for i in range(npairs):
                 self.one_pair(i, self.qs[i & 1])
 
-    api = ("per pair, host pointers: orbx_extract (L) and orbx_extract (R) on two threads as in Frame.cpp:84-87, then orbm_stereo_match + orbm_frame_create + orbm_search_by_projection_frame + "
-           "orbm_frame_destroy; wall clock, H2D/D2H inside every call")
-    for nthreads, npairs in ((1, 40), (4, 40)):
-        pipes = [Pipeline() for _ in range(nthreads)]
+    apis = {False: ("per pair, host pointers: orbx_extract (L) and orbx_extract (R) on two threads as in Frame.cpp:84-87, then orbm_stereo_match + orbm_frame_create + "
+                    "orbm_search_by_projection_frame + orbm_frame_destroy; wall clock, H2D/D2H inside every call"),
+            True: ("per pair, host pointers: orbm_stereo_frame_create (Frame.cpp:61-115 as one call: both images as one batch, stereo matching and grid on the device "
+                   "results) + orbm_search_by_projection_frame (mvuRight of the frame) + orbm_frame_destroy; wall clock, H2D/D2H inside every call")}
+    for fused, nthreads, npairs in ((False, 1, 40), (False, 4, 40), (True, 1, 40), (True, 4, 40)):
+        pipes = [Pipeline(fused) for _ in range(nthreads)]
         barrier()
         t0 = time.perf_counter()
         th = [threading.Thread(target=p_.run, args=(npairs,)) for p_ in pipes]
@@ -432,11 +453,12 @@ def measure_configs(rank, world, local_rank, dev, barrier, max_over_ranks):
         dt = max_over_ranks(time.perf_counter() - t0)
         st_ = {k: sum(p_.stats[k] for p_ in pipes) for k in ("stereo", "proj", "kp")}
         tot = nthreads * npairs
-        rows["C2_kitti_stereo_pair_pipeline" + ("" if nthreads == 1 else f"_{nthreads}_host_threads")] = {
+        name = ("C2_kitti_stereo_pair_fused_constructor" if fused else "C2_kitti_stereo_pair_pipeline") + ("" if nthreads == 1 else f"_{nthreads}_host_threads")
+        rows[name] = {
             "pairs_per_s": world * tot / dt, "frames_per_s": 2 * world * tot / dt, "ms_per_pair_per_thread": dt / npairs * 1e3, "host_threads_per_gpu": nthreads,
             "stereo_matches_per_s": world * st_["stereo"] / dt, "projection_matches_per_s": world * st_["proj"] / dt,
             "matches_per_s": world * (st_["stereo"] + st_["proj"]) / dt, "keypoints_per_frame": st_["kp"] / (2 * tot),
-            "stereo_matches_per_pair": st_["stereo"] / tot, "projection_matches_per_pair": st_["proj"] / tot, "api": api}
+            "stereo_matches_per_pair": st_["stereo"] / tot, "projection_matches_per_pair": st_["proj"] / tot, "api": apis[fused]}
         for p_ in pipes:
             p_.close()
         del pipes

@@ -316,6 +316,24 @@ int orbm_stereo_match(orbx_handle* left, orbx_handle* right,
                       const orbx_keypoint* kps_right_host, const uint8_t* desc_right_host, int n_right,
                       float mbf, float mb, float* u_right_host, float* depth_host);
 
+/* Frame::Frame, the stereo constructor (Frame.cpp:61-115), as ONE call: ExtractORB(0, imLeft) || ExtractORB(1, imRight) (:84-87, the two
+ * threads become one two-frame batch of `h`, which therefore needs max_batch >= 2 and plays both mpORBextractorLeft and ...Right),
+ * UndistortKeyPoints for rectified input (mDistCoef[0] == 0 => mvKeysUn = mvKeys, :467-472: what the reference's stereo examples feed),
+ * ComputeStereoMatches (:540-748) and AssignFeaturesToGrid (:241-257) on the results where they lie in device memory.  Nothing is uploaded
+ * twice and the host synchronises twice (counts known; everything done).  Results are bit-equal to orbx_extract (left), orbx_extract
+ * (right), orbm_stereo_match, orbm_frame_create called one after the other (tests/test_gpu_match.py::test_stereo_frame_create).
+ * Out: *out (for the Search* calls; orbm_frame_destroy), mvKeys / mDescriptors (kps_left, desc_left, *n_left), mvKeysRight /
+ * mDescriptorsRight (kps_right, desc_right, *n_right; both may be NULL), mvuRight / mvDepth (n_left floats, -1 = none).  `capacity` rows
+ * per host array; ORBB_E_CAPACITY (counts still set) when an image has more keypoints.  min_x..max_y: mnMinX.. (orbm_image_bounds). */
+int orbm_stereo_frame_create(orbx_handle* h, const uint8_t* left_host, const uint8_t* right_host, int w, int h_, size_t stride_bytes,
+                             float mbf, float mb, float min_x, float min_y, float max_x, float max_y, orbm_frame** out,
+                             orbx_keypoint* kps_left_host, uint8_t* desc_left_host, int* n_left,
+                             orbx_keypoint* kps_right_host, uint8_t* desc_right_host, int* n_right, int capacity,
+                             float* u_right_host, float* depth_host);
+/* Pass as mvuRight_host to orbm_search_by_projection_points / _frame on a frame built by orbm_stereo_frame_create: the search uses the
+ * mvuRight that constructor left on the device instead of uploading the host copy (ORBB_E_STATE on any other frame). */
+#define ORBM_URIGHT_OF_FRAME ((const float*)(uintptr_t)1)
+
 /* Brute-force top-2 over a descriptor database shard with the reference's top-2 update rule
  * (SearchByBoW, ORBmatcher.cpp:249-275: strict '<', first index wins, second may equal best).
  * A database object holds one shard: rows [row_offset, row_offset + nrows) of the global database. */

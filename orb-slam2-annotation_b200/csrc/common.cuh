@@ -61,6 +61,22 @@ struct LevelGeom {
     int dxs_off, dys_off;// offsets into the per-tile first-destination-index tables
 };
 
+}  // namespace orbb
+
+// What orbx__extract_resident (extract.cu) hands to orbm_stereo_frame_create (match.cu): where one batch's results and pyramids live.
+struct orbx_resident_view {
+    orbx_keypoint* kps_dev; uint8_t* desc_dev;           // [frame][devcap] rows
+    const orbx_keypoint* kps_pinned; const uint8_t* desc_pinned;   // the handle's pinned copies, same layout (valid after s_out is drained)
+    int devcap;
+    const orbb::LevelGeom *geom_host, *geom_dev; int nlevels;
+    const uint8_t* src0; long long src0_pitch, src0_fstride;       // level 0 of frame 0 and its strides
+    const uint8_t* pyr; long long pyr_fstride;                     // levels >= 1 at geom[L].off inside each frame's block
+    const float *scale, *inv_scale;
+    int device; void *stream, *s_out;
+};
+
+namespace orbb {
+
 // ORBmatcher::DescriptorDistance (ORBmatcher.cpp:1838-1854) / FORB::distance (DBoW2/FORB.cpp:82-102) on two 32-byte rows
 __device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
 {

@@ -1190,3 +1190,51 @@ extern "C" int orbx__pyramid_view(orbx_handle* h, const LevelGeom** geom_host, c
     *scale = h->scale; *inv_scale = h->inv_scale; *stream = (void*)h->stream;
     return ORBB_OK;
 }
+
+// Internal (not part of include/orbb200.h): the extraction half of orbm_stereo_frame_create (match.cu).  `nframes` separate host
+// images of one shape are extracted as ONE batch of the handle; on return the per-frame counts are on the host, the keypoints and
+// descriptors are still on the device (view->kps_dev / desc_dev, `devcap` rows per frame) and a copy of them into the handle's
+// pinned buffers is in flight on view->s_out (exactly counts[f] rows per frame).  Only view->stream was synchronised.
+extern "C" int orbx__extract_resident(orbx_handle* h, const uint8_t* const* imgs_host, int nframes, int w, int ht, size_t stride,
+                                      int32_t* counts_host, orbx_resident_view* v)
+{
+    if (!h || !imgs_host || !counts_host || !v || nframes < 1 || nframes > h->cfg.max_batch) return ORBB_E_INVALID;
+    for (int f = 0; f < nframes; f++) if (!imgs_host[f]) return ORBB_E_INVALID;
+    if (w < 1 || ht < 1 || w > h->cfg.max_width || ht > h->cfg.max_height || stride < (size_t)w) return ORBB_E_BAD_SHAPE;
+    ORBB_CUDA(cudaSetDevice(h->cfg.device));
+    { const int rc = ensure_geometry(h, w, ht); if (rc != ORBB_OK) return rc; }
+    cudaStream_t st = h->stream;
+    ORBB_CUDA(cudaStreamSynchronize(st));       // an earlier asynchronous call may still be reading the level-0 slots
+    const LevelGeom& g0 = h->geom[0];
+    const bool tight = (w % 16) == 0 && (size_t)w * ht <= (size_t)g0.pitch * g0.h;
+    const size_t dpitch0 = tight ? (size_t)w : (size_t)g0.pitch;
+    for (int f = 0; f < nframes; f++) {         // pageable or pinned alike: through the pinned staging block, so that every copy is asynchronous
+        uint8_t* stg = h->h_img + (size_t)f * w * ht;
+        if (stride == (size_t)w) memcpy(stg, imgs_host[f], (size_t)w * ht);
+        else for (int y = 0; y < ht; y++) memcpy(stg + (size_t)y * w, imgs_host[f] + (size_t)y * stride, w);
+        ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, dpitch0, stg, (size_t)w, w, ht, cudaMemcpyHostToDevice, st));
+    }
+    const int devcap = h->dev_capacity;
+    static const bool side = getenv("ORBB_RESIDENT_SIDE") ? atoi(getenv("ORBB_RESIDENT_SIDE")) != 0 : false;
+    const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, 0, side);
+    if (rc != ORBB_OK) return rc;
+    ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaStreamSynchronize(st));
+    int ret = ORBB_OK;
+    for (int f = 0; f < nframes; f++) {
+        const int n = h->h_counts[f] < devcap ? h->h_counts[f] : devcap;
+        counts_host[f] = n;
+        if (h->h_status[f] || h->h_counts[f] > devcap) ret = ORBB_E_CAPACITY;
+        if (n > 0) {
+            ORBB_CUDA(cudaMemcpyAsync(h->h_kps + (size_t)f * devcap, h->d_kps + (size_t)f * devcap, sizeof(orbx_keypoint) * (size_t)n, cudaMemcpyDeviceToHost, h->s_out));
+            ORBB_CUDA(cudaMemcpyAsync(h->h_desc + (size_t)f * devcap * 32, h->d_desc + (size_t)f * devcap * 32, (size_t)32 * n, cudaMemcpyDeviceToHost, h->s_out));
+        }
+    }
+    v->kps_dev = h->d_kps; v->desc_dev = h->d_desc; v->kps_pinned = h->h_kps; v->desc_pinned = h->h_desc; v->devcap = devcap;
+    v->geom_host = h->geom; v->geom_dev = h->d_geom; v->nlevels = h->nlevels;
+    v->src0 = h->last_src; v->src0_pitch = h->last_src_pitch; v->src0_fstride = h->last_src_fstride;
+    v->pyr = h->d_pyr; v->pyr_fstride = (long long)h->pyr_fstride;
+    v->scale = h->scale; v->inv_scale = h->inv_scale; v->device = h->cfg.device; v->stream = (void*)st; v->s_out = (void*)h->s_out;
+    return ret;
+}

@@ -11,6 +11,9 @@ extern "C" int orbx__pyramid_view(orbx_handle* h, const LevelGeom** geom_host, c
                                   const uint8_t** src0, long long* src0_pitch, const uint8_t** pyr, int* device,
                                   const float** scale, const float** inv_scale, void** stream);
 
+extern "C" int orbx__extract_resident(orbx_handle* h, const uint8_t* const* imgs_host, int nframes, int w, int ht, size_t stride,
+                                      int32_t* counts_host, orbx_resident_view* v);
+
 namespace {
 
 // Device scratch from the library's block cache (common.cuh): no cudaMalloc / cudaFree on the per-frame paths after warm-up.
@@ -30,6 +33,25 @@ struct DevBuf {
     }
     template <typename T> T* as() { return (T*)p; }
 };
+
+// Pinned staging of the host-pointer entry points, one block per calling thread (grown on demand, never shrunk): a call packs its
+// uploads here, queues asynchronous copies around its kernels and synchronises once, instead of one blocking pageable copy per array.
+struct PinnedArena {
+    void* p = nullptr; size_t cap = 0;
+    ~PinnedArena() { if (p) cudaFreeHost(p); }
+    uint8_t* get(size_t bytes)           // only at the start of a call: nothing of this thread is in flight then
+    {
+        if (bytes <= cap) return (uint8_t*)p;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 2;
+        if (want < ((size_t)1 << 20)) want = (size_t)1 << 20;
+        if (cudaHostAlloc(&p, want, cudaHostAllocPortable) != cudaSuccess) { set_cuda_error(cudaGetLastError(), "pinned staging"); p = nullptr; return nullptr; }
+        cap = want;
+        return (uint8_t*)p;
+    }
+};
+thread_local PinnedArena t_pin;
 
 int check_device(int device)
 {
@@ -172,6 +194,7 @@ struct orbm_frame {
     mutable std::vector<uint8_t> h_desc;
     mutable bool host_valid = false;
     DevBuf kps, desc, cell_of, cell_start, cell_items, cursor;
+    DevBuf uright_own; bool uright_valid = false;      // mvuRight computed by orbm_stereo_frame_create (ORBM_URIGHT_OF_FRAME)
     // workspace of the device resolve (orbm_search_by_projection_*_device); calls on one frame are serialised by the caller
     mutable DevBuf ws_counts, ws_offs, ws_idx, ws_dist, ws_choice, ws_taker, ws_uright, ws_mp, ws_obs, ws_scalars;
     // recorded after the copies and grid kernels of orbm_frame_create_device on the caller's stream: the host-pointer entry points
@@ -232,8 +255,15 @@ static int frame_create_impl(orbm_frame** out, const orbx_keypoint* kps, const u
     f.cell_of = fr->cell_of.as<int>(); f.cell_start = fr->cell_start.as<int>(); f.cell_items = fr->cell_items.as<int>();
     auto fail = [&](int code) { delete fr; return code; };
     if (n > 0) {
-        if (cudaMemcpyAsync(fr->kps.p, kps, (size_t)n * sizeof(orbx_keypoint), kind, st) != cudaSuccess) return fail(ORBB_E_CUDA);
-        if (cudaMemcpyAsync(fr->desc.p, desc, (size_t)n * 32, kind, st) != cudaSuccess) return fail(ORBB_E_CUDA);
+        const void *ksrc = kps, *dsrc = desc;
+        if (from_host) {             // through this thread's pinned block: the copies are asynchronous and the call synchronises once
+            uint8_t* pin = t_pin.get((size_t)n * (sizeof(orbx_keypoint) + 32));
+            if (!pin) return fail(ORBB_E_NOMEM);
+            memcpy(pin, kps, (size_t)n * sizeof(orbx_keypoint)); memcpy(pin + (size_t)n * sizeof(orbx_keypoint), desc, (size_t)n * 32);
+            ksrc = pin; dsrc = pin + (size_t)n * sizeof(orbx_keypoint);
+        }
+        if (cudaMemcpyAsync(fr->kps.p, ksrc, (size_t)n * sizeof(orbx_keypoint), kind, st) != cudaSuccess) return fail(ORBB_E_CUDA);
+        if (cudaMemcpyAsync(fr->desc.p, dsrc, (size_t)n * 32, kind, st) != cudaSuccess) return fail(ORBB_E_CUDA);
     }
     if (cudaMemsetAsync(fr->cursor.p, 0, (size_t)NC * 4, st) != cudaSuccess) return fail(ORBB_E_CUDA);
     if (n > 0) { grid_assign_kernel<<<ceil_div(n, 256), 256, 0, st>>>(f, fr->cursor.as<int>()); ORBB_LAUNCHED(); }
@@ -419,34 +449,51 @@ static int search_projection_host(const orbm_frame* f, int mode, const float* ur
     int rc = check_device(f->device);
     if (rc != ORBB_OK) return rc;
     if (nq == 0) return ORBB_OK;
-    const size_t nb = (size_t)f->n * 4;
+    const bool own_uright = uright == ORBM_URIGHT_OF_FRAME;            // mvuRight as orbm_stereo_frame_create left it on the device
+    if (own_uright && !f->uright_valid && f->n > 0) return ORBB_E_STATE;
+    const size_t nb = (size_t)f->n * 4, qb = (size_t)nq * sizeof(orbm_proj_query);
+    const bool up_uright = uright && !own_uright && f->n > 0;
     DevBuf q;
-    if ((rc = q.alloc((size_t)nq * sizeof(orbm_proj_query))) || (rc = f->ws_mp.reserve(nb)) || (rc = f->ws_obs.reserve(nb)) ||
-        (rc = f->ws_scalars.reserve(16)) || (uright && (rc = f->ws_uright.reserve(nb)))) return rc;
-    ORBB_CUDA(cudaMemcpy(q.p, pq, (size_t)nq * sizeof(orbm_proj_query), cudaMemcpyHostToDevice));
-    if (uright && f->n > 0) ORBB_CUDA(cudaMemcpy(f->ws_uright.p, uright, nb, cudaMemcpyHostToDevice));
+    if ((rc = q.alloc(qb)) || (rc = f->ws_mp.reserve(nb)) || (rc = f->ws_obs.reserve(nb)) ||
+        (rc = f->ws_scalars.reserve(16)) || (up_uright && (rc = f->ws_uright.reserve(nb)))) return rc;
+    // one pinned block per call: [queries | mvuRight | mvpMapPoints | observations | header]; every copy is asynchronous on this thread's
+    // stream and the call synchronises once per attempt
+    uint8_t* pin = t_pin.get(qb + 3 * nb + 64);
+    if (!pin) return ORBB_E_NOMEM;
+    uint8_t *p_q = pin, *p_u = pin + qb, *p_mp = p_u + nb, *p_obs = p_mp + nb;
+    int32_t* p_h = reinterpret_cast<int32_t*>(p_obs + nb);
+    cudaStream_t st = 0;                                               // this thread's default stream
+    memcpy(p_q, pq, qb);
+    ORBB_CUDA(cudaMemcpyAsync(q.p, p_q, qb, cudaMemcpyHostToDevice, st));
+    if (up_uright) { memcpy(p_u, uright, nb); ORBB_CUDA(cudaMemcpyAsync(f->ws_uright.p, p_u, nb, cudaMemcpyHostToDevice, st)); }
+    const float* ur_dev = own_uright ? (f->n > 0 ? (const float*)f->uright_own.p : nullptr) : (uright ? f->ws_uright.as<float>() : nullptr);
     int32_t* sc = f->ws_scalars.as<int32_t>();
     int cap = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
         if (f->n > 0) {
-            ORBB_CUDA(cudaMemcpy(f->ws_mp.p, frame_mp, nb, cudaMemcpyHostToDevice));
-            if (frame_mp_obs) ORBB_CUDA(cudaMemcpy(f->ws_obs.p, frame_mp_obs, nb, cudaMemcpyHostToDevice));
+            memcpy(p_mp, frame_mp, nb);
+            ORBB_CUDA(cudaMemcpyAsync(f->ws_mp.p, p_mp, nb, cudaMemcpyHostToDevice, st));
+            if (frame_mp_obs) { memcpy(p_obs, frame_mp_obs, nb); ORBB_CUDA(cudaMemcpyAsync(f->ws_obs.p, p_obs, nb, cudaMemcpyHostToDevice, st)); }
         }
-        rc = resolve_on_device(f, mode, uright ? f->ws_uright.as<float>() : nullptr, q.as<orbm_proj_query>(), nq, nnratio, check_ori,
-                               f->ws_mp.as<int32_t>(), frame_mp_obs ? f->ws_obs.as<int32_t>() : nullptr, sc, sc + 1, sc + 2, cap, 0, max_dist);
+        rc = resolve_on_device(f, mode, ur_dev, q.as<orbm_proj_query>(), nq, nnratio, check_ori,
+                               f->ws_mp.as<int32_t>(), frame_mp_obs ? f->ws_obs.as<int32_t>() : nullptr, sc, sc + 1, sc + 2, cap, st, max_dist);
         if (rc != ORBB_OK) return rc;
-        int32_t h[3] = {0, 0, 0};
-        ORBB_CUDA(cudaMemcpy(h, sc, sizeof(h), cudaMemcpyDeviceToHost));
-        if (h[1] == ORBB_E_CAPACITY && attempt == 0) {            // more candidates than the default budget: size it exactly
-            ORBB_CUDA(cudaMemcpy(&cap, f->ws_offs.as<int>() + nq, 4, cudaMemcpyDeviceToHost));
-            cap += 16;
+        ORBB_CUDA(cudaMemcpyAsync(p_h, sc, 12, cudaMemcpyDeviceToHost, st));
+        ORBB_CUDA(cudaMemcpyAsync(p_h + 3, f->ws_offs.as<int>() + nq, 4, cudaMemcpyDeviceToHost, st));
+        if (f->n > 0) {
+            ORBB_CUDA(cudaMemcpyAsync(p_mp, f->ws_mp.p, nb, cudaMemcpyDeviceToHost, st));
+            if (frame_mp_obs) ORBB_CUDA(cudaMemcpyAsync(p_obs, f->ws_obs.p, nb, cudaMemcpyDeviceToHost, st));
+        }
+        ORBB_CUDA(cudaStreamSynchronize(st));
+        if (p_h[1] == ORBB_E_CAPACITY && attempt == 0) {            // more candidates than the default budget: size it exactly
+            cap = p_h[3] + 16;
             continue;
         }
-        if (h[1] != ORBB_OK) return h[1];
-        *nmatches = h[0];
+        if (p_h[1] != ORBB_OK) return p_h[1];
+        *nmatches = p_h[0];
         if (f->n > 0) {
-            ORBB_CUDA(cudaMemcpy(frame_mp, f->ws_mp.p, nb, cudaMemcpyDeviceToHost));
-            if (frame_mp_obs) ORBB_CUDA(cudaMemcpy(frame_mp_obs, f->ws_obs.p, nb, cudaMemcpyDeviceToHost));
+            memcpy(frame_mp, p_mp, nb);
+            if (frame_mp_obs) memcpy(frame_mp_obs, p_obs, nb);
         }
         return ORBB_OK;
     }
@@ -842,11 +889,20 @@ extern "C" int orbm_stereo_match(orbx_handle* left, orbx_handle* right, const or
         (rc = bkR.alloc((size_t)nR * sizeof(orbx_keypoint))) || (rc = bdR.alloc((size_t)nR * 32)) ||
         (rc = bu.alloc((size_t)nL * 4)) || (rc = bd.alloc((size_t)nL * 4)) || (rc = bs.alloc((size_t)nL * 4)) ||
         (rc = bi.alloc((size_t)nL * 4)) || (rc = bb.alloc((size_t)nL * 4))) return rc;
-    ORBB_CUDA(cudaMemcpy(bkL.p, kL, (size_t)nL * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
-    ORBB_CUDA(cudaMemcpy(bdL.p, dL, (size_t)nL * 32, cudaMemcpyHostToDevice));
+    // one pinned block per call: [kL | dL | kR | dR | uRight | depth]; asynchronous copies on this thread's stream, one synchronisation
+    const size_t bk = sizeof(orbx_keypoint);
+    uint8_t* pin = t_pin.get((size_t)(nL + nR) * (bk + 32) + (size_t)nL * 8);
+    if (!pin) return ORBB_E_NOMEM;
+    uint8_t *p_kL = pin, *p_dL = p_kL + (size_t)nL * bk, *p_kR = p_dL + (size_t)nL * 32, *p_dR = p_kR + (size_t)nR * bk, *p_u = p_dR + (size_t)nR * 32,
+            *p_d = p_u + (size_t)nL * 4;
+    cudaStream_t st = 0;
+    memcpy(p_kL, kL, (size_t)nL * bk); memcpy(p_dL, dL, (size_t)nL * 32);
+    ORBB_CUDA(cudaMemcpyAsync(bkL.p, p_kL, (size_t)nL * bk, cudaMemcpyHostToDevice, st));
+    ORBB_CUDA(cudaMemcpyAsync(bdL.p, p_dL, (size_t)nL * 32, cudaMemcpyHostToDevice, st));
     if (nR > 0) {
-        ORBB_CUDA(cudaMemcpy(bkR.p, kR, (size_t)nR * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
-        ORBB_CUDA(cudaMemcpy(bdR.p, dR, (size_t)nR * 32, cudaMemcpyHostToDevice));
+        memcpy(p_kR, kR, (size_t)nR * bk); memcpy(p_dR, dR, (size_t)nR * 32);
+        ORBB_CUDA(cudaMemcpyAsync(bkR.p, p_kR, (size_t)nR * bk, cudaMemcpyHostToDevice, st));
+        ORBB_CUDA(cudaMemcpyAsync(bdR.p, p_dR, (size_t)nR * 32, cudaMemcpyHostToDevice, st));
     }
     StereoArgs a;
     memset(&a, 0, sizeof a);
@@ -859,14 +915,79 @@ extern "C" int orbm_stereo_match(orbx_handle* left, orbx_handle* right, const or
     // Frame.cpp:579-581: minZ = mb, minD = 0, maxD = mbf/minZ (mb == 0 at the reference's call => +inf)
     a.mbf = mbf; a.minD = 0.f; a.maxD = mbf / mb;
     a.uRight = bu.as<float>(); a.depth = bd.as<float>(); a.sad = bs.as<int>(); a.bestIdx = bi.as<int>(); a.bestDist = bb.as<int>();
-    stereo_match_kernel<<<ceil_div(nL, 8), 256>>>(a);
+    stereo_match_kernel<<<ceil_div(nL, 8), 256, 0, st>>>(a);
     ORBB_LAUNCHED();
     const float k21 = 1.5f * 1.4f;
-    stereo_median_filter_kernel<<<1, 256>>>(nL, a.sad, a.uRight, a.depth, k21);
+    stereo_median_filter_kernel<<<1, 256, 0, st>>>(nL, a.sad, a.uRight, a.depth, k21);
     ORBB_LAUNCHED();
     ORBB_CUDA(cudaGetLastError());
-    ORBB_CUDA(cudaMemcpy(uR_host, bu.p, (size_t)nL * 4, cudaMemcpyDeviceToHost));
-    ORBB_CUDA(cudaMemcpy(depth_host, bd.p, (size_t)nL * 4, cudaMemcpyDeviceToHost));
+    ORBB_CUDA(cudaMemcpyAsync(p_u, bu.p, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaMemcpyAsync(p_d, bd.p, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaStreamSynchronize(st));
+    memcpy(uR_host, p_u, (size_t)nL * 4); memcpy(depth_host, p_d, (size_t)nL * 4);
+    return ORBB_OK;
+}
+
+// Frame::Frame, stereo constructor (Frame.cpp:61-115) as ONE call: ExtractORB(0, left) || ExtractORB(1, right) as one two-frame batch of
+// the handle, UndistortKeyPoints for rectified input (mDistCoef[0] == 0: mvKeysUn = mvKeys, Frame.cpp:467-472), ComputeStereoMatches
+// and AssignFeaturesToGrid on the results where they lie in HBM.  Nothing is uploaded twice; the host gets every Frame member back
+// (mvKeys, mDescriptors, mvKeysRight, mDescriptorsRight, mvuRight, mvDepth) and the device keeps the frame for the Search* calls.
+extern "C" int orbm_stereo_frame_create(orbx_handle* h, const uint8_t* left_host, const uint8_t* right_host, int w, int ht, size_t stride,
+                                        float mbf, float mb, float min_x, float min_y, float max_x, float max_y, orbm_frame** out,
+                                        orbx_keypoint* kL_host, uint8_t* dL_host, int* nL_out, orbx_keypoint* kR_host, uint8_t* dR_host,
+                                        int* nR_out, int capacity, float* uR_host, float* depth_host)
+{
+    if (!h || !left_host || !right_host || !out || !nL_out || !nR_out || capacity < 1 || !kL_host || !dL_host || !uR_host || !depth_host ||
+        ((kR_host == nullptr) != (dR_host == nullptr))) return ORBB_E_INVALID;
+    *out = nullptr; *nL_out = 0; *nR_out = 0;
+    const uint8_t* imgs[2] = {left_host, right_host};
+    int32_t cnt[2] = {0, 0};
+    orbx_resident_view v{};
+    int rc = orbx__extract_resident(h, imgs, 2, w, ht, stride, cnt, &v);
+    if (rc != ORBB_OK) { if (v.s_out) cudaStreamSynchronize((cudaStream_t)v.s_out); return rc; }
+    cudaStream_t st = (cudaStream_t)v.stream, s_out = (cudaStream_t)v.s_out;
+    const int nL = cnt[0], nR = cnt[1];
+    *nL_out = nL; *nR_out = nR;
+    if (nL > capacity || (kR_host && nR > capacity) || nR >= 65536) { cudaStreamSynchronize(s_out); return ORBB_E_CAPACITY; }
+    uint8_t* pin = t_pin.get((size_t)(nL > 0 ? nL : 1) * 8);
+    if (!pin) { cudaStreamSynchronize(s_out); return ORBB_E_NOMEM; }
+    orbm_frame* fr = nullptr;
+    rc = frame_create_impl(&fr, v.kps_dev, v.desc_dev, nL, min_x, min_y, max_x, max_y, v.device, cudaMemcpyDeviceToDevice, st);
+    if (rc != ORBB_OK) { cudaStreamSynchronize(s_out); return rc; }
+    auto fail = [&](int code) { cudaStreamSynchronize(st); cudaStreamSynchronize(s_out); orbm_frame_destroy(fr); return code; };
+    DevBuf bd, bs, bi, bb;
+    if (nL > 0) {
+        if ((rc = fr->uright_own.alloc((size_t)nL * 4)) || (rc = bd.alloc((size_t)nL * 4)) || (rc = bs.alloc((size_t)nL * 4)) ||
+            (rc = bi.alloc((size_t)nL * 4)) || (rc = bb.alloc((size_t)nL * 4))) return fail(rc);
+        StereoArgs a;
+        memset(&a, 0, sizeof a);
+        a.kL = v.kps_dev; a.dL = reinterpret_cast<const uint4*>(v.desc_dev); a.nL = nL;
+        a.kR = v.kps_dev + v.devcap; a.dR = reinterpret_cast<const uint4*>(v.desc_dev + (size_t)v.devcap * 32); a.nR = nR;
+        a.geom = v.geom_dev; a.nlevels = v.nlevels; a.nRows = v.geom_host[0].h;
+        a.src0L = v.src0; a.src0L_pitch = v.src0_pitch; a.pyrL = v.pyr;
+        a.src0R = v.src0 + v.src0_fstride; a.src0R_pitch = v.src0_pitch; a.pyrR = v.pyr + v.pyr_fstride;
+        for (int i = 0; i < v.nlevels; i++) { a.scale[i] = v.scale[i]; a.inv_scale[i] = v.inv_scale[i]; }
+        a.mbf = mbf; a.minD = 0.f; a.maxD = mbf / mb;                      // Frame.cpp:579-581
+        a.uRight = fr->uright_own.as<float>(); a.depth = bd.as<float>(); a.sad = bs.as<int>(); a.bestIdx = bi.as<int>(); a.bestDist = bb.as<int>();
+        stereo_match_kernel<<<ceil_div(nL, 8), 256, 0, st>>>(a);
+        ORBB_LAUNCHED();
+        stereo_median_filter_kernel<<<1, 256, 0, st>>>(nL, a.sad, a.uRight, a.depth, 1.5f * 1.4f);
+        ORBB_LAUNCHED();
+        if (cudaMemcpyAsync(pin, a.uRight, (size_t)nL * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+            cudaMemcpyAsync(pin + (size_t)nL * 4, a.depth, (size_t)nL * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return fail(ORBB_E_CUDA);
+        fr->uright_valid = true;
+    }
+    cudaError_t e = cudaStreamSynchronize(s_out);              // keypoints and descriptors of both images are in the handle's pinned block
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { set_cuda_error(e, "orbm_stereo_frame_create"); return fail(ORBB_E_CUDA); }
+    if (nL > 0) {
+        memcpy(kL_host, v.kps_pinned, (size_t)nL * sizeof(orbx_keypoint)); memcpy(dL_host, v.desc_pinned, (size_t)nL * 32);
+        memcpy(uR_host, pin, (size_t)nL * 4); memcpy(depth_host, pin + (size_t)nL * 4, (size_t)nL * 4);
+    }
+    if (kR_host && nR > 0) {
+        memcpy(kR_host, v.kps_pinned + v.devcap, (size_t)nR * sizeof(orbx_keypoint)); memcpy(dR_host, v.desc_pinned + (size_t)v.devcap * 32, (size_t)nR * 32);
+    }
+    *out = fr;
     return ORBB_OK;
 }
 

@@ -29,7 +29,7 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "or
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbx_set_rectification", "orbx_extract_batch_rectified", "orbx_remap_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_frame_create_device", "orbm_undistort_keypoints", "orbm_undistort_keypoints_device", "orbm_image_bounds",
            "orbm_search_by_projection_points_device", "orbm_search_by_projection_frame_device", "orbm_search_by_projection_reloc", "orbm_search_by_projection_reloc_device", "orbm_search_by_projection_loop", "orbm_fuse_best",
-           "orbm_stereo_match", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
+           "orbm_stereo_match", "orbm_stereo_frame_create", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_bf_top2_noalloc", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
            "orbv_compute_bow", "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak", "orbb200_measure_imma_peak", "orbb200_measure_tcgen05_i8_peak",
@@ -111,6 +111,7 @@ def lib():
         L.orbm_search_for_triangulation.argtypes = ([vp] * 4 + [i32] + [vp] * 3 + [i32]) * 2 + [vp, f32, f32, vp, vp, i32, i32, vp, C.POINTER(i32), i32]
         L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, C.POINTER(i32)]
         L.orbm_stereo_match.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, f32, f32, vp, vp]
+        L.orbm_stereo_frame_create.argtypes = [vp, vp, vp, i32, i32, C.c_size_t, f32, f32, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp]
         L.orbm_db_create.argtypes = [C.POINTER(vp), C.c_int64, C.c_int64, i32]
         L.orbm_db_append.argtypes = [vp, vp, C.c_int64]
         L.orbm_db_append_device.argtypes = [vp, vp, C.c_int64]
@@ -138,6 +139,8 @@ def _p(a):
         return None
     if isinstance(a, int):
         return C.c_void_p(a)
+    if isinstance(a, C.c_void_p):
+        return a
     return a.ctypes.data_as(C.c_void_p)
 
 
@@ -538,7 +541,7 @@ class ORBmatcher:
     def SearchByProjection_points(self, frame, proj_queries, frame_mp, frame_mp_obs, mvuRight=None):
         q = np.ascontiguousarray(proj_queries, PROJ_QUERY_DTYPE)
         mp = np.ascontiguousarray(frame_mp, np.int32).copy(); ob = np.ascontiguousarray(frame_mp_obs, np.int32).copy()
-        ur = None if mvuRight is None else np.ascontiguousarray(mvuRight, np.float32)
+        ur = mvuRight if mvuRight is None or isinstance(mvuRight, C.c_void_p) else np.ascontiguousarray(mvuRight, np.float32)
         n = C.c_int()
         _check(self.L.orbm_search_by_projection_points(frame.h, _p(ur), _p(q), len(q), self.mfNNratio, _p(mp), _p(ob), C.byref(n)),
                "orbm_search_by_projection_points")
@@ -547,7 +550,7 @@ class ORBmatcher:
     def SearchByProjection_frame(self, frame, proj_queries, frame_mp, frame_mp_obs, mvuRight=None):
         q = np.ascontiguousarray(proj_queries, PROJ_QUERY_DTYPE)
         mp = np.ascontiguousarray(frame_mp, np.int32).copy(); ob = np.ascontiguousarray(frame_mp_obs, np.int32).copy()
-        ur = None if mvuRight is None else np.ascontiguousarray(mvuRight, np.float32)
+        ur = mvuRight if mvuRight is None or isinstance(mvuRight, C.c_void_p) else np.ascontiguousarray(mvuRight, np.float32)
         n = C.c_int()
         _check(self.L.orbm_search_by_projection_frame(frame.h, _p(ur), _p(q), len(q), int(self.mbCheckOrientation), _p(mp), _p(ob), C.byref(n)),
                "orbm_search_by_projection_frame")
@@ -585,7 +588,7 @@ class ORBmatcher:
     def FuseBest(self, frame, proj_queries, mvuRight, inv_level_sigma2, max_dist):
         """Per-point search of Fuse / Fuse(Scw) / SearchBySim3 (ORBmatcher.cpp:962-1500): (best_idx, best_dist)."""
         q = np.ascontiguousarray(proj_queries, PROJ_QUERY_DTYPE)
-        ur = None if mvuRight is None else np.ascontiguousarray(mvuRight, np.float32)
+        ur = mvuRight if mvuRight is None or isinstance(mvuRight, C.c_void_p) else np.ascontiguousarray(mvuRight, np.float32)
         s2 = None if inv_level_sigma2 is None else np.ascontiguousarray(inv_level_sigma2, np.float32)
         bi = np.zeros(len(q), np.int32); bd = np.zeros(len(q), np.int32)
         _check(self.L.orbm_fuse_best(frame.h, _p(q), len(q), _p(ur), _p(s2), max_dist, _p(bi), _p(bd)), "orbm_fuse_best")
@@ -610,6 +613,29 @@ def stereo_match(exL, exR, kpsL, descL, kpsR, descR, mbf, mb=0.0):
         _check(lib().orbm_stereo_match(exL.h, exR.h, _p(kL), _p(dL), len(kL), _p(kR), _p(dR), len(kR), mbf, mb, _p(ur), _p(dp)),
                "orbm_stereo_match")
     return ur, dp
+
+
+URIGHT_OF_FRAME = C.c_void_p(1)      # ORBM_URIGHT_OF_FRAME
+
+
+def stereo_frame(ex, left, right, mbf, bounds, mb=0.0, capacity=None):
+    """Frame::Frame (stereo constructor, Frame.cpp:61-115) as one call (orbm_stereo_frame_create): both images extracted as one batch of
+    `ex` (max_batch >= 2), stereo matching and the grid on the device.  Returns (FrameMatcher, kL, dL, kR, dR, mvuRight, mvDepth)."""
+    left = np.ascontiguousarray(left, np.uint8); right = np.ascontiguousarray(right, np.uint8)
+    assert left.shape == right.shape and left.ndim == 2
+    ht, w = left.shape
+    cap = int(capacity or ex.default_capacity)
+    kL = np.zeros(cap, KP_DTYPE); dL = np.zeros((cap, 32), np.uint8); kR = np.zeros(cap, KP_DTYPE); dR = np.zeros((cap, 32), np.uint8)
+    ur = np.zeros(cap, np.float32); dp = np.zeros(cap, np.float32)
+    nL, nR = C.c_int(), C.c_int()
+    F = FrameMatcher.__new__(FrameMatcher)
+    F.L = lib(); F.kps = None; F.desc = None; F.h = C.c_void_p(); F.n = 0
+    with np.errstate(divide="ignore"):
+        _check(F.L.orbm_stereo_frame_create(ex.h, _p(left), _p(right), w, ht, w, mbf, mb, *[float(b) for b in bounds], C.byref(F.h),
+                                            _p(kL), _p(dL), C.byref(nL), _p(kR), _p(dR), C.byref(nR), cap, _p(ur), _p(dp)), "orbm_stereo_frame_create")
+    F.n = nL.value
+    F.kps = kL[:F.n]; F.desc = dL[:F.n]
+    return F, kL[:nL.value], dL[:nL.value], kR[:nR.value], dR[:nR.value], ur[:nL.value], dp[:nL.value]
 
 
 class DescriptorDB:

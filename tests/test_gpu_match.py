@@ -688,3 +688,44 @@ def test_bf_top2_ties_across_chunks(gpu, variant, monkeypatch):
     assert np.array_equal(d1, o1) and np.array_equal(i1, oi) and np.array_equal(d2, o2)
     assert np.all(d1[:7] == 0) and np.all(d2[:7] == 0)
     D.close()
+
+
+@pytest.mark.parametrize("w,h,nf,seed", [(1241, 376, 2000, 21), (752, 480, 1200, 22), (638, 401, 1000, 23)])
+def test_stereo_frame_create(gpu, w, h, nf, seed):
+    """orbm_stereo_frame_create (Frame.cpp:61-115 as one call) == the oracle's extraction of both images + its ComputeStereoMatches, and
+    == the library's own four calls one after the other; the frame it leaves on the device answers a tracked-frame search like a frame
+    built from the host arrays, with mvuRight taken from the device (ORBM_URIGHT_OF_FRAME) or uploaded."""
+    import orbb200, pyoracle
+    from synth import synth_stereo
+    L, R = synth_stereo(w, h, seed)
+    oL, oR = pyoracle.OracleExtractor(nf), pyoracle.OracleExtractor(nf)
+    okL, odL = oL.extract(L); okR, odR = oR.extract(R)
+    mbf = 386.1448
+    ex = orbb200.ORBextractor(nf, max_size=(w, h), max_batch=2)
+    scale = ex.GetScaleFactors()
+    rng = np.random.default_rng(seed)
+    for rep in range(2):                                      # twice in a row through the same handle and pinned blocks
+        for mb in (0.0, 0.537):
+            F, kL, dL, kR, dR, ur, dp = orbb200.stereo_frame(ex, L, R, mbf, (0, 0, w, h), mb)
+            assert kL.tobytes() == okL.tobytes() and np.array_equal(dL, odL) and kR.tobytes() == okR.tobytes() and np.array_equal(dR, odR)
+            with np.errstate(divide="ignore"):
+                our, odp, _, _ = pyoracle.stereo_match(oL, oR, mbf, mb)
+            assert np.array_equal(ur, our) and np.array_equal(dp, odp)
+            # tracked-frame search on the frame the constructor left on the device
+            q = _queries(kL, dL, scale, 15.0, (2, 1), rng)
+            mp0 = np.full(len(kL), -1, np.int32); ob0 = np.zeros(len(kL), np.int32)
+            m = orbb200.ORBmatcher(0.9, True)
+            G = orbb200.FrameMatcher(kL, dL, (0, 0, w, h)); O = pyoracle.OracleFrame(kL, dL, (0, 0, w, h))
+            on, omp, oob = O.search_last_frame(_to_oracle_queries(q), True, mp0, ob0, ur)
+            for frame, uright in ((F, orbb200.URIGHT_OF_FRAME), (F, ur), (G, ur)):
+                n, mp, ob = m.SearchByProjection_frame(frame, q, mp0, ob0, uright)
+                assert n == on and np.array_equal(mp, omp) and np.array_equal(ob, oob)
+            assert on > 0.3 * len(kL)
+            with pytest.raises(orbb200.OrbError):             # a frame built from host arrays has no mvuRight of its own
+                m.SearchByProjection_frame(G, q, mp0, ob0, orbb200.URIGHT_OF_FRAME)
+            F.close(); G.close()
+    # a handle that cannot hold two frames, and a capacity below the keypoint count
+    with pytest.raises(orbb200.OrbError):
+        orbb200.stereo_frame(orbb200.ORBextractor(nf, max_size=(w, h)), L, R, mbf, (0, 0, w, h))
+    with pytest.raises(orbb200.OrbError):
+        orbb200.stereo_frame(ex, L, R, mbf, (0, 0, w, h), capacity=len(okL) - 1)

@@ -10,6 +10,7 @@
 #   ncu-ham                        ncu --set full of the brute-force scan kernel (ORBB_BF_VARIANT from the environment) on 2000 x 10 M
 #   ncu-match                      ncu --set full of the guided-matching kernels at the C2 shape
 #   rows                           tools/bench_rows.py (secondary rows) + its ncu launch list
+#   pair [reps]                    matcher tests on the stereo / projection paths + tools/pair_timing.py (per-call medians of one KITTI pair)
 mkdir -p gpurun_out
 NCU="ncu --set full --clock-control none --import-source on"
 summary() { python - "$1" <<'PY'
@@ -62,5 +63,8 @@ case $mode in
     timeout 600 python tools/bench_rows.py > gpurun_out/rows.json 2> gpurun_out/rows.err || { tail -5 gpurun_out/rows.err; exit 1; }
     timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/rows_launches.csv python tools/bench_rows.py > gpurun_out/rows_ncu.log 2>&1
     echo "ncu rc=$?";;
-  *) sed -n 2,14p $0; exit 1;;
+  pair)
+    timeout 600 python -m pytest tests/test_gpu_match.py -x -q -k 'stereo or projection or host_form or tracked' 2>&1 | tail -4
+    timeout 300 python tools/pair_timing.py ${1:-200} > gpurun_out/pair_timing.json 2> gpurun_out/pair_timing.err; echo "pair rc=$?"; cat gpurun_out/pair_timing.json; tail -3 gpurun_out/pair_timing.err;;
+  *) sed -n 2,15p $0; exit 1;;
 esac
