@@ -72,7 +72,7 @@ struct orbx_resident_view {
     const uint8_t* src0; long long src0_pitch, src0_fstride;       // level 0 of frame 0 and its strides
     const uint8_t* pyr; long long pyr_fstride;                     // levels >= 1 at geom[L].off inside each frame's block
     const float *scale, *inv_scale;
-    int device; void *stream, *s_out;
+    int device; void *stream, *s_out, *s_aux;                      // s_aux: an idle stream of the handle for work beside `stream`
 };
 
 namespace orbb {

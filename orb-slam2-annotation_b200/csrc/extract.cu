@@ -1204,23 +1204,44 @@ extern "C" int orbx__extract_resident(orbx_handle* h, const uint8_t* const* imgs
     ORBB_CUDA(cudaSetDevice(h->cfg.device));
     { const int rc = ensure_geometry(h, w, ht); if (rc != ORBB_OK) return rc; }
     cudaStream_t st = h->stream;
+    static const bool trace = getenv("ORBB_TRACE_PAIR") != nullptr;
+    static double acc[3] = {0, 0, 0}; static int ncalls = 0;
+    auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
+    const double t0 = trace ? now() : 0.0;
     ORBB_CUDA(cudaStreamSynchronize(st));       // an earlier asynchronous call may still be reading the level-0 slots
     const LevelGeom& g0 = h->geom[0];
     const bool tight = (w % 16) == 0 && (size_t)w * ht <= (size_t)g0.pitch * g0.h;
     const size_t dpitch0 = tight ? (size_t)w : (size_t)g0.pitch;
-    for (int f = 0; f < nframes; f++) {         // pageable or pinned alike: through the pinned staging block, so that every copy is asynchronous
-        uint8_t* stg = h->h_img + (size_t)f * w * ht;
-        if (stride == (size_t)w) memcpy(stg, imgs_host[f], (size_t)w * ht);
-        else for (int y = 0; y < ht; y++) memcpy(stg + (size_t)y * w, imgs_host[f] + (size_t)y * stride, w);
-        ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, dpitch0, stg, (size_t)w, w, ht, cudaMemcpyHostToDevice, st));
+    for (int f = 0; f < nframes; f++) {         // pageable images go through the pinned staging block, so that every copy is asynchronous
+        cudaPointerAttributes attr;
+        const bool pinned = cudaPointerGetAttributes(&attr, imgs_host[f]) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        const uint8_t* src = imgs_host[f]; size_t spitch = stride;
+        if (!pinned) {
+            uint8_t* stg = h->h_img + (size_t)f * w * ht;
+            if (stride == (size_t)w) memcpy(stg, imgs_host[f], (size_t)w * ht);
+            else for (int y = 0; y < ht; y++) memcpy(stg + (size_t)y * w, imgs_host[f] + (size_t)y * stride, w);
+            src = stg; spitch = (size_t)w;
+        }
+        ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, dpitch0, src, spitch, w, ht, cudaMemcpyHostToDevice, st));
     }
     const int devcap = h->dev_capacity;
     static const bool side = getenv("ORBB_RESIDENT_SIDE") ? atoi(getenv("ORBB_RESIDENT_SIDE")) != 0 : false;
+    const double t1 = trace ? now() : 0.0;
     const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, 0, side);
     if (rc != ORBB_OK) return rc;
     ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
     ORBB_CUDA(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
+    const double t2 = trace ? now() : 0.0;
     ORBB_CUDA(cudaStreamSynchronize(st));
+    if (trace) {
+        const double t3 = now();
+        acc[0] += t1 - t0; acc[1] += t2 - t1; acc[2] += t3 - t2;
+        if (++ncalls % 100 == 0) {
+            fprintf(stderr, "[pair trace] images staged and queued %.1f us, extraction launched %.1f us, waited %.1f us\n", acc[0] / 100, acc[1] / 100, acc[2] / 100);
+            acc[0] = acc[1] = acc[2] = 0;
+        }
+    }
     int ret = ORBB_OK;
     for (int f = 0; f < nframes; f++) {
         const int n = h->h_counts[f] < devcap ? h->h_counts[f] : devcap;
@@ -1235,6 +1256,6 @@ extern "C" int orbx__extract_resident(orbx_handle* h, const uint8_t* const* imgs
     v->geom_host = h->geom; v->geom_dev = h->d_geom; v->nlevels = h->nlevels;
     v->src0 = h->last_src; v->src0_pitch = h->last_src_pitch; v->src0_fstride = h->last_src_fstride;
     v->pyr = h->d_pyr; v->pyr_fstride = (long long)h->pyr_fstride;
-    v->scale = h->scale; v->inv_scale = h->inv_scale; v->device = h->cfg.device; v->stream = (void*)st; v->s_out = (void*)h->s_out;
+    v->scale = h->scale; v->inv_scale = h->inv_scale; v->device = h->cfg.device; v->stream = (void*)st; v->s_out = (void*)h->s_out; v->s_aux = (void*)h->s_in;
     return ret;
 }

@@ -943,22 +943,24 @@ extern "C" int orbm_stereo_frame_create(orbx_handle* h, const uint8_t* left_host
     const uint8_t* imgs[2] = {left_host, right_host};
     int32_t cnt[2] = {0, 0};
     orbx_resident_view v{};
+    static const bool trace = getenv("ORBB_TRACE_PAIR") != nullptr;      // debugging aid: host-side phase times on stderr every 100 calls
+    static double acc[5] = {0, 0, 0, 0, 0}; static int ncalls = 0;
+    auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
+    const double t0 = trace ? now() : 0.0;
     int rc = orbx__extract_resident(h, imgs, 2, w, ht, stride, cnt, &v);
+    const double t1 = trace ? now() : 0.0;
     if (rc != ORBB_OK) { if (v.s_out) cudaStreamSynchronize((cudaStream_t)v.s_out); return rc; }
-    cudaStream_t st = (cudaStream_t)v.stream, s_out = (cudaStream_t)v.s_out;
+    cudaStream_t st = (cudaStream_t)v.stream, s_out = (cudaStream_t)v.s_out, s_aux = (cudaStream_t)v.s_aux;
     const int nL = cnt[0], nR = cnt[1];
     *nL_out = nL; *nR_out = nR;
     if (nL > capacity || (kR_host && nR > capacity) || nR >= 65536) { cudaStreamSynchronize(s_out); return ORBB_E_CAPACITY; }
     uint8_t* pin = t_pin.get((size_t)(nL > 0 ? nL : 1) * 8);
     if (!pin) { cudaStreamSynchronize(s_out); return ORBB_E_NOMEM; }
-    orbm_frame* fr = nullptr;
-    rc = frame_create_impl(&fr, v.kps_dev, v.desc_dev, nL, min_x, min_y, max_x, max_y, v.device, cudaMemcpyDeviceToDevice, st);
-    if (rc != ORBB_OK) { cudaStreamSynchronize(s_out); return rc; }
-    auto fail = [&](int code) { cudaStreamSynchronize(st); cudaStreamSynchronize(s_out); orbm_frame_destroy(fr); return code; };
-    DevBuf bd, bs, bi, bb;
+    // all three streams are idle here (the extraction was drained to read the counts): stereo matching runs on s_aux beside the grid on st
+    DevBuf ur, bd, bs, bi, bb;
     if (nL > 0) {
-        if ((rc = fr->uright_own.alloc((size_t)nL * 4)) || (rc = bd.alloc((size_t)nL * 4)) || (rc = bs.alloc((size_t)nL * 4)) ||
-            (rc = bi.alloc((size_t)nL * 4)) || (rc = bb.alloc((size_t)nL * 4))) return fail(rc);
+        if ((rc = ur.alloc((size_t)nL * 4)) || (rc = bd.alloc((size_t)nL * 4)) || (rc = bs.alloc((size_t)nL * 4)) ||
+            (rc = bi.alloc((size_t)nL * 4)) || (rc = bb.alloc((size_t)nL * 4))) { cudaStreamSynchronize(s_out); return rc; }
         StereoArgs a;
         memset(&a, 0, sizeof a);
         a.kL = v.kps_dev; a.dL = reinterpret_cast<const uint4*>(v.desc_dev); a.nL = nL;
@@ -968,24 +970,45 @@ extern "C" int orbm_stereo_frame_create(orbx_handle* h, const uint8_t* left_host
         a.src0R = v.src0 + v.src0_fstride; a.src0R_pitch = v.src0_pitch; a.pyrR = v.pyr + v.pyr_fstride;
         for (int i = 0; i < v.nlevels; i++) { a.scale[i] = v.scale[i]; a.inv_scale[i] = v.inv_scale[i]; }
         a.mbf = mbf; a.minD = 0.f; a.maxD = mbf / mb;                      // Frame.cpp:579-581
-        a.uRight = fr->uright_own.as<float>(); a.depth = bd.as<float>(); a.sad = bs.as<int>(); a.bestIdx = bi.as<int>(); a.bestDist = bb.as<int>();
-        stereo_match_kernel<<<ceil_div(nL, 8), 256, 0, st>>>(a);
+        a.uRight = ur.as<float>(); a.depth = bd.as<float>(); a.sad = bs.as<int>(); a.bestIdx = bi.as<int>(); a.bestDist = bb.as<int>();
+        stereo_match_kernel<<<ceil_div(nL, 8), 256, 0, s_aux>>>(a);
         ORBB_LAUNCHED();
-        stereo_median_filter_kernel<<<1, 256, 0, st>>>(nL, a.sad, a.uRight, a.depth, 1.5f * 1.4f);
+        stereo_median_filter_kernel<<<1, 256, 0, s_aux>>>(nL, a.sad, a.uRight, a.depth, 1.5f * 1.4f);
         ORBB_LAUNCHED();
-        if (cudaMemcpyAsync(pin, a.uRight, (size_t)nL * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-            cudaMemcpyAsync(pin + (size_t)nL * 4, a.depth, (size_t)nL * 4, cudaMemcpyDeviceToHost, st) != cudaSuccess) return fail(ORBB_E_CUDA);
-        fr->uright_valid = true;
+        if (cudaMemcpyAsync(pin, a.uRight, (size_t)nL * 4, cudaMemcpyDeviceToHost, s_aux) != cudaSuccess ||
+            cudaMemcpyAsync(pin + (size_t)nL * 4, a.depth, (size_t)nL * 4, cudaMemcpyDeviceToHost, s_aux) != cudaSuccess) {
+            cudaStreamSynchronize(s_aux); cudaStreamSynchronize(s_out); return ORBB_E_CUDA;
+        }
     }
+    orbm_frame* fr = nullptr;
+    rc = frame_create_impl(&fr, v.kps_dev, v.desc_dev, nL, min_x, min_y, max_x, max_y, v.device, cudaMemcpyDeviceToDevice, st);
+    if (rc != ORBB_OK) { cudaStreamSynchronize(s_aux); cudaStreamSynchronize(s_out); return rc; }
+    auto fail = [&](int code) { cudaStreamSynchronize(st); cudaStreamSynchronize(s_aux); cudaStreamSynchronize(s_out); orbm_frame_destroy(fr); return code; };
+    const double t2 = trace ? now() : 0.0;
     cudaError_t e = cudaStreamSynchronize(s_out);              // keypoints and descriptors of both images are in the handle's pinned block
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s_aux);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     if (e != cudaSuccess) { set_cuda_error(e, "orbm_stereo_frame_create"); return fail(ORBB_E_CUDA); }
+    const double t3 = trace ? now() : 0.0;
+    if (nL > 0) {                                              // mvuRight stays with the frame (ORBM_URIGHT_OF_FRAME)
+        fr->uright_own.p = ur.p; fr->uright_own.cap = ur.cap; ur.p = nullptr; ur.cap = 0;
+        fr->uright_valid = true;
+    }
     if (nL > 0) {
         memcpy(kL_host, v.kps_pinned, (size_t)nL * sizeof(orbx_keypoint)); memcpy(dL_host, v.desc_pinned, (size_t)nL * 32);
         memcpy(uR_host, pin, (size_t)nL * 4); memcpy(depth_host, pin + (size_t)nL * 4, (size_t)nL * 4);
     }
     if (kR_host && nR > 0) {
         memcpy(kR_host, v.kps_pinned + v.devcap, (size_t)nR * sizeof(orbx_keypoint)); memcpy(dR_host, v.desc_pinned + (size_t)v.devcap * 32, (size_t)nR * 32);
+    }
+    if (trace) {
+        const double t4 = now();
+        acc[0] += t1 - t0; acc[1] += t2 - t1; acc[2] += t3 - t2; acc[3] += t4 - t3;
+        if (++ncalls % 100 == 0) {
+            fprintf(stderr, "[pair trace] extract (stage, launch, wait for counts) %.1f us, stereo + grid queued %.1f us, drained %.1f us, results copied out %.1f us\n",
+                    acc[0] / 100, acc[1] / 100, acc[2] / 100, acc[3] / 100);
+            acc[0] = acc[1] = acc[2] = acc[3] = 0;
+        }
     }
     *out = fr;
     return ORBB_OK;

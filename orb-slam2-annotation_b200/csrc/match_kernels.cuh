@@ -320,7 +320,8 @@ __global__ void excl_scan_kernel(const int* __restrict__ in, int* __restrict__ o
 // it.  So choice(i) depends only on the choices of queries j < i: the sequence of choices is the unique fixed point of
 //     choice(i) = best candidate k of i with  !(initially taken(k))  and  !(exists j < i: choice(j) == k and has_obs(j)).
 // One CTA iterates it in parallel (thread per query; taker[k] = min such j by atomicMin) until no choice changes; after round
-// r the first r queries are final, and dependency chains are a handful long in practice.  Slot k finally holds the LAST query
+// r the first r queries are final, and dependency chains are a handful long in practice.  Only displaced queries are evaluated again
+// (see the loop).  Slot k finally holds the LAST query
 // that chose it (a point without observations does not block and is overwritten, as in the reference), nmatches counts every
 // accepted query (:150, :1618), and MODE 1's rotation histogram (:1620-1656, ComputeThreeMaxima :1792-1833) then clears the
 // slots of the queries outside the three dominant bins.
@@ -370,34 +371,56 @@ template <int MODE>
 __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_constant__ ResolveArgs a)
 {
     extern __shared__ int taker_s[];
-    __shared__ int changed_s, nm_s, hist_s[30], ind_s[3];
+    __shared__ int nm_s, hist_s[30], ind_s[3];
     const int tid = threadIdx.x, nt = blockDim.x;
     if (a.offs[a.nq] > a.cap) { if (tid == 0) { *a.status = ORBB_E_CAPACITY; *a.nmatches = 0; } return; }
     int* taker = a.f.n <= RESOLVE_SMEM_SLOTS ? taker_s : a.taker;
     for (int i = tid; i < a.nq; i += nt) a.choice[i] = -2;
     for (int k = tid; k < a.f.n; k += nt) taker[k] = 0x7fffffff;
-    if (tid == 0) { nm_s = 0; changed_s = 0; }
+    if (tid == 0) nm_s = 0;
     if (tid < 30) hist_s[tid] = 0;
     __syncthreads();
     int rounds = 0;
-    for (;;) {
-        bool changed = false;
-        for (int i = tid; i < a.nq; i += nt) {
-            const int c = resolve_choose<MODE>(a, taker, i);
-            if (c != a.choice[i]) { a.choice[i] = c; changed = true; }
+    if (MODE == 0) {
+        // The ratio test makes a query's verdict depend on its best AND second-best unblocked candidate, and a query that loses its
+        // second best may turn from accepted to rejected, which frees its slot again: every round rebuilds taker[] and evaluates all.
+        for (;;) {
+            bool changed = false;
+            for (int i = tid; i < a.nq; i += nt) {
+                const int c = resolve_choose<MODE>(a, taker, i);
+                if (c != a.choice[i]) { a.choice[i] = c; changed = true; }
+            }
+            rounds++;
+            const int any = __syncthreads_or(changed);
+            for (int k = tid; k < a.f.n; k += nt) taker[k] = 0x7fffffff;
+            __syncthreads();
+            if (!any) break;
+            for (int i = tid; i < a.nq; i += nt) {
+                const int c = a.choice[i];
+                if (c >= 0 && a.q[i].has_obs > 0) atomicMin(&taker[c], i);
+            }
+            __syncthreads();
         }
-        if (changed) changed_s = 1;
-        __syncthreads();
-        const int any = changed_s;
-        rounds++;
+    } else {
+        // MODE 1 / 2 accept the best unblocked candidate on its distance alone, so blocked sets only grow: slot k is blocked for query i
+        // by taker[k] = the smallest j < i (with observations) that chose it, and that j leaves k only when an even smaller index takes
+        // k.  So (1) taker[] accumulates by atomicMin without being rebuilt - the minimum over every query that ever chose k is a query
+        // that stays on k - (2) a rejected query stays rejected, and (3) a query is evaluated again only when its current choice became
+        // blocked: after the first round a round costs one shared-memory load per query plus the few displaced queries.
+        for (;;) {
+            bool changed = false;
+            for (int i = tid; i < a.nq; i += nt) {
+                const int c = a.choice[i];
+                if (c == -2 || (c >= 0 && taker[c] < i)) {
+                    const int nc = resolve_choose<MODE>(a, taker, i);
+                    a.choice[i] = nc; changed = true;
+                    if (nc >= 0 && (MODE == 2 || a.q[i].has_obs > 0)) atomicMin(&taker[nc], i);      // MODE 2: any MapPoint blocks the slot for later queries
+                }
+            }
+            rounds++;
+            if (!__syncthreads_or(changed)) break;
+        }
         for (int k = tid; k < a.f.n; k += nt) taker[k] = 0x7fffffff;
-        __syncthreads();
-        if (!any) break;
-        if (tid == 0) changed_s = 0;
-        for (int i = tid; i < a.nq; i += nt) {
-            const int c = a.choice[i];
-            if (c >= 0 && (MODE == 2 || a.q[i].has_obs > 0)) atomicMin(&taker[c], i);      // MODE 2: any MapPoint blocks the slot for later queries
-        }
         __syncthreads();
     }
     // slot k <- the last query that chose it; taker is reused as "last chooser" (reset to INT_MAX above: store -i-1 as min)

@@ -59,7 +59,7 @@ void ORBextractor::EnsureHandle(int w, int h)
     cfg.nfeatures = nfeatures; cfg.scale_factor = (float)scaleFactor; cfg.nlevels = nlevels;
     cfg.ini_th_fast = iniThFAST; cfg.min_th_fast = minThFAST;
     cfg.max_width = w > mnMaxW ? w : mnMaxW; cfg.max_height = h > mnMaxH ? h : mnMaxH;
-    cfg.max_batch = 1; cfg.device = mnDevice; cfg.blur_legacy = 0;
+    cfg.max_batch = 2; cfg.device = mnDevice; cfg.blur_legacy = 0;      // two frames: a stereo pair as one batch (orbm_stereo_frame_create)
     check(orbx_create(&cfg, &mpHandle), "orbx_create");
     mnMaxW = cfg.max_width; mnMaxH = cfg.max_height;
     std::vector<float> sc(nlevels), isc(nlevels), s2(nlevels), is2(nlevels);

@@ -53,6 +53,7 @@ public:
     void SetPyramidDownload(bool on) { mbDownloadPyramid = on; }
     void SetDevice(int device) { mnDevice = device; }
     orbx_handle* Handle() { return mpHandle; }                    // for orbm_stereo_match(left->Handle(), right->Handle(), ...)
+    int Capacity() const { return nfeatures + 64 * nlevels + 256; } // rows the octree can return at most (as sized in operator())
 
 protected:
     void EnsureHandle(int w, int h);

@@ -57,6 +57,28 @@ public:
         for (int i = 0; i < n_; i++) memcpy(&d[(size_t)i * 32], descriptors.ptr(i), 32);
         orbm_check(orbm_frame_create(&f_, (const orbx_keypoint*)keysUn.data(), d.data(), n_, minX, minY, maxX, maxY, device), "orbm_frame_create");
     }
+    // Frame::Frame, stereo constructor (src/Frame.cpp:61-115) as one device call (orbm_stereo_frame_create): both images are extracted
+    // as one batch of `extractor`'s handle (it plays mpORBextractorLeft and ...Right), ComputeStereoMatches and AssignFeaturesToGrid run
+    // on the results in device memory.  Fills every vector the constructor fills; mvKeysUn = mvKeys (rectified input, :467-472).
+    // SearchByProjection / SearchByProjectionLastFrame with mvuRight == StoredURight() reuse the device copy of mvuRight.
+    static const std::vector<float>* StoredURight() { static const std::vector<float> tag; return &tag; }
+    DeviceFrame(ORBextractor& extractor, const cv::Mat& imLeft, const cv::Mat& imRight, float mbf, float mb, float minX, float minY, float maxX,
+                float maxY, std::vector<cv::KeyPoint>& mvKeys, cv::Mat& mDescriptors, std::vector<cv::KeyPoint>& mvKeysRight, cv::Mat& mDescriptorsRight,
+                std::vector<float>& mvuRight, std::vector<float>& mvDepth)
+        : f_(nullptr), n_(0)
+    {
+        extractor.Reserve(imLeft.cols, imLeft.rows);
+        const int cap = extractor.Capacity();
+        int nL = 0, nR = 0;
+        mvKeys.resize(cap); mvKeysRight.resize(cap); mvuRight.assign(cap, -1.0f); mvDepth.assign(cap, -1.0f);
+        mDescriptors.create(cap, 32, CV_8U); mDescriptorsRight.create(cap, 32, CV_8U);
+        orbm_check(orbm_stereo_frame_create(extractor.Handle(), imLeft.ptr(0), imRight.ptr(0), imLeft.cols, imLeft.rows, imLeft.step, mbf, mb, minX, minY,
+                                            maxX, maxY, &f_, (orbx_keypoint*)mvKeys.data(), mDescriptors.ptr(0), &nL, (orbx_keypoint*)mvKeysRight.data(),
+                                            mDescriptorsRight.ptr(0), &nR, cap, mvuRight.data(), mvDepth.data()), "orbm_stereo_frame_create");
+        n_ = nL;
+        mvKeys.resize(nL); mvKeysRight.resize(nR); mvuRight.resize(nL); mvDepth.resize(nL);
+        mDescriptors.rows = nL; mDescriptorsRight.rows = nR;
+    }
     ~DeviceFrame() { if (f_) orbm_frame_destroy(f_); }
     DeviceFrame(const DeviceFrame&) = delete;
     DeviceFrame& operator=(const DeviceFrame&) = delete;
@@ -138,12 +160,13 @@ public:
         orbm_check(orbm_distance_pairs(a, b, n, out, device), "orbm_distance_pairs");
     }
 
+    static const float* URightArg(const std::vector<float>* v) { return !v ? nullptr : (v == DeviceFrame::StoredURight() ? ORBM_URIGHT_OF_FRAME : v->data()); }
     // src/ORBmatcher.cpp:63-155 after the caller filled one orbm_proj_query per visible map point.
     int SearchByProjection(const DeviceFrame& F, const std::vector<float>* mvuRight, const std::vector<orbm_proj_query>& q,
                            std::vector<int32_t>& frameMapPointIds, std::vector<int32_t>& frameMapPointHasObs) const
     {
         int n = 0;
-        orbm_check(orbm_search_by_projection_points(F.get(), mvuRight ? mvuRight->data() : nullptr, q.data(), (int)q.size(), mfNNratio,
+        orbm_check(orbm_search_by_projection_points(F.get(), URightArg(mvuRight), q.data(), (int)q.size(), mfNNratio,
                                                     frameMapPointIds.data(), frameMapPointHasObs.data(), &n), "orbm_search_by_projection_points");
         return n;
     }
@@ -152,7 +175,7 @@ public:
                                     std::vector<int32_t>& frameMapPointIds, std::vector<int32_t>& frameMapPointHasObs) const
     {
         int n = 0;
-        orbm_check(orbm_search_by_projection_frame(Current.get(), mvuRight ? mvuRight->data() : nullptr, q.data(), (int)q.size(),
+        orbm_check(orbm_search_by_projection_frame(Current.get(), URightArg(mvuRight), q.data(), (int)q.size(),
                                                    mbCheckOrientation ? 1 : 0, frameMapPointIds.data(), frameMapPointHasObs.data(), &n),
                    "orbm_search_by_projection_frame");
         return n;

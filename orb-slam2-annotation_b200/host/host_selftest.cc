@@ -110,6 +110,28 @@ static int match_mode(const char* in, const char* outp)
         ComputeStereoMatches(exL, exR, kL, dL, kR, dR, mbf, 0.0f, uR, depth);
         const int n = (int)kL.size();
         put(&n, 4); put(uR.data(), 4 * (size_t)n); put(depth.data(), 4 * (size_t)n);
+        // the same constructor as ONE device call (orbm_stereo_frame_create): every member must come back identical, and a tracked-frame
+        // search on the frame it leaves on the device must not depend on where mvuRight comes from
+        std::vector<cv::KeyPoint> kL2, kR2;
+        cv::Mat dL2, dR2;
+        std::vector<float> uR2, depth2;
+        DeviceFrame F(exL, imL, imR, mbf, 0.0f, 0.f, 0.f, (float)w, (float)h, kL2, dL2, kR2, dR2, uR2, depth2);
+        if (kL2.size() != kL.size() || kR2.size() != kR.size() || memcmp(kL2.data(), kL.data(), sizeof(cv::KeyPoint) * kL.size()) ||
+            memcmp(kR2.data(), kR.data(), sizeof(cv::KeyPoint) * kR.size()) || memcmp(uR2.data(), uR.data(), 4 * uR.size()) ||
+            memcmp(depth2.data(), depth.data(), 4 * depth.size())) { fprintf(stderr, "fused stereo constructor differs (keypoints / uRight / depth)\n"); return 4; }
+        for (int i = 0; i < n; i++) if (memcmp(dL2.ptr(i), dL.ptr(i), 32)) { fprintf(stderr, "fused stereo constructor differs (descriptor %d)\n", i); return 4; }
+        std::vector<orbm_proj_query> qs((size_t)n);
+        for (int i = 0; i < n; i++) {
+            orbm_proj_query& e = qs[i];
+            memset(&e, 0, sizeof e);
+            e.q.u = kL[i].pt.x + 2.0f; e.q.v = kL[i].pt.y + 1.0f; e.q.r = 15.0f * exL.GetScaleFactors()[kL[i].octave];
+            e.q.min_level = kL[i].octave - 1; e.q.max_level = kL[i].octave + 1; memcpy(e.q.desc, dL.ptr(i), 32);
+            e.u_right = e.q.u - 5.0f; e.max_err_right = e.q.r; e.id = i; e.has_obs = 1; e.angle = kL[i].angle;
+        }
+        std::vector<int32_t> mpA(n, -1), obA(n, 0), mpB(n, -1), obB(n, 0);
+        const int nA = ORBmatcher(0.9f, true).SearchByProjectionLastFrame(F, DeviceFrame::StoredURight(), qs, mpA, obA);
+        const int nB = ORBmatcher(0.9f, true).SearchByProjectionLastFrame(F, &uR, qs, mpB, obB);
+        if (nA != nB || nA < n / 4 || mpA != mpB || obA != obB) { fprintf(stderr, "search on the fused frame: %d vs %d matches\n", nA, nB); return 4; }
     }
     {   // batched distances: row i of frame 1 against row i of frame 2
         const int n = n1 < n2 ? n1 : n2;

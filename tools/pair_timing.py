@@ -54,8 +54,12 @@ def old_pair(i, q):
     tick("a_pair", t00)
 
 
+pinned_pairs = [tuple(torch.from_numpy(x).pin_memory().numpy() for x in pr) for pr in pairs]
+use_pinned = False
+
+
 def new_pair(i, q):
-    left, right = pairs[i & 1]
+    left, right = (pinned_pairs if use_pinned else pairs)[i & 1]
     t = t00 = time.perf_counter()
     fh = vp()
     assert L.orbm_stereo_frame_create(ex2.h, ptr(left), ptr(right), w, h, w, mbf, C.c_float(0.0), *bounds, C.byref(fh), ptr(b["kL"]), ptr(b["dL"]), C.byref(nL),
@@ -81,4 +85,11 @@ with np.errstate(divide="ignore"):
             fn(i, qs[i & 1])
         res.update({k: round(float(np.median(v)), 1) for k, v in T.items()})
         res[fn.__name__ + "_matches"] = int(nm.value)
+    use_pinned = True                                         # (c) the fused constructor on page-locked images
+    for i in range(10):
+        new_pair(i, qs[i & 1])
+    T.clear()
+    for i in range(reps):
+        new_pair(i, qs[i & 1])
+    res.update({"c_pinned_images_" + k[2:]: round(float(np.median(v)), 1) for k, v in T.items()})
 print(json.dumps(res))
