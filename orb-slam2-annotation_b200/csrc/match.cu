@@ -196,7 +196,7 @@ struct orbm_frame {
     DevBuf kps, desc, cell_of, cell_start, cell_items, cursor;
     DevBuf uright_own; bool uright_valid = false;      // mvuRight computed by orbm_stereo_frame_create (ORBM_URIGHT_OF_FRAME)
     // workspace of the device resolve (orbm_search_by_projection_*_device); calls on one frame are serialised by the caller
-    mutable DevBuf ws_counts, ws_offs, ws_idx, ws_dist, ws_choice, ws_taker, ws_uright, ws_mp, ws_obs, ws_scalars;
+    mutable DevBuf ws_counts, ws_offs, ws_idx, ws_dist, ws_choice, ws_taker, ws_uright, ws_mp;   // ws_mp: [mvpMapPoints | observations | 4 scalars] of the host-pointer searches
     // recorded after the copies and grid kernels of orbm_frame_create_device on the caller's stream: the host-pointer entry points
     // run on the legacy default stream, which does not order against cudaStreamNonBlocking streams, so they wait on it first
     cudaEvent_t ready = nullptr;
@@ -385,28 +385,28 @@ inline int rot_bin(float a1, float a2)
 // (SURVEY 8(f)-1).  Everything is queued on `st`; nothing is read back here.
 static int resolve_on_device(const orbm_frame* fr, int mode, const float* uright_dev, const orbm_proj_query* q_dev, int nq, float nnratio,
                              int check_ori, int32_t* frame_mp_dev, int32_t* frame_mp_obs_dev, int32_t* nmatches_dev, int32_t* status_dev,
-                             int32_t* rounds_dev, int cand_capacity, cudaStream_t st, int max_dist = 100 /* TH_HIGH */)
+                             int32_t* rounds_dev, int cand_capacity, cudaStream_t st, int max_dist = 100 /* TH_HIGH */, int32_t* total_out_dev = nullptr)
 {
     const int cap = cand_capacity > 0 ? cand_capacity : 64 * nq + 1024;
     int rc;
     if (fr->ready) ORBB_CUDA(cudaStreamWaitEvent(st, fr->ready, 0));      // the frame may have been built on another stream
     if (fr->s_last != st && fr->s_last != fr->s_create) cudaStreamSynchronize(fr->s_last);       // a third stream: keep only two to drain at destroy
     fr->s_last = st;
+    // ws_offs: [0, nq) first candidate of each query, [nq] total (host retry reads it), ws_counts: [0, nq) one past the last candidate
     if ((rc = fr->ws_counts.reserve((size_t)nq * 4)) ||
         (rc = fr->ws_offs.reserve((size_t)(nq + 1) * 4)) || (rc = fr->ws_idx.reserve((size_t)cap * 4)) ||
         (rc = fr->ws_dist.reserve((size_t)cap * 4)) || (rc = fr->ws_choice.reserve((size_t)nq * 4)) ||
         (rc = fr->ws_taker.reserve((size_t)fr->n * 4))) return rc;
     const int wpb = 8;
     const WindowFilter flt{frame_mp_dev, frame_mp_obs_dev, uright_dev};
-    window_search_kernel<false, true><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, fr->ws_counts.as<int>(), nullptr, nullptr,
-                                                                            nullptr, 0, flt);
-    ORBB_LAUNCHED();
-    excl_scan_kernel<<<1, 1024, 0, st>>>(fr->ws_counts.as<int>(), fr->ws_offs.as<int>(), nq); ORBB_LAUNCHED();
-    window_search_kernel<true, true><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, nullptr, fr->ws_offs.as<int>(),
-                                                                           fr->ws_idx.as<int>(), fr->ws_dist.as<int>(), cap, flt);
+    int* total_dev = total_out_dev ? total_out_dev : fr->ws_offs.as<int>() + nq;      // number of candidates found (> cap: overflow)
+    ORBB_CUDA(cudaMemsetAsync(total_dev, 0, 4, st));
+    window_search_onepass_kernel<true><<<ceil_div(nq, wpb), wpb * 32, 0, st>>>(fr->f, q_dev, sizeof(orbm_proj_query), nq, fr->ws_offs.as<int>(), fr->ws_counts.as<int>(),
+                                                                             total_dev, fr->ws_idx.as<int>(), fr->ws_dist.as<int>(), cap, flt);
     ORBB_LAUNCHED();
     ResolveArgs a{};
-    a.f = fr->f; a.q = q_dev; a.nq = nq; a.offs = fr->ws_offs.as<int>(); a.idx = fr->ws_idx.as<int>(); a.dist = fr->ws_dist.as<int>(); a.cap = cap;
+    a.f = fr->f; a.q = q_dev; a.nq = nq; a.offs = fr->ws_offs.as<int>(); a.ends = fr->ws_counts.as<int>(); a.total = total_dev;
+    a.idx = fr->ws_idx.as<int>(); a.dist = fr->ws_dist.as<int>(); a.cap = cap;
     a.uright = uright_dev; a.nnratio = nnratio; a.check_ori = check_ori; a.max_dist = max_dist; a.frame_mp = frame_mp_dev; a.frame_mp_obs = frame_mp_obs_dev;
     a.choice = fr->ws_choice.as<int>(); a.taker = fr->ws_taker.as<int>(); a.nmatches = nmatches_dev; a.status = status_dev; a.rounds = rounds_dev;
     const size_t smem = fr->n <= RESOLVE_SMEM_SLOTS ? (size_t)fr->n * 4 : 0;
@@ -453,37 +453,32 @@ static int search_projection_host(const orbm_frame* f, int mode, const float* ur
     if (own_uright && !f->uright_valid && f->n > 0) return ORBB_E_STATE;
     const size_t nb = (size_t)f->n * 4, qb = (size_t)nq * sizeof(orbm_proj_query);
     const bool up_uright = uright && !own_uright && f->n > 0;
+    // device state block [mvpMapPoints | observations | nmatches, status, rounds, candidates]: one copy in, one copy out
     DevBuf q;
-    if ((rc = q.alloc(qb)) || (rc = f->ws_mp.reserve(nb)) || (rc = f->ws_obs.reserve(nb)) ||
-        (rc = f->ws_scalars.reserve(16)) || (up_uright && (rc = f->ws_uright.reserve(nb)))) return rc;
-    // one pinned block per call: [queries | mvuRight | mvpMapPoints | observations | header]; every copy is asynchronous on this thread's
-    // stream and the call synchronises once per attempt
+    if ((rc = q.alloc(qb)) || (rc = f->ws_mp.reserve(2 * nb + 16)) || (up_uright && (rc = f->ws_uright.reserve(nb)))) return rc;
+    // one pinned block per call: [queries | mvuRight | state block]; every copy is asynchronous on this thread's stream and the call
+    // synchronises once per attempt
     uint8_t* pin = t_pin.get(qb + 3 * nb + 64);
     if (!pin) return ORBB_E_NOMEM;
     uint8_t *p_q = pin, *p_u = pin + qb, *p_mp = p_u + nb, *p_obs = p_mp + nb;
     int32_t* p_h = reinterpret_cast<int32_t*>(p_obs + nb);
+    int32_t *d_mp = f->ws_mp.as<int32_t>(), *d_obs = d_mp + f->n, *sc = d_obs + f->n;
     cudaStream_t st = 0;                                               // this thread's default stream
     memcpy(p_q, pq, qb);
     ORBB_CUDA(cudaMemcpyAsync(q.p, p_q, qb, cudaMemcpyHostToDevice, st));
     if (up_uright) { memcpy(p_u, uright, nb); ORBB_CUDA(cudaMemcpyAsync(f->ws_uright.p, p_u, nb, cudaMemcpyHostToDevice, st)); }
     const float* ur_dev = own_uright ? (f->n > 0 ? (const float*)f->uright_own.p : nullptr) : (uright ? f->ws_uright.as<float>() : nullptr);
-    int32_t* sc = f->ws_scalars.as<int32_t>();
     int cap = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
         if (f->n > 0) {
             memcpy(p_mp, frame_mp, nb);
-            ORBB_CUDA(cudaMemcpyAsync(f->ws_mp.p, p_mp, nb, cudaMemcpyHostToDevice, st));
-            if (frame_mp_obs) { memcpy(p_obs, frame_mp_obs, nb); ORBB_CUDA(cudaMemcpyAsync(f->ws_obs.p, p_obs, nb, cudaMemcpyHostToDevice, st)); }
+            if (frame_mp_obs) memcpy(p_obs, frame_mp_obs, nb);
+            ORBB_CUDA(cudaMemcpyAsync(d_mp, p_mp, frame_mp_obs ? 2 * nb : nb, cudaMemcpyHostToDevice, st));
         }
-        rc = resolve_on_device(f, mode, ur_dev, q.as<orbm_proj_query>(), nq, nnratio, check_ori,
-                               f->ws_mp.as<int32_t>(), frame_mp_obs ? f->ws_obs.as<int32_t>() : nullptr, sc, sc + 1, sc + 2, cap, st, max_dist);
+        rc = resolve_on_device(f, mode, ur_dev, q.as<orbm_proj_query>(), nq, nnratio, check_ori, d_mp, frame_mp_obs ? d_obs : nullptr, sc, sc + 1, sc + 2, cap, st,
+                               max_dist, sc + 3);
         if (rc != ORBB_OK) return rc;
-        ORBB_CUDA(cudaMemcpyAsync(p_h, sc, 12, cudaMemcpyDeviceToHost, st));
-        ORBB_CUDA(cudaMemcpyAsync(p_h + 3, f->ws_offs.as<int>() + nq, 4, cudaMemcpyDeviceToHost, st));
-        if (f->n > 0) {
-            ORBB_CUDA(cudaMemcpyAsync(p_mp, f->ws_mp.p, nb, cudaMemcpyDeviceToHost, st));
-            if (frame_mp_obs) ORBB_CUDA(cudaMemcpyAsync(p_obs, f->ws_obs.p, nb, cudaMemcpyDeviceToHost, st));
-        }
+        ORBB_CUDA(cudaMemcpyAsync(p_mp, d_mp, 2 * nb + 16, cudaMemcpyDeviceToHost, st));
         ORBB_CUDA(cudaStreamSynchronize(st));
         if (p_h[1] == ORBB_E_CAPACITY && attempt == 0) {            // more candidates than the default budget: size it exactly
             cap = p_h[3] + 16;

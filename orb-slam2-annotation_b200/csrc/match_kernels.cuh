@@ -216,6 +216,69 @@ __global__ void grid_sort_kernel(FrameDev f)
 // :1727-1728, :438-439); else only slots whose MapPoint has observations (:1590-1592, :107-109)
 struct WindowFilter { const int* frame_mp; const int* frame_mp_obs; const float* uright; };
 
+// One walk over the query's cell window.  FILL = false: count the candidates; FILL = true: write them from cand[obase] on (GetFeaturesInArea
+// order) with their distances.
+template <bool FILL, bool FILTER>
+__device__ __forceinline__ int window_walk(const FrameDev& f, const orbm_query& q, int lane, int obase, int* __restrict__ cand_idx,
+                                           int* __restrict__ cand_dist, int cap, const WindowFilter& flt)
+{
+    const float x = q.u, y = q.v, r = q.r;
+    const int minLevel = q.min_level, maxLevel = q.max_level;
+    int total = 0;
+    // cell window (Frame.cpp:384-398)
+    const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, f.minX), r), f.invW)));
+    const int nMaxCellX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, f.minX), r), f.invW)));
+    const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, f.minY), r), f.invH)));
+    const int nMaxCellY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, f.minY), r), f.invH)));
+    const bool empty = nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0;
+    if (empty) return 0;
+    const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
+    uint4 q0, q1;
+    if (FILL) {   // orbm_query::desc sits at byte offset 20 of a 52-byte record: 4-byte aligned only
+        const unsigned* qd = reinterpret_cast<const unsigned*>(q.desc);
+        q0 = make_uint4(qd[0], qd[1], qd[2], qd[3]); q1 = make_uint4(qd[4], qd[5], qd[6], qd[7]);
+    }
+    for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
+        // cells (ix, nMinCellY..nMaxCellY) are contiguous in the CSR (cell id = ix*GRID_ROWS + iy)
+        const int b = f.cell_start[ix * GRID_ROWS + nMinCellY], e = f.cell_start[ix * GRID_ROWS + nMaxCellY + 1];
+        for (int base = b; base < e; base += 32) {
+            const int j = base + lane;
+            bool ok = false; int idx = -1, oct = 0;
+            if (j < e) {
+                idx = f.cell_items[j];
+                const orbx_keypoint kp = f.kps[idx];
+                ok = true;
+                if (bCheckLevels) {
+                    if (kp.octave < minLevel) ok = false;
+                    if (maxLevel >= 0 && kp.octave > maxLevel) ok = false;
+                }
+                const float dx = __fsub_rn(kp.x, x), dy = __fsub_rn(kp.y, y);
+                if (!(fabsf(dx) < r && fabsf(dy) < r)) ok = false;
+                oct = kp.octave;
+                if (FILTER && ok) {
+                    const orbm_proj_query& pq = reinterpret_cast<const orbm_proj_query&>(q);
+                    if (flt.frame_mp[idx] >= 0 && (!flt.frame_mp_obs || flt.frame_mp_obs[idx] > 0)) ok = false;
+                    if (flt.uright) {
+                        const float urk = flt.uright[idx];
+                        if (urk > 0 && fabsf(__fsub_rn(pq.u_right, urk)) > pq.max_err_right) ok = false;
+                    }
+                }
+            }
+            const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            if (FILL && ok) {
+                const int pos = obase + total + __popc(bal & ((1u << lane) - 1));
+                if (pos < cap) {
+                    cand_idx[pos] = idx;
+                    const int d = hamming256(q0, q1, f.desc[2 * idx], f.desc[2 * idx + 1]);
+                    cand_dist[pos] = FILTER ? (d | (oct << 16)) : d;
+                }
+            }
+            total += __popc(bal);
+        }
+    }
+    return total;
+}
+
 template <bool FILL, bool FILTER = false>
 __global__ void window_search_kernel(FrameDev f, const void* __restrict__ qs, size_t qstride, int nq,   // records that START with an orbm_query
                                      int* __restrict__ counts, const int* __restrict__ offsets,
@@ -225,63 +288,27 @@ __global__ void window_search_kernel(FrameDev f, const void* __restrict__ qs, si
     const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (qi >= nq) return;
     const orbm_query& q = *reinterpret_cast<const orbm_query*>(static_cast<const char*>(qs) + (size_t)qi * qstride);
-    const float x = q.u, y = q.v, r = q.r;
-    const int minLevel = q.min_level, maxLevel = q.max_level;
-    int total = 0;
-    const int obase = FILL ? offsets[qi] : 0;
-    // cell window (Frame.cpp:384-398)
-    const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, f.minX), r), f.invW)));
-    const int nMaxCellX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, f.minX), r), f.invW)));
-    const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, f.minY), r), f.invH)));
-    const int nMaxCellY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, f.minY), r), f.invH)));
-    const bool empty = nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0;
-    if (!empty) {
-        const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
-        uint4 q0, q1;
-        if (FILL) {   // orbm_query::desc sits at byte offset 20 of a 52-byte record: 4-byte aligned only
-            const unsigned* qd = reinterpret_cast<const unsigned*>(q.desc);
-            q0 = make_uint4(qd[0], qd[1], qd[2], qd[3]); q1 = make_uint4(qd[4], qd[5], qd[6], qd[7]);
-        }
-        for (int ix = nMinCellX; ix <= nMaxCellX; ix++) {
-            // cells (ix, nMinCellY..nMaxCellY) are contiguous in the CSR (cell id = ix*GRID_ROWS + iy)
-            const int b = f.cell_start[ix * GRID_ROWS + nMinCellY], e = f.cell_start[ix * GRID_ROWS + nMaxCellY + 1];
-            for (int base = b; base < e; base += 32) {
-                const int j = base + lane;
-                bool ok = false; int idx = -1, oct = 0;
-                if (j < e) {
-                    idx = f.cell_items[j];
-                    const orbx_keypoint kp = f.kps[idx];
-                    ok = true;
-                    if (bCheckLevels) {
-                        if (kp.octave < minLevel) ok = false;
-                        if (maxLevel >= 0 && kp.octave > maxLevel) ok = false;
-                    }
-                    const float dx = __fsub_rn(kp.x, x), dy = __fsub_rn(kp.y, y);
-                    if (!(fabsf(dx) < r && fabsf(dy) < r)) ok = false;
-                    oct = kp.octave;
-                    if (FILTER && ok) {
-                        const orbm_proj_query& pq = reinterpret_cast<const orbm_proj_query&>(q);
-                        if (flt.frame_mp[idx] >= 0 && (!flt.frame_mp_obs || flt.frame_mp_obs[idx] > 0)) ok = false;
-                        if (flt.uright) {
-                            const float urk = flt.uright[idx];
-                            if (urk > 0 && fabsf(__fsub_rn(pq.u_right, urk)) > pq.max_err_right) ok = false;
-                        }
-                    }
-                }
-                const unsigned bal = __ballot_sync(0xffffffffu, ok);
-                if (FILL && ok) {
-                    const int pos = obase + total + __popc(bal & ((1u << lane) - 1));
-                    if (pos < cap) {
-                        cand_idx[pos] = idx;
-                        const int d = hamming256(q0, q1, f.desc[2 * idx], f.desc[2 * idx + 1]);
-                        cand_dist[pos] = FILTER ? (d | (oct << 16)) : d;
-                    }
-                }
-                total += __popc(bal);
-            }
-        }
-    }
+    const int total = window_walk<FILL, FILTER>(f, q, lane, FILL ? offsets[qi] : 0, cand_idx, cand_dist, cap, flt);
     if (!FILL && lane == 0) counts[qi] = total;
+}
+
+// Count, reserve and fill in ONE launch (the device resolve does not need the candidate lists in query order): the warp counts its
+// window, lane 0 reserves that many slots with one atomicAdd on *total (zeroed by the caller) and the warp walks the window again to
+// fill them - the second walk hits the lines the first one brought in.  begin[qi] / end[qi] delimit the query's candidates;
+// *total > cap afterwards means overflow (slots past cap were not written), as offs[nq] > cap does in the three-launch form.
+template <bool FILTER>
+__global__ void window_search_onepass_kernel(FrameDev f, const void* __restrict__ qs, size_t qstride, int nq, int* __restrict__ begin, int* __restrict__ end,
+                                             int* __restrict__ total, int* __restrict__ cand_idx, int* __restrict__ cand_dist, int cap, WindowFilter flt)
+{
+    const int lane = threadIdx.x & 31;
+    const int qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (qi >= nq) return;
+    const orbm_query& q = *reinterpret_cast<const orbm_query*>(static_cast<const char*>(qs) + (size_t)qi * qstride);
+    const int n = window_walk<false, FILTER>(f, q, lane, 0, nullptr, nullptr, 0, flt);
+    int obase = 0;
+    if (lane == 0) { obase = n > 0 ? atomicAdd(total, n) : 0; begin[qi] = obase; end[qi] = obase + n; }
+    obase = __shfl_sync(0xffffffffu, obase, 0);
+    if (n > 0) window_walk<true, FILTER>(f, q, lane, obase, cand_idx, cand_dist, cap, flt);
 }
 
 // single-block exclusive scan (n up to a few hundred thousand): offsets[0..n], offsets[n] = total
@@ -329,7 +356,8 @@ __global__ void excl_scan_kernel(const int* __restrict__ in, int* __restrict__ o
 struct ResolveArgs {
     FrameDev f;
     const orbm_proj_query* q; int nq;
-    const int* offs; const int* idx; const int* dist; int cap;     // candidate CSR (offs[nq] > cap: overflow, nothing is written)
+    const int* offs; const int* ends; const int* total;            // candidates of query i: [offs[i], ends[i]); *total > cap: overflow, nothing is written
+    const int* idx; const int* dist; int cap;
     const float* uright;                                           // mvuRight or nullptr
     float nnratio; int check_ori;
     int max_dist;                                                  // accept best <= max_dist: TH_HIGH (a10, a11), ORBdist (reloc), TH_LOW (loop)
@@ -345,7 +373,7 @@ template <int MODE>
 __device__ __forceinline__ int resolve_choose(const ResolveArgs& a, const int* __restrict__ taker, int i)
 {
     int bestDist = 256, bestDist2 = 256, bestLevel = -1, bestLevel2 = -1, bestIdx = -1;
-    const int e = a.offs[i + 1];
+    const int e = a.ends[i];
     for (int c0 = a.offs[i]; c0 < e; c0 += 4) {          // four candidates' loads in flight, then the reference's sequential update
         int k[4], pd[4], tk[4];
 #pragma unroll
@@ -373,7 +401,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
     extern __shared__ int taker_s[];
     __shared__ int nm_s, hist_s[30], ind_s[3];
     const int tid = threadIdx.x, nt = blockDim.x;
-    if (a.offs[a.nq] > a.cap) { if (tid == 0) { *a.status = ORBB_E_CAPACITY; *a.nmatches = 0; } return; }
+    if (*a.total > a.cap) { if (tid == 0) { *a.status = ORBB_E_CAPACITY; *a.nmatches = 0; } return; }
     int* taker = a.f.n <= RESOLVE_SMEM_SLOTS ? taker_s : a.taker;
     for (int i = tid; i < a.nq; i += nt) a.choice[i] = -2;
     for (int k = tid; k < a.f.n; k += nt) taker[k] = 0x7fffffff;
