@@ -578,7 +578,12 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         }
         {
             dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, nw * L3_RG), nframes);
-            if (nw == 8) { if (legacy) level3_kernel<8, true><<<grid, 256, 0, st>>>(a); else level3_kernel<8, false><<<grid, 256, 0, st>>>(a); }
+            // at most two CTAs per SM in the whole launch (one frame, a stereo pair): the level is bound by the serial chain of a tile, not by
+            // throughput - twice the warps per tile, FAST reject beside blur + resize (ORBB_L3_SPLIT = 0 | 1 forces the choice)
+            static const int split_env = getenv("ORBB_L3_SPLIT") ? atoi(getenv("ORBB_L3_SPLIT")) : -1;
+            const bool split = nw == 4 && (split_env >= 0 ? split_env != 0 : (long long)grid.x * grid.y * grid.z <= 2ll * h->sm_count);
+            if (split) { if (legacy) level3_kernel<4, true, true><<<grid, 256, 0, st>>>(a); else level3_kernel<4, false, true><<<grid, 256, 0, st>>>(a); }
+            else if (nw == 8) { if (legacy) level3_kernel<8, true><<<grid, 256, 0, st>>>(a); else level3_kernel<8, false><<<grid, 256, 0, st>>>(a); }
             else if (nw == 2) { if (legacy) level3_kernel<2, true><<<grid, 64, 0, st>>>(a); else level3_kernel<2, false><<<grid, 64, 0, st>>>(a); }
             else if (legacy) level3_kernel<4, true><<<grid, 128, 0, st>>>(a);
             else level3_kernel<4, false><<<grid, 128, 0, st>>>(a);

@@ -100,13 +100,16 @@ __device__ __forceinline__ int l3_arc_score(const uint8_t* c)
 }
 
 // LEGACY: the Q8 kernel of OpenCV <= 3.3 sums to 257, so the rounded result needs a clamp (default kernel: it is byte 2 of the sum).
-template <int NW, bool LEGACY>
+// SPLIT (launches of at most a CTA or two per SM: one frame, a stereo pair): the tile keeps its NW row groups but the CTA has 2 * NW
+// warps - warps 0 .. NW-1 run the FAST reject while warps NW .. 2NW-1 run blur + resize on the same staged tile, and all 2 * NW share
+// the scoring and the NMS.  Same results; the tile's serial chain is about 40 % shorter, which is what a lone CTA per SM is bound by.
+template <int NW, bool LEGACY, bool SPLIT = false>
 #ifndef L3_MINB
 #define L3_MINB 8
 #endif
-__global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) level3_kernel(const __grid_constant__ Level3Args a)
+__global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) ? L3_MINB / 2 : L3_MINB) level3_kernel(const __grid_constant__ Level3Args a)
 {
-    constexpr int TH = L3_RG * NW, SMH = TH + 8, SCH = TH + 2, NT = 32 * NW;
+    constexpr int TH = L3_RG * NW, SMH = TH + 8, SCH = TH + 2, NWT = SPLIT ? 2 * NW : NW, NT = 32 * NWT;
     constexpr int QCAP = SCH * 122;                      // every scored pixel a candidate (uniform-noise images)
     constexpr unsigned FULL = 0xffffffffu;
     __shared__ __align__(128) uint32_t tws[(SMH + NW - 2) * L3_SP];   // tile + halo, 4 pixels per word (TMA destination: SMH rows); the
@@ -116,7 +119,9 @@ __global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) leve
     __shared__ uint16_t queue[QCAP];
     __shared__ int s_qn;
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, wraw = tid >> 5;
+    const int warp = SPLIT ? (wraw & (NW - 1)) : wraw;       // row group of this warp
+    const bool role_fast = !SPLIT || wraw < NW, role_blur = !SPLIT || wraw >= NW;
     const int f = blockIdx.z;
     const int x0 = blockIdx.x * L3_TWPX, y0 = blockIdx.y * TH;
     const uint8_t* __restrict__ src = a.src + (long long)f * a.src_fstride;
@@ -152,7 +157,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) leve
         const bool ytop = y0 < 4, ybot = y0 + TH + 4 > a.h, xl = x0 < 4, xr = x0 + L3_TWPX + 4 > a.w;
         if (ytop || ybot || xl || xr) {                           // block-uniform: border tile
             if (ytop || ybot) {                                   // rows outside the image <- their mirror rows (which are inside)
-                for (int r = warp; r < SMH; r += NW) {
+                for (int r = wraw; r < SMH; r += NWT) {
                     const int gy = y0 - 4 + r;
                     if (gy < 0 || gy >= a.h) {
                         const int rs = min(max(l3_reflect101(gy, a.h) - (y0 - 4), 0), SMH - 1);
@@ -190,14 +195,17 @@ __global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) leve
         unsigned v[RPW];
 #pragma unroll
         for (int i = 0; i < RPW; i++) {
+            if (SPLIT && wraw >= NW) break;                       // the first NW warps stage the tile
             const uint8_t* row = src + (unsigned)l3_reflect101(y0 - 4 + warp + NW * i, a.h) * pitch;
             unsigned vw = 0;
             if (word_ok) vw = *reinterpret_cast<const uint32_t*>(row + xw);
             const unsigned vb = (unsigned)row[xb0] | ((unsigned)row[xb1] << 8) | ((unsigned)row[xb2] << 16) | ((unsigned)row[xb3] << 24);
             v[i] = inside ? vw : (bytes ? vb : 0u);
         }
+        if (!SPLIT || wraw < NW) {
 #pragma unroll
-        for (int i = 0; i < RPW; i++) tw[(warp + NW * i) * L3_SP + lane] = v[i];
+            for (int i = 0; i < RPW; i++) tw[(warp + NW * i) * L3_SP + lane] = v[i];
+        }
         __syncthreads();
     }
 
@@ -205,7 +213,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) leve
     const bool rows_live = y0 + ry0 < a.h;
 
     // ---- 2. blur: vertical pass on u16x2 pairs (even pixels | odd pixels), horizontal pass with IDP.2A ----
-    if (rows_live) {
+    if (rows_live && role_blur) {
         unsigned E[14], O[14];
 #pragma unroll
         for (int i = 0; i < 14; i++) {
@@ -246,7 +254,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) leve
     // ---- 3. bilinear resize: lane = one destination word whose first source column lies in this tile; the warp walks the 9
     //         staged source rows of its group once (horizontal pass per source row, unrolled), emitting a destination row
     //         whenever its two source rows are at hand ----
-    if (a.dst && rows_live) {
+    if (a.dst && rows_live && role_blur) {
         uint8_t* __restrict__ dst = a.dst + (long long)f * a.dst_fstride;
         const int k0 = a.xws[blockIdx.x], k1 = a.xws[blockIdx.x + 1];
         const int g8 = (y0 + ry0) >> 3;
@@ -290,7 +298,7 @@ __global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) leve
 
     // ---- 4. FAST quick reject on words -> warp-compacted candidate queue; score rows -1 .. TH of the tile ----
     const bool fast_tile = a.fast_on && (x0 + L3_TWPX >= 19) && (x0 - 1 <= a.w - 20) && (y0 + TH >= 19) && (y0 - 1 <= a.h - 20);
-    if (fast_tile) {
+    if (fast_tile && role_fast) {
         // Conservative threshold t' = 2^k - 1 <= minTh (exact for the usual minTh = 7): |d| > t'  <=>  (|d| & ~t') != 0, so the
         // OR of two ring differences is tested with one mask; nz(x) = bit 7 of (x >> 1) + (0x80 - 2^(k-1)) for x with k low zero bits.
         const unsigned M = a.qmask, C = a.qadd;
@@ -372,8 +380,8 @@ __global__ void __launch_bounds__(32 * NW, NW == 8 ? L3_MINB / 2 : L3_MINB) leve
     // ---- 5. exact arc score of the queued pixels.  Each warp owns a contiguous chunk of the queue and compacts the entries that
     //         survive (owned pixel, score above minTh) to the front of its own chunk: warp-level sync only. ----
     const int qn = s_qn;
-    const int chunk = (qn + NW - 1) / NW;
-    const int cbeg = warp * chunk, cend = min(qn, cbeg + chunk);
+    const int chunk = (qn + NWT - 1) / NWT;
+    const int cbeg = wraw * chunk, cend = min(qn, cbeg + chunk);
     int wcnt = 0;
     for (int j0 = cbeg; j0 < cend; j0 += 32) {
         const int j = j0 + lane;
