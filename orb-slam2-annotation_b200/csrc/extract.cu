@@ -149,6 +149,7 @@ struct orbx_handle {
     cudaGraphExec_t graph_exec = nullptr;
     int graph_frames = 0, graph_kernels = 0;
     cudaEvent_t ev_fork = nullptr, ev_join[7] = {};           // chunked device-resident batches
+    cudaEvent_t ev_fan[ORBB_MAX_LEVELS] = {};                  // latency mode: one octree stream per level, joined before the descriptors
 };
 
 static void level_sizes(const orbx_handle* h, int w, int ht, int* lw, int* lh)
@@ -474,6 +475,7 @@ extern "C" int orbx_destroy(orbx_handle* h)
     }
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     for (cudaEvent_t e : h->ev_join) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->ev_fan) if (e) cudaEventDestroy(e);
     if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -508,7 +510,13 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
     // the octree of a level only needs that level's FAST records: it runs beside the next levels' kernels (not while profiling:
     // the per-kernel-class event times are taken with the classes back to back).  Even and odd levels use two side streams, so
     // a long octree (level 0 of a large frame, few frames per launch) does not hold up the octrees of the levels after it.
-    const bool overlap = h->oct_overlap && side_octree && !h->profiling;
+    // Latency mode (one frame, a stereo pair: at most two level-0 CTAs per SM): every level's octree gets a stream of its own, so that
+    // only the LAST level's (small) octree is left on the critical path behind the resize chain (ORBB_OCT_FAN = 0 switches it off)
+    static const bool fan_on = getenv("ORBB_OCT_FAN") ? atoi(getenv("ORBB_OCT_FAN")) != 0 : true;
+    const bool fan = fan_on && slot == 0 && h->oct_overlap && !h->profiling && nl <= 16 &&
+                     (long long)ceil_div(h->geom[0].w, L3_TWPX) * ceil_div(h->geom[0].h, h->l3_warps * L3_RG) * nframes <= 2ll * h->sm_count;
+    const bool overlap = (h->oct_overlap && side_octree && !h->profiling) || fan;
+    if (fan) for (int l = 0; l < nl; l++) if (!h->ev_fan[l]) ORBB_CUDA(cudaEventCreateWithFlags(&h->ev_fan[l], cudaEventDisableTiming));
     while ((int)h->ev_lvl[slot].size() < nl) {
         cudaEvent_t e;
         ORBB_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -597,7 +605,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             ORBB_LAUNCHED();
         }
         if (overlap) {
-            cudaStream_t sl = (l & 1) ? side2 : side;
+            cudaStream_t sl = fan ? (l < 8 ? h->s_side[l] : h->s_side2[l - 8]) : ((l & 1) ? side2 : side);
             ORBB_CUDA(cudaEventRecord(h->ev_lvl[slot][l], st));
             ORBB_CUDA(cudaStreamWaitEvent(sl, h->ev_lvl[slot][l], 0));
             oa.level0 = l;
@@ -611,6 +619,11 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
     if (!overlap) {
         octree_kernel<<<dim3(nl, nframes), NTO, 0, st>>>(oa);
         ORBB_LAUNCHED();
+    } else if (fan) {
+        for (int l = 0; l < nl; l++) {
+            ORBB_CUDA(cudaEventRecord(h->ev_fan[l], l < 8 ? h->s_side[l] : h->s_side2[l - 8]));
+            ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_fan[l], 0));
+        }
     } else {
         ORBB_CUDA(cudaEventRecord(h->ev_side[slot], side));
         ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_side[slot], 0));
