@@ -590,7 +590,17 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             // throughput - twice the warps per tile, FAST reject beside blur + resize (ORBB_L3_SPLIT = 0 | 1 forces the choice)
             static const int split_env = getenv("ORBB_L3_SPLIT") ? atoi(getenv("ORBB_L3_SPLIT")) : -1;
             const bool split = nw == 4 && (split_env >= 0 ? split_env != 0 : (long long)grid.x * grid.y * grid.z <= 2ll * h->sm_count);
-            if (split) { if (legacy) level3_kernel<4, true, true><<<grid, 256, 0, st>>>(a); else level3_kernel<4, false, true><<<grid, 256, 0, st>>>(a); }
+            if (split) {
+                // levels >= 1 follow their source level by programmatic dependent launch: launch latency and prologue leave the chain
+                static const bool pdl_on = getenv("ORBB_L3_PDL") ? atoi(getenv("ORBB_L3_PDL")) != 0 : true;
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = grid; cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
+                cfg.attrs = at; cfg.numAttrs = (pdl_on && l > 0) ? 1 : 0;
+                if (legacy) ORBB_CUDA(cudaLaunchKernelEx(&cfg, level3_kernel<4, true, true>, a));
+                else ORBB_CUDA(cudaLaunchKernelEx(&cfg, level3_kernel<4, false, true>, a));
+            }
             else if (nw == 8) { if (legacy) level3_kernel<8, true><<<grid, 256, 0, st>>>(a); else level3_kernel<8, false><<<grid, 256, 0, st>>>(a); }
             else if (nw == 2) { if (legacy) level3_kernel<2, true><<<grid, 64, 0, st>>>(a); else level3_kernel<2, false><<<grid, 64, 0, st>>>(a); }
             else if (legacy) level3_kernel<4, true><<<grid, 128, 0, st>>>(a);

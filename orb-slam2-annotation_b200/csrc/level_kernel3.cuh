@@ -130,10 +130,14 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
     uint32_t* const tw = tws + cb;                          // tile word (r, c) = tw[r * L3_SP + c]
     const uint8_t* tb = reinterpret_cast<const uint8_t*>(tw);
     if (tid == 0) s_qn = 0;
+    // SPLIT launches are chained by programmatic dependent launch: the next level's CTAs may become resident now and run their prologue;
+    // they wait below, before the first read of this kernel's output (no-ops when the launch carries no such attribute)
+    if (SPLIT) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
 #pragma unroll
     for (int i = 0; i < (SCH * L3_SCP / 16 + NT - 1) / NT; i++)                                  // visible after the next barrier
         if (i * NT + tid < SCH * L3_SCP / 16) reinterpret_cast<uint4*>(sc)[i * NT + tid] = make_uint4(0u, 0u, 0u, 0u);
+    if (SPLIT) asm volatile("griddepcontrol.wait;" ::: "memory");      // the previous level (this level's source image) is complete and visible
 
     // ---- 1. stage tile + halo (128 bytes x SMH rows, lane = word column).  Normal case: ONE bulk tensor copy (TMA) issued by
     //         thread 0 lands the box [(x0-4) & ~15, +144) x [y0-4, y0+TH+4) of frame f in shared memory (out-of-image bytes arrive as
