@@ -107,6 +107,7 @@ struct orbx_handle {
     float scale[ORBB_MAX_LEVELS], inv_scale[ORBB_MAX_LEVELS], sigma2[ORBB_MAX_LEVELS], inv_sigma2[ORBB_MAX_LEVELS];
     int per_level[ORBB_MAX_LEVELS], umax[16];
     int q[7];
+    int l3_ow[ORBB_MAX_LEVELS];   // owned words per tile row of each level: 30 (120-pixel tiles) or 32 (128-pixel tiles, where that saves a tile column)
     int l3_warps = 4;          // warps per level-kernel CTA (tile = 120 x 8*warps pixels); ORBB_L3_WARPS = 2 | 4 | 8
     bool l3_warps_forced = false;
     int sm_count = 148;
@@ -227,10 +228,17 @@ static int setup_geometry(orbx_handle* h, int w, int ht, bool allocate_only)
         h->cell_off[l] = (long long)cell; cell += align_up((size_t)nCols * nRows + 16, 16);
         g.scale = h->scale[l];
         g.size = (float)(int)(31 * h->scale[l]);              // ORBextractor.cpp:847
+        {   // 128-pixel tiles where they save a tile column (640 -> 5 instead of 6), else the cheaper 120-pixel tiles; ORBB_L3_OW = 30 | 32 forces one
+            static const int ow_env = getenv("ORBB_L3_OW") ? atoi(getenv("ORBB_L3_OW")) : 0;
+            int ow = ceil_div(g.w, 128) < ceil_div(g.w, 120) ? 32 : 30;
+            if (ow_env == 30 || ow_env == 32) ow = ow_env;
+            if (h->l3_warps != 4) ow = 30;
+            h->l3_ow[l] = ow;
+        }
         if (l + 1 < h->nlevels) {
             g.xt_off = (int)tab; tab += align_up((size_t)lw[l + 1], 4);
             g.yt_off = (int)tab; tab += align_up((size_t)lh[l + 1], 4);      // keeps every xt 16-byte aligned (int4 loads)
-            g.dxs_off = (int)tile; tile += ceil_div(g.w, L3_TWPX) + 1;
+            g.dxs_off = (int)tile; tile += ceil_div(g.w, 4 * 30) + 1;       // (room for the narrower tile's count)
             g.dys_off = (int)tile; tile += ceil_div(g.h, L3_RG) + 1;
         }
     }
@@ -258,7 +266,8 @@ static int upload_geometry(orbx_handle* h)
         const LevelGeom& g = h->geom[l];
         const LevelGeom& n = h->geom[l + 1];
         // x: a tile column owns the destination WORDS whose first source column is in [x0 - 2, x0 + 118)
-        build_axis_table(g.w, n.w, (int)align_up((size_t)n.w, 4), tab.data() + g.xt_off, L3_TWPX, 2, 4, tiles.data() + g.dxs_off, ceil_div(g.w, L3_TWPX));
+        const int twpx = 4 * h->l3_ow[l];
+        build_axis_table(g.w, n.w, (int)align_up((size_t)n.w, 4), tab.data() + g.xt_off, twpx, 2, 4, tiles.data() + g.dxs_off, ceil_div(g.w, twpx));
         // y: an 8-row group owns the destination rows whose (upper) source row lies in it
         build_axis_table(g.h, n.h, n.h, tab.data() + g.yt_off, L3_RG, 0, 1, tiles.data() + g.dys_off, ceil_div(g.h, L3_RG));
     }
@@ -325,7 +334,7 @@ static tmap_encode_fn get_tmap_encode()
 
 // Level image as a 3-D u8 tensor (x, y, frame) with a 144 B x box_rows x 1 box.  Returns false when the layout cannot be
 // described (base or strides not 16-byte aligned): the kernel then stages its tile with ordinary loads.
-static bool encode_level_tmap(CUtensorMap* tm, const uint8_t* base, int w, int ht, int nframes, size_t pitch, size_t fstride, int box_rows)
+static bool encode_level_tmap(CUtensorMap* tm, const uint8_t* base, int w, int ht, int nframes, size_t pitch, size_t fstride, int box_rows, int box_bytes = 144)
 {
     static const bool off = getenv("ORBB_NO_TMA") != nullptr;
     tmap_encode_fn enc = get_tmap_encode();
@@ -334,7 +343,7 @@ static bool encode_level_tmap(CUtensorMap* tm, const uint8_t* base, int w, int h
     if (fstride & 15) return false;
     const cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)ht, (cuuint64_t)(nframes > 0 ? nframes : 1)};
     const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)fstride};
-    const cuuint32_t box[3] = {144u, (cuuint32_t)box_rows, 1u};             // 128 B tile + halo, start rounded down to 16 B
+    const cuuint32_t box[3] = {(cuuint32_t)box_bytes, (cuuint32_t)box_rows, 1u};   // tile + halo, start rounded down to 16 B: 144 B (120-pixel tiles) or 160 B (128)
     const cuuint32_t estr[3] = {1u, 1u, 1u};
     return enc(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -514,7 +523,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
     // only the LAST level's (small) octree is left on the critical path behind the resize chain (ORBB_OCT_FAN = 0 switches it off)
     static const bool fan_on = getenv("ORBB_OCT_FAN") ? atoi(getenv("ORBB_OCT_FAN")) != 0 : true;
     const bool fan = fan_on && slot == 0 && h->oct_overlap && !h->profiling && nl <= 16 &&
-                     (long long)ceil_div(h->geom[0].w, L3_TWPX) * ceil_div(h->geom[0].h, h->l3_warps * L3_RG) * nframes <= 2ll * h->sm_count;
+                     (long long)ceil_div(h->geom[0].w, 4 * h->l3_ow[0]) * ceil_div(h->geom[0].h, h->l3_warps * L3_RG) * nframes <= 2ll * h->sm_count;
     const bool overlap = (h->oct_overlap && side_octree && !h->profiling) || fan;
     if (fan) for (int l = 0; l < nl; l++) if (!h->ev_fan[l]) ORBB_CUDA(cudaEventCreateWithFlags(&h->ev_fan[l], cudaEventDisableTiming));
     while ((int)h->ev_lvl[slot].size() < nl) {
@@ -558,7 +567,8 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
         a.status = d_status;
         const int nw = h->l3_warps;          // (half-height tiles, ORBB_L3_WARPS=2, do not shorten a single frame's chain: 209 vs 207 us; neither does building the
                                              //  pyramid first with a light resize kernel and running the levels side by side on eight streams: 242 vs 179 us)
-        a.use_tma = encode_level_tmap(&a.tmap, a.src, g.w, g.h, nframes, (size_t)a.src_pitch, (size_t)a.src_fstride, 8 * nw + 8) ? 1 : 0;
+        const int ow = h->l3_ow[l];
+        a.use_tma = encode_level_tmap(&a.tmap, a.src, g.w, g.h, nframes, (size_t)a.src_pitch, (size_t)a.src_fstride, 8 * nw + 8, 4 * l3_sp(ow)) ? 1 : 0;
         a.blur = d_blur + g.off; a.blur_pitch = g.pitch; a.blur_fstride = (long long)h->pyr_fstride;
         const bool has_next = l + 1 < nl;
         // the fused resize needs the 4 source columns of a destination word inside the 4-pixel halo: scale <= 1.25
@@ -585,7 +595,7 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             else { a.qmask = 0; a.qadd = 0x80808080u; }           // every valid pixel passes
         }
         {
-            dim3 grid(ceil_div(g.w, L3_TWPX), ceil_div(g.h, nw * L3_RG), nframes);
+            dim3 grid(ceil_div(g.w, 4 * ow), ceil_div(g.h, nw * L3_RG), nframes);
             // at most two CTAs per SM in the whole launch (one frame, a stereo pair): the level is bound by the serial chain of a tile, not by
             // throughput - twice the warps per tile, FAST reject beside blur + resize (ORBB_L3_SPLIT = 0 | 1 forces the choice)
             static const int split_env = getenv("ORBB_L3_SPLIT") ? atoi(getenv("ORBB_L3_SPLIT")) : -1;
@@ -598,9 +608,13 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
                 cudaLaunchAttribute at[1];
                 at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[0].val.programmaticStreamSerializationAllowed = 1;
                 cfg.attrs = at; cfg.numAttrs = (pdl_on && l > 0) ? 1 : 0;
-                if (legacy) ORBB_CUDA(cudaLaunchKernelEx(&cfg, level3_kernel<4, true, true>, a));
+                if (ow == 32) {
+                    if (legacy) ORBB_CUDA(cudaLaunchKernelEx(&cfg, level3_kernel<4, true, true, 32>, a));
+                    else ORBB_CUDA(cudaLaunchKernelEx(&cfg, level3_kernel<4, false, true, 32>, a));
+                } else if (legacy) ORBB_CUDA(cudaLaunchKernelEx(&cfg, level3_kernel<4, true, true>, a));
                 else ORBB_CUDA(cudaLaunchKernelEx(&cfg, level3_kernel<4, false, true>, a));
             }
+            else if (ow == 32) { if (legacy) level3_kernel<4, true, false, 32><<<grid, 128, 0, st>>>(a); else level3_kernel<4, false, false, 32><<<grid, 128, 0, st>>>(a); }
             else if (nw == 8) { if (legacy) level3_kernel<8, true><<<grid, 256, 0, st>>>(a); else level3_kernel<8, false><<<grid, 256, 0, st>>>(a); }
             else if (nw == 2) { if (legacy) level3_kernel<2, true><<<grid, 64, 0, st>>>(a); else level3_kernel<2, false><<<grid, 64, 0, st>>>(a); }
             else if (legacy) level3_kernel<4, true><<<grid, 128, 0, st>>>(a);

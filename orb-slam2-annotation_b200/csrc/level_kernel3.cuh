@@ -20,14 +20,21 @@
 
 namespace orbb {
 
-constexpr int L3_LANES = 32;                 // staged word columns: halo word | 30 owned words | halo word
-constexpr int L3_OWNW = 30;                  // owned words per tile row
+constexpr int L3_LANES = 32;                 // OW = 30: staged word columns halo word | 30 owned words | halo word, one per lane
+constexpr int L3_OWNW = 30;                  // owned words per tile row (default tile)
 constexpr int L3_TWPX = 4 * L3_OWNW;         // 120 owned pixels per tile row
 constexpr int L3_RG = 8;                     // rows per warp
-constexpr int L3_SP = 36;                    // shared tile pitch in words: the TMA box is 144 B wide because its first column must
-                                             // be 16-byte aligned in global memory; tile word (r, c) sits at r*36 + cb + c, cb = 1 or 3
-constexpr int L3_SPB = 4 * L3_SP;            // ... in bytes
-constexpr int L3_SCP = 128;                  // score map pitch (byte column = staged tile byte column)
+// Tile width variants (template parameter OW = owned words per tile row):
+//   OW = 30: 120-pixel tiles, lane l <-> staged word l (lanes 0 and 31 carry the halo words), shared pitch 36 words (the TMA box is
+//            144 B wide because its first column must be 16-byte aligned in global memory; tile word c sits at cb + 1 + c, cb = 1 or 3).
+//   OW = 32: 128-pixel tiles, lane l <-> owned word l, the two halo words (and the FAST ring pixels -1 and 128) are handled by small
+//            extra passes; shared pitch 40 words (box 160 B).  Chosen by the host for the levels where it saves a tile column
+//            (640 -> 5 instead of 6, 370 -> 3 instead of 4).  Measured (512 C1 frames): level 0 0.488 -> 0.467 ms, level 3 0.226 ->
+//            0.219 ms - a full 128-pixel tile costs about 10 % more than a 120-pixel one, and the partly filled last column it
+//            removes was cheap in the candidate-dependent phases, so the level sequence gains 1.5 %, not the 7 % the lane count suggests.
+__host__ __device__ constexpr int l3_sp(int ow) { return ow == 32 ? 40 : 36; }           // shared tile pitch in words
+__host__ __device__ constexpr int l3_scp(int ow) { return ow == 32 ? 136 : 128; }        // score map pitch in bytes (byte column = staged tile byte column)
+__host__ __device__ constexpr int l3_scp_shift(int ow) { return ow == 32 ? 8 : 7; }      // queue entries are (score-map row << shift) | byte column
 
 struct Level3Args {
     CUtensorMap tmap;        // level L as a 3-D tensor (x, y, frame), box 144 B x (tile rows + 8) x 1; valid when use_tma
@@ -69,9 +76,9 @@ __device__ __forceinline__ int l3_reflect101(int p, int n)
 // Threshold-independent FAST arc score m = max over the 16 arcs of 9 contiguous ring pixels of
 // max(min(v - p_k), min(p_k - v)); cv::FAST's response is m - 1 and a pixel is a corner at threshold t iff m > t.
 // Both polarities ride in one register as biased u16 halves: lo = 256 + v - p_k, hi = 256 - v + p_k.
+template <int P>
 __device__ __forceinline__ int l3_arc_score(const uint8_t* c)
 {
-    constexpr int P = L3_SPB;
     const unsigned v = c[0];
     const unsigned av = (256u + v) + ((256u - v) << 16);
     unsigned X[16];
@@ -103,14 +110,17 @@ __device__ __forceinline__ int l3_arc_score(const uint8_t* c)
 // SPLIT (launches of at most a CTA or two per SM: one frame, a stereo pair): the tile keeps its NW row groups but the CTA has 2 * NW
 // warps - warps 0 .. NW-1 run the FAST reject while warps NW .. 2NW-1 run blur + resize on the same staged tile, and all 2 * NW share
 // the scoring and the NMS.  Same results; the tile's serial chain is about 40 % shorter, which is what a lone CTA per SM is bound by.
-template <int NW, bool LEGACY, bool SPLIT = false>
+template <int NW, bool LEGACY, bool SPLIT = false, int OW = 30>
 #ifndef L3_MINB
 #define L3_MINB 8
 #endif
 __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) ? L3_MINB / 2 : L3_MINB) level3_kernel(const __grid_constant__ Level3Args a)
 {
     constexpr int TH = L3_RG * NW, SMH = TH + 8, SCH = TH + 2, NWT = SPLIT ? 2 * NW : NW, NT = 32 * NWT;
-    constexpr int QCAP = SCH * 122;                      // every scored pixel a candidate (uniform-noise images)
+    constexpr int L3_SP = l3_sp(OW), L3_SPB = 4 * L3_SP, L3_SCP = l3_scp(OW), SCSH = l3_scp_shift(OW), TWPX = 4 * OW;
+    constexpr int L3_TWPX = TWPX, L3_OWNW = OW;          // (shadow the namespace constants of the default tile)
+    constexpr int NSW = OW + 2;                          // staged words per row that are used
+    constexpr int QCAP = SCH * (TWPX + 2);               // every scored pixel a candidate (uniform-noise images)
     constexpr unsigned FULL = 0xffffffffu;
     __shared__ __align__(128) uint32_t tws[(SMH + NW - 2) * L3_SP];   // tile + halo, 4 pixels per word (TMA destination: SMH rows); the
                                                                       // FAST row window of the last warp reads NW - 2 rows past it (masked)
@@ -118,10 +128,12 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
     __shared__ __align__(16) uint8_t sc[SCH * L3_SCP];   // arc scores (> minTh) of the tile's pixels + 1-px ring
     __shared__ uint16_t queue[QCAP];
     __shared__ int s_qn;
+    __shared__ uint2 hsum[OW == 32 ? NW * L3_RG * 2 : 1];  // OW = 32: vertical blur sums (even | odd pairs) of the two halo words, [row][side]
 
     const int tid = threadIdx.x, lane = tid & 31, wraw = tid >> 5;
     const int warp = SPLIT ? (wraw & (NW - 1)) : wraw;       // row group of this warp
     const bool role_fast = !SPLIT || wraw < NW, role_blur = !SPLIT || wraw >= NW;
+    const int lw = OW == 32 ? lane + 1 : lane;               // index of this lane's word in a staged row (0 = the left halo word)
     const int f = blockIdx.z;
     const int x0 = blockIdx.x * L3_TWPX, y0 = blockIdx.y * TH;
     const uint8_t* __restrict__ src = a.src + (long long)f * a.src_fstride;
@@ -166,6 +178,7 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
                     if (gy < 0 || gy >= a.h) {
                         const int rs = min(max(l3_reflect101(gy, a.h) - (y0 - 4), 0), SMH - 1);
                         tw[r * L3_SP + lane] = tw[rs * L3_SP + lane];
+                        if (OW == 32 && lane < 2) tw[r * L3_SP + 32 + lane] = tw[rs * L3_SP + 32 + lane];
                     }
                 }
                 __syncthreads();
@@ -178,7 +191,7 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
 #pragma unroll
                         for (int b = 0; b < 4; b++) {                                                     // pixels w..w+3 <- w-2 .. w-5
                             const int di = a.w + b - (x0 - 4), si = l3_reflect101(a.w + b, a.w) - (x0 - 4);
-                            if (di >= 0 && di < 128) tbw[r * L3_SPB + di] = tbw[r * L3_SPB + max(si, 0)];
+                            if (di >= 0 && di < 4 * NSW) tbw[r * L3_SPB + di] = tbw[r * L3_SPB + max(si, 0)];
                         }
                     }
                 }
@@ -188,27 +201,31 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
     } else {
         constexpr int RPW = SMH / NW;                             // staged rows per warp (SMH is a multiple of NW)
         const bool word_ok = ((a.src_pitch & 3) == 0) && ((reinterpret_cast<unsigned long long>(src) & 3) == 0);
-        const int gx = x0 - 4 + 4 * lane;
-        const bool inside = word_ok && gx >= 0 && gx + 3 < a.w;
-        const bool bytes = !inside && gx < a.w + 4;               // edge lanes: 4 reflected byte loads per row
         const unsigned pitch = (unsigned)a.src_pitch;             // one frame is < 4 GB: 32-bit offsets
-        // every lane issues the same loads from a safe address and selects afterwards, so the loads go out back to back
-        const unsigned xw = inside ? (unsigned)gx : 0u;
-        const unsigned xb0 = bytes ? l3_reflect101(gx, a.w) : 0, xb1 = bytes ? l3_reflect101(gx + 1, a.w) : 0;
-        const unsigned xb2 = bytes ? l3_reflect101(gx + 2, a.w) : 0, xb3 = bytes ? l3_reflect101(gx + 3, a.w) : 0;
-        unsigned v[RPW];
+        // staged word column `col` of the rows warp, warp + NW, ...: every lane issues the same loads from a safe address and selects
+        // afterwards, so the loads go out back to back
+        auto stage_col = [&](int col) {
+            const int gx = x0 - 4 + 4 * col;
+            const bool inside = word_ok && gx >= 0 && gx + 3 < a.w;
+            const bool bytes = !inside && gx < a.w + 4;           // edge lanes: 4 reflected byte loads per row
+            const unsigned xw = inside ? (unsigned)gx : 0u;
+            const unsigned xb0 = bytes ? l3_reflect101(gx, a.w) : 0, xb1 = bytes ? l3_reflect101(gx + 1, a.w) : 0;
+            const unsigned xb2 = bytes ? l3_reflect101(gx + 2, a.w) : 0, xb3 = bytes ? l3_reflect101(gx + 3, a.w) : 0;
+            unsigned v[RPW];
 #pragma unroll
-        for (int i = 0; i < RPW; i++) {
-            if (SPLIT && wraw >= NW) break;                       // the first NW warps stage the tile
-            const uint8_t* row = src + (unsigned)l3_reflect101(y0 - 4 + warp + NW * i, a.h) * pitch;
-            unsigned vw = 0;
-            if (word_ok) vw = *reinterpret_cast<const uint32_t*>(row + xw);
-            const unsigned vb = (unsigned)row[xb0] | ((unsigned)row[xb1] << 8) | ((unsigned)row[xb2] << 16) | ((unsigned)row[xb3] << 24);
-            v[i] = inside ? vw : (bytes ? vb : 0u);
-        }
-        if (!SPLIT || wraw < NW) {
+            for (int i = 0; i < RPW; i++) {
+                const uint8_t* row = src + (unsigned)l3_reflect101(y0 - 4 + warp + NW * i, a.h) * pitch;
+                unsigned vw = 0;
+                if (word_ok) vw = *reinterpret_cast<const uint32_t*>(row + xw);
+                const unsigned vb = (unsigned)row[xb0] | ((unsigned)row[xb1] << 8) | ((unsigned)row[xb2] << 16) | ((unsigned)row[xb3] << 24);
+                v[i] = inside ? vw : (bytes ? vb : 0u);
+            }
 #pragma unroll
-            for (int i = 0; i < RPW; i++) tw[(warp + NW * i) * L3_SP + lane] = v[i];
+            for (int i = 0; i < RPW; i++) tw[(warp + NW * i) * L3_SP + col] = v[i];
+        };
+        if (!SPLIT || wraw < NW) {                                // (SPLIT: the first NW warps stage the tile)
+            stage_col(lane);
+            if (OW == 32 && lane < 2) stage_col(32 + lane);
         }
         __syncthreads();
     }
@@ -218,25 +235,42 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
 
     // ---- 2. blur: vertical pass on u16x2 pairs (even pixels | odd pixels), horizontal pass with IDP.2A ----
     if (rows_live && role_blur) {
+        const unsigned q0 = a.q[0], q1 = a.q[1], q2 = a.q[2], q3 = a.q[3];      // symmetric kernel (checked by the host)
+        if (OW == 32) {
+            // the vertical sums of the two halo words, which no lane owns: lanes 0..15 take one (row, side) each of the warp's 8 rows
+            if (lane < 2 * L3_RG) {
+                const int j = lane >> 1, side = lane & 1;
+                const uint32_t* hp = tw + (ry0 + 1 + j) * L3_SP + (side ? OW + 1 : 0);
+                unsigned e[7], o[7];
+#pragma unroll
+                for (int i = 0; i < 7; i++) { const unsigned w = hp[i * L3_SP]; e[i] = w & 0x00ff00ffu; o[i] = __byte_perm(w, 0u, 0x4341); }
+                hsum[(ry0 + j) * 2 + side] = make_uint2(q3 * e[3] + q2 * (e[2] + e[4]) + q1 * (e[1] + e[5]) + q0 * (e[0] + e[6]),
+                                                        q3 * o[3] + q2 * (o[2] + o[4]) + q1 * (o[1] + o[5]) + q0 * (o[0] + o[6]));
+            }
+            __syncwarp();
+        }
         unsigned E[14], O[14];
 #pragma unroll
         for (int i = 0; i < 14; i++) {
-            const unsigned w = tw[(ry0 + 1 + i) * L3_SP + lane];
+            const unsigned w = tw[(ry0 + 1 + i) * L3_SP + lw];
             E[i] = w & 0x00ff00ffu;
             O[i] = __byte_perm(w, 0u, 0x4341);
         }
-        const unsigned q0 = a.q[0], q1 = a.q[1], q2 = a.q[2], q3 = a.q[3];      // symmetric kernel (checked by the host)
         const unsigned KA = a.kq[0], KB = a.kq[1], KC = a.kq[2], KD = a.kq[3], KE = a.kq[4], KF = a.kq[5], KG = a.kq[6], KH = a.kq[7];
-        const int gx = x0 - 4 + 4 * lane;
-        const bool store_lane = lane >= 1 && lane <= L3_OWNW && gx < a.w;
+        const int gx = x0 - 4 + 4 * lw;
+        const bool store_lane = (OW == 32 || (lane >= 1 && lane <= L3_OWNW)) && gx < a.w;
         uint8_t* __restrict__ bp = a.blur + (long long)f * a.blur_fstride + (long long)(y0 + ry0) * a.blur_pitch + gx;
         const int nrows = store_lane ? min(L3_RG, a.h - (y0 + ry0)) : 0;
 #pragma unroll
         for (int j = 0; j < L3_RG; j++) {
             const unsigned VE = q3 * E[j + 3] + q2 * (E[j + 2] + E[j + 4]) + q1 * (E[j + 1] + E[j + 5]) + q0 * (E[j] + E[j + 6]);
             const unsigned VO = q3 * O[j + 3] + q2 * (O[j + 2] + O[j + 4]) + q1 * (O[j + 1] + O[j + 5]) + q0 * (O[j] + O[j + 6]);
-            const unsigned lE = __shfl_up_sync(FULL, VE, 1), lO = __shfl_up_sync(FULL, VO, 1);
-            const unsigned rE = __shfl_down_sync(FULL, VE, 1), rO = __shfl_down_sync(FULL, VO, 1);
+            unsigned lE = __shfl_up_sync(FULL, VE, 1), lO = __shfl_up_sync(FULL, VO, 1);
+            unsigned rE = __shfl_down_sync(FULL, VE, 1), rO = __shfl_down_sync(FULL, VO, 1);
+            if (OW == 32) {                                          // the edge lanes' outer neighbours are the halo words
+                if (lane == 0) { const uint2 t = hsum[(ry0 + j) * 2]; lE = t.x; lO = t.y; }
+                if (lane == 31) { const uint2 t = hsum[(ry0 + j) * 2 + 1]; rE = t.x; rO = t.y; }
+            }
             // taps: q0..q6 with q4=q2, q5=q1, q6=q0; pairs are (even, odd) = (V0|V2<<16, V1|V3<<16) of the left / own / right word
             unsigned r0 = __dp2a_lo(lO, KA, 32768u); r0 = __dp2a_hi(lE, KA, r0); r0 = __dp2a_lo(VE, KB, r0); r0 = __dp2a_hi(VO, KB, r0);
             unsigned r1 = __dp2a_lo(lE, KC, 32768u); r1 = __dp2a_hi(lO, KC, r1); r1 = __dp2a_lo(VE, KD, r1); r1 = __dp2a_hi(VO, KD, r1);
@@ -307,7 +341,7 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
         // OR of two ring differences is tested with one mask; nz(x) = bit 7 of (x >> 1) + (0x80 - 2^(k-1)) for x with k low zero bits.
         const unsigned M = a.qmask, C = a.qadd;
         // valid bytes of this lane's word: pixels max(19, x0-1) .. min(w-20, x0+120)
-        const int lo = max(19, x0 - 1) - (x0 - 4) - 4 * lane, hi = min(a.w - 20, x0 + L3_TWPX) - (x0 - 4) - 4 * lane;
+        const int lo = max(19, x0 - 1) - (x0 - 4) - 4 * lw, hi = min(a.w - 20, x0 + L3_TWPX) - (x0 - 4) - 4 * lw;
         unsigned valid = 0x80808080u;
         if (lo > 3 || hi < 0) valid = 0;
         else {
@@ -329,7 +363,7 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
         // private candidate flags: byte b of m0 holds rows it = 0..7 of pixel b (bit it), m1 holds row 8 at bit 7 of byte b
         unsigned m0 = 0, m1 = 0;
         if (rowok) {                                              // warp-uniform
-            const uint32_t* rp = tw + (sb + 1) * L3_SP + lane;   // staged row j of the window = tile row sb - 3 + j
+            const uint32_t* rp = tw + (sb + 1) * L3_SP + lw;     // staged row j of the window = tile row sb - 3 + j
             unsigned Vw[7], Aw[7] = {}, Bw[7] = {};              // sliding window: own word, +2-pixel view, -2-pixel view
 #pragma unroll
             for (int j = 0; j < 6; j++) {
@@ -365,16 +399,31 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
         const int n = __popc(m0) + __popc(m1);
         if (n) {
             int slot = atomicAdd(&s_qn, n);
-            const int pbase = (sb + 1) * L3_SCP + 4 * lane;      // position of (row sb, byte 0 of this lane's word)
+            const int pbase = ((sb + 1) << SCSH) + 4 * lw;       // queue code of (row sb, byte 0 of this lane's word)
             while (m0) {                                          // bit t = 8 * byte + it  ->  pbase + it * L3_SCP + byte
                 const int t = __ffs((int)m0) - 1;
                 m0 &= m0 - 1;
-                queue[slot++] = (uint16_t)(pbase + ((t & 7) << 7) + (t >> 3));
+                queue[slot++] = (uint16_t)(pbase + ((t & 7) << SCSH) + (t >> 3));
             }
             while (m1) {                                          // bit t = 8 * byte + 7
                 const int t = __ffs((int)m1) - 1;
                 m1 &= m1 - 1;
-                queue[slot++] = (uint16_t)(pbase + 8 * L3_SCP + (t >> 3));
+                queue[slot++] = (uint16_t)(pbase + (8 << SCSH) + (t >> 3));
+            }
+        }
+        if (OW == 32 && lane < 2 * RPW9) {
+            // the ring pixels -1 and 128 of the warp's 9 rows lie in the halo words: one lane each, the same conservative test on single bytes
+            const int it = lane >> 1, side = lane & 1;
+            const int c = side ? 4 + L3_TWPX : 3;                 // staged byte column
+            const int gxr = x0 - 4 + c;
+            if (((rowok >> it) & 1u) && gxr >= 19 && gxr <= a.w - 20) {
+                const uint8_t* cp = tb + (sb + it + 4) * L3_SPB + c;          // tile row sb + it is staged row sb + it + 4
+                const int tq = (int)((~M) & 0xffu);               // t' (M = 0: minTh = 0, everything passes)
+                const int v = cp[0];
+                auto far = [&](int off) { return abs(v - (int)cp[off]) > tq; };
+                const bool cand = M == 0u || ((far(3 * L3_SPB) || far(-3 * L3_SPB)) && (far(3) || far(-3)) &&
+                                              (far(2 * L3_SPB + 2) || far(-2 * L3_SPB - 2)) && (far(-2 * L3_SPB + 2) || far(2 * L3_SPB - 2)));
+                if (cand) queue[atomicAdd(&s_qn, 1)] = (uint16_t)(((sb + it + 1) << SCSH) + c);
             }
         }
     }
@@ -392,10 +441,10 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
         bool surv = false; int pos = 0;
         if (j < cend) {
             pos = queue[j];
-            const int r = pos >> 7, c = pos & 127;                // score-map row (tile row + 1), staged byte column
-            const int m = l3_arc_score(tb + (r + 3) * L3_SPB + c);
+            const int r = pos >> SCSH, c = pos & ((1 << SCSH) - 1);   // score-map row (tile row + 1), staged byte column
+            const int m = l3_arc_score<L3_SPB>(tb + (r + 3) * L3_SPB + c);
             if (m > a.minTh) {
-                sc[pos] = (uint8_t)m;
+                sc[r * L3_SCP + c] = (uint8_t)m;
                 surv = r >= 1 && r <= TH && c >= 4 && c < 4 + L3_TWPX;     // the ring around the tile is scored for its neighbours only
             }
         }
@@ -414,8 +463,8 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
         bool keep = false; unsigned record = 0;
         if (j < cbeg + wcnt) {
             const int pos = queue[j];
-            const int r = pos >> 7, c = pos & 127;
-            const uint8_t* sp = sc + pos;
+            const int r = pos >> SCSH, c = pos & ((1 << SCSH) - 1);
+            const uint8_t* sp = sc + r * L3_SCP + c;
             const int m = sp[0];
             const int gx = x0 - 4 + c, gy = y0 - 1 + r;
             // position inside the 30-px FAST cell: a neighbour in ANOTHER cell never suppresses (cv::FAST ran per cell)
