@@ -418,3 +418,18 @@ def test_cuda_graph_replay_equals_plain_launches(gpu):
     ex.set_profiling(True)
     assert ex.L.orbx_graph_capture(ex.h, orbb200._p(imgs.data_ptr()), B, W, H, W, W * H, orbb200._p(k.data_ptr()), orbb200._p(d.data_ptr()),
                                    orbb200._p(c.data_ptr()), CAP) == orbb200.E_STATE
+
+
+@pytest.mark.parametrize("env", [{"ORBB_L3_OW": "32"}, {"ORBB_L3_OW": "30"}, {"ORBB_L3_OW": "32", "ORBB_L3_SPLIT": "1"}, {"ORBB_L3_OW": "30", "ORBB_L3_SPLIT": "0"},
+                                 {"ORBB_L3_OW": "32", "ORBB_NO_TMA": "1"}, {"ORBB_OCT_FAN": "0", "ORBB_L3_PDL": "0"}],
+                         ids=lambda e: ",".join(f"{k[5:]}={v}" for k, v in e.items()))
+def test_every_level_kernel_variant(gpu, env):
+    """The level kernel has a tile-width (120 / 128 pixels), a latency (SPLIT + dependent launch + per-level octree streams) and a staging
+    (TMA / ordinary loads) variant; the library picks them per level and per launch.  The knobs are read once per process, so each forced
+    combination runs the stage-by-stage and the final parity tests (single frames, batches, odd shapes, noise) in a process of its own."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_extract.py"), "-m", "gpu", "-x", "-q", "-k",
+                        "stage_parity or final_parity or noise or batch_equals_single or odd_shapes or multi_chunk or graph_replay"],
+                       env={**os.environ, **env}, capture_output=True, text=True, timeout=900, cwd=root)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
