@@ -228,9 +228,12 @@ static int setup_geometry(orbx_handle* h, int w, int ht, bool allocate_only)
         h->cell_off[l] = (long long)cell; cell += align_up((size_t)nCols * nRows + 16, 16);
         g.scale = h->scale[l];
         g.size = (float)(int)(31 * h->scale[l]);              // ORBextractor.cpp:847
-        {   // 128-pixel tiles where they save a tile column (640 -> 5 instead of 6), else the cheaper 120-pixel tiles; ORBB_L3_OW = 30 | 32 forces one
+        {   // 128-pixel tiles where they pay (640 -> 5 instead of 6 columns), else the cheaper 120-pixel tiles; ORBB_L3_OW = 30 | 32 forces one
             static const int ow_env = getenv("ORBB_L3_OW") ? atoi(getenv("ORBB_L3_OW")) : 0;
-            int ow = ceil_div(g.w, 128) < ceil_div(g.w, 120) ? 32 : 30;
+            // measured cost model (512-frame batches): a full 128-pixel tile costs 1.10 of a full 120-pixel one; a partly filled tile
+            // 0.55 + 0.45 x its fill (the candidate-dependent phases scale with the pixels it really holds)
+            auto row_cost = [](int w, int tw) { const int full = w / tw, rem = w % tw; return full + (rem ? 0.55 + 0.45 * rem / tw : 0.0); };
+            int ow = 1.10 * row_cost(g.w, 128) < 0.98 * row_cost(g.w, 120) ? 32 : 30;
             if (ow_env == 30 || ow_env == 32) ow = ow_env;
             if (h->l3_warps != 4) ow = 30;
             h->l3_ow[l] = ow;
@@ -910,20 +913,23 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
     const bool tight = (w % 16) == 0 && (size_t)w * ht <= (size_t)g0.pitch * g0.h;
     const size_t dpitch0 = tight ? (size_t)w : (size_t)g0.pitch;
     const bool packed = tight && (!pinned || (stride == (size_t)w && (nframes == 1 || fstride >= (size_t)w * ht)));
-    if (trace) cudaEventRecord(ev_t0, h->s_in);
+    // one chunk (a single frame, a few frames): copies and kernels on ONE stream - no event hops between the three stages
+    const bool one = nchunks == 1 && !prof && !trace;
+    cudaStream_t sin_ = one ? st : h->s_in, sout_ = one ? st : h->s_out;
+    if (trace) cudaEventRecord(ev_t0, sin_);
     for (int c = 0; c < nchunks; c++) {
         const int f0 = cstart[c], nf = cstart[c + 1] - f0;
         if (staged) {          // colour / raw frames land packed in d_color (pageable sources are staged by the driver)
             const size_t fbytes = (size_t)in_w * in_h * CH_;
             if (stride == (size_t)in_w * CH_ && (nframes == 1 || fstride >= fbytes)) {
                 ORBB_CUDA(cudaMemcpy2DAsync(h->d_color + (size_t)f0 * fbytes, fbytes, imgs_host + (size_t)f0 * fstride,
-                                            nf > 1 ? fstride : fbytes, fbytes, nf, cudaMemcpyHostToDevice, h->s_in));
+                                            nf > 1 ? fstride : fbytes, fbytes, nf, cudaMemcpyHostToDevice, sin_));
             } else {
                 for (int f = f0; f < f0 + nf; f++)
                     ORBB_CUDA(cudaMemcpy2DAsync(h->d_color + (size_t)f * fbytes, (size_t)in_w * CH_, imgs_host + (size_t)f * fstride, stride,
-                                                (size_t)in_w * CH_, in_h, cudaMemcpyHostToDevice, h->s_in));
+                                                (size_t)in_w * CH_, in_h, cudaMemcpyHostToDevice, sin_));
             }
-            ORBB_CUDA(cudaEventRecord(h->ev_in[c], h->s_in));
+            if (!one) ORBB_CUDA(cudaEventRecord(h->ev_in[c], sin_));
             continue;
         }
         if (!pinned) {         // stage through pinned memory so the copy is truly asynchronous
@@ -938,20 +944,20 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
         const size_t cstride = pinned ? stride : (size_t)w, cfstride = pinned ? fstride : (size_t)w * ht;
         if (packed) {
             ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f0 * h->pyr_fstride + g0.off, h->pyr_fstride, cbase + (size_t)f0 * cfstride,
-                                        nf > 1 ? cfstride : (size_t)w * ht, (size_t)w * ht, nf, cudaMemcpyHostToDevice, h->s_in));
+                                        nf > 1 ? cfstride : (size_t)w * ht, (size_t)w * ht, nf, cudaMemcpyHostToDevice, sin_));
         } else {
             for (int f = f0; f < f0 + nf; f++)
                 ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, dpitch0, cbase + (size_t)f * cfstride, cstride, w, ht,
-                                            cudaMemcpyHostToDevice, h->s_in));
+                                            cudaMemcpyHostToDevice, sin_));
         }
-        ORBB_CUDA(cudaEventRecord(h->ev_in[c], h->s_in));
+        if (!one) ORBB_CUDA(cudaEventRecord(h->ev_in[c], sin_));
     }
     // every input copy is queued before the first kernel: the copy engine never waits for the host to finish launching a chunk
     for (int c = 0; c < nchunks && !prof; c++) {
         const int f0 = cstart[c], nf = cstart[c + 1] - f0;
         const int ks = c % h->n_kstreams;
         cudaStream_t kst = ks ? h->s_k[ks - 1] : st;
-        ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
+        if (!one) ORBB_CUDA(cudaStreamWaitEvent(kst, h->ev_in[c], 0));
         if (remap) {
             const size_t fbytes = (size_t)in_w * in_h;
             launch_remap(h->d_color + (size_t)f0 * fbytes, (long long)in_w, (long long)fbytes, in_w, in_h, h->d_map, w, ht,
@@ -965,12 +971,14 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
         }
         const int rc = enqueue_extract(h, h->d_pyr + g0.off, f0, nf, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, ks, false);   // chunks already overlap each other: side octrees only add launches
         if (rc != ORBB_OK) return rc;
-        ORBB_CUDA(cudaEventRecord(h->ev_done[c], kst));
-        ORBB_CUDA(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));
-        ORBB_CUDA(cudaMemcpyAsync(h->h_counts + f0, h->d_counts + f0, sizeof(int) * nf, cudaMemcpyDeviceToHost, h->s_out));
-        ORBB_CUDA(cudaMemcpyAsync(h->h_status + f0, h->d_status + f0, sizeof(int) * nf, cudaMemcpyDeviceToHost, h->s_out));
-        ORBB_CUDA(cudaMemcpyAsync(kdst + (size_t)f0 * devcap, h->d_kps + (size_t)f0 * devcap, sizeof(orbx_keypoint) * (size_t)nf * devcap, cudaMemcpyDeviceToHost, h->s_out));
-        ORBB_CUDA(cudaMemcpyAsync(ddst + (size_t)f0 * devcap * 32, h->d_desc + (size_t)f0 * devcap * 32, (size_t)32 * nf * devcap, cudaMemcpyDeviceToHost, h->s_out));
+        if (!one) {
+            ORBB_CUDA(cudaEventRecord(h->ev_done[c], kst));
+            ORBB_CUDA(cudaStreamWaitEvent(sout_, h->ev_done[c], 0));
+        }
+        ORBB_CUDA(cudaMemcpyAsync(h->h_counts + f0, h->d_counts + f0, sizeof(int) * nf, cudaMemcpyDeviceToHost, sout_));
+        ORBB_CUDA(cudaMemcpyAsync(h->h_status + f0, h->d_status + f0, sizeof(int) * nf, cudaMemcpyDeviceToHost, sout_));
+        ORBB_CUDA(cudaMemcpyAsync(kdst + (size_t)f0 * devcap, h->d_kps + (size_t)f0 * devcap, sizeof(orbx_keypoint) * (size_t)nf * devcap, cudaMemcpyDeviceToHost, sout_));
+        ORBB_CUDA(cudaMemcpyAsync(ddst + (size_t)f0 * devcap * 32, h->d_desc + (size_t)f0 * devcap * 32, (size_t)32 * nf * devcap, cudaMemcpyDeviceToHost, sout_));
     }
     if (prof) {
         ORBB_CUDA(cudaStreamWaitEvent(st, h->ev_in[nchunks - 1], 0));
@@ -993,8 +1001,10 @@ static int extract_batch_impl(orbx_handle* h, const uint8_t* imgs_host, int nfra
         ORBB_CUDA(cudaStreamSynchronize(st));
     }
     if (trace) cudaEventRecord(ev_t1, h->s_out);
-    ORBB_CUDA(cudaStreamSynchronize(h->s_out));
-    for (int i = 0; i < 7; i++) ORBB_CUDA(cudaStreamSynchronize(h->s_k[i]));
+    if (!one) {
+        ORBB_CUDA(cudaStreamSynchronize(h->s_out));
+        for (int i = 0; i < 7; i++) ORBB_CUDA(cudaStreamSynchronize(h->s_k[i]));
+    }
     if (trace && !prof) {
         float t = 0.f, u = 0.f;
         for (int c = 0; c < nchunks; c++) {
