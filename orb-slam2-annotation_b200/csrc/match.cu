@@ -635,17 +635,25 @@ static int bow_join(const uint8_t* desc_a, const uint8_t* has_a, int n_a, const 
     if (entries.empty() || total == 0) return ORBB_OK;
     DevBuf dA, dB, dF, dE, dD;
     const int nfeatB = fb_off[nfb];
-    if ((rc = dA.alloc((size_t)n_a * 32)) || (rc = dB.alloc((size_t)n_b * 32)) || (rc = dF.alloc((size_t)nfeatB * 4)) ||
-        (rc = dE.alloc(entries.size() * sizeof(int4))) || (rc = dD.alloc((size_t)total * 2))) return rc;
-    ORBB_CUDA(cudaMemcpy(dA.p, desc_a, (size_t)n_a * 32, cudaMemcpyHostToDevice));
-    ORBB_CUDA(cudaMemcpy(dB.p, desc_b, (size_t)n_b * 32, cudaMemcpyHostToDevice));
-    ORBB_CUDA(cudaMemcpy(dF.p, fb_feat, (size_t)nfeatB * 4, cudaMemcpyHostToDevice));
-    ORBB_CUDA(cudaMemcpy(dE.p, entries.data(), entries.size() * sizeof(int4), cudaMemcpyHostToDevice));
-    bow_join_kernel<<<ceil_div((int)entries.size(), 8), 256>>>(dA.as<uint4>(), dB.as<uint4>(), dF.as<int>(), dE.as<int4>(), (int)entries.size(),
-                                                               dD.as<uint16_t>());
+    const size_t bA = (size_t)n_a * 32, bB = (size_t)n_b * 32, bF = (size_t)nfeatB * 4, bE = entries.size() * sizeof(int4), bD = (size_t)total * 2;
+    if ((rc = dA.alloc(bA)) || (rc = dB.alloc(bB)) || (rc = dF.alloc(bF)) || (rc = dE.alloc(bE)) || (rc = dD.alloc(bD))) return rc;
+    // one pinned block per call: [desc A | desc B | features of B | entries | distances]; asynchronous copies, one synchronisation
+    uint8_t* pin = t_pin.get(bA + bB + bF + bE + bD + 64);
+    if (!pin) return ORBB_E_NOMEM;
+    uint8_t *pA = pin, *pB = pA + bA, *pF = pB + bB, *pE = pF + bF, *pD = pE + bE;
+    cudaStream_t st = 0;
+    memcpy(pA, desc_a, bA); memcpy(pB, desc_b, bB); memcpy(pF, fb_feat, bF); memcpy(pE, entries.data(), bE);
+    ORBB_CUDA(cudaMemcpyAsync(dA.p, pA, bA, cudaMemcpyHostToDevice, st));
+    ORBB_CUDA(cudaMemcpyAsync(dB.p, pB, bB, cudaMemcpyHostToDevice, st));
+    ORBB_CUDA(cudaMemcpyAsync(dF.p, pF, bF, cudaMemcpyHostToDevice, st));
+    ORBB_CUDA(cudaMemcpyAsync(dE.p, pE, bE, cudaMemcpyHostToDevice, st));
+    bow_join_kernel<<<ceil_div((int)entries.size(), 8), 256, 0, st>>>(dA.as<uint4>(), dB.as<uint4>(), dF.as<int>(), dE.as<int4>(), (int)entries.size(),
+                                                                      dD.as<uint16_t>());
     ORBB_LAUNCHED();
     ORBB_CUDA(cudaGetLastError());
-    ORBB_CUDA(cudaMemcpy(dist.data(), dD.p, (size_t)total * 2, cudaMemcpyDeviceToHost));
+    ORBB_CUDA(cudaMemcpyAsync(pD, dD.p, bD, cudaMemcpyDeviceToHost, st));
+    ORBB_CUDA(cudaStreamSynchronize(st));
+    memcpy(dist.data(), pD, bD);
     return ORBB_OK;
 }
 
