@@ -729,3 +729,41 @@ def test_stereo_frame_create(gpu, w, h, nf, seed):
         orbb200.stereo_frame(orbb200.ORBextractor(nf, max_size=(w, h)), L, R, mbf, (0, 0, w, h))
     with pytest.raises(orbb200.OrbError):
         orbb200.stereo_frame(ex, L, R, mbf, (0, 0, w, h), capacity=len(okL) - 1)
+
+
+def test_stereo_frame_create_degenerate_inputs(gpu):
+    """The fused stereo constructor on images without a single corner (left, right, both), on a non-contiguous (strided) pair and right after
+    a different shape went through the same handle: counts, empty outputs and the searches on an empty frame behave like the separate calls."""
+    import orbb200, pyoracle
+    from synth import synth_stereo
+    w, h, nf = 640, 480, 1000
+    L, R = synth_stereo(w, h, 5)
+    flat = np.full((h, w), 128, np.uint8)
+    ex = orbb200.ORBextractor(nf, max_size=(800, 600), max_batch=2)
+    o = pyoracle.OracleExtractor(nf)
+    okL, odL = o.extract(L)
+    q = _queries(okL, odL, ex.GetScaleFactors(), 15.0, (2, 1), np.random.default_rng(1))
+    m = orbb200.ORBmatcher(0.9, True)
+    for left, right, nl_expected in ((flat, R, 0), (L, flat, len(okL)), (flat, flat, 0)):
+        F, kL, dL, kR, dR, ur, dp = orbb200.stereo_frame(ex, left, right, 40.0, (0, 0, w, h))
+        assert len(kL) == nl_expected and len(ur) == nl_expected and (len(kR) == 0) == (right is flat)
+        if right is flat:
+            assert np.all(ur == -1) and np.all(dp == -1)              # no right keypoints: no stereo match
+        n, mp, ob = m.SearchByProjection_frame(F, q, np.full(len(kL), -1, np.int32), np.zeros(len(kL), np.int32),
+                                               orbb200.URIGHT_OF_FRAME if nl_expected else None)
+        assert (n == 0) == (nl_expected == 0)
+        F.close()
+    # another shape through the same handle, then the first one again: the geometry tables follow
+    L2, R2 = synth_stereo(752, 480, 6)
+    F2, k2, d2, _, _, ur2, _ = orbb200.stereo_frame(ex, L2, R2, 47.9, (0, 0, 752, 480))
+    ok2, od2 = pyoracle.OracleExtractor(nf).extract(L2)
+    assert k2.tobytes() == ok2.tobytes() and np.array_equal(d2, od2)
+    F2.close()
+    F, kL, dL, kR, dR, ur, dp = orbb200.stereo_frame(ex, L, R, 40.0, (0, 0, w, h))
+    assert kL.tobytes() == okL.tobytes() and np.array_equal(dL, odL)
+    oL, oR = pyoracle.OracleExtractor(nf), pyoracle.OracleExtractor(nf)
+    oL.extract(L); oR.extract(R)
+    with np.errstate(divide="ignore"):
+        our, odp, _, _ = pyoracle.stereo_match(oL, oR, 40.0, 0.0)
+    assert np.array_equal(ur, our) and np.array_equal(dp, odp)
+    F.close()
