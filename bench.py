@@ -237,6 +237,29 @@ def measure_latency(local_rank, dev):
            "orbx_extract_pageable_host": timed(call_pageable), "keypoints": 0}
     out["keypoints"] = int(n.value)
     out["orbx_extract_pinned_host"] = timed(call_pinned)
+    # the monocular Frame constructor (Frame.cpp:171-224, TUM1.yaml calibration): member by member, and as one call
+    K4 = (C.c_float * 4)(517.306408, 516.469215, 318.643040, 255.313989)
+    D5 = (C.c_float * 5)(0.262383, -0.953104, -0.005358, 0.002628, 1.163314)
+    b4 = (C.c_float * 4)()
+    assert L.orbm_image_bounds(W, H, K4, D5, 5, b4, local_rank) == 0
+    kun = np.zeros(CAPACITY, orbb200.KP_DTYPE)
+    vp = C.c_void_p
+
+    def ctor_members():
+        call_pageable()
+        assert L.orbm_undistort_keypoints(kps.ctypes.data_as(vp), n.value, K4, D5, 5, kun.ctypes.data_as(vp), local_rank) == 0
+        fh = vp()
+        assert L.orbm_frame_create(C.byref(fh), kun.ctypes.data_as(vp), desc.ctypes.data_as(vp), n.value, b4[0], b4[1], b4[2], b4[3], local_rank) == 0
+        L.orbm_frame_destroy(fh)
+
+    def ctor_one_call():
+        fh = vp()
+        rc = L.orbm_mono_frame_create(ex.h, img.ctypes.data_as(vp), W, H, W, K4, D5, 5, b4[0], b4[1], b4[2], b4[3], C.byref(fh), kps.ctypes.data_as(vp),
+                                      kun.ctypes.data_as(vp), desc.ctypes.data_as(vp), C.byref(n), CAPACITY)
+        assert rc == 0, rc
+        L.orbm_frame_destroy(fh)
+    out["mono_frame_constructor_member_calls"] = timed(ctor_members)
+    out["mono_frame_constructor_one_call"] = timed(ctor_one_call)
     out["device_resident_plain_launches"] = timed(call_device)
     ref_cnt = int(dc.item()); ref_desc = dd.clone()
     ex.graph_capture(dimg.data_ptr(), 1, W, H, W, W * H, dk.data_ptr(), dd.data_ptr(), dc.data_ptr(), CAPACITY)

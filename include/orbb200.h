@@ -330,6 +330,14 @@ int orbm_stereo_frame_create(orbx_handle* h, const uint8_t* left_host, const uin
                              orbx_keypoint* kps_left_host, uint8_t* desc_left_host, int* n_left,
                              orbx_keypoint* kps_right_host, uint8_t* desc_right_host, int* n_right, int capacity,
                              float* u_right_host, float* depth_host);
+/* Frame::Frame, the monocular constructor (Frame.cpp:171-224; the RGB-D constructor :117-169 differs by its depth lookup only), as ONE call:
+ * ExtractORB(0, imGray) (:186), UndistortKeyPoints (:462-496; K4 / dist may be NULL, and dist[0] == 0 means mvKeysUn = mvKeys as at :465-469)
+ * and AssignFeaturesToGrid (:241-257) on the keypoints where the extraction left them.  Out: *out, mvKeys (kps), mvKeysUn (kps_un),
+ * mDescriptors (desc), *n; `capacity` rows per array, ORBB_E_CAPACITY (*n still set) when the image has more keypoints.  Bit-equal to
+ * orbx_extract + orbm_undistort_keypoints + orbm_frame_create (tests/test_gpu_match.py::test_mono_frame_create). */
+int orbm_mono_frame_create(orbx_handle* h, const uint8_t* img_host, int w, int h_, size_t stride_bytes,
+                           const float* K4, const float* dist, int ndist, float min_x, float min_y, float max_x, float max_y,
+                           orbm_frame** out, orbx_keypoint* kps_host, orbx_keypoint* kps_un_host, uint8_t* desc_host, int* n, int capacity);
 /* Pass as mvuRight_host to orbm_search_by_projection_points / _frame on a frame built by orbm_stereo_frame_create: the search uses the
  * mvuRight that constructor left on the device instead of uploading the host copy (ORBB_E_STATE on any other frame). */
 #define ORBM_URIGHT_OF_FRAME ((const float*)(uintptr_t)1)

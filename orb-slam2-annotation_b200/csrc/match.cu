@@ -1017,6 +1017,53 @@ extern "C" int orbm_stereo_frame_create(orbx_handle* h, const uint8_t* left_host
     return ORBB_OK;
 }
 
+// Frame::Frame, monocular constructor (Frame.cpp:171-224; the RGB-D one :117-169 differs by its depth lookup only) as ONE call: ExtractORB(0, imGray),
+// UndistortKeyPoints (:462-496) and AssignFeaturesToGrid (:241-257) on the keypoints where the extraction left them.  K4 / dist may be NULL
+// (or dist[0] == 0, :465): mvKeysUn = mvKeys.
+extern "C" int orbm_mono_frame_create(orbx_handle* h, const uint8_t* img_host, int w, int ht, size_t stride, const float* K4, const float* dist, int ndist,
+                                      float min_x, float min_y, float max_x, float max_y, orbm_frame** out, orbx_keypoint* kps_host,
+                                      orbx_keypoint* kps_un_host, uint8_t* desc_host, int* n_out, int capacity)
+{
+    if (!h || !img_host || !out || !n_out || capacity < 1 || !kps_host || !kps_un_host || !desc_host) return ORBB_E_INVALID;
+    *out = nullptr; *n_out = 0;
+    UndistortArgs ua;
+    const bool undist = K4 && dist && dist[0] != 0.0f;
+    if (undist && undistort_args(K4, dist, ndist, ua) != ORBB_OK) return ORBB_E_INVALID;
+    const uint8_t* imgs[1] = {img_host};
+    int32_t cnt[1] = {0};
+    orbx_resident_view v{};
+    int rc = orbx__extract_resident(h, imgs, 1, w, ht, stride, cnt, &v);
+    if (rc != ORBB_OK) { if (v.s_out) cudaStreamSynchronize((cudaStream_t)v.s_out); return rc; }
+    cudaStream_t st = (cudaStream_t)v.stream, s_out = (cudaStream_t)v.s_out;
+    const int n = cnt[0];
+    *n_out = n;
+    if (n > capacity) { cudaStreamSynchronize(s_out); return ORBB_E_CAPACITY; }
+    const size_t bk = (size_t)n * sizeof(orbx_keypoint);
+    uint8_t* pin = t_pin.get(bk + 16);
+    if (!pin) { cudaStreamSynchronize(s_out); return ORBB_E_NOMEM; }
+    DevBuf un;
+    const orbx_keypoint* kun_dev = v.kps_dev;
+    if (undist && n > 0) {
+        if ((rc = un.alloc(bk))) { cudaStreamSynchronize(s_out); return rc; }
+        undistort_kernel<<<ceil_div(n, 256), 256, 0, st>>>(v.kps_dev, un.as<orbx_keypoint>(), n, ua);
+        ORBB_LAUNCHED();
+        kun_dev = un.as<orbx_keypoint>();
+        if (cudaMemcpyAsync(pin, un.p, bk, cudaMemcpyDeviceToHost, st) != cudaSuccess) { cudaStreamSynchronize(st); cudaStreamSynchronize(s_out); return ORBB_E_CUDA; }
+    }
+    orbm_frame* fr = nullptr;
+    rc = frame_create_impl(&fr, kun_dev, v.desc_dev, n, min_x, min_y, max_x, max_y, v.device, cudaMemcpyDeviceToDevice, st);
+    if (rc != ORBB_OK) { cudaStreamSynchronize(st); cudaStreamSynchronize(s_out); return rc; }
+    cudaError_t e = cudaStreamSynchronize(s_out);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { set_cuda_error(e, "orbm_mono_frame_create"); orbm_frame_destroy(fr); return ORBB_E_CUDA; }
+    if (n > 0) {
+        memcpy(kps_host, v.kps_pinned, bk); memcpy(desc_host, v.desc_pinned, (size_t)n * 32);
+        memcpy(kps_un_host, undist ? (const void*)pin : (const void*)v.kps_pinned, bk);
+    }
+    *out = fr;
+    return ORBB_OK;
+}
+
 // ---- brute-force database ----------------------------------------------------------------------------
 struct orbm_db {
     int device = 0;

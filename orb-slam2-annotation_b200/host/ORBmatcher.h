@@ -57,6 +57,22 @@ public:
         for (int i = 0; i < n_; i++) memcpy(&d[(size_t)i * 32], descriptors.ptr(i), 32);
         orbm_check(orbm_frame_create(&f_, (const orbx_keypoint*)keysUn.data(), d.data(), n_, minX, minY, maxX, maxY, device), "orbm_frame_create");
     }
+    // Frame::Frame, monocular constructor (src/Frame.cpp:171-224) as one device call (orbm_mono_frame_create): ExtractORB(0, imGray),
+    // UndistortKeyPoints and AssignFeaturesToGrid.  distCoef empty or distCoef[0] == 0: mvKeysUn = mvKeys (:465-469).
+    DeviceFrame(ORBextractor& extractor, const cv::Mat& imGray, const float K4[4], const std::vector<float>& distCoef, float minX, float minY, float maxX,
+                float maxY, std::vector<cv::KeyPoint>& mvKeys, std::vector<cv::KeyPoint>& mvKeysUn, cv::Mat& mDescriptors)
+        : f_(nullptr), n_(0)
+    {
+        extractor.Reserve(imGray.cols, imGray.rows);
+        const int cap = extractor.Capacity();
+        int n = 0;
+        mvKeys.resize(cap); mvKeysUn.resize(cap); mDescriptors.create(cap, 32, CV_8U);
+        orbm_check(orbm_mono_frame_create(extractor.Handle(), imGray.ptr(0), imGray.cols, imGray.rows, imGray.step, distCoef.empty() ? nullptr : K4,
+                                          distCoef.empty() ? nullptr : distCoef.data(), (int)distCoef.size(), minX, minY, maxX, maxY, &f_,
+                                          (orbx_keypoint*)mvKeys.data(), (orbx_keypoint*)mvKeysUn.data(), mDescriptors.ptr(0), &n, cap), "orbm_mono_frame_create");
+        n_ = n;
+        mvKeys.resize(n); mvKeysUn.resize(n); mDescriptors.rows = n;
+    }
     // Frame::Frame, stereo constructor (src/Frame.cpp:61-115) as one device call (orbm_stereo_frame_create): both images are extracted
     // as one batch of `extractor`'s handle (it plays mpORBextractorLeft and ...Right), ComputeStereoMatches and AssignFeaturesToGrid run
     // on the results in device memory.  Fills every vector the constructor fills; mvKeysUn = mvKeys (rectified input, :467-472).

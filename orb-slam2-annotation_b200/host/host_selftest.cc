@@ -133,6 +133,22 @@ static int match_mode(const char* in, const char* outp)
         const int nB = ORBmatcher(0.9f, true).SearchByProjectionLastFrame(F, &uR, qs, mpB, obB);
         if (nA != nB || nA < n / 4 || mpA != mpB || obA != obB) { fprintf(stderr, "search on the fused frame: %d vs %d matches\n", nA, nB); return 4; }
     }
+    {   // Frame::Frame (monocular) as one device call against ExtractORB + UndistortKeyPoints done member by member (TUM1.yaml calibration)
+        const float K4[4] = {517.306408f, 516.469215f, 318.643040f, 255.313989f};
+        const std::vector<float> D = {0.262383f, -0.953104f, -0.005358f, 0.002628f, 1.163314f};
+        ORBextractor ex(nf, 1.2f, 8, 20, 7);
+        std::vector<cv::KeyPoint> k, ku, k2, ku2;
+        cv::Mat d, d2;
+        ex(imL, cv::Mat(), k, d);
+        UndistortKeyPoints(k, K4, D, ku);
+        float bx0, by0, bx1, by1;
+        ComputeImageBounds(w, h, K4, D, bx0, by0, bx1, by1);
+        DeviceFrame F(ex, imL, K4, D, bx0, by0, bx1, by1, k2, ku2, d2);
+        if (k2.size() != k.size() || memcmp(k2.data(), k.data(), sizeof(cv::KeyPoint) * k.size()) || memcmp(ku2.data(), ku.data(), sizeof(cv::KeyPoint) * k.size()))
+        { fprintf(stderr, "fused monocular constructor differs (keypoints)\n"); return 5; }
+        for (size_t i = 0; i < k.size(); i++) if (memcmp(d2.ptr((int)i), d.ptr((int)i), 32)) { fprintf(stderr, "fused monocular constructor differs (descriptor %zu)\n", i); return 5; }
+        if (F.size() != (int)k.size()) return 5;
+    }
     {   // batched distances: row i of frame 1 against row i of frame 2
         const int n = n1 < n2 ? n1 : n2;
         std::vector<int32_t> dist(n);

@@ -29,7 +29,7 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_get_tables", "orbx_extract", "or
            "orbx_extract_batch_color", "orbx_cvt_gray_device", "orbx_set_rectification", "orbx_extract_batch_rectified", "orbx_remap_device", "orbm_distance_pairs", "orbm_distinctive_descriptors", "orbm_distinctive_descriptors_device", "orbm_frame_create", "orbm_frame_destroy", "orbm_window_search",
            "orbm_search_by_projection_points", "orbm_search_by_projection_frame", "orbm_search_for_initialization", "orbm_search_by_bow", "orbm_search_by_bow_kf", "orbm_search_for_triangulation", "orbm_frame_create_device", "orbm_undistort_keypoints", "orbm_undistort_keypoints_device", "orbm_image_bounds",
            "orbm_search_by_projection_points_device", "orbm_search_by_projection_frame_device", "orbm_search_by_projection_reloc", "orbm_search_by_projection_reloc_device", "orbm_search_by_projection_loop", "orbm_fuse_best",
-           "orbm_stereo_match", "orbm_stereo_frame_create", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
+           "orbm_stereo_match", "orbm_stereo_frame_create", "orbm_mono_frame_create", "orbm_db_create", "orbm_db_append", "orbm_db_append_device", "orbm_db_destroy",
            "orbm_db_rows", "orbm_bf_top2", "orbm_bf_top2_device", "orbm_bf_top2_noalloc", "orbm_merge_top2_device", "orbm_ratio_test",
            "orbv_vocab_create", "orbv_vocab_destroy", "orbv_vocab_words", "orbv_transform", "orbv_transform_device",
            "orbv_compute_bow", "orbb200_strerror", "orbb200_last_cuda_error", "orbb200_device_count", "orbb200_measure_popc_peak", "orbb200_measure_imma_peak", "orbb200_measure_tcgen05_i8_peak",
@@ -111,6 +111,7 @@ def lib():
         L.orbm_search_for_triangulation.argtypes = ([vp] * 4 + [i32] + [vp] * 3 + [i32]) * 2 + [vp, f32, f32, vp, vp, i32, i32, vp, C.POINTER(i32), i32]
         L.orbm_search_for_initialization.argtypes = [vp, vp, vp, vp, i32, f32, i32, C.POINTER(i32)]
         L.orbm_stereo_match.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, f32, f32, vp, vp]
+        L.orbm_mono_frame_create.argtypes = [vp, vp, i32, i32, C.c_size_t, vp, vp, i32, f32, f32, f32, f32, vp, vp, vp, vp, vp, i32]
         L.orbm_stereo_frame_create.argtypes = [vp, vp, vp, i32, i32, C.c_size_t, f32, f32, f32, f32, f32, f32, vp, vp, vp, vp, vp, vp, vp, i32, vp, vp]
         L.orbm_db_create.argtypes = [C.POINTER(vp), C.c_int64, C.c_int64, i32]
         L.orbm_db_append.argtypes = [vp, vp, C.c_int64]
@@ -636,6 +637,22 @@ def stereo_frame(ex, left, right, mbf, bounds, mb=0.0, capacity=None):
     F.n = nL.value
     F.kps = kL[:F.n]; F.desc = dL[:F.n]
     return F, kL[:nL.value], dL[:nL.value], kR[:nR.value], dR[:nR.value], ur[:nL.value], dp[:nL.value]
+
+
+def mono_frame(ex, image, bounds, K4=None, dist=None, capacity=None):
+    """Frame::Frame (monocular constructor, Frame.cpp:171-224) as one call (orbm_mono_frame_create).  Returns (FrameMatcher, mvKeys, mvKeysUn, mDescriptors)."""
+    image = np.ascontiguousarray(image, np.uint8)
+    ht, w = image.shape
+    cap = int(capacity or ex.default_capacity)
+    k = np.zeros(cap, KP_DTYPE); ku = np.zeros(cap, KP_DTYPE); d = np.zeros((cap, 32), np.uint8)
+    n = C.c_int()
+    K = None if K4 is None else np.ascontiguousarray(K4, np.float32); D = None if dist is None else np.ascontiguousarray(dist, np.float32)
+    F = FrameMatcher.__new__(FrameMatcher)
+    F.L = lib(); F.kps = None; F.desc = None; F.h = C.c_void_p(); F.n = 0
+    _check(F.L.orbm_mono_frame_create(ex.h, _p(image), w, ht, w, _p(K), _p(D), 0 if D is None else len(D), *[float(b) for b in bounds], C.byref(F.h),
+                                      _p(k), _p(ku), _p(d), C.byref(n), cap), "orbm_mono_frame_create")
+    F.n = n.value; F.kps = ku[:F.n]; F.desc = d[:F.n]
+    return F, k[:n.value], ku[:n.value], d[:n.value]
 
 
 class DescriptorDB:

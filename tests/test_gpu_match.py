@@ -767,3 +767,34 @@ def test_stereo_frame_create_degenerate_inputs(gpu):
         our, odp, _, _ = pyoracle.stereo_match(oL, oR, 40.0, 0.0)
     assert np.array_equal(ur, our) and np.array_equal(dp, odp)
     F.close()
+
+
+@pytest.mark.parametrize("w,h,nf,seed,dist", [(640, 480, 1000, 31, [0.262383, -0.953104, -0.005358, 0.002628, 1.163314]),   # TUM1.yaml
+                                             (752, 480, 1200, 32, None), (638, 401, 1000, 33, [0.0, 0.2, 0.0, 0.0])])
+def test_mono_frame_create(gpu, w, h, nf, seed, dist):
+    """orbm_mono_frame_create (Frame.cpp:171-224 as one call) == oracle extraction + oracle UndistortKeyPoints, and the frame it leaves on
+    the device answers a local-map search like a frame built from the host arrays."""
+    import orbb200, pyoracle
+    from synth import synth
+    img = synth(w, h, seed)
+    K4 = [517.306408, 516.469215, 318.643040, 255.313989]
+    ok, od = pyoracle.OracleExtractor(nf).extract(img)
+    oun = pyoracle.undistort_keypoints(ok, K4, dist) if dist is not None else ok
+    bounds = orbb200.image_bounds(w, h, K4, dist) if dist is not None else (0, 0, w, h)
+    ex = orbb200.ORBextractor(nf, max_size=(w, h))
+    rng = np.random.default_rng(seed)
+    for rep in range(2):
+        F, k, ku, d = orbb200.mono_frame(ex, img, bounds, K4 if dist is not None else None, dist)
+        assert k.tobytes() == ok.tobytes() and np.array_equal(d, od) and ku.tobytes() == oun.tobytes()
+        G = orbb200.FrameMatcher(ku, d, bounds); O = pyoracle.OracleFrame(ku, d, bounds)
+        q = _queries(ku, d, ex.GetScaleFactors(), 10.0, (1, 1), rng)
+        mp0 = np.full(len(k), -1, np.int32); ob0 = np.zeros(len(k), np.int32)
+        m = orbb200.ORBmatcher(0.8, True)
+        on, omp, oob = O.search_local_points(_to_oracle_queries(q), 0.8, mp0, ob0, None)
+        for frame in (F, G):
+            n, mp, ob = m.SearchByProjection_points(frame, q, mp0, ob0, None)
+            assert n == on and np.array_equal(mp, omp) and np.array_equal(ob, oob)
+        assert on > 0.3 * len(k)
+        F.close(); G.close()
+    with pytest.raises(orbb200.OrbError):
+        orbb200.mono_frame(ex, img, bounds, capacity=len(ok) - 1)
