@@ -257,6 +257,7 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
             O[i] = __byte_perm(w, 0u, 0x4341);
         }
         const unsigned KA = a.kq[0], KB = a.kq[1], KC = a.kq[2], KD = a.kq[3], KE = a.kq[4], KF = a.kq[5], KG = a.kq[6], KH = a.kq[7];
+        const uint2* const hedge = hsum + ry0 * 2 + (lane == 31 ? 1 : 0);      // (OW = 32) this lane's side of the halo sums, row j at [2 * j]
         const int gx = x0 - 4 + 4 * lw;
         const bool store_lane = (OW == 32 || (lane >= 1 && lane <= L3_OWNW)) && gx < a.w;
         uint8_t* __restrict__ bp = a.blur + (long long)f * a.blur_fstride + (long long)(y0 + ry0) * a.blur_pitch + gx;
@@ -267,9 +268,10 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
             const unsigned VO = q3 * O[j + 3] + q2 * (O[j + 2] + O[j + 4]) + q1 * (O[j + 1] + O[j + 5]) + q0 * (O[j] + O[j + 6]);
             unsigned lE = __shfl_up_sync(FULL, VE, 1), lO = __shfl_up_sync(FULL, VO, 1);
             unsigned rE = __shfl_down_sync(FULL, VE, 1), rO = __shfl_down_sync(FULL, VO, 1);
-            if (OW == 32) {                                          // the edge lanes' outer neighbours are the halo words
-                if (lane == 0) { const uint2 t = hsum[(ry0 + j) * 2]; lE = t.x; lO = t.y; }
-                if (lane == 31) { const uint2 t = hsum[(ry0 + j) * 2 + 1]; rE = t.x; rO = t.y; }
+            if (OW == 32) {                                          // the edge lanes' outer neighbours are the halo words: one broadcast load, four selects
+                const uint2 t = hedge[2 * j];
+                lE = lane == 0 ? t.x : lE; lO = lane == 0 ? t.y : lO;
+                rE = lane == 31 ? t.x : rE; rO = lane == 31 ? t.y : rO;
             }
             // taps: q0..q6 with q4=q2, q5=q1, q6=q0; pairs are (even, odd) = (V0|V2<<16, V1|V3<<16) of the left / own / right word
             unsigned r0 = __dp2a_lo(lO, KA, 32768u); r0 = __dp2a_hi(lE, KA, r0); r0 = __dp2a_lo(VE, KB, r0); r0 = __dp2a_hi(VO, KB, r0);
@@ -354,12 +356,9 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
         constexpr int RPW9 = 9;
         static_assert(RPW9 * NW >= TH + 2, "9 rows per warp cover the tile and its ring");
         const int sb = RPW9 * warp - 1;                           // first score-map row of this warp (tile row index)
-        unsigned rowok = 0;                                       // bit it: row sb + it is a scored row of the image
-#pragma unroll
-        for (int it = 0; it < RPW9; it++) {
-            const int s = sb + it, gy = y0 + s;
-            if (s <= TH && gy >= 19 && gy <= a.h - 20) rowok |= 1u << it;
-        }
+        // bit it: row s = sb + it is a scored row of the image (s <= TH, 19 <= y0 + s <= h - 20): a run of bits lo_it .. hi_it
+        const int lo_it = max(0, 19 - y0 - sb), hi_it = min(min(RPW9 - 1, TH - sb), a.h - 20 - y0 - sb);
+        const unsigned rowok = lo_it <= hi_it ? ((2u << hi_it) - 1u) & ~((1u << lo_it) - 1u) : 0u;
         // private candidate flags: byte b of m0 holds rows it = 0..7 of pixel b (bit it), m1 holds row 8 at bit 7 of byte b
         unsigned m0 = 0, m1 = 0;
         if (rowok) {                                              // warp-uniform
@@ -398,17 +397,19 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
         // each lane appends its own candidates: one shared atomic per lane, no warp scan (queue order is irrelevant)
         const int n = __popc(m0) + __popc(m1);
         if (n) {
+            // queue code: row group << 12 | staged word << 6 | tt, tt = 8 * byte + it for the rows it = 0..7, 32 + byte for row 8 (decoded,
+            // 32 candidates per instruction, by the scoring pass; this loop runs once per candidate of the warp's busiest lane)
             int slot = atomicAdd(&s_qn, n);
-            const int pbase = ((sb + 1) << SCSH) + 4 * lw;       // queue code of (row sb, byte 0 of this lane's word)
-            while (m0) {                                          // bit t = 8 * byte + it  ->  pbase + it * L3_SCP + byte
+            const unsigned lanecode = ((unsigned)warp << 12) | ((unsigned)lw << 6);
+            while (m0) {
                 const int t = __ffs((int)m0) - 1;
                 m0 &= m0 - 1;
-                queue[slot++] = (uint16_t)(pbase + ((t & 7) << SCSH) + (t >> 3));
+                queue[slot++] = (uint16_t)(lanecode | (unsigned)t);
             }
             while (m1) {                                          // bit t = 8 * byte + 7
                 const int t = __ffs((int)m1) - 1;
                 m1 &= m1 - 1;
-                queue[slot++] = (uint16_t)(pbase + (8 << SCSH) + (t >> 3));
+                queue[slot++] = (uint16_t)(lanecode | 32u | (unsigned)(t >> 3));
             }
         }
         if (OW == 32 && lane < 2 * RPW9) {
@@ -420,10 +421,11 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
                 const uint8_t* cp = tb + (sb + it + 4) * L3_SPB + c;          // tile row sb + it is staged row sb + it + 4
                 const int tq = (int)((~M) & 0xffu);               // t' (M = 0: minTh = 0, everything passes)
                 const int v = cp[0];
-                auto far = [&](int off) { return abs(v - (int)cp[off]) > tq; };
-                const bool cand = M == 0u || ((far(3 * L3_SPB) || far(-3 * L3_SPB)) && (far(3) || far(-3)) &&
-                                              (far(2 * L3_SPB + 2) || far(-2 * L3_SPB - 2)) && (far(-2 * L3_SPB + 2) || far(2 * L3_SPB - 2)));
-                if (cand) queue[atomicAdd(&s_qn, 1)] = (uint16_t)(((sb + it + 1) << SCSH) + c);
+                auto far = [&](int off) { return (int)(abs(v - (int)cp[off]) > tq); };         // branch-free: all eight loads go out together
+                const int cand = (far(3 * L3_SPB) | far(-3 * L3_SPB)) & (far(3) | far(-3)) &
+                                 (far(2 * L3_SPB + 2) | far(-2 * L3_SPB - 2)) & (far(-2 * L3_SPB + 2) | far(2 * L3_SPB - 2));
+                if (cand || M == 0u)                              // staged byte column c = 4 * word + byte: word 0 byte 3, or word OW + 1 byte 0
+                    queue[atomicAdd(&s_qn, 1)] = (uint16_t)(((unsigned)warp << 12) | ((unsigned)(c >> 2) << 6) | (it < 8 ? (unsigned)(8 * (c & 3) + it) : 32u + (c & 3)));
             }
         }
     }
@@ -440,8 +442,10 @@ __global__ void __launch_bounds__(SPLIT ? 64 * NW : 32 * NW, (NW == 8 || SPLIT) 
         const int j = j0 + lane;
         bool surv = false; int pos = 0;
         if (j < cend) {
-            pos = queue[j];
-            const int r = pos >> SCSH, c = pos & ((1 << SCSH) - 1);   // score-map row (tile row + 1), staged byte column
+            const int code = queue[j], tt = code & 63;
+            const int r = 9 * (code >> 12) + (tt < 32 ? (tt & 7) : 8);                   // score-map row (tile row + 1): row group base 9 * warp - 1, + it, + 1
+            const int c = 4 * ((code >> 6) & 63) + (tt < 32 ? (tt >> 3) : tt - 32);     // staged byte column
+            pos = (r << SCSH) | c;
             const int m = l3_arc_score<L3_SPB>(tb + (r + 3) * L3_SPB + c);
             if (m > a.minTh) {
                 sc[r * L3_SCP + c] = (uint8_t)m;
