@@ -1430,6 +1430,9 @@ extern "C" int orbb200_measure_tcgen05_i8_peak(int device, double* int8_tops)
     return ORBB_OK;
 }
 
+#ifdef RESOLVE_TIMING
+extern "C" int orbb200__resolve_timing(unsigned long long* out) { return cudaMemcpyFromSymbol(out, g_resolve_t, sizeof(unsigned long long) * 8) == cudaSuccess ? 0 : -2; }
+#endif
 #ifdef B2_TIMING
 extern "C" int orbb200__b2_gtiming(long long* out) { return cudaMemcpyFromSymbol(out, g_b2_g, sizeof(long long) * 2 * 32 * 2 * 8) == cudaSuccess ? 0 : -2; }
 extern "C" int orbb200__b2_timing(long long* out) { return cudaMemcpyFromSymbol(out, g_b2_t, sizeof(long long) * 32 * 2 * 8) == cudaSuccess ? 0 : -2; }

@@ -395,9 +395,16 @@ __device__ __forceinline__ int resolve_choose(const ResolveArgs& a, const int* _
     return bestIdx;
 }
 
+#ifdef RESOLVE_TIMING
+__device__ unsigned long long g_resolve_t[8];
+#define RT_STAMP(k) do { if (threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_resolve_t[k] = t_; } } while (0)
+#else
+#define RT_STAMP(k)
+#endif
 template <int MODE>
 __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_constant__ ResolveArgs a)
 {
+    RT_STAMP(0);
     extern __shared__ int taker_s[];
     __shared__ int nm_s, hist_s[30], ind_s[3];
     const int tid = threadIdx.x, nt = blockDim.x;
@@ -408,6 +415,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
     if (tid == 0) nm_s = 0;
     if (tid < 30) hist_s[tid] = 0;
     __syncthreads();
+    RT_STAMP(1);
     int rounds = 0;
     if (MODE == 0) {
         // The ratio test makes a query's verdict depend on its best AND second-best unblocked candidate, and a query that loses its
@@ -451,6 +459,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
         for (int k = tid; k < a.f.n; k += nt) taker[k] = 0x7fffffff;
         __syncthreads();
     }
+    RT_STAMP(2);
     // slot k <- the last query that chose it; taker is reused as "last chooser" (reset to INT_MAX above: store -i-1 as min)
     for (int i = tid; i < a.nq; i += nt) {
         const int c = a.choice[i];
@@ -473,6 +482,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
     }
     if (mine) atomicAdd(&nm_s, mine);
     __syncthreads();
+    RT_STAMP(3);
     if (MODE >= 1 && a.check_ori) {
         if (tid == 0) {                                     // ComputeThreeMaxima
             int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
@@ -500,7 +510,11 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
         if (gone) atomicSub(&nm_s, gone);
         __syncthreads();
     }
+    RT_STAMP(4);
     if (tid == 0) { *a.nmatches = nm_s; *a.status = ORBB_OK; if (a.rounds) *a.rounds = rounds; }
+#ifdef RESOLVE_TIMING
+    if (tid == 0) g_resolve_t[5] = (unsigned long long)rounds;
+#endif
 }
 
 // The per-point search of Fuse / SearchBySim3 (ORBmatcher.cpp:962-1115, :1119-1251, :1253-1500) on the candidate CSR: queries do not
