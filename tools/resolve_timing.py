@@ -1,6 +1,6 @@
 """Phase times of resolve_projection_kernel (build with -DRESOLVE_TIMING as liborbb200_rt.so): runs tools/pair_timing's search and reads the stamps."""
 import ctypes as C, os, sys, shutil
-ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 P = os.path.join(ROOT, "orb-slam2-annotation_b200")
 shutil.copy(os.path.join(P, "liborbb200.so"), "/tmp/orig.so"); shutil.copy(os.path.join(P, "liborbb200_rt.so"), os.path.join(P, "liborbb200.so"))
 try:
