@@ -367,7 +367,7 @@ struct ResolveArgs {
     int* nmatches; int* status; int* rounds;                       // device scalars (rounds may be nullptr)
 };
 
-constexpr int RESOLVE_SMEM_SLOTS = 12 * 1024;       // taker table in shared memory up to this many Frame features (48 KB)
+constexpr int RESOLVE_SMEM_SLOTS = 10 * 1024;       // taker table in shared memory up to this many Frame features (40 KB dynamic + static < the 48 KB default limit)
 
 template <int MODE>
 __device__ __forceinline__ int resolve_choose(const ResolveArgs& a, const int* __restrict__ taker, int i)
