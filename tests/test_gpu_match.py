@@ -798,3 +798,30 @@ def test_mono_frame_create(gpu, w, h, nf, seed, dist):
         F.close(); G.close()
     with pytest.raises(orbb200.OrbError):
         orbb200.mono_frame(ex, img, bounds, capacity=len(ok) - 1)
+
+
+@pytest.mark.parametrize("n", [10240, 10241, 12288, 20000])
+def test_resolve_large_frames_around_the_shared_memory_limit(gpu, n):
+    """The resolve kernel keeps its slot table in shared memory up to 10 240 Frame features and in global memory beyond: synthetic frames of
+    n keypoints on both sides of that limit (and at the old 12 288 one), both resolve modes, against the oracle."""
+    import orbb200, pyoracle
+    rng = np.random.default_rng(n)
+    w, h = 3840, 2160
+    kps = np.zeros(n, orbb200.KP_DTYPE)
+    kps["x"] = rng.integers(20, w - 20, n); kps["y"] = rng.integers(20, h - 20, n); kps["octave"] = rng.integers(0, 8, n)
+    kps["angle"] = rng.uniform(0, 360, n).astype(np.float32); kps["size"] = 31; kps["class_id"] = -1
+    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    scale = (1.2 ** np.arange(8)).astype(np.float32)
+    pick = rng.permutation(n)[:3000]
+    q = _queries(kps[pick], desc[pick], scale, 25.0, (2, 1), rng)
+    noise = rng.integers(0, 256, (len(q), 32), dtype=np.uint8) & rng.integers(0, 256, (len(q), 32), dtype=np.uint8) & rng.integers(0, 256, (len(q), 32), dtype=np.uint8)
+    q["q"]["desc"] ^= noise                                   # ~32 flipped bits: matches survive TH_HIGH, rivals differ
+    F = orbb200.FrameMatcher(kps, desc, (0, 0, w, h)); O = pyoracle.OracleFrame(kps, desc, (0, 0, w, h))
+    mp0 = np.full(n, -1, np.int32); ob0 = np.zeros(n, np.int32)
+    nf, mp, ob = orbb200.ORBmatcher(0.9, True).SearchByProjection_frame(F, q, mp0, ob0, None)
+    on, omp, oob = O.search_last_frame(_to_oracle_queries(q), True, mp0, ob0, None)
+    assert nf == on and np.array_equal(mp, omp) and np.array_equal(ob, oob) and nf > 500
+    nf, mp, ob = orbb200.ORBmatcher(0.8).SearchByProjection_points(F, q, mp0, ob0, None)
+    on, omp, oob = O.search_local_points(_to_oracle_queries(q), 0.8, mp0, ob0, None)
+    assert nf == on and np.array_equal(mp, omp) and np.array_equal(ob, oob)
+    F.close()
