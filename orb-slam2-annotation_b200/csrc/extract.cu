@@ -1278,9 +1278,8 @@ extern "C" int orbx__extract_resident(orbx_handle* h, const uint8_t* const* imgs
         ORBB_CUDA(cudaMemcpy2DAsync(h->d_pyr + (size_t)f * h->pyr_fstride + g0.off, dpitch0, src, spitch, w, ht, cudaMemcpyHostToDevice, st));
     }
     const int devcap = h->dev_capacity;
-    static const bool side = getenv("ORBB_RESIDENT_SIDE") ? atoi(getenv("ORBB_RESIDENT_SIDE")) != 0 : false;
     const double t1 = trace ? now() : 0.0;
-    const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, 0, side);
+    const int rc = enqueue_extract(h, h->d_pyr + g0.off, 0, nframes, w, ht, dpitch0, h->pyr_fstride, h->d_kps, h->d_desc, h->d_counts, devcap, 0, false);   // (small launches fan their octrees out anyway)
     if (rc != ORBB_OK) return rc;
     ORBB_CUDA(cudaMemcpyAsync(h->h_counts, h->d_counts, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
     ORBB_CUDA(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(int) * nframes, cudaMemcpyDeviceToHost, st));
