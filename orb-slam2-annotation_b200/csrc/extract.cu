@@ -584,7 +584,10 @@ static int enqueue_extract(orbx_handle* h, const uint8_t* imgs_dev0, int f0, int
             const LevelGeom& n = h->geom[l + 1];
             a.dst = d_pyr + n.off; a.dst_pitch = n.pitch; a.dst_fstride = (long long)h->pyr_fstride;
         }
-        a.fast_on = g.nCols > 0; a.wCell = g.wCell; a.hCell = g.hCell; a.minTh = h->cfg.min_th_fast;
+        a.fast_on = g.nCols > 0; a.wCell = g.wCell; a.hCell = g.hCell;
+        // a corner is recorded when its arc score m exceeds minThFAST; cv::FAST's 3x3 NMS keeps a pixel only if its score m - 1 is strictly above
+        // its neighbours', and a non-corner neighbour scores 0: at minThFAST = 0 the corners with m = 1 (score 0) never survive it
+        a.minTh = h->cfg.min_th_fast > 1 ? h->cfg.min_th_fast : 1;
         a.magicW = g.magicW; a.magicH = g.magicH;
         a.rec = d_rec + g.rec_off; a.rec_cap = g.rec_cap; a.rec_fstride = (long long)h->rec_total;
         a.rec_count = d_rec_count + l; a.rec_count_stride = nl;

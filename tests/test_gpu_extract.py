@@ -433,3 +433,42 @@ def test_every_level_kernel_variant(gpu, env):
                         "stage_parity or final_parity or noise or batch_equals_single or odd_shapes or multi_chunk or graph_replay"],
                        env={**os.environ, **env}, capture_output=True, text=True, timeout=900, cwd=root)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_random_shapes_and_parameters(gpu):
+    """Thirty seeded random configurations (image size 90 .. 1000 x 70 .. 700, 3 .. 10 levels, scale factor 1.1 .. 1.25, FAST thresholds,
+    feature budget), each as a single frame and as a batch of three through one handle: every pyramid / blur level, every keypoint field
+    and (to the angle tolerance) every descriptor against the oracle.  The sizes fall on both sides of every tile-geometry decision the
+    library takes per level (tile width, latency mode, TMA / ordinary staging through odd pitches)."""
+    import orbb200, pyoracle
+    from synth import synth
+    rng = np.random.default_rng(20261105)
+    for case in range(30):
+        w = int(rng.integers(90, 1001)); h = int(rng.integers(70, 701))
+        nl = int(rng.integers(3, 11)); sf = float(np.float32(rng.uniform(1.1, 1.25)))
+        ini = int(rng.integers(8, 40)); mn = int(rng.integers(0, ini + 1)); nf = int(rng.integers(50, 1500))
+        if min(w, h) / sf ** (nl - 1) < 40:                      # the reference needs every level larger than its 2 x 19 px border
+            nl = max(1, int(np.log(min(w, h) / 40.0) / np.log(sf)))
+        tag = f"case {case}: {w}x{h} nlevels={nl} scale={sf:.4f} ini={ini} min={mn} nf={nf}"
+        imgs = [synth(w, h, 1000 + 3 * case + i) for i in range(3)]
+        orc = pyoracle.OracleExtractor(nf, sf, nl, ini, mn)
+        ex = orbb200.ORBextractor(nf, sf, nl, ini, mn, max_size=(w, h), max_batch=3)
+        ok, od = orc.extract(imgs[0])
+        k, d = ex(imgs[0])
+        for L in range(nl):
+            assert np.array_equal(ex.pyramid_level(L), orc.level_image(L)), f"{tag}: pyramid level {L}"
+            assert np.array_equal(ex.blurred_level(L), orc.level_image(L, blurred=True)), f"{tag}: blur level {L}"
+        assert len(k) == len(ok), tag
+        for f in ("x", "y", "size", "response", "octave"):
+            assert np.array_equal(k[f], ok[f]), f"{tag}: {f}"
+        if len(k):
+            assert np.max(np.abs(k["angle"] - ok["angle"])) <= 1e-3, tag
+            assert np.any(d != od, axis=1).sum() <= max(1, 0.001 * len(d)), tag
+        res = ex.extract_batch(np.stack(imgs))
+        for i in range(3):
+            oki, odi = orc.extract(imgs[i])
+            kb, db = res[i]
+            assert len(kb) == len(oki), f"{tag}: frame {i}"
+            for f in ("x", "y", "response", "octave"):
+                assert np.array_equal(kb[f], oki[f]), f"{tag}: frame {i} {f}"
+        ex.close()
