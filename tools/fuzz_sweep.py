@@ -1,0 +1,52 @@
+"""Randomized parity sweep (not part of the test suite: minutes of oracle time): extractor configurations as in
+tests/test_gpu_extract.py::test_random_shapes_and_parameters with another seed, plus for every third case the fused stereo constructor
+and a tracked-frame search against the oracle.  Prints one line per failing case and a summary.
+usage: fuzz_sweep.py ncases seed"""
+import sys, os, traceback
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [os.path.join(ROOT, "orb-slam2-annotation_b200"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")]
+import numpy as np, orbb200, pyoracle
+from synth import synth
+ncases = int(sys.argv[1]) if len(sys.argv) > 1 else 60
+rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 7)
+bad = 0
+for case in range(ncases):
+    w = int(rng.integers(90, 1301)); h = int(rng.integers(70, 801))
+    nl = int(rng.integers(1, 11)); sf = float(np.float32(rng.uniform(1.05, 1.4)))
+    ini = int(rng.integers(1, 60)); mn = int(rng.integers(0, ini + 1)); nf = int(rng.integers(20, 2500))
+    while nl > 1 and min(w, h) / sf ** (nl - 1) < 40:
+        nl -= 1
+    seed = int(rng.integers(0, 1 << 30))
+    tag = f"{w} {h} {nl} {sf:.6f} {ini} {mn} {nf} {seed}"
+    try:
+        img = synth(w, h, seed)
+        orc = pyoracle.OracleExtractor(nf, sf, nl, ini, mn)
+        ex = orbb200.ORBextractor(nf, sf, nl, ini, mn, max_size=(w, h), max_batch=2)
+        ok, od = orc.extract(img)
+        k, d = ex(img)
+        for L in range(nl):
+            assert np.array_equal(ex.pyramid_level(L), orc.level_image(L)), f"pyramid level {L}"
+            assert np.array_equal(ex.blurred_level(L), orc.level_image(L, blurred=True)), f"blur level {L}"
+        assert len(k) == len(ok), f"count {len(k)} vs {len(ok)}"
+        for f in ("x", "y", "size", "response", "octave"):
+            assert np.array_equal(k[f], ok[f]), f
+        if len(k):
+            assert np.max(np.abs(k["angle"] - ok["angle"])) <= 1e-3, "angle"
+            assert np.any(d != od, axis=1).sum() <= max(1, 0.002 * len(d)), "descriptors"
+        if case % 3 == 0 and len(k) > 20:
+            right = np.roll(img, -7, axis=1)
+            oL, oR = pyoracle.OracleExtractor(nf, sf, nl, ini, mn), pyoracle.OracleExtractor(nf, sf, nl, ini, mn)
+            oL.extract(img); okR, _ = oR.extract(right)
+            F, kL, dL, kR, dR, ur, dp = orbb200.stereo_frame(ex, img, right, 40.0, (0, 0, w, h))
+            with np.errstate(divide="ignore"):
+                our, odp, _, _ = pyoracle.stereo_match(oL, oR, 40.0, 0.0)
+            assert kR.tobytes() == okR.tobytes(), "right keypoints"
+            exact = np.all(kL["angle"] == ok["angle"]) and np.array_equal(dL, od)
+            if exact:
+                assert np.array_equal(ur, our) and np.array_equal(dp, odp), "stereo"
+            F.close()
+        ex.close()
+    except Exception as e:
+        bad += 1
+        print("FAIL", tag, "|", type(e).__name__, str(e)[:160], flush=True)
+print("cases", ncases, "failures", bad)
