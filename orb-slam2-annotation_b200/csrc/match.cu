@@ -377,6 +377,7 @@ inline int rot_bin(float a1, float a2)
     if (rot < 0.0) rot += 360.0f;
     int bin = (int)roundf(rot * (HISTO_LENGTH / 360.0f));
     if (bin == HISTO_LENGTH) bin = 0;
+    if (bin < 0 || bin > HISTO_LENGTH) bin = 0;        // angles outside [0, 360) are outside the reference's domain (it would index past rotHist): keep the C ABI memory-safe
     return bin;
 }
 }  // namespace

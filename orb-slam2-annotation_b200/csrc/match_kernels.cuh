@@ -476,7 +476,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
             float rot = __fsub_rn(a.q[i].angle, a.f.kps[c].angle);
             if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
             int bin = (int)roundf(__fmul_rn(rot, 30 / 360.0f));
-            if (bin == 30) bin = 0;
+            if (bin == 30 || bin < 0 || bin > 30) bin = 0;           // (beyond 30: angles outside [0, 360), outside the reference's domain; stay inside the histogram)
             atomicAdd(&hist_s[bin], 1);
         }
     }
@@ -504,7 +504,7 @@ __global__ void __launch_bounds__(1024) resolve_projection_kernel(const __grid_c
             float rot = __fsub_rn(a.q[i].angle, a.f.kps[c].angle);
             if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
             int bin = (int)roundf(__fmul_rn(rot, 30 / 360.0f));
-            if (bin == 30) bin = 0;
+            if (bin == 30 || bin < 0 || bin > 30) bin = 0;           // (beyond 30: angles outside [0, 360), outside the reference's domain; stay inside the histogram)
             if (bin != ind_s[0] && bin != ind_s[1] && bin != ind_s[2]) { a.frame_mp[c] = -1; gone++; }
         }
         if (gone) atomicSub(&nm_s, gone);
