@@ -64,6 +64,33 @@ for case in range(ncases):
             ql = q.copy(); ql["q"]["min_level"] = lv - 1; ql["q"]["max_level"] = lv          # the loop overload's window is [p - 1, p] (include/orbb200.h)
             r4 = orbb200.ORBmatcher().SearchByProjection_loop(F, ql, mp0); o4 = O.search_loop(oq(ql), mp0)
             assert r4[0] == o4[0] and np.array_equal(r4[1], o4[1]), "loop search"
+        if nq and n:
+            # fusion / Sim3 search: level window [p - 1, p] like the loop overload, chi-square gate with or without mvuRight
+            sigma2 = (scale ** 2).astype(np.float32); inv_s2 = (np.float32(1.0) / sigma2).astype(np.float32)
+            gate = bool(rng.random() < 0.5); maxd = int(rng.choice([50, 100]))
+            urf = ur if gate else None
+            bi, bd = orbb200.ORBmatcher().FuseBest(F, ql, urf, inv_s2 if gate else None, maxd)
+            obi, obd = O.fuse_best(oq(ql), urf, inv_s2, gate, maxd)
+            assert np.array_equal(bi, obi) and np.array_equal(bd, obd), "fuse best"
+            # GetFeaturesInArea order and distances
+            wq = np.zeros(min(nq, 400), orbb200.QUERY_DTYPE)
+            for f_ in ("u", "v", "r", "min_level", "max_level", "desc"): wq[f_] = q["q"][f_][: len(wq)]
+            offs, idx, dist = F.window_search(wq)
+            ow = np.zeros(len(wq), pyoracle.QUERY_DTYPE)
+            ow["u"] = wq["u"]; ow["v"] = wq["v"]; ow["r"] = wq["r"]; ow["minLevel"] = wq["min_level"]; ow["maxLevel"] = wq["max_level"]; ow["desc"] = wq["desc"]
+            ooffs, oidx, odist = O.window_search(ow)
+            assert np.array_equal(offs, ooffs) and np.array_equal(idx[: offs[-1]], oidx[: ooffs[-1]]) and np.array_equal(dist[: offs[-1]], odist[: ooffs[-1]]), "window search"
+        if n > 1 and case % 3 == 0:
+            # SearchForInitialization: the frame against a jittered copy of itself
+            k2 = kps.copy(); k2["x"] = np.clip(kps["x"] + rng.integers(-4, 5, n), 0, w - 1); k2["y"] = np.clip(kps["y"] + rng.integers(-4, 5, n), 0, h - 1)
+            d2 = desc ^ (rng.integers(0, 256, (n, 32), dtype=np.uint8) & rng.integers(0, 256, (n, 32), dtype=np.uint8) & rng.integers(0, 256, (n, 32), dtype=np.uint8))
+            F2 = orbb200.FrameMatcher(k2, d2, (0, 0, w, h)); O2 = pyoracle.OracleFrame(k2, d2, (0, 0, w, h))
+            prev = np.stack([kps["x"], kps["y"]], 1).astype(np.float32)
+            win = int(rng.choice([10, 50, 100]))
+            r5 = orbb200.ORBmatcher(0.9, chk).SearchForInitialization(F, F2, prev, win)
+            o5 = pyoracle.search_for_initialization(O, O2, prev, win, 0.9, chk)
+            assert r5[0] == o5[0] and np.array_equal(r5[1], o5[1]) and np.array_equal(r5[2], o5[2].reshape(r5[2].shape)), "initialization search"
+            F2.close()
         F.close()
         if case % 4 == 0:
             nr = int(rng.integers(1, 70000)); nqq = int(rng.integers(1, 600))
