@@ -20,8 +20,10 @@ for case in range(ncases):
     tag = f"{w} {h} {nl} {sf:.6f} {ini} {mn} {nf} {seed}"
     try:
         img = synth(w, h, seed)
-        orc = pyoracle.OracleExtractor(nf, sf, nl, ini, mn)
-        ex = orbb200.ORBextractor(nf, sf, nl, ini, mn, max_size=(w, h), max_batch=2)
+        legacy = bool(rng.random() < 0.25)                      # the Q8 blur kernel of OpenCV <= 3.3 (sums to 257: clamped)
+        orc = pyoracle.OracleExtractor(nf, sf, nl, ini, mn, 0, legacy)
+        ex = orbb200.ORBextractor(nf, sf, nl, ini, mn, max_size=(w, h), max_batch=2, blur_legacy=legacy)
+        tag += f" legacy={int(legacy)}"
         ok, od = orc.extract(img)
         k, d = ex(img)
         for L in range(nl):
@@ -35,7 +37,7 @@ for case in range(ncases):
             assert np.any(d != od, axis=1).sum() <= max(1, 0.002 * len(d)), "descriptors"
         if case % 3 == 0 and len(k) > 20:
             right = np.roll(img, -7, axis=1)
-            oL, oR = pyoracle.OracleExtractor(nf, sf, nl, ini, mn), pyoracle.OracleExtractor(nf, sf, nl, ini, mn)
+            oL, oR = pyoracle.OracleExtractor(nf, sf, nl, ini, mn, 0, legacy), pyoracle.OracleExtractor(nf, sf, nl, ini, mn, 0, legacy)
             oL.extract(img); okR, _ = oR.extract(right)
             F, kL, dL, kR, dR, ur, dp = orbb200.stereo_frame(ex, img, right, 40.0, (0, 0, w, h))
             with np.errstate(divide="ignore"):
