@@ -825,3 +825,48 @@ def test_resolve_large_frames_around_the_shared_memory_limit(gpu, n):
     on, omp, oob = O.search_local_points(_to_oracle_queries(q), 0.8, mp0, ob0, None)
     assert nf == on and np.array_equal(mp, omp) and np.array_equal(ob, oob)
     F.close()
+
+
+def test_frame_constructors_from_concurrent_host_threads(gpu):
+    """Four tracking threads, each with its own extractor handle, run the fused stereo constructor, the fused monocular constructor and a
+    tracked-frame search at once (per-thread default streams, per-thread pinned staging, the shared scratch cache, latency-mode launches
+    with per-level octree streams and dependent launches): every thread's results equal the serial ones, every iteration."""
+    import threading
+    import orbb200
+    from synth import synth_stereo
+    shapes = [(640, 480, 1000), (752, 480, 1200), (638, 401, 800), (1241, 376, 2000)]
+    inputs, expected = [], []
+    for t, (w, h, nf) in enumerate(shapes):
+        L, R = synth_stereo(w, h, 40 + t)
+        ex = orbb200.ORBextractor(nf, max_size=(w, h), max_batch=2)
+        F, kL, dL, kR, dR, ur, dp = orbb200.stereo_frame(ex, L, R, 40.0, (0, 0, w, h))
+        q = _queries(kL, dL, ex.GetScaleFactors(), 15.0, (2, 1), np.random.default_rng(t))
+        mp0 = np.full(len(kL), -1, np.int32); ob0 = np.zeros(len(kL), np.int32)
+        res = orbb200.ORBmatcher(0.9, True).SearchByProjection_frame(F, q, mp0, ob0, orbb200.URIGHT_OF_FRAME)
+        F.close()
+        G, k1, ku1, d1 = orbb200.mono_frame(ex, L, (0, 0, w, h)); G.close()
+        assert res[0] > 0.3 * len(kL)
+        inputs.append((w, h, nf, L, R, q, mp0, ob0)); expected.append((kL, dL, kR, dR, ur, dp, res, k1, d1))
+        ex.close()
+    errs = []
+
+    def work(t):
+        try:
+            w, h, nf, L, R, q, mp0, ob0 = inputs[t]; kL0, dL0, kR0, dR0, ur0, dp0, res0, k10, d10 = expected[t]
+            ex = orbb200.ORBextractor(nf, max_size=(w, h), max_batch=2)
+            for it in range(15):
+                F, kL, dL, kR, dR, ur, dp = orbb200.stereo_frame(ex, L, R, 40.0, (0, 0, w, h))
+                assert kL.tobytes() == kL0.tobytes() and np.array_equal(dL, dL0) and kR.tobytes() == kR0.tobytes() and np.array_equal(dR, dR0), ("extract", t, it)
+                assert np.array_equal(ur, ur0) and np.array_equal(dp, dp0), ("stereo", t, it)
+                res = orbb200.ORBmatcher(0.9, True).SearchByProjection_frame(F, q, mp0, ob0, orbb200.URIGHT_OF_FRAME)
+                assert res[0] == res0[0] and np.array_equal(res[1], res0[1]) and np.array_equal(res[2], res0[2]), ("search", t, it)
+                F.close()
+                G, k1, ku1, d1 = orbb200.mono_frame(ex, L, (0, 0, w, h))
+                assert k1.tobytes() == k10.tobytes() and np.array_equal(d1, d10) and ku1.tobytes() == k10.tobytes(), ("mono", t, it)
+                G.close()
+            ex.close()
+        except Exception as e:          # surfaced after join
+            errs.append(e)
+    th = [threading.Thread(target=work, args=(t,)) for t in range(4)]
+    [t.start() for t in th]; [t.join() for t in th]
+    assert not errs, errs[0]
