@@ -47,6 +47,29 @@ for case in range(ncases):
             if exact:
                 assert np.array_equal(ur, our) and np.array_equal(dp, odp), "stereo"
             F.close()
+        if case % 4 == 1:
+            # device-resident entry point on two frames with an arbitrary base offset, row stride and frame stride (aligned: bulk tensor copies;
+            # otherwise the ordinary-load staging of level 0), results in caller buffers of arbitrary capacity
+            import torch
+            offb = int(rng.choice([0, 16, 1, 4, 7])); stride = w + int(rng.choice([0, 0, 16, 3, 37])); fstride = stride * h + int(rng.choice([0, 16, 5]))
+            buf = torch.zeros(offb + 2 * fstride + 64, dtype=torch.uint8, device="cuda")
+            img2 = synth(w, h, seed + 1)
+            for f_, im in enumerate((img, img2)):
+                view = buf[offb + f_ * fstride: offb + f_ * fstride + stride * h].view(h, stride)
+                view[:, :w] = torch.from_numpy(im).cuda()
+            capd = len(ok) + int(rng.integers(0, 300))
+            dk = torch.zeros((2, capd, 7), dtype=torch.float32, device="cuda"); dd = torch.zeros((2, capd, 32), dtype=torch.uint8, device="cuda"); dc = torch.zeros(2, dtype=torch.int32, device="cuda")
+            ex.extract_batch_device(buf.data_ptr() + offb, 2, w, h, stride, fstride, dk.data_ptr(), dd.data_ptr(), dc.data_ptr(), capd)
+            ex.sync()
+            ok2, od2 = orc.extract(img2)
+            cnt = dc.cpu().numpy()
+            if len(ok2) <= capd:
+                assert cnt[0] == len(ok) and cnt[1] == len(ok2), f"device counts {cnt} vs {len(ok)}, {len(ok2)}"
+                for f_, (okf, odf) in enumerate(((ok, od), (ok2, od2))):
+                    kk = dk[f_, :cnt[f_]].cpu().numpy().view(orbb200.KP_DTYPE).reshape(-1)
+                    for fld in ("x", "y", "response", "octave"):
+                        assert np.array_equal(kk[fld], okf[fld]), f"device frame {f_} {fld}"
+                    assert np.any(dd[f_, :cnt[f_]].cpu().numpy() != odf, axis=1).sum() <= max(1, 0.002 * len(odf)), f"device frame {f_} descriptors"
         ex.close()
     except Exception as e:
         bad += 1
