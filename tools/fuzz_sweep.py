@@ -1,7 +1,7 @@
 """Randomized parity sweep (not part of the test suite: minutes of oracle time): extractor configurations as in
 tests/test_gpu_extract.py::test_random_shapes_and_parameters with another seed, plus for every third case the fused stereo constructor
 and a tracked-frame search against the oracle.  Prints one line per failing case and a summary.
-usage: fuzz_sweep.py ncases seed"""
+usage: fuzz_sweep.py ncases seed [max_width max_height max_features]"""
 import sys, os, traceback
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "orb-slam2-annotation_b200"), os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")]
@@ -9,11 +9,13 @@ import numpy as np, orbb200, pyoracle
 from synth import synth
 ncases = int(sys.argv[1]) if len(sys.argv) > 1 else 60
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 7)
+MAXW = int(sys.argv[3]) if len(sys.argv) > 3 else 1300; MAXH = int(sys.argv[4]) if len(sys.argv) > 4 else 800
+NFMAX = int(sys.argv[5]) if len(sys.argv) > 5 else 2500
 bad = 0
 for case in range(ncases):
-    w = int(rng.integers(90, 1301)); h = int(rng.integers(70, 801))
+    w = int(rng.integers(90, MAXW + 1)); h = int(rng.integers(70, MAXH + 1))
     nl = int(rng.integers(1, 11)); sf = float(np.float32(rng.uniform(1.05, 1.4)))
-    ini = int(rng.integers(1, 60)); mn = int(rng.integers(0, ini + 1)); nf = int(rng.integers(20, 2500))
+    ini = int(rng.integers(1, 60)); mn = int(rng.integers(0, ini + 1)); nf = int(rng.integers(20, NFMAX))
     while nl > 1 and min(w, h) / sf ** (nl - 1) < 40:
         nl -= 1
     seed = int(rng.integers(0, 1 << 30))
